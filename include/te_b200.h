@@ -1,0 +1,149 @@
+/* te_b200.h — C ABI of libte_b200.so: the sm_100a kernels behind torcheval_b200.
+ *
+ * This is the drop-in boundary for torcheval's ranking & counting metric hot path.  The
+ * reference (Connor-Guo/torcheval 0.0.6) is pure Python over ATen ops, so there is no native
+ * FFI to bind to: each entry point below replaces the ATen op sequence of the cited reference
+ * function (paths relative to the reference tree, torcheval/metrics/...).  INTEGRATION.md shows
+ * the ctypes stub a maintainer of the reference would add at each call site.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every pointer is DEVICE memory of the current CUDA device
+ *     unless stated otherwise; `stream` is a cudaStream_t passed as void* (NULL = default);
+ *   - calls only enqueue work on `stream`; nothing synchronises, nothing is allocated or freed:
+ *     the caller asks te_*_scratch_bytes() and passes a scratch buffer (256-byte aligned);
+ *   - return value: 0 = TE_OK; negative = TE_ERR_* (argument rejected, nothing enqueued);
+ *     positive = the cudaError_t reported by the runtime;
+ *   - counters are int64 and ACCUMULATE (+=) so that a metric state can be updated in place.
+ */
+#ifndef TE_B200_H_
+#define TE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TE_B200_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define TE_API __attribute__((visibility("default")))
+#else
+#define TE_API
+#endif
+
+enum {
+  TE_OK = 0,
+  TE_ERR_INVALID_ARGUMENT = -1,
+  TE_ERR_SCRATCH_TOO_SMALL = -2,
+  TE_ERR_UNSUPPORTED = -3
+};
+
+/* ABI version of the loaded library (TE_B200_ABI_VERSION at build time). */
+TE_API int te_abi_version(void);
+/* Static description of a status code returned by any entry point. */
+TE_API const char* te_status_string(int status);
+
+/* ------------------------------------------------------------------------------------------
+ * K4  confusion-matrix counting
+ * replaces functional/classification/confusion_matrix.py:219-234 (`_update`: vstack +
+ * sparse_coo_tensor(...).to_dense()) and the torch.max range checks of :271-282.
+ * ------------------------------------------------------------------------------------------ */
+enum {
+  TE_CM_AUTO = 0,      /* pick by num_classes */
+  TE_CM_GLOBAL64 = 1,  /* RED.ADD.64 straight into `cm` (L2 resident)            */
+  TE_CM_GLOBAL32 = 2,  /* RED.ADD.32 into scratch bins, folded into `cm`         */
+  TE_CM_SMEM_REPL = 3, /* per-CTA smem bins, replicated per lane (tiny C)        */
+  TE_CM_SMEM = 4       /* per-CTA smem bins (C*C*4 bytes must fit in smem)       */
+};
+
+TE_API size_t te_cm_scratch_bytes(int32_t num_classes, int32_t variant);
+
+/* cm[target[i] * C + pred[i]] += 1 for i < n.
+ * range[4] is overwritten with {min_pred, max_pred, min_target, max_target} taken over the
+ * OUT-OF-RANGE entries only (untouched sentinels INT64_MAX / INT64_MIN mean "all in range");
+ * out-of-range samples are not counted.  The host raises the reference's ValueError
+ * (confusion_matrix.py:271-282) from these four values. */
+TE_API int te_cm_update(const int64_t* pred, const int64_t* target, int64_t n, int32_t num_classes,
+                 int64_t* cm, int64_t* range, void* scratch, size_t scratch_bytes,
+                 int32_t variant, void* stream);
+
+/* Same with pred = argmax(logits[i, :]) (first maximal index, NaN counts as maximal —
+ * torch.argmax, confusion_matrix.py:225-226).  logits is (n, num_classes) float32 with row
+ * stride `ld` elements. */
+TE_API int te_cm_update_logits(const float* logits, int64_t ld, const int64_t* target, int64_t n,
+                        int32_t num_classes, int64_t* cm, int64_t* range, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K3  binned (thresholded) counting
+ * replaces functional/classification/binned_precision_recall_curve.py:84-110 (`_update`:
+ * searchsorted + histc + flip-cumsum-flip) and functional/classification/binned_auroc.py:117-125
+ * (the (T, tasks, N) boolean formulation), which count the same thing.
+ * ------------------------------------------------------------------------------------------ */
+TE_API size_t te_binned_scratch_bytes(int32_t num_thresholds);
+
+/* hist[task][bucket][label] += 1 with bucket = #{j : threshold[j] <= x} in [0, T] and
+ * label = (target != 0); hist is int64 [num_tasks][T + 1][2].  `threshold` is float32, sorted
+ * ascending (binned_auroc.py:78-82).  x/target rows of task k start at k * *_task_stride
+ * elements.  NaN scores fall in bucket 0 (counted at no threshold). */
+TE_API int te_binned_hist_update(const float* x, int64_t x_task_stride, const int64_t* target,
+                          int64_t target_task_stride, int64_t n, int32_t num_tasks,
+                          const float* threshold, int32_t num_thresholds, int64_t* hist,
+                          void* scratch, size_t scratch_bytes, void* stream);
+
+/* Suffix sums: num_tp[task][j] = #{label 1, x >= threshold[j]}, num_fp likewise for label 0,
+ * num_fn = positives - num_tp (binned_precision_recall_curve.py:102-110).  num_fn may be NULL.
+ * Outputs are overwritten. */
+TE_API int te_binned_counts(const int64_t* hist, int32_t num_thresholds, int32_t num_tasks,
+                     int64_t* num_tp, int64_t* num_fp, int64_t* num_fn, void* stream);
+
+enum { TE_BINNED_AUROC = 0, TE_BINNED_AUPRC = 1 };
+/* out[task] (float64) = trapezoid AUROC over the thresholds (binned_auroc.py:120-136; 0.5 when
+ * TP*FP == 0) or step-integrated AUPRC (binned_precision_recall_curve.py:113-129 +
+ * functional/tensor_utils.py:12-16; NaN -> 0 as binned_auprc.py:110). */
+TE_API int te_binned_integrate(const int64_t* num_tp, const int64_t* num_fp, const int64_t* num_fn,
+                        int32_t num_thresholds, int32_t num_tasks, int32_t mode, double* out,
+                        void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K1  exact binary AUROC / AUPRC (sort + fused scan / tie dedup / integrate)
+ * replaces functional/classification/auroc.py:115-152 (`_binary_auroc_compute_jit`) and
+ * functional/classification/precision_recall_curve.py:208-231 (`_compute_for_each_class`) +
+ * functional/tensor_utils.py:12-16 (`_riemann_integral`).
+ * ------------------------------------------------------------------------------------------ */
+enum { TE_DTYPE_I64 = 0, TE_DTYPE_I32 = 1, TE_DTYPE_U8 = 2, TE_DTYPE_F32 = 3, TE_DTYPE_F64 = 4 };
+
+/* Conditions the packed path cannot represent; reported in out[4], the caller then uses the
+ * general entry point instead. */
+enum {
+  TE_RANK_FLAG_BAD_LABEL = 1,      /* a target is not exactly 0 or 1 (soft labels)   */
+  TE_RANK_FLAG_NEGATIVE_SCORE = 2  /* a score has its sign bit set (other than -0.0) */
+};
+
+TE_API size_t te_binary_rank_scratch_bytes(int64_t n);
+
+/* Unweighted binary AUROC of n float32 scores against 0/1 targets of `target_dtype`.
+ * out (float64[8], device): [0] AUROC (0.5 when there are no positives or no negatives,
+ * auroc.py:146-151)  [1] #positives  [2] #negatives  [3] 2*U (exact integer, as double)
+ * [4] TE_RANK_FLAG_* (non-zero: [0..3] are not valid).  n <= 2^31 - 1. */
+TE_API int te_binary_auroc(const float* score, const void* target, int32_t target_dtype, int64_t n,
+                           double* out, void* scratch, size_t scratch_bytes, void* stream);
+
+/* Same contract for AUPRC (average precision, step integration): out[0] = AP, -0.0 when there
+ * are no positives (precision_recall_curve.py:227-229); out[3] = sum of per-positive precisions.
+ * A target counts as positive iff it equals 1. */
+TE_API int te_binary_auprc(const float* score, const void* target, int32_t target_dtype, int64_t n,
+                           double* out, void* scratch, size_t scratch_bytes, void* stream);
+
+/* The sort on its own: ascending, stable, 32-bit keys with an optional 32-bit payload
+ * (vals_in/vals_out both NULL or both set).  Replaces torch.sort at auroc.py:121. */
+TE_API size_t te_sort_u32_scratch_bytes(int64_t n, int32_t with_values);
+TE_API int te_sort_u32(const uint32_t* keys_in, uint32_t* keys_out, const uint32_t* vals_in,
+                       uint32_t* vals_out, int64_t n, void* scratch, size_t scratch_bytes,
+                       void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TE_B200_H_ */

@@ -1,0 +1,193 @@
+"""Generate tests/golden/reference_vectors.npz by RUNNING THE REFERENCE (torcheval 0.0.6).
+
+Run in the build container only (needs /root/reference, which does not exist on the GPU box):
+
+    PYTHONPATH=/root/reference python oracle/gen_golden.py
+
+Every case stores its inputs and the reference's outputs, so tests can check both the oracle
+(oracle/te_oracle.c) and the CUDA path against the reference without importing it.
+"""
+from __future__ import annotations
+
+import sys
+from pathlib import Path
+
+import numpy as np
+import torch
+
+sys.path.insert(0, "/root/reference")
+from torcheval.metrics import functional as F  # noqa: E402
+from torcheval.metrics.functional.classification.binned_precision_recall_curve import (  # noqa: E402
+    _binary_binned_precision_recall_curve_update,
+    _multiclass_binned_precision_recall_curve_update,
+    _multilabel_binned_precision_recall_curve_update,
+)
+
+OUT = Path(__file__).resolve().parent.parent / "tests" / "golden" / "reference_vectors.npz"
+store: dict[str, np.ndarray] = {}
+
+
+def put(case: str, **arrays) -> None:
+    for k, v in arrays.items():
+        if isinstance(v, torch.Tensor):
+            v = v.detach().cpu().numpy()
+        store[f"{case}/{k}"] = np.asarray(v)
+
+
+def main() -> None:
+    g = torch.Generator().manual_seed(20261106)
+
+    def rand(*shape):
+        return torch.rand(*shape, generator=g)
+
+    def randint(lo, hi, shape):
+        return torch.randint(lo, hi, shape, generator=g)
+
+    # ---------------- exact binary AUROC / AUPRC -------------------------------------------
+    n = 3000
+    binary_cases = {
+        "uniform": (rand(n), randint(0, 2, (n,))),
+        "ties64": (randint(0, 64, (n,)).float() / 64, randint(0, 2, (n,))),
+        "ties4": (randint(0, 4, (n,)).float() / 4, randint(0, 2, (n,))),
+        "constant": (torch.full((n,), 0.25), randint(0, 2, (n,))),
+        "all_pos": (rand(n), torch.ones(n, dtype=torch.int64)),
+        "all_neg": (rand(n), torch.zeros(n, dtype=torch.int64)),
+        "signed_zero": (
+            torch.where(randint(0, 2, (n,)) == 0, torch.tensor(0.0), torch.tensor(-0.0))
+            * (randint(0, 3, (n,)) == 0)
+            + rand(n) * (randint(0, 2, (n,)) == 0),
+            randint(0, 2, (n,)),
+        ),
+        "logits": (torch.randn(n, generator=g) * 3, randint(0, 2, (n,))),
+        "skewed": (rand(n), (rand(n) < 0.01).long()),
+        "int_scores": (randint(0, 2, (n,)).float(), randint(0, 2, (n,))),
+        "tiny": (torch.tensor([0.1, 0.5, 0.7, 0.8]), torch.tensor([1, 0, 1, 1])),
+        "single": (torch.tensor([0.3]), torch.tensor([1])),
+        "n8193": (rand(8193), randint(0, 2, (8193,))),
+    }
+    for name, (x, y) in binary_cases.items():
+        x = x.float()
+        # class path of the reference = float64 weights (classification/auroc.py:112-113)
+        auroc64 = F.binary_auroc(x, y, weight=torch.ones_like(x, dtype=torch.float64))
+        auroc32 = F.binary_auroc(x, y)
+        auprc = F.binary_auprc(x, y)
+        put(f"binary/{name}", x=x, y=y, auroc_f64=auroc64, auroc_fn=auroc32, auprc=auprc)
+
+    # weighted + soft labels + multi-task
+    x, y = rand(n), randint(0, 2, (n,))
+    w = rand(n).double() * 3
+    put("binary_weighted/w", x=x, y=y, w=w, auroc=F.binary_auroc(x, y, weight=w))
+    xs = randint(0, 32, (n,)).float() / 32
+    put("binary_weighted/w_ties", x=xs, y=y, w=w, auroc=F.binary_auroc(xs, y, weight=w))
+    soft = rand(n).double()
+    put("binary_weighted/soft", x=xs, y=soft, w=w, auroc=F.binary_auroc(xs, soft, weight=w))
+    xt, yt = rand(3, 1000), randint(0, 2, (3, 1000))
+    put(
+        "binary_multitask/t3",
+        x=xt,
+        y=yt,
+        auroc=F.binary_auroc(xt, yt, num_tasks=3, weight=torch.ones_like(xt, dtype=torch.float64)),
+        auprc=F.binary_auprc(xt, yt, num_tasks=3),
+    )
+
+    # ---------------- multiclass / multilabel ------------------------------------------------
+    for name, (nn, c) in {"c5": (400, 5), "c17": (257, 17)}.items():
+        inp = rand(nn, c)
+        tgt = randint(0, c, (nn,))
+        if name == "c17":
+            tgt[tgt == 3] = 4  # class 3 never occurs
+            inp = (inp * 8).floor() / 8  # ties
+        put(
+            f"multiclass/{name}",
+            x=inp,
+            y=tgt,
+            auroc=F.multiclass_auroc(inp, tgt, num_classes=c, average=None),
+            auroc_macro=F.multiclass_auroc(inp, tgt, num_classes=c),
+            auprc=F.multiclass_auprc(inp, tgt, num_classes=c, average=None),
+            auprc_macro=F.multiclass_auprc(inp, tgt, num_classes=c),
+        )
+        ml = randint(0, 2, (nn, c))
+        if name == "c17":
+            ml[:, 2] = 0
+        put(
+            f"multilabel/{name}",
+            x=inp,
+            y=ml,
+            auprc=F.multilabel_auprc(inp, ml, num_labels=c, average=None),
+            auprc_macro=F.multilabel_auprc(inp, ml, num_labels=c),
+        )
+
+    # ---------------- binned -----------------------------------------------------------------
+    thr_sets = {
+        "lin5": torch.linspace(0, 1, 5),
+        "lin200": torch.linspace(0, 1, 200),
+        "lin10000": torch.linspace(0, 1, 10000),
+        "custom": torch.tensor([0.0, 0.1, 0.1, 0.35, 0.5, 0.77, 0.9, 1.0]),
+        "inner": torch.tensor([0.2, 0.4, 0.6]),
+    }
+    xb = torch.cat([rand(1500), randint(0, 11, (500,)).float() / 10, torch.tensor([0.0, 1.0, 1.0, 0.0])])
+    yb = randint(0, 2, (xb.numel(),))
+    for tname, thr in thr_sets.items():
+        tp, fp, fn = _binary_binned_precision_recall_curve_update(xb, yb, thr)
+        rec = dict(x=xb, y=yb, thr=thr, tp=tp, fp=fp, fn=fn)
+        if thr.numel() <= 200:
+            auroc, _ = F.binary_binned_auroc(xb, yb, threshold=thr)
+            rec["auroc"] = auroc
+        if thr[0] == 0 and thr[-1] == 1:
+            auprc, _ = F.binary_binned_auprc(xb, yb, threshold=thr)
+            rec["auprc"] = auprc
+        put(f"binned/{tname}", **rec)
+    xb2, yb2 = rand(2, 700), randint(0, 2, (2, 700))
+    auroc, _ = F.binary_binned_auroc(xb2, yb2, num_tasks=2, threshold=50)
+    auprc, _ = F.binary_binned_auprc(xb2, yb2, num_tasks=2, threshold=50)
+    put("binned_multitask/t2", x=xb2, y=yb2, thr=torch.linspace(0, 1, 50), auroc=auroc, auprc=auprc)
+
+    # multiclass / multilabel binned PR counts (the "memory" formulation is the histogram one)
+    inp = rand(300, 6)
+    tgt = randint(0, 6, (300,))
+    thr = torch.linspace(0, 1, 33)
+    tp, fp, fn = _multiclass_binned_precision_recall_curve_update(inp, tgt, 6, thr, "memory")
+    tpv, fpv, fnv = _multiclass_binned_precision_recall_curve_update(inp, tgt, 6, thr, "vectorized")
+    assert torch.equal(tp, tpv) and torch.equal(fp, fpv) and torch.equal(fn, fnv)
+    auprc, _ = F.multiclass_binned_auprc(inp, tgt, num_classes=6, threshold=thr, average=None)
+    put("binned_multiclass/c6", x=inp, y=tgt, thr=thr, tp=tp, fp=fp, fn=fn, auprc=auprc)
+    ml = randint(0, 2, (300, 6))
+    tp, fp, fn = _multilabel_binned_precision_recall_curve_update(inp, ml, 6, thr, "memory")
+    auprc, _ = F.multilabel_binned_auprc(inp, ml, num_labels=6, threshold=thr, average=None)
+    put("binned_multilabel/l6", x=inp, y=ml, thr=thr, tp=tp, fp=fp, fn=fn, auprc=auprc)
+
+    # ---------------- confusion matrix / accuracy / f1 ------------------------------------------
+    for name, (nn, c) in {"c10": (5000, 10), "c3": (64, 3), "c100": (20000, 100)}.items():
+        p, t = randint(0, c, (nn,)), randint(0, c, (nn,))
+        put(f"cm/{name}", pred=p, target=t, cm=F.multiclass_confusion_matrix(p, t, num_classes=c))
+    logits = torch.randn(1000, 7, generator=g)
+    logits[::10, 2] = logits[::10].max(dim=1).values  # ties: first max wins
+    t = randint(0, 7, (1000,))
+    put("cm_logits/c7", logits=logits, target=t, cm=F.multiclass_confusion_matrix(logits, t, num_classes=7))
+    logits = torch.randn(300, 130, generator=g)
+    t = randint(0, 130, (300,))
+    put("cm_logits/c130", logits=logits, target=t, cm=F.multiclass_confusion_matrix(logits, t, num_classes=130))
+    xb3, t = rand(999), randint(0, 2, (999,))
+    put("cm_binary/t05", x=xb3, target=t, cm=F.binary_confusion_matrix(xb3, t, threshold=0.5))
+
+    p, t = randint(0, 5, (777,)), randint(0, 5, (777,))
+    put(
+        "acc_f1/c5",
+        pred=p,
+        target=t,
+        acc_micro=F.multiclass_accuracy(p, t),
+        acc_macro=F.multiclass_accuracy(p, t, average="macro", num_classes=5),
+        acc_none=F.multiclass_accuracy(p, t, average=None, num_classes=5),
+        f1_micro=F.multiclass_f1_score(p, t),
+        f1_macro=F.multiclass_f1_score(p, t, num_classes=5, average="macro"),
+        f1_weighted=F.multiclass_f1_score(p, t, num_classes=5, average="weighted"),
+        f1_none=F.multiclass_f1_score(p, t, num_classes=5, average=None),
+    )
+
+    OUT.parent.mkdir(parents=True, exist_ok=True)
+    np.savez_compressed(OUT, **store)
+    print(f"wrote {OUT} ({OUT.stat().st_size / 1024:.0f} KiB, {len(store)} arrays)")
+
+
+if __name__ == "__main__":
+    main()

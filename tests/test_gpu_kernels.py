@@ -1,0 +1,356 @@
+"""Parity of the CUDA kernels (through the C ABI, via torcheval_b200.ops) against the oracle and
+the committed reference fixtures.  Counts are bit-exact; AUROC within 1e-6 relative (fp64),
+values the reference itself computes in fp32 within 1e-4."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+RTOL64 = 1e-6
+RTOL32 = 1e-4
+
+
+@pytest.fixture(scope="module")
+def ops():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    from torcheval_b200 import ops as _ops
+
+    return _ops
+
+
+def dev(a, dtype=None):
+    t = torch.as_tensor(np.ascontiguousarray(a))
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.cuda()
+
+
+def close(a, b, rtol):
+    np.testing.assert_allclose(np.float64(a), np.float64(b), rtol=rtol, atol=rtol * 1e-3)
+
+
+# =============================================================================== K4
+def run_cm(ops, pred, target, C, variant=0, cm=None):
+    if cm is None:
+        cm = torch.zeros((C, C), dtype=torch.int64, device="cuda")
+    rng = ops.cm_update_(cm, pred, target, C, variant)
+    torch.cuda.synchronize()
+    return cm.cpu().numpy(), rng.cpu().numpy()
+
+
+def cm_variants(C):
+    v = [0, 1, 2]
+    if C * C * 128 <= 200 * 1024:
+        v.append(3)
+    if C * C * 4 <= 200 * 1024:
+        v.append(4)
+    return v
+
+
+def test_cm_golden_all_variants(ops, golden):
+    for name in golden.cases("cm"):
+        c = golden.case(f"cm/{name}")
+        C = c["cm"].shape[0]
+        for v in cm_variants(C):
+            cm, rng = run_cm(ops, dev(c["pred"]), dev(c["target"]), C, v)
+            np.testing.assert_array_equal(cm, c["cm"], err_msg=f"{name} variant {v}")
+            assert rng[0] == np.iinfo(np.int64).max and rng[1] == np.iinfo(np.int64).min
+
+
+@pytest.mark.parametrize("C,n", [(2, 100003), (10, 1 << 20), (16, 999), (100, 300001), (1000, (1 << 21) + 3)])
+def test_cm_random_vs_oracle(ops, C, n):
+    rs = np.random.default_rng(C * 7 + n)
+    p = rs.integers(0, C, n)
+    t = rs.integers(0, C, n)
+    want, bad, _ = oracle.confusion_matrix(p, t, C)
+    assert not bad
+    for v in cm_variants(C):
+        cm, _ = run_cm(ops, dev(p), dev(t), C, v)
+        np.testing.assert_array_equal(cm, want, err_msg=f"variant {v}")
+
+
+def test_cm_skewed_diagonal(ops):
+    rs = np.random.default_rng(3)
+    n, C = 1 << 20, 1000
+    t = rs.integers(0, C, n)
+    p = np.where(rs.random(n) < 0.9, t, rs.integers(0, C, n))
+    p[: n // 4] = 7
+    t[: n // 4] = 7  # one very hot bin
+    want, _, _ = oracle.confusion_matrix(p, t, C)
+    for v in (1, 2):
+        cm, _ = run_cm(ops, dev(p), dev(t), C, v)
+        np.testing.assert_array_equal(cm, want)
+
+
+def test_cm_unaligned_views_and_accumulate(ops):
+    rs = np.random.default_rng(11)
+    C, n = 37, 50001
+    p, t = rs.integers(0, C, n), rs.integers(0, C, n)
+    P, T = dev(p), dev(t)
+    cm = torch.zeros((C, C), dtype=torch.int64, device="cuda")
+    ops.cm_update_(cm, P[1:], T[1:], C)       # 8-byte aligned only -> scalar path
+    ops.cm_update_(cm, P[:1], T[:1], C)       # accumulates
+    ops.cm_update_(cm, P, T, C)
+    torch.cuda.synchronize()
+    want, _, _ = oracle.confusion_matrix(p, t, C)
+    np.testing.assert_array_equal(cm.cpu().numpy(), 2 * want)
+
+
+def test_cm_out_of_range_report(ops):
+    C = 5
+    p = np.array([0, 1, 2, 3, 4, 9, 1, -3, 2], dtype=np.int64)
+    t = np.array([0, 1, 2, 3, 4, 1, 7, 2, -1], dtype=np.int64)
+    for v in cm_variants(C):
+        cm, rng = run_cm(ops, dev(p), dev(t), C, v)
+        assert list(rng) == [-3, 9, -1, 7]
+        np.testing.assert_array_equal(cm, np.eye(C, dtype=np.int64))
+    want, bad, orng = oracle.confusion_matrix(p, t, C)
+    assert bad and orng[1] == 9 and orng[3] == 7
+    np.testing.assert_array_equal(want, np.eye(C, dtype=np.int64))
+
+
+def test_cm_empty(ops):
+    cm, rng = run_cm(ops, torch.zeros(0, dtype=torch.int64, device="cuda"), torch.zeros(0, dtype=torch.int64, device="cuda"), 4)
+    assert cm.sum() == 0
+
+
+def test_cm_logits(ops, golden):
+    for name in golden.cases("cm_logits"):
+        c = golden.case(f"cm_logits/{name}")
+        C = c["cm"].shape[0]
+        cm = torch.zeros((C, C), dtype=torch.int64, device="cuda")
+        ops.cm_update_logits_(cm, dev(c["logits"]), dev(c["target"]), C)
+        np.testing.assert_array_equal(cm.cpu().numpy(), c["cm"])
+    rs = np.random.default_rng(5)
+    for n, C in [(5000, 1000), (3001, 33), (777, 64), (100, 65)]:
+        lg = rs.standard_normal((n, C)).astype(np.float32)
+        lg[::7, C // 2] = lg[::7].max(axis=1)  # ties -> first index
+        lg[3, 1] = np.nan
+        t = rs.integers(0, C, n)
+        want, _, _ = oracle.confusion_matrix(oracle.argmax_rows(lg), t, C)
+        cm = torch.zeros((C, C), dtype=torch.int64, device="cuda")
+        ops.cm_update_logits_(cm, dev(lg), dev(t), C)
+        np.testing.assert_array_equal(cm.cpu().numpy(), want)
+        np.testing.assert_array_equal(oracle.argmax_rows(lg), torch.argmax(torch.as_tensor(lg), dim=1).numpy())
+
+
+# =============================================================================== K3
+def run_binned(ops, x, y, thr):
+    x, y, thr = dev(x, torch.float32), dev(y, torch.int64), dev(thr, torch.float32)
+    tasks = 1 if x.dim() == 1 else x.shape[0]
+    T = thr.numel()
+    hist = torch.zeros((tasks, T + 1, 2), dtype=torch.int64, device="cuda")
+    ops.binned_hist_update_(hist, x, y, thr)
+    tp, fp, fn = ops.binned_counts(hist, T)
+    auroc = ops.binned_integrate(tp, fp, fn, 0)
+    auprc = ops.binned_integrate(tp, fp, fn, 1)
+    torch.cuda.synchronize()
+    return [a.cpu().numpy() for a in (hist, tp, fp, fn, auroc, auprc)]
+
+
+def test_binned_golden(ops, golden):
+    for name in golden.cases("binned"):
+        c = golden.case(f"binned/{name}")
+        hist, tp, fp, fn, auroc, auprc = run_binned(ops, c["x"], c["y"], c["thr"])
+        np.testing.assert_array_equal(hist[0], oracle.binned_hist(c["x"], c["y"], c["thr"]))
+        np.testing.assert_array_equal(tp[0], c["tp"], err_msg=name)
+        np.testing.assert_array_equal(fp[0], c["fp"])
+        np.testing.assert_array_equal(fn[0], c["fn"])
+        if "auroc" in c:
+            close(auroc[0], c["auroc"][0], RTOL64)
+        if "auprc" in c:
+            close(auprc[0], c["auprc"], RTOL32)
+    c = golden.case("binned_multitask/t2")
+    hist, tp, fp, fn, auroc, auprc = run_binned(ops, c["x"], c["y"], c["thr"])
+    close(auroc, c["auroc"], RTOL64)
+    close(auprc, c["auprc"], RTOL32)
+
+
+@pytest.mark.parametrize("T", [1, 2, 200, 10000, 14000, 30000])
+def test_binned_random_vs_oracle(ops, T):
+    rs = np.random.default_rng(T)
+    n = (1 << 20) + 1
+    x = rs.random(n, dtype=np.float32)
+    x[:1000] = rs.integers(0, T, 1000) / max(T - 1, 1)  # exactly on thresholds (in fp32 or not)
+    x[1000:1010] = [-0.5, 1.5, np.inf, -np.inf, 0.0, 1.0, -0.0, np.nan, 1e-45, 0.99999994]
+    y = rs.integers(0, 2, n)
+    thr = np.linspace(0, 1, T, dtype=np.float32) if T > 1 else np.array([0.5], dtype=np.float32)
+    hist, tp, fp, fn, auroc, auprc = run_binned(ops, x, y, thr)
+    # NaN: bucket 0 here, bucket T for searchsorted — drop it from the comparison
+    keep = ~np.isnan(x)
+    want = oracle.binned_hist(x[keep], y[keep], thr)
+    want[0, int(y[1007] != 0)] += 1
+    np.testing.assert_array_equal(hist[0], want)
+    wtp, wfp, wfn = oracle.binned_counts(want)
+    np.testing.assert_array_equal(tp[0], wtp)
+    np.testing.assert_array_equal(fp[0], wfp)
+    np.testing.assert_array_equal(fn[0], wfn)
+    close(auroc[0], oracle.binned_auroc_from_counts(wtp, wfp), 1e-12)
+    if T > 1:
+        close(auprc[0], oracle.binned_auprc_from_counts(wtp, wfp, wfn), 1e-12)
+
+
+def test_binned_irregular_thresholds_and_alignment(ops):
+    rs = np.random.default_rng(9)
+    n = 200003
+    x = rs.random(n, dtype=np.float32)
+    y = rs.integers(0, 2, n)
+    thr = np.sort(np.concatenate([[0.0], np.full(3000, 0.5), 0.5 + rs.random(500) * 1e-4, rs.random(300), [0.25] * 7, [1.0]])).astype(np.float32)
+    x[:5000] = rs.choice(thr, 5000)
+    want = oracle.binned_hist(x, y, thr)
+    hist = run_binned(ops, x, y, thr)[0]
+    np.testing.assert_array_equal(hist[0], want)
+    # unaligned view -> scalar path
+    X, Y, TH = dev(x), dev(y), dev(thr)
+    h2 = torch.zeros((1, thr.size + 1, 2), dtype=torch.int64, device="cuda")
+    ops.binned_hist_update_(h2, X[1:], Y[1:], TH)
+    ops.binned_hist_update_(h2, X[:1], Y[:1], TH)
+    np.testing.assert_array_equal(h2.cpu().numpy()[0], want)
+
+
+def test_binned_multitask_random(ops):
+    rs = np.random.default_rng(10)
+    K, n, T = 5, 40004, 100
+    x = rs.random((K, n), dtype=np.float32)
+    y = rs.integers(0, 2, (K, n))
+    thr = np.linspace(0, 1, T, dtype=np.float32)
+    hist = run_binned(ops, x, y, thr)[0]
+    for k in range(K):
+        np.testing.assert_array_equal(hist[k], oracle.binned_hist(x[k], y[k], thr))
+
+
+# =============================================================================== K1: the sort
+@pytest.mark.parametrize("n", [0, 1, 5, 511, 8191, 8192, 8193, 100000, (1 << 20) + 77])
+def test_sort_u32_keys(ops, n):
+    rs = np.random.default_rng(n + 1)
+    k = rs.integers(0, 1 << 32, n, dtype=np.uint64).astype(np.uint32)
+    out, _ = ops.sort_u32(dev(k.view(np.int32)))
+    np.testing.assert_array_equal(out.cpu().numpy().view(np.uint32), np.sort(k))
+
+
+@pytest.mark.parametrize("n,bits", [(8193, 32), (300001, 32), (300001, 6), ((1 << 21) + 5, 12)])
+def test_sort_u32_pairs_stable(ops, n, bits):
+    rs = np.random.default_rng(n + bits)
+    k = rs.integers(0, 1 << bits, n, dtype=np.uint64).astype(np.uint32)
+    if bits == 6:
+        k <<= 13  # ties on a middle digit only
+    v = np.arange(n, dtype=np.int32)
+    ok, ov = ops.sort_u32(dev(k.view(np.int32)), dev(v))
+    order = np.argsort(k, kind="stable")
+    np.testing.assert_array_equal(ok.cpu().numpy().view(np.uint32), k[order])
+    np.testing.assert_array_equal(ov.cpu().numpy(), order.astype(np.int32))
+
+
+def test_sort_u32_skewed_digits(ops):
+    # float-like keys: half of them share the top byte (the exponent) -> long look-back chains
+    rs = np.random.default_rng(2)
+    n = (1 << 20) + 9
+    k = (rs.random(n, dtype=np.float32).view(np.uint32) << 1) | rs.integers(0, 2, n).astype(np.uint32)
+    out, _ = ops.sort_u32(dev(k.view(np.int32)))
+    np.testing.assert_array_equal(out.cpu().numpy().view(np.uint32), np.sort(k))
+    k[:] = 0xDEADBEEF
+    out, _ = ops.sort_u32(dev(k.view(np.int32)))
+    assert (out.cpu().numpy().view(np.uint32) == 0xDEADBEEF).all()
+
+
+# =============================================================================== K1: AUROC / AUPRC
+def run_rank(ops, x, y, ydtype=torch.int64):
+    X, Y = dev(x, torch.float32), dev(y, ydtype)
+    a = ops.binary_auroc_packed(X, Y).cpu().numpy()
+    p = ops.binary_auprc_packed(X, Y).cpu().numpy()
+    return a, p
+
+
+def test_rank_golden(ops, golden):
+    for name in golden.cases("binary"):
+        c = golden.case(f"binary/{name}")
+        a, p = run_rank(ops, c["x"], c["y"])
+        if (np.signbit(c["x"]) & (c["x"] != 0)).any():
+            assert int(a[4]) & 2 and int(p[4]) & 2, name  # negative scores are reported, not mis-sorted
+            continue
+        assert a[4] == 0 and p[4] == 0, name
+        close(a[0], c["auroc_f64"], RTOL64)
+        close(a[0], c["auroc_fn"], RTOL32)
+        close(p[0], c["auprc"], RTOL32)
+        assert a[1] == c["y"].sum() and a[2] == (1 - c["y"]).sum()
+        if c["y"].sum() == 0:
+            assert np.signbit(p[0])
+        # exact integer statistic against the oracle
+        v, tp, fp = oracle.binary_auroc(c["x"], c["y"])
+        if tp * fp > 0:
+            assert a[3] == round(2 * v * tp * fp), name
+
+
+@pytest.mark.parametrize(
+    "n,kind",
+    [(4097, "uniform"), (8192 * 3, "uniform"), ((1 << 22) + 5, "uniform"), (1 << 21, "ties4096"),
+     (1 << 20, "ties3"), (300000, "constant"), (1 << 20, "skew"), (70001, "allpos"), (70001, "allneg")],
+)
+def test_rank_random_vs_oracle(ops, n, kind):
+    rs = np.random.default_rng(n % 1000 + len(kind))
+    y = rs.integers(0, 2, n)
+    if kind == "uniform":
+        x = rs.random(n, dtype=np.float32)
+    elif kind == "ties4096":
+        x = (rs.integers(0, 4096, n) / 4096).astype(np.float32)
+    elif kind == "ties3":
+        x = (rs.integers(0, 3, n) / 2).astype(np.float32)
+    elif kind == "constant":
+        x = np.full(n, 0.7, dtype=np.float32)
+    elif kind == "skew":
+        x = rs.random(n, dtype=np.float32)
+        y = (rs.random(n) < 0.01).astype(np.int64)
+    elif kind == "allpos":
+        x, y = rs.random(n, dtype=np.float32), np.ones(n, dtype=np.int64)
+    else:
+        x, y = rs.random(n, dtype=np.float32), np.zeros(n, dtype=np.int64)
+    a, p = run_rank(ops, x, y)
+    assert a[4] == 0
+    v, tp, fp = oracle.binary_auroc(x, y)
+    close(a[0], v, RTOL64)
+    assert (a[1], a[2]) == (tp, fp)
+    close(p[0], oracle.binary_auprc(x, y), RTOL64)
+    a2, p2 = run_rank(ops, x, y)
+    assert a2[0] == a[0] and a2[3] == a[3] and p2[0] == p[0]  # run-to-run bit identical
+
+
+def test_rank_target_dtypes_and_flags(ops):
+    rs = np.random.default_rng(0)
+    n = 50001
+    x = rs.random(n, dtype=np.float32)
+    y = rs.integers(0, 2, n)
+    ref = oracle.binary_auroc(x, y)[0]
+    for dt in (torch.int64, torch.int32, torch.uint8, torch.bool, torch.float32, torch.float64):
+        a, _ = run_rank(ops, x, y, dt)
+        assert a[4] == 0
+        close(a[0], ref, 1e-12)
+    y2 = y.copy()
+    y2[17] = 2
+    assert int(run_rank(ops, x, y2)[0][4]) & 1
+    assert int(run_rank(ops, x, y.astype(np.float32) * 0.5, torch.float32)[0][4]) & 1
+    x2 = x.copy()
+    x2[5] = -1e-30
+    assert int(run_rank(ops, x2, y)[0][4]) & 2
+    x2[5] = -0.0  # signed zero is fine and ties with +0.0
+    x2[6] = 0.0
+    a, _ = run_rank(ops, x2, y)
+    assert a[4] == 0
+    close(a[0], oracle.binary_auroc(x2, y)[0], 1e-12)
+
+
+def test_rank_large_closed_form(ops):
+    """Size-independent property at a size the sort-based oracle cannot afford: scores on a grid
+    of G levels -> AUROC in closed form from the (level, label) histogram."""
+    n, G = 1 << 26, 1 << 16
+    g = torch.Generator(device="cuda").manual_seed(7)
+    lev = torch.randint(0, G, (n,), device="cuda", generator=g)
+    y = (torch.rand(n, device="cuda", generator=g) < 0.3).long()
+    x = lev.float() / G
+    a = ops.binary_auroc_packed(x, y).cpu().numpy()
+    neg = torch.bincount(lev[y == 0], minlength=G).cpu().numpy()
+    pos = torch.bincount(lev[y == 1], minlength=G).cpu().numpy()
+    assert a[4] == 0 and a[1] == pos.sum() and a[2] == neg.sum()
+    close(a[0], oracle.auroc_from_level_hist(neg, pos), 1e-9)

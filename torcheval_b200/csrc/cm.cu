@@ -1,0 +1,368 @@
+// K4 — confusion-matrix counting: cm[target[i], pred[i]] += 1.
+//
+// Replaces the reference's sparse_coo_tensor(...).to_dense() coalesce
+// (torcheval/metrics/functional/classification/confusion_matrix.py:219-234) and the two
+// torch.max(...) range checks with their host syncs (:271-282) by one streaming pass:
+// 128-bit loads of the two int64 label streams, a fused range check, and either
+//   * a shared-memory privatised histogram (small C: bins live in smem, lane-replicated so
+//     that a warp never collides with itself), or
+//   * fire-and-forget RED.ADD into the L2-resident C*C matrix (large C: 10^6 bins at C=1000).
+// Algorithmic traffic: 16 B / sample.
+#include "common.cuh"
+
+namespace te {
+namespace {
+
+constexpr int kCmBlock = 256;
+
+struct RangeReport {
+  long long* range;  // {min_pred, max_pred, min_target, max_target} over OUT-OF-RANGE values only
+  __device__ __forceinline__ void bad(long long p, long long t, unsigned long long C) const {
+    if ((unsigned long long)p >= C) {
+      atomicMin(range + 0, p);
+      atomicMax(range + 1, p);
+    }
+    if ((unsigned long long)t >= C) {
+      atomicMin(range + 2, t);
+      atomicMax(range + 3, t);
+    }
+  }
+};
+
+__global__ void cm_init_range_kernel(long long* range) {
+  if (threadIdx.x == 0) {
+    range[0] = 0x7fffffffffffffffLL;
+    range[1] = (long long)0x8000000000000000ULL;
+    range[2] = 0x7fffffffffffffffLL;
+    range[3] = (long long)0x8000000000000000ULL;
+  }
+}
+
+// Sink policies: where one (target, pred) hit goes.
+template <typename BinT>
+struct GlobalSink {
+  BinT* bins;
+  __device__ __forceinline__ void add(uint32_t bin) const { atomicAdd(bins + bin, (BinT)1); }
+};
+template <int REPL>
+struct SmemSink {
+  uint32_t* sh;
+  unsigned lane;
+  __device__ __forceinline__ void add(uint32_t bin) const {
+    atomicAdd(sh + (size_t)bin * REPL + (REPL > 1 ? lane : 0u), 1u);
+  }
+};
+
+template <int VEC, int UNROLL, typename Sink>
+__device__ __forceinline__ void cm_stream(const long long* __restrict__ pred,
+                                          const long long* __restrict__ target, int64_t n,
+                                          uint32_t C, const Sink& sink, const RangeReport& rr) {
+  const int64_t nvec = n / VEC;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t first = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (int64_t base = first; base < nvec; base += stride * UNROLL) {
+    long long p[UNROLL][VEC], t[UNROLL][VEC];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const int64_t idx = base + (int64_t)u * stride;
+      if (idx < nvec) {
+        if (VEC == 2) {
+          int4 a = ld_stream_v4(pred + 2 * idx);
+          int4 b = ld_stream_v4(target + 2 * idx);
+          p[u][0] = ((long long)(uint32_t)a.y << 32) | (uint32_t)a.x;
+          p[u][VEC - 1] = ((long long)(uint32_t)a.w << 32) | (uint32_t)a.z;
+          t[u][0] = ((long long)(uint32_t)b.y << 32) | (uint32_t)b.x;
+          t[u][VEC - 1] = ((long long)(uint32_t)b.w << 32) | (uint32_t)b.z;
+        } else {
+          p[u][0] = __ldg(pred + idx);
+          t[u][0] = __ldg(target + idx);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const int64_t idx = base + (int64_t)u * stride;
+      if (idx < nvec) {
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) {
+          const unsigned long long pu = (unsigned long long)p[u][v];
+          const unsigned long long tu = (unsigned long long)t[u][v];
+          if (pu < C && tu < C)
+            sink.add((uint32_t)tu * C + (uint32_t)pu);
+          else
+            rr.bad(p[u][v], t[u][v], C);
+        }
+      }
+    }
+  }
+  // scalar tail (n % VEC elements)
+  if (VEC > 1 && first == 0) {
+    for (int64_t i = nvec * VEC; i < n; ++i) {
+      const long long pv = pred[i], tv = target[i];
+      if ((unsigned long long)pv < C && (unsigned long long)tv < C)
+        sink.add((uint32_t)tv * C + (uint32_t)pv);
+      else
+        rr.bad(pv, tv, C);
+    }
+  }
+}
+
+template <int VEC, typename BinT>
+__global__ void __launch_bounds__(kCmBlock)
+    cm_global_kernel(const long long* __restrict__ pred, const long long* __restrict__ target,
+                     int64_t n, uint32_t C, BinT* bins, long long* range) {
+  GlobalSink<BinT> sink{bins};
+  RangeReport rr{range};
+  cm_stream<VEC, 4>(pred, target, n, C, sink, rr);
+}
+
+template <int VEC, int REPL>
+__global__ void __launch_bounds__(kCmBlock)
+    cm_smem_kernel(const long long* __restrict__ pred, const long long* __restrict__ target,
+                   int64_t n, uint32_t C, unsigned long long* cm, long long* range) {
+  extern __shared__ uint32_t sh[];
+  const uint32_t nbins = C * C;
+  for (uint32_t i = threadIdx.x; i < nbins * REPL; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  SmemSink<REPL> sink{sh, lane_id()};
+  RangeReport rr{range};
+  cm_stream<VEC, 4>(pred, target, n, C, sink, rr);
+  __syncthreads();
+  for (uint32_t b = threadIdx.x; b < nbins; b += blockDim.x) {
+    uint32_t s = 0;
+#pragma unroll
+    for (int r = 0; r < REPL; ++r) s += sh[(size_t)b * REPL + ((r + threadIdx.x) & (REPL - 1))];
+    if (s) atomicAdd(cm + b, (unsigned long long)s);
+  }
+}
+
+__global__ void cm_fold32_kernel(const uint32_t* __restrict__ bins, unsigned long long* cm,
+                                 uint32_t nbins) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nbins; i += gridDim.x * blockDim.x)
+    cm[i] += bins[i];
+}
+
+// ---- logits (N, C) -> argmax -> count ---------------------------------------------------
+// torch.argmax semantics (confusion_matrix.py:225-226): first maximal index, NaN counts as max.
+struct Best {
+  float v;
+  int i;
+};
+__device__ __forceinline__ bool better(float av, int ai, float bv, int bi) {
+  const bool an = av != av, bn = bv != bv;
+  if (an || bn) return an && (!bn || ai < bi);
+  return av > bv || (av == bv && ai < bi);
+}
+
+// One warp per row; lanes stride over the columns (coalesced 128 B per instruction).
+template <typename BinT>
+__global__ void __launch_bounds__(kCmBlock)
+    cm_logits_warp_kernel(const float* __restrict__ logits, int64_t ld,
+                          const long long* __restrict__ target, int64_t n, uint32_t C, BinT* bins,
+                          long long* range) {
+  const unsigned lane = lane_id();
+  const int64_t warps = (int64_t)gridDim.x * (blockDim.x / kWarp);
+  RangeReport rr{range};
+  for (int64_t row = (int64_t)blockIdx.x * (blockDim.x / kWarp) + threadIdx.x / kWarp; row < n;
+       row += warps) {
+    const float* r = logits + row * ld;
+    float bv = 0.f;
+    int bi = -1;
+    for (uint32_t c = lane; c < C; c += kWarp) {
+      const float v = __ldg(r + c);
+      if (bi < 0 || better(v, (int)c, bv, bi)) {
+        bv = v;
+        bi = (int)c;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(kFull, bv, o);
+      const int oi = __shfl_xor_sync(kFull, bi, o);
+      if (oi >= 0 && (bi < 0 || better(ov, oi, bv, bi))) {
+        bv = ov;
+        bi = oi;
+      }
+    }
+    if (lane == 0) {
+      const long long t = target[row];
+      if ((unsigned long long)t < C)
+        atomicAdd(bins + (uint32_t)t * C + (uint32_t)bi, (BinT)1);
+      else
+        rr.bad(0, t, C);
+    }
+  }
+}
+
+// Small C: a CTA stages a tile of whole rows in smem with coalesced loads, then one thread
+// scans one row.
+constexpr int kLogitsTileFloats = 8192;
+template <typename BinT>
+__global__ void __launch_bounds__(kCmBlock)
+    cm_logits_tile_kernel(const float* __restrict__ logits, int64_t ld,
+                          const long long* __restrict__ target, int64_t n, uint32_t C, BinT* bins,
+                          long long* range) {
+  __shared__ float tile[kLogitsTileFloats];
+  const int rows_per_tile = kLogitsTileFloats / (int)C;
+  const int64_t ntiles = (n + rows_per_tile - 1) / rows_per_tile;
+  RangeReport rr{range};
+  for (int64_t tl = blockIdx.x; tl < ntiles; tl += gridDim.x) {
+    const int64_t row0 = tl * rows_per_tile;
+    const int rows = (int)min((int64_t)rows_per_tile, n - row0);
+    if (ld == (int64_t)C) {
+      const float* src = logits + row0 * ld;
+      for (int i = threadIdx.x; i < rows * (int)C; i += blockDim.x) tile[i] = __ldg(src + i);
+    } else {
+      for (int i = threadIdx.x; i < rows * (int)C; i += blockDim.x) {
+        const int r = i / (int)C, c = i - r * (int)C;
+        tile[i] = __ldg(logits + (row0 + r) * ld + c);
+      }
+    }
+    __syncthreads();
+    for (int r = threadIdx.x; r < rows; r += blockDim.x) {
+      const float* q = tile + r * (int)C;
+      float bv = q[0];
+      int bi = 0;
+      for (int c = 1; c < (int)C; ++c) {
+        const float v = q[c];
+        if (better(v, c, bv, bi)) {
+          bv = v;
+          bi = c;
+        }
+      }
+      const long long t = target[row0 + r];
+      if ((unsigned long long)t < C)
+        atomicAdd(bins + (uint32_t)t * C + (uint32_t)bi, (BinT)1);
+      else
+        rr.bad(0, t, C);
+    }
+    __syncthreads();
+  }
+}
+
+int pick_variant(int32_t C, int32_t variant) {
+  if (variant != TE_CM_AUTO) return variant;
+  const int64_t nbins = (int64_t)C * C;
+  if (nbins * 32 * 4 <= 32 * 1024) return TE_CM_SMEM_REPL;   // C <= 16
+  if (nbins * 4 <= 48 * 1024) return TE_CM_SMEM;             // C <= 110
+  return TE_CM_GLOBAL64;
+}
+
+}  // namespace
+}  // namespace te
+
+using namespace te;
+
+extern "C" size_t te_cm_scratch_bytes(int32_t num_classes, int32_t variant) {
+  if (num_classes < 1) return 0;
+  const int v = pick_variant(num_classes, variant);
+  if (v == TE_CM_GLOBAL32) return align_up((size_t)num_classes * num_classes * 4, 256);
+  return 0;
+}
+
+template <int VEC>
+static int cm_launch(const long long* pred, const long long* target, int64_t n, int32_t C,
+                     unsigned long long* cm, long long* range, void* scratch, int v, int sms,
+                     cudaStream_t st) {
+  const uint32_t nbins = (uint32_t)C * (uint32_t)C;
+  const int64_t nvec = (n + VEC - 1) / VEC;
+  int64_t want = (nvec + kCmBlock * 4 - 1) / (kCmBlock * 4);
+  if (want < 1) want = 1;
+  const int grid = (int)(want < (int64_t)sms * 8 ? want : (int64_t)sms * 8);
+  switch (v) {
+    case TE_CM_GLOBAL64:
+      cm_global_kernel<VEC, unsigned long long>
+          <<<grid, kCmBlock, 0, st>>>(pred, target, n, (uint32_t)C, cm, range);
+      break;
+    case TE_CM_GLOBAL32: {
+      // int32 bins hold at most 2^31 hits: feed the stream in slices.
+      const int64_t slice = (int64_t)1 << 30;
+      for (int64_t off = 0; off < n; off += slice) {
+        const int64_t len = (n - off) < slice ? (n - off) : slice;
+        TE_CUDA_TRY(cudaMemsetAsync(scratch, 0, (size_t)nbins * 4, st));
+        cm_global_kernel<VEC, uint32_t>
+            <<<grid, kCmBlock, 0, st>>>(pred + off, target + off, len, (uint32_t)C,
+                                        (uint32_t*)scratch, range);
+        cm_fold32_kernel<<<(nbins + 255) / 256 < 1184 ? (nbins + 255) / 256 : 1184, 256, 0, st>>>(
+            (const uint32_t*)scratch, cm, nbins);
+      }
+      break;
+    }
+    case TE_CM_SMEM_REPL: {
+      const size_t sh = (size_t)nbins * 32 * 4;
+      if (sh > 48 * 1024)
+        TE_CUDA_TRY(cudaFuncSetAttribute(cm_smem_kernel<VEC, 32>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
+      const int g = grid < sms * 4 ? grid : sms * 4;
+      cm_smem_kernel<VEC, 32><<<g, kCmBlock, sh, st>>>(pred, target, n, (uint32_t)C, cm, range);
+      break;
+    }
+    case TE_CM_SMEM: {
+      const size_t sh = (size_t)nbins * 4;
+      if (sh > 48 * 1024)
+        TE_CUDA_TRY(cudaFuncSetAttribute(cm_smem_kernel<VEC, 1>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
+      const int g = grid < sms * 4 ? grid : sms * 4;
+      cm_smem_kernel<VEC, 1><<<g, kCmBlock, sh, st>>>(pred, target, n, (uint32_t)C, cm, range);
+      break;
+    }
+    default:
+      return TE_ERR_INVALID_ARGUMENT;
+  }
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+extern "C" int te_cm_update(const int64_t* pred, const int64_t* target, int64_t n,
+                            int32_t num_classes, int64_t* cm, int64_t* range, void* scratch,
+                            size_t scratch_bytes, int32_t variant, void* stream) {
+  if (n < 0 || num_classes < 1 || num_classes > 46340 || !cm || !range) return TE_ERR_INVALID_ARGUMENT;
+  if (n > 0 && (!pred || !target)) return TE_ERR_INVALID_ARGUMENT;
+  const int v = pick_variant(num_classes, variant);
+  if ((v == TE_CM_SMEM_REPL && (size_t)num_classes * num_classes * 128 > 200 * 1024) ||
+      (v == TE_CM_SMEM && (size_t)num_classes * num_classes * 4 > 200 * 1024))
+    return TE_ERR_INVALID_ARGUMENT;
+  if (scratch_bytes < te_cm_scratch_bytes(num_classes, v) || (v == TE_CM_GLOBAL32 && !scratch))
+    return TE_ERR_SCRATCH_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  cm_init_range_kernel<<<1, 32, 0, st>>>((long long*)range);
+  TE_LAUNCH_CHECK();
+  if (n == 0) return TE_OK;
+  const bool aligned = (((uintptr_t)pred | (uintptr_t)target) & 15) == 0;
+  if (aligned)
+    return cm_launch<2>((const long long*)pred, (const long long*)target, n, num_classes,
+                        (unsigned long long*)cm, (long long*)range, scratch, v, sms, st);
+  return cm_launch<1>((const long long*)pred, (const long long*)target, n, num_classes,
+                      (unsigned long long*)cm, (long long*)range, scratch, v, sms, st);
+}
+
+extern "C" int te_cm_update_logits(const float* logits, int64_t ld, const int64_t* target,
+                                   int64_t n, int32_t num_classes, int64_t* cm, int64_t* range,
+                                   void* stream) {
+  if (n < 0 || num_classes < 1 || num_classes > 46340 || !cm || !range || ld < num_classes)
+    return TE_ERR_INVALID_ARGUMENT;
+  if (n > 0 && (!logits || !target)) return TE_ERR_INVALID_ARGUMENT;
+  cudaStream_t st = (cudaStream_t)stream;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  cm_init_range_kernel<<<1, 32, 0, st>>>((long long*)range);
+  TE_LAUNCH_CHECK();
+  if (n == 0) return TE_OK;
+  const uint32_t C = (uint32_t)num_classes;
+  if (C <= 64) {
+    const int rows_per_tile = kLogitsTileFloats / (int)C;
+    const int64_t ntiles = (n + rows_per_tile - 1) / rows_per_tile;
+    const int grid = (int)(ntiles < (int64_t)sms * 8 ? ntiles : (int64_t)sms * 8);
+    cm_logits_tile_kernel<unsigned long long><<<grid, kCmBlock, 0, st>>>(
+        logits, ld, (const long long*)target, n, C, (unsigned long long*)cm, (long long*)range);
+  } else {
+    const int64_t want = (n + (kCmBlock / kWarp) - 1) / (kCmBlock / kWarp);
+    const int grid = (int)(want < (int64_t)sms * 8 ? want : (int64_t)sms * 8);
+    cm_logits_warp_kernel<unsigned long long><<<grid, kCmBlock, 0, st>>>(
+        logits, ld, (const long long*)target, n, C, (unsigned long long*)cm, (long long*)range);
+  }
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}

@@ -1,0 +1,637 @@
+// K1 — exact binary AUROC / AUPRC.
+//
+// Reference path: torcheval/metrics/functional/classification/auroc.py:115-152
+// (_binary_auroc_compute_jit: sort(descending) + diff!=0 mask + gather + 2x cumsum +
+// 2x masked_scatter_ + trapz) and precision_recall_curve.py:208-231 (_compute_for_each_class)
+// + functional/tensor_utils.py:12-16 (_riemann_integral) for AUPRC.
+//
+// Here:  ingest (score -> order-preserving 32-bit key with the 0/1 label in bit 0, four digit
+// histograms on the fly)  ->  4 single-sweep radix passes (rank_sort.cuh)  ->  ONE fused pass
+// over the sorted keys that does the TP/FP running counts (block scan + decoupled look-back
+// across tiles), the tie-group detection (`diff != 0` of the reference) and the trapezoid /
+// step integration, leaving one partial per tile; a one-CTA reduce sums the partials in a fixed
+// order.  AUROC is accumulated exactly in integers:
+//     2*U = sum over positives of (#negatives with score <= s) + (#negatives with score < s)
+//     AUROC = U / (P * N)          (identical to the reference's trapezoid sum over tie groups)
+// so the result does not depend on launch geometry or timing.
+//
+// Bytes per score (SURVEY.md §8d formula, b_in = 12, r = 4, P = 4): 16 + 32 + 4 = 52.
+#include "rank_sort.cuh"
+
+namespace te {
+namespace {
+
+// ------------------------------------------------------------------------------------------
+// ingest: raw (score, target) -> keys (+ payload) and the four digit histograms
+// ------------------------------------------------------------------------------------------
+constexpr int kIngestBlock = 1024;
+constexpr size_t kIngestSmem = (size_t)4 * kRadix * kWarp * sizeof(uint32_t);  // 128 KB
+
+enum IngestMode { kPacked = 0, kIndexed = 1, kRawKeys = 2 };
+
+struct RankScalars {            // lives in the zeroed part of the scratch buffer
+  unsigned long long positives; // #label==1 (packed mode)
+  uint32_t flags;               // TE_RANK_FLAG_*
+  uint32_t pad;
+};
+
+template <typename T>
+struct LabelOf;
+template <>
+struct LabelOf<long long> {
+  static __device__ __forceinline__ uint32_t get(long long t, uint32_t& bad) {
+    bad |= ((unsigned long long)t > 1ull);
+    return (uint32_t)t & 1u;
+  }
+};
+template <>
+struct LabelOf<int> {
+  static __device__ __forceinline__ uint32_t get(int t, uint32_t& bad) {
+    bad |= ((unsigned)t > 1u);
+    return (uint32_t)t & 1u;
+  }
+};
+template <>
+struct LabelOf<unsigned char> {
+  static __device__ __forceinline__ uint32_t get(unsigned char t, uint32_t& bad) {
+    bad |= (t > 1);
+    return t & 1u;
+  }
+};
+template <>
+struct LabelOf<float> {
+  static __device__ __forceinline__ uint32_t get(float t, uint32_t& bad) {
+    bad |= !(t == 0.f || t == 1.f);
+    return t == 1.f ? 1u : 0u;
+  }
+};
+template <>
+struct LabelOf<double> {
+  static __device__ __forceinline__ uint32_t get(double t, uint32_t& bad) {
+    bad |= !(t == 0.0 || t == 1.0);
+    return t == 1.0 ? 1u : 0u;
+  }
+};
+
+template <int MODE, typename TargetT>
+__global__ void __launch_bounds__(kIngestBlock, 1)
+    rank_ingest_kernel(const float* __restrict__ score, const TargetT* __restrict__ target,
+                       const uint32_t* __restrict__ raw_keys, uint32_t n, bool vec_ok,
+                       uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+                       uint32_t* ghist, RankScalars* scal) {
+  extern __shared__ uint32_t sh[];  // [pass][digit][lane]
+  const unsigned tid = threadIdx.x, lane = tid & 31;
+  for (int i = tid; i < 4 * kRadix * kWarp; i += kIngestBlock) sh[i] = 0;
+  __syncthreads();
+
+  uint32_t npos = 0, bad_label = 0, neg_score = 0;
+  const uint32_t ngroups = (n + 3) / 4;
+  const uint32_t stride = gridDim.x * kIngestBlock;
+  for (uint32_t g = blockIdx.x * kIngestBlock + tid; g < ngroups; g += stride) {
+    const uint32_t i0 = g * 4;
+    const uint32_t cnt = min(4u, n - i0);
+    uint32_t k[4];
+    if (MODE == kRawKeys) {
+      if (cnt == 4 && vec_ok) {
+        const int4 a = ld_stream_v4(raw_keys + i0);
+        k[0] = a.x, k[1] = a.y, k[2] = a.z, k[3] = a.w;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) k[j] = j < (int)cnt ? raw_keys[i0 + j] : 0u;
+      }
+    } else {
+      float x[4];
+      if (cnt == 4 && vec_ok) {
+        const int4 a = ld_stream_v4(score + i0);
+        x[0] = __int_as_float(a.x), x[1] = __int_as_float(a.y);
+        x[2] = __int_as_float(a.z), x[3] = __int_as_float(a.w);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) x[j] = j < (int)cnt ? score[i0 + j] : 0.f;
+      }
+      if (MODE == kPacked) {
+        uint32_t lab[4];
+        if constexpr (sizeof(TargetT) == 8) {
+          if (cnt == 4 && vec_ok) {
+          const int4 t0 = ld_stream_v4(target + i0);
+          const int4 t1 = ld_stream_v4(target + i0 + 2);
+          TargetT tv[4];
+          const unsigned long long u0 = ((unsigned long long)(uint32_t)t0.y << 32) | (uint32_t)t0.x;
+          const unsigned long long u1 = ((unsigned long long)(uint32_t)t0.w << 32) | (uint32_t)t0.z;
+          const unsigned long long u2 = ((unsigned long long)(uint32_t)t1.y << 32) | (uint32_t)t1.x;
+          const unsigned long long u3 = ((unsigned long long)(uint32_t)t1.w << 32) | (uint32_t)t1.z;
+          memcpy(&tv[0], &u0, 8), memcpy(&tv[1], &u1, 8), memcpy(&tv[2], &u2, 8), memcpy(&tv[3], &u3, 8);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) lab[j] = LabelOf<TargetT>::get(tv[j], bad_label);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              lab[j] = j < (int)cnt ? LabelOf<TargetT>::get(target[i0 + j], bad_label) : 0u;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            lab[j] = j < (int)cnt ? LabelOf<TargetT>::get(target[i0 + j], bad_label) : 0u;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint32_t b = __float_as_uint(x[j]);
+          if (b == 0x80000000u) b = 0u;  // -0.0 ties with +0.0
+          neg_score |= b >> 31;          // sign bit: this path needs non-negative scores
+          k[j] = (b << 1) | lab[j];
+          if (j < (int)cnt) npos += lab[j];
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) k[j] = orderable_f32(x[j]);
+      }
+      if (cnt == 4) {
+        st_stream_v4(keys_out + i0, make_int4((int)k[0], (int)k[1], (int)k[2], (int)k[3]));
+        if (MODE == kIndexed)
+          st_stream_v4(vals_out + i0, make_int4((int)i0, (int)i0 + 1, (int)i0 + 2, (int)i0 + 3));
+      } else {
+        for (uint32_t j = 0; j < cnt; ++j) {
+          keys_out[i0 + j] = k[j];
+          if (MODE == kIndexed) vals_out[i0 + j] = i0 + j;
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (j < (int)cnt) {
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          const uint32_t d = (k[j] >> (8 * p)) & 0xffu;
+          atomicAdd(sh + ((p << 8) + d) * kWarp + lane, 1u);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  {
+    uint32_t s = 0;  // thread t owns (pass, digit) = t
+#pragma unroll
+    for (int r = 0; r < kWarp; ++r) s += sh[tid * kWarp + ((r + tid) & 31)];
+    if (s) atomicAdd(ghist + tid, s);
+  }
+  if (MODE == kPacked) {
+    npos = warp_sum(npos);
+    const uint32_t anybad = __any_sync(kFull, bad_label != 0);
+    const uint32_t anyneg = __any_sync(kFull, neg_score != 0);
+    if (lane == 0) {
+      if (npos) atomicAdd(&scal->positives, (unsigned long long)npos);
+      const uint32_t f = (anybad ? TE_RANK_FLAG_BAD_LABEL : 0) | (anyneg ? TE_RANK_FLAG_NEGATIVE_SCORE : 0);
+      if (f) atomicOr(&scal->flags, f);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// fused scan / tie-dedup / integrate over sorted packed keys (ascending; bit 0 = label, so
+// inside a tie group the negatives come first)
+// ------------------------------------------------------------------------------------------
+constexpr int kFinBlock = 256;
+constexpr int kFinIpt = 16;
+constexpr int kFinTile = kFinBlock * kFinIpt;
+
+struct FState {
+  uint32_t S;   // negatives in the segment
+  uint32_t M;   // negatives (from segment start) before the segment's last group start
+  uint32_t Mp;  // global index of that group start
+  uint32_t F;   // segment contains a group start
+};
+__device__ __forceinline__ FState f_identity() { return FState{0, 0, 0, 0}; }
+__device__ __forceinline__ FState f_combine(const FState& a, const FState& b) {  // a then b
+  FState r;
+  r.S = a.S + b.S;
+  r.F = a.F | b.F;
+  r.M = b.F ? a.S + b.M : a.M;
+  r.Mp = b.F ? b.Mp : a.Mp;
+  return r;
+}
+__device__ __forceinline__ FState f_shfl_up(const FState& v, int o) {
+  FState u;
+  u.S = __shfl_up_sync(kFull, v.S, o);
+  u.M = __shfl_up_sync(kFull, v.M, o);
+  u.Mp = __shfl_up_sync(kFull, v.Mp, o);
+  u.F = __shfl_up_sync(kFull, v.F, o);
+  return u;
+}
+
+// One record per tile and kind (own aggregate / inclusive prefix); written once, then flagged.
+struct alignas(32) ScanRec {
+  unsigned long long flag;
+  unsigned long long w0;  // S | M << 32
+  unsigned long long w1;  // Mp | F << 32
+  unsigned long long pad;
+};
+__device__ __forceinline__ void rec_publish(ScanRec* r, const FState& s) {
+  st_relaxed_u64(&r->w0, (unsigned long long)s.S | ((unsigned long long)s.M << 32));
+  st_relaxed_u64(&r->w1, (unsigned long long)s.Mp | ((unsigned long long)s.F << 32));
+  st_release_u64(&r->flag, 1ull);
+}
+__device__ __forceinline__ bool rec_try(const ScanRec* r, FState& s) {
+  if (ld_acquire_u64(&r->flag) == 0ull) return false;
+  const unsigned long long w0 = ld_relaxed_u64(&r->w0), w1 = ld_relaxed_u64(&r->w1);
+  s.S = (uint32_t)w0;
+  s.M = (uint32_t)(w0 >> 32);
+  s.Mp = (uint32_t)w1;
+  s.F = (uint32_t)(w1 >> 32);
+  return true;
+}
+
+template <int MODE>  // 0: AUROC (u64 partials)  1: AUPRC (double partials)
+__global__ void __launch_bounds__(kFinBlock)
+    rank_final_kernel(const uint32_t* __restrict__ keys, uint32_t n, ScanRec* agg, ScanRec* inc,
+                      uint32_t* ticket, const RankScalars* __restrict__ scal,
+                      unsigned long long* partial) {
+  __shared__ FState s_warp[kFinBlock / kWarp];
+  __shared__ FState s_excl;
+  __shared__ uint32_t s_tile;
+  __shared__ unsigned long long s_red[kFinBlock / kWarp];
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+  __syncthreads();
+  const uint32_t tile = s_tile;
+  const uint32_t i0 = tile * (uint32_t)kFinTile + tid * kFinIpt;
+
+  uint32_t k[kFinIpt];
+  if (i0 + kFinIpt <= n) {
+#pragma unroll
+    for (int q = 0; q < kFinIpt / 4; ++q) {
+      const int4 a = ld_stream_v4(keys + i0 + 4 * q);
+      k[4 * q] = a.x, k[4 * q + 1] = a.y, k[4 * q + 2] = a.z, k[4 * q + 3] = a.w;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < kFinIpt; ++j) k[j] = (i0 + j < n) ? keys[i0 + j] : 0u;
+  }
+  const uint32_t cnt = i0 < n ? min((uint32_t)kFinIpt, n - i0) : 0u;
+  uint32_t prev = (i0 > 0 && i0 < n) ? (keys[i0 - 1] >> 1) : 0u;
+
+  // phase 1: thread aggregate + group-start mask
+  FState mine = f_identity();
+  uint32_t starts = 0;
+#pragma unroll
+  for (int j = 0; j < kFinIpt; ++j) {
+    if (j < (int)cnt) {
+      const uint32_t s = k[j] >> 1;
+      const bool st = (j == 0 && i0 == 0) || s != prev;
+      prev = s;
+      if (st) {
+        starts |= 1u << j;
+        mine.F = 1;
+        mine.M = mine.S;
+        mine.Mp = i0 + j;
+      }
+      mine.S += (k[j] & 1u) ^ 1u;
+    }
+  }
+
+  // block exclusive scan of the thread aggregates
+  FState incl = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const FState u = f_shfl_up(incl, o);
+    if (lane >= (unsigned)o) incl = f_combine(u, incl);
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  FState excl = f_shfl_up(incl, 1);
+  if (lane == 0) excl = f_identity();
+  __syncthreads();
+  FState wprefix = f_identity(), tile_agg = f_identity();
+#pragma unroll
+  for (int w = 0; w < kFinBlock / kWarp; ++w) {
+    const FState x = s_warp[w];
+    if (w < (int)warp) wprefix = f_combine(wprefix, x);
+    tile_agg = f_combine(tile_agg, x);
+  }
+  excl = f_combine(wprefix, excl);
+
+  // decoupled look-back across tiles (one thread walks the chain)
+  if (tid == 0) {
+    rec_publish(agg + tile, tile_agg);
+    FState e = f_identity();
+    for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
+      FState r;
+      bool full = false;
+      for (;;) {
+        if (rec_try(inc + t, r)) {
+          full = true;
+          break;
+        }
+        if (rec_try(agg + t, r)) break;
+      }
+      e = f_combine(r, e);
+      if (full) break;
+    }
+    rec_publish(inc + tile, f_combine(e, tile_agg));
+    s_excl = e;
+  }
+  __syncthreads();
+  const FState g = f_combine(s_excl, excl);
+
+  // phase 2: integrate
+  uint32_t c = g.S, gs = g.M, gp = g.Mp;
+  unsigned long long acc_u = 0;
+  double acc_d = 0.0;
+  const double ptot = (double)scal->positives;
+#pragma unroll
+  for (int j = 0; j < kFinIpt; ++j) {
+    if (j < (int)cnt) {
+      if (starts & (1u << j)) {
+        gs = c;
+        gp = i0 + j;
+      }
+      if (k[j] & 1u) {
+        if (MODE == 0) {
+          acc_u += (unsigned long long)c + gs;
+        } else {
+          // precision at this tie group's threshold: TP / (TP + FP), counts of score >= s
+          const double tp = ptot - (double)(gp - gs);
+          acc_d += tp / (double)(n - gp);
+        }
+      } else {
+        ++c;
+      }
+    }
+  }
+  if (MODE == 0) {
+    acc_u = warp_sum(acc_u);
+    if (lane == 0) s_red[warp] = acc_u;
+    __syncthreads();
+    if (tid == 0) {
+      unsigned long long t = 0;
+      for (int w = 0; w < kFinBlock / kWarp; ++w) t += s_red[w];
+      partial[tile] = t;
+    }
+  } else {
+    acc_d = warp_sum(acc_d);
+    if (lane == 0) s_red[warp] = (unsigned long long)__double_as_longlong(acc_d);
+    __syncthreads();
+    if (tid == 0) {
+      double t = 0.0;
+      for (int w = 0; w < kFinBlock / kWarp; ++w) t += __longlong_as_double((long long)s_red[w]);
+      partial[tile] = (unsigned long long)__double_as_longlong(t);
+    }
+  }
+}
+
+// Fixed-order sum of the per-tile partials and the final division.
+//   out[0] = metric   out[1] = #positives   out[2] = #negatives   out[3] = raw sum
+//   out[4] = TE_RANK_FLAG_* seen by the ingest kernel (non-zero: out[0] is not valid)
+template <int MODE>
+__global__ void __launch_bounds__(1024)
+    rank_reduce_kernel(const unsigned long long* __restrict__ partial, uint32_t ntiles, uint32_t n,
+                       const RankScalars* __restrict__ scal, double* out) {
+  __shared__ unsigned long long s_u[32];
+  __shared__ double s_d[32];
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  unsigned long long au = 0;
+  double ad = 0.0;
+  // contiguous slab per thread keeps the summation order independent of anything dynamic
+  const uint32_t per = (ntiles + 1023) / 1024;
+  const uint32_t b = min(ntiles, tid * per), e = min(ntiles, b + per);
+  for (uint32_t i = b; i < e; ++i) {
+    if (MODE == 0)
+      au += partial[i];
+    else
+      ad += __longlong_as_double((long long)partial[i]);
+  }
+  au = warp_sum(au);
+  // butterfly sums are order-symmetric, so `ad` is the same on every run as well
+  ad = warp_sum(ad);
+  if (lane == 0) s_u[warp] = au, s_d[warp] = ad;
+  __syncthreads();
+  if (tid == 0) {
+    unsigned long long tu = 0;
+    double td = 0.0;
+    for (int w = 0; w < 32; ++w) tu += s_u[w], td += s_d[w];
+    const double P = (double)scal->positives, N = (double)n - P;
+    out[1] = P;
+    out[2] = N;
+    out[4] = (double)scal->flags;
+    if (MODE == 0) {
+      out[3] = (double)tu;
+      out[0] = (P * N == 0.0) ? 0.5 : ((double)tu * 0.5) / (P * N);
+    } else {
+      out[3] = td;
+      // no positives: recall is NaN -> 1.0, the last step then contributes -0.0
+      // (precision_recall_curve.py:227-229)
+      out[0] = P == 0.0 ? -0.0 : td / P;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side: scratch plan + launch sequences
+// ------------------------------------------------------------------------------------------
+struct RankPlan {
+  uint32_t n;
+  uint32_t sort_tiles, fin_tiles;
+  size_t off_keys_a, off_keys_b, off_vals_a, off_vals_b;
+  size_t off_zero;      // start of the region that must be zero before launch
+  size_t off_hist;      // 4*256 u32
+  size_t off_ticket;    // 8 u32
+  size_t off_scal;      // RankScalars
+  size_t off_lookback;  // 4 passes * sort_tiles * 256 u32
+  size_t off_agg, off_inc;
+  size_t zero_bytes;
+  size_t off_partial;
+  size_t total;
+};
+
+RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final) {
+  RankPlan p{};
+  p.n = (uint32_t)n64;
+  p.sort_tiles = (uint32_t)((n64 + kSortTile - 1) / kSortTile);
+  p.fin_tiles = (uint32_t)((n64 + kFinTile - 1) / kFinTile);
+  if (p.sort_tiles == 0) p.sort_tiles = 1;
+  if (p.fin_tiles == 0) p.fin_tiles = 1;
+  size_t o = 0;
+  auto take = [&](size_t bytes) {
+    const size_t at = o;
+    o += align_up(bytes ? bytes : 1, 256);
+    return at;
+  };
+  const size_t kb = (size_t)n64 * 4;
+  p.off_keys_a = take(with_keys ? kb : 0);
+  p.off_keys_b = take(with_keys ? kb : 0);
+  p.off_vals_a = take(with_vals ? kb : 0);
+  p.off_vals_b = take(with_vals ? kb : 0);
+  p.off_zero = o;
+  p.off_hist = take(4 * kRadix * 4);
+  p.off_ticket = take(8 * 4);
+  p.off_scal = take(sizeof(RankScalars));
+  p.off_lookback = take((size_t)4 * p.sort_tiles * kRadix * 4);
+  p.off_agg = take(with_final ? (size_t)p.fin_tiles * sizeof(ScanRec) : 0);
+  p.off_inc = take(with_final ? (size_t)p.fin_tiles * sizeof(ScanRec) : 0);
+  p.zero_bytes = o - p.off_zero;
+  p.off_partial = take(with_final ? (size_t)p.fin_tiles * 8 : 0);
+  p.total = o;
+  return p;
+}
+
+template <typename T>
+T* at(void* base, size_t off) {
+  return reinterpret_cast<T*>(static_cast<char*>(base) + off);
+}
+
+int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t* k_x, uint32_t* k_y,
+               const uint32_t* v_in0, uint32_t* v_x, uint32_t* v_y, cudaStream_t st) {
+  // 4 passes: in0 -> x -> y -> x -> y
+  uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
+  uint32_t* ticket = at<uint32_t>(scratch, p.off_ticket);
+  uint32_t* lb = at<uint32_t>(scratch, p.off_lookback);
+  digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 4);
+  TE_LAUNCH_CHECK();
+  constexpr size_t smem = onesweep_smem_bytes<uint32_t>();
+  TE_CUDA_TRY(cudaFuncSetAttribute(onesweep_pass_kernel<uint32_t, true>,
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  TE_CUDA_TRY(cudaFuncSetAttribute(onesweep_pass_kernel<uint32_t, false>,
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const uint32_t* kin = k_in0;
+  const uint32_t* vin = v_in0;
+  for (int pass = 0; pass < 4; ++pass) {
+    uint32_t* kout = (pass & 1) ? k_y : k_x;
+    uint32_t* vout = (pass & 1) ? v_y : v_x;
+    uint32_t* lbp = lb + (size_t)pass * p.sort_tiles * kRadix;
+    if (v_in0)
+      onesweep_pass_kernel<uint32_t, true><<<p.sort_tiles, kSortBlock, smem, st>>>(
+          kin, kout, vin, vout, p.n, 8 * pass, hist + pass * kRadix, lbp, ticket + pass);
+    else
+      onesweep_pass_kernel<uint32_t, false><<<p.sort_tiles, kSortBlock, smem, st>>>(
+          kin, kout, nullptr, nullptr, p.n, 8 * pass, hist + pass * kRadix, lbp, ticket + pass);
+    TE_LAUNCH_CHECK();
+    kin = kout;
+    vin = vout;
+  }
+  return TE_OK;
+}
+
+template <int MODE, typename TargetT>
+int launch_ingest(const float* score, const void* target, const uint32_t* raw, const RankPlan& p,
+                  uint32_t* keys_out, uint32_t* vals_out, void* scratch, int sms, cudaStream_t st) {
+  auto kern = rank_ingest_kernel<MODE, TargetT>;
+  TE_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)kIngestSmem));
+  const uint32_t ngroups = (p.n + 3) / 4;
+  uint32_t grid = (ngroups + kIngestBlock - 1) / kIngestBlock;
+  if (grid > (uint32_t)sms) grid = sms;
+  if (grid < 1) grid = 1;
+  uintptr_t a = (uintptr_t)score | (uintptr_t)target | (uintptr_t)raw;
+  const bool vec_ok = (a & 15) == 0;
+  kern<<<grid, kIngestBlock, kIngestSmem, st>>>(score, (const TargetT*)target, raw, p.n, vec_ok,
+                                                 keys_out, vals_out, at<uint32_t>(scratch, p.off_hist),
+                                                 at<RankScalars>(scratch, p.off_scal));
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+template <int MODE>
+int launch_ingest_dtype(const float* score, const void* target, int32_t dt, const RankPlan& p,
+                        uint32_t* keys_out, uint32_t* vals_out, void* scratch, int sms,
+                        cudaStream_t st) {
+  switch (dt) {
+    case TE_DTYPE_I64:
+      return launch_ingest<MODE, long long>(score, target, nullptr, p, keys_out, vals_out, scratch, sms, st);
+    case TE_DTYPE_I32:
+      return launch_ingest<MODE, int>(score, target, nullptr, p, keys_out, vals_out, scratch, sms, st);
+    case TE_DTYPE_U8:
+      return launch_ingest<MODE, unsigned char>(score, target, nullptr, p, keys_out, vals_out, scratch, sms, st);
+    case TE_DTYPE_F32:
+      return launch_ingest<MODE, float>(score, target, nullptr, p, keys_out, vals_out, scratch, sms, st);
+    case TE_DTYPE_F64:
+      return launch_ingest<MODE, double>(score, target, nullptr, p, keys_out, vals_out, scratch, sms, st);
+    default:
+      return TE_ERR_INVALID_ARGUMENT;
+  }
+}
+
+int binary_rank_packed(const float* score, const void* target, int32_t dt, int64_t n, int mode,
+                       double* out, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+  if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  const RankPlan p = make_plan(n, false, true, true);
+  if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
+  uint32_t* ka = at<uint32_t>(scratch, p.off_keys_a);
+  uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
+  if (n > 0) {
+    int rc = launch_ingest_dtype<kPacked>(score, target, dt, p, ka, nullptr, scratch, sms, st);
+    if (rc) return rc;
+    // a -> b -> a -> b -> a : sorted keys end in `ka`
+    rc = run_passes(p, scratch, ka, kb, ka, nullptr, nullptr, nullptr, st);
+    if (rc) return rc;
+  }
+  ScanRec* agg = at<ScanRec>(scratch, p.off_agg);
+  ScanRec* inc = at<ScanRec>(scratch, p.off_inc);
+  uint32_t* ticket = at<uint32_t>(scratch, p.off_ticket) + 4;
+  unsigned long long* partial = at<unsigned long long>(scratch, p.off_partial);
+  const RankScalars* scal = at<RankScalars>(scratch, p.off_scal);
+  const uint32_t ftiles = n > 0 ? p.fin_tiles : 0;
+  if (mode == 0) {
+    if (ftiles)
+      rank_final_kernel<0><<<ftiles, kFinBlock, 0, st>>>(ka, p.n, agg, inc, ticket, scal, partial);
+    rank_reduce_kernel<0><<<1, 1024, 0, st>>>(partial, ftiles, p.n, scal, out);
+  } else {
+    if (ftiles)
+      rank_final_kernel<1><<<ftiles, kFinBlock, 0, st>>>(ka, p.n, agg, inc, ticket, scal, partial);
+    rank_reduce_kernel<1><<<1, 1024, 0, st>>>(partial, ftiles, p.n, scal, out);
+  }
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+}  // namespace
+}  // namespace te
+
+using namespace te;
+
+extern "C" size_t te_binary_rank_scratch_bytes(int64_t n) {
+  if (n < 0 || n > 0x7fffffffLL) return 0;
+  return make_plan(n, false, true, true).total;
+}
+
+extern "C" int te_binary_auroc(const float* score, const void* target, int32_t target_dtype,
+                               int64_t n, double* out, void* scratch, size_t scratch_bytes,
+                               void* stream) {
+  if (!out || (n > 0 && (!score || !target))) return TE_ERR_INVALID_ARGUMENT;
+  return binary_rank_packed(score, target, target_dtype, n, 0, out, scratch, scratch_bytes,
+                            (cudaStream_t)stream);
+}
+
+extern "C" int te_binary_auprc(const float* score, const void* target, int32_t target_dtype,
+                               int64_t n, double* out, void* scratch, size_t scratch_bytes,
+                               void* stream) {
+  if (!out || (n > 0 && (!score || !target))) return TE_ERR_INVALID_ARGUMENT;
+  return binary_rank_packed(score, target, target_dtype, n, 1, out, scratch, scratch_bytes,
+                            (cudaStream_t)stream);
+}
+
+extern "C" size_t te_sort_u32_scratch_bytes(int64_t n, int32_t with_values) {
+  if (n < 0 || n > 0x7fffffffLL) return 0;
+  return make_plan(n, with_values != 0, true, false).total;
+}
+
+extern "C" int te_sort_u32(const uint32_t* keys_in, uint32_t* keys_out, const uint32_t* vals_in,
+                           uint32_t* vals_out, int64_t n, void* scratch, size_t scratch_bytes,
+                           void* stream) {
+  if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  if (n > 0 && (!keys_in || !keys_out)) return TE_ERR_INVALID_ARGUMENT;
+  if ((vals_in == nullptr) != (vals_out == nullptr)) return TE_ERR_INVALID_ARGUMENT;
+  const bool wv = vals_in != nullptr;
+  const RankPlan p = make_plan(n, wv, true, false);
+  if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
+  if (n == 0) return TE_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
+  int rc = launch_ingest<kRawKeys, long long>(nullptr, nullptr, keys_in, p, nullptr, nullptr, scratch, sms, st);
+  if (rc) return rc;
+  // in -> tmp -> out -> tmp -> out
+  return run_passes(p, scratch, keys_in, at<uint32_t>(scratch, p.off_keys_a), keys_out, vals_in,
+                    wv ? at<uint32_t>(scratch, p.off_vals_a) : nullptr, vals_out, st);
+}

@@ -1,0 +1,234 @@
+// Building blocks of the exact ranking path (K1/K2): single-sweep LSD radix sort.
+//
+// One pass = one kernel: every CTA takes a tile of keys (ticket order), ranks them by the
+// current 8-bit digit with warp-private shared-memory digit counters, learns where its digit
+// runs start in the output through a decoupled look-back chain over the preceding tiles
+// (one chain per digit), and writes the tile out through shared memory so that every digit run
+// leaves as a contiguous burst.  The four digit histograms are produced up front by the ingest
+// kernel, so each pass reads and writes every record exactly once (2*r bytes per record, the
+// "bytes moved per sort pass" of BASELINE.json).
+#pragma once
+#include "common.cuh"
+
+namespace te {
+
+constexpr int kRadixBits = 8;
+constexpr int kRadix = 1 << kRadixBits;
+
+constexpr int kSortBlock = 512;
+constexpr int kSortIpt = 16;
+constexpr int kSortTile = kSortBlock * kSortIpt;  // 8192 records per CTA
+
+// Look-back word of the sort passes (one per tile and digit), written at most twice:
+//   0                     : tile has not published yet
+//   v      (bit31 == 0)   : v - 1 = this tile's own count for the digit
+//   v      (bit31 == 1)   : v & 0x7fffffff = count over this tile and every tile before it
+// A word carries its own validity, so relaxed loads/stores are enough.  Limits n to 2^31 - 1.
+constexpr uint32_t kLbInclusive = 0x80000000u;
+
+template <typename KeyT>
+__device__ __forceinline__ uint32_t digit_of(KeyT k, int shift) {
+  return (uint32_t)(k >> shift) & (kRadix - 1);
+}
+
+// Lanes of the warp holding the same 8-bit digit (ballot per bit).
+__device__ __forceinline__ uint32_t match_digit(uint32_t d) {
+  uint32_t peers = kFull;
+#pragma unroll
+  for (int b = 0; b < kRadixBits; ++b) {
+    const bool bit = (d >> b) & 1u;
+    const uint32_t m = __ballot_sync(kFull, bit);
+    peers &= bit ? m : ~m;
+  }
+  return peers;
+}
+
+template <typename KeyT>
+constexpr size_t onesweep_smem_bytes() {
+  return sizeof(KeyT) * kSortTile + sizeof(uint32_t) * ((kSortBlock / kWarp) * kRadix + kRadix + kRadix / kWarp + 4);
+}
+
+template <typename KeyT, bool HAS_VAL>
+__global__ void __launch_bounds__(kSortBlock, 2)
+    onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
+                         const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
+                         uint32_t n, int shift, const uint32_t* __restrict__ digit_base,
+                         uint32_t* lookback, uint32_t* ticket) {
+  constexpr int WARPS = kSortBlock / kWarp;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  KeyT* s_keys = reinterpret_cast<KeyT*>(smem_raw);
+  uint32_t(*s_whist)[kRadix] = reinterpret_cast<uint32_t(*)[kRadix]>(s_keys + kSortTile);
+  uint32_t* s_goff = &s_whist[WARPS][0];
+  uint32_t* s_wsum = s_goff + kRadix;
+  uint32_t& s_tile = s_wsum[kRadix / kWarp];
+
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+  for (int i = tid; i < WARPS * kRadix; i += kSortBlock) (&s_whist[0][0])[i] = 0;
+  __syncthreads();
+  const uint32_t tile = s_tile;
+  const uint32_t base = tile * (uint32_t)kSortTile;
+  const uint32_t valid = min((uint32_t)kSortTile, n - base);
+  const uint32_t wbase = warp * (kWarp * kSortIpt);  // tile-relative start of this warp's chunk
+
+  // ---- load (warp-striped: slot i of lane l is record wbase + i*32 + l, so (i, l) order is
+  //      array order and the ranking below is stable) ----
+  KeyT key[kSortIpt];
+#pragma unroll
+  for (int i = 0; i < kSortIpt; ++i) {
+    const uint32_t r = wbase + i * kWarp + lane;
+    key[i] = r < valid ? keys_in[base + r] : ~(KeyT)0;  // padding sorts last, is never written
+  }
+
+  // ---- rank inside the warp ----
+  uint32_t* wh = s_whist[warp];
+  uint32_t rk[kSortIpt / 2];  // two 16-bit ranks per register
+#pragma unroll
+  for (int i = 0; i < kSortIpt; ++i) {
+    const uint32_t d = digit_of(key[i], shift);
+    const uint32_t peers = match_digit(d);
+    const int leader = __ffs(peers) - 1;
+    const uint32_t below = __popc(peers & lanemask_lt());
+    uint32_t first = 0;
+    if ((int)lane == leader) {
+      first = wh[d];
+      wh[d] = first + __popc(peers);
+    }
+    __syncwarp();
+    first = __shfl_sync(kFull, first, leader);
+    const uint32_t r = first + below;  // < 512
+    if (i & 1)
+      rk[i >> 1] |= r << 16;
+    else
+      rk[i >> 1] = r;
+  }
+  __syncthreads();
+
+  // ---- per-digit: tile count, publish, look back, local layout ----
+  if (tid < kRadix) {
+    const uint32_t d = tid;
+    uint32_t cnt = 0;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) cnt += s_whist[w][d];
+    uint32_t* lb = lookback + (size_t)tile * kRadix + d;
+    st_relaxed_u32(lb, cnt + 1u);
+
+    // exclusive scan of cnt over the 256 digits (8 warps, named barrier 1)
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t u = __shfl_up_sync(kFull, incl, o);
+      if (lane >= (unsigned)o) incl += u;
+    }
+    if (lane == 31) s_wsum[warp] = incl;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    uint32_t wb = 0;
+#pragma unroll
+    for (int w = 0; w < kRadix / kWarp; ++w)
+      if (w < (int)warp) wb += s_wsum[w];
+    const uint32_t bin_start = wb + incl - cnt;
+
+    // warp-exclusive offsets inside the digit run, shifted to tile-local positions
+    uint32_t run = bin_start;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) {
+      const uint32_t c = s_whist[w][d];
+      s_whist[w][d] = run;
+      run += c;
+    }
+
+    // decoupled look-back over the preceding tiles
+    uint32_t excl = 0;
+    for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
+      const uint32_t* p = lookback + (size_t)t * kRadix + d;
+      uint32_t w;
+      do {
+        w = ld_relaxed_u32(p);
+      } while (w == 0);
+      if (w & kLbInclusive) {
+        excl += w & ~kLbInclusive;
+        break;
+      }
+      excl += w - 1u;
+    }
+    st_relaxed_u32(lb, kLbInclusive | (excl + cnt));
+    s_goff[d] = digit_base[d] + excl - bin_start;  // output index = s_goff[d] + tile position
+  }
+  __syncthreads();
+
+  // ---- scatter into tile order through shared memory ----
+#pragma unroll
+  for (int i = 0; i < kSortIpt; ++i) {
+    const uint32_t d = digit_of(key[i], shift);
+    const uint32_t r = (i & 1) ? (rk[i >> 1] >> 16) : (rk[i >> 1] & 0xffffu);
+    const uint32_t p = wh[d] + r;
+    s_keys[p] = key[i];
+    if (HAS_VAL) {
+      if (i & 1)
+        rk[i >> 1] = (rk[i >> 1] & 0xffffu) | (p << 16);
+      else
+        rk[i >> 1] = (rk[i >> 1] & 0xffff0000u) | p;
+    }
+  }
+  __syncthreads();
+
+  uint32_t dpack[kSortIpt / 4];  // digit of tile position tid + k*BLOCK, four per register
+#pragma unroll
+  for (int k = 0; k < kSortIpt; ++k) {
+    const uint32_t p = tid + k * kSortBlock;
+    const KeyT kk = s_keys[p];
+    const uint32_t d = digit_of(kk, shift);
+    if (p < valid) keys_out[s_goff[d] + p] = kk;
+    if (HAS_VAL) {
+      if ((k & 3) == 0)
+        dpack[k >> 2] = d;
+      else
+        dpack[k >> 2] |= d << (8 * (k & 3));
+    }
+  }
+
+  if (HAS_VAL) {
+    uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_keys);
+    uint32_t val[kSortIpt];
+#pragma unroll
+    for (int i = 0; i < kSortIpt; ++i) {
+      const uint32_t r = wbase + i * kWarp + lane;
+      val[i] = r < valid ? vals_in[base + r] : 0u;
+    }
+    __syncthreads();  // everybody is done reading s_keys
+#pragma unroll
+    for (int i = 0; i < kSortIpt; ++i) {
+      const uint32_t p = (i & 1) ? (rk[i >> 1] >> 16) : (rk[i >> 1] & 0xffffu);
+      s_vals[p] = val[i];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kSortIpt; ++k) {
+      const uint32_t p = tid + k * kSortBlock;
+      const uint32_t d = (dpack[k >> 2] >> (8 * (k & 3))) & 0xffu;
+      if (p < valid) vals_out[s_goff[d] + p] = s_vals[p];
+    }
+  }
+}
+
+// Exclusive scan of the four 256-bin digit histograms, in place (one warp-scan chain per pass).
+__global__ void __launch_bounds__(1024) digit_scan_kernel(uint32_t* hist, int passes) {
+  __shared__ uint32_t ws[32];
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int pass = tid >> 8;
+  uint32_t v = pass < passes ? hist[tid] : 0u;
+  uint32_t incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t u = __shfl_up_sync(kFull, incl, o);
+    if (lane >= (unsigned)o) incl += u;
+  }
+  if (lane == 31) ws[warp] = incl;
+  __syncthreads();
+  uint32_t wb = 0;
+  const unsigned w0 = (unsigned)pass * 8;  // first warp of this pass
+  for (unsigned w = w0; w < warp; ++w) wb += ws[w];
+  if (pass < passes) hist[tid] = wb + incl - v;
+}
+
+}  // namespace te

@@ -1,0 +1,208 @@
+"""Tensor-level entry points: torch owns device memory and streams, libte_b200.so does the work.
+
+Every function takes CUDA tensors, enqueues on ``torch.cuda.current_stream()`` of the tensors'
+device and returns CUDA tensors.  Nothing here computes a metric in PyTorch; if the native
+library is missing these functions raise (see ``_native.load``).
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _native as N
+
+_DTYPE_CODE = {
+    torch.int64: N.TE_DTYPE_I64,
+    torch.int32: N.TE_DTYPE_I32,
+    torch.uint8: N.TE_DTYPE_U8,
+    torch.bool: N.TE_DTYPE_U8,
+    torch.float32: N.TE_DTYPE_F32,
+    torch.float64: N.TE_DTYPE_F64,
+}
+
+
+def _require_cuda(*tensors: torch.Tensor) -> torch.device:
+    dev = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError(
+                "torcheval_b200 kernels run on CUDA tensors only (no CPU fallback); "
+                f"got a tensor on {t.device}"
+            )
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise RuntimeError(f"tensors on different devices: {dev} and {t.device}")
+    assert dev is not None
+    return dev
+
+
+def _stream_ptr(dev: torch.device) -> int:
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+def _scratch(nbytes: int, dev: torch.device) -> torch.Tensor:
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev)
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+# ----------------------------------------------------------------------------- K4
+def cm_update_(
+    cm: torch.Tensor,
+    pred: torch.Tensor,
+    target: torch.Tensor,
+    num_classes: int,
+    variant: int = N.TE_CM_AUTO,
+) -> torch.Tensor:
+    """cm (int64 [C, C], updated in place) += counts of (target, pred).  Returns the int64[4]
+    device tensor {min_pred, max_pred, min_target, max_target} over out-of-range entries."""
+    lib = N.load()
+    dev = _require_cuda(cm, pred, target)
+    assert cm.dtype == torch.int64 and cm.is_contiguous() and cm.numel() == num_classes * num_classes
+    assert pred.dtype == torch.int64 and target.dtype == torch.int64
+    pred, target = pred.contiguous(), target.contiguous()
+    rng = torch.empty(4, dtype=torch.int64, device=dev)
+    sb = lib.te_cm_scratch_bytes(num_classes, variant)
+    scratch = _scratch(sb, dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_cm_update",
+            lib.te_cm_update(
+                pred.data_ptr(), target.data_ptr(), pred.numel(), num_classes, cm.data_ptr(),
+                rng.data_ptr(), scratch.data_ptr(), scratch.numel(), variant, _stream_ptr(dev),
+            ),
+        )
+    return rng
+
+
+def cm_update_logits_(
+    cm: torch.Tensor, logits: torch.Tensor, target: torch.Tensor, num_classes: int
+) -> torch.Tensor:
+    lib = N.load()
+    dev = _require_cuda(cm, logits, target)
+    assert cm.dtype == torch.int64 and cm.is_contiguous()
+    assert logits.dtype == torch.float32 and logits.dim() == 2 and target.dtype == torch.int64
+    if logits.stride(1) != 1:
+        logits = logits.contiguous()
+    target = target.contiguous()
+    rng = torch.empty(4, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_cm_update_logits",
+            lib.te_cm_update_logits(
+                logits.data_ptr(), logits.stride(0), target.data_ptr(), logits.shape[0], num_classes,
+                cm.data_ptr(), rng.data_ptr(), _stream_ptr(dev),
+            ),
+        )
+    return rng
+
+
+# ----------------------------------------------------------------------------- K3
+def binned_hist_update_(
+    hist: torch.Tensor, x: torch.Tensor, target: torch.Tensor, threshold: torch.Tensor
+) -> None:
+    """hist (int64 [tasks, T+1, 2], in place) += (bucket, label) counts of x/target
+    ((n,) or (tasks, n), float32 / int64)."""
+    lib = N.load()
+    dev = _require_cuda(hist, x, target, threshold)
+    T = threshold.numel()
+    assert x.dtype == torch.float32 and target.dtype == torch.int64
+    assert threshold.dtype == torch.float32 and threshold.is_contiguous()
+    x, target = x.contiguous(), target.contiguous()
+    tasks = 1 if x.dim() == 1 else x.shape[0]
+    n = x.shape[-1]
+    assert hist.dtype == torch.int64 and hist.is_contiguous() and hist.numel() == tasks * (T + 1) * 2
+    scratch = _scratch(lib.te_binned_scratch_bytes(T), dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_binned_hist_update",
+            lib.te_binned_hist_update(
+                x.data_ptr(), n, target.data_ptr(), n, n, tasks, threshold.data_ptr(), T,
+                hist.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev),
+            ),
+        )
+
+
+def binned_counts(hist: torch.Tensor, T: int, want_fn: bool = True):
+    """(num_tp, num_fp, num_fn) int64 [tasks, T] from the (bucket, label) histogram."""
+    lib = N.load()
+    dev = _require_cuda(hist)
+    tasks = hist.numel() // ((T + 1) * 2)
+    tp = torch.empty((tasks, T), dtype=torch.int64, device=dev)
+    fp = torch.empty_like(tp)
+    fn = torch.empty_like(tp) if want_fn else None
+    with torch.cuda.device(dev):
+        N.check(
+            "te_binned_counts",
+            lib.te_binned_counts(hist.data_ptr(), T, tasks, tp.data_ptr(), fp.data_ptr(), _ptr(fn), _stream_ptr(dev)),
+        )
+    return tp, fp, fn
+
+
+def binned_integrate(tp: torch.Tensor, fp: torch.Tensor, fn: Optional[torch.Tensor], mode: int) -> torch.Tensor:
+    lib = N.load()
+    dev = _require_cuda(tp, fp, fn)
+    tasks, T = tp.shape
+    out = torch.empty(tasks, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_binned_integrate",
+            lib.te_binned_integrate(tp.data_ptr(), fp.data_ptr(), _ptr(fn), T, tasks, mode, out.data_ptr(), _stream_ptr(dev)),
+        )
+    return out
+
+
+# ----------------------------------------------------------------------------- K1
+def _binary_rank(fn_name: str, score: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+    lib = N.load()
+    dev = _require_cuda(score, target)
+    assert score.dim() == 1 and score.shape == target.shape and score.dtype == torch.float32
+    score, target = score.contiguous(), target.contiguous()
+    code = _DTYPE_CODE[target.dtype]
+    n = score.numel()
+    scratch = _scratch(lib.te_binary_rank_scratch_bytes(n), dev)
+    out = torch.empty(8, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        N.check(
+            fn_name,
+            getattr(lib, fn_name)(
+                score.data_ptr(), target.data_ptr(), code, n, out.data_ptr(), scratch.data_ptr(),
+                scratch.numel(), _stream_ptr(dev),
+            ),
+        )
+    return out
+
+
+def binary_auroc_packed(score: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+    """float64[8] device tensor: [auroc, #pos, #neg, 2U, flags, ...] (see te_binary_auroc)."""
+    return _binary_rank("te_binary_auroc", score, target)
+
+
+def binary_auprc_packed(score: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+    return _binary_rank("te_binary_auprc", score, target)
+
+
+def sort_u32(keys: torch.Tensor, vals: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """Ascending stable sort of uint32 keys held in an int32/uint32 tensor (bit pattern)."""
+    lib = N.load()
+    dev = _require_cuda(keys, vals)
+    assert keys.dim() == 1 and keys.element_size() == 4 and keys.is_contiguous()
+    n = keys.numel()
+    out_k = torch.empty_like(keys)
+    out_v = torch.empty_like(vals) if vals is not None else None
+    scratch = _scratch(lib.te_sort_u32_scratch_bytes(n, 1 if vals is not None else 0), dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_sort_u32",
+            lib.te_sort_u32(
+                keys.data_ptr(), out_k.data_ptr(), _ptr(vals), _ptr(out_v), n, scratch.data_ptr(),
+                scratch.numel(), _stream_ptr(dev),
+            ),
+        )
+    return out_k, out_v
