@@ -45,6 +45,16 @@ TE_API int te_abi_version(void);
 /* Static description of a status code returned by any entry point. */
 TE_API const char* te_status_string(int status);
 
+/* Per-kernel timing for bench.py (no counterpart in the reference; off by default).  While
+ * enabled, every kernel launch made by this library is bracketed by CUDA events recorded on the
+ * launching stream.  te_profile_read() waits for those events and returns the number of distinct
+ * kernel names n (<= max_entries): names is filled with n newline-terminated names,
+ * total_ms[i] / launches[i] with the summed duration and launch count of name i.
+ * te_profile_enable(0 or 1) also discards what was recorded so far. */
+TE_API int te_profile_enable(int on);
+TE_API int te_profile_read(char* names, size_t names_bytes, double* total_ms, int64_t* launches,
+                           int32_t max_entries);
+
 /* ------------------------------------------------------------------------------------------
  * K4  confusion-matrix counting
  * replaces functional/classification/confusion_matrix.py:219-234 (`_update`: vstack +

@@ -23,6 +23,8 @@ _vp, _i32, _i64, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_size_t
 SIGNATURES = {
     "te_abi_version": (C.c_int, []),
     "te_status_string": (C.c_char_p, [C.c_int]),
+    "te_profile_enable": (C.c_int, [C.c_int]),
+    "te_profile_read": (C.c_int, [C.c_char_p, _sz, _vp, _vp, _i32]),
     "te_cm_scratch_bytes": (_sz, [_i32, _i32]),
     "te_cm_update": (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _vp, _sz, _i32, _vp]),
     "te_cm_update_logits": (C.c_int, [_vp, _i64, _vp, _i64, _i32, _vp, _vp, _vp]),

@@ -10,6 +10,7 @@
 // read once with 128-bit loads (12 B / score) and the per-CTA counters are merged
 // into the caller's int64 histogram with one RED per non-empty bin.
 #include "common.cuh"
+#include "prof.cuh"
 
 namespace te {
 namespace {
@@ -268,7 +269,10 @@ extern "C" int te_binned_hist_update(const float* x, int64_t x_task_stride, cons
   const int T = num_thresholds;
   const BinGeom g = binned_geom(T);
   uint32_t* lut = (uint32_t*)scratch;
-  binned_lut_kernel<<<(g.cells + 1 + 255) / 256, 256, 0, st>>>(threshold, T, lut, g.cells);
+  {
+    TE_PROF("binned_lut", st);
+    binned_lut_kernel<<<(g.cells + 1 + 255) / 256, 256, 0, st>>>(threshold, T, lut, g.cells);
+  }
   TE_LAUNCH_CHECK();
   int sms = 0;
   TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
@@ -287,6 +291,7 @@ extern "C" int te_binned_hist_update(const float* x, int64_t x_task_stride, cons
   dim3 grid(gx, num_tasks);
   unsigned long long* h = (unsigned long long*)hist;
   const long long* tg = (const long long*)target;
+  TE_PROF(g.smem ? "binned_hist_smem" : "binned_hist_global", st);
   if (g.smem) {
     if (vec) {
       TE_CUDA_TRY(cudaFuncSetAttribute(binned_hist_kernel<4, true>,
@@ -315,6 +320,7 @@ extern "C" int te_binned_counts(const int64_t* hist, int32_t num_thresholds, int
                                 int64_t* num_tp, int64_t* num_fp, int64_t* num_fn, void* stream) {
   if (!hist || !num_tp || !num_fp || num_thresholds < 1 || num_tasks < 1)
     return TE_ERR_INVALID_ARGUMENT;
+  TE_PROF("binned_counts", (cudaStream_t)stream);
   binned_counts_kernel<<<num_tasks, kBinBlock, 0, (cudaStream_t)stream>>>(
       (const long long*)hist, num_thresholds, (long long*)num_tp, (long long*)num_fp,
       (long long*)num_fn);
@@ -329,6 +335,7 @@ extern "C" int te_binned_integrate(const int64_t* num_tp, const int64_t* num_fp,
       (mode != TE_BINNED_AUROC && mode != TE_BINNED_AUPRC) ||
       (mode == TE_BINNED_AUPRC && !num_fn))
     return TE_ERR_INVALID_ARGUMENT;
+  TE_PROF("binned_integrate", (cudaStream_t)stream);
   binned_integrate_kernel<<<num_tasks, kBinBlock, 0, (cudaStream_t)stream>>>(
       (const long long*)num_tp, (const long long*)num_fp, (const long long*)num_fn,
       num_thresholds, mode, out);

@@ -9,6 +9,7 @@
 //   * fire-and-forget RED.ADD into the L2-resident C*C matrix (large C: 10^6 bins at C=1000).
 // Algorithmic traffic: 16 B / sample.
 #include "common.cuh"
+#include "prof.cuh"
 
 namespace te {
 namespace {
@@ -270,19 +271,25 @@ static int cm_launch(const long long* pred, const long long* target, int64_t n, 
   if (want < 1) want = 1;
   const int grid = (int)(want < (int64_t)sms * 8 ? want : (int64_t)sms * 8);
   switch (v) {
-    case TE_CM_GLOBAL64:
+    case TE_CM_GLOBAL64: {
+      TE_PROF("cm_global64", st);
       cm_global_kernel<VEC, unsigned long long>
           <<<grid, kCmBlock, 0, st>>>(pred, target, n, (uint32_t)C, cm, range);
       break;
+    }
     case TE_CM_GLOBAL32: {
       // int32 bins hold at most 2^31 hits: feed the stream in slices.
       const int64_t slice = (int64_t)1 << 30;
       for (int64_t off = 0; off < n; off += slice) {
         const int64_t len = (n - off) < slice ? (n - off) : slice;
         TE_CUDA_TRY(cudaMemsetAsync(scratch, 0, (size_t)nbins * 4, st));
-        cm_global_kernel<VEC, uint32_t>
-            <<<grid, kCmBlock, 0, st>>>(pred + off, target + off, len, (uint32_t)C,
-                                        (uint32_t*)scratch, range);
+        {
+          TE_PROF("cm_global32", st);
+          cm_global_kernel<VEC, uint32_t>
+              <<<grid, kCmBlock, 0, st>>>(pred + off, target + off, len, (uint32_t)C,
+                                          (uint32_t*)scratch, range);
+        }
+        TE_PROF("cm_fold32", st);
         cm_fold32_kernel<<<(nbins + 255) / 256 < 1184 ? (nbins + 255) / 256 : 1184, 256, 0, st>>>(
             (const uint32_t*)scratch, cm, nbins);
       }
@@ -294,6 +301,7 @@ static int cm_launch(const long long* pred, const long long* target, int64_t n, 
         TE_CUDA_TRY(cudaFuncSetAttribute(cm_smem_kernel<VEC, 32>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
       const int g = grid < sms * 4 ? grid : sms * 4;
+      TE_PROF("cm_smem_repl", st);
       cm_smem_kernel<VEC, 32><<<g, kCmBlock, sh, st>>>(pred, target, n, (uint32_t)C, cm, range);
       break;
     }
@@ -303,6 +311,7 @@ static int cm_launch(const long long* pred, const long long* target, int64_t n, 
         TE_CUDA_TRY(cudaFuncSetAttribute(cm_smem_kernel<VEC, 1>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
       const int g = grid < sms * 4 ? grid : sms * 4;
+      TE_PROF("cm_smem", st);
       cm_smem_kernel<VEC, 1><<<g, kCmBlock, sh, st>>>(pred, target, n, (uint32_t)C, cm, range);
       break;
     }
@@ -355,11 +364,13 @@ extern "C" int te_cm_update_logits(const float* logits, int64_t ld, const int64_
     const int rows_per_tile = kLogitsTileFloats / (int)C;
     const int64_t ntiles = (n + rows_per_tile - 1) / rows_per_tile;
     const int grid = (int)(ntiles < (int64_t)sms * 8 ? ntiles : (int64_t)sms * 8);
+    TE_PROF("cm_logits_tile", st);
     cm_logits_tile_kernel<unsigned long long><<<grid, kCmBlock, 0, st>>>(
         logits, ld, (const long long*)target, n, C, (unsigned long long*)cm, (long long*)range);
   } else {
     const int64_t want = (n + (kCmBlock / kWarp) - 1) / (kCmBlock / kWarp);
     const int grid = (int)(want < (int64_t)sms * 8 ? want : (int64_t)sms * 8);
+    TE_PROF("cm_logits_warp", st);
     cm_logits_warp_kernel<unsigned long long><<<grid, kCmBlock, 0, st>>>(
         logits, ld, (const long long*)target, n, C, (unsigned long long*)cm, (long long*)range);
   }

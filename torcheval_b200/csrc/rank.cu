@@ -17,6 +17,7 @@
 //
 // Bytes per score (SURVEY.md §8d formula, b_in = 12, r = 4, P = 4): 16 + 32 + 4 = 52.
 #include "rank_sort.cuh"
+#include "prof.cuh"
 
 namespace te {
 namespace {
@@ -483,7 +484,10 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
   uint32_t* ticket = at<uint32_t>(scratch, p.off_ticket);
   uint32_t* lb = at<uint32_t>(scratch, p.off_lookback);
-  digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 4);
+  {
+    TE_PROF("digit_scan", st);
+    digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 4);
+  }
   TE_LAUNCH_CHECK();
   constexpr size_t smem = onesweep_smem_bytes<uint32_t>();
   TE_CUDA_TRY(cudaFuncSetAttribute(onesweep_pass_kernel<uint32_t, true>,
@@ -496,6 +500,7 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
     uint32_t* kout = (pass & 1) ? k_y : k_x;
     uint32_t* vout = (pass & 1) ? v_y : v_x;
     uint32_t* lbp = lb + (size_t)pass * p.sort_tiles * kRadix;
+    TE_PROF(v_in0 ? "onesweep_pass_pairs" : "onesweep_pass_keys", st);
     if (v_in0)
       onesweep_pass_kernel<uint32_t, true><<<p.sort_tiles, kSortBlock, smem, st>>>(
           kin, kout, vin, vout, p.n, 8 * pass, hist + pass * kRadix, lbp, ticket + pass);
@@ -521,6 +526,7 @@ int launch_ingest(const float* score, const void* target, const uint32_t* raw, c
   if (grid < 1) grid = 1;
   uintptr_t a = (uintptr_t)score | (uintptr_t)target | (uintptr_t)raw;
   const bool vec_ok = (a & 15) == 0;
+  TE_PROF(MODE == kPacked ? "rank_ingest_packed" : (MODE == kIndexed ? "rank_ingest_indexed" : "rank_hist_keys"), st);
   kern<<<grid, kIngestBlock, kIngestSmem, st>>>(score, (const TargetT*)target, raw, p.n, vec_ok,
                                                  keys_out, vals_out, at<uint32_t>(scratch, p.off_hist),
                                                  at<RankScalars>(scratch, p.off_scal));
@@ -572,12 +578,18 @@ int binary_rank_packed(const float* score, const void* target, int32_t dt, int64
   const RankScalars* scal = at<RankScalars>(scratch, p.off_scal);
   const uint32_t ftiles = n > 0 ? p.fin_tiles : 0;
   if (mode == 0) {
-    if (ftiles)
+    if (ftiles) {
+      TE_PROF("rank_final_auroc", st);
       rank_final_kernel<0><<<ftiles, kFinBlock, 0, st>>>(ka, p.n, agg, inc, ticket, scal, partial);
+    }
+    TE_PROF("rank_reduce", st);
     rank_reduce_kernel<0><<<1, 1024, 0, st>>>(partial, ftiles, p.n, scal, out);
   } else {
-    if (ftiles)
+    if (ftiles) {
+      TE_PROF("rank_final_auprc", st);
       rank_final_kernel<1><<<ftiles, kFinBlock, 0, st>>>(ka, p.n, agg, inc, ticket, scal, partial);
+    }
+    TE_PROF("rank_reduce", st);
     rank_reduce_kernel<1><<<1, 1024, 0, st>>>(partial, ftiles, p.n, scal, out);
   }
   TE_LAUNCH_CHECK();
