@@ -146,6 +146,18 @@ TE_API int te_binary_auroc(const float* score, const void* target, int32_t targe
 TE_API int te_binary_auprc(const float* score, const void* target, int32_t target_dtype, int64_t n,
                            double* out, void* scratch, size_t scratch_bytes, void* stream);
 
+/* General variants: any float32 score (negative values, mixed signs), soft labels (AUROC uses
+ * w*t and w*(1-t) as auroc.py:129-130), optional float64 per-sample weights (NULL = 1).  Same
+ * out[] layout with [1] = sum w*t, [2] = sum w*(1-t), [3] = the signed cross term; [4] = 0.
+ * Sorts (key, index) pairs and gathers target/weight by index in the fused pass. */
+TE_API size_t te_binary_rank_general_scratch_bytes(int64_t n);
+TE_API int te_binary_auroc_general(const float* score, const void* target, int32_t target_dtype,
+                                   const double* weight, int64_t n, double* out, void* scratch,
+                                   size_t scratch_bytes, void* stream);
+TE_API int te_binary_auprc_general(const float* score, const void* target, int32_t target_dtype,
+                                   int64_t n, double* out, void* scratch, size_t scratch_bytes,
+                                   void* stream);
+
 /* The sort on its own: ascending, stable, 32-bit keys with an optional 32-bit payload
  * (vals_in/vals_out both NULL or both set).  Replaces torch.sort at auroc.py:121. */
 TE_API size_t te_sort_u32_scratch_bytes(int64_t n, int32_t with_values);

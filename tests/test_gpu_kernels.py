@@ -354,3 +354,77 @@ def test_rank_large_closed_form(ops):
     pos = torch.bincount(lev[y == 1], minlength=G).cpu().numpy()
     assert a[4] == 0 and a[1] == pos.sum() and a[2] == neg.sum()
     close(a[0], oracle.auroc_from_level_hist(neg, pos), 1e-9)
+
+
+# =============================================================================== K1: general path
+def run_general(ops, x, y, w=None, ydtype=None):
+    X = dev(x, torch.float32)
+    Y = dev(y, ydtype)
+    W = None if w is None else dev(w, torch.float64)
+    a = ops.binary_auroc_general(X, Y, W).cpu().numpy()
+    return a
+
+
+def test_general_golden(ops, golden):
+    for name in golden.cases("binary"):
+        c = golden.case(f"binary/{name}")
+        a = run_general(ops, c["x"], c["y"])
+        close(a[0], c["auroc_f64"], RTOL64)
+        assert a[1] == c["y"].sum() and a[2] == (1 - c["y"]).sum()
+        p = ops.binary_auprc_general(dev(c["x"], torch.float32), dev(c["y"])).cpu().numpy()
+        close(p[0], c["auprc"], RTOL32)
+        if c["y"].sum() == 0:
+            assert np.signbit(p[0])
+    for name in golden.cases("binary_weighted"):
+        c = golden.case(f"binary_weighted/{name}")
+        a = run_general(ops, c["x"], c["y"], c["w"])
+        close(a[0], c["auroc"], RTOL64)
+
+
+@pytest.mark.parametrize("n,kind", [(2049, "logits"), ((1 << 20) + 3, "logits"), (1 << 19, "ties"), (100000, "soft")])
+def test_general_random_vs_oracle(ops, n, kind):
+    rs = np.random.default_rng(n % 97 + len(kind))
+    w = rs.random(n) * 2
+    if kind == "logits":
+        x = (rs.standard_normal(n) * 4).astype(np.float32)
+        y = rs.integers(0, 2, n).astype(np.float64)
+    elif kind == "ties":
+        x = (rs.integers(-50, 50, n) / 7).astype(np.float32)
+        y = rs.integers(0, 2, n).astype(np.float64)
+    else:
+        x = (rs.integers(-500, 500, n) / 77).astype(np.float32)
+        y = rs.random(n)
+    for weight in (None, w):
+        a = run_general(ops, x, y, weight, torch.float64)
+        v, tp, fp = oracle.binary_auroc(x, y, weight)
+        close(a[0], v, RTOL64)
+        close(a[1], tp, 1e-9)
+        close(a[2], fp, 1e-9)
+    if kind != "soft":
+        yi = y.astype(np.int64)
+        p = ops.binary_auprc_general(dev(x), dev(yi)).cpu().numpy()
+        close(p[0], oracle.binary_auprc(x, yi), RTOL64)
+        # packed and general agree where both apply
+        xp = np.abs(x)
+        a1 = ops.binary_auroc_packed(dev(xp), dev(yi)).cpu().numpy()
+        a2 = run_general(ops, xp, yi)
+        assert a1[4] == 0
+        close(a1[0], a2[0], 1e-12)
+
+
+def test_functional_binary_auroc_dispatch(ops, golden):
+    from torcheval_b200.metrics.functional.classification.auroc import binary_auroc
+
+    for name in ("uniform", "logits", "ties64", "all_pos"):
+        c = golden.case(f"binary/{name}")
+        got = binary_auroc(torch.as_tensor(c["x"]), torch.as_tensor(c["y"]))  # host tensors in, host out
+        assert got.device.type == "cpu" and got.dtype == torch.float64 and got.shape == ()
+        close(got.item(), c["auroc_f64"], RTOL64)
+    c = golden.case("binary_weighted/soft")
+    got = binary_auroc(torch.as_tensor(c["x"]).cuda(), torch.as_tensor(c["y"]).cuda(), weight=torch.as_tensor(c["w"]).cuda())
+    assert got.is_cuda
+    close(got.item(), c["auroc"], RTOL64)
+    c = golden.case("binary_multitask/t3")
+    got = binary_auroc(torch.as_tensor(c["x"]), torch.as_tensor(c["y"]), num_tasks=3)
+    assert got.shape == (3,)
+    close(got.numpy(), c["auroc"], RTOL64)

