@@ -65,7 +65,8 @@ enum {
   TE_CM_GLOBAL64 = 1,  /* RED.ADD.64 straight into `cm` (L2 resident)            */
   TE_CM_GLOBAL32 = 2,  /* RED.ADD.32 into scratch bins, folded into `cm`         */
   TE_CM_SMEM_REPL = 3, /* per-CTA smem bins, replicated per lane (tiny C)        */
-  TE_CM_SMEM = 4       /* per-CTA smem bins (C*C*4 bytes must fit in smem)       */
+  TE_CM_SMEM = 4,      /* per-CTA smem bins (C*C*4 bytes must fit in smem)       */
+  TE_CM_CLUSTER = 5    /* bins spread over the distributed smem of a 16/8-CTA cluster */
 };
 
 TE_API size_t te_cm_scratch_bytes(int32_t num_classes, int32_t variant);
@@ -101,6 +102,14 @@ TE_API int te_binned_hist_update(const float* x, int64_t x_task_stride, const in
                           int64_t target_task_stride, int64_t n, int32_t num_tasks,
                           const float* threshold, int32_t num_thresholds, int64_t* hist,
                           void* scratch, size_t scratch_bytes, void* stream);
+
+/* (n, C) row-major float32 scores.  multilabel == 0: target is (n,) int64 and
+ * label = (target[i] == c) (binned_precision_recall_curve.py:239-291); multilabel != 0: target
+ * is (n, C) int64 and label = (target[i, c] != 0) (:434-486).  hist is int64 [C][T + 1][2]. */
+TE_API int te_binned_hist2d_update(const float* x, const int64_t* target, int64_t n,
+                                   int32_t num_classes, int32_t multilabel, const float* threshold,
+                                   int32_t num_thresholds, int64_t* hist, void* scratch,
+                                   size_t scratch_bytes, void* stream);
 
 /* Suffix sums: num_tp[task][j] = #{label 1, x >= threshold[j]}, num_fp likewise for label 0,
  * num_fn = positives - num_tp (binned_precision_recall_curve.py:102-110).  num_fn may be NULL.

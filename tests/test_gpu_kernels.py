@@ -47,6 +47,8 @@ def cm_variants(C):
         v.append(3)
     if C * C * 4 <= 200 * 1024:
         v.append(4)
+    if C >= 300:
+        v.append(5)  # cluster / distributed-smem bins
     return v
 
 
@@ -60,7 +62,7 @@ def test_cm_golden_all_variants(ops, golden):
             assert rng[0] == np.iinfo(np.int64).max and rng[1] == np.iinfo(np.int64).min
 
 
-@pytest.mark.parametrize("C,n", [(2, 100003), (10, 1 << 20), (16, 999), (100, 300001), (1000, (1 << 21) + 3)])
+@pytest.mark.parametrize("C,n", [(2, 100003), (10, 1 << 20), (16, 999), (100, 300001), (1000, (1 << 21) + 3), (300, 70001), (1500, 1 << 20)])
 def test_cm_random_vs_oracle(ops, C, n):
     rs = np.random.default_rng(C * 7 + n)
     p = rs.integers(0, C, n)
@@ -80,7 +82,7 @@ def test_cm_skewed_diagonal(ops):
     p[: n // 4] = 7
     t[: n // 4] = 7  # one very hot bin
     want, _, _ = oracle.confusion_matrix(p, t, C)
-    for v in (1, 2):
+    for v in (1, 2, 5):
         cm, _ = run_cm(ops, dev(p), dev(t), C, v)
         np.testing.assert_array_equal(cm, want)
 

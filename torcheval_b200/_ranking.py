@@ -64,3 +64,52 @@ def _binary_auroc_row(x: torch.Tensor, t: torch.Tensor, w: Optional[torch.Tensor
         if flags == 0:
             return out[0].clone()
     return ops.binary_auroc_general(x, t, w)[0].clone()
+
+
+def _binary_auprc_row(x: torch.Tensor, t: torch.Tensor) -> torch.Tensor:
+    if t.dtype in ops._DTYPE_CODE:
+        out = ops.binary_auprc_packed(x, t)
+        if int(out[4].item()) == 0:
+            return out[0].clone()
+    return ops.binary_auprc_general(x, t)[0].clone()
+
+
+def binary_auprc(input: torch.Tensor, target: torch.Tensor, num_tasks: int = 1) -> torch.Tensor:
+    """float32 like the reference (auprc.py:239-251): () for 1-D input with num_tasks == 1,
+    otherwise (num_tasks,)."""
+    out_dev = input.device
+    dev = compute_device(input)
+    x = _as_f32_scores(stage(input, dev))
+    t = stage(target, dev)
+    if num_tasks == 1 and x.dim() == 1:
+        return _binary_auprc_row(x, t).to(torch.float32).to(out_dev)
+    vals = [_binary_auprc_row(x[k], t[k]) for k in range(num_tasks)]
+    return torch.stack(vals).to(torch.float32).to(out_dev)
+
+
+def _one_vs_rest(input: torch.Tensor, target: torch.Tensor, auprc: bool, multilabel: bool) -> torch.Tensor:
+    """Per class / per label values (float64, on the compute device).  Columns are transposed to
+    contiguous rows once; positives are target == c (multiclass) or target[:, c] == 1."""
+    dev = compute_device(input)
+    x = _as_f32_scores(stage(input, dev))
+    t = stage(target, dev)
+    xt = x.t().contiguous()
+    C = xt.shape[0]
+    vals = []
+    for c in range(C):
+        lab = (t[:, c] == 1) if multilabel else (t == c)
+        row = _binary_auprc_row(xt[c], lab) if auprc else _binary_auroc_row(xt[c], lab, None)
+        vals.append(row)
+    return torch.stack(vals)
+
+
+def multiclass_auroc(input: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+    return _one_vs_rest(input, target, auprc=False, multilabel=False)
+
+
+def multiclass_auprc(input: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+    return _one_vs_rest(input, target, auprc=True, multilabel=False)
+
+
+def multilabel_auprc(input: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+    return _one_vs_rest(input, target, auprc=True, multilabel=True)

@@ -243,6 +243,90 @@ __global__ void __launch_bounds__(kBinBlock)
   }
 }
 
+
+// ---- (N, C) inputs: multiclass (label = target[n] == c) and multilabel (label = target[n, c])
+// binned counting (binned_precision_recall_curve.py:239-291 and :434-486, the "memory"
+// formulations; the "vectorized" ones :214-236 / :406-431 count the same thing).
+// hist[c][bucket][label]; thresholds and lookup table in smem; bins in smem when C*(T+1)*2 u32
+// fit, otherwise RED into the int64 histogram.
+template <bool MULTILABEL, bool SMEM_HIST>
+__global__ void __launch_bounds__(kBinBlock, 1)
+    binned_hist2d_kernel(const float* __restrict__ x, const long long* __restrict__ target,
+                         int64_t n, int C, const float* __restrict__ thr, int T,
+                         const uint32_t* __restrict__ lut, int G, bool vec_ok,
+                         unsigned long long* hist) {
+  extern __shared__ __align__(16) unsigned char smraw[];
+  float* sthr = reinterpret_cast<float*>(smraw);
+  uint16_t* slut = reinterpret_cast<uint16_t*>(sthr + T);
+  uint32_t* sh = reinterpret_cast<uint32_t*>(smraw + (((size_t)4 * T + (size_t)2 * (G + 1) + 15) & ~(size_t)15));
+  const int nbins = C * (T + 1) * 2;
+  for (int i = threadIdx.x; i < T; i += blockDim.x) sthr[i] = thr[i];
+  for (int i = threadIdx.x; i <= G; i += blockDim.x) slut[i] = (uint16_t)lut[i];
+  if (SMEM_HIST)
+    for (int i = threadIdx.x; i < nbins; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  const float lo = sthr[0], hi = sthr[T - 1];
+  const float scale = cell_scale(lo, hi, G);
+
+  const int64_t total = n * C;
+  const int64_t ngroups = (total + 3) / 4;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g < ngroups) {
+    // (row, col) of the first element of my group, advanced incrementally
+    int64_t row = (g * 4) / C;
+    int col = (int)((g * 4) - row * C);
+    const int64_t step = stride * 4;
+    const int64_t step_rows = step / C;
+    const int step_cols = (int)(step - step_rows * C);
+    for (; g < ngroups; g += stride) {
+      const int64_t e0 = g * 4;
+      const int cnt = (int)min((int64_t)4, total - e0);
+      float xv[4];
+      if (cnt == 4 && vec_ok) {
+        const int4 a = ld_stream_v4(x + e0);
+        xv[0] = __int_as_float(a.x), xv[1] = __int_as_float(a.y);
+        xv[2] = __int_as_float(a.z), xv[3] = __int_as_float(a.w);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) xv[j] = j < cnt ? x[e0 + j] : 0.f;
+      }
+      int64_t r = row;
+      int c = col;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (j < cnt) {
+          const long long tv = MULTILABEL ? target[e0 + j] : target[r];
+          const int label = MULTILABEL ? (tv != 0 ? 1 : 0) : (tv == (long long)c ? 1 : 0);
+          const int b = bucket_of<uint16_t>(xv[j], lo, hi, scale, G, T, sthr, slut);
+          const int bin = (c * (T + 1) + b) * 2 + label;
+          if (SMEM_HIST)
+            atomicAdd(sh + bin, 1u);
+          else
+            atomicAdd(hist + bin, 1ull);
+          if (++c == C) {
+            c = 0;
+            ++r;
+          }
+        }
+      }
+      row += step_rows;
+      col += step_cols;
+      if (col >= C) {
+        col -= C;
+        ++row;
+      }
+    }
+  }
+  if (SMEM_HIST) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < nbins; i += blockDim.x) {
+      const uint32_t v = sh[i];
+      if (v) atomicAdd(hist + i, (unsigned long long)v);
+    }
+  }
+}
+
 }  // namespace
 }  // namespace te
 
@@ -339,6 +423,64 @@ extern "C" int te_binned_integrate(const int64_t* num_tp, const int64_t* num_fp,
   binned_integrate_kernel<<<num_tasks, kBinBlock, 0, (cudaStream_t)stream>>>(
       (const long long*)num_tp, (const long long*)num_fp, (const long long*)num_fn,
       num_thresholds, mode, out);
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+extern "C" int te_binned_hist2d_update(const float* x, const int64_t* target, int64_t n,
+                                       int32_t num_classes, int32_t multilabel,
+                                       const float* threshold, int32_t num_thresholds,
+                                       int64_t* hist, void* scratch, size_t scratch_bytes,
+                                       void* stream) {
+  if (n < 0 || num_classes < 1 || num_thresholds < 1 || !threshold || !hist)
+    return TE_ERR_INVALID_ARGUMENT;
+  if (n > 0 && (!x || !target)) return TE_ERR_INVALID_ARGUMENT;
+  if (!scratch || scratch_bytes < te_binned_scratch_bytes(num_thresholds))
+    return TE_ERR_SCRATCH_TOO_SMALL;
+  const int T = num_thresholds;
+  const BinGeom g = binned_geom(T);
+  const size_t tab = (((size_t)4 * T + (size_t)2 * (g.cells + 1) + 15) & ~(size_t)15);
+  if (T >= 65536 || tab > kBinSmemBudget) return TE_ERR_UNSUPPORTED;
+  if ((int64_t)num_classes * (T + 1) * 2 > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  if (n == 0) return TE_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  uint32_t* lut = (uint32_t*)scratch;
+  {
+    TE_PROF("binned_lut", st);
+    binned_lut_kernel<<<(g.cells + 1 + 255) / 256, 256, 0, st>>>(threshold, T, lut, g.cells);
+  }
+  TE_LAUNCH_CHECK();
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  const size_t hist_bytes = (size_t)num_classes * (T + 1) * 2 * 4;
+  const bool smem_hist = tab + hist_bytes <= kBinSmemBudget;
+  const size_t smem = tab + (smem_hist ? hist_bytes : 0);
+  const int64_t ngroups = (n * num_classes + 3) / 4;
+  int64_t want = (ngroups + kBinBlock * 2 - 1) / (kBinBlock * 2);
+  const int grid = (int)(want < 1 ? 1 : (want < sms ? want : sms));
+  const bool vec_ok = ((uintptr_t)x & 15) == 0;
+  unsigned long long* h = (unsigned long long*)hist;
+  const long long* tg = (const long long*)target;
+  TE_PROF(smem_hist ? "binned_hist2d_smem" : "binned_hist2d_global", st);
+#define TE_LAUNCH_2D(ML, SH)                                                                     \
+  do {                                                                                           \
+    TE_CUDA_TRY(cudaFuncSetAttribute(binned_hist2d_kernel<ML, SH>,                               \
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));   \
+    binned_hist2d_kernel<ML, SH><<<grid, kBinBlock, smem, st>>>(x, tg, n, num_classes, threshold, \
+                                                                 T, lut, g.cells, vec_ok, h);    \
+  } while (0)
+  if (multilabel) {
+    if (smem_hist)
+      TE_LAUNCH_2D(true, true);
+    else
+      TE_LAUNCH_2D(true, false);
+  } else {
+    if (smem_hist)
+      TE_LAUNCH_2D(false, true);
+    else
+      TE_LAUNCH_2D(false, false);
+  }
+#undef TE_LAUNCH_2D
   TE_LAUNCH_CHECK();
   return TE_OK;
 }

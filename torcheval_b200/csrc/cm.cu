@@ -137,6 +137,67 @@ __global__ void __launch_bounds__(kCmBlock)
   }
 }
 
+// Large C on B200: the bins do not fit one SM's shared memory, and RED into L2 tops out near
+// 190 G updates/s chip-wide (profiles/r01_ubench_b200.txt).  A thread-block cluster of S CTAs owns
+// S * kClusterBinsPerCta bins in its *distributed* shared memory: bin b lives in the smem of
+// cluster rank b / kClusterBinsPerCta and is updated with red.shared::cluster; only bins beyond
+// the cluster's capacity fall back to RED in L2.  Each cluster keeps private counts for the
+// samples it streams and folds them into `cm` once at the end.
+constexpr uint32_t kClusterBinsPerCta = 57344;  // 224 KB of u32 counters per CTA
+constexpr int kClusterBlock = 1024;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+struct ClusterSink {
+  uint32_t smem_base;   // shared::cta address of this CTA's bin array
+  uint32_t dsm_bins;    // bins held in distributed shared memory (multiple of kClusterBinsPerCta)
+  unsigned long long* cm;
+  __device__ __forceinline__ void add(uint32_t bin) const {
+    if (bin < dsm_bins) {
+      const uint32_t owner = bin / kClusterBinsPerCta;
+      const uint32_t off = bin - owner * kClusterBinsPerCta;
+      uint32_t raddr;
+      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(raddr) : "r"(smem_base + off * 4u), "r"(owner));
+      asm volatile("red.relaxed.cluster.shared::cluster.add.u32 [%0], %1;" ::"r"(raddr), "r"(1u) : "memory");
+    } else {
+      atomicAdd(cm + bin, 1ull);
+    }
+  }
+};
+
+template <int VEC>
+__global__ void __launch_bounds__(kClusterBlock, 1)
+    cm_cluster_kernel(const long long* __restrict__ pred, const long long* __restrict__ target,
+                      int64_t n, uint32_t C, unsigned long long* cm, long long* range) {
+  extern __shared__ __align__(16) uint32_t shbins[];
+  const uint32_t rank = cluster_ctarank(), csize = cluster_nctarank();
+  const uint32_t nbins = C * C;
+  for (uint32_t i = threadIdx.x; i < kClusterBinsPerCta; i += blockDim.x) shbins[i] = 0;
+  cluster_sync_all();  // every CTA's bins are zero before anybody adds remotely
+  uint32_t dsm = csize * kClusterBinsPerCta;
+  ClusterSink sink{(uint32_t)__cvta_generic_to_shared(shbins), dsm, cm};
+  RangeReport rr{range};
+  cm_stream<VEC, 2>(pred, target, n, C, sink, rr);
+  cluster_sync_all();  // all remote adds into my bins have landed
+  const uint32_t first = rank * kClusterBinsPerCta;
+  for (uint32_t i = threadIdx.x; i < kClusterBinsPerCta; i += blockDim.x) {
+    const uint32_t v = shbins[i];
+    if (v && first + i < nbins) atomicAdd(cm + first + i, (unsigned long long)v);
+  }
+}
+
 __global__ void cm_fold32_kernel(const uint32_t* __restrict__ bins, unsigned long long* cm,
                                  uint32_t nbins) {
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nbins; i += gridDim.x * blockDim.x)
@@ -313,6 +374,42 @@ static int cm_launch(const long long* pred, const long long* target, int64_t n, 
       const int g = grid < sms * 4 ? grid : sms * 4;
       TE_PROF("cm_smem", st);
       cm_smem_kernel<VEC, 1><<<g, kCmBlock, sh, st>>>(pred, target, n, (uint32_t)C, cm, range);
+      break;
+    }
+    case TE_CM_CLUSTER: {
+      const size_t sh = (size_t)kClusterBinsPerCta * 4;
+      auto kern = cm_cluster_kernel<VEC>;
+      TE_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
+      TE_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      cudaLaunchConfig_t cfg{};
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      cfg.blockDim = dim3(kClusterBlock);
+      cfg.dynamicSmemBytes = sh;
+      cfg.stream = st;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      // largest cluster the device can co-schedule: 16, else 8
+      int csize = 16, nclusters = 0;
+      for (; csize >= 8; csize /= 2) {
+        attr[0].val.clusterDim.x = csize;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.gridDim = dim3(csize);
+        if (cudaOccupancyMaxActiveClusters(&nclusters, kern, &cfg) == cudaSuccess && nclusters > 0) break;
+        (void)cudaGetLastError();
+        nclusters = 0;
+      }
+      if (nclusters <= 0) return TE_ERR_UNSUPPORTED;
+      cfg.gridDim = dim3(nclusters * csize);
+      const long long* a0 = pred;
+      const long long* a1 = target;
+      int64_t a2 = n;
+      uint32_t a3 = (uint32_t)C;
+      unsigned long long* a4 = cm;
+      long long* a5 = range;
+      TE_PROF(csize == 16 ? "cm_cluster16" : "cm_cluster8", st);
+      TE_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, a0, a1, a2, a3, a4, a5));
       break;
     }
     default:

@@ -219,31 +219,75 @@ __device__ __forceinline__ FState f_shfl_up(const FState& v, int o) {
   return u;
 }
 
-// One record per tile and kind (own aggregate / inclusive prefix); written once, then flagged.
-struct alignas(32) ScanRec {
-  unsigned long long flag;
-  unsigned long long w0;  // S | M << 32
-  unsigned long long w1;  // Mp | F << 32
-  unsigned long long pad;
+// One 16-byte record per tile, written twice (own aggregate, then inclusive prefix).  The
+// status sits in the top two bits of BOTH halves, so a reader that catches the two halves of
+// different writes sees mismatching statuses and simply polls again.
+struct alignas(16) ScanRec {
+  unsigned long long lo;  // S | M << 31 | status << 62
+  unsigned long long hi;  // Mp | F << 32 | status << 62
 };
-__device__ __forceinline__ void rec_publish(ScanRec* r, const FState& s) {
-  st_relaxed_u64(&r->w0, (unsigned long long)s.S | ((unsigned long long)s.M << 32));
-  st_relaxed_u64(&r->w1, (unsigned long long)s.Mp | ((unsigned long long)s.F << 32));
-  st_release_u64(&r->flag, 1ull);
+enum : uint32_t { kRecEmpty = 0, kRecAgg = 1, kRecInc = 2 };
+__device__ __forceinline__ void rec_publish(ScanRec* r, const FState& s, uint32_t status) {
+  const unsigned long long lo =
+      (unsigned long long)s.S | ((unsigned long long)s.M << 31) | ((unsigned long long)status << 62);
+  const unsigned long long hi =
+      (unsigned long long)s.Mp | ((unsigned long long)s.F << 32) | ((unsigned long long)status << 62);
+  asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(r), "l"(lo), "l"(hi) : "memory");
 }
-__device__ __forceinline__ bool rec_try(const ScanRec* r, FState& s) {
-  if (ld_acquire_u64(&r->flag) == 0ull) return false;
-  const unsigned long long w0 = ld_relaxed_u64(&r->w0), w1 = ld_relaxed_u64(&r->w1);
-  s.S = (uint32_t)w0;
-  s.M = (uint32_t)(w0 >> 32);
-  s.Mp = (uint32_t)w1;
-  s.F = (uint32_t)(w1 >> 32);
-  return true;
+__device__ __forceinline__ uint32_t rec_load(const ScanRec* r, FState& s) {
+  unsigned long long lo, hi;
+  asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(lo), "=l"(hi) : "l"(r) : "memory");
+  const uint32_t st = (uint32_t)(lo >> 62);
+  if (st != (uint32_t)(hi >> 62)) return kRecEmpty;
+  s.S = (uint32_t)(lo & 0x7fffffffull);
+  s.M = (uint32_t)((lo >> 31) & 0x7fffffffull);
+  s.Mp = (uint32_t)(hi & 0x7fffffffull);
+  s.F = (uint32_t)((hi >> 32) & 1ull);
+  return st;
+}
+__device__ __forceinline__ FState f_shfl_down(const FState& v, int o) {
+  FState u;
+  u.S = __shfl_down_sync(kFull, v.S, o);
+  u.M = __shfl_down_sync(kFull, v.M, o);
+  u.Mp = __shfl_down_sync(kFull, v.Mp, o);
+  u.F = __shfl_down_sync(kFull, v.F, o);
+  return u;
+}
+
+// Warp-wide decoupled look-back: the 32 lanes inspect the 32 preceding tiles at once, the
+// nearest inclusive record ends the walk.  Returns (on lane 0) the state of everything before
+// `tile`.  Called by one full warp.
+__device__ __forceinline__ FState warp_lookback(const ScanRec* rec, uint32_t tile, unsigned lane) {
+  FState e = f_identity();
+  for (int64_t base = (int64_t)tile - 1; base >= 0; base -= 32) {
+    const int64_t idx = base - lane;
+    FState r = f_identity();
+    uint32_t st, incl, need;
+    do {
+      st = idx >= 0 ? rec_load(rec + idx, r) : (uint32_t)kRecInc;
+      if (idx < 0) r = f_identity();
+      incl = __ballot_sync(kFull, st == kRecInc);
+      const uint32_t valid = __ballot_sync(kFull, st != kRecEmpty);
+      // every lane up to and including the nearest inclusive one must be published
+      need = incl ? ((2u << (__ffs(incl) - 1)) - 1u) : kFull;
+      if ((valid & need) == need) break;
+    } while (true);
+    const unsigned first = incl ? (unsigned)(__ffs(incl) - 1) : 31u;
+    if (lane > first) r = f_identity();
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {  // higher lane = earlier tile = left operand
+      const FState u = f_shfl_down(r, o);
+      if (lane + o < 32) r = f_combine(u, r);
+    }
+    e = f_combine(r, e);  // meaningful on lane 0
+    if (incl) break;
+  }
+  return e;
 }
 
 template <int MODE>  // 0: AUROC (u64 partials)  1: AUPRC (double partials)
 __global__ void __launch_bounds__(kFinBlock)
-    rank_final_kernel(const uint32_t* __restrict__ keys, uint32_t n, ScanRec* agg, ScanRec* inc,
+    rank_final_kernel(const uint32_t* __restrict__ keys, uint32_t n, ScanRec* rec,
                       uint32_t* ticket, const RankScalars* __restrict__ scal,
                       unsigned long long* partial) {
   __shared__ FState s_warp[kFinBlock / kWarp];
@@ -309,25 +353,14 @@ __global__ void __launch_bounds__(kFinBlock)
   }
   excl = f_combine(wprefix, excl);
 
-  // decoupled look-back across tiles (one thread walks the chain)
-  if (tid == 0) {
-    rec_publish(agg + tile, tile_agg);
-    FState e = f_identity();
-    for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
-      FState r;
-      bool full = false;
-      for (;;) {
-        if (rec_try(inc + t, r)) {
-          full = true;
-          break;
-        }
-        if (rec_try(agg + t, r)) break;
-      }
-      e = f_combine(r, e);
-      if (full) break;
+  // decoupled look-back across tiles, by warp 0
+  if (warp == 0) {
+    if (lane == 0) rec_publish(rec + tile, tile_agg, kRecAgg);
+    const FState e = warp_lookback(rec, tile, lane);
+    if (lane == 0) {
+      rec_publish(rec + tile, f_combine(e, tile_agg), kRecInc);
+      s_excl = e;
     }
-    rec_publish(inc + tile, f_combine(e, tile_agg));
-    s_excl = e;
   }
   __syncthreads();
   const FState g = f_combine(s_excl, excl);
@@ -466,7 +499,7 @@ RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final)
   p.off_scal = take(sizeof(RankScalars));
   p.off_lookback = take((size_t)4 * p.sort_tiles * kRadix * 4);
   p.off_agg = take(with_final ? (size_t)p.fin_tiles * sizeof(ScanRec) : 0);
-  p.off_inc = take(with_final ? (size_t)p.fin_tiles * sizeof(ScanRec) : 0);
+  p.off_inc = p.off_agg;
   p.zero_bytes = o - p.off_zero;
   p.off_partial = take(with_final ? (size_t)p.fin_tiles * 8 : 0);
   p.total = o;
@@ -571,8 +604,7 @@ int binary_rank_packed(const float* score, const void* target, int32_t dt, int64
     rc = run_passes(p, scratch, ka, kb, ka, nullptr, nullptr, nullptr, st);
     if (rc) return rc;
   }
-  ScanRec* agg = at<ScanRec>(scratch, p.off_agg);
-  ScanRec* inc = at<ScanRec>(scratch, p.off_inc);
+  ScanRec* rec = at<ScanRec>(scratch, p.off_agg);
   uint32_t* ticket = at<uint32_t>(scratch, p.off_ticket) + 4;
   unsigned long long* partial = at<unsigned long long>(scratch, p.off_partial);
   const RankScalars* scal = at<RankScalars>(scratch, p.off_scal);
@@ -580,14 +612,14 @@ int binary_rank_packed(const float* score, const void* target, int32_t dt, int64
   if (mode == 0) {
     if (ftiles) {
       TE_PROF("rank_final_auroc", st);
-      rank_final_kernel<0><<<ftiles, kFinBlock, 0, st>>>(ka, p.n, agg, inc, ticket, scal, partial);
+      rank_final_kernel<0><<<ftiles, kFinBlock, 0, st>>>(ka, p.n, rec, ticket, scal, partial);
     }
     TE_PROF("rank_reduce", st);
     rank_reduce_kernel<0><<<1, 1024, 0, st>>>(partial, ftiles, p.n, scal, out);
   } else {
     if (ftiles) {
       TE_PROF("rank_final_auprc", st);
-      rank_final_kernel<1><<<ftiles, kFinBlock, 0, st>>>(ka, p.n, agg, inc, ticket, scal, partial);
+      rank_final_kernel<1><<<ftiles, kFinBlock, 0, st>>>(ka, p.n, rec, ticket, scal, partial);
     }
     TE_PROF("rank_reduce", st);
     rank_reduce_kernel<1><<<1, 1024, 0, st>>>(partial, ftiles, p.n, scal, out);
@@ -769,24 +801,40 @@ __global__ void __launch_bounds__(kGenBlock)
   }
   excl = g_combine(wprefix, excl);
 
-  if (tid == 0) {
-    grec_publish(agg + tile, tile_agg);
+  if (warp == 0) {
+    if (lane == 0) grec_publish(agg + tile, tile_agg);
     GState e = g_identity();
-    for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
-      GState r;
-      bool full = false;
-      for (;;) {
-        if (grec_try(inc + t, r)) {
-          full = true;
-          break;
-        }
-        if (grec_try(agg + t, r)) break;
+    for (int64_t base = (int64_t)tile - 1; base >= 0; base -= 32) {
+      const int64_t idx = base - lane;
+      GState r = g_identity();
+      uint32_t incl, need;
+      do {
+        uint32_t st = 2;  // 0 nothing yet, 1 aggregate, 2 inclusive
+        if (idx >= 0) st = grec_try(inc + idx, r) ? 2u : (grec_try(agg + idx, r) ? 1u : 0u);
+        incl = __ballot_sync(kFull, st == 2u);
+        const uint32_t valid = __ballot_sync(kFull, st != 0u);
+        need = incl ? ((2u << (__ffs(incl) - 1)) - 1u) : kFull;
+        if ((valid & need) == need) break;
+      } while (true);
+      const unsigned first = incl ? (unsigned)(__ffs(incl) - 1) : 31u;
+      if (lane > first || idx < 0) r = g_identity();
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        GState u;
+        u.Stp = __shfl_down_sync(kFull, r.Stp, o);
+        u.Sfp = __shfl_down_sync(kFull, r.Sfp, o);
+        u.Mtp = __shfl_down_sync(kFull, r.Mtp, o);
+        u.Mfp = __shfl_down_sync(kFull, r.Mfp, o);
+        u.F = __shfl_down_sync(kFull, r.F, o);
+        if (lane + o < 32) r = g_combine(u, r);
       }
       e = g_combine(r, e);
-      if (full) break;
+      if (incl) break;
     }
-    grec_publish(inc + tile, g_combine(e, tile_agg));
-    s_excl = e;
+    if (lane == 0) {
+      grec_publish(inc + tile, g_combine(e, tile_agg));
+      s_excl = e;
+    }
   }
   __syncthreads();
   const GState g = g_combine(s_excl, excl);

@@ -25,6 +25,7 @@ constexpr int kSortTile = kSortBlock * kSortIpt;  // 8192 records per CTA
 //   v      (bit31 == 1)   : v & 0x7fffffff = count over this tile and every tile before it
 // A word carries its own validity, so relaxed loads/stores are enough.  Limits n to 2^31 - 1.
 constexpr uint32_t kLbInclusive = 0x80000000u;
+constexpr int kLbWindow = 8;  // predecessors fetched per look-back round trip
 
 template <typename KeyT>
 __device__ __forceinline__ uint32_t digit_of(KeyT k, int shift) {
@@ -105,14 +106,14 @@ __global__ void __launch_bounds__(kSortBlock, 2)
   }
   __syncthreads();
 
-  // ---- per-digit: tile count, publish, look back, local layout ----
+  // ---- per-digit: tile count, publish, local layout ----
+  uint32_t my_cnt = 0, my_bin_start = 0;
   if (tid < kRadix) {
     const uint32_t d = tid;
     uint32_t cnt = 0;
 #pragma unroll
     for (int w = 0; w < WARPS; ++w) cnt += s_whist[w][d];
-    uint32_t* lb = lookback + (size_t)tile * kRadix + d;
-    st_relaxed_u32(lb, cnt + 1u);
+    st_relaxed_u32(lookback + (size_t)tile * kRadix + d, cnt + 1u);
 
     // exclusive scan of cnt over the 256 digits (8 warps, named barrier 1)
     uint32_t incl = cnt;
@@ -137,25 +138,45 @@ __global__ void __launch_bounds__(kSortBlock, 2)
       s_whist[w][d] = run;
       run += c;
     }
-
-    // decoupled look-back over the preceding tiles
-    uint32_t excl = 0;
-    for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
-      const uint32_t* p = lookback + (size_t)t * kRadix + d;
-      uint32_t w;
-      do {
-        w = ld_relaxed_u32(p);
-      } while (w == 0);
-      if (w & kLbInclusive) {
-        excl += w & ~kLbInclusive;
-        break;
-      }
-      excl += w - 1u;
-    }
-    st_relaxed_u32(lb, kLbInclusive | (excl + cnt));
-    s_goff[d] = digit_base[d] + excl - bin_start;  // output index = s_goff[d] + tile position
+    my_cnt = cnt;
+    my_bin_start = bin_start;
   }
   __syncthreads();
+
+  // ---- decoupled look-back over the preceding tiles (digit threads = warps 0..7), overlapped
+  //      with the other warps already scattering their keys into tile order.  A B200 pass runs
+  //      at tens of millions of tiles per second while one L2 round trip is ~0.5 us, so a tile
+  //      routinely has to add up dozens of not-yet-prefixed predecessors: fetch them kLbWindow at
+  //      a time with independent loads instead of one dependent load per predecessor. ----
+  if (tid < kRadix) {
+    const uint32_t d = tid;
+    uint32_t excl = 0;
+    int64_t t = (int64_t)tile - 1;
+    while (t >= 0) {
+      uint32_t w[kLbWindow];
+#pragma unroll
+      for (int j = 0; j < kLbWindow; ++j)
+        w[j] = (t - j >= 0) ? ld_relaxed_u32(lookback + (size_t)(t - j) * kRadix + d) : kLbInclusive;
+      int used = 0;
+      bool done = false;
+#pragma unroll
+      for (int j = 0; j < kLbWindow; ++j) {
+        if (!done && used == j) {
+          if (w[j] & kLbInclusive) {
+            excl += w[j] & ~kLbInclusive;
+            done = true;
+          } else if (w[j] != 0) {
+            excl += w[j] - 1u;
+            used = j + 1;
+          }
+        }
+      }
+      if (done) break;
+      t -= used;  // the first unpublished predecessor is polled again
+    }
+    st_relaxed_u32(lookback + (size_t)tile * kRadix + d, kLbInclusive | (excl + my_cnt));
+    s_goff[d] = digit_base[d] + excl - my_bin_start;  // output index = s_goff[d] + tile position
+  }
 
   // ---- scatter into tile order through shared memory ----
 #pragma unroll

@@ -64,3 +64,59 @@ def _binary_auroc_update_input_check(
         raise ValueError(
             f"`num_tasks = {num_tasks}`, `input`'s shape is expected to be ({num_tasks}, num_samples), but got shape ({input.shape})."
         )
+
+
+@torch.inference_mode()
+def multiclass_auroc(
+    input: torch.Tensor,
+    target: torch.Tensor,
+    *,
+    num_classes: int,
+    average: Optional[str] = "macro",
+) -> torch.Tensor:
+    """One-vs-rest AUROC (reference auroc.py:75-112): float32; ``average="macro"`` -> scalar mean
+    over classes, ``None``/"none" -> (num_classes,).  A class that never occurs scores 0.5."""
+    _multiclass_auroc_param_check(num_classes, average)
+    _multiclass_auroc_update_input_check(input, target, num_classes)
+    return _multiclass_auroc_compute(input, target, num_classes, average)
+
+
+def _multiclass_auroc_compute(
+    input: torch.Tensor,
+    target: torch.Tensor,
+    num_classes: int,
+    average: Optional[str] = "macro",
+) -> torch.Tensor:
+    auroc = _ranking.multiclass_auroc(input, target).to(torch.float32).to(input.device)
+    if isinstance(average, str) and average == "macro":
+        return auroc.mean()
+    return auroc
+
+
+def _multiclass_auroc_param_check(num_classes: int, average: Optional[str]) -> None:
+    average_options = ("macro", "none", None)
+    if average not in average_options:
+        raise ValueError(
+            f"`average` was not in the allowed value of {average_options}, got {average}."
+        )
+    if num_classes < 2:
+        raise ValueError("`num_classes` has to be at least 2.")
+
+
+def _multiclass_auroc_update_input_check(
+    input: torch.Tensor,
+    target: torch.Tensor,
+    num_classes: int,
+) -> None:
+    if input.size(0) != target.size(0):
+        raise ValueError(
+            "The `input` and `target` should have the same first dimension, "
+            f"got shapes {input.shape} and {target.shape}."
+        )
+    if target.ndim != 1:
+        raise ValueError("target should be a one-dimensional tensor, " f"got shape {target.shape}.")
+    if not (input.ndim == 2 and input.shape[1] == num_classes):
+        raise ValueError(
+            f"input should have shape of (num_sample, num_classes), "
+            f"got {input.shape} and num_classes={num_classes}."
+        )

@@ -129,6 +129,29 @@ def binned_hist_update_(
         )
 
 
+def binned_hist2d_update_(hist: torch.Tensor, x: torch.Tensor, target: torch.Tensor, threshold: torch.Tensor, multilabel: bool) -> None:
+    """hist (int64 [C, T+1, 2], in place) += counts for (n, C) scores; target (n,) (multiclass,
+    label = target == c) or (n, C) (multilabel)."""
+    lib = N.load()
+    dev = _require_cuda(hist, x, target, threshold)
+    T = threshold.numel()
+    assert x.dim() == 2 and x.dtype == torch.float32 and target.dtype == torch.int64
+    assert threshold.dtype == torch.float32 and threshold.is_contiguous()
+    x, target = x.contiguous(), target.contiguous()
+    n, C = x.shape
+    assert target.shape == ((n, C) if multilabel else (n,))
+    assert hist.dtype == torch.int64 and hist.is_contiguous() and hist.numel() == C * (T + 1) * 2
+    scratch = _scratch(lib.te_binned_scratch_bytes(T), dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_binned_hist2d_update",
+            lib.te_binned_hist2d_update(
+                x.data_ptr(), target.data_ptr(), n, C, 1 if multilabel else 0, threshold.data_ptr(), T,
+                hist.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev),
+            ),
+        )
+
+
 def binned_counts(hist: torch.Tensor, T: int, want_fn: bool = True):
     """(num_tp, num_fp, num_fn) int64 [tasks, T] from the (bucket, label) histogram."""
     lib = N.load()
