@@ -86,6 +86,21 @@ TE_API int te_cm_update(const int64_t* pred, const int64_t* target, int64_t n, i
 TE_API int te_cm_update_logits(const float* logits, int64_t ld, const int64_t* target, int64_t n,
                         int32_t num_classes, int64_t* cm, int64_t* range, void* stream);
 
+/* Per-class counts for accuracy and F1: counts3 is int64 [3][C] (+=) holding
+ * num_tp[c] = #{pred == target == c}, num_label[c] = #{target == c}, num_pred[c] = #{pred == c}
+ * — the diagonal, row sums and column sums of the confusion matrix, i.e. the three
+ * scatter_(reduce="add") of functional/classification/f1_score.py:184-192 and the two of
+ * accuracy.py:275-277.  Exactly one of `pred` (int64 classes) and `logits` ((n, C) float32, row
+ * stride ld, argmax'ed) is non-NULL.  `range` as in te_cm_update. */
+TE_API int te_class_counts(const int64_t* pred, const float* logits, int64_t ld, const int64_t* target,
+                           int64_t n, int32_t num_classes, int64_t* counts3, int64_t* range,
+                           void* stream);
+
+/* *out (int64, +=) gets #{pred[i] == target[i]}: micro accuracy / micro F1 without a class
+ * count (accuracy.py:269-272, f1_score.py:176-180). */
+TE_API int te_match_count(const int64_t* pred, const int64_t* target, int64_t n, int64_t* out,
+                          void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * K3  binned (thresholded) counting
  * replaces functional/classification/binned_precision_recall_curve.py:84-110 (`_update`:

@@ -28,6 +28,8 @@ SIGNATURES = {
     "te_cm_scratch_bytes": (_sz, [_i32, _i32]),
     "te_cm_update": (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _vp, _sz, _i32, _vp]),
     "te_cm_update_logits": (C.c_int, [_vp, _i64, _vp, _i64, _i32, _vp, _vp, _vp]),
+    "te_class_counts": (C.c_int, [_vp, _vp, _i64, _vp, _i64, _i32, _vp, _vp, _vp]),
+    "te_match_count": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
     "te_binned_scratch_bytes": (_sz, [_i32]),
     "te_binned_hist_update": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i32, _vp, _i32, _vp, _vp, _sz, _vp]),
     "te_binned_hist2d_update": (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _i32, _vp, _vp, _sz, _vp]),

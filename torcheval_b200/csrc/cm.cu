@@ -302,6 +302,155 @@ __global__ void __launch_bounds__(kCmBlock)
   }
 }
 
+// ---- per-class counts for accuracy / F1 -------------------------------------------------
+// num_label[c] = #{target == c}, num_pred[c] = #{pred == c}, num_tp[c] = #{pred == target == c}
+// i.e. the row sums, column sums and diagonal of the confusion matrix, which is what the
+// reference's scatter_(reduce="add") calls compute (accuracy.py:275-277, f1_score.py:184-192) —
+// but 3*C bins fit in shared memory even at C = 1000, so this runs at streaming speed where the
+// full C*C matrix is bound by L2 atomics.
+struct ClassSink {
+  uint32_t* sh;  // [3][C]: tp, label, pred
+  uint32_t C;
+  __device__ __forceinline__ void add(uint32_t p, uint32_t t) const {
+    atomicAdd(sh + C + t, 1u);
+    atomicAdd(sh + 2 * C + p, 1u);
+    if (p == t) atomicAdd(sh + t, 1u);
+  }
+};
+
+template <int VEC>
+__global__ void __launch_bounds__(kCmBlock)
+    class_counts_kernel(const long long* __restrict__ pred, const long long* __restrict__ target,
+                        int64_t n, uint32_t C, unsigned long long* out3, long long* range) {
+  extern __shared__ uint32_t sh[];
+  for (uint32_t i = threadIdx.x; i < 3 * C; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  ClassSink sink{sh, C};
+  RangeReport rr{range};
+  const int64_t nvec = n / VEC;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t first = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  constexpr int UNROLL = 4;
+  for (int64_t base = first; base < nvec; base += stride * UNROLL) {
+    long long p[UNROLL][VEC], t[UNROLL][VEC];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const int64_t idx = base + (int64_t)u * stride;
+      if (idx < nvec) {
+        if (VEC == 2) {
+          const int4 a = ld_stream_v4(pred + 2 * idx);
+          const int4 b = ld_stream_v4(target + 2 * idx);
+          p[u][0] = ((long long)(uint32_t)a.y << 32) | (uint32_t)a.x;
+          p[u][VEC - 1] = ((long long)(uint32_t)a.w << 32) | (uint32_t)a.z;
+          t[u][0] = ((long long)(uint32_t)b.y << 32) | (uint32_t)b.x;
+          t[u][VEC - 1] = ((long long)(uint32_t)b.w << 32) | (uint32_t)b.z;
+        } else {
+          p[u][0] = __ldg(pred + idx);
+          t[u][0] = __ldg(target + idx);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const int64_t idx = base + (int64_t)u * stride;
+      if (idx < nvec) {
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) {
+          if ((unsigned long long)p[u][v] < C && (unsigned long long)t[u][v] < C)
+            sink.add((uint32_t)p[u][v], (uint32_t)t[u][v]);
+          else
+            rr.bad(p[u][v], t[u][v], C);
+        }
+      }
+    }
+  }
+  if (VEC > 1 && first == 0)
+    for (int64_t i = nvec * VEC; i < n; ++i) {
+      const long long pv = pred[i], tv = target[i];
+      if ((unsigned long long)pv < C && (unsigned long long)tv < C)
+        sink.add((uint32_t)pv, (uint32_t)tv);
+      else
+        rr.bad(pv, tv, C);
+    }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < 3 * C; i += blockDim.x) {
+    const uint32_t v = sh[i];
+    if (v) atomicAdd(out3 + i, (unsigned long long)v);
+  }
+}
+
+// logits variant: one warp per row, argmax as in cm_logits_warp_kernel
+__global__ void __launch_bounds__(kCmBlock)
+    class_counts_logits_kernel(const float* __restrict__ logits, int64_t ld,
+                               const long long* __restrict__ target, int64_t n, uint32_t C,
+                               unsigned long long* out3, long long* range) {
+  extern __shared__ uint32_t sh[];
+  for (uint32_t i = threadIdx.x; i < 3 * C; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  ClassSink sink{sh, C};
+  RangeReport rr{range};
+  const unsigned lane = lane_id();
+  const int64_t warps = (int64_t)gridDim.x * (blockDim.x / kWarp);
+  for (int64_t row = (int64_t)blockIdx.x * (blockDim.x / kWarp) + threadIdx.x / kWarp; row < n;
+       row += warps) {
+    const float* r = logits + row * ld;
+    float bv = 0.f;
+    int bi = -1;
+    for (uint32_t c = lane; c < C; c += kWarp) {
+      const float v = __ldg(r + c);
+      if (bi < 0 || better(v, (int)c, bv, bi)) {
+        bv = v;
+        bi = (int)c;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(kFull, bv, o);
+      const int oi = __shfl_xor_sync(kFull, bi, o);
+      if (oi >= 0 && (bi < 0 || better(ov, oi, bv, bi))) {
+        bv = ov;
+        bi = oi;
+      }
+    }
+    if (lane == 0) {
+      const long long t = target[row];
+      if ((unsigned long long)t < C)
+        sink.add((uint32_t)bi, (uint32_t)t);
+      else
+        rr.bad(0, t, C);
+    }
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < 3 * C; i += blockDim.x) {
+    const uint32_t v = sh[i];
+    if (v) atomicAdd(out3 + i, (unsigned long long)v);
+  }
+}
+
+// #{pred[i] == target[i]} — micro accuracy / micro F1 when the number of classes is not given
+// (accuracy.py:269-272, f1_score.py:176-180).
+__global__ void __launch_bounds__(kCmBlock)
+    match_count_kernel(const long long* __restrict__ pred, const long long* __restrict__ target,
+                       int64_t n, bool vec, unsigned long long* out) {
+  __shared__ unsigned long long ws[kCmBlock / 32];
+  unsigned long long acc = 0;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t first = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (vec) {
+    const int64_t nvec = n / 2;
+    for (int64_t i = first; i < nvec; i += stride) {
+      const int4 a = ld_stream_v4(pred + 2 * i), b = ld_stream_v4(target + 2 * i);
+      acc += (a.x == b.x && a.y == b.y) + (a.z == b.z && a.w == b.w);
+    }
+    if (first == 0 && (n & 1)) acc += pred[n - 1] == target[n - 1];
+  } else {
+    for (int64_t i = first; i < n; i += stride) acc += __ldg(pred + i) == __ldg(target + i);
+  }
+  unsigned long long tot;
+  block_scan_incl<unsigned long long, kCmBlock>(acc, ws, tot);
+  if (threadIdx.x == 0 && tot) atomicAdd(out, tot);
+}
+
 int pick_variant(int32_t C, int32_t variant) {
   if (variant != TE_CM_AUTO) return variant;
   const int64_t nbins = (int64_t)C * C;
@@ -471,6 +620,69 @@ extern "C" int te_cm_update_logits(const float* logits, int64_t ld, const int64_
     cm_logits_warp_kernel<unsigned long long><<<grid, kCmBlock, 0, st>>>(
         logits, ld, (const long long*)target, n, C, (unsigned long long*)cm, (long long*)range);
   }
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+extern "C" int te_class_counts(const int64_t* pred, const float* logits, int64_t ld,
+                               const int64_t* target, int64_t n, int32_t num_classes,
+                               int64_t* counts3, int64_t* range, void* stream) {
+  if (n < 0 || num_classes < 1 || num_classes > 18000 || !counts3 || !range)
+    return TE_ERR_INVALID_ARGUMENT;
+  if ((pred == nullptr) == (logits == nullptr) && n > 0) return TE_ERR_INVALID_ARGUMENT;
+  if (n > 0 && !target) return TE_ERR_INVALID_ARGUMENT;
+  if (logits && ld < num_classes) return TE_ERR_INVALID_ARGUMENT;
+  cudaStream_t st = (cudaStream_t)stream;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  cm_init_range_kernel<<<1, 32, 0, st>>>((long long*)range);
+  TE_LAUNCH_CHECK();
+  if (n == 0) return TE_OK;
+  const uint32_t C = (uint32_t)num_classes;
+  const size_t sh = (size_t)3 * C * 4;
+  unsigned long long* out3 = (unsigned long long*)counts3;
+  if (pred) {
+    const bool aligned = (((uintptr_t)pred | (uintptr_t)target) & 15) == 0;
+    const int64_t nvec = aligned ? (n + 1) / 2 : n;
+    int64_t want = (nvec + kCmBlock * 4 - 1) / (kCmBlock * 4);
+    const int occ = sh > 100 * 1024 ? 1 : (sh > 48 * 1024 ? 2 : 4);
+    const int grid = (int)(want < (int64_t)sms * occ ? (want < 1 ? 1 : want) : (int64_t)sms * occ);
+    TE_PROF("class_counts", st);
+    if (aligned) {
+      if (sh > 48 * 1024)
+        TE_CUDA_TRY(cudaFuncSetAttribute(class_counts_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
+      class_counts_kernel<2><<<grid, kCmBlock, sh, st>>>((const long long*)pred, (const long long*)target, n, C, out3, (long long*)range);
+    } else {
+      if (sh > 48 * 1024)
+        TE_CUDA_TRY(cudaFuncSetAttribute(class_counts_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
+      class_counts_kernel<1><<<grid, kCmBlock, sh, st>>>((const long long*)pred, (const long long*)target, n, C, out3, (long long*)range);
+    }
+  } else {
+    const int64_t want = (n + (kCmBlock / kWarp) - 1) / (kCmBlock / kWarp);
+    const int occ = sh > 100 * 1024 ? 1 : (sh > 48 * 1024 ? 2 : 8);
+    const int grid = (int)(want < (int64_t)sms * occ ? want : (int64_t)sms * occ);
+    if (sh > 48 * 1024)
+      TE_CUDA_TRY(cudaFuncSetAttribute(class_counts_logits_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
+    TE_PROF("class_counts_logits", st);
+    class_counts_logits_kernel<<<grid, kCmBlock, sh, st>>>(logits, ld, (const long long*)target, n, C, out3, (long long*)range);
+  }
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+extern "C" int te_match_count(const int64_t* pred, const int64_t* target, int64_t n, int64_t* out,
+                              void* stream) {
+  if (n < 0 || !out || (n > 0 && (!pred || !target))) return TE_ERR_INVALID_ARGUMENT;
+  if (n == 0) return TE_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  const bool vec = (((uintptr_t)pred | (uintptr_t)target) & 15) == 0;
+  int64_t want = (n / 2 + kCmBlock * 4 - 1) / (kCmBlock * 4);
+  const int grid = (int)(want < 1 ? 1 : (want < (int64_t)sms * 8 ? want : (int64_t)sms * 8));
+  TE_PROF("match_count", st);
+  match_count_kernel<<<grid, kCmBlock, 0, st>>>((const long long*)pred, (const long long*)target, n,
+                                                vec, (unsigned long long*)out);
   TE_LAUNCH_CHECK();
   return TE_OK;
 }

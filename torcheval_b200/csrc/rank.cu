@@ -16,6 +16,8 @@
 // so the result does not depend on launch geometry or timing.
 //
 // Bytes per score (SURVEY.md §8d formula, b_in = 12, r = 4, P = 4): 16 + 32 + 4 = 52.
+#include <stdlib.h>
+
 #include "rank_sort.cuh"
 #include "prof.cuh"
 
@@ -190,10 +192,27 @@ __global__ void __launch_bounds__(kIngestBlock, 1)
 // ------------------------------------------------------------------------------------------
 // fused scan / tie-dedup / integrate over sorted packed keys (ascending; bit 0 = label, so
 // inside a tie group the negatives come first)
+//
+// Every CTA owns one contiguous CHUNK of the sorted array and streams it tile by tile, carrying
+// its running state (negatives so far, negatives at the start of the current tie group, position
+// of that start) in registers.  Chunks do not wait on one another:
+//   * AUROC is linear in what a chunk does not know yet.  A positive contributes
+//     (#neg before it) + (#neg before its tie group); with E = state of everything before the
+//     chunk this is local + E.S (+ E.S, or + E.M if the group started before the chunk), so a
+//     chunk reports {state, A = local sum, P = #positives, lead = #positives of the leading run}
+//     and a one-CTA scan over the <= 1024 chunk records finishes the job:
+//         2U = sum_c  A_c + E_c.S * (2 P_c - lead_c) + E_c.M * lead_c.
+//   * AUPRC is not (precision is a ratio of prefix counts), so it takes two sweeps: the same
+//     counting sweep, the scan publishes every chunk's E, and a second sweep integrates with
+//     exact global counts.
+// (A first version used a tile-granular decoupled look-back inside one pass; at B200 speeds a
+// 16 KB tile lasts well under the L2 round trip that links neighbouring tiles, and the chain —
+// not HBM — set the pace: profiles/r01_tune_rank_v2.txt, 21 % of the HBM roofline.)
 // ------------------------------------------------------------------------------------------
 constexpr int kFinBlock = 256;
 constexpr int kFinIpt = 16;
 constexpr int kFinTile = kFinBlock * kFinIpt;
+constexpr int kMaxChunks = 1024;
 
 struct FState {
   uint32_t S;   // negatives in the segment
@@ -219,122 +238,178 @@ __device__ __forceinline__ FState f_shfl_up(const FState& v, int o) {
   return u;
 }
 
-// One 16-byte record per tile, written twice (own aggregate, then inclusive prefix).  The
-// status sits in the top two bits of BOTH halves, so a reader that catches the two halves of
-// different writes sees mismatching statuses and simply polls again.
-struct alignas(16) ScanRec {
-  unsigned long long lo;  // S | M << 31 | status << 62
-  unsigned long long hi;  // Mp | F << 32 | status << 62
+struct alignas(16) ChunkRec {
+  FState st;                 // state of the whole chunk
+  unsigned long long A;      // AUROC: local part of 2U
+  unsigned long long P;      // positives in the chunk
+  unsigned long long lead;   // positives whose tie group started before the chunk
+  unsigned long long pad;
 };
-enum : uint32_t { kRecEmpty = 0, kRecAgg = 1, kRecInc = 2 };
-__device__ __forceinline__ void rec_publish(ScanRec* r, const FState& s, uint32_t status) {
-  const unsigned long long lo =
-      (unsigned long long)s.S | ((unsigned long long)s.M << 31) | ((unsigned long long)status << 62);
-  const unsigned long long hi =
-      (unsigned long long)s.Mp | ((unsigned long long)s.F << 32) | ((unsigned long long)status << 62);
-  asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(r), "l"(lo), "l"(hi) : "memory");
-}
-__device__ __forceinline__ uint32_t rec_load(const ScanRec* r, FState& s) {
-  unsigned long long lo, hi;
-  asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(lo), "=l"(hi) : "l"(r) : "memory");
-  const uint32_t st = (uint32_t)(lo >> 62);
-  if (st != (uint32_t)(hi >> 62)) return kRecEmpty;
-  s.S = (uint32_t)(lo & 0x7fffffffull);
-  s.M = (uint32_t)((lo >> 31) & 0x7fffffffull);
-  s.Mp = (uint32_t)(hi & 0x7fffffffull);
-  s.F = (uint32_t)((hi >> 32) & 1ull);
-  return st;
-}
-__device__ __forceinline__ FState f_shfl_down(const FState& v, int o) {
-  FState u;
-  u.S = __shfl_down_sync(kFull, v.S, o);
-  u.M = __shfl_down_sync(kFull, v.M, o);
-  u.Mp = __shfl_down_sync(kFull, v.Mp, o);
-  u.F = __shfl_down_sync(kFull, v.F, o);
-  return u;
+
+struct ChunkGeom {
+  uint32_t nchunks, tiles_per_chunk;
+};
+inline ChunkGeom chunk_geom(uint32_t fin_tiles, int sms) {
+  ChunkGeom g;
+  uint32_t want = (uint32_t)sms * 4u;
+  if (want > (uint32_t)kMaxChunks) want = kMaxChunks;
+  if (want > fin_tiles) want = fin_tiles;
+  if (want < 1) want = 1;
+  g.tiles_per_chunk = (fin_tiles + want - 1) / want;
+  if (g.tiles_per_chunk < 1) g.tiles_per_chunk = 1;
+  g.nchunks = (fin_tiles + g.tiles_per_chunk - 1) / g.tiles_per_chunk;
+  if (g.nchunks < 1) g.nchunks = 1;
+  return g;
 }
 
-// Warp-wide decoupled look-back: the 32 lanes inspect the 32 preceding tiles at once, the
-// nearest inclusive record ends the walk.  Returns (on lane 0) the state of everything before
-// `tile`.  Called by one full warp.
-__device__ __forceinline__ FState warp_lookback(const ScanRec* rec, uint32_t tile, unsigned lane) {
-  FState e = f_identity();
-  for (int64_t base = (int64_t)tile - 1; base >= 0; base -= 32) {
-    const int64_t idx = base - lane;
-    FState r = f_identity();
-    uint32_t st, incl, need;
-    do {
-      st = idx >= 0 ? rec_load(rec + idx, r) : (uint32_t)kRecInc;
-      if (idx < 0) r = f_identity();
-      incl = __ballot_sync(kFull, st == kRecInc);
-      const uint32_t valid = __ballot_sync(kFull, st != kRecEmpty);
-      // every lane up to and including the nearest inclusive one must be published
-      need = incl ? ((2u << (__ffs(incl) - 1)) - 1u) : kFull;
-      if ((valid & need) == need) break;
-    } while (true);
-    const unsigned first = incl ? (unsigned)(__ffs(incl) - 1) : 31u;
-    if (lane > first) r = f_identity();
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {  // higher lane = earlier tile = left operand
-      const FState u = f_shfl_down(r, o);
-      if (lane + o < 32) r = f_combine(u, r);
-    }
-    e = f_combine(r, e);  // meaningful on lane 0
-    if (incl) break;
-  }
-  return e;
-}
-
-template <int MODE>  // 0: AUROC (u64 partials)  1: AUPRC (double partials)
+// MODE 0: counting / AUROC sweep -> rec[chunk].   MODE 1: AUPRC integrate sweep, starts from
+// excl[chunk] (global state before the chunk) -> partial[chunk] (double bits).
+template <int MODE>
 __global__ void __launch_bounds__(kFinBlock)
-    rank_final_kernel(const uint32_t* __restrict__ keys, uint32_t n, ScanRec* rec,
-                      uint32_t* ticket, const RankScalars* __restrict__ scal,
-                      unsigned long long* partial) {
+    rank_chunk_kernel(const uint32_t* __restrict__ keys, uint32_t n, uint32_t tiles_per_chunk,
+                      ChunkRec* rec, const FState* __restrict__ excl_in,
+                      const RankScalars* __restrict__ scal, unsigned long long* partial) {
   __shared__ FState s_warp[kFinBlock / kWarp];
-  __shared__ FState s_excl;
-  __shared__ uint32_t s_tile;
-  __shared__ unsigned long long s_red[kFinBlock / kWarp];
+  __shared__ unsigned long long s_red[3][kFinBlock / kWarp];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-  __syncthreads();
-  const uint32_t tile = s_tile;
-  const uint32_t i0 = tile * (uint32_t)kFinTile + tid * kFinIpt;
+  const uint32_t chunk = blockIdx.x;
+  const uint32_t tile0 = chunk * tiles_per_chunk;
 
-  uint32_t k[kFinIpt];
-  if (i0 + kFinIpt <= n) {
+  FState carry = MODE == 1 ? excl_in[chunk] : f_identity();
+  unsigned long long accA = 0, accP = 0, accLead = 0;
+  double accD = 0.0;
+  const double ptot = MODE == 1 ? (double)scal->positives : 0.0;
+
+  for (uint32_t tl = 0; tl < tiles_per_chunk; ++tl) {
+    const uint64_t base64 = (uint64_t)(tile0 + tl) * kFinTile;
+    if (base64 >= n) break;
+    const uint32_t i0 = (uint32_t)base64 + tid * kFinIpt;
+
+    uint32_t k[kFinIpt];
+    if (i0 + kFinIpt <= n) {
 #pragma unroll
-    for (int q = 0; q < kFinIpt / 4; ++q) {
-      const int4 a = ld_stream_v4(keys + i0 + 4 * q);
-      k[4 * q] = a.x, k[4 * q + 1] = a.y, k[4 * q + 2] = a.z, k[4 * q + 3] = a.w;
+      for (int q = 0; q < kFinIpt / 4; ++q) {
+        const int4 a = ld_stream_v4(keys + i0 + 4 * q);
+        k[4 * q] = a.x, k[4 * q + 1] = a.y, k[4 * q + 2] = a.z, k[4 * q + 3] = a.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < kFinIpt; ++j) k[j] = (i0 + j < n) ? keys[i0 + j] : 0u;
+    }
+    const uint32_t cnt = i0 < n ? min((uint32_t)kFinIpt, n - i0) : 0u;
+    uint32_t prev = (i0 > 0 && i0 < n) ? (keys[i0 - 1] >> 1) : 0u;
+
+    // phase 1: thread aggregate + group-start mask
+    FState mine = f_identity();
+    uint32_t starts = 0;
+#pragma unroll
+    for (int j = 0; j < kFinIpt; ++j) {
+      if (j < (int)cnt) {
+        const uint32_t s = k[j] >> 1;
+        const bool st = (j == 0 && i0 == 0) || s != prev;
+        prev = s;
+        if (st) {
+          starts |= 1u << j;
+          mine.F = 1;
+          mine.M = mine.S;
+          mine.Mp = i0 + j;
+        }
+        mine.S += (k[j] & 1u) ^ 1u;
+      }
+    }
+
+    // block exclusive scan of the thread aggregates
+    FState incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const FState u = f_shfl_up(incl, o);
+      if (lane >= (unsigned)o) incl = f_combine(u, incl);
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    FState excl = f_shfl_up(incl, 1);
+    if (lane == 0) excl = f_identity();
+    __syncthreads();
+    FState wprefix = f_identity(), tile_agg = f_identity();
+#pragma unroll
+    for (int w = 0; w < kFinBlock / kWarp; ++w) {
+      const FState x = s_warp[w];
+      if (w < (int)warp) wprefix = f_combine(wprefix, x);
+      tile_agg = f_combine(tile_agg, x);
+    }
+    __syncthreads();  // s_warp is rewritten by the next tile
+    const FState g = f_combine(carry, f_combine(wprefix, excl));
+
+    // phase 2: integrate with chunk-relative (MODE 0) or global (MODE 1) counts
+    uint32_t c = g.S, gs = g.M, gp = g.Mp, have = g.F;
+#pragma unroll
+    for (int j = 0; j < kFinIpt; ++j) {
+      if (j < (int)cnt) {
+        if (starts & (1u << j)) {
+          gs = c;
+          gp = i0 + j;
+          have = 1;
+        }
+        if (k[j] & 1u) {
+          if (MODE == 0) {
+            ++accP;
+            if (have) {
+              accA += (unsigned long long)c + gs;
+            } else {
+              accA += c;
+              ++accLead;
+            }
+          } else {
+            // precision at this tie group's threshold: TP / (TP + FP), counts of score >= s
+            const double tp = ptot - (double)(gp - gs);
+            accD += tp / (double)(n - gp);
+          }
+        } else {
+          ++c;
+        }
+      }
+    }
+    carry = f_combine(carry, tile_agg);
+  }
+
+  if (MODE == 0) {
+    accA = warp_sum(accA);
+    accP = warp_sum(accP);
+    accLead = warp_sum(accLead);
+    if (lane == 0) s_red[0][warp] = accA, s_red[1][warp] = accP, s_red[2][warp] = accLead;
+    __syncthreads();
+    if (tid == 0) {
+      ChunkRec r;
+      r.st = carry;
+      r.A = r.P = r.lead = r.pad = 0;
+      for (int w = 0; w < kFinBlock / kWarp; ++w) r.A += s_red[0][w], r.P += s_red[1][w], r.lead += s_red[2][w];
+      rec[chunk] = r;
     }
   } else {
-#pragma unroll
-    for (int j = 0; j < kFinIpt; ++j) k[j] = (i0 + j < n) ? keys[i0 + j] : 0u;
-  }
-  const uint32_t cnt = i0 < n ? min((uint32_t)kFinIpt, n - i0) : 0u;
-  uint32_t prev = (i0 > 0 && i0 < n) ? (keys[i0 - 1] >> 1) : 0u;
-
-  // phase 1: thread aggregate + group-start mask
-  FState mine = f_identity();
-  uint32_t starts = 0;
-#pragma unroll
-  for (int j = 0; j < kFinIpt; ++j) {
-    if (j < (int)cnt) {
-      const uint32_t s = k[j] >> 1;
-      const bool st = (j == 0 && i0 == 0) || s != prev;
-      prev = s;
-      if (st) {
-        starts |= 1u << j;
-        mine.F = 1;
-        mine.M = mine.S;
-        mine.Mp = i0 + j;
-      }
-      mine.S += (k[j] & 1u) ^ 1u;
+    accD = warp_sum(accD);
+    if (lane == 0) s_red[0][warp] = (unsigned long long)__double_as_longlong(accD);
+    __syncthreads();
+    if (tid == 0) {
+      double t = 0.0;
+      for (int w = 0; w < kFinBlock / kWarp; ++w) t += __longlong_as_double((long long)s_red[0][w]);
+      partial[chunk] = (unsigned long long)__double_as_longlong(t);
     }
   }
+}
 
-  // block exclusive scan of the thread aggregates
-  FState incl = mine;
+// One CTA: exclusive scan of the chunk states.  MODE 0 finishes AUROC (out[] as documented at
+// te_binary_auroc); MODE 1 publishes excl[chunk] for the AUPRC integrate sweep.
+template <int MODE>
+__global__ void __launch_bounds__(kMaxChunks)
+    rank_chunk_scan_kernel(const ChunkRec* __restrict__ rec, uint32_t nchunks, uint32_t n,
+                           const RankScalars* __restrict__ scal, FState* excl_out, double* out) {
+  __shared__ FState s_warp[kMaxChunks / kWarp];
+  __shared__ unsigned long long s_u[kMaxChunks / kWarp];
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  ChunkRec r;
+  r.st = f_identity();
+  r.A = r.P = r.lead = 0;
+  if (tid < nchunks) r = rec[tid];
+  FState incl = r.st;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const FState u = f_shfl_up(incl, o);
@@ -344,70 +419,27 @@ __global__ void __launch_bounds__(kFinBlock)
   FState excl = f_shfl_up(incl, 1);
   if (lane == 0) excl = f_identity();
   __syncthreads();
-  FState wprefix = f_identity(), tile_agg = f_identity();
-#pragma unroll
-  for (int w = 0; w < kFinBlock / kWarp; ++w) {
-    const FState x = s_warp[w];
-    if (w < (int)warp) wprefix = f_combine(wprefix, x);
-    tile_agg = f_combine(tile_agg, x);
-  }
+  FState wprefix = f_identity();
+  for (int w = 0; w < (int)warp; ++w) wprefix = f_combine(wprefix, s_warp[w]);
   excl = f_combine(wprefix, excl);
-
-  // decoupled look-back across tiles, by warp 0
-  if (warp == 0) {
-    if (lane == 0) rec_publish(rec + tile, tile_agg, kRecAgg);
-    const FState e = warp_lookback(rec, tile, lane);
-    if (lane == 0) {
-      rec_publish(rec + tile, f_combine(e, tile_agg), kRecInc);
-      s_excl = e;
-    }
+  if (MODE == 1) {
+    if (tid < nchunks) excl_out[tid] = excl;
+    return;
   }
+  unsigned long long u2 = 0;
+  if (tid < nchunks) u2 = r.A + (unsigned long long)excl.S * (2ull * r.P - r.lead) + (unsigned long long)excl.M * r.lead;
+  u2 = warp_sum(u2);
+  if (lane == 0) s_u[warp] = u2;
   __syncthreads();
-  const FState g = f_combine(s_excl, excl);
-
-  // phase 2: integrate
-  uint32_t c = g.S, gs = g.M, gp = g.Mp;
-  unsigned long long acc_u = 0;
-  double acc_d = 0.0;
-  const double ptot = (double)scal->positives;
-#pragma unroll
-  for (int j = 0; j < kFinIpt; ++j) {
-    if (j < (int)cnt) {
-      if (starts & (1u << j)) {
-        gs = c;
-        gp = i0 + j;
-      }
-      if (k[j] & 1u) {
-        if (MODE == 0) {
-          acc_u += (unsigned long long)c + gs;
-        } else {
-          // precision at this tie group's threshold: TP / (TP + FP), counts of score >= s
-          const double tp = ptot - (double)(gp - gs);
-          acc_d += tp / (double)(n - gp);
-        }
-      } else {
-        ++c;
-      }
-    }
-  }
-  if (MODE == 0) {
-    acc_u = warp_sum(acc_u);
-    if (lane == 0) s_red[warp] = acc_u;
-    __syncthreads();
-    if (tid == 0) {
-      unsigned long long t = 0;
-      for (int w = 0; w < kFinBlock / kWarp; ++w) t += s_red[w];
-      partial[tile] = t;
-    }
-  } else {
-    acc_d = warp_sum(acc_d);
-    if (lane == 0) s_red[warp] = (unsigned long long)__double_as_longlong(acc_d);
-    __syncthreads();
-    if (tid == 0) {
-      double t = 0.0;
-      for (int w = 0; w < kFinBlock / kWarp; ++w) t += __longlong_as_double((long long)s_red[w]);
-      partial[tile] = (unsigned long long)__double_as_longlong(t);
-    }
+  if (tid == 0) {
+    unsigned long long tu = 0;
+    for (int w = 0; w < kMaxChunks / kWarp; ++w) tu += s_u[w];
+    const double P = (double)scal->positives, N = (double)n - P;
+    out[0] = (P * N == 0.0) ? 0.5 : ((double)tu * 0.5) / (P * N);
+    out[1] = P;
+    out[2] = N;
+    out[3] = (double)tu;
+    out[4] = (double)scal->flags;
   }
 }
 
@@ -498,10 +530,10 @@ RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final)
   p.off_ticket = take(8 * 4);
   p.off_scal = take(sizeof(RankScalars));
   p.off_lookback = take((size_t)4 * p.sort_tiles * kRadix * 4);
-  p.off_agg = take(with_final ? (size_t)p.fin_tiles * sizeof(ScanRec) : 0);
-  p.off_inc = p.off_agg;
+  p.off_agg = take(with_final ? (size_t)kMaxChunks * sizeof(ChunkRec) : 0);
+  p.off_inc = take(with_final ? (size_t)kMaxChunks * sizeof(FState) : 0);
   p.zero_bytes = o - p.off_zero;
-  p.off_partial = take(with_final ? (size_t)p.fin_tiles * 8 : 0);
+  p.off_partial = take(with_final ? (size_t)kMaxChunks * 8 : 0);
   p.total = o;
   return p;
 }
@@ -523,10 +555,24 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   }
   TE_LAUNCH_CHECK();
   constexpr size_t smem = onesweep_smem_bytes<uint32_t>();
-  TE_CUDA_TRY(cudaFuncSetAttribute(onesweep_pass_kernel<uint32_t, true>,
-                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  TE_CUDA_TRY(cudaFuncSetAttribute(onesweep_pass_kernel<uint32_t, false>,
-                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // look-back window: tunable for profiling through TE_B200_LB_WINDOW (8, 16 or 32)
+  static const int window = [] {
+    const char* e = getenv("TE_B200_LB_WINDOW");
+    const int w = e ? atoi(e) : kLbWindowDefault;
+    return (w == 8 || w == 16 || w == 32) ? w : kLbWindowDefault;
+  }();
+  using PassFn = void (*)(const uint32_t*, uint32_t*, const uint32_t*, uint32_t*, uint32_t, int,
+                          const uint32_t*, uint32_t*, uint32_t*);
+  PassFn fn;
+  if (v_in0)
+    fn = window == 8 ? onesweep_pass_kernel<uint32_t, true, 8>
+                     : (window == 16 ? onesweep_pass_kernel<uint32_t, true, 16>
+                                     : onesweep_pass_kernel<uint32_t, true, 32>);
+  else
+    fn = window == 8 ? onesweep_pass_kernel<uint32_t, false, 8>
+                     : (window == 16 ? onesweep_pass_kernel<uint32_t, false, 16>
+                                     : onesweep_pass_kernel<uint32_t, false, 32>);
+  TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const uint32_t* kin = k_in0;
   const uint32_t* vin = v_in0;
   for (int pass = 0; pass < 4; ++pass) {
@@ -534,12 +580,8 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
     uint32_t* vout = (pass & 1) ? v_y : v_x;
     uint32_t* lbp = lb + (size_t)pass * p.sort_tiles * kRadix;
     TE_PROF(v_in0 ? "onesweep_pass_pairs" : "onesweep_pass_keys", st);
-    if (v_in0)
-      onesweep_pass_kernel<uint32_t, true><<<p.sort_tiles, kSortBlock, smem, st>>>(
-          kin, kout, vin, vout, p.n, 8 * pass, hist + pass * kRadix, lbp, ticket + pass);
-    else
-      onesweep_pass_kernel<uint32_t, false><<<p.sort_tiles, kSortBlock, smem, st>>>(
-          kin, kout, nullptr, nullptr, p.n, 8 * pass, hist + pass * kRadix, lbp, ticket + pass);
+    fn<<<p.sort_tiles, kSortBlock, smem, st>>>(kin, kout, vin, vout, p.n, 8 * pass,
+                                               hist + pass * kRadix, lbp, ticket + pass);
     TE_LAUNCH_CHECK();
     kin = kout;
     vin = vout;
@@ -604,25 +646,31 @@ int binary_rank_packed(const float* score, const void* target, int32_t dt, int64
     rc = run_passes(p, scratch, ka, kb, ka, nullptr, nullptr, nullptr, st);
     if (rc) return rc;
   }
-  ScanRec* rec = at<ScanRec>(scratch, p.off_agg);
-  uint32_t* ticket = at<uint32_t>(scratch, p.off_ticket) + 4;
+  ChunkRec* rec = at<ChunkRec>(scratch, p.off_agg);
+  FState* excl = at<FState>(scratch, p.off_inc);
   unsigned long long* partial = at<unsigned long long>(scratch, p.off_partial);
   const RankScalars* scal = at<RankScalars>(scratch, p.off_scal);
-  const uint32_t ftiles = n > 0 ? p.fin_tiles : 0;
+  const ChunkGeom cg = chunk_geom(p.fin_tiles, sms);
+  const uint32_t nchunks = n > 0 ? cg.nchunks : 0;
+  if (nchunks) {
+    TE_PROF("rank_chunk_sweep", st);
+    rank_chunk_kernel<0><<<nchunks, kFinBlock, 0, st>>>(ka, p.n, cg.tiles_per_chunk, rec, nullptr, scal, nullptr);
+  }
+  TE_LAUNCH_CHECK();
   if (mode == 0) {
-    if (ftiles) {
-      TE_PROF("rank_final_auroc", st);
-      rank_final_kernel<0><<<ftiles, kFinBlock, 0, st>>>(ka, p.n, rec, ticket, scal, partial);
-    }
-    TE_PROF("rank_reduce", st);
-    rank_reduce_kernel<0><<<1, 1024, 0, st>>>(partial, ftiles, p.n, scal, out);
+    TE_PROF("rank_chunk_scan", st);
+    rank_chunk_scan_kernel<0><<<1, kMaxChunks, 0, st>>>(rec, nchunks, p.n, scal, nullptr, out);
   } else {
-    if (ftiles) {
-      TE_PROF("rank_final_auprc", st);
-      rank_final_kernel<1><<<ftiles, kFinBlock, 0, st>>>(ka, p.n, rec, ticket, scal, partial);
+    if (nchunks) {
+      {
+        TE_PROF("rank_chunk_scan", st);
+        rank_chunk_scan_kernel<1><<<1, kMaxChunks, 0, st>>>(rec, nchunks, p.n, scal, excl, nullptr);
+      }
+      TE_PROF("rank_chunk_integrate", st);
+      rank_chunk_kernel<1><<<nchunks, kFinBlock, 0, st>>>(ka, p.n, cg.tiles_per_chunk, nullptr, excl, scal, partial);
     }
     TE_PROF("rank_reduce", st);
-    rank_reduce_kernel<1><<<1, 1024, 0, st>>>(partial, ftiles, p.n, scal, out);
+    rank_reduce_kernel<1><<<1, 1024, 0, st>>>(partial, nchunks, p.n, scal, out);
   }
   TE_LAUNCH_CHECK();
   return TE_OK;

@@ -25,7 +25,7 @@ constexpr int kSortTile = kSortBlock * kSortIpt;  // 8192 records per CTA
 //   v      (bit31 == 1)   : v & 0x7fffffff = count over this tile and every tile before it
 // A word carries its own validity, so relaxed loads/stores are enough.  Limits n to 2^31 - 1.
 constexpr uint32_t kLbInclusive = 0x80000000u;
-constexpr int kLbWindow = 8;  // predecessors fetched per look-back round trip
+constexpr int kLbWindowDefault = 16;  // predecessors fetched per look-back round trip
 
 template <typename KeyT>
 __device__ __forceinline__ uint32_t digit_of(KeyT k, int shift) {
@@ -40,7 +40,7 @@ constexpr size_t onesweep_smem_bytes() {
          sizeof(uint32_t) * ((kSortBlock / kWarp) * kRadix + kRadix + kRadix / kWarp + 4);
 }
 
-template <typename KeyT, bool HAS_VAL>
+template <typename KeyT, bool HAS_VAL, int kLbWindow>
 __global__ void __launch_bounds__(kSortBlock, 2)
     onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                          const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,

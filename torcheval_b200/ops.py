@@ -103,6 +103,43 @@ def cm_update_logits_(
     return rng
 
 
+def class_counts_(counts3: torch.Tensor, input: torch.Tensor, target: torch.Tensor, num_classes: int) -> torch.Tensor:
+    """counts3 (int64 [3, C], in place) += (num_tp, num_label, num_pred); input is (n,) int64
+    classes or (n, C) float32 scores (argmax'ed in the kernel).  Returns the int64[4] range report."""
+    lib = N.load()
+    dev = _require_cuda(counts3, input, target)
+    assert counts3.dtype == torch.int64 and counts3.is_contiguous() and counts3.numel() == 3 * num_classes
+    assert target.dtype == torch.int64
+    target = target.contiguous()
+    rng = torch.empty(4, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        if input.dim() == 2:
+            assert input.dtype == torch.float32
+            if input.stride(1) != 1:
+                input = input.contiguous()
+            rc = lib.te_class_counts(None, input.data_ptr(), input.stride(0), target.data_ptr(), input.shape[0],
+                                     num_classes, counts3.data_ptr(), rng.data_ptr(), _stream_ptr(dev))
+        else:
+            assert input.dtype == torch.int64
+            input = input.contiguous()
+            rc = lib.te_class_counts(input.data_ptr(), None, 0, target.data_ptr(), input.numel(), num_classes,
+                                     counts3.data_ptr(), rng.data_ptr(), _stream_ptr(dev))
+        N.check("te_class_counts", rc)
+    return rng
+
+
+def match_count(pred: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+    """int64 scalar tensor: number of positions where pred == target."""
+    lib = N.load()
+    dev = _require_cuda(pred, target)
+    assert pred.dtype == torch.int64 and target.dtype == torch.int64 and pred.shape == target.shape
+    pred, target = pred.contiguous(), target.contiguous()
+    out = torch.zeros((), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        N.check("te_match_count", lib.te_match_count(pred.data_ptr(), target.data_ptr(), pred.numel(), out.data_ptr(), _stream_ptr(dev)))
+    return out
+
+
 # ----------------------------------------------------------------------------- K3
 def binned_hist_update_(
     hist: torch.Tensor, x: torch.Tensor, target: torch.Tensor, threshold: torch.Tensor
