@@ -249,9 +249,9 @@ struct alignas(16) ChunkRec {
 struct ChunkGeom {
   uint32_t nchunks, tiles_per_chunk;
 };
-inline ChunkGeom chunk_geom(uint32_t fin_tiles, int sms) {
+inline ChunkGeom chunk_geom(uint32_t fin_tiles, int sms, int ctas_per_sm) {
   ChunkGeom g;
-  uint32_t want = (uint32_t)sms * 4u;
+  uint32_t want = (uint32_t)sms * (uint32_t)(ctas_per_sm > 0 ? ctas_per_sm : 1);
   if (want > (uint32_t)kMaxChunks) want = kMaxChunks;
   if (want > fin_tiles) want = fin_tiles;
   if (want < 1) want = 1;
@@ -280,25 +280,39 @@ __global__ void __launch_bounds__(kFinBlock)
   double accD = 0.0;
   const double ptot = MODE == 1 ? (double)scal->positives : 0.0;
 
+  // register double buffering: the loads of tile t+1 are in flight while tile t is processed
+  auto load_tile = [&](uint32_t tl, uint32_t (&dst)[kFinIpt], uint32_t& prev_key) {
+    const uint64_t b = (uint64_t)(tile0 + tl) * kFinTile;
+    if (tl >= tiles_per_chunk || b >= n) return;
+    const uint32_t j0 = (uint32_t)b + tid * kFinIpt;
+    if (j0 + kFinIpt <= n) {
+#pragma unroll
+      for (int q = 0; q < kFinIpt / 4; ++q) {
+        const int4 a = ld_stream_v4(keys + j0 + 4 * q);
+        dst[4 * q] = a.x, dst[4 * q + 1] = a.y, dst[4 * q + 2] = a.z, dst[4 * q + 3] = a.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < kFinIpt; ++j) dst[j] = (j0 + j < n) ? keys[j0 + j] : 0u;
+    }
+    prev_key = (j0 > 0 && j0 < n) ? keys[j0 - 1] : 0u;
+  };
+  uint32_t knext[kFinIpt], prev_next = 0;
+  load_tile(0, knext, prev_next);
+
   for (uint32_t tl = 0; tl < tiles_per_chunk; ++tl) {
     const uint64_t base64 = (uint64_t)(tile0 + tl) * kFinTile;
     if (base64 >= n) break;
     const uint32_t i0 = (uint32_t)base64 + tid * kFinIpt;
 
     uint32_t k[kFinIpt];
-    if (i0 + kFinIpt <= n) {
 #pragma unroll
-      for (int q = 0; q < kFinIpt / 4; ++q) {
-        const int4 a = ld_stream_v4(keys + i0 + 4 * q);
-        k[4 * q] = a.x, k[4 * q + 1] = a.y, k[4 * q + 2] = a.z, k[4 * q + 3] = a.w;
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < kFinIpt; ++j) k[j] = (i0 + j < n) ? keys[i0 + j] : 0u;
-    }
+    for (int j = 0; j < kFinIpt; ++j) k[j] = knext[j];
+    uint32_t prev = prev_next >> 1;
+    load_tile(tl + 1, knext, prev_next);
     const uint32_t cnt = i0 < n ? min((uint32_t)kFinIpt, n - i0) : 0u;
-    uint32_t prev = (i0 > 0 && i0 < n) ? (keys[i0 - 1] >> 1) : 0u;
 
+    // phase 1: thread aggregate + group-start mask
     // phase 1: thread aggregate + group-start mask
     FState mine = f_identity();
     uint32_t starts = 0;
@@ -492,8 +506,18 @@ __global__ void __launch_bounds__(1024)
 // ------------------------------------------------------------------------------------------
 // host side: scratch plan + launch sequences
 // ------------------------------------------------------------------------------------------
+inline int sort_block_from_env() {
+  static const int b = [] {
+    const char* e = getenv("TE_B200_SORT_BLOCK");
+    const int v = e ? atoi(e) : kSortBlockDefault;
+    return (v == 256 || v == 512) ? v : kSortBlockDefault;
+  }();
+  return b;
+}
+
 struct RankPlan {
   uint32_t n;
+  int sort_block;
   uint32_t sort_tiles, fin_tiles;
   size_t off_keys_a, off_keys_b, off_vals_a, off_vals_b;
   size_t off_zero;      // start of the region that must be zero before launch
@@ -510,7 +534,9 @@ struct RankPlan {
 RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final) {
   RankPlan p{};
   p.n = (uint32_t)n64;
-  p.sort_tiles = (uint32_t)((n64 + kSortTile - 1) / kSortTile);
+  p.sort_block = sort_block_from_env();
+  const int64_t sort_tile = (int64_t)p.sort_block * kSortIpt;
+  p.sort_tiles = (uint32_t)((n64 + sort_tile - 1) / sort_tile);
   p.fin_tiles = (uint32_t)((n64 + kFinTile - 1) / kFinTile);
   if (p.sort_tiles == 0) p.sort_tiles = 1;
   if (p.fin_tiles == 0) p.fin_tiles = 1;
@@ -554,24 +580,25 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
     digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 4);
   }
   TE_LAUNCH_CHECK();
-  constexpr size_t smem = onesweep_smem_bytes<uint32_t>();
-  // look-back window: tunable for profiling through TE_B200_LB_WINDOW (8, 16 or 32)
+  // look-back window and CTA size: tunable for profiling through the environment
   static const int window = [] {
     const char* e = getenv("TE_B200_LB_WINDOW");
     const int w = e ? atoi(e) : kLbWindowDefault;
     return (w == 8 || w == 16 || w == 32) ? w : kLbWindowDefault;
   }();
+  const int block = p.sort_block;
+  const size_t smem = block == 256 ? onesweep_smem_bytes<uint32_t, 256>() : onesweep_smem_bytes<uint32_t, 512>();
   using PassFn = void (*)(const uint32_t*, uint32_t*, const uint32_t*, uint32_t*, uint32_t, int,
                           const uint32_t*, uint32_t*, uint32_t*);
-  PassFn fn;
+  PassFn fn = nullptr;
+#define TE_PICK(HV, W, B) onesweep_pass_kernel<uint32_t, HV, W, B>
+#define TE_PICK_W(HV, B) (window == 8 ? TE_PICK(HV, 8, B) : (window == 16 ? TE_PICK(HV, 16, B) : TE_PICK(HV, 32, B)))
   if (v_in0)
-    fn = window == 8 ? onesweep_pass_kernel<uint32_t, true, 8>
-                     : (window == 16 ? onesweep_pass_kernel<uint32_t, true, 16>
-                                     : onesweep_pass_kernel<uint32_t, true, 32>);
+    fn = block == 256 ? TE_PICK_W(true, 256) : TE_PICK_W(true, 512);
   else
-    fn = window == 8 ? onesweep_pass_kernel<uint32_t, false, 8>
-                     : (window == 16 ? onesweep_pass_kernel<uint32_t, false, 16>
-                                     : onesweep_pass_kernel<uint32_t, false, 32>);
+    fn = block == 256 ? TE_PICK_W(false, 256) : TE_PICK_W(false, 512);
+#undef TE_PICK_W
+#undef TE_PICK
   TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const uint32_t* kin = k_in0;
   const uint32_t* vin = v_in0;
@@ -580,7 +607,7 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
     uint32_t* vout = (pass & 1) ? v_y : v_x;
     uint32_t* lbp = lb + (size_t)pass * p.sort_tiles * kRadix;
     TE_PROF(v_in0 ? "onesweep_pass_pairs" : "onesweep_pass_keys", st);
-    fn<<<p.sort_tiles, kSortBlock, smem, st>>>(kin, kout, vin, vout, p.n, 8 * pass,
+    fn<<<p.sort_tiles, block, smem, st>>>(kin, kout, vin, vout, p.n, 8 * pass,
                                                hist + pass * kRadix, lbp, ticket + pass);
     TE_LAUNCH_CHECK();
     kin = kout;
@@ -650,7 +677,10 @@ int binary_rank_packed(const float* score, const void* target, int32_t dt, int64
   FState* excl = at<FState>(scratch, p.off_inc);
   unsigned long long* partial = at<unsigned long long>(scratch, p.off_partial);
   const RankScalars* scal = at<RankScalars>(scratch, p.off_scal);
-  const ChunkGeom cg = chunk_geom(p.fin_tiles, sms);
+  int occ = 0;  // one resident wave: every chunk runs concurrently, all the same length
+  TE_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+      &occ, mode == 0 ? rank_chunk_kernel<0> : rank_chunk_kernel<1>, kFinBlock, 0));
+  const ChunkGeom cg = chunk_geom(p.fin_tiles, sms, occ);
   const uint32_t nchunks = n > 0 ? cg.nchunks : 0;
   if (nchunks) {
     TE_PROF("rank_chunk_sweep", st);

@@ -15,9 +15,8 @@ namespace te {
 constexpr int kRadixBits = 8;
 constexpr int kRadix = 1 << kRadixBits;
 
-constexpr int kSortBlock = 512;
 constexpr int kSortIpt = 16;
-constexpr int kSortTile = kSortBlock * kSortIpt;  // 8192 records per CTA
+constexpr int kSortBlockDefault = 512;  // 8192 records per CTA; 256 (4096 records) is the alternative
 
 // Look-back word of the sort passes (one per tile and digit), written at most twice:
 //   0                     : tile has not published yet
@@ -25,28 +24,30 @@ constexpr int kSortTile = kSortBlock * kSortIpt;  // 8192 records per CTA
 //   v      (bit31 == 1)   : v & 0x7fffffff = count over this tile and every tile before it
 // A word carries its own validity, so relaxed loads/stores are enough.  Limits n to 2^31 - 1.
 constexpr uint32_t kLbInclusive = 0x80000000u;
-constexpr int kLbWindowDefault = 16;  // predecessors fetched per look-back round trip
+constexpr int kLbWindowDefault = 8;   // predecessors fetched per look-back round trip
 
 template <typename KeyT>
 __device__ __forceinline__ uint32_t digit_of(KeyT k, int shift) {
   return (uint32_t)(k >> shift) & (kRadix - 1);
 }
 
-template <typename KeyT>
+template <typename KeyT, int kSortBlock>
 constexpr size_t onesweep_smem_bytes() {
-  static_assert(sizeof(KeyT) * kSortTile >= sizeof(uint32_t) * (kSortBlock / kWarp) * kRadix,
+  static_assert(sizeof(KeyT) * kSortBlock * kSortIpt >= sizeof(uint32_t) * (kSortBlock / kWarp) * kRadix,
                 "the peer-mask tables alias the key staging area");
-  return sizeof(KeyT) * kSortTile +
+  return sizeof(KeyT) * kSortBlock * kSortIpt +
          sizeof(uint32_t) * ((kSortBlock / kWarp) * kRadix + kRadix + kRadix / kWarp + 4);
 }
 
-template <typename KeyT, bool HAS_VAL, int kLbWindow>
-__global__ void __launch_bounds__(kSortBlock, 2)
+template <typename KeyT, bool HAS_VAL, int kLbWindow, int kSortBlock>
+__global__ void __launch_bounds__(kSortBlock, 1024 / kSortBlock)
     onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                          const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
                          uint32_t n, int shift, const uint32_t* __restrict__ digit_base,
                          uint32_t* lookback, uint32_t* ticket) {
+  static_assert(kSortBlock >= kRadix && kSortBlock % kRadix == 0, "one thread per digit is needed");
   constexpr int WARPS = kSortBlock / kWarp;
+  constexpr int kSortTile = kSortBlock * kSortIpt;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   KeyT* s_keys = reinterpret_cast<KeyT*>(smem_raw);
   uint32_t(*s_whist)[kRadix] = reinterpret_cast<uint32_t(*)[kRadix]>(s_keys + kSortTile);

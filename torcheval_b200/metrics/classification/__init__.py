@@ -1,0 +1,34 @@
+from .accuracy import BinaryAccuracy, MulticlassAccuracy
+from .auprc import BinaryAUPRC, MulticlassAUPRC, MultilabelAUPRC
+from .auroc import BinaryAUROC, MulticlassAUROC
+from .binned_auprc import BinaryBinnedAUPRC, MulticlassBinnedAUPRC, MultilabelBinnedAUPRC
+from .binned_auroc import BinaryBinnedAUROC, MulticlassBinnedAUROC
+from .binned_precision_recall_curve import (
+    BinaryBinnedPrecisionRecallCurve,
+    MulticlassBinnedPrecisionRecallCurve,
+    MultilabelBinnedPrecisionRecallCurve,
+)
+from .confusion_matrix import BinaryConfusionMatrix, MulticlassConfusionMatrix
+from .f1_score import BinaryF1Score, MulticlassF1Score
+
+__all__ = [
+    "BinaryAccuracy",
+    "BinaryAUPRC",
+    "BinaryAUROC",
+    "BinaryBinnedAUPRC",
+    "BinaryBinnedAUROC",
+    "BinaryBinnedPrecisionRecallCurve",
+    "BinaryConfusionMatrix",
+    "BinaryF1Score",
+    "MulticlassAccuracy",
+    "MulticlassAUPRC",
+    "MulticlassAUROC",
+    "MulticlassBinnedAUPRC",
+    "MulticlassBinnedAUROC",
+    "MulticlassBinnedPrecisionRecallCurve",
+    "MulticlassConfusionMatrix",
+    "MulticlassF1Score",
+    "MultilabelAUPRC",
+    "MultilabelBinnedAUPRC",
+    "MultilabelBinnedPrecisionRecallCurve",
+]

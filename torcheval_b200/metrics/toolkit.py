@@ -1,0 +1,253 @@
+"""Distributed glue with the reference's entry points (torcheval/metrics/toolkit.py:34-471):
+``sync_and_compute``, ``sync_and_compute_collection``, ``get_synced_metric(_collection)``,
+``get_synced_state_dict(_collection)``, ``clone_metric(s)``, ``reset_metrics``, ``to_device``,
+``classwise_converter``.
+
+What changed underneath: the reference pickles whole Metric objects
+through ``dist.all_gather_object`` and re-merges them on every rank.  Here
+
+* counter-state metrics (confusion matrix, binned metrics, accuracy, F1) flatten their additive
+  int64 states into ONE buffer and all-reduce it (NCCL over NVLink on GPUs, gloo on CPU);
+* exact binary AUROC over rank-sharded samples runs as a distributed sample sort
+  (``torcheval_b200.distributed``): no rank ever holds more than its share of the samples;
+* sample-keeping metrics are merged with tensor all-gathers (no pickle);
+* anything else (user-defined metrics with arbitrary states) falls back to the reference's
+  object all-gather, so the contract "every Metric syncs" still holds.
+
+Every rank of the group must call these functions in the same order, as with the reference.
+"""
+from __future__ import annotations
+
+import logging
+from copy import deepcopy
+from typing import Any, Dict, Iterable, List, MutableMapping, Optional, TypeVar, Union
+
+import torch
+import torch.distributed as dist
+
+from .metric import Metric
+
+log: logging.Logger = logging.getLogger(__name__)
+
+_TMetrics = TypeVar("_TMetrics", bound=Iterable[Metric])
+
+
+# ------------------------------------------------------------------------------ group helpers
+def _world_size(process_group: Optional[dist.ProcessGroup]) -> int:
+    if not (dist.is_available() and dist.is_initialized()):
+        return 1
+    return dist.get_world_size(process_group)
+
+
+def _validate_rank_and_world_size(world_size: int) -> None:
+    if world_size == 1:
+        log.warning("World size is 1, and metric(s) not synced. returning the input metric(s).")
+    elif world_size == -1:
+        raise RuntimeError("The current process is not part of the process group")
+    if world_size < 1:
+        raise RuntimeError(f"Unexpected world_size {world_size} is seen when syncing metrics!")
+
+
+def _comm_device(metric_device: torch.device, process_group: Optional[dist.ProcessGroup]) -> torch.device:
+    """Tensors handed to a collective must live where the backend works: CUDA for nccl."""
+    backend = dist.get_backend(process_group)
+    if "nccl" in str(backend):
+        if metric_device.type == "cuda":
+            return metric_device
+        return torch.device("cuda", torch.cuda.current_device())
+    return torch.device("cpu")
+
+
+# ------------------------------------------------------------------------------ fast paths
+def _is_additive(metric: Metric) -> bool:
+    return bool(getattr(metric, "_additive_states", False)) and all(
+        isinstance(getattr(metric, n), torch.Tensor) for n in metric._state_name_to_default
+    )
+
+
+def _allreduce_additive(metrics: List[Metric], process_group: Optional[dist.ProcessGroup]) -> List[Metric]:
+    """One all-reduce for all additive states of all given metrics; returns merged clones."""
+    clones = [clone_metric(m) for m in metrics]
+    states = [(c, n) for c in clones for n in c._state_name_to_default]
+    if not states:
+        return clones
+    dev = _comm_device(clones[0].device, process_group)
+    flat = torch.cat([getattr(c, n).reshape(-1).to(device=dev, dtype=torch.int64) for c, n in states])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=process_group)
+    off = 0
+    for c, n in states:
+        old = getattr(c, n)
+        k = old.numel()
+        setattr(c, n, flat[off : off + k].reshape(old.shape).to(device=old.device, dtype=old.dtype))
+        off += k
+    return clones
+
+
+def _all_gather_variable(t: torch.Tensor, cat_dim: int, process_group, dev: torch.device) -> List[torch.Tensor]:
+    """All-gather tensors whose size differs along ``cat_dim`` (pad to the max, trim after)."""
+    world = dist.get_world_size(process_group)
+    t = t.to(dev)
+    moved = t.movedim(cat_dim, 0).contiguous()
+    n = torch.tensor([moved.shape[0]], dtype=torch.int64, device=dev)
+    sizes = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(sizes, n, group=process_group)
+    sizes = [int(s.item()) for s in sizes]
+    m = max(sizes)
+    pad = torch.zeros((m,) + tuple(moved.shape[1:]), dtype=moved.dtype, device=dev)
+    pad[: moved.shape[0]] = moved
+    out = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(out, pad, group=process_group)
+    return [o[:s].movedim(0, cat_dim) for o, s in zip(out, sizes)]
+
+
+def _gather_sample_store(metric: Metric, process_group) -> Optional[Metric]:
+    """Merged clone of a sample-keeping metric via tensor all-gathers; None if not applicable."""
+    from .classification._sample_store import SampleStoreMetric
+    from .classification.auroc import BinaryAUROC, MulticlassAUROC, _resolve_weights
+
+    is_store = isinstance(metric, (SampleStoreMetric, MulticlassAUROC))
+    is_bauroc = isinstance(metric, BinaryAUROC)
+    if not (is_store or is_bauroc):
+        return None
+    cat_dim = -1 if is_bauroc else getattr(metric, "_cat_dim", 0)
+    dev = _comm_device(metric.device, process_group)
+    world = dist.get_world_size(process_group)
+    # every rank must take the same branch: agree on who has data / weights
+    has = torch.tensor(
+        [1 if metric.inputs else 0, 1 if (is_bauroc and metric.inputs and _resolve_weights(metric.inputs, metric.weights) is not None) else 0],
+        dtype=torch.int64, device=dev,
+    )
+    flags = [torch.zeros_like(has) for _ in range(world)]
+    dist.all_gather(flags, has, group=process_group)
+    flags = [f.tolist() for f in flags]
+    if not all(f[0] for f in flags):
+        return None  # some rank is empty: shapes unknown there, use the generic path
+    any_weight = any(f[1] for f in flags)
+    metric._prepare_for_merge_state()
+    merged = clone_metric(metric)
+    xs = _all_gather_variable(metric.inputs[0], cat_dim, process_group, dev)
+    ts = _all_gather_variable(metric.targets[0], cat_dim, process_group, dev)
+    merged.inputs = [x.to(metric.device) for x in xs]
+    merged.targets = [t.to(metric.device) for t in ts]
+    if is_bauroc:
+        if any_weight:
+            w = _resolve_weights(metric.inputs, metric.weights)
+            if w is None:
+                w = torch.ones_like(metric.inputs[0], dtype=torch.double)
+            ws = _all_gather_variable(w, cat_dim, process_group, dev)
+            merged.weights = [w.to(metric.device) for w in ws]
+        else:
+            merged.weights = [x.new_empty(x.shape[:-1] + (0,), dtype=torch.double) for x in merged.inputs]
+    return merged
+
+
+def _sync_metric_object(metric: Any, process_group, world_size: int) -> List[Any]:
+    """The reference's generic path (toolkit.py:371-391): pickle + all_gather_object."""
+    if isinstance(metric, Metric):
+        metric._prepare_for_merge_state()
+    else:
+        for m in metric.values():
+            m._prepare_for_merge_state()
+    gathered = [None] * world_size
+    dist.all_gather_object(gathered, metric, group=process_group)
+    return gathered
+
+
+# ------------------------------------------------------------------------------ public API
+def get_synced_metric(metric: Metric, process_group: Optional[dist.ProcessGroup] = None) -> Metric:
+    """A metric whose state is the merge over all ranks of ``process_group`` (on every rank).
+    With world size 1 the input object itself is returned, like the reference."""
+    world_size = _world_size(process_group)
+    _validate_rank_and_world_size(world_size)
+    if world_size == 1:
+        return metric
+    if _is_additive(metric):
+        return _allreduce_additive([metric], process_group)[0]
+    merged = _gather_sample_store(metric, process_group)
+    if merged is not None:
+        return merged
+    gathered = _sync_metric_object(metric, process_group if process_group else dist.group.WORLD, world_size)
+    return clone_metric(gathered[0]).to(metric.device).merge_state(gathered[1:])
+
+
+def sync_and_compute(metric: Metric, process_group: Optional[dist.ProcessGroup] = None) -> Any:
+    """``compute()`` of the state merged over all ranks, returned on all ranks."""
+    world_size = _world_size(process_group)
+    if world_size > 1:
+        from .. import distributed as tdist
+
+        fast = tdist.try_sharded_compute(metric, process_group)
+        if fast is not None:
+            return fast
+    return get_synced_metric(metric, process_group).compute()
+
+
+def get_synced_metric_collection(
+    metric_collection: Union[Dict[str, Metric], MutableMapping[str, Metric]],
+    process_group: Optional[dist.ProcessGroup] = None,
+) -> Union[Dict[str, Metric], MutableMapping[str, Metric]]:
+    world_size = _world_size(process_group)
+    _validate_rank_and_world_size(world_size)
+    if world_size == 1:
+        return metric_collection
+    names = list(metric_collection.keys())
+    additive = [k for k in names if _is_additive(metric_collection[k])]
+    out: Dict[str, Metric] = {}
+    if additive:  # all counter metrics of the collection share one all-reduce
+        for k, m in zip(additive, _allreduce_additive([metric_collection[k] for k in additive], process_group)):
+            out[k] = m
+    for k in names:
+        if k not in out:
+            out[k] = get_synced_metric(metric_collection[k], process_group)
+    return {k: out[k] for k in names}
+
+
+def sync_and_compute_collection(
+    metrics: MutableMapping[str, Metric], process_group: Optional[dist.ProcessGroup] = None
+) -> Dict[str, Any]:
+    synced = get_synced_metric_collection(metrics, process_group)
+    return {key: m.compute() for key, m in synced.items()}
+
+
+def get_synced_state_dict(metric: Metric, process_group: Optional[dist.ProcessGroup] = None) -> Dict[str, Any]:
+    return get_synced_metric(metric, process_group).state_dict()
+
+
+def get_synced_state_dict_collection(
+    metric_collection: MutableMapping[str, Metric], process_group: Optional[dist.ProcessGroup] = None
+) -> Dict[str, Dict[str, Any]]:
+    synced = get_synced_metric_collection(metric_collection, process_group)
+    return {key: m.state_dict() for key, m in synced.items()}
+
+
+def clone_metric(metric: Metric) -> Metric:
+    return deepcopy(metric)
+
+
+def clone_metrics(metrics: _TMetrics) -> List[Metric]:
+    return [clone_metric(metric) for metric in metrics]
+
+
+def reset_metrics(metrics: _TMetrics) -> _TMetrics:
+    for metric in metrics:
+        metric.reset()
+    return metrics
+
+
+def to_device(metrics: _TMetrics, device: torch.device, *args: Any, **kwargs: Any) -> _TMetrics:
+    for metric in metrics:
+        metric.to(device, *args, **kwargs)
+    return metrics
+
+
+def classwise_converter(
+    input: torch.Tensor, name: str, labels: Optional[List[str]] = None
+) -> Dict[str, torch.Tensor]:
+    """{f"{name}_{label}": row} for an un-averaged per-class result."""
+    if labels is None:
+        return {f"{name}_{i}": val for i, val in enumerate(input)}
+    if input.size(dim=0) != len(labels):
+        raise ValueError(
+            f"Number of labels {len(labels)} must be equal to the number of classes {input.size(dim=0)}!"
+        )
+    return {f"{name}_{label}": val for label, val in zip(labels, input)}
