@@ -182,6 +182,26 @@ TE_API int te_binary_auprc_general(const float* score, const void* target, int32
                                    int64_t n, double* out, void* scratch, size_t scratch_bytes,
                                    void* stream);
 
+/* Pieces of the distributed sample sort of rank-sharded scores (torcheval_b200/distributed.py;
+ * replaces dist.all_gather_object of the whole sample set at toolkit.py:388).
+ *  te_rank_pack: score/target -> packed keys ((float bits << 1) | label), info[0] = #positives,
+ *    info[1] = TE_RANK_FLAG_* (int64[2], device).  keys_out must be 16-byte aligned.
+ *  te_partition_u32: stable partition of keys by up to 15 ascending splitters given in HOST
+ *    memory (bucket = #{splitters <= key}); counts (int64[num_splitters + 1], device) receives
+ *    the bucket sizes, keys_out the keys grouped by bucket.
+ *  te_binary_auroc_from_keys: sort packed keys and integrate; out[] as te_binary_auroc plus
+ *    out[5], out[6] = high / low 32 bits of the exact integer 2U and out[7] = n. */
+TE_API size_t te_rank_pack_scratch_bytes(int64_t n);
+TE_API int te_rank_pack(const float* score, const void* target, int32_t target_dtype, int64_t n,
+                        uint32_t* keys_out, int64_t* info, void* scratch, size_t scratch_bytes,
+                        void* stream);
+TE_API size_t te_partition_u32_scratch_bytes(int64_t n);
+TE_API int te_partition_u32(const uint32_t* keys_in, int64_t n, const uint32_t* splitters_host,
+                            int32_t num_splitters, uint32_t* keys_out, int64_t* counts, void* scratch,
+                            size_t scratch_bytes, void* stream);
+TE_API int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, double* out, void* scratch,
+                                     size_t scratch_bytes, void* stream);
+
 /* The sort on its own: ascending, stable, 32-bit keys with an optional 32-bit payload
  * (vals_in/vals_out both NULL or both set).  Replaces torch.sort at auroc.py:121. */
 TE_API size_t te_sort_u32_scratch_bytes(int64_t n, int32_t with_values);

@@ -1,0 +1,62 @@
+"""One rank of an NCCL group: the same checks as tests/_dist_worker.py with the real kernels."""
+import json
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+import oracle  # noqa: E402
+
+
+def main():
+    local = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    rank, world = dist.get_rank(), dist.get_world_size()
+    from torcheval_b200 import distributed as tdist
+    from torcheval_b200.metrics import BinaryAUROC, BinaryBinnedAUPRC, MulticlassConfusionMatrix
+    from torcheval_b200.metrics import toolkit
+
+    res = {}
+    rs = np.random.default_rng(11)
+    n = 1 << 21
+    cases = {
+        "uniform": (rs.random(n, dtype=np.float32), rs.integers(0, 2, n)),
+        "ties": ((rs.integers(0, 999, n) / 999).astype(np.float32), rs.integers(0, 2, n)),
+        "heavy_tie": (np.where(rs.random(n) < 0.6, 0.5, rs.random(n)).astype(np.float32), rs.integers(0, 2, n)),
+    }
+    for name, (x, y) in cases.items():
+        cut = [0] + [int(n * (i + 1) / (world * 2)) for i in range(world - 1)] + [n]
+        xs = torch.from_numpy(x[cut[rank]:cut[rank + 1]]).to(dev)
+        ys = torch.from_numpy(y[cut[rank]:cut[rank + 1]]).to(dev)
+        out = tdist.sharded_binary_auroc(xs, ys).cpu().numpy()
+        want, tp, fp = oracle.binary_auroc(x, y)
+        res[f"sharded/{name}"] = [float(out[0]), want, float(out[1]), tp, float(out[2]), fp]
+        m = BinaryAUROC(device=dev).update(xs, ys)
+        res[f"sync/{name}"] = [float(toolkit.sync_and_compute(m)), want]
+        mh = BinaryAUROC().update(xs.cpu(), ys.cpu())  # host-resident state, NCCL group
+        res[f"sync_host/{name}"] = [float(toolkit.sync_and_compute(mh)), want]
+    C = 1000
+    p, t = rs.integers(0, C, n), rs.integers(0, C, n)
+    sl = slice(rank * n // world, (rank + 1) * n // world)
+    cm = MulticlassConfusionMatrix(C, device=dev).update(torch.from_numpy(p[sl]).to(dev), torch.from_numpy(t[sl]).to(dev))
+    got = toolkit.sync_and_compute(cm)
+    res["sync/cm_equal"] = bool(np.array_equal(got.cpu().numpy(), oracle.confusion_matrix(p, t, C)[0].astype(np.float32)))
+    xb = rs.random(n, dtype=np.float32)
+    yb = rs.integers(0, 2, n)
+    bb = BinaryBinnedAUPRC(threshold=10000, device=dev).update(torch.from_numpy(xb[sl]).to(dev), torch.from_numpy(yb[sl]).to(dev))
+    tp_, fp_, fn_ = oracle.binned_update(xb, yb, np.linspace(0, 1, 10000, dtype=np.float32))
+    res["sync/binned_auprc"] = [float(toolkit.sync_and_compute(bb)[0][0]), oracle.binned_auprc_from_counts(tp_, fp_, fn_)]
+    Path(os.environ["TE_TEST_OUT"] + f".{rank}").write_text(json.dumps(res))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,112 @@
+"""Worker for tests/test_distributed_cpu.py: one rank of a gloo group on CPU.  The kernels are
+replaced by the CPU stand-ins (tests/cpu_backend.py); what is under test is the host-side
+protocol: splitters, partition/exchange bookkeeping, prefix fix-up, all-reduce of counters,
+tensor all-gathers, and that every rank gets the same answer."""
+import json
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+
+import cpu_backend  # noqa: E402
+import oracle  # noqa: E402
+
+
+def shard(a, rank, world, axis=0):
+    return np.array_split(a, world, axis=axis)[rank]
+
+
+def main():
+    dist.init_process_group("gloo")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    cpu_backend.install()
+    from torcheval_b200 import distributed as tdist
+    from torcheval_b200.metrics import (
+        BinaryAUPRC, BinaryAUROC, BinaryBinnedAUPRC, MulticlassAccuracy, MulticlassAUROC, MulticlassConfusionMatrix,
+    )
+    from torcheval_b200.metrics import toolkit
+
+    res = {}
+    rs = np.random.default_rng(7)
+    n = 20011
+    cases = {
+        "uniform": (rs.random(n, dtype=np.float32), rs.integers(0, 2, n)),
+        "ties": ((rs.integers(0, 50, n) / 50).astype(np.float32), rs.integers(0, 2, n)),
+        "heavy_tie": (np.where(rs.random(n) < 0.6, 0.5, rs.random(n)).astype(np.float32), rs.integers(0, 2, n)),
+        "constant": (np.full(n, 0.25, dtype=np.float32), rs.integers(0, 2, n)),
+        "sorted_input": (np.sort(rs.random(n, dtype=np.float32)), rs.integers(0, 2, n)),
+        "all_pos": (rs.random(n, dtype=np.float32), np.ones(n, dtype=np.int64)),
+    }
+    for name, (x, y) in cases.items():
+        # uneven shards, the last rank gets most
+        cut = [0] + [int(n * (i + 1) / (world * 3)) for i in range(world - 1)] + [n]
+        xs, ys = x[cut[rank]:cut[rank + 1]], y[cut[rank]:cut[rank + 1]]
+        out = tdist.sharded_binary_auroc(torch.from_numpy(xs), torch.from_numpy(ys))
+        want, tp, fp = oracle.binary_auroc(x, y)
+        res[f"sharded/{name}"] = [float(out[0]), want, float(out[1]), tp, float(out[2]), fp]
+        m = BinaryAUROC()
+        half = xs.size // 2
+        m.update(torch.from_numpy(xs[:half]), torch.from_numpy(ys[:half]))
+        m.update(torch.from_numpy(xs[half:]), torch.from_numpy(ys[half:]))
+        res[f"sync/{name}"] = [float(toolkit.sync_and_compute(m)), want]
+        assert len(m.inputs) == 1  # compacted by _prepare_for_merge_state, data unchanged
+    # negative scores: the sharded path declines on every rank, the gather path answers
+    x, y = (rs.standard_normal(n) * 2).astype(np.float32), rs.integers(0, 2, n)
+    m = BinaryAUROC().update(torch.from_numpy(shard(x, rank, world)), torch.from_numpy(shard(y, rank, world)))
+    res["sync/logits"] = [float(toolkit.sync_and_compute(m)), oracle.binary_auroc(x, y)[0]]
+    # weighted: gather path with weights
+    w = rs.random(n) + 0.5
+    m = BinaryAUROC().update(
+        torch.from_numpy(shard(x, rank, world)), torch.from_numpy(shard(y, rank, world)), torch.from_numpy(shard(w, rank, world))
+    )
+    res["sync/weighted"] = [float(toolkit.sync_and_compute(m)), oracle.binary_auroc(x, y, w)[0]]
+    m = BinaryAUPRC().update(torch.from_numpy(shard(x, rank, world)), torch.from_numpy(shard(y, rank, world)))
+    res["sync/auprc"] = [float(toolkit.sync_and_compute(m)), oracle.binary_auprc(x, y)]
+    # counters: one all-reduce
+    C = 7
+    p, t = rs.integers(0, C, n), rs.integers(0, C, n)
+    cm = MulticlassConfusionMatrix(C).update(torch.from_numpy(shard(p, rank, world)), torch.from_numpy(shard(t, rank, world)))
+    local_before = cm.confusion_matrix.clone()
+    got = toolkit.sync_and_compute(cm)
+    res["sync/cm_equal"] = bool(np.array_equal(got.numpy(), oracle.confusion_matrix(p, t, C)[0].astype(np.float32)))
+    res["sync/cm_input_unchanged"] = bool(torch.equal(cm.confusion_matrix, local_before))
+    acc = MulticlassAccuracy().update(torch.from_numpy(shard(p, rank, world)), torch.from_numpy(shard(t, rank, world)))
+    xb = rs.random(n, dtype=np.float32)
+    bb = BinaryBinnedAUPRC(threshold=64).update(torch.from_numpy(shard(xb, rank, world)), torch.from_numpy(shard(y, rank, world)))
+    coll = toolkit.sync_and_compute_collection({"acc": acc, "cm": cm, "bb": bb})
+    res["coll/acc"] = [float(coll["acc"]), float((p == t).mean())]
+    tp_, fp_, fn_ = oracle.binned_update(xb, y, np.linspace(0, 1, 64, dtype=np.float32))
+    res["coll/bb"] = [float(coll["bb"][0][0]), oracle.binned_auprc_from_counts(tp_, fp_, fn_)]
+    sd = toolkit.get_synced_state_dict(cm)
+    res["sd/cm_total"] = [int(sd["confusion_matrix"].sum()), n]
+    # multiclass AUROC: tensor all-gather path (uneven shards)
+    nn, CC = 901, 4
+    xi, yi = rs.random((nn, CC), dtype=np.float32), rs.integers(0, CC, nn)
+    cut = [0, 100 if world > 1 else nn, nn] if world == 2 else [0] + [nn * (i + 1) // world for i in range(world)]
+    mm = MulticlassAUROC(num_classes=CC, average=None).update(
+        torch.from_numpy(xi[cut[rank]:cut[rank + 1]]), torch.from_numpy(yi[cut[rank]:cut[rank + 1]])
+    )
+    res["sync/mc_auroc"] = [toolkit.sync_and_compute(mm).tolist(), oracle.multiclass_auroc(xi, yi).tolist()]
+    # a rank with no data: generic object path still works
+    me = BinaryAUROC()
+    if rank != 0:
+        me.update(torch.from_numpy(xs), torch.from_numpy(ys))
+    try:
+        v = float(toolkit.sync_and_compute(me))
+        res["sync/empty_rank_ok"] = bool(np.isfinite(v))
+    except Exception as e:  # noqa: BLE001
+        res["sync/empty_rank_ok"] = f"raised {type(e).__name__}: {e}"
+    Path(os.environ["TE_TEST_OUT"] + f".{rank}").write_text(json.dumps(res))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

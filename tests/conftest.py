@@ -5,6 +5,7 @@ import numpy as np
 import pytest
 
 ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(Path(__file__).resolve().parent))
 if str(ROOT) not in sys.path:
     sys.path.insert(0, str(ROOT))
 

@@ -1,0 +1,224 @@
+"""TEST-ONLY stand-in for the CUDA kernels: every function of ``torcheval_b200.ops`` re-implemented
+on CPU tensors with the oracle (oracle/te_oracle.c) and numpy, so that the host-side logic —
+argument checks, state handling, merge/sync, the distributed sample-sort protocol — can be tested
+without a GPU.  Installed by monkeypatching (``install()``); the product never imports this and
+has no CPU path of its own."""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+import oracle
+
+I64_MAX = np.iinfo(np.int64).max
+I64_MIN = np.iinfo(np.int64).min
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+def _range_report(p, t, C):
+    bad_p = p[(p < 0) | (p >= C)]
+    bad_t = t[(t < 0) | (t >= C)]
+    r = [I64_MAX, I64_MIN, I64_MAX, I64_MIN]
+    if bad_p.size:
+        r[0], r[1] = int(bad_p.min()), int(bad_p.max())
+    if bad_t.size:
+        r[2], r[3] = int(bad_t.min()), int(bad_t.max())
+    return torch.tensor(r, dtype=torch.int64)
+
+
+def cm_update_(cm, pred, target, num_classes, variant=0):
+    p, t = _np(pred), _np(target)
+    add, _, _ = oracle.confusion_matrix(p, t, num_classes)
+    cm += torch.from_numpy(add)
+    return _range_report(p, t, num_classes)
+
+
+def cm_update_logits_(cm, logits, target, num_classes):
+    return cm_update_(cm, torch.from_numpy(oracle.argmax_rows(_np(logits))), target, num_classes)
+
+
+def class_counts_(counts3, input, target, num_classes):
+    p = oracle.argmax_rows(_np(input)) if input.dim() == 2 else _np(input)
+    t = _np(target)
+    ok = (p >= 0) & (p < num_classes) & (t >= 0) & (t < num_classes)
+    po, to = p[ok], t[ok]
+    counts3[0] += torch.from_numpy(np.bincount(to[po == to], minlength=num_classes))
+    counts3[1] += torch.from_numpy(np.bincount(to, minlength=num_classes))
+    counts3[2] += torch.from_numpy(np.bincount(po, minlength=num_classes))
+    return _range_report(p, t, num_classes)
+
+
+def match_count(pred, target):
+    return (pred == target).sum().to(torch.int64)
+
+
+def binned_hist_update_(hist, x, target, threshold):
+    xs, ts = _np(x), _np(target)
+    thr = _np(threshold)
+    if xs.ndim == 1:
+        xs, ts = xs[None], ts[None]
+    for k in range(xs.shape[0]):
+        keep = ~np.isnan(xs[k])
+        h = oracle.binned_hist(xs[k][keep], ts[k][keep], thr)
+        h[0, 0] += int(((~keep) & (ts[k] == 0)).sum())
+        h[0, 1] += int(((~keep) & (ts[k] != 0)).sum())
+        hist.view(-1, thr.size + 1, 2)[k] += torch.from_numpy(h)
+
+
+def binned_hist2d_update_(hist, x, target, threshold, multilabel):
+    xs, ts, thr = _np(x), _np(target), _np(threshold)
+    for c in range(xs.shape[1]):
+        lab = ts[:, c] != 0 if multilabel else ts == c
+        hist[c] += torch.from_numpy(oracle.binned_hist(xs[:, c], lab.astype(np.int64), thr))
+
+
+def binned_counts(hist, T, want_fn=True):
+    h = _np(hist).reshape(-1, T + 1, 2)
+    tp, fp, fn = zip(*(oracle.binned_counts(h[k]) for k in range(h.shape[0])))
+    f = lambda a: torch.from_numpy(np.stack(a))  # noqa: E731
+    return f(tp), f(fp), (f(fn) if want_fn else None)
+
+
+def binned_integrate(tp, fp, fn, mode):
+    out = []
+    for k in range(tp.shape[0]):
+        if mode == 0:
+            out.append(oracle.binned_auroc_from_counts(_np(tp[k]), _np(fp[k])))
+        else:
+            out.append(oracle.binned_auprc_from_counts(_np(tp[k]), _np(fp[k]), _np(fn[k])))
+    return torch.tensor(out, dtype=torch.float64)
+
+
+def _flags(score, target):
+    x, t = _np(score), _np(target).astype(np.float64)
+    f = 0
+    if ((t != 0) & (t != 1)).any():
+        f |= 1
+    if (np.signbit(x) & (x != 0)).any():
+        f |= 2
+    return f
+
+
+def _exact_2u(x, y):
+    """2U as an exact Python int from the (score, label) pairs, ties included."""
+    order = np.argsort(x, kind="stable")
+    xs, ys = x[order], y[order].astype(np.int64)
+    _, start, cnt = np.unique(xs, return_index=True, return_counts=True)
+    neg = np.add.reduceat(1 - ys, start)
+    pos = np.add.reduceat(ys, start)
+    below = np.concatenate([[0], np.cumsum(neg)[:-1]])
+    return int(np.sum(pos.astype(object) * (2 * below.astype(object) + neg.astype(object))))
+
+
+def binary_auroc_packed(score, target):
+    f = _flags(score, target)
+    out = torch.zeros(8, dtype=torch.float64)
+    out[4] = f
+    if f:
+        return out
+    x, y = _np(score), _np(target).astype(np.int64)
+    v, tp, fp = oracle.binary_auroc(x, y)
+    u2 = _exact_2u(x, y) if x.size else 0
+    out[:4] = torch.tensor([v, tp, fp, float(u2)], dtype=torch.float64)
+    out[5], out[6], out[7] = float(u2 >> 32), float(u2 & 0xFFFFFFFF), float(x.size)
+    return out
+
+
+def binary_auprc_packed(score, target):
+    f = _flags(score, target)
+    out = torch.zeros(8, dtype=torch.float64)
+    out[4] = f
+    if not f:
+        y = _np(target).astype(np.int64)
+        out[0] = oracle.binary_auprc(_np(score), y)
+        out[1], out[2] = y.sum(), (1 - y).sum()
+    return out
+
+
+def binary_auroc_general(score, target, weight=None):
+    v, tp, fp = oracle.binary_auroc(_np(score), _np(target).astype(np.float64), None if weight is None else _np(weight))
+    out = torch.zeros(8, dtype=torch.float64)
+    out[:3] = torch.tensor([v, tp, fp], dtype=torch.float64)
+    return out
+
+
+def binary_auprc_general(score, target):
+    t = _np(target)
+    out = torch.zeros(8, dtype=torch.float64)
+    out[0] = oracle.binary_auprc(_np(score), (t == 1).astype(np.int64))
+    return out
+
+
+def sort_u32(keys, vals=None):
+    k = _np(keys).view(np.uint32)
+    order = np.argsort(k, kind="stable")
+    ok = torch.from_numpy(k[order].view(np.int32).copy())
+    return ok, (None if vals is None else vals[torch.from_numpy(order)])
+
+
+def rank_pack(score, target):
+    x = _np(score).astype(np.float32).copy()
+    bits = x.view(np.uint32).copy()
+    bits[bits == 0x80000000] = 0
+    y = _np(target)
+    lab = (y == 1).astype(np.uint32)
+    keys = ((bits << np.uint32(1)) | lab).astype(np.uint32)
+    info = torch.tensor([int(lab.sum()), _flags(score, target)], dtype=torch.int64)
+    return torch.from_numpy(keys.view(np.int32).copy()), info
+
+
+def partition_u32(keys, splitters):
+    k = _np(keys).view(np.uint32)
+    sp = np.asarray([int(v) & 0xFFFFFFFF for v in splitters], dtype=np.uint64)
+    bucket = np.searchsorted(sp, k.astype(np.uint64), side="right") if sp.size else np.zeros(k.size, dtype=np.int64)
+    order = np.argsort(bucket, kind="stable")
+    counts = np.bincount(bucket, minlength=len(splitters) + 1).astype(np.int64)
+    return torch.from_numpy(k[order].view(np.int32).copy()), torch.from_numpy(counts)
+
+
+def binary_auroc_from_keys(keys):
+    k = _np(keys).view(np.uint32)
+    x = (k >> np.uint32(1)).astype(np.uint32).view(np.float32)
+    y = (k & np.uint32(1)).astype(np.int64)
+    return binary_auroc_packed(torch.from_numpy(x.copy()), torch.from_numpy(y))
+
+
+_NAMES = [
+    "cm_update_", "cm_update_logits_", "class_counts_", "match_count", "binned_hist_update_",
+    "binned_hist2d_update_", "binned_counts", "binned_integrate", "binary_auroc_packed",
+    "binary_auprc_packed", "binary_auroc_general", "binary_auprc_general", "sort_u32", "rank_pack",
+    "partition_u32", "binary_auroc_from_keys",
+]
+
+
+def install(monkeypatch=None):
+    """Route torcheval_b200.ops to the CPU stand-ins and make the CPU the 'compute device'."""
+    import torcheval_b200._binned as _binned
+    import torcheval_b200._counting as _counting
+    import torcheval_b200._ranking as _ranking
+    import torcheval_b200.ops as ops
+
+    def setter(obj, name, val):
+        if monkeypatch is not None:
+            monkeypatch.setattr(obj, name, val)
+        else:
+            setattr(obj, name, val)
+
+    g = globals()
+    for name in _NAMES:
+        setter(ops, name, g[name])
+    cpu = lambda t: torch.device("cpu")  # noqa: E731
+    for mod in (_ranking, _binned, _counting):
+        setter(mod, "compute_device", cpu)
+    import torcheval_b200.metrics.functional.classification.accuracy as acc
+    import torcheval_b200.metrics.functional.classification.binned_auroc as bauroc
+    import torcheval_b200.metrics.functional.classification.f1_score as f1
+
+    for mod in (acc, bauroc, f1):
+        setter(mod, "compute_device", cpu)
+    import torcheval_b200.distributed as tdist
+
+    setter(tdist, "compute_device", cpu) if hasattr(tdist, "compute_device") else None

@@ -1,0 +1,403 @@
+"""The drop-in surface (functional + class API) against the reference fixtures.
+
+Every test runs twice: with the CPU stand-in kernels of tests/cpu_backend.py (host logic only,
+no GPU needed) and, marked ``gpu``, with the real sm_100a kernels — same assertions."""
+import copy
+import pickle
+
+import numpy as np
+import pytest
+import torch
+
+import cpu_backend
+
+
+@pytest.fixture(params=["cpu_standin", pytest.param("cuda", marks=pytest.mark.gpu)])
+def backend(request, monkeypatch):
+    if request.param == "cpu_standin":
+        cpu_backend.install(monkeypatch)
+    else:
+        assert torch.cuda.is_available()
+    return request.param
+
+
+def T(a, dtype=None):
+    t = torch.as_tensor(np.ascontiguousarray(a))
+    return t if dtype is None else t.to(dtype)
+
+
+def close(a, b, rtol=1e-6):
+    a = a.detach().cpu().numpy() if isinstance(a, torch.Tensor) else a
+    np.testing.assert_allclose(np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64), rtol=rtol, atol=rtol * 1e-2)
+
+
+# ------------------------------------------------------------------------------ functional
+def test_functional_exact(backend, golden):
+    from torcheval_b200.metrics import functional as F
+
+    for name in golden.cases("binary"):
+        c = golden.case(f"binary/{name}")
+        a = F.binary_auroc(T(c["x"]), T(c["y"]))
+        assert a.dtype == torch.float64 and a.shape == () and a.device.type == "cpu"
+        close(a, c["auroc_f64"])
+        p = F.binary_auprc(T(c["x"]), T(c["y"]))
+        assert p.dtype == torch.float32 and p.shape == ()
+        close(p, c["auprc"], 1e-4)
+    c = golden.case("binary_weighted/soft")
+    close(F.binary_auroc(T(c["x"]), T(c["y"]), weight=T(c["w"])), c["auroc"])
+    c = golden.case("binary_multitask/t3")
+    close(F.binary_auroc(T(c["x"]), T(c["y"]), num_tasks=3), c["auroc"])
+    p = F.binary_auprc(T(c["x"]), T(c["y"]), num_tasks=3)
+    assert p.shape == (3,) and p.dtype == torch.float32
+    close(p, c["auprc"], 1e-4)
+    assert F.binary_auprc(T(c["x"][:1]), T(c["y"][:1])).shape == (1,)  # 1 x N keeps its leading dim
+    for name in golden.cases("multiclass"):
+        c = golden.case(f"multiclass/{name}")
+        C = c["x"].shape[1]
+        a = F.multiclass_auroc(T(c["x"]), T(c["y"]), num_classes=C, average=None)
+        assert a.dtype == torch.float32 and a.shape == (C,)
+        close(a, c["auroc"], 1e-4)
+        close(F.multiclass_auroc(T(c["x"]), T(c["y"]), num_classes=C), c["auroc_macro"], 1e-4)
+        close(F.multiclass_auprc(T(c["x"]), T(c["y"]), average=None), c["auprc"], 1e-4)
+        close(F.multiclass_auprc(T(c["x"]), T(c["y"]), num_classes=C), c["auprc_macro"], 1e-4)
+    for name in golden.cases("multilabel"):
+        c = golden.case(f"multilabel/{name}")
+        close(F.multilabel_auprc(T(c["x"]), T(c["y"]), average=None), c["auprc"], 1e-4)
+        close(F.multilabel_auprc(T(c["x"]), T(c["y"])), c["auprc_macro"], 1e-4)
+
+
+def test_functional_binned(backend, golden):
+    from torcheval_b200.metrics import functional as F
+    from torcheval_b200.metrics.functional.classification.binned_precision_recall_curve import (
+        _binary_binned_precision_recall_curve_update,
+    )
+
+    for name in golden.cases("binned"):
+        c = golden.case(f"binned/{name}")
+        thr = T(c["thr"])
+        tp, fp, fn = _binary_binned_precision_recall_curve_update(T(c["x"]), T(c["y"]), thr)
+        assert tp.dtype == torch.int64
+        np.testing.assert_array_equal(tp.numpy(), c["tp"])
+        np.testing.assert_array_equal(fp.numpy(), c["fp"])
+        np.testing.assert_array_equal(fn.numpy(), c["fn"])
+        prec, rec, t2 = F.binary_binned_precision_recall_curve(T(c["x"]), T(c["y"]), threshold=thr)
+        assert prec.shape == (thr.numel() + 1,) and prec[-1] == 1 and rec[-1] == 0 and t2 is thr
+        if "auroc" in c:
+            a, _ = F.binary_binned_auroc(T(c["x"]), T(c["y"]), threshold=thr)
+            assert a.dtype == torch.float64 and a.shape == (1,)
+            close(a, c["auroc"])
+        if "auprc" in c:
+            p, _ = F.binary_binned_auprc(T(c["x"]), T(c["y"]), threshold=thr)
+            assert p.dtype == torch.float32 and p.shape == ()
+            close(p, c["auprc"], 1e-4)
+    c = golden.case("binned_multitask/t2")
+    a, thr = F.binary_binned_auroc(T(c["x"]), T(c["y"]), num_tasks=2, threshold=50)
+    close(a, c["auroc"])
+    np.testing.assert_array_equal(thr.numpy(), c["thr"])
+    close(F.binary_binned_auprc(T(c["x"]), T(c["y"]), num_tasks=2, threshold=50)[0], c["auprc"], 1e-4)
+    c = golden.case("binned_multiclass/c6")
+    from torcheval_b200.metrics.functional.classification.binned_precision_recall_curve import (
+        _multiclass_binned_precision_recall_curve_update as mc_update,
+        _multilabel_binned_precision_recall_curve_update as ml_update,
+    )
+
+    for opt in ("vectorized", "memory"):
+        tp, fp, fn = mc_update(T(c["x"]), T(c["y"]), 6, T(c["thr"]), opt)
+        np.testing.assert_array_equal(tp.numpy(), c["tp"])
+        np.testing.assert_array_equal(fp.numpy(), c["fp"])
+        np.testing.assert_array_equal(fn.numpy(), c["fn"])
+    close(F.multiclass_binned_auprc(T(c["x"]), T(c["y"]), num_classes=6, threshold=T(c["thr"]), average=None)[0], c["auprc"], 1e-4)
+    pr, rc, _ = F.multiclass_binned_precision_recall_curve(T(c["x"]), T(c["y"]), num_classes=6, threshold=T(c["thr"]))
+    assert len(pr) == 6 and pr[0].shape == (c["thr"].size + 1,)
+    c = golden.case("binned_multilabel/l6")
+    tp, fp, fn = ml_update(T(c["x"]), T(c["y"]), 6, T(c["thr"]))
+    np.testing.assert_array_equal(tp.numpy(), c["tp"])
+    np.testing.assert_array_equal(fn.numpy(), c["fn"])
+    close(F.multilabel_binned_auprc(T(c["x"]), T(c["y"]), num_labels=6, threshold=T(c["thr"]), average=None)[0], c["auprc"], 1e-4)
+
+
+def test_functional_counting(backend, golden):
+    from torcheval_b200.metrics import functional as F
+
+    for name in golden.cases("cm"):
+        c = golden.case(f"cm/{name}")
+        cm = F.multiclass_confusion_matrix(T(c["pred"]), T(c["target"]), c["cm"].shape[0])
+        assert cm.dtype == torch.int64
+        np.testing.assert_array_equal(cm.numpy(), c["cm"])
+    for name in golden.cases("cm_logits"):
+        c = golden.case(f"cm_logits/{name}")
+        cm = F.multiclass_confusion_matrix(T(c["logits"]), T(c["target"]), c["cm"].shape[0])
+        np.testing.assert_array_equal(cm.numpy(), c["cm"])
+    c = golden.case("cm_binary/t05")
+    np.testing.assert_array_equal(F.binary_confusion_matrix(T(c["x"]), T(c["target"])).numpy(), c["cm"])
+    n = F.multiclass_confusion_matrix(T(c["x"] >= 0.5, torch.int64), T(c["target"]), 2, normalize="all")
+    assert n.dtype == torch.float32
+    close(n.sum(), 1.0)
+    c = golden.case("acc_f1/c5")
+    p, t = T(c["pred"]), T(c["target"])
+    for avg, key in (("micro", "acc_micro"), ("macro", "acc_macro"), (None, "acc_none")):
+        r = F.multiclass_accuracy(p, t, average=avg, num_classes=5)
+        assert r.dtype == torch.float32
+        close(r, c[key])
+    for avg, key in (("micro", "f1_micro"), ("macro", "f1_macro"), ("weighted", "f1_weighted"), (None, "f1_none")):
+        close(F.multiclass_f1_score(p, t, num_classes=5, average=avg), c[key])
+    close(F.binary_accuracy(T([0.1, 0.9, 0.6, 0.2]), T([0, 1, 0, 0])), 0.75)
+    close(F.binary_f1_score(T([0.1, 0.9, 0.6, 0.2]), T([0, 1, 0, 0])), 2 / 3)
+    close(F.multiclass_accuracy(T([[0.9, 0.1, 0], [0.1, 0.2, 0.7], [0.3, 0.4, 0.3]]), T([0, 1, 1]), k=2), 1.0)
+
+
+def test_error_messages(backend):
+    from torcheval_b200.metrics import functional as F
+
+    x, y = torch.rand(4), torch.randint(0, 2, (4,))
+    with pytest.raises(ValueError, match="The `input` and `target` should have the same shape, "):
+        F.binary_auroc(torch.rand(4), torch.rand(3))
+    with pytest.raises(ValueError, match="`num_tasks = 1`, `input` is expected to be one-dimensional tensor,"):
+        F.binary_auroc(torch.rand(4, 5), torch.rand(4, 5))
+    with pytest.raises(ValueError, match="The `weight` and `target` should have the same shape, "):
+        F.binary_auroc(x, y, weight=torch.rand(3))
+    with pytest.raises(ValueError, match="`average` was not in the allowed value of"):
+        F.multiclass_auroc(torch.rand(4, 3), torch.randint(0, 3, (4,)), num_classes=3, average="weighted")
+    with pytest.raises(ValueError, match="`num_classes` has to be at least 2."):
+        F.multiclass_auroc(torch.rand(4, 1), torch.zeros(4, dtype=torch.long), num_classes=1)
+    with pytest.raises(ValueError, match="input should have shape of \\(num_sample, num_classes\\)"):
+        F.multiclass_auprc(torch.rand(4, 2), torch.zeros(4, dtype=torch.long), num_classes=3)
+    with pytest.raises(ValueError, match="The `threshold` should be a sorted tensor."):
+        F.binary_binned_auroc(x, y, threshold=torch.tensor([0.1, 0.2, 0.5, 0.7, 0.6]))
+    with pytest.raises(ValueError, match="The values in `threshold` should be in the range of \\[0, 1\\]."):
+        F.binary_binned_auroc(x, y, threshold=torch.tensor([-0.1, 0.2, 0.5, 0.7]))
+    with pytest.raises(ValueError, match="First value in `threshold` should be 0."):
+        F.binary_binned_auprc(x, y, threshold=torch.tensor([0.1, 0.2, 1.0]))
+    with pytest.raises(ValueError, match="Last value in `threshold` should be 1."):
+        F.binary_binned_auprc(x, y, threshold=torch.tensor([0.0, 0.2, 0.9]))
+    with pytest.raises(ValueError, match="Unknown memory approach: expected 'vectorized' or 'memory'"):
+        F.multiclass_binned_auprc(torch.rand(4, 3), torch.randint(0, 3, (4,)), optimization="cpu")
+    with pytest.raises(ValueError, match="Must be at least two classes for confusion matrix"):
+        F.multiclass_confusion_matrix(y, y, 1)
+    with pytest.raises(ValueError, match="normalize must be one of 'all', 'pred', 'true', or 'none'."):
+        F.multiclass_confusion_matrix(y, y, 2, normalize="rows")
+    with pytest.raises(ValueError, match="num_classes: 3 must be strictly greater than max class predicted: 4."):
+        F.multiclass_confusion_matrix(T([1, 4, 0]), T([0, 1, 2]), 3)
+    with pytest.raises(ValueError, match="num_classes: 3 must be strictly greater than max target: 5."):
+        F.multiclass_confusion_matrix(T([1, 2, 0]), T([0, 5, 2]), 3)
+    with pytest.raises(ValueError, match="num_classes should be a positive number when average=macro"):
+        F.multiclass_accuracy(y, y, average="macro")
+    with pytest.raises(TypeError, match="Expected `k` to be an integer"):
+        F.multiclass_accuracy(y, y, k=1.5)
+    with pytest.raises(ValueError, match="input should be a one-dimensional tensor for binary f1 score"):
+        F.binary_f1_score(torch.rand(2, 2), torch.rand(2, 2))
+
+
+# ------------------------------------------------------------------------------ classes
+def _split(a, k):
+    return np.array_split(a, k, axis=-1 if a.ndim == 1 or a.shape[0] < a.shape[-1] else 0)
+
+
+def check_lifecycle(make, feed, expect_fn, state_names):
+    """update in 4 batches == one shot; 2-way merge == one shot; merge leaves its arguments alone;
+    pickle / deepcopy / hash / state_dict round trips; reset (reference tester :148-290)."""
+    m = make()
+    assert set(m._state_name_to_default) == state_names
+    pickle.loads(pickle.dumps(m))
+    hash(m)
+    batches = feed()
+    for b in batches:
+        m.update(*b)
+    r1 = m.compute()
+    r2 = m.compute()  # idempotent
+    expect_fn(r1)
+    expect_fn(r2)
+    a, b = make(), make()
+    for i, bt in enumerate(batches):
+        (a if i % 2 == 0 else b).update(*bt)
+    b_state = copy.deepcopy(b.state_dict())
+    a.merge_state([b])
+    expect_fn(a.compute())
+    for k, v in b.state_dict().items():  # untouched
+        if isinstance(v, torch.Tensor):
+            assert torch.equal(v, b_state[k])
+        else:
+            assert all(torch.equal(x, y) for x, y in zip(v, b_state[k]))
+    a.update(*batches[0])  # still usable after a merge
+    c = make()
+    c.load_state_dict(m.state_dict())
+    expect_fn(c.compute())
+    expect_fn(pickle.loads(pickle.dumps(m)).compute())
+    m.reset()
+    for name, default in m._state_name_to_default.items():
+        v = getattr(m, name)
+        assert (v == default).all() if isinstance(v, torch.Tensor) else v == []
+    empty = make()
+    empty.merge_state([make()])  # merging empties is fine
+
+
+def test_class_binary_auroc(backend, golden):
+    from torcheval_b200.metrics import BinaryAUROC
+
+    c = golden.case("binary/ties64")
+    xs, ys = _split(c["x"], 4), _split(c["y"], 4)
+    check_lifecycle(
+        BinaryAUROC, lambda: [(T(x), T(y)) for x, y in zip(xs, ys)],
+        lambda r: (close(r, c["auroc_f64"]), r.dtype == torch.float64), {"inputs", "targets", "weights"},
+    )
+    m = BinaryAUROC()
+    m.update(T(c["x"]), T(c["y"]))
+    assert m.weights[0].numel() == 0  # no 8 B/sample of ones for unweighted updates
+    w = golden.case("binary_weighted/w")
+    m = BinaryAUROC()
+    half = w["x"].size // 2
+    m.update(T(w["x"][:half]), T(w["y"][:half]), T(w["w"][:half]))
+    m.update(T(w["x"][half:]), T(w["y"][half:]), T(w["w"][half:]))
+    close(m.compute(), w["auroc"])
+    m2 = BinaryAUROC()  # mixing weighted and unweighted updates
+    m2.update(T(w["x"][:half]), T(w["y"][:half]), T(w["w"][:half]))
+    m2.update(T(w["x"][half:]), T(w["y"][half:]))
+    ww = w["w"].copy()
+    ww[half:] = 1.0
+    import oracle
+
+    close(m2.compute(), oracle.binary_auroc(w["x"], w["y"], ww)[0])
+    m2._prepare_for_merge_state()
+    close(m2.compute(), oracle.binary_auroc(w["x"], w["y"], ww)[0])
+    t3 = golden.case("binary_multitask/t3")
+    m = BinaryAUROC(num_tasks=3)
+    m.update(T(t3["x"][:, :500]), T(t3["y"][:, :500])).update(T(t3["x"][:, 500:]), T(t3["y"][:, 500:]))
+    close(m.compute(), t3["auroc"])
+    with pytest.raises(ValueError, match="`num_tasks` value should be greater than or equal to 1"):
+        BinaryAUROC(num_tasks=0)
+    with pytest.raises(ValueError, match="`use_fbgemm` is enabled but `fbgemm_gpu` is not found"):
+        BinaryAUROC(use_fbgemm=True)
+    with pytest.raises(Exception):
+        BinaryAUROC().compute()  # like the reference: cat of an empty list
+
+
+def test_class_exact_others(backend, golden):
+    from torcheval_b200.metrics import BinaryAUPRC, MulticlassAUPRC, MulticlassAUROC, MultilabelAUPRC
+
+    c = golden.case("binary/uniform")
+    check_lifecycle(
+        BinaryAUPRC, lambda: [(T(x), T(y)) for x, y in zip(_split(c["x"], 4), _split(c["y"], 4))],
+        lambda r: close(r, c["auprc"], 1e-4), {"inputs", "targets"},
+    )
+    mc = golden.case("multiclass/c5")
+    rows = np.array_split(np.arange(mc["x"].shape[0]), 4)
+    feed = lambda: [(T(mc["x"][r]), T(mc["y"][r])) for r in rows]  # noqa: E731
+    check_lifecycle(lambda: MulticlassAUROC(num_classes=5, average=None), feed, lambda r: close(r, mc["auroc"], 1e-4), {"inputs", "targets"})
+    check_lifecycle(lambda: MulticlassAUPRC(num_classes=5), feed, lambda r: close(r, mc["auprc_macro"], 1e-4), {"inputs", "targets"})
+    ml = golden.case("multilabel/c5")
+    check_lifecycle(
+        lambda: MultilabelAUPRC(num_labels=5, average=None), lambda: [(T(ml["x"][r]), T(ml["y"][r])) for r in rows],
+        lambda r: close(r, ml["auprc"], 1e-4), {"inputs", "targets"},
+    )
+
+
+def test_class_binned(backend, golden):
+    from torcheval_b200.metrics import (
+        BinaryBinnedAUPRC, BinaryBinnedAUROC, BinaryBinnedPrecisionRecallCurve, MulticlassBinnedAUPRC,
+        MulticlassBinnedPrecisionRecallCurve, MultilabelBinnedAUPRC,
+    )
+
+    c = golden.case("binned/lin200")
+    feed = lambda: [(T(x), T(y)) for x, y in zip(_split(c["x"], 4), _split(c["y"], 4))]  # noqa: E731
+    check_lifecycle(lambda: BinaryBinnedAUROC(threshold=200), feed, lambda r: close(r[0], c["auroc"]), {"num_tp", "num_fp"})
+    check_lifecycle(lambda: BinaryBinnedAUPRC(threshold=200), feed, lambda r: close(r[0], c["auprc"], 1e-4), {"num_tp", "num_fp", "num_fn"})
+
+    def pr_ok(r):
+        np.testing.assert_array_equal(r[0].shape, (201,))
+        tp, fp = c["tp"].astype(np.float64), c["fp"].astype(np.float64)
+        want = np.where(tp + fp > 0, tp / np.maximum(tp + fp, 1), 1.0)
+        close(r[0][:-1], want, 1e-6)
+
+    check_lifecycle(lambda: BinaryBinnedPrecisionRecallCurve(threshold=200), feed, pr_ok, {"num_tp", "num_fp", "num_fn"})
+    m = BinaryBinnedAUROC(threshold=200)
+    assert m.num_tp.dtype == torch.int64 and m.num_tp.shape == (1, 200)
+    t2 = golden.case("binned_multitask/t2")
+    m = BinaryBinnedAUROC(num_tasks=2, threshold=50)
+    m.update(T(t2["x"][:, :300]), T(t2["y"][:, :300])).update(T(t2["x"][:, 300:]), T(t2["y"][:, 300:]))
+    close(m.compute()[0], t2["auroc"])
+    mc = golden.case("binned_multiclass/c6")
+    rows = np.array_split(np.arange(300), 3)
+    feed = lambda: [(T(mc["x"][r]), T(mc["y"][r])) for r in rows]  # noqa: E731
+    check_lifecycle(
+        lambda: MulticlassBinnedAUPRC(num_classes=6, threshold=T(mc["thr"]), average=None), feed,
+        lambda r: close(r, mc["auprc"], 1e-4), {"num_tp", "num_fp", "num_fn"},
+    )
+    m = MulticlassBinnedPrecisionRecallCurve(num_classes=6, threshold=33)
+    for b in feed():
+        m.update(*b)
+    np.testing.assert_array_equal(m.num_tp.numpy(), mc["tp"])
+    ml = golden.case("binned_multilabel/l6")
+    check_lifecycle(
+        lambda: MultilabelBinnedAUPRC(num_labels=6, threshold=T(ml["thr"]), average=None),
+        lambda: [(T(ml["x"][r]), T(ml["y"][r])) for r in rows], lambda r: close(r, ml["auprc"], 1e-4),
+        {"num_tp", "num_fp", "num_fn"},
+    )
+
+
+def test_class_counting(backend, golden):
+    from torcheval_b200.metrics import (
+        BinaryAccuracy, BinaryConfusionMatrix, BinaryF1Score, MulticlassAccuracy, MulticlassConfusionMatrix, MulticlassF1Score,
+    )
+
+    c = golden.case("cm/c10")
+    feed = lambda: [(T(p), T(t)) for p, t in zip(_split(c["pred"], 4), _split(c["target"], 4))]  # noqa: E731
+
+    def cm_ok(r):
+        assert r.dtype == torch.float32  # class API returns float32 like the reference
+        np.testing.assert_array_equal(r.numpy(), c["cm"].astype(np.float32))
+
+    check_lifecycle(lambda: MulticlassConfusionMatrix(10), feed, cm_ok, {"confusion_matrix"})
+    m = MulticlassConfusionMatrix(10)
+    for b in feed():
+        m.update(*b)
+    close(m.normalized("true").sum(dim=1), np.ones(10))
+    before = m.confusion_matrix.clone()
+    with pytest.raises(ValueError, match="too large for the number of classes"):
+        m.update(T([3, 11]), T([1, 2]))
+    assert torch.equal(m.confusion_matrix, before)  # a rejected update leaves the state alone
+    b = golden.case("cm_binary/t05")
+    mb = BinaryConfusionMatrix()
+    mb.update(T(b["x"]), T(b["target"]))
+    np.testing.assert_array_equal(mb.compute().numpy(), b["cm"].astype(np.float32))
+    a = golden.case("acc_f1/c5")
+    feed = lambda: [(T(p), T(t)) for p, t in zip(_split(a["pred"], 3), _split(a["target"], 3))]  # noqa: E731
+    check_lifecycle(MulticlassAccuracy, feed, lambda r: close(r, a["acc_micro"]), {"num_correct", "num_total"})
+    check_lifecycle(lambda: MulticlassAccuracy(average="macro", num_classes=5), feed, lambda r: close(r, a["acc_macro"]), {"num_correct", "num_total"})
+    check_lifecycle(lambda: MulticlassF1Score(num_classes=5, average="weighted"), feed, lambda r: close(r, a["f1_weighted"]), {"num_tp", "num_label", "num_prediction"})
+    check_lifecycle(MulticlassF1Score, feed, lambda r: close(r, a["f1_micro"]), {"num_tp", "num_label", "num_prediction"})
+    ba = BinaryAccuracy().update(T([0.1, 0.9, 0.6, 0.2]), T([0, 1, 0, 0]))
+    close(ba.compute(), 0.75)
+    bf = BinaryF1Score().update(T([0.1, 0.9, 0.6, 0.2]), T([0, 1, 0, 0]))
+    close(bf.compute(), 2 / 3)
+    assert torch.isnan(MulticlassAccuracy().compute())
+
+
+def test_metric_base_and_toolkit_single_process(backend, golden):
+    from torcheval_b200.metrics import BinaryAUROC, Metric, MulticlassConfusionMatrix
+    from torcheval_b200.metrics import toolkit
+
+    with pytest.raises(TypeError, match="The value of state variable must be"):
+        MulticlassConfusionMatrix(3)._add_state("bad", "a string")
+    m = MulticlassConfusionMatrix(3)
+    with pytest.raises(RuntimeError, match="Error\\(s\\) in loading state_dict for MulticlassConfusionMatrix"):
+        m.load_state_dict({"nope": torch.zeros(1)})
+    m.load_state_dict({"nope": torch.zeros(1)}, strict=False)
+    m.load_state_dict({"confusion_matrix": torch.ones(3, 3)})  # a reference float32 checkpoint loads
+    m.update(T([0, 1]), T([0, 1]))
+    assert m.confusion_matrix.dtype == torch.float32 and m.confusion_matrix[0, 0] == 2
+    assert m.to("cpu").device == torch.device("cpu")
+    assert issubclass(BinaryAUROC, Metric)
+    c = golden.case("binary/uniform")
+    a = BinaryAUROC().update(T(c["x"]), T(c["y"]))
+    close(toolkit.sync_and_compute(a), c["auroc_f64"])  # world size 1: plain compute
+    assert toolkit.get_synced_metric(a) is a
+    out = toolkit.sync_and_compute_collection({"auroc": a, "cm": m})
+    assert set(out) == {"auroc", "cm"}
+    cl = toolkit.clone_metric(a)
+    assert cl is not a and torch.equal(cl.inputs[0], a.inputs[0])
+    toolkit.reset_metrics([a])
+    assert a.inputs == []
+    d = toolkit.classwise_converter(torch.tensor([1.0, 2.0]), "acc", ["a", "b"])
+    assert set(d) == {"acc_a", "acc_b"}
+    with pytest.raises(ValueError, match="Number of labels 1 must be equal to the number of classes 2!"):
+        toolkit.classwise_converter(torch.tensor([1.0, 2.0]), "acc", ["a"])

@@ -430,3 +430,31 @@ def test_functional_binary_auroc_dispatch(ops, golden):
     got = binary_auroc(torch.as_tensor(c["x"]), torch.as_tensor(c["y"]), num_tasks=3)
     assert got.shape == (3,)
     close(got.numpy(), c["auroc"], RTOL64)
+
+
+# =============================================================================== distributed pieces
+def test_rank_pack_partition_from_keys(ops):
+    import cpu_backend
+
+    rs = np.random.default_rng(21)
+    for n in (1, 4097, 300001):
+        x = rs.random(n, dtype=np.float32)
+        x[::17] = 0.5
+        if n > 10:
+            x[3], x[4] = -0.0, 0.0
+        y = rs.integers(0, 2, n)
+        keys, info = ops.rank_pack(dev(x), dev(y))
+        wk, winfo = cpu_backend.rank_pack(torch.from_numpy(x), torch.from_numpy(y))
+        np.testing.assert_array_equal(keys.cpu().numpy(), wk.numpy())
+        assert info.tolist() == winfo.tolist()
+        for sp in ([], [int(0.5 * 2**31) & ~1], sorted(int(v) & ~1 for v in rs.integers(0, 2**31, 7)), [10, 10, 2**32 - 2]):
+            part, counts = ops.partition_u32(keys, sp)
+            wp, wc = cpu_backend.partition_u32(wk, sp)
+            assert counts.tolist() == wc.tolist(), (n, sp)
+            np.testing.assert_array_equal(part.cpu().numpy(), wp.numpy())  # stable
+        out = ops.binary_auroc_from_keys(keys).cpu().numpy()
+        want = cpu_backend.binary_auroc_from_keys(wk).numpy()
+        close(out[0], want[0], 1e-12)
+        assert list(out[1:4]) == list(want[1:4]) and list(out[5:8]) == list(want[5:8])
+    _, info = ops.rank_pack(dev(np.array([0.5, -1.0], dtype=np.float32)), dev(np.array([0, 1])))
+    assert info.tolist() == [1, 2]

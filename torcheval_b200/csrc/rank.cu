@@ -102,6 +102,9 @@ __global__ void __launch_bounds__(kIngestBlock, 1)
 #pragma unroll
         for (int j = 0; j < 4; ++j) k[j] = j < (int)cnt ? raw_keys[i0 + j] : 0u;
       }
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (j < (int)cnt) npos += k[j] & 1u;  // packed keys carry the label in bit 0
     } else {
       float x[4];
       if (cnt == 4 && vec_ok) {
@@ -176,6 +179,10 @@ __global__ void __launch_bounds__(kIngestBlock, 1)
 #pragma unroll
     for (int r = 0; r < kWarp; ++r) s += sh[tid * kWarp + ((r + tid) & 31)];
     if (s) atomicAdd(ghist + tid, s);
+  }
+  if (MODE == kRawKeys) {
+    npos = warp_sum(npos);
+    if (lane == 0 && npos) atomicAdd(&scal->positives, (unsigned long long)npos);
   }
   if (MODE == kPacked) {
     npos = warp_sum(npos);
@@ -313,9 +320,14 @@ __global__ void __launch_bounds__(kFinBlock)
     const uint32_t cnt = i0 < n ? min((uint32_t)kFinIpt, n - i0) : 0u;
 
     // phase 1: thread aggregate + group-start mask
-    // phase 1: thread aggregate + group-start mask
+    // one local pass: thread aggregate, group-start mask and (MODE 0) the local sums of the
+    // AUROC integrand, all relative to the start of this thread's 16 keys and in 32-bit
     FState mine = f_identity();
     uint32_t starts = 0;
+    uint32_t n_pre = 0, n_post = 0;  // positives before / after the first group start seen here
+    uint32_t s_lc = 0;               // sum over positives of (#negatives before it, local)
+    uint32_t s_lgs = 0;              // sum over "post" positives of (#negatives before its group, local)
+    uint32_t lgs = 0;
 #pragma unroll
     for (int j = 0; j < kFinIpt; ++j) {
       if (j < (int)cnt) {
@@ -327,8 +339,21 @@ __global__ void __launch_bounds__(kFinBlock)
           mine.F = 1;
           mine.M = mine.S;
           mine.Mp = i0 + j;
+          lgs = mine.S;
         }
-        mine.S += (k[j] & 1u) ^ 1u;
+        if (k[j] & 1u) {
+          if (MODE == 0) {
+            s_lc += mine.S;
+            if (mine.F) {
+              ++n_post;
+              s_lgs += lgs;
+            } else {
+              ++n_pre;
+            }
+          }
+        } else {
+          ++mine.S;
+        }
       }
     }
 
@@ -353,32 +378,36 @@ __global__ void __launch_bounds__(kFinBlock)
     __syncthreads();  // s_warp is rewritten by the next tile
     const FState g = f_combine(carry, f_combine(wprefix, excl));
 
-    // phase 2: integrate with chunk-relative (MODE 0) or global (MODE 1) counts
-    uint32_t c = g.S, gs = g.M, gp = g.Mp, have = g.F;
+    if (MODE == 0) {
+      // a positive contributes (#neg before it) + (#neg before its tie group): with g = state
+      // of everything before this thread inside the chunk,
+      //   "post" positives: (g.S + lc) + (g.S + lgs)
+      //   "pre"  positives: (g.S + lc) + g.M      (group known inside the chunk: g.F)
+      //                     (g.S + lc) + [E.M]    (group older than the chunk: counted in lead)
+      const uint32_t npos = n_pre + n_post;
+      accP += npos;
+      accA += (unsigned long long)g.S * (npos + n_post) + s_lc + s_lgs;
+      if (g.F)
+        accA += (unsigned long long)g.M * n_pre;
+      else
+        accLead += n_pre;
+    } else {
+      // AUPRC: needs exact global counts per positive
+      uint32_t c = g.S, gs = g.M, gp = g.Mp;
 #pragma unroll
-    for (int j = 0; j < kFinIpt; ++j) {
-      if (j < (int)cnt) {
-        if (starts & (1u << j)) {
-          gs = c;
-          gp = i0 + j;
-          have = 1;
-        }
-        if (k[j] & 1u) {
-          if (MODE == 0) {
-            ++accP;
-            if (have) {
-              accA += (unsigned long long)c + gs;
-            } else {
-              accA += c;
-              ++accLead;
-            }
-          } else {
+      for (int j = 0; j < kFinIpt; ++j) {
+        if (j < (int)cnt) {
+          if (starts & (1u << j)) {
+            gs = c;
+            gp = i0 + j;
+          }
+          if (k[j] & 1u) {
             // precision at this tie group's threshold: TP / (TP + FP), counts of score >= s
             const double tp = ptot - (double)(gp - gs);
             accD += tp / (double)(n - gp);
+          } else {
+            ++c;
           }
-        } else {
-          ++c;
         }
       }
     }
@@ -454,6 +483,9 @@ __global__ void __launch_bounds__(kMaxChunks)
     out[2] = N;
     out[3] = (double)tu;
     out[4] = (double)scal->flags;
+    out[5] = (double)(tu >> 32);           // 2U exactly, as two 32-bit halves
+    out[6] = (double)(tu & 0xffffffffull);
+    out[7] = (double)n;
   }
 }
 
@@ -555,7 +587,7 @@ RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final)
   p.off_hist = take(4 * kRadix * 4);
   p.off_ticket = take(8 * 4);
   p.off_scal = take(sizeof(RankScalars));
-  p.off_lookback = take((size_t)4 * p.sort_tiles * kRadix * 4);
+  p.off_lookback = take((size_t)4 * 2 * p.sort_tiles * kRadix * 4);  // counts + prefixes, 4 passes
   p.off_agg = take(with_final ? (size_t)kMaxChunks * sizeof(ChunkRec) : 0);
   p.off_inc = take(with_final ? (size_t)kMaxChunks * sizeof(FState) : 0);
   p.zero_bytes = o - p.off_zero;
@@ -584,15 +616,15 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   static const int window = [] {
     const char* e = getenv("TE_B200_LB_WINDOW");
     const int w = e ? atoi(e) : kLbWindowDefault;
-    return (w == 8 || w == 16 || w == 32) ? w : kLbWindowDefault;
+    return (w == 0 || w == 8 || w == 16) ? w : kLbWindowDefault;
   }();
   const int block = p.sort_block;
   const size_t smem = block == 256 ? onesweep_smem_bytes<uint32_t, 256>() : onesweep_smem_bytes<uint32_t, 512>();
-  using PassFn = void (*)(const uint32_t*, uint32_t*, const uint32_t*, uint32_t*, uint32_t, int,
-                          const uint32_t*, uint32_t*, uint32_t*);
+  using PassFn = void (*)(const uint32_t*, uint32_t*, const uint32_t*, uint32_t*, uint32_t,
+                          const RadixDigit, const uint32_t*, uint32_t*, uint32_t*, uint32_t*);
   PassFn fn = nullptr;
-#define TE_PICK(HV, W, B) onesweep_pass_kernel<uint32_t, HV, W, B>
-#define TE_PICK_W(HV, B) (window == 8 ? TE_PICK(HV, 8, B) : (window == 16 ? TE_PICK(HV, 16, B) : TE_PICK(HV, 32, B)))
+#define TE_PICK(HV, W, B) onesweep_pass_kernel<uint32_t, HV, W, B, RadixDigit>
+#define TE_PICK_W(HV, B) (window == 8 ? TE_PICK(HV, 8, B) : (window == 16 ? TE_PICK(HV, 16, B) : TE_PICK(HV, 0, B)))
   if (v_in0)
     fn = block == 256 ? TE_PICK_W(true, 256) : TE_PICK_W(true, 512);
   else
@@ -605,10 +637,11 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   for (int pass = 0; pass < 4; ++pass) {
     uint32_t* kout = (pass & 1) ? k_y : k_x;
     uint32_t* vout = (pass & 1) ? v_y : v_x;
-    uint32_t* lbp = lb + (size_t)pass * p.sort_tiles * kRadix;
+    uint32_t* lbp = lb + (size_t)pass * 2 * p.sort_tiles * kRadix;
     TE_PROF(v_in0 ? "onesweep_pass_pairs" : "onesweep_pass_keys", st);
-    fn<<<p.sort_tiles, block, smem, st>>>(kin, kout, vin, vout, p.n, 8 * pass,
-                                               hist + pass * kRadix, lbp, ticket + pass);
+    fn<<<p.sort_tiles + (window == 0 ? 1 : 0), block, smem, st>>>(
+        kin, kout, vin, vout, p.n, RadixDigit{8 * pass}, hist + pass * kRadix, lbp,
+        lbp + (size_t)p.sort_tiles * kRadix, ticket + pass);
     TE_LAUNCH_CHECK();
     kin = kout;
     vin = vout;
@@ -656,23 +689,10 @@ int launch_ingest_dtype(const float* score, const void* target, int32_t dt, cons
   }
 }
 
-int binary_rank_packed(const float* score, const void* target, int32_t dt, int64_t n, int mode,
-                       double* out, void* scratch, size_t scratch_bytes, cudaStream_t st) {
-  if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
-  const RankPlan p = make_plan(n, false, true, true);
-  if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
-  int sms = 0;
-  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
-  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
-  uint32_t* ka = at<uint32_t>(scratch, p.off_keys_a);
-  uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
-  if (n > 0) {
-    int rc = launch_ingest_dtype<kPacked>(score, target, dt, p, ka, nullptr, scratch, sms, st);
-    if (rc) return rc;
-    // a -> b -> a -> b -> a : sorted keys end in `ka`
-    rc = run_passes(p, scratch, ka, kb, ka, nullptr, nullptr, nullptr, st);
-    if (rc) return rc;
-  }
+// fused scan / integrate over the sorted packed keys + final division (both modes)
+int finish_packed(const RankPlan& p, const uint32_t* ka, int mode, double* out, void* scratch, int sms,
+                  cudaStream_t st) {
+  const int64_t n = p.n;
   ChunkRec* rec = at<ChunkRec>(scratch, p.off_agg);
   FState* excl = at<FState>(scratch, p.off_inc);
   unsigned long long* partial = at<unsigned long long>(scratch, p.off_partial);
@@ -704,6 +724,26 @@ int binary_rank_packed(const float* score, const void* target, int32_t dt, int64
   }
   TE_LAUNCH_CHECK();
   return TE_OK;
+}
+
+int binary_rank_packed(const float* score, const void* target, int32_t dt, int64_t n, int mode,
+                       double* out, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+  if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  const RankPlan p = make_plan(n, false, true, true);
+  if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
+  uint32_t* ka = at<uint32_t>(scratch, p.off_keys_a);
+  uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
+  if (n > 0) {
+    int rc = launch_ingest_dtype<kPacked>(score, target, dt, p, ka, nullptr, scratch, sms, st);
+    if (rc) return rc;
+    // a -> b -> a -> b -> a : sorted keys end in `ka`
+    rc = run_passes(p, scratch, ka, kb, ka, nullptr, nullptr, nullptr, st);
+    if (rc) return rc;
+  }
+  return finish_packed(p, ka, mode, out, scratch, sms, st);
 }
 
 
@@ -1071,6 +1111,52 @@ int binary_rank_general(const float* score, const void* target, int32_t dt, cons
   }
 }
 
+
+// ------------------------------------------------------------------------------------------
+// pieces of the distributed sample sort (torcheval_b200/distributed.py)
+// ------------------------------------------------------------------------------------------
+__global__ void rank_info_kernel(const RankScalars* __restrict__ scal, long long* info) {
+  if (threadIdx.x == 0) {
+    info[0] = (long long)scal->positives;
+    info[1] = (long long)scal->flags;
+  }
+}
+
+// bucket histogram for the splitter partition: hist[b] = #{keys with bucket b}, b < 16
+__global__ void __launch_bounds__(1024)
+    bucket_hist_kernel(const uint32_t* __restrict__ keys, uint32_t n, const SplitterDigit dop,
+                       uint32_t* hist) {
+  __shared__ uint32_t sh[16 * kWarp];
+  const unsigned tid = threadIdx.x, lane = tid & 31;
+  if (tid < 16 * kWarp) sh[tid] = 0;
+  __syncthreads();
+  const uint32_t ngroups = (n + 3) / 4;
+  for (uint32_t g = blockIdx.x * blockDim.x + tid; g < ngroups; g += gridDim.x * blockDim.x) {
+    const uint32_t i0 = g * 4, cnt = min(4u, n - i0);
+    uint32_t k[4];
+    if (cnt == 4) {
+      const int4 a = ld_stream_v4(keys + i0);
+      k[0] = a.x, k[1] = a.y, k[2] = a.z, k[3] = a.w;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) k[j] = j < (int)cnt ? keys[i0 + j] : 0u;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (j < (int)cnt) atomicAdd(sh + dop(k[j]) * kWarp + lane, 1u);
+  }
+  __syncthreads();
+  if (tid < 16) {
+    uint32_t s = 0;
+    for (int r = 0; r < kWarp; ++r) s += sh[tid * kWarp + r];
+    if (s) atomicAdd(hist + tid, s);
+  }
+}
+
+__global__ void copy_counts_kernel(const uint32_t* __restrict__ hist, long long* counts, int nb) {
+  if ((int)threadIdx.x < nb) counts[threadIdx.x] = (long long)hist[threadIdx.x];
+}
+
 }  // namespace
 }  // namespace te
 
@@ -1142,4 +1228,109 @@ extern "C" int te_binary_auprc_general(const float* score, const void* target, i
   if (!out || (n > 0 && (!score || !target))) return TE_ERR_INVALID_ARGUMENT;
   return binary_rank_general(score, target, target_dtype, nullptr, n, 1, out, scratch, scratch_bytes,
                              (cudaStream_t)stream);
+}
+
+extern "C" size_t te_rank_pack_scratch_bytes(int64_t n) {
+  if (n < 0 || n > 0x7fffffffLL) return 0;
+  return make_plan(n, false, false, false).total;
+}
+
+extern "C" int te_rank_pack(const float* score, const void* target, int32_t target_dtype, int64_t n,
+                            uint32_t* keys_out, int64_t* info, void* scratch, size_t scratch_bytes,
+                            void* stream) {
+  if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  if (!info || (n > 0 && (!score || !target || !keys_out))) return TE_ERR_INVALID_ARGUMENT;
+  if (((uintptr_t)keys_out & 15) != 0) return TE_ERR_INVALID_ARGUMENT;
+  const RankPlan p = make_plan(n, false, false, false);
+  if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
+  if (n > 0) {
+    const int rc = launch_ingest_dtype<kPacked>(score, target, target_dtype, p, keys_out, nullptr, scratch, sms, st);
+    if (rc) return rc;
+  }
+  rank_info_kernel<<<1, 32, 0, st>>>(at<RankScalars>(scratch, p.off_scal), (long long*)info);
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+extern "C" size_t te_partition_u32_scratch_bytes(int64_t n) { return te_rank_pack_scratch_bytes(n); }
+
+extern "C" int te_partition_u32(const uint32_t* keys_in, int64_t n, const uint32_t* splitters_host,
+                                int32_t num_splitters, uint32_t* keys_out, int64_t* counts,
+                                void* scratch, size_t scratch_bytes, void* stream) {
+  if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  if (num_splitters < 0 || num_splitters > kMaxSplitters || !counts) return TE_ERR_INVALID_ARGUMENT;
+  if (num_splitters > 0 && !splitters_host) return TE_ERR_INVALID_ARGUMENT;
+  if (n > 0 && (!keys_in || !keys_out)) return TE_ERR_INVALID_ARGUMENT;
+  if (((uintptr_t)keys_in & 15) != 0) return TE_ERR_INVALID_ARGUMENT;
+  SplitterDigit dop{};
+  dop.nsp = num_splitters;
+  for (int i = 0; i < num_splitters; ++i) {
+    if (i > 0 && splitters_host[i] < splitters_host[i - 1]) return TE_ERR_INVALID_ARGUMENT;
+    dop.sp[i] = splitters_host[i];
+  }
+  const RankPlan p = make_plan(n, false, false, false);
+  if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
+  uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
+  if (n > 0) {
+    TE_PROF("bucket_hist", st);
+    const uint32_t ngroups = (p.n + 3) / 4;
+    uint32_t grid = (ngroups + 1023) / 1024;
+    if (grid > (uint32_t)sms * 2) grid = sms * 2;
+    bucket_hist_kernel<<<grid, 1024, 0, st>>>(keys_in, p.n, dop, hist);
+  }
+  TE_LAUNCH_CHECK();
+  copy_counts_kernel<<<1, 32, 0, st>>>(hist, (long long*)counts, num_splitters + 1);
+  TE_LAUNCH_CHECK();
+  if (n == 0) return TE_OK;
+  {
+    TE_PROF("digit_scan", st);
+    digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 1);
+  }
+  TE_LAUNCH_CHECK();
+  TE_PROF("onesweep_partition", st);
+  if (p.sort_block == 256) {
+    auto fn = onesweep_pass_kernel<uint32_t, false, 8, 256, SplitterDigit>;
+    const size_t smem = onesweep_smem_bytes<uint32_t, 256>();
+    TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    fn<<<p.sort_tiles, 256, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist,
+                                        at<uint32_t>(scratch, p.off_lookback), nullptr, at<uint32_t>(scratch, p.off_ticket));
+  } else {
+    auto fn = onesweep_pass_kernel<uint32_t, false, 8, 512, SplitterDigit>;
+    const size_t smem = onesweep_smem_bytes<uint32_t, 512>();
+    TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    fn<<<p.sort_tiles, 512, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist,
+                                        at<uint32_t>(scratch, p.off_lookback), nullptr, at<uint32_t>(scratch, p.off_ticket));
+  }
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+extern "C" int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, double* out, void* scratch,
+                                         size_t scratch_bytes, void* stream) {
+  if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  if (!out || (n > 0 && !keys)) return TE_ERR_INVALID_ARGUMENT;
+  if (((uintptr_t)keys & 15) != 0) return TE_ERR_INVALID_ARGUMENT;
+  const RankPlan p = make_plan(n, false, true, true);
+  if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
+  uint32_t* ka = at<uint32_t>(scratch, p.off_keys_a);
+  uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
+  if (n > 0) {
+    int rc = launch_ingest<kRawKeys, long long>(nullptr, nullptr, keys, p, nullptr, nullptr, scratch, sms, st);
+    if (rc) return rc;
+    rc = run_passes(p, scratch, keys, ka, kb, nullptr, nullptr, nullptr, st);  // sorted keys end in kb
+    if (rc) return rc;
+  }
+  return finish_packed(p, kb, 0, out, scratch, sms, st);
 }

@@ -26,10 +26,27 @@ constexpr int kSortBlockDefault = 512;  // 8192 records per CTA; 256 (4096 recor
 constexpr uint32_t kLbInclusive = 0x80000000u;
 constexpr int kLbWindowDefault = 8;   // predecessors fetched per look-back round trip
 
-template <typename KeyT>
-__device__ __forceinline__ uint32_t digit_of(KeyT k, int shift) {
-  return (uint32_t)(k >> shift) & (kRadix - 1);
-}
+// What a pass sorts by: an 8-bit digit of the key ...
+struct RadixDigit {
+  int shift;
+  template <typename KeyT>
+  __device__ __forceinline__ uint32_t operator()(KeyT k) const {
+    return (uint32_t)(k >> shift) & (kRadix - 1);
+  }
+};
+// ... or the index of the range the key falls in, given up to 15 ascending splitters
+// (bucket = #{splitters <= key}): the partition step of the distributed sample sort.
+constexpr int kMaxSplitters = 15;
+struct SplitterDigit {
+  uint32_t sp[kMaxSplitters];
+  int nsp;
+  __device__ __forceinline__ uint32_t operator()(uint32_t k) const {
+    uint32_t b = 0;
+#pragma unroll
+    for (int i = 0; i < kMaxSplitters; ++i) b += (i < nsp && sp[i] <= k) ? 1u : 0u;
+    return b;
+  }
+};
 
 template <typename KeyT, int kSortBlock>
 constexpr size_t onesweep_smem_bytes() {
@@ -39,12 +56,21 @@ constexpr size_t onesweep_smem_bytes() {
          sizeof(uint32_t) * ((kSortBlock / kWarp) * kRadix + kRadix + kRadix / kWarp + 4);
 }
 
-template <typename KeyT, bool HAS_VAL, int kLbWindow, int kSortBlock>
+// kLbWindow > 0: every tile walks back over its predecessors' counts, kLbWindow at a time.
+// kLbWindow == 0: "scan service" — the CTA that draws ticket 0 does no sorting; its 256 threads
+// (one per digit) stream over the tiles in order, kServiceBatch tiles per L2 round trip, turning
+// published tile counts (lookback[t][d]) into exclusive prefixes (prefix[t][d]).  A tile then
+// reads exactly one word per digit instead of walking a chain whose length grows with the tile
+// rate (tens of millions of tiles per second on B200) times the L2 latency.
+constexpr int kServiceBatch = 32;
+
+template <typename KeyT, bool HAS_VAL, int kLbWindow, int kSortBlock, typename DigitOp>
 __global__ void __launch_bounds__(kSortBlock, 1024 / kSortBlock)
     onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                          const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
-                         uint32_t n, int shift, const uint32_t* __restrict__ digit_base,
-                         uint32_t* lookback, uint32_t* ticket) {
+                         uint32_t n, const DigitOp dop, const uint32_t* __restrict__ digit_base,
+                         uint32_t* lookback, uint32_t* prefix, uint32_t* ticket) {
+  constexpr bool kService = kLbWindow == 0;
   static_assert(kSortBlock >= kRadix && kSortBlock % kRadix == 0, "one thread per digit is needed");
   constexpr int WARPS = kSortBlock / kWarp;
   constexpr int kSortTile = kSortBlock * kSortIpt;
@@ -62,7 +88,29 @@ __global__ void __launch_bounds__(kSortBlock, 1024 / kSortBlock)
     reinterpret_cast<uint32_t*>(s_keys)[i] = 0;  // per-warp peer masks, see the ranking loop
   }
   __syncthreads();
-  const uint32_t tile = s_tile;
+  if (kService && s_tile == 0) {
+    // ---- scan service (ticket 0 is always drawn by a resident CTA, and no tile ever waits
+    //      before publishing its counts, so this loop cannot starve) ----
+    if (tid >= kRadix) return;
+    const uint32_t tiles = (n + kSortTile - 1) / kSortTile;
+    uint32_t run = 0;  // keys with digit `tid` in all tiles before the current one
+    for (uint32_t t0 = 0; t0 < tiles; t0 += kServiceBatch) {
+      uint32_t a[kServiceBatch];
+#pragma unroll
+      for (int j = 0; j < kServiceBatch; ++j)
+        a[j] = (t0 + j < tiles) ? ld_relaxed_u32(lookback + (size_t)(t0 + j) * kRadix + tid) : 1u;
+#pragma unroll
+      for (int j = 0; j < kServiceBatch; ++j) {
+        if (t0 + j < tiles) {
+          while (a[j] == 0) a[j] = ld_relaxed_u32(lookback + (size_t)(t0 + j) * kRadix + tid);
+          st_relaxed_u32(prefix + (size_t)(t0 + j) * kRadix + tid, kLbInclusive | run);
+          run += a[j] - 1u;
+        }
+      }
+    }
+    return;
+  }
+  const uint32_t tile = kService ? s_tile - 1u : s_tile;
   const uint32_t base = tile * (uint32_t)kSortTile;
   const uint32_t valid = min((uint32_t)kSortTile, n - base);
   const uint32_t wbase = warp * (kWarp * kSortIpt);  // tile-relative start of this warp's chunk
@@ -87,7 +135,7 @@ __global__ void __launch_bounds__(kSortBlock, 1024 / kSortBlock)
   uint32_t rk[kSortIpt / 2];  // two 16-bit ranks per register
 #pragma unroll
   for (int i = 0; i < kSortIpt; ++i) {
-    const uint32_t d = digit_of(key[i], shift);
+    const uint32_t d = dop(key[i]);
     atomicOr(wm + d, lane_bit);
     __syncwarp();
     const uint32_t peers = wm[d];
@@ -149,19 +197,20 @@ __global__ void __launch_bounds__(kSortBlock, 1024 / kSortBlock)
   //      at tens of millions of tiles per second while one L2 round trip is ~0.5 us, so a tile
   //      routinely has to add up dozens of not-yet-prefixed predecessors: fetch them kLbWindow at
   //      a time with independent loads instead of one dependent load per predecessor. ----
-  if (tid < kRadix) {
+  if (!kService && tid < kRadix) {
     const uint32_t d = tid;
     uint32_t excl = 0;
     int64_t t = (int64_t)tile - 1;
+    constexpr int W = kLbWindow > 0 ? kLbWindow : 1;
     while (t >= 0) {
-      uint32_t w[kLbWindow];
+      uint32_t w[W];
 #pragma unroll
-      for (int j = 0; j < kLbWindow; ++j)
+      for (int j = 0; j < W; ++j)
         w[j] = (t - j >= 0) ? ld_relaxed_u32(lookback + (size_t)(t - j) * kRadix + d) : kLbInclusive;
       int used = 0;
       bool done = false;
 #pragma unroll
-      for (int j = 0; j < kLbWindow; ++j) {
+      for (int j = 0; j < W; ++j) {
         if (!done && used == j) {
           if (w[j] & kLbInclusive) {
             excl += w[j] & ~kLbInclusive;
@@ -182,7 +231,7 @@ __global__ void __launch_bounds__(kSortBlock, 1024 / kSortBlock)
   // ---- scatter into tile order through shared memory ----
 #pragma unroll
   for (int i = 0; i < kSortIpt; ++i) {
-    const uint32_t d = digit_of(key[i], shift);
+    const uint32_t d = dop(key[i]);
     const uint32_t r = (i & 1) ? (rk[i >> 1] >> 16) : (rk[i >> 1] & 0xffffu);
     const uint32_t p = wh[d] + r;
     s_keys[p] = key[i];
@@ -193,6 +242,15 @@ __global__ void __launch_bounds__(kSortBlock, 1024 / kSortBlock)
         rk[i >> 1] = (rk[i >> 1] & 0xffff0000u) | p;
     }
   }
+  if (kService && tid < kRadix) {
+    // by now the service has usually been past this tile for a while: one load per digit
+    const uint32_t* pp = prefix + (size_t)tile * kRadix + tid;
+    uint32_t w;
+    do {
+      w = ld_relaxed_u32(pp);
+    } while (w == 0);
+    s_goff[tid] = digit_base[tid] + (w & ~kLbInclusive) - my_bin_start;
+  }
   __syncthreads();
 
   uint32_t dpack[kSortIpt / 4];  // digit of tile position tid + k*BLOCK, four per register
@@ -200,7 +258,7 @@ __global__ void __launch_bounds__(kSortBlock, 1024 / kSortBlock)
   for (int k = 0; k < kSortIpt; ++k) {
     const uint32_t p = tid + k * kSortBlock;
     const KeyT kk = s_keys[p];
-    const uint32_t d = digit_of(kk, shift);
+    const uint32_t d = dop(kk);
     if (p < valid) keys_out[s_goff[d] + p] = kk;
     if (HAS_VAL) {
       if ((k & 3) == 0)

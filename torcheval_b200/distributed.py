@@ -1,0 +1,179 @@
+"""Multi-GPU paths (one process per GPU, torch.distributed / NCCL over NVLink).
+
+Exact binary AUROC over rank-sharded scores as a distributed sample sort:
+
+  1. pack      every rank turns (score, label) into 32-bit order-preserving keys      [kernel]
+  2. splitters s regular samples per rank -> all_gather -> W-1 quantile splitters; splitters
+               are score values (label bit cleared), so equal scores go to ONE rank and no tie
+               group ever straddles a rank boundary
+  3. partition one radix-style pass groups the local keys by destination rank         [kernel]
+  4. exchange  all_gather of the W bucket sizes, then one all_to_all_single of the keys
+  5. local     sort + fused scan/integrate of the received range                      [kernels]
+  6. fix-up    all_gather of (P_r, N_r, 2U_r) — three integers per rank:
+               2U = sum_r ( 2U_r + 2 * P_r * sum_{q<r} N_q )   (rank order = score order)
+
+The reference instead pickles every rank's whole sample set to every rank and re-sorts all N
+samples everywhere (torcheval/metrics/toolkit.py:371-391, classification/auroc.py:131-136).
+
+The three kernel-backed steps are looked up through ``_local`` so that the host logic can be
+exercised on CPU/gloo by tests that substitute them.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from . import ops
+
+SAMPLES_PER_RANK = 4096
+
+
+class _LocalKernels:
+    """Kernel-backed local steps (CUDA tensors in, CUDA tensors out)."""
+
+    @staticmethod
+    def pack(score: torch.Tensor, target: torch.Tensor):
+        return ops.rank_pack(score, target)
+
+    @staticmethod
+    def partition(keys: torch.Tensor, splitters):
+        return ops.partition_u32(keys, splitters)
+
+    @staticmethod
+    def auroc_from_keys(keys: torch.Tensor) -> torch.Tensor:
+        return ops.binary_auroc_from_keys(keys)
+
+
+_local = _LocalKernels
+
+
+def _as_u32_list(t: torch.Tensor):
+    return [int(v) & 0xFFFFFFFF for v in t.tolist()]
+
+
+def choose_splitters(samples_sorted, world: int):
+    """W-1 ascending splitters from the sorted pool of sampled keys; label bit cleared so that
+    both labels of one score compare alike."""
+    m = len(samples_sorted)
+    out = []
+    for i in range(1, world):
+        v = samples_sorted[min(m - 1, (i * m) // world)] if m else 0
+        out.append(v & 0xFFFFFFFE)
+    return out
+
+
+def combine_rank_stats(stats):
+    """stats: list over ranks (ascending score ranges) of (P_r, N_r, 2U_r) Python ints.
+    Returns (auroc, P, N, 2U) with exact integer arithmetic."""
+    u2 = 0
+    neg_below = 0
+    P = N = 0
+    for p_r, n_r, u2_r in stats:
+        u2 += u2_r + 2 * p_r * neg_below
+        neg_below += n_r
+        P += p_r
+        N += n_r
+    auroc = 0.5 if P == 0 or N == 0 else u2 / (2 * P * N)
+    return auroc, P, N, u2
+
+
+def sharded_binary_auroc(
+    score: torch.Tensor, target: torch.Tensor, group: Optional[dist.ProcessGroup] = None
+) -> torch.Tensor:
+    """AUROC of the union of all ranks' (score, target) shards; float64[8] on score.device:
+    [auroc, P, N, 2U, flags, n_received_here, 0, 0].  flags != 0 (negative scores / soft labels
+    somewhere) means the packed representation does not apply and [0] is not valid."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    dev = score.device
+    keys, info = _local.pack(score, target)
+
+    # --- splitters from regular samples ------------------------------------------------
+    n = keys.numel()
+    s = SAMPLES_PER_RANK
+    if n > 0:
+        idx = torch.div(torch.arange(s, device=dev, dtype=torch.int64) * n, s, rounding_mode="floor")
+        mine = keys[idx]
+    else:
+        mine = torch.zeros(s, dtype=keys.dtype, device=dev)
+    # header: [n, flags] travels with the samples so that one collective does it all
+    head = torch.stack([torch.tensor(n, device=dev, dtype=torch.int64), info[1]]).to(torch.int32)
+    msg = torch.cat([head, mine])
+    gathered = [torch.empty_like(msg) for _ in range(world)]
+    dist.all_gather(gathered, msg, group=group)
+    pool, flags = [], 0
+    for g in gathered:
+        h = g[:2].tolist()
+        flags |= int(h[1])
+        if h[0] > 0:
+            pool.extend(_as_u32_list(g[2:]))
+    if flags:
+        out = torch.zeros(8, dtype=torch.float64, device=dev)
+        out[4] = float(flags)
+        return out
+    pool.sort()
+    splitters = choose_splitters(pool, world)
+
+    # --- partition + exchange -----------------------------------------------------------
+    part, counts = _local.partition(keys, splitters)
+    all_counts = [torch.empty_like(counts) for _ in range(world)]
+    dist.all_gather(all_counts, counts, group=group)
+    send = [int(c) for c in counts.tolist()]
+    recv = [int(c[rank].item()) for c in all_counts]
+    inbox = torch.empty(sum(recv), dtype=keys.dtype, device=dev)
+    dist.all_to_all_single(inbox, part, recv, send, group=group)
+
+    # --- local sort + integrate, then the 3-integer fix-up ------------------------------
+    loc = _local.auroc_from_keys(inbox)
+    st = torch.stack([loc[1], loc[2], loc[5], loc[6]]).to(torch.int64)
+    all_st = [torch.empty_like(st) for _ in range(world)]
+    dist.all_gather(all_st, st, group=group)
+    stats = []
+    for t in all_st:
+        p_r, n_r, hi, lo = (int(v) for v in t.tolist())
+        stats.append((p_r, n_r, (hi << 32) | lo))
+    auroc, P, N, u2 = combine_rank_stats(stats)
+    return torch.tensor([auroc, P, N, float(u2), 0.0, float(inbox.numel()), 0.0, 0.0], dtype=torch.float64, device=dev)
+
+
+def try_sharded_compute(metric, group: Optional[dist.ProcessGroup] = None):
+    """Fast path of ``toolkit.sync_and_compute``: exact BinaryAUROC (one task, no weights) held
+    as rank-local shards.  Returns the metric value, or None if the metric / its state does not
+    qualify on some rank (every rank then takes the generic path together)."""
+    from .metrics.classification.auroc import BinaryAUROC, _resolve_weights
+    from ._ranking import _as_f32_scores, compute_device, stage
+
+    if not isinstance(metric, BinaryAUROC):
+        return None
+    world = dist.get_world_size(group)
+    ok = (
+        metric.num_tasks == 1
+        and len(metric.inputs) > 0
+        and _resolve_weights(metric.inputs, metric.weights) is None
+        and metric.inputs[0].dim() == 1
+    )
+    from .metrics.toolkit import _comm_device
+
+    cdev = _comm_device(metric.device, group)
+    flag = torch.tensor([1 if ok else 0], dtype=torch.int64, device=cdev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    if int(flag.item()) == 0:
+        return None
+    metric._prepare_for_merge_state()
+    x, t = metric.inputs[0], metric.targets[0]
+    dev = cdev if cdev.type == "cuda" else compute_device(x)
+    try:
+        xs = _as_f32_scores(stage(x, dev))
+        representable = 1
+    except NotImplementedError:
+        xs, representable = None, 0
+    flag = torch.tensor([representable], dtype=torch.int64, device=cdev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    if int(flag.item()) == 0:
+        return None
+    out = sharded_binary_auroc(xs, stage(t, dev), group)
+    if int(out[4].item()) != 0:
+        return None  # same answer on every rank (flags were all-gathered)
+    return out[0].clone().to(metric.device)

@@ -305,3 +305,62 @@ def sort_u32(keys: torch.Tensor, vals: Optional[torch.Tensor] = None) -> Tuple[t
             ),
         )
     return out_k, out_v
+
+
+# ----------------------------------------------------------------------------- distributed pieces
+def rank_pack(score: torch.Tensor, target: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(packed keys as int32 tensor [n], info int64[2] = {#positives, flags})."""
+    lib = N.load()
+    dev = _require_cuda(score, target)
+    assert score.dim() == 1 and score.shape == target.shape and score.dtype == torch.float32
+    score, target = score.contiguous(), target.contiguous()
+    n = score.numel()
+    keys = torch.empty(n, dtype=torch.int32, device=dev)
+    info = torch.zeros(2, dtype=torch.int64, device=dev)
+    scratch = _scratch(lib.te_rank_pack_scratch_bytes(n), dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_rank_pack",
+            lib.te_rank_pack(score.data_ptr(), target.data_ptr(), _DTYPE_CODE[target.dtype], n, keys.data_ptr(),
+                             info.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
+        )
+    return keys, info
+
+
+def partition_u32(keys: torch.Tensor, splitters) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Stable partition of uint32 keys (int32 tensor) by ascending host-side splitters; returns
+    (keys grouped by bucket, int64 bucket counts [len(splitters) + 1])."""
+    import ctypes
+
+    lib = N.load()
+    dev = _require_cuda(keys)
+    keys = keys.contiguous()
+    n = keys.numel()
+    nsp = len(splitters)
+    sp = (ctypes.c_uint32 * max(nsp, 1))(*[int(v) & 0xFFFFFFFF for v in splitters])
+    out = torch.empty_like(keys)
+    counts = torch.zeros(nsp + 1, dtype=torch.int64, device=dev)
+    scratch = _scratch(lib.te_partition_u32_scratch_bytes(n), dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_partition_u32",
+            lib.te_partition_u32(keys.data_ptr(), n, ctypes.cast(sp, ctypes.c_void_p), nsp, out.data_ptr(),
+                                 counts.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
+        )
+    return out, counts
+
+
+def binary_auroc_from_keys(keys: torch.Tensor) -> torch.Tensor:
+    """float64[8] as te_binary_auroc_from_keys: [auroc, P, N, 2U, flags, 2U_hi32, 2U_lo32, n]."""
+    lib = N.load()
+    dev = _require_cuda(keys)
+    keys = keys.contiguous()
+    n = keys.numel()
+    out = torch.empty(8, dtype=torch.float64, device=dev)
+    scratch = _scratch(lib.te_binary_rank_scratch_bytes(n), dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_binary_auroc_from_keys",
+            lib.te_binary_auroc_from_keys(keys.data_ptr(), n, out.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
+        )
+    return out
