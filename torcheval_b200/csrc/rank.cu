@@ -547,9 +547,18 @@ inline int sort_block_from_env() {
   return b;
 }
 
+inline int sort_ipt_from_env() {
+  static const int b = [] {
+    const char* e = getenv("TE_B200_SORT_IPT");
+    const int v = e ? atoi(e) : kSortIptDefault;
+    return (v == 12 || v == 16) ? v : kSortIptDefault;
+  }();
+  return b;
+}
+
 struct RankPlan {
   uint32_t n;
-  int sort_block;
+  int sort_block, sort_ipt;
   uint32_t sort_tiles, fin_tiles;
   size_t off_keys_a, off_keys_b, off_vals_a, off_vals_b;
   size_t off_zero;      // start of the region that must be zero before launch
@@ -567,7 +576,8 @@ RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final)
   RankPlan p{};
   p.n = (uint32_t)n64;
   p.sort_block = sort_block_from_env();
-  const int64_t sort_tile = (int64_t)p.sort_block * kSortIpt;
+  p.sort_ipt = sort_ipt_from_env();
+  const int64_t sort_tile = (int64_t)p.sort_block * p.sort_ipt;
   p.sort_tiles = (uint32_t)((n64 + sort_tile - 1) / sort_tile);
   p.fin_tiles = (uint32_t)((n64 + kFinTile - 1) / kFinTile);
   if (p.sort_tiles == 0) p.sort_tiles = 1;
@@ -631,7 +641,14 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
     fn = block == 256 ? TE_PICK_W(false, 256) : TE_PICK_W(false, 512);
 #undef TE_PICK_W
 #undef TE_PICK
-  TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  size_t smem_used = smem;
+  if (p.sort_ipt == 12) {  // experimental geometry: 512 x 12 keys, 3 CTAs per SM
+    if (block != 512 || window != 8) return TE_ERR_UNSUPPORTED;
+    fn = v_in0 ? onesweep_pass_kernel<uint32_t, true, 8, 512, RadixDigit, 12>
+               : onesweep_pass_kernel<uint32_t, false, 8, 512, RadixDigit, 12>;
+    smem_used = onesweep_smem_bytes<uint32_t, 512, 12>();
+  }
+  TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_used));
   const uint32_t* kin = k_in0;
   const uint32_t* vin = v_in0;
   for (int pass = 0; pass < 4; ++pass) {
@@ -639,7 +656,7 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
     uint32_t* vout = (pass & 1) ? v_y : v_x;
     uint32_t* lbp = lb + (size_t)pass * 2 * p.sort_tiles * kRadix;
     TE_PROF(v_in0 ? "onesweep_pass_pairs" : "onesweep_pass_keys", st);
-    fn<<<p.sort_tiles + (window == 0 ? 1 : 0), block, smem, st>>>(
+    fn<<<p.sort_tiles + (window == 0 ? 1 : 0), block, smem_used, st>>>(
         kin, kout, vin, vout, p.n, RadixDigit{8 * pass}, hist + pass * kRadix, lbp,
         lbp + (size_t)p.sort_tiles * kRadix, ticket + pass);
     TE_LAUNCH_CHECK();

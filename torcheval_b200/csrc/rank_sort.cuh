@@ -15,7 +15,7 @@ namespace te {
 constexpr int kRadixBits = 8;
 constexpr int kRadix = 1 << kRadixBits;
 
-constexpr int kSortIpt = 16;
+constexpr int kSortIptDefault = 16;
 constexpr int kSortBlockDefault = 512;  // 8192 records per CTA; 256 (4096 records) is the alternative
 
 // Look-back word of the sort passes (one per tile and digit), written at most twice:
@@ -48,7 +48,7 @@ struct SplitterDigit {
   }
 };
 
-template <typename KeyT, int kSortBlock>
+template <typename KeyT, int kSortBlock, int kSortIpt = kSortIptDefault>
 constexpr size_t onesweep_smem_bytes() {
   static_assert(sizeof(KeyT) * kSortBlock * kSortIpt >= sizeof(uint32_t) * (kSortBlock / kWarp) * kRadix,
                 "the peer-mask tables alias the key staging area");
@@ -64,8 +64,9 @@ constexpr size_t onesweep_smem_bytes() {
 // rate (tens of millions of tiles per second on B200) times the L2 latency.
 constexpr int kServiceBatch = 32;
 
-template <typename KeyT, bool HAS_VAL, int kLbWindow, int kSortBlock, typename DigitOp>
-__global__ void __launch_bounds__(kSortBlock, 1024 / kSortBlock)
+template <typename KeyT, bool HAS_VAL, int kLbWindow, int kSortBlock, typename DigitOp,
+          int kSortIpt = kSortIptDefault>
+__global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / kSortBlock)
     onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                          const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
                          uint32_t n, const DigitOp dop, const uint32_t* __restrict__ digit_base,
@@ -132,6 +133,7 @@ __global__ void __launch_bounds__(kSortBlock, 1024 / kSortBlock)
   uint32_t* wh = s_whist[warp];
   uint32_t* wm = reinterpret_cast<uint32_t*>(s_keys) + warp * kRadix;  // zeroed above, unused yet
   const uint32_t lane_bit = 1u << lane, lt = lanemask_lt();
+  static_assert(kSortIpt % 4 == 0, "ranks and digits are packed 2 and 4 per register");
   uint32_t rk[kSortIpt / 2];  // two 16-bit ranks per register
 #pragma unroll
   for (int i = 0; i < kSortIpt; ++i) {
