@@ -37,7 +37,8 @@ enum {
   TE_OK = 0,
   TE_ERR_INVALID_ARGUMENT = -1,
   TE_ERR_SCRATCH_TOO_SMALL = -2,
-  TE_ERR_UNSUPPORTED = -3
+  TE_ERR_UNSUPPORTED = -3,
+  TE_ERR_STATIC_SCRATCH_TOO_SMALL = -4 /* size exceeds the built-in scratch of a *_noalloc entry */
 };
 
 /* ABI version of the loaded library (TE_B200_ABI_VERSION at build time). */
@@ -79,6 +80,23 @@ TE_API size_t te_cm_scratch_bytes(int32_t num_classes, int32_t variant);
 TE_API int te_cm_update(const int64_t* pred, const int64_t* target, int64_t n, int32_t num_classes,
                  int64_t* cm, int64_t* range, void* scratch, size_t scratch_bytes,
                  int32_t variant, void* stream);
+
+/* No counterpart in the reference.  te_cm_update for callers that are not allowed to allocate
+ * device memory where they call it and therefore have no scratch buffer to pass (a serving
+ * process whose HBM was fully handed out at start-up, a plugin inside a runtime that owns all
+ * device memory): same inputs, outputs and semantics as te_cm_update(..., TE_CM_GLOBAL32, ...),
+ * but the int32 bins live in a static device array inside the library
+ * (TE_CM_NOALLOC_MAX_CLASSES^2 counters = 4 MiB, resident on every GPU that loads the library
+ * until the process exits).  num_classes above TE_CM_NOALLOC_MAX_CLASSES is refused with
+ * TE_ERR_STATIC_SCRATCH_TOO_SMALL and nothing is enqueued.  The call performs no cudaMalloc /
+ * cudaFree and calls no allocating routine.  All calls on a device share the one array and it
+ * keeps the previous call's counts, so every call clears the part it uses first; calls whose GPU
+ * work overlaps in time race on it — issue them one after the other.  The first call on each
+ * device looks up the array's address (cudaGetSymbolAddress); make that first call before any
+ * stream capture begins on that device. */
+#define TE_CM_NOALLOC_MAX_CLASSES 1024
+TE_API int te_cm_update_noalloc(const int64_t* pred, const int64_t* target, int64_t n,
+                                int32_t num_classes, int64_t* cm, int64_t* range, void* stream);
 
 /* Same with pred = argmax(logits[i, :]) (first maximal index, NaN counts as maximal —
  * torch.argmax, confusion_matrix.py:225-226).  logits is (n, num_classes) float32 with row

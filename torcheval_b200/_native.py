@@ -27,6 +27,7 @@ SIGNATURES = {
     "te_profile_read": (C.c_int, [C.c_char_p, _sz, _vp, _vp, _i32]),
     "te_cm_scratch_bytes": (_sz, [_i32, _i32]),
     "te_cm_update": (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _vp, _sz, _i32, _vp]),
+    "te_cm_update_noalloc": (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _vp]),
     "te_cm_update_logits": (C.c_int, [_vp, _i64, _vp, _i64, _i32, _vp, _vp, _vp]),
     "te_class_counts": (C.c_int, [_vp, _vp, _i64, _vp, _i64, _i32, _vp, _vp, _vp]),
     "te_match_count": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),

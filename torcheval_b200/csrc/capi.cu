@@ -13,6 +13,8 @@ extern "C" const char* te_status_string(int status) {
       return "scratch buffer missing or too small (ask te_*_scratch_bytes)";
     case TE_ERR_UNSUPPORTED:
       return "unsupported configuration";
+    case TE_ERR_STATIC_SCRATCH_TOO_SMALL:
+      return "problem size exceeds the built-in static scratch of this no-allocation entry point";
     default:
       return status > 0 ? cudaGetErrorString((cudaError_t)status) : "unknown status";
   }

@@ -686,3 +686,79 @@ extern "C" int te_match_count(const int64_t* pred, const int64_t* target, int64_
   TE_LAUNCH_CHECK();
   return TE_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// te_cm_update_noalloc — the TE_CM_GLOBAL32 variant with its int32 bins in a static device array
+// ------------------------------------------------------------------------------------------
+// Who needs this: hosts that hand this library raw device pointers but cannot give it a scratch
+// buffer because they are not allowed to allocate at the point of the call — an inference server
+// whose whole HBM budget was carved up at start-up and whose request path is forbidden from
+// touching the allocator (a cudaMalloc there can stall on the device or simply fail), or a plugin
+// called back from someone else's runtime that owns all device memory.  They still pass the
+// inputs and the output matrix; the only thing this entry point supplies itself is the 4-byte
+// bin array that te_cm_update(TE_CM_GLOBAL32) takes as `scratch`.
+//
+// The bins live in a file-scope __device__ array of TE_CM_NOALLOC_MAX_CLASSES^2 counters
+// (4 MiB), present on every GPU that loads the library for as long as the process lives.
+//   * Nothing is allocated or freed here: no cudaMalloc/cudaFree, no allocating library call.
+//   * The array is shared by every call on the device and keeps whatever the last call left in
+//     it, so each call first clears the C*C counters it is going to use (cudaMemsetAsync on the
+//     caller's stream).  Two calls whose GPU work overlaps (different streams, or different
+//     threads) would count into the same bins and both results would be wrong: serialise them.
+//   * `g_cm_static_bins` names a device symbol; in host code that name is not a device address.
+//     The address is fetched once per device with cudaGetSymbolAddress, with that device
+//     current, and cached.  The first call on a device does this set-up — make that first call
+//     before any stream capture is started on the device.
+static __device__ __align__(256) uint32_t g_cm_static_bins[TE_CM_NOALLOC_MAX_CLASSES * TE_CM_NOALLOC_MAX_CLASSES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+uint32_t* g_static_bins_ptr[kMaxDevices] = {};
+}  // namespace
+
+extern "C" int te_cm_update_noalloc(const int64_t* pred, const int64_t* target, int64_t n,
+                                    int32_t num_classes, int64_t* cm, int64_t* range, void* stream) {
+  if (n < 0 || num_classes < 1 || !cm || !range) return TE_ERR_INVALID_ARGUMENT;
+  if (n > 0 && (!pred || !target)) return TE_ERR_INVALID_ARGUMENT;
+  if (num_classes > TE_CM_NOALLOC_MAX_CLASSES) return TE_ERR_STATIC_SCRATCH_TOO_SMALL;
+  int dev = -1;
+  TE_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return TE_ERR_UNSUPPORTED;
+  uint32_t* bins = g_static_bins_ptr[dev];
+  if (!bins) {
+    // once per device, with that device current: turn the symbol into a device address
+    void* p = nullptr;
+    TE_CUDA_TRY(cudaGetSymbolAddress(&p, g_cm_static_bins));
+    if (!p) return TE_ERR_UNSUPPORTED;
+    bins = static_cast<uint32_t*>(p);
+    g_static_bins_ptr[dev] = bins;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  int sms = 0;
+  TE_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  cm_init_range_kernel<<<1, 32, 0, st>>>((long long*)range);
+  TE_LAUNCH_CHECK();
+  if (n == 0) return TE_OK;
+  const uint32_t C = (uint32_t)num_classes, nbins = C * C;
+  const bool aligned = (((uintptr_t)pred | (uintptr_t)target) & 15) == 0;
+  const int64_t slice = (int64_t)1 << 30;  // int32 bins hold at most 2^31 hits per fold
+  for (int64_t off = 0; off < n; off += slice) {
+    const int64_t len = (n - off) < slice ? (n - off) : slice;
+    const int64_t nvec = aligned ? (len + 1) / 2 : len;
+    int64_t want = (nvec + kCmBlock * 4 - 1) / (kCmBlock * 4);
+    const int grid = (int)(want < 1 ? 1 : (want < (int64_t)sms * 8 ? want : (int64_t)sms * 8));
+    // the array still holds the previous call's counts: clear what this call will use
+    TE_CUDA_TRY(cudaMemsetAsync(bins, 0, (size_t)nbins * sizeof(uint32_t), st));
+    if (aligned)
+      cm_global_kernel<2, uint32_t><<<grid, kCmBlock, 0, st>>>(
+          (const long long*)pred + off, (const long long*)target + off, len, C, bins, (long long*)range);
+    else
+      cm_global_kernel<1, uint32_t><<<grid, kCmBlock, 0, st>>>(
+          (const long long*)pred + off, (const long long*)target + off, len, C, bins, (long long*)range);
+    TE_LAUNCH_CHECK();
+    const uint32_t fgrid = (nbins + 255) / 256 < 1184 ? (nbins + 255) / 256 : 1184;
+    cm_fold32_kernel<<<fgrid, 256, 0, st>>>(bins, (unsigned long long*)cm, nbins);
+    TE_LAUNCH_CHECK();
+  }
+  return TE_OK;
+}
