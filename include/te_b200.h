@@ -56,6 +56,12 @@ TE_API int te_profile_enable(int on);
 TE_API int te_profile_read(char* names, size_t names_bytes, double* total_ms, int64_t* launches,
                            int32_t max_entries);
 
+/* Debug aid, meaningful only in a build with -DTE_PHASE_STATS (python -m torcheval_b200._build
+ * --stats): out8 (HOST memory) receives the clock cycles that thread 0 of every radix-pass CTA
+ * spent in {setup, load, rank, wait, digit phase, look-back, scatter, output}; reset != 0 clears
+ * the counters.  Synchronises the device. */
+TE_API int te_debug_phase_stats(uint64_t* out8, int reset);
+
 /* ------------------------------------------------------------------------------------------
  * K4  confusion-matrix counting
  * replaces functional/classification/confusion_matrix.py:219-234 (`_update`: vstack +

@@ -53,6 +53,19 @@ def is_stale() -> bool:
     return not (LIB.exists() and stamp.exists() and stamp.read_text().strip() == _digest())
 
 
+def build_stats_variant() -> Path:
+    """libte_b200_stats.so: same sources with -DTE_PHASE_STATS (per-phase cycle counters in the
+    radix pass; see te_debug_phase_stats).  Select it with TE_B200_LIB=<path>."""
+    LIBDIR.mkdir(exist_ok=True)
+    out = LIBDIR / "libte_b200_stats.so"
+    cmd = [_nvcc(), *[f for f in NVCC_FLAGS if f not in ("-Xptxas", "-v")], "-DTE_PHASE_STATS", "-I", str(INCLUDE),
+           "-shared", "-o", str(out), *map(str, sources())]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"nvcc failed:\n{r.stdout}\n{r.stderr}")
+    return out
+
+
 def build(force: bool = False, verbose: bool = False) -> Path:
     """Compile every .cu under csrc/ for sm_100a and link libte_b200.so."""
     if not force and not is_stale():
@@ -87,3 +100,5 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--stats" in sys.argv:
+        print(build_stats_variant())

@@ -25,6 +25,7 @@ SIGNATURES = {
     "te_status_string": (C.c_char_p, [C.c_int]),
     "te_profile_enable": (C.c_int, [C.c_int]),
     "te_profile_read": (C.c_int, [C.c_char_p, _sz, _vp, _vp, _i32]),
+    "te_debug_phase_stats": (C.c_int, [_vp, C.c_int]),
     "te_cm_scratch_bytes": (_sz, [_i32, _i32]),
     "te_cm_update": (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _vp, _sz, _i32, _vp]),
     "te_cm_update_noalloc": (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _vp]),

@@ -1351,3 +1351,16 @@ extern "C" int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, double
   }
   return finish_packed(p, kb, 0, out, scratch, sms, st);
 }
+
+extern "C" int te_debug_phase_stats(uint64_t* out8, int reset) {
+  unsigned long long h[8] = {};
+  if (out8) {
+    TE_CUDA_TRY(cudaMemcpyFromSymbol(h, g_phase_cycles, sizeof(h)));
+    for (int i = 0; i < 8; ++i) out8[i] = h[i];
+  }
+  if (reset) {
+    unsigned long long z[8] = {};
+    TE_CUDA_TRY(cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z)));
+  }
+  return TE_OK;
+}

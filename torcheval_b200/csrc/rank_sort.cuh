@@ -48,20 +48,54 @@ struct SplitterDigit {
   }
 };
 
+// Optional per-phase cycle accounting of the pass kernel (compile with -DTE_PHASE_STATS; read with
+// te_debug_phase_stats).  Thread 0 of every CTA adds the clock64() deltas between phase boundaries.
+__device__ unsigned long long g_phase_cycles[8];
+#ifdef TE_PHASE_STATS
+#define TE_PHASE_MARK(idx)                                              \
+  do {                                                                  \
+    if (threadIdx.x == 0) {                                             \
+      const long long _now = clock64();                                 \
+      atomicAdd(&g_phase_cycles[idx], (unsigned long long)(_now - _t)); \
+      _t = _now;                                                        \
+    }                                                                   \
+  } while (0)
+#define TE_PHASE_BEGIN() long long _t = clock64()
+#else
+#define TE_PHASE_MARK(idx) do { } while (0)
+#define TE_PHASE_BEGIN() do { } while (0)
+#endif
+
+// ---- one LSD pass -----------------------------------------------------------------------------
+// Work decomposition inside a CTA: the tile is cut into GROUPS of 16 * kSortIpt consecutive
+// records, one per half-warp.  Slot i of sub-lane s in group g is record g*16*IPT + i*16 + s, so
+// (i, s) order is array order and ranking round by round, lane by lane, is stable.
+//
+// The pass is bound by the L1/shared-memory data pipe (ncu: l1tex__data_pipe_lsu_wavefronts at
+// ~80 % of peak with the first versions, ALU at 30 %), and every shared access indexed by a random
+// digit costs ~3.4 wavefronts in bank conflicts.  Ranking with half-warp groups needs a 16-bit
+// peer mask, which leaves room for the group's running digit count in the same 32-bit word:
+// three 32-bit shared instructions per round (ATOMS.OR, LDS, STS) instead of five.
+template <typename KeyT, int kSortBlock, int kSortIpt = kSortIptDefault>
+constexpr size_t onesweep_stage_bytes() {
+  // the key staging area doubles as the per-group {count << 16 | peer mask} tables of the ranking
+  // loop, which are dead by the time keys are staged
+  constexpr size_t keys = sizeof(KeyT) * kSortBlock * kSortIpt;
+  constexpr size_t tables = sizeof(uint32_t) * (kSortBlock / 16) * kRadix;
+  return keys > tables ? keys : tables;
+}
 template <typename KeyT, int kSortBlock, int kSortIpt = kSortIptDefault>
 constexpr size_t onesweep_smem_bytes() {
-  static_assert(sizeof(KeyT) * kSortBlock * kSortIpt >= sizeof(uint32_t) * (kSortBlock / kWarp) * kRadix,
-                "the peer-mask tables alias the key staging area");
-  return sizeof(KeyT) * kSortBlock * kSortIpt +
-         sizeof(uint32_t) * ((kSortBlock / kWarp) * kRadix + kRadix + kRadix / kWarp + 4);
+  return onesweep_stage_bytes<KeyT, kSortBlock, kSortIpt>() +
+         sizeof(uint32_t) * ((kSortBlock / 16) * kRadix + kRadix + kRadix / kWarp + 4);
 }
 
 // kLbWindow > 0: every tile walks back over its predecessors' counts, kLbWindow at a time.
 // kLbWindow == 0: "scan service" — the CTA that draws ticket 0 does no sorting; its 256 threads
 // (one per digit) stream over the tiles in order, kServiceBatch tiles per L2 round trip, turning
-// published tile counts (lookback[t][d]) into exclusive prefixes (prefix[t][d]).  A tile then
-// reads exactly one word per digit instead of walking a chain whose length grows with the tile
-// rate (tens of millions of tiles per second on B200) times the L2 latency.
+// published tile counts (lookback[t][d]) into exclusive prefixes (prefix[t][d]).  Measured slower
+// than the walk (one serial chain at 32 tiles per round trip cannot keep up with ~28 tiles/us);
+// kept selectable for profiling.
 constexpr int kServiceBatch = 32;
 
 template <typename KeyT, bool HAS_VAL, int kLbWindow, int kSortBlock, typename DigitOp,
@@ -73,22 +107,25 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
                          uint32_t* lookback, uint32_t* prefix, uint32_t* ticket) {
   constexpr bool kService = kLbWindow == 0;
   static_assert(kSortBlock >= kRadix && kSortBlock % kRadix == 0, "one thread per digit is needed");
-  constexpr int WARPS = kSortBlock / kWarp;
+  static_assert(kSortIpt % 4 == 0 && 16 * kSortIpt <= 256, "ranks are packed four per register");
+  constexpr int GROUPS = kSortBlock / 16;
+  constexpr int kGroupKeys = 16 * kSortIpt;
   constexpr int kSortTile = kSortBlock * kSortIpt;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   KeyT* s_keys = reinterpret_cast<KeyT*>(smem_raw);
-  uint32_t(*s_whist)[kRadix] = reinterpret_cast<uint32_t(*)[kRadix]>(s_keys + kSortTile);
-  uint32_t* s_goff = &s_whist[WARPS][0];
+  uint32_t* s_rank = reinterpret_cast<uint32_t*>(smem_raw);  // [GROUPS][256]; aliases s_keys
+  uint32_t(*s_base)[kRadix] = reinterpret_cast<uint32_t(*)[kRadix]>(
+      smem_raw + onesweep_stage_bytes<KeyT, kSortBlock, kSortIpt>());  // [GROUPS][256]
+  uint32_t* s_goff = &s_base[GROUPS][0];
   uint32_t* s_wsum = s_goff + kRadix;
   uint32_t& s_tile = s_wsum[kRadix / kWarp];
 
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  TE_PHASE_BEGIN();
   if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-  for (int i = tid; i < WARPS * kRadix; i += kSortBlock) {
-    (&s_whist[0][0])[i] = 0;
-    reinterpret_cast<uint32_t*>(s_keys)[i] = 0;  // per-warp peer masks, see the ranking loop
-  }
+  for (int i = tid; i < GROUPS * kRadix; i += kSortBlock) s_rank[i] = 0u;
   __syncthreads();
+  TE_PHASE_MARK(0);  // setup
   if (kService && s_tile == 0) {
     // ---- scan service (ticket 0 is always drawn by a resident CTA, and no tile ever waits
     //      before publishing its counts, so this loop cannot starve) ----
@@ -114,48 +151,51 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
   const uint32_t tile = kService ? s_tile - 1u : s_tile;
   const uint32_t base = tile * (uint32_t)kSortTile;
   const uint32_t valid = min((uint32_t)kSortTile, n - base);
-  const uint32_t wbase = warp * (kWarp * kSortIpt);  // tile-relative start of this warp's chunk
+  const uint32_t sub = lane & 15u;
+  const uint32_t group = tid >> 4;
+  const uint32_t gbase = group * kGroupKeys;  // tile-relative start of this half-warp's records
 
-  // ---- load (warp-striped: slot i of lane l is record wbase + i*32 + l, so (i, l) order is
-  //      array order and the ranking below is stable) ----
+  // ---- load: a warp instruction fetches two 64-byte runs, one per half-warp ----
   KeyT key[kSortIpt];
 #pragma unroll
   for (int i = 0; i < kSortIpt; ++i) {
-    const uint32_t r = wbase + i * kWarp + lane;
+    const uint32_t r = gbase + i * 16 + sub;
     key[i] = r < valid ? keys_in[base + r] : ~(KeyT)0;  // padding sorts last, is never written
   }
+#ifdef TE_PHASE_STATS
+  {  // force the loads to complete here so that the load phase is visible on its own
+    KeyT acc = 0;
+#pragma unroll
+    for (int i = 0; i < kSortIpt; ++i) acc |= key[i];
+    if (acc == (KeyT)0x12345677) s_goff[0] = 1;
+  }
+  TE_PHASE_MARK(1);  // load (thread 0's own loads)
+#endif
 
-  // ---- rank inside the warp ----
-  // Peer discovery goes through shared memory instead of eight warp votes (measured on B200:
-  // the ballot loop alone caps a pass at ~400 G keys/s, shared atomics run at >5 lanes/clk/SM):
-  // every lane ORs its lane bit into a warp-private word per digit, reads the word back (= the
-  // set of lanes holding the same digit), and the lowest of them bumps the warp's digit counter.
-  uint32_t* wh = s_whist[warp];
-  uint32_t* wm = reinterpret_cast<uint32_t*>(s_keys) + warp * kRadix;  // zeroed above, unused yet
-  const uint32_t lane_bit = 1u << lane, lt = lanemask_lt();
-  static_assert(kSortIpt % 4 == 0, "ranks and digits are packed 2 and 4 per register");
-  uint32_t rk[kSortIpt / 2];  // two 16-bit ranks per register
+  // ---- rank inside the group: ranks are group-relative (< 256), four per register ----
+  uint32_t* gt = s_rank + group * kRadix;
+  const uint32_t sub_bit = 1u << sub, sub_lt = sub_bit - 1u;
+  uint32_t rk[kSortIpt / 4];
 #pragma unroll
   for (int i = 0; i < kSortIpt; ++i) {
     const uint32_t d = dop(key[i]);
-    atomicOr(wm + d, lane_bit);
+    atomicOr(gt + d, sub_bit);
     __syncwarp();
-    const uint32_t peers = wm[d];
-    const uint32_t first = wh[d];
+    const uint32_t e = gt[d];  // count << 16 | lanes of the group holding digit d this round
     __syncwarp();
-    const uint32_t below = __popc(peers & lt);
-    if (below == 0) {  // lowest lane of the group
-      wh[d] = first + __popc(peers);
-      wm[d] = 0;
-    }
+    const uint32_t peers = e & 0xffffu, cnt = e >> 16;
+    const uint32_t below = __popc(peers & sub_lt);
+    if (below == 0) gt[d] = (cnt + __popc(peers)) << 16;  // lowest peer: bump count, clear mask
     __syncwarp();
-    const uint32_t r = first + below;  // < 512
-    if (i & 1)
-      rk[i >> 1] |= r << 16;
+    const uint32_t r = cnt + below;
+    if ((i & 3) == 0)
+      rk[i >> 2] = r;
     else
-      rk[i >> 1] = r;
+      rk[i >> 2] |= r << (8 * (i & 3));
   }
+  TE_PHASE_MARK(2);  // rank (thread 0's warp)
   __syncthreads();
+  TE_PHASE_MARK(3);  // wait for the other warps' load + rank
 
   // ---- per-digit: tile count, publish, local layout ----
   uint32_t my_cnt = 0, my_bin_start = 0;
@@ -163,7 +203,7 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
     const uint32_t d = tid;
     uint32_t cnt = 0;
 #pragma unroll
-    for (int w = 0; w < WARPS; ++w) cnt += s_whist[w][d];
+    for (int g = 0; g < GROUPS; ++g) cnt += s_rank[g * kRadix + d] >> 16;
     st_relaxed_u32(lookback + (size_t)tile * kRadix + d, cnt + 1u);
 
     // exclusive scan of cnt over the 256 digits (8 warps, named barrier 1)
@@ -181,18 +221,18 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
       if (w < (int)warp) wb += s_wsum[w];
     const uint32_t bin_start = wb + incl - cnt;
 
-    // warp-exclusive offsets inside the digit run, shifted to tile-local positions
+    // group-exclusive offsets inside the digit run, shifted to tile-local positions
     uint32_t run = bin_start;
 #pragma unroll
-    for (int w = 0; w < WARPS; ++w) {
-      const uint32_t c = s_whist[w][d];
-      s_whist[w][d] = run;
-      run += c;
+    for (int g = 0; g < GROUPS; ++g) {
+      s_base[g][d] = run;
+      run += s_rank[g * kRadix + d] >> 16;
     }
     my_cnt = cnt;
     my_bin_start = bin_start;
   }
   __syncthreads();
+  TE_PHASE_MARK(4);  // digit phase
 
   // ---- decoupled look-back over the preceding tiles (digit threads = warps 0..7), overlapped
   //      with the other warps already scattering their keys into tile order.  A B200 pass runs
@@ -229,19 +269,22 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
     st_relaxed_u32(lookback + (size_t)tile * kRadix + d, kLbInclusive | (excl + my_cnt));
     s_goff[d] = digit_base[d] + excl - my_bin_start;  // output index = s_goff[d] + tile position
   }
+  TE_PHASE_MARK(5);  // look-back (thread 0 is a digit thread)
 
   // ---- scatter into tile order through shared memory ----
+  const uint32_t* gb = s_base[group];
+  uint32_t pos[HAS_VAL ? kSortIpt / 2 : 1];  // tile positions, two per register (pairs only)
 #pragma unroll
   for (int i = 0; i < kSortIpt; ++i) {
     const uint32_t d = dop(key[i]);
-    const uint32_t r = (i & 1) ? (rk[i >> 1] >> 16) : (rk[i >> 1] & 0xffffu);
-    const uint32_t p = wh[d] + r;
+    const uint32_t r = (rk[i >> 2] >> (8 * (i & 3))) & 0xffu;
+    const uint32_t p = gb[d] + r;
     s_keys[p] = key[i];
     if (HAS_VAL) {
       if (i & 1)
-        rk[i >> 1] = (rk[i >> 1] & 0xffffu) | (p << 16);
+        pos[i >> 1] |= p << 16;
       else
-        rk[i >> 1] = (rk[i >> 1] & 0xffff0000u) | p;
+        pos[i >> 1] = p;
     }
   }
   if (kService && tid < kRadix) {
@@ -254,6 +297,7 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
     s_goff[tid] = digit_base[tid] + (w & ~kLbInclusive) - my_bin_start;
   }
   __syncthreads();
+  TE_PHASE_MARK(6);  // scatter to smem
 
   uint32_t dpack[kSortIpt / 4];  // digit of tile position tid + k*BLOCK, four per register
 #pragma unroll
@@ -269,19 +313,20 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
         dpack[k >> 2] |= d << (8 * (k & 3));
     }
   }
+  TE_PHASE_MARK(7);  // output
 
   if (HAS_VAL) {
     uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_keys);
     uint32_t val[kSortIpt];
 #pragma unroll
     for (int i = 0; i < kSortIpt; ++i) {
-      const uint32_t r = wbase + i * kWarp + lane;
+      const uint32_t r = gbase + i * 16 + sub;
       val[i] = r < valid ? vals_in[base + r] : 0u;
     }
     __syncthreads();  // everybody is done reading s_keys
 #pragma unroll
     for (int i = 0; i < kSortIpt; ++i) {
-      const uint32_t p = (i & 1) ? (rk[i >> 1] >> 16) : (rk[i >> 1] & 0xffffu);
+      const uint32_t p = (i & 1) ? (pos[i >> 1] >> 16) : (pos[i >> 1] & 0xffffu);
       s_vals[p] = val[i];
     }
     __syncthreads();
