@@ -87,7 +87,7 @@ constexpr size_t onesweep_stage_bytes() {
 template <typename KeyT, int kSortBlock, int kSortIpt = kSortIptDefault>
 constexpr size_t onesweep_smem_bytes() {
   return onesweep_stage_bytes<KeyT, kSortBlock, kSortIpt>() +
-         sizeof(uint32_t) * ((kSortBlock / 16) * kRadix + kRadix + kRadix / kWarp + 4);
+         sizeof(uint32_t) * ((kSortBlock / 16) * kRadix + 2 * kRadix + kRadix / kWarp + 4);
 }
 
 // kLbWindow > 0: every tile walks back over its predecessors' counts, kLbWindow at a time.
@@ -116,16 +116,21 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
   uint32_t* s_rank = reinterpret_cast<uint32_t*>(smem_raw);  // [GROUPS][256]; aliases s_keys
   uint32_t(*s_base)[kRadix] = reinterpret_cast<uint32_t(*)[kRadix]>(
       smem_raw + onesweep_stage_bytes<KeyT, kSortBlock, kSortIpt>());  // [GROUPS][256]
-  uint32_t* s_goff = &s_base[GROUPS][0];
-  uint32_t* s_wsum = s_goff + kRadix;
+  uint32_t* s_goff = &s_base[GROUPS][0];       // 2*256 words: also the slice starts of the digit phase
+  uint32_t* s_wsum = s_goff + 2 * kRadix;
   uint32_t& s_tile = s_wsum[kRadix / kWarp];
 
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   TE_PHASE_BEGIN();
-  if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-  for (int i = tid; i < GROUPS * kRadix; i += kSortBlock) s_rank[i] = 0u;
-  __syncthreads();
-  TE_PHASE_MARK(0);  // setup
+  // Tile order = block order.  The look-back below waits on lower-numbered tiles, which is safe
+  // because thread blocks are dispatched in increasing blockIdx order: a lower-numbered tile is
+  // always resident or finished (the same assumption CUB's decoupled look-back scan makes).
+  // Not drawing a ticket keeps a ~700-cycle global atomic off the head of every tile.
+  if (kService) {
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+    for (int i = tid; i < GROUPS * kRadix; i += kSortBlock) s_rank[i] = 0u;
+    __syncthreads();
+  }
   if (kService && s_tile == 0) {
     // ---- scan service (ticket 0 is always drawn by a resident CTA, and no tile ever waits
     //      before publishing its counts, so this loop cannot starve) ----
@@ -148,20 +153,26 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
     }
     return;
   }
-  const uint32_t tile = kService ? s_tile - 1u : s_tile;
+  const uint32_t tile = kService ? s_tile - 1u : blockIdx.x;
   const uint32_t base = tile * (uint32_t)kSortTile;
   const uint32_t valid = min((uint32_t)kSortTile, n - base);
   const uint32_t sub = lane & 15u;
   const uint32_t group = tid >> 4;
   const uint32_t gbase = group * kGroupKeys;  // tile-relative start of this half-warp's records
 
-  // ---- load: a warp instruction fetches two 64-byte runs, one per half-warp ----
+  // ---- load: a warp instruction fetches two 64-byte runs, one per half-warp.  The loads are
+  //      issued first; the ranking tables are cleared while they are in flight. ----
   KeyT key[kSortIpt];
 #pragma unroll
   for (int i = 0; i < kSortIpt; ++i) {
     const uint32_t r = gbase + i * 16 + sub;
     key[i] = r < valid ? keys_in[base + r] : ~(KeyT)0;  // padding sorts last, is never written
   }
+  if (!kService) {
+    for (int i = tid; i < GROUPS * kRadix; i += kSortBlock) s_rank[i] = 0u;
+    __syncthreads();
+  }
+  TE_PHASE_MARK(0);  // setup
 #ifdef TE_PHASE_STATS
   {  // force the loads to complete here so that the load phase is visible on its own
     KeyT acc = 0;
@@ -197,39 +208,53 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
   __syncthreads();
   TE_PHASE_MARK(3);  // wait for the other warps' load + rank
 
-  // ---- per-digit: tile count, publish, local layout ----
+  // ---- per-digit: tile count, publish, local layout.  Thread (d, h) sums the groups of slice
+  //      h = tid / 256 so that the 2*GROUPS shared-memory reads per digit are spread over the
+  //      whole CTA; the digit threads (h == 0) combine the slices. ----
+  constexpr int SLICES = kSortBlock / kRadix;
+  constexpr int GPS = GROUPS / SLICES;  // groups per slice
+  uint32_t* s_slice = s_goff;           // [SLICES][256] slice starts; s_goff proper is written later
+  static_assert(SLICES <= 2, "s_goff has room for two slices");
   uint32_t my_cnt = 0, my_bin_start = 0;
-  if (tid < kRadix) {
-    const uint32_t d = tid;
-    uint32_t cnt = 0;
+  {
+    const uint32_t d = tid & (kRadix - 1), h = tid >> 8;
+    uint32_t part = 0;
 #pragma unroll
-    for (int g = 0; g < GROUPS; ++g) cnt += s_rank[g * kRadix + d] >> 16;
-    st_relaxed_u32(lookback + (size_t)tile * kRadix + d, cnt + 1u);
-
-    // exclusive scan of cnt over the 256 digits (8 warps, named barrier 1)
-    uint32_t incl = cnt;
+    for (int g = 0; g < GPS; ++g) part += s_rank[(h * GPS + g) * kRadix + d] >> 16;
+    if (SLICES > 1 && h > 0) s_base[GROUPS - 1][d] = part;  // parked in the last row, rewritten below
+    __syncthreads();
+    uint32_t cnt = part;
+    if (SLICES > 1 && h == 0) cnt += s_base[GROUPS - 1][d];
+    uint32_t bin_start = 0;
+    if (tid < kRadix) {
+      st_relaxed_u32(lookback + (size_t)tile * kRadix + d, cnt + 1u);
+      // exclusive scan of cnt over the 256 digits (8 warps, named barrier 1)
+      uint32_t incl = cnt;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t u = __shfl_up_sync(kFull, incl, o);
-      if (lane >= (unsigned)o) incl += u;
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t u = __shfl_up_sync(kFull, incl, o);
+        if (lane >= (unsigned)o) incl += u;
+      }
+      if (lane == 31) s_wsum[warp] = incl;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      uint32_t wb = 0;
+#pragma unroll
+      for (int w = 0; w < kRadix / kWarp; ++w)
+        if (w < (int)warp) wb += s_wsum[w];
+      bin_start = wb + incl - cnt;
+      my_cnt = cnt;
+      my_bin_start = bin_start;
+      s_slice[d] = bin_start;                      // start of slice 0
+      if (SLICES > 1) s_slice[kRadix + d] = bin_start + part;  // start of slice 1
     }
-    if (lane == 31) s_wsum[warp] = incl;
-    asm volatile("bar.sync 1, 256;" ::: "memory");
-    uint32_t wb = 0;
-#pragma unroll
-    for (int w = 0; w < kRadix / kWarp; ++w)
-      if (w < (int)warp) wb += s_wsum[w];
-    const uint32_t bin_start = wb + incl - cnt;
-
+    __syncthreads();
     // group-exclusive offsets inside the digit run, shifted to tile-local positions
-    uint32_t run = bin_start;
+    uint32_t run = s_slice[h * kRadix + d];  // (s_slice overlays s_goff, which is written after the next barrier)
 #pragma unroll
-    for (int g = 0; g < GROUPS; ++g) {
-      s_base[g][d] = run;
-      run += s_rank[g * kRadix + d] >> 16;
+    for (int g = 0; g < GPS; ++g) {
+      s_base[h * GPS + g][d] = run;
+      run += s_rank[(h * GPS + g) * kRadix + d] >> 16;
     }
-    my_cnt = cnt;
-    my_bin_start = bin_start;
   }
   __syncthreads();
   TE_PHASE_MARK(4);  // digit phase
