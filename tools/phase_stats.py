@@ -11,7 +11,7 @@ import torch
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 from torcheval_b200 import _native, ops  # noqa: E402
 
-NAMES = ["setup", "load", "rank", "wait-others", "digit-phase", "look-back", "scatter", "output"]
+NAMES = ["setup", "load", "rank", "wait-others", "digit-phase", "scatter", "look-back", "output"]
 
 
 def main():

@@ -622,30 +622,22 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
     digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 4);
   }
   TE_LAUNCH_CHECK();
-  // look-back window and CTA size: tunable for profiling through the environment
-  static const int window = [] {
-    const char* e = getenv("TE_B200_LB_WINDOW");
-    const int w = e ? atoi(e) : kLbWindowDefault;
-    return (w == 0 || w == 8 || w == 16) ? w : kLbWindowDefault;
-  }();
   const int block = p.sort_block;
   const size_t smem = block == 256 ? onesweep_smem_bytes<uint32_t, 256>() : onesweep_smem_bytes<uint32_t, 512>();
   using PassFn = void (*)(const uint32_t*, uint32_t*, const uint32_t*, uint32_t*, uint32_t,
-                          const RadixDigit, const uint32_t*, uint32_t*, uint32_t*, uint32_t*);
+                          const RadixDigit, const uint32_t*, uint32_t*, uint32_t*);
   PassFn fn = nullptr;
-#define TE_PICK(HV, W, B) onesweep_pass_kernel<uint32_t, HV, W, B, RadixDigit>
-#define TE_PICK_W(HV, B) (window == 8 ? TE_PICK(HV, 8, B) : (window == 16 ? TE_PICK(HV, 16, B) : TE_PICK(HV, 0, B)))
   if (v_in0)
-    fn = block == 256 ? TE_PICK_W(true, 256) : TE_PICK_W(true, 512);
+    fn = block == 256 ? onesweep_pass_kernel<uint32_t, true, 256, RadixDigit>
+                      : onesweep_pass_kernel<uint32_t, true, 512, RadixDigit>;
   else
-    fn = block == 256 ? TE_PICK_W(false, 256) : TE_PICK_W(false, 512);
-#undef TE_PICK_W
-#undef TE_PICK
+    fn = block == 256 ? onesweep_pass_kernel<uint32_t, false, 256, RadixDigit>
+                      : onesweep_pass_kernel<uint32_t, false, 512, RadixDigit>;
   size_t smem_used = smem;
   if (p.sort_ipt == 12) {  // experimental geometry: 512 x 12 keys, 3 CTAs per SM
-    if (block != 512 || window != 8) return TE_ERR_UNSUPPORTED;
-    fn = v_in0 ? onesweep_pass_kernel<uint32_t, true, 8, 512, RadixDigit, 12>
-               : onesweep_pass_kernel<uint32_t, false, 8, 512, RadixDigit, 12>;
+    if (block != 512) return TE_ERR_UNSUPPORTED;
+    fn = v_in0 ? onesweep_pass_kernel<uint32_t, true, 512, RadixDigit, 12>
+               : onesweep_pass_kernel<uint32_t, false, 512, RadixDigit, 12>;
     smem_used = onesweep_smem_bytes<uint32_t, 512, 12>();
   }
   TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_used));
@@ -656,9 +648,9 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
     uint32_t* vout = (pass & 1) ? v_y : v_x;
     uint32_t* lbp = lb + (size_t)pass * 2 * p.sort_tiles * kRadix;
     TE_PROF(v_in0 ? "onesweep_pass_pairs" : "onesweep_pass_keys", st);
-    fn<<<p.sort_tiles + (window == 0 ? 1 : 0), block, smem_used, st>>>(
-        kin, kout, vin, vout, p.n, RadixDigit{8 * pass}, hist + pass * kRadix, lbp,
-        lbp + (size_t)p.sort_tiles * kRadix, ticket + pass);
+    fn<<<p.sort_tiles, block, smem_used, st>>>(kin, kout, vin, vout, p.n, RadixDigit{8 * pass},
+                                               hist + pass * kRadix, lbp,
+                                               lbp + (size_t)p.sort_tiles * kRadix);
     TE_LAUNCH_CHECK();
     kin = kout;
     vin = vout;
@@ -1314,17 +1306,19 @@ extern "C" int te_partition_u32(const uint32_t* keys_in, int64_t n, const uint32
   TE_LAUNCH_CHECK();
   TE_PROF("onesweep_partition", st);
   if (p.sort_block == 256) {
-    auto fn = onesweep_pass_kernel<uint32_t, false, 8, 256, SplitterDigit>;
+    auto fn = onesweep_pass_kernel<uint32_t, false, 256, SplitterDigit>;
     const size_t smem = onesweep_smem_bytes<uint32_t, 256>();
     TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     fn<<<p.sort_tiles, 256, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist,
-                                        at<uint32_t>(scratch, p.off_lookback), nullptr, at<uint32_t>(scratch, p.off_ticket));
+                                        at<uint32_t>(scratch, p.off_lookback),
+                                        at<uint32_t>(scratch, p.off_lookback) + (size_t)p.sort_tiles * kRadix);
   } else {
-    auto fn = onesweep_pass_kernel<uint32_t, false, 8, 512, SplitterDigit>;
+    auto fn = onesweep_pass_kernel<uint32_t, false, 512, SplitterDigit>;
     const size_t smem = onesweep_smem_bytes<uint32_t, 512>();
     TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     fn<<<p.sort_tiles, 512, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist,
-                                        at<uint32_t>(scratch, p.off_lookback), nullptr, at<uint32_t>(scratch, p.off_ticket));
+                                        at<uint32_t>(scratch, p.off_lookback),
+                                        at<uint32_t>(scratch, p.off_lookback) + (size_t)p.sort_tiles * kRadix);
   }
   TE_LAUNCH_CHECK();
   return TE_OK;

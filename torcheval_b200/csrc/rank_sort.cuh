@@ -90,22 +90,24 @@ constexpr size_t onesweep_smem_bytes() {
          sizeof(uint32_t) * ((kSortBlock / 16) * kRadix + 2 * kRadix + kRadix / kWarp + 4);
 }
 
-// kLbWindow > 0: every tile walks back over its predecessors' counts, kLbWindow at a time.
-// kLbWindow == 0: "scan service" — the CTA that draws ticket 0 does no sorting; its 256 threads
-// (one per digit) stream over the tiles in order, kServiceBatch tiles per L2 round trip, turning
-// published tile counts (lookback[t][d]) into exclusive prefixes (prefix[t][d]).  Measured slower
-// than the walk (one serial chain at 32 tiles per round trip cannot keep up with ~28 tiles/us);
-// kept selectable for profiling.
-constexpr int kServiceBatch = 32;
+// Cross-tile offsets: two-level decoupled look-back.  With ~30-60 million tiles per second per
+// pass and an L2 round trip of ~500 cycles, a tile that walks back over its predecessors until
+// it meets a finished one ends up adding ~100 of them, and the pass settles at exactly
+// (window / round trip) tiles per cycle (profiles/r01_phase_stats.txt: look-back grew from 25 %
+// to 33 % of the tile time as the other phases were shortened).  So tiles are grouped by
+// kLbGroup = 32: a tile needs (a) the counts of the earlier tiles of its own group — independent
+// loads, one round trip — and (b) ONE word per digit, the prefix over all earlier groups, which
+// the last tile of the previous group publishes.  Only those last tiles form a chain, and it
+// advances 32 tiles per round trip.  Tile order = block order (see below), so nothing waits on
+// a tile that has not been dispatched.
+constexpr int kLbGroup = 32;
 
-template <typename KeyT, bool HAS_VAL, int kLbWindow, int kSortBlock, typename DigitOp,
-          int kSortIpt = kSortIptDefault>
+template <typename KeyT, bool HAS_VAL, int kSortBlock, typename DigitOp, int kSortIpt = kSortIptDefault>
 __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / kSortBlock)
     onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                          const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
                          uint32_t n, const DigitOp dop, const uint32_t* __restrict__ digit_base,
-                         uint32_t* lookback, uint32_t* prefix, uint32_t* ticket) {
-  constexpr bool kService = kLbWindow == 0;
+                         uint32_t* lookback, uint32_t* group_prefix) {
   static_assert(kSortBlock >= kRadix && kSortBlock % kRadix == 0, "one thread per digit is needed");
   static_assert(kSortIpt % 4 == 0 && 16 * kSortIpt <= 256, "ranks are packed four per register");
   constexpr int GROUPS = kSortBlock / 16;
@@ -118,7 +120,6 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
       smem_raw + onesweep_stage_bytes<KeyT, kSortBlock, kSortIpt>());  // [GROUPS][256]
   uint32_t* s_goff = &s_base[GROUPS][0];       // 2*256 words: also the slice starts of the digit phase
   uint32_t* s_wsum = s_goff + 2 * kRadix;
-  uint32_t& s_tile = s_wsum[kRadix / kWarp];
 
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   TE_PHASE_BEGIN();
@@ -126,34 +127,7 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
   // because thread blocks are dispatched in increasing blockIdx order: a lower-numbered tile is
   // always resident or finished (the same assumption CUB's decoupled look-back scan makes).
   // Not drawing a ticket keeps a ~700-cycle global atomic off the head of every tile.
-  if (kService) {
-    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-    for (int i = tid; i < GROUPS * kRadix; i += kSortBlock) s_rank[i] = 0u;
-    __syncthreads();
-  }
-  if (kService && s_tile == 0) {
-    // ---- scan service (ticket 0 is always drawn by a resident CTA, and no tile ever waits
-    //      before publishing its counts, so this loop cannot starve) ----
-    if (tid >= kRadix) return;
-    const uint32_t tiles = (n + kSortTile - 1) / kSortTile;
-    uint32_t run = 0;  // keys with digit `tid` in all tiles before the current one
-    for (uint32_t t0 = 0; t0 < tiles; t0 += kServiceBatch) {
-      uint32_t a[kServiceBatch];
-#pragma unroll
-      for (int j = 0; j < kServiceBatch; ++j)
-        a[j] = (t0 + j < tiles) ? ld_relaxed_u32(lookback + (size_t)(t0 + j) * kRadix + tid) : 1u;
-#pragma unroll
-      for (int j = 0; j < kServiceBatch; ++j) {
-        if (t0 + j < tiles) {
-          while (a[j] == 0) a[j] = ld_relaxed_u32(lookback + (size_t)(t0 + j) * kRadix + tid);
-          st_relaxed_u32(prefix + (size_t)(t0 + j) * kRadix + tid, kLbInclusive | run);
-          run += a[j] - 1u;
-        }
-      }
-    }
-    return;
-  }
-  const uint32_t tile = kService ? s_tile - 1u : blockIdx.x;
+  const uint32_t tile = blockIdx.x;
   const uint32_t base = tile * (uint32_t)kSortTile;
   const uint32_t valid = min((uint32_t)kSortTile, n - base);
   const uint32_t sub = lane & 15u;
@@ -168,10 +142,8 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
     const uint32_t r = gbase + i * 16 + sub;
     key[i] = r < valid ? keys_in[base + r] : ~(KeyT)0;  // padding sorts last, is never written
   }
-  if (!kService) {
-    for (int i = tid; i < GROUPS * kRadix; i += kSortBlock) s_rank[i] = 0u;
-    __syncthreads();
-  }
+  for (int i = tid; i < GROUPS * kRadix; i += kSortBlock) s_rank[i] = 0u;
+  __syncthreads();
   TE_PHASE_MARK(0);  // setup
 #ifdef TE_PHASE_STATS
   {  // force the loads to complete here so that the load phase is visible on its own
@@ -259,44 +231,7 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
   __syncthreads();
   TE_PHASE_MARK(4);  // digit phase
 
-  // ---- decoupled look-back over the preceding tiles (digit threads = warps 0..7), overlapped
-  //      with the other warps already scattering their keys into tile order.  A B200 pass runs
-  //      at tens of millions of tiles per second while one L2 round trip is ~0.5 us, so a tile
-  //      routinely has to add up dozens of not-yet-prefixed predecessors: fetch them kLbWindow at
-  //      a time with independent loads instead of one dependent load per predecessor. ----
-  if (!kService && tid < kRadix) {
-    const uint32_t d = tid;
-    uint32_t excl = 0;
-    int64_t t = (int64_t)tile - 1;
-    constexpr int W = kLbWindow > 0 ? kLbWindow : 1;
-    while (t >= 0) {
-      uint32_t w[W];
-#pragma unroll
-      for (int j = 0; j < W; ++j)
-        w[j] = (t - j >= 0) ? ld_relaxed_u32(lookback + (size_t)(t - j) * kRadix + d) : kLbInclusive;
-      int used = 0;
-      bool done = false;
-#pragma unroll
-      for (int j = 0; j < W; ++j) {
-        if (!done && used == j) {
-          if (w[j] & kLbInclusive) {
-            excl += w[j] & ~kLbInclusive;
-            done = true;
-          } else if (w[j] != 0) {
-            excl += w[j] - 1u;
-            used = j + 1;
-          }
-        }
-      }
-      if (done) break;
-      t -= used;  // the first unpublished predecessor is polled again
-    }
-    st_relaxed_u32(lookback + (size_t)tile * kRadix + d, kLbInclusive | (excl + my_cnt));
-    s_goff[d] = digit_base[d] + excl - my_bin_start;  // output index = s_goff[d] + tile position
-  }
-  TE_PHASE_MARK(5);  // look-back (thread 0 is a digit thread)
-
-  // ---- scatter into tile order through shared memory ----
+  // ---- scatter into tile order through shared memory (needs only tile-local positions) ----
   const uint32_t* gb = s_base[group];
   uint32_t pos[HAS_VAL ? kSortIpt / 2 : 1];  // tile positions, two per register (pairs only)
 #pragma unroll
@@ -312,17 +247,40 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
         pos[i >> 1] = p;
     }
   }
-  if (kService && tid < kRadix) {
-    // by now the service has usually been past this tile for a while: one load per digit
-    const uint32_t* pp = prefix + (size_t)tile * kRadix + tid;
-    uint32_t w;
-    do {
-      w = ld_relaxed_u32(pp);
-    } while (w == 0);
-    s_goff[tid] = digit_base[tid] + (w & ~kLbInclusive) - my_bin_start;
+  TE_PHASE_MARK(5);  // scatter to smem
+
+  // ---- two-level look-back: the whole CTA takes part, thread (d, h) fetches slice h of the
+  //      in-group predecessors of digit d; the keys are in shared memory by now, so the loads
+  //      have the registers to themselves ----
+  {
+    constexpr int JH = kLbGroup / SLICES;  // in-group predecessors per thread
+    const uint32_t d = tid & (kRadix - 1), h = tid >> 8;
+    const uint32_t grp = tile / kLbGroup, k = tile % kLbGroup;
+    const uint32_t* arow = lookback + ((size_t)grp * kLbGroup + h * JH) * kRadix + d;
+    const uint32_t* gp = group_prefix + (size_t)(grp - 1) * kRadix + d;  // used only if grp > 0
+    uint32_t w[JH];
+#pragma unroll
+    for (int j = 0; j < JH; ++j) w[j] = (h * JH + j < k) ? ld_relaxed_u32(arow + (size_t)j * kRadix) : 1u;
+    uint32_t gpre = (h == 0 && grp > 0) ? ld_relaxed_u32(gp) : kLbInclusive;
+    uint32_t sum = 0;
+#pragma unroll
+    for (int j = 0; j < JH; ++j) {
+      while (w[j] == 0) w[j] = ld_relaxed_u32(arow + (size_t)j * kRadix);
+      sum += w[j] - 1u;
+    }
+    while (gpre == 0) gpre = ld_relaxed_u32(gp);
+    sum += gpre & ~kLbInclusive;
+    if (SLICES > 1 && h > 0) s_slice[kRadix + d] = sum;
+    __syncthreads();  // also: every key is staged in s_keys
+    if (tid < kRadix) {
+      const uint32_t excl = sum + (SLICES > 1 ? s_slice[kRadix + d] : 0u);
+      if (k == kLbGroup - 1)  // last tile of the group: extend the chain of group prefixes
+        st_relaxed_u32(group_prefix + (size_t)grp * kRadix + d, kLbInclusive | (excl + my_cnt));
+      s_goff[d] = digit_base[d] + excl - my_bin_start;  // output index = s_goff[d] + tile position
+    }
   }
   __syncthreads();
-  TE_PHASE_MARK(6);  // scatter to smem
+  TE_PHASE_MARK(6);  // look-back
 
   uint32_t dpack[kSortIpt / 4];  // digit of tile position tid + k*BLOCK, four per register
 #pragma unroll
