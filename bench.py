@@ -246,6 +246,9 @@ def run_ours(args) -> dict:
     e2e = None
     cpu = None
     secondary = None
+    binned = None
+    if world == 1:
+        binned = binned_bench(args, x, y, peak_gbs, peak_src)
     if world == 1:
         xh = torch.empty(n_local, dtype=torch.float32, pin_memory=True)
         yh = torch.empty(n_local, dtype=torch.int64, pin_memory=True)
@@ -350,6 +353,8 @@ def run_ours(args) -> dict:
         line["cpu_baseline"] = cpu
     if secondary:
         line["secondary"] = secondary
+    if binned:
+        line["secondary_binned"] = binned
     if world > 1:
         import torch.distributed as dist
 
@@ -373,6 +378,54 @@ def cpu_baseline_auroc(xh: torch.Tensor, yh: torch.Tensor, log2_sample: int = 25
         "host_cpus": os.cpu_count(),
         "kind": "port",
         "sample": f"first 2^{m.bit_length() - 1} scores of the same workload, 1 run, {dt:.1f} s (oracle/oracle_torch.py)",
+    }
+
+
+def binned_bench(args, x, y, peak_gbs, peak_src) -> dict:
+    """configs[2] on one GPU: BinaryBinnedAUROC/AUPRC counting, 10k thresholds, the same 2^30 scores."""
+    from torcheval_b200 import ops
+
+    T = 10_000
+    n = x.numel()
+    thr = torch.linspace(0, 1, T, device=x.device)
+    hist = torch.zeros((1, T + 1, 2), dtype=torch.int64, device=x.device)
+    for _ in range(3):
+        ops.binned_hist_update_(hist, x, y, thr)
+    torch.cuda.synchronize()
+    hist.zero_()
+    steps = max(args.steps, 5)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with KernelProfile() as prof:
+        ev0.record()
+        for _ in range(steps):
+            ops.binned_hist_update_(hist, x, y, thr)
+        ev1.record()
+        torch.cuda.synchronize()
+        kernels = prof.read()
+    ms = ev0.elapsed_time(ev1) / steps
+    assert int(hist.sum().item()) == steps * n
+    k = kernels.get("binned_hist_smem", {"total_ms": ms * steps, "launches": steps})
+    kavg = k["total_ms"] / k["launches"]
+    kgbs = 12.0 * n / (kavg * 1e-3) / 1e9
+    tp, fp, fn = ops.binned_counts(hist, T)
+    auroc = float(ops.binned_integrate(tp, fp, fn, 0)[0].item())
+    return {
+        "metric": "binary_binned_auroc_update_scores_per_sec",
+        "value": n / (ms * 1e-3),
+        "unit": "scores/s",
+        "ms_per_step": ms,
+        "config": {"workload": f"BinaryBinnedAUROC/AUPRC update, T={T} thresholds, N=2^{n.bit_length() - 1} scores, 1 GPU", "binned_auroc": auroc},
+        "roofline": {
+            "kernel": "binned_hist_smem",
+            "bound": "hbm",
+            "achieved": round(kgbs, 1),
+            "peak": peak_gbs,
+            "peak_source": peak_src,
+            "unit": "GB/s",
+            "frac": round(kgbs / peak_gbs, 4),
+            "traffic": None,
+            "avg_launch_ms": round(kavg, 4),
+        },
     }
 
 

@@ -206,23 +206,37 @@ TE_API int te_binary_auprc_general(const float* score, const void* target, int32
                                    int64_t n, double* out, void* scratch, size_t scratch_bytes,
                                    void* stream);
 
+/* K2 — one-vs-rest ranking over an (n, C) row-major float32 score matrix (row stride ld):
+ * replaces functional/classification/auroc.py:213-235 (multiclass AUROC) and auprc.py:279-347 +
+ * precision_recall_curve.py:296-310 (multiclass / multilabel AUPRC, a Python loop over labels).
+ * multilabel == 0: target is (n,) int64 class ids, positives of class c are target == c;
+ * multilabel != 0: target is (n, C) int64 with row stride target_ld, positives are == 1.
+ * mode 0 = AUROC, 1 = AUPRC.  out is float64 [C][8], row c laid out as te_binary_auroc's out
+ * (out[c][4] != 0: class c has negative scores, use the general entry point for that column). */
+TE_API size_t te_ovr_rank_scratch_bytes(int64_t n);
+TE_API int te_ovr_rank(const float* input, int64_t ld, const int64_t* target, int64_t target_ld, int64_t n,
+                       int32_t num_classes, int32_t multilabel, int32_t mode, double* out, void* scratch,
+                       size_t scratch_bytes, void* stream);
+
 /* Pieces of the distributed sample sort of rank-sharded scores (torcheval_b200/distributed.py;
  * replaces dist.all_gather_object of the whole sample set at toolkit.py:388).
- *  te_rank_pack: score/target -> packed keys ((float bits << 1) | label), info[0] = #positives,
- *    info[1] = TE_RANK_FLAG_* (int64[2], device).  keys_out must be 16-byte aligned.
- *  te_partition_u32: stable partition of keys by up to 15 ascending splitters given in HOST
- *    memory (bucket = #{splitters <= key}); counts (int64[num_splitters + 1], device) receives
- *    the bucket sizes, keys_out the keys grouped by bucket.
+ *  te_rank_pack: score/target -> packed keys ((float bits << 1) | label); info (int64[2], device)
+ *    = {#positives, TE_RANK_FLAG_*}; counts (int64[num_splitters + 1], device) = sizes of the
+ *    buckets the keys fall in, bucket = #{splitters <= key}, for up to 15 ascending splitters
+ *    given in HOST memory (num_splitters may be 0).  keys_out must be 16-byte aligned.
+ *  te_partition_u32: stable partition of keys by the same kind of splitters; counts_in (device,
+ *    may be NULL) are bucket sizes already known from te_rank_pack, counts receives them again,
+ *    keys_out the keys grouped by bucket.
  *  te_binary_auroc_from_keys: sort packed keys and integrate; out[] as te_binary_auroc plus
  *    out[5], out[6] = high / low 32 bits of the exact integer 2U and out[7] = n. */
 TE_API size_t te_rank_pack_scratch_bytes(int64_t n);
 TE_API int te_rank_pack(const float* score, const void* target, int32_t target_dtype, int64_t n,
-                        uint32_t* keys_out, int64_t* info, void* scratch, size_t scratch_bytes,
-                        void* stream);
+                        const uint32_t* splitters_host, int32_t num_splitters, uint32_t* keys_out,
+                        int64_t* info, int64_t* counts, void* scratch, size_t scratch_bytes, void* stream);
 TE_API size_t te_partition_u32_scratch_bytes(int64_t n);
 TE_API int te_partition_u32(const uint32_t* keys_in, int64_t n, const uint32_t* splitters_host,
-                            int32_t num_splitters, uint32_t* keys_out, int64_t* counts, void* scratch,
-                            size_t scratch_bytes, void* stream);
+                            int32_t num_splitters, const int64_t* counts_in, uint32_t* keys_out,
+                            int64_t* counts, void* scratch, size_t scratch_bytes, void* stream);
 TE_API int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, double* out, void* scratch,
                                      size_t scratch_bytes, void* stream);
 

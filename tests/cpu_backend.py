@@ -152,6 +152,16 @@ def binary_auprc_general(score, target):
     return out
 
 
+def ovr_rank(input, target, multilabel, mode):
+    xs, ts = _np(input), _np(target)
+    rows = []
+    for c in range(xs.shape[1]):
+        lab = torch.from_numpy(((ts[:, c] == 1) if multilabel else (ts == c)).astype(np.int64))
+        col = torch.from_numpy(xs[:, c].copy())
+        rows.append(binary_auprc_packed(col, lab) if mode == 1 else binary_auroc_packed(col, lab))
+    return torch.stack(rows)
+
+
 def sort_u32(keys, vals=None):
     k = _np(keys).view(np.uint32)
     order = np.argsort(k, kind="stable")
@@ -159,7 +169,7 @@ def sort_u32(keys, vals=None):
     return ok, (None if vals is None else vals[torch.from_numpy(order)])
 
 
-def rank_pack(score, target):
+def rank_pack(score, target, splitters=()):
     x = _np(score).astype(np.float32).copy()
     bits = x.view(np.uint32).copy()
     bits[bits == 0x80000000] = 0
@@ -167,10 +177,12 @@ def rank_pack(score, target):
     lab = (y == 1).astype(np.uint32)
     keys = ((bits << np.uint32(1)) | lab).astype(np.uint32)
     info = torch.tensor([int(lab.sum()), _flags(score, target)], dtype=torch.int64)
-    return torch.from_numpy(keys.view(np.int32).copy()), info
+    kt = torch.from_numpy(keys.view(np.int32).copy())
+    _, counts = partition_u32(kt, splitters)
+    return kt, info, counts
 
 
-def partition_u32(keys, splitters):
+def partition_u32(keys, splitters, counts_in=None):
     k = _np(keys).view(np.uint32)
     sp = np.asarray([int(v) & 0xFFFFFFFF for v in splitters], dtype=np.uint64)
     bucket = np.searchsorted(sp, k.astype(np.uint64), side="right") if sp.size else np.zeros(k.size, dtype=np.int64)
@@ -189,7 +201,7 @@ def binary_auroc_from_keys(keys):
 _NAMES = [
     "cm_update_", "cm_update_logits_", "class_counts_", "match_count", "binned_hist_update_",
     "binned_hist2d_update_", "binned_counts", "binned_integrate", "binary_auroc_packed",
-    "binary_auprc_packed", "binary_auroc_general", "binary_auprc_general", "sort_u32", "rank_pack",
+    "binary_auprc_packed", "binary_auroc_general", "binary_auprc_general", "sort_u32", "rank_pack", "ovr_rank",
     "partition_u32", "binary_auroc_from_keys",
 ]
 

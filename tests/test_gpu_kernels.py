@@ -443,18 +443,64 @@ def test_rank_pack_partition_from_keys(ops):
         if n > 10:
             x[3], x[4] = -0.0, 0.0
         y = rs.integers(0, 2, n)
-        keys, info = ops.rank_pack(dev(x), dev(y))
-        wk, winfo = cpu_backend.rank_pack(torch.from_numpy(x), torch.from_numpy(y))
+        keys, info, cnt0 = ops.rank_pack(dev(x), dev(y))
+        wk, winfo, _ = cpu_backend.rank_pack(torch.from_numpy(x), torch.from_numpy(y))
         np.testing.assert_array_equal(keys.cpu().numpy(), wk.numpy())
-        assert info.tolist() == winfo.tolist()
+        assert info.tolist() == winfo.tolist() and cnt0.tolist() == [n]
         for sp in ([], [int(0.5 * 2**31) & ~1], sorted(int(v) & ~1 for v in rs.integers(0, 2**31, 7)), [10, 10, 2**32 - 2]):
-            part, counts = ops.partition_u32(keys, sp)
             wp, wc = cpu_backend.partition_u32(wk, sp)
-            assert counts.tolist() == wc.tolist(), (n, sp)
-            np.testing.assert_array_equal(part.cpu().numpy(), wp.numpy())  # stable
+            k2, _, c2 = ops.rank_pack(dev(x), dev(y), sp)  # bucket sizes straight from the pack pass
+            assert c2.tolist() == wc.tolist(), (n, sp)
+            for known in (None, c2):
+                part, counts = ops.partition_u32(k2, sp, known)
+                assert counts.tolist() == wc.tolist(), (n, sp)
+                np.testing.assert_array_equal(part.cpu().numpy(), wp.numpy())  # stable
         out = ops.binary_auroc_from_keys(keys).cpu().numpy()
         want = cpu_backend.binary_auroc_from_keys(wk).numpy()
         close(out[0], want[0], 1e-12)
         assert list(out[1:4]) == list(want[1:4]) and list(out[5:8]) == list(want[5:8])
-    _, info = ops.rank_pack(dev(np.array([0.5, -1.0], dtype=np.float32)), dev(np.array([0, 1])))
+    _, info, _ = ops.rank_pack(dev(np.array([0.5, -1.0], dtype=np.float32)), dev(np.array([0, 1])))
     assert info.tolist() == [1, 2]
+
+
+# =============================================================================== K2: one-vs-rest
+@pytest.mark.parametrize("n,C", [(1, 3), (257, 17), (5000, 8), (40001, 13), (3000, 1000)])
+def test_ovr_rank_vs_oracle(ops, n, C):
+    rs = np.random.default_rng(n + C)
+    x = (rs.integers(0, 200, (n, C)) / 200).astype(np.float32) if C < 100 else rs.random((n, C), dtype=np.float32)
+    y = rs.integers(0, C, n)
+    if C > 3:
+        y[y == 2] = 1  # class 2 never occurs
+    a = ops.ovr_rank(dev(x), dev(y), False, 0).cpu().numpy()
+    p = ops.ovr_rank(dev(x), dev(y), False, 1).cpu().numpy()
+    assert (a[:, 4] == 0).all()
+    close(a[:, 0], oracle.multiclass_auroc(x, y), RTOL64)
+    close(p[:, 0], oracle.multiclass_auprc(x, y), RTOL64)
+    np.testing.assert_array_equal(a[:, 1], np.bincount(y, minlength=C))
+    ml = rs.integers(0, 2, (n, C))
+    if C > 3:
+        ml[:, 1] = 0
+    q = ops.ovr_rank(dev(x), dev(ml), True, 1).cpu().numpy()
+    close(q[:, 0], oracle.multilabel_auprc(x, ml), RTOL64)
+    # a strided view (row stride > C) and a column with negative scores
+    wide = np.concatenate([x, -np.ones((n, 3), dtype=np.float32)], axis=1)
+    a2 = ops.ovr_rank(dev(wide)[:, :C], dev(y), False, 0).cpu().numpy()
+    np.testing.assert_array_equal(a2[:, 0], a[:, 0])
+    x2 = x.copy()
+    x2[:, 0] -= 0.5
+    a3 = ops.ovr_rank(dev(x2), dev(y), False, 0).cpu().numpy()
+    assert a3[0, 4] == 2 and (a3[1:, 4] == 0).all()
+    np.testing.assert_array_equal(a3[1:, 0], a[1:, 0])
+
+
+def test_functional_multiclass_with_negative_columns(ops):
+    from torcheval_b200.metrics import functional as F
+
+    rs = np.random.default_rng(3)
+    n, C = 3001, 6
+    x = rs.standard_normal((n, C)).astype(np.float32)  # logits: every column flagged -> general path
+    y = rs.integers(0, C, n)
+    got = F.multiclass_auroc(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda(), num_classes=C, average=None)
+    close(got.cpu().numpy(), oracle.multiclass_auroc(x, y), RTOL32)
+    got = F.multiclass_auprc(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda(), average=None)
+    close(got.cpu().numpy(), oracle.multiclass_auprc(x, y), RTOL32)

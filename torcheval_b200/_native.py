@@ -43,10 +43,12 @@ SIGNATURES = {
     "te_binary_rank_general_scratch_bytes": (_sz, [_i64]),
     "te_binary_auroc_general": (C.c_int, [_vp, _vp, _i32, _vp, _i64, _vp, _vp, _sz, _vp]),
     "te_binary_auprc_general": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp, _sz, _vp]),
+    "te_ovr_rank_scratch_bytes": (_sz, [_i64]),
+    "te_ovr_rank": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i32, _i32, _i32, _vp, _vp, _sz, _vp]),
     "te_rank_pack_scratch_bytes": (_sz, [_i64]),
-    "te_rank_pack": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp, _vp, _sz, _vp]),
+    "te_rank_pack": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
     "te_partition_u32_scratch_bytes": (_sz, [_i64]),
-    "te_partition_u32": (C.c_int, [_vp, _i64, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "te_partition_u32": (C.c_int, [_vp, _i64, _vp, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
     "te_binary_auroc_from_keys": (C.c_int, [_vp, _i64, _vp, _vp, _sz, _vp]),
     "te_sort_u32_scratch_bytes": (_sz, [_i64, _i32]),
     "te_sort_u32": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _sz, _vp]),

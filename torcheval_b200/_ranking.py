@@ -88,19 +88,22 @@ def binary_auprc(input: torch.Tensor, target: torch.Tensor, num_tasks: int = 1) 
 
 
 def _one_vs_rest(input: torch.Tensor, target: torch.Tensor, auprc: bool, multilabel: bool) -> torch.Tensor:
-    """Per class / per label values (float64, on the compute device).  Columns are transposed to
-    contiguous rows once; positives are target == c (multiclass) or target[:, c] == 1."""
+    """Per class / per label values (float64, on the compute device): the batched one-vs-rest
+    kernels do all columns; a column the packed representation cannot take (negative scores) is
+    redone on its own through the general path."""
     dev = compute_device(input)
     x = _as_f32_scores(stage(input, dev))
     t = stage(target, dev)
-    xt = x.t().contiguous()
-    C = xt.shape[0]
-    vals = []
-    for c in range(C):
+    if t.dtype != torch.int64:
+        t = t.to(torch.int64)
+    out = ops.ovr_rank(x, t, multilabel, 1 if auprc else 0)
+    vals = out[:, 0].clone()
+    flagged = torch.nonzero(out[:, 4] != 0).flatten().tolist()  # the one host read of this path
+    for c in flagged:
+        col = x[:, c].contiguous()
         lab = (t[:, c] == 1) if multilabel else (t == c)
-        row = _binary_auprc_row(xt[c], lab) if auprc else _binary_auroc_row(xt[c], lab, None)
-        vals.append(row)
-    return torch.stack(vals)
+        vals[c] = ops.binary_auprc_general(col, lab)[0] if auprc else ops.binary_auroc_general(col, lab, None)[0]
+    return vals
 
 
 def multiclass_auroc(input: torch.Tensor, target: torch.Tensor) -> torch.Tensor:

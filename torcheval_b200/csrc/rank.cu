@@ -1131,6 +1131,89 @@ __global__ void rank_info_kernel(const RankScalars* __restrict__ scal, long long
   }
 }
 
+// pack for the distributed path: (score, target) -> packed keys, #positives, flags, and — the
+// splitters are already known — the sizes of the destination buckets, all in one streaming pass
+// (12 B read + 4 B written per score; no radix histograms, the keys are re-histogrammed after the
+// exchange).
+template <typename TargetT>
+__global__ void __launch_bounds__(1024)
+    pack_bucket_kernel(const float* __restrict__ score, const TargetT* __restrict__ target, uint32_t n,
+                       bool vec_ok, const SplitterDigit dop, uint32_t* __restrict__ keys_out, uint32_t* hist,
+                       RankScalars* scal) {
+  __shared__ uint32_t sh[16 * kWarp];
+  const unsigned tid = threadIdx.x, lane = tid & 31;
+  if (tid < 16 * kWarp) sh[tid] = 0;
+  __syncthreads();
+  uint32_t npos = 0, bad_label = 0, neg_score = 0;
+  const uint32_t ngroups = (n + 3) / 4;
+  for (uint32_t g = blockIdx.x * blockDim.x + tid; g < ngroups; g += gridDim.x * blockDim.x) {
+    const uint32_t i0 = g * 4, cnt = min(4u, n - i0);
+    float x[4];
+    uint32_t lab[4];
+    if (cnt == 4 && vec_ok) {
+      const int4 a = ld_stream_v4(score + i0);
+      x[0] = __int_as_float(a.x), x[1] = __int_as_float(a.y), x[2] = __int_as_float(a.z), x[3] = __int_as_float(a.w);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) x[j] = j < (int)cnt ? score[i0 + j] : 0.f;
+    }
+    bool done = false;
+    if constexpr (sizeof(TargetT) == 8) {
+      if (cnt == 4 && vec_ok) {
+        const int4 t0 = ld_stream_v4(target + i0), t1 = ld_stream_v4(target + i0 + 2);
+        TargetT tv[4];
+        const unsigned long long u0 = ((unsigned long long)(uint32_t)t0.y << 32) | (uint32_t)t0.x;
+        const unsigned long long u1 = ((unsigned long long)(uint32_t)t0.w << 32) | (uint32_t)t0.z;
+        const unsigned long long u2 = ((unsigned long long)(uint32_t)t1.y << 32) | (uint32_t)t1.x;
+        const unsigned long long u3 = ((unsigned long long)(uint32_t)t1.w << 32) | (uint32_t)t1.z;
+        memcpy(&tv[0], &u0, 8), memcpy(&tv[1], &u1, 8), memcpy(&tv[2], &u2, 8), memcpy(&tv[3], &u3, 8);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) lab[j] = LabelOf<TargetT>::get(tv[j], bad_label);
+        done = true;
+      }
+    }
+    if (!done) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) lab[j] = j < (int)cnt ? LabelOf<TargetT>::get(target[i0 + j], bad_label) : 0u;
+    }
+    uint32_t k[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      uint32_t b = __float_as_uint(x[j]);
+      if (b == 0x80000000u) b = 0u;
+      neg_score |= b >> 31;
+      k[j] = (b << 1) | lab[j];
+      if (j < (int)cnt) {
+        npos += lab[j];
+        atomicAdd(sh + dop(k[j]) * kWarp + lane, 1u);
+      }
+    }
+    if (cnt == 4) {
+      st_stream_v4(keys_out + i0, make_int4((int)k[0], (int)k[1], (int)k[2], (int)k[3]));
+    } else {
+      for (uint32_t j = 0; j < cnt; ++j) keys_out[i0 + j] = k[j];
+    }
+  }
+  __syncthreads();
+  if (tid < 16) {
+    uint32_t s = 0;
+    for (int r = 0; r < kWarp; ++r) s += sh[tid * kWarp + r];
+    if (s) atomicAdd(hist + tid, s);
+  }
+  npos = warp_sum(npos);
+  const uint32_t anybad = __any_sync(kFull, bad_label != 0);
+  const uint32_t anyneg = __any_sync(kFull, neg_score != 0);
+  if (lane == 0) {
+    if (npos) atomicAdd(&scal->positives, (unsigned long long)npos);
+    const uint32_t f = (anybad ? TE_RANK_FLAG_BAD_LABEL : 0) | (anyneg ? TE_RANK_FLAG_NEGATIVE_SCORE : 0);
+    if (f) atomicOr(&scal->flags, f);
+  }
+}
+
+__global__ void counts_to_hist_kernel(const long long* __restrict__ counts, uint32_t* hist, int nb) {
+  if ((int)threadIdx.x < nb) hist[threadIdx.x] = (uint32_t)counts[threadIdx.x];
+}
+
 // bucket histogram for the splitter partition: hist[b] = #{keys with bucket b}, b < 16
 __global__ void __launch_bounds__(1024)
     bucket_hist_kernel(const uint32_t* __restrict__ keys, uint32_t n, const SplitterDigit dop,
@@ -1164,6 +1247,92 @@ __global__ void __launch_bounds__(1024)
 
 __global__ void copy_counts_kernel(const uint32_t* __restrict__ hist, long long* counts, int nb) {
   if ((int)threadIdx.x < nb) counts[threadIdx.x] = (long long)hist[threadIdx.x];
+}
+
+
+// ------------------------------------------------------------------------------------------
+// K2 — one-vs-rest (multiclass / multilabel) ranking: batched transposing ingest
+// ------------------------------------------------------------------------------------------
+// Reference: functional/classification/auroc.py:213-235 (input.T.sort(dim=1) + target[indices] ==
+// arange[:, None]) and auprc.py:279-347 / precision_recall_curve.py:296-310 (Python loop over
+// labels).  The (n, C) score matrix is row-major, so a class is a strided column.  One thread
+// takes one row and kOvrBatch = 8 consecutive classes (32 contiguous bytes = one sector, no read
+// amplification), builds the eight packed keys (label = target[i] == c, or target[i, c] == 1) and
+// writes them to eight class-major key arrays — coalesced across the threads of a warp — while
+// the per-class digit histograms accumulate in shared memory.  Each class array then goes
+// through the same radix passes and fused sweep as the binary metric.
+constexpr int kOvrBatch = 8;
+constexpr int kOvrBlock = 512;
+
+template <bool MULTILABEL>
+__global__ void __launch_bounds__(kOvrBlock)
+    ovr_ingest_kernel(const float* __restrict__ input, int64_t ld, const long long* __restrict__ target,
+                      int64_t ld_t, uint32_t n, int c0, int nb, bool vec_ok, char* scratch0,
+                      size_t plan_stride, size_t off_keys, size_t off_hist, size_t off_scal) {
+  extern __shared__ uint32_t sh[];  // [nb][4][256]
+  const unsigned tid = threadIdx.x, lane = tid & 31;
+  for (int i = tid; i < kOvrBatch * 4 * kRadix; i += kOvrBlock) sh[i] = 0;
+  __syncthreads();
+  uint32_t npos[kOvrBatch];
+  uint32_t negmask = 0, badmask = 0;
+#pragma unroll
+  for (int j = 0; j < kOvrBatch; ++j) npos[j] = 0;
+  for (uint32_t i = blockIdx.x * kOvrBlock + tid; i < n; i += gridDim.x * kOvrBlock) {
+    const float* row = input + (int64_t)i * ld + c0;
+    float x[kOvrBatch];
+    if (vec_ok && nb == kOvrBatch) {
+      const int4 a = ld_stream_v4(row), b = ld_stream_v4(row + 4);
+      x[0] = __int_as_float(a.x), x[1] = __int_as_float(a.y), x[2] = __int_as_float(a.z), x[3] = __int_as_float(a.w);
+      x[4] = __int_as_float(b.x), x[5] = __int_as_float(b.y), x[6] = __int_as_float(b.z), x[7] = __int_as_float(b.w);
+    } else {
+#pragma unroll
+      for (int j = 0; j < kOvrBatch; ++j) x[j] = j < nb ? __ldg(row + j) : 0.f;
+    }
+    long long tcls = 0;
+    if (!MULTILABEL) tcls = __ldg(target + i);
+#pragma unroll
+    for (int j = 0; j < kOvrBatch; ++j) {
+      if (j < nb) {
+        uint32_t lab;
+        if (MULTILABEL) {
+          const long long t = __ldg(target + (int64_t)i * ld_t + c0 + j);
+          lab = t == 1 ? 1u : 0u;
+        } else {
+          lab = tcls == (long long)(c0 + j) ? 1u : 0u;
+        }
+        uint32_t bits = __float_as_uint(x[j]);
+        if (bits == 0x80000000u) bits = 0u;
+        negmask |= (bits >> 31) << j;
+        const uint32_t k = (bits << 1) | lab;
+        npos[j] += lab;
+        reinterpret_cast<uint32_t*>(scratch0 + (size_t)j * plan_stride + off_keys)[i] = k;
+        uint32_t* h = sh + j * 4 * kRadix;
+#pragma unroll
+        for (int p = 0; p < 4; ++p) atomicAdd(h + p * kRadix + ((k >> (8 * p)) & 0xffu), 1u);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < nb * 4 * kRadix; i += kOvrBlock) {
+    const uint32_t v = sh[i];
+    if (v) {
+      const int j = i / (4 * kRadix);
+      atomicAdd(reinterpret_cast<uint32_t*>(scratch0 + (size_t)j * plan_stride + off_hist) + (i - j * 4 * kRadix), v);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < kOvrBatch; ++j) {
+    if (j < nb) {
+      const uint32_t s = warp_sum(npos[j]);
+      const uint32_t anyneg = __any_sync(kFull, (negmask >> j) & 1u);
+      if (lane == 0) {
+        RankScalars* sc = reinterpret_cast<RankScalars*>(scratch0 + (size_t)j * plan_stride + off_scal);
+        if (s) atomicAdd(&sc->positives, (unsigned long long)s);
+        if (anyneg) atomicOr(&sc->flags, (uint32_t)TE_RANK_FLAG_NEGATIVE_SCORE);
+      }
+    }
+  }
+  (void)badmask;
 }
 
 }  // namespace
@@ -1244,23 +1413,60 @@ extern "C" size_t te_rank_pack_scratch_bytes(int64_t n) {
   return make_plan(n, false, false, false).total;
 }
 
+static int fill_splitters(SplitterDigit& dop, const uint32_t* splitters_host, int32_t num_splitters) {
+  if (num_splitters < 0 || num_splitters > kMaxSplitters) return TE_ERR_INVALID_ARGUMENT;
+  if (num_splitters > 0 && !splitters_host) return TE_ERR_INVALID_ARGUMENT;
+  dop = SplitterDigit{};
+  dop.nsp = num_splitters;
+  for (int i = 0; i < num_splitters; ++i) {
+    if (i > 0 && splitters_host[i] < splitters_host[i - 1]) return TE_ERR_INVALID_ARGUMENT;
+    dop.sp[i] = splitters_host[i];
+  }
+  return TE_OK;
+}
+
+template <typename TargetT>
+static void launch_pack(const float* score, const void* target, const RankPlan& p, const SplitterDigit& dop,
+                        uint32_t* keys_out, void* scratch, int sms, cudaStream_t st) {
+  const uint32_t ngroups = (p.n + 3) / 4;
+  uint32_t grid = (ngroups + 1023) / 1024;
+  if (grid > (uint32_t)sms * 2) grid = sms * 2;
+  const bool vec_ok = ((((uintptr_t)score) | ((uintptr_t)target)) & 15) == 0;
+  pack_bucket_kernel<TargetT><<<grid, 1024, 0, st>>>(score, (const TargetT*)target, p.n, vec_ok, dop, keys_out,
+                                                     at<uint32_t>(scratch, p.off_hist),
+                                                     at<RankScalars>(scratch, p.off_scal));
+}
+
 extern "C" int te_rank_pack(const float* score, const void* target, int32_t target_dtype, int64_t n,
-                            uint32_t* keys_out, int64_t* info, void* scratch, size_t scratch_bytes,
+                            const uint32_t* splitters_host, int32_t num_splitters, uint32_t* keys_out,
+                            int64_t* info, int64_t* counts, void* scratch, size_t scratch_bytes,
                             void* stream) {
   if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
-  if (!info || (n > 0 && (!score || !target || !keys_out))) return TE_ERR_INVALID_ARGUMENT;
+  if (!info || !counts || (n > 0 && (!score || !target || !keys_out))) return TE_ERR_INVALID_ARGUMENT;
   if (((uintptr_t)keys_out & 15) != 0) return TE_ERR_INVALID_ARGUMENT;
+  SplitterDigit dop;
+  const int rs = fill_splitters(dop, splitters_host, num_splitters);
+  if (rs) return rs;
   const RankPlan p = make_plan(n, false, false, false);
   if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
   cudaStream_t st = (cudaStream_t)stream;
   int sms = 0;
   TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
-  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
+  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.off_scal + 256 - p.off_zero, st));
   if (n > 0) {
-    const int rc = launch_ingest_dtype<kPacked>(score, target, target_dtype, p, keys_out, nullptr, scratch, sms, st);
-    if (rc) return rc;
+    TE_PROF("pack_bucket", st);
+    switch (target_dtype) {
+      case TE_DTYPE_I64: launch_pack<long long>(score, target, p, dop, keys_out, scratch, sms, st); break;
+      case TE_DTYPE_I32: launch_pack<int>(score, target, p, dop, keys_out, scratch, sms, st); break;
+      case TE_DTYPE_U8: launch_pack<unsigned char>(score, target, p, dop, keys_out, scratch, sms, st); break;
+      case TE_DTYPE_F32: launch_pack<float>(score, target, p, dop, keys_out, scratch, sms, st); break;
+      case TE_DTYPE_F64: launch_pack<double>(score, target, p, dop, keys_out, scratch, sms, st); break;
+      default: return TE_ERR_INVALID_ARGUMENT;
+    }
+    TE_LAUNCH_CHECK();
   }
   rank_info_kernel<<<1, 32, 0, st>>>(at<RankScalars>(scratch, p.off_scal), (long long*)info);
+  copy_counts_kernel<<<1, 32, 0, st>>>(at<uint32_t>(scratch, p.off_hist), (long long*)counts, num_splitters + 1);
   TE_LAUNCH_CHECK();
   return TE_OK;
 }
@@ -1268,19 +1474,15 @@ extern "C" int te_rank_pack(const float* score, const void* target, int32_t targ
 extern "C" size_t te_partition_u32_scratch_bytes(int64_t n) { return te_rank_pack_scratch_bytes(n); }
 
 extern "C" int te_partition_u32(const uint32_t* keys_in, int64_t n, const uint32_t* splitters_host,
-                                int32_t num_splitters, uint32_t* keys_out, int64_t* counts,
-                                void* scratch, size_t scratch_bytes, void* stream) {
+                                int32_t num_splitters, const int64_t* counts_in, uint32_t* keys_out,
+                                int64_t* counts, void* scratch, size_t scratch_bytes, void* stream) {
   if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
-  if (num_splitters < 0 || num_splitters > kMaxSplitters || !counts) return TE_ERR_INVALID_ARGUMENT;
-  if (num_splitters > 0 && !splitters_host) return TE_ERR_INVALID_ARGUMENT;
+  if (!counts) return TE_ERR_INVALID_ARGUMENT;
   if (n > 0 && (!keys_in || !keys_out)) return TE_ERR_INVALID_ARGUMENT;
   if (((uintptr_t)keys_in & 15) != 0) return TE_ERR_INVALID_ARGUMENT;
-  SplitterDigit dop{};
-  dop.nsp = num_splitters;
-  for (int i = 0; i < num_splitters; ++i) {
-    if (i > 0 && splitters_host[i] < splitters_host[i - 1]) return TE_ERR_INVALID_ARGUMENT;
-    dop.sp[i] = splitters_host[i];
-  }
+  SplitterDigit dop;
+  const int rs = fill_splitters(dop, splitters_host, num_splitters);
+  if (rs) return rs;
   const RankPlan p = make_plan(n, false, false, false);
   if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
   cudaStream_t st = (cudaStream_t)stream;
@@ -1288,7 +1490,9 @@ extern "C" int te_partition_u32(const uint32_t* keys_in, int64_t n, const uint32
   TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
   TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
   uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
-  if (n > 0) {
+  if (counts_in) {  // bucket sizes already known (te_rank_pack computed them)
+    counts_to_hist_kernel<<<1, 32, 0, st>>>((const long long*)counts_in, hist, num_splitters + 1);
+  } else if (n > 0) {
     TE_PROF("bucket_hist", st);
     const uint32_t ngroups = (p.n + 3) / 4;
     uint32_t grid = (ngroups + 1023) / 1024;
@@ -1355,6 +1559,61 @@ extern "C" int te_debug_phase_stats(uint64_t* out8, int reset) {
   if (reset) {
     unsigned long long z[8] = {};
     TE_CUDA_TRY(cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z)));
+  }
+  return TE_OK;
+}
+
+extern "C" size_t te_ovr_rank_scratch_bytes(int64_t n) {
+  if (n < 0 || n > 0x7fffffffLL) return 0;
+  return align_up(make_plan(n, false, true, true).total, 256) * kOvrBatch;
+}
+
+extern "C" int te_ovr_rank(const float* input, int64_t ld, const int64_t* target, int64_t target_ld,
+                           int64_t n, int32_t num_classes, int32_t multilabel, int32_t mode, double* out,
+                           void* scratch, size_t scratch_bytes, void* stream) {
+  if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  if (num_classes < 1 || !out || (mode != 0 && mode != 1) || ld < num_classes) return TE_ERR_INVALID_ARGUMENT;
+  if (n > 0 && (!input || !target)) return TE_ERR_INVALID_ARGUMENT;
+  if (multilabel && target_ld < num_classes) return TE_ERR_INVALID_ARGUMENT;
+  const RankPlan p = make_plan(n, false, true, true);
+  const size_t stride = align_up(p.total, 256);
+  if (!scratch || scratch_bytes < stride * kOvrBatch) return TE_ERR_SCRATCH_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  const size_t smem = (size_t)kOvrBatch * 4 * kRadix * sizeof(uint32_t);
+  char* base = static_cast<char*>(scratch);
+  for (int c0 = 0; c0 < num_classes; c0 += kOvrBatch) {
+    const int nb = num_classes - c0 < kOvrBatch ? num_classes - c0 : kOvrBatch;
+    for (int j = 0; j < nb; ++j)
+      TE_CUDA_TRY(cudaMemsetAsync(base + (size_t)j * stride + p.off_zero, 0, p.zero_bytes, st));
+    if (n > 0) {
+      const bool vec_ok = (((uintptr_t)input) & 15) == 0 && (ld % 4) == 0 && (c0 % 4) == 0;
+      int64_t want = (n + kOvrBlock - 1) / kOvrBlock;
+      const int grid = (int)(want < (int64_t)sms * 2 ? want : (int64_t)sms * 2);
+      TE_PROF("ovr_ingest", st);
+      if (multilabel) {
+        TE_CUDA_TRY(cudaFuncSetAttribute(ovr_ingest_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ovr_ingest_kernel<true><<<grid, kOvrBlock, smem, st>>>(input, ld, (const long long*)target, target_ld, p.n, c0,
+                                                                 nb, vec_ok, base, stride, p.off_keys_a, p.off_hist, p.off_scal);
+      } else {
+        TE_CUDA_TRY(cudaFuncSetAttribute(ovr_ingest_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ovr_ingest_kernel<false><<<grid, kOvrBlock, smem, st>>>(input, ld, (const long long*)target, target_ld, p.n, c0,
+                                                                  nb, vec_ok, base, stride, p.off_keys_a, p.off_hist, p.off_scal);
+      }
+      TE_LAUNCH_CHECK();
+    }
+    for (int j = 0; j < nb; ++j) {
+      void* sj = base + (size_t)j * stride;
+      uint32_t* ka = at<uint32_t>(sj, p.off_keys_a);
+      uint32_t* kb = at<uint32_t>(sj, p.off_keys_b);
+      if (n > 0) {
+        const int rc = run_passes(p, sj, ka, kb, ka, nullptr, nullptr, nullptr, st);
+        if (rc) return rc;
+      }
+      const int rc = finish_packed(p, ka, mode, out + (size_t)(c0 + j) * 8, sj, sms, st);
+      if (rc) return rc;
+    }
   }
   return TE_OK;
 }

@@ -42,8 +42,8 @@ struct SplitterDigit {
   int nsp;
   __device__ __forceinline__ uint32_t operator()(uint32_t k) const {
     uint32_t b = 0;
-#pragma unroll
-    for (int i = 0; i < kMaxSplitters; ++i) b += (i < nsp && sp[i] <= k) ? 1u : 0u;
+#pragma unroll 1
+    for (int i = 0; i < nsp; ++i) b += sp[i] <= k ? 1u : 0u;  // nsp = ranks - 1, usually 1..7
     return b;
   }
 };

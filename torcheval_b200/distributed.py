@@ -34,12 +34,12 @@ class _LocalKernels:
     """Kernel-backed local steps (CUDA tensors in, CUDA tensors out)."""
 
     @staticmethod
-    def pack(score: torch.Tensor, target: torch.Tensor):
-        return ops.rank_pack(score, target)
+    def pack(score: torch.Tensor, target: torch.Tensor, splitters):
+        return ops.rank_pack(score, target, splitters)
 
     @staticmethod
-    def partition(keys: torch.Tensor, splitters):
-        return ops.partition_u32(keys, splitters)
+    def partition(keys: torch.Tensor, splitters, counts):
+        return ops.partition_u32(keys, splitters, counts)
 
     @staticmethod
     def auroc_from_keys(keys: torch.Tensor) -> torch.Tensor:
@@ -49,17 +49,13 @@ class _LocalKernels:
 _local = _LocalKernels
 
 
-def _as_u32_list(t: torch.Tensor):
-    return [int(v) & 0xFFFFFFFF for v in t.tolist()]
-
-
 def choose_splitters(samples_sorted, world: int):
     """W-1 ascending splitters from the sorted pool of sampled keys; label bit cleared so that
     both labels of one score compare alike."""
     m = len(samples_sorted)
     out = []
     for i in range(1, world):
-        v = samples_sorted[min(m - 1, (i * m) // world)] if m else 0
+        v = int(samples_sorted[min(m - 1, (i * m) // world)]) if m else 0
         out.append(v & 0xFFFFFFFE)
     return out
 
@@ -79,61 +75,69 @@ def combine_rank_stats(stats):
     return auroc, P, N, u2
 
 
+def _gather_rows(t: torch.Tensor, world: int, group) -> torch.Tensor:
+    out = torch.empty((world,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+    dist.all_gather_into_tensor(out.view(-1), t.contiguous().view(-1), group=group) if t.is_cuda else dist.all_gather(
+        list(out.unbind(0)), t.contiguous(), group=group
+    )
+    return out
+
+
 def sharded_binary_auroc(
     score: torch.Tensor, target: torch.Tensor, group: Optional[dist.ProcessGroup] = None
 ) -> torch.Tensor:
     """AUROC of the union of all ranks' (score, target) shards; float64[8] on score.device:
     [auroc, P, N, 2U, flags, n_received_here, 0, 0].  flags != 0 (negative scores / soft labels
-    somewhere) means the packed representation does not apply and [0] is not valid."""
+    somewhere) means the packed representation does not apply and [0] is not valid.
+    Three host round trips in total: splitters, bucket sizes, per-rank statistics."""
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = score.device
-    keys, info = _local.pack(score, target)
+    n = score.numel()
 
-    # --- splitters from regular samples ------------------------------------------------
-    n = keys.numel()
+    # --- splitters from regular samples of the raw scores (key space: float bits << 1) -------
     s = SAMPLES_PER_RANK
     if n > 0:
         idx = torch.div(torch.arange(s, device=dev, dtype=torch.int64) * n, s, rounding_mode="floor")
-        mine = keys[idx]
+        bits = score.contiguous().view(torch.int32)[idx].to(torch.int64) & 0xFFFFFFFF
+        smp = (bits << 1) & 0xFFFFFFFF
     else:
-        mine = torch.zeros(s, dtype=keys.dtype, device=dev)
-    # header: [n, flags] travels with the samples so that one collective does it all
-    head = torch.stack([torch.tensor(n, device=dev, dtype=torch.int64), info[1]]).to(torch.int32)
-    msg = torch.cat([head, mine])
-    gathered = [torch.empty_like(msg) for _ in range(world)]
-    dist.all_gather(gathered, msg, group=group)
-    pool, flags = [], 0
-    for g in gathered:
-        h = g[:2].tolist()
-        flags |= int(h[1])
-        if h[0] > 0:
-            pool.extend(_as_u32_list(g[2:]))
+        smp = torch.zeros(s, dtype=torch.int64, device=dev)
+    msg = torch.cat([torch.tensor([n], dtype=torch.int64, device=dev), smp])
+    rows = _gather_rows(msg, world, group)
+    pool = rows[rows[:, 0] > 0][:, 1:].reshape(-1)
+    pool, _ = torch.sort(pool)
+    m = pool.numel()
+    if m:
+        pick = torch.tensor([min(m - 1, (i * m) // world) for i in range(1, world)], dtype=torch.int64, device=dev)
+        splitters = [int(v) & 0xFFFFFFFE for v in pool[pick].tolist()]
+    else:
+        splitters = [0] * (world - 1)
+
+    # --- pack (+ bucket sizes), exchange sizes and flags --------------------------------------
+    keys, info, counts = _local.pack(score, target, splitters)
+    rows = _gather_rows(torch.cat([counts, info[1:2]]), world, group).tolist()
+    flags = 0
+    for r in rows:
+        flags |= int(r[world])
     if flags:
         out = torch.zeros(8, dtype=torch.float64, device=dev)
         out[4] = float(flags)
         return out
-    pool.sort()
-    splitters = choose_splitters(pool, world)
+    send = [int(c) for c in rows[rank][:world]]
+    recv = [int(rows[q][rank]) for q in range(world)]
 
-    # --- partition + exchange -----------------------------------------------------------
-    part, counts = _local.partition(keys, splitters)
-    all_counts = [torch.empty_like(counts) for _ in range(world)]
-    dist.all_gather(all_counts, counts, group=group)
-    send = [int(c) for c in counts.tolist()]
-    recv = [int(c[rank].item()) for c in all_counts]
+    # --- partition + all-to-all ----------------------------------------------------------------
+    part, _ = _local.partition(keys, splitters, counts)
     inbox = torch.empty(sum(recv), dtype=keys.dtype, device=dev)
     dist.all_to_all_single(inbox, part, recv, send, group=group)
 
-    # --- local sort + integrate, then the 3-integer fix-up ------------------------------
+    # --- local sort + integrate, then the 3-integer fix-up -------------------------------------
     loc = _local.auroc_from_keys(inbox)
     st = torch.stack([loc[1], loc[2], loc[5], loc[6]]).to(torch.int64)
-    all_st = [torch.empty_like(st) for _ in range(world)]
-    dist.all_gather(all_st, st, group=group)
     stats = []
-    for t in all_st:
-        p_r, n_r, hi, lo = (int(v) for v in t.tolist())
-        stats.append((p_r, n_r, (hi << 32) | lo))
+    for p_r, n_r, hi, lo in _gather_rows(st, world, group).tolist():
+        stats.append((int(p_r), int(n_r), (int(hi) << 32) | int(lo)))
     auroc, P, N, u2 = combine_rank_stats(stats)
     return torch.tensor([auroc, P, N, float(u2), 0.0, float(inbox.numel()), 0.0, 0.0], dtype=torch.float64, device=dev)
 

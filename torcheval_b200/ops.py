@@ -307,27 +307,62 @@ def sort_u32(keys: torch.Tensor, vals: Optional[torch.Tensor] = None) -> Tuple[t
     return out_k, out_v
 
 
+def ovr_rank(input: torch.Tensor, target: torch.Tensor, multilabel: bool, mode: int) -> torch.Tensor:
+    """One-vs-rest AUROC (mode 0) / AUPRC (mode 1) of an (n, C) float32 matrix; float64 [C, 8],
+    row c = [value, #pos, #neg, raw, flags, ...] as te_binary_auroc."""
+    lib = N.load()
+    dev = _require_cuda(input, target)
+    assert input.dim() == 2 and input.dtype == torch.float32 and target.dtype == torch.int64
+    if input.stride(1) != 1:
+        input = input.contiguous()
+    target = target.contiguous()
+    n, C = input.shape
+    assert target.shape == ((n, C) if multilabel else (n,))
+    out = torch.empty((C, 8), dtype=torch.float64, device=dev)
+    scratch = _scratch(lib.te_ovr_rank_scratch_bytes(n), dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_ovr_rank",
+            lib.te_ovr_rank(input.data_ptr(), input.stride(0), target.data_ptr(), C if multilabel else 0, n, C,
+                            1 if multilabel else 0, mode, out.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
+        )
+    return out
+
+
 # ----------------------------------------------------------------------------- distributed pieces
-def rank_pack(score: torch.Tensor, target: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
-    """(packed keys as int32 tensor [n], info int64[2] = {#positives, flags})."""
+def _host_splitters(splitters):
+    import ctypes
+
+    nsp = len(splitters)
+    return (ctypes.c_uint32 * max(nsp, 1))(*[int(v) & 0xFFFFFFFF for v in splitters]), nsp
+
+
+def rank_pack(score: torch.Tensor, target: torch.Tensor, splitters=()):
+    """(packed keys as int32 tensor [n], info int64[2] = {#positives, flags}, bucket sizes
+    int64[len(splitters) + 1])."""
+    import ctypes
+
     lib = N.load()
     dev = _require_cuda(score, target)
     assert score.dim() == 1 and score.shape == target.shape and score.dtype == torch.float32
     score, target = score.contiguous(), target.contiguous()
     n = score.numel()
+    sp, nsp = _host_splitters(splitters)
     keys = torch.empty(n, dtype=torch.int32, device=dev)
     info = torch.zeros(2, dtype=torch.int64, device=dev)
+    counts = torch.zeros(nsp + 1, dtype=torch.int64, device=dev)
     scratch = _scratch(lib.te_rank_pack_scratch_bytes(n), dev)
     with torch.cuda.device(dev):
         N.check(
             "te_rank_pack",
-            lib.te_rank_pack(score.data_ptr(), target.data_ptr(), _DTYPE_CODE[target.dtype], n, keys.data_ptr(),
-                             info.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
+            lib.te_rank_pack(score.data_ptr(), target.data_ptr(), _DTYPE_CODE[target.dtype], n,
+                             ctypes.cast(sp, ctypes.c_void_p), nsp, keys.data_ptr(), info.data_ptr(),
+                             counts.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
         )
-    return keys, info
+    return keys, info, counts
 
 
-def partition_u32(keys: torch.Tensor, splitters) -> Tuple[torch.Tensor, torch.Tensor]:
+def partition_u32(keys: torch.Tensor, splitters, counts_in: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
     """Stable partition of uint32 keys (int32 tensor) by ascending host-side splitters; returns
     (keys grouped by bucket, int64 bucket counts [len(splitters) + 1])."""
     import ctypes
@@ -336,16 +371,15 @@ def partition_u32(keys: torch.Tensor, splitters) -> Tuple[torch.Tensor, torch.Te
     dev = _require_cuda(keys)
     keys = keys.contiguous()
     n = keys.numel()
-    nsp = len(splitters)
-    sp = (ctypes.c_uint32 * max(nsp, 1))(*[int(v) & 0xFFFFFFFF for v in splitters])
+    sp, nsp = _host_splitters(splitters)
     out = torch.empty_like(keys)
     counts = torch.zeros(nsp + 1, dtype=torch.int64, device=dev)
     scratch = _scratch(lib.te_partition_u32_scratch_bytes(n), dev)
     with torch.cuda.device(dev):
         N.check(
             "te_partition_u32",
-            lib.te_partition_u32(keys.data_ptr(), n, ctypes.cast(sp, ctypes.c_void_p), nsp, out.data_ptr(),
-                                 counts.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
+            lib.te_partition_u32(keys.data_ptr(), n, ctypes.cast(sp, ctypes.c_void_p), nsp, _ptr(counts_in),
+                                 out.data_ptr(), counts.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
         )
     return out, counts
 
