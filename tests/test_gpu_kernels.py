@@ -487,7 +487,7 @@ def test_ovr_rank_vs_oracle(ops, n, C):
     a2 = ops.ovr_rank(dev(wide)[:, :C], dev(y), False, 0).cpu().numpy()
     np.testing.assert_array_equal(a2[:, 0], a[:, 0])
     x2 = x.copy()
-    x2[:, 0] -= 0.5
+    x2[:, 0] -= 2.0
     a3 = ops.ovr_rank(dev(x2), dev(y), False, 0).cpu().numpy()
     assert a3[0, 4] == 2 and (a3[1:, 4] == 0).all()
     np.testing.assert_array_equal(a3[1:, 0], a[1:, 0])

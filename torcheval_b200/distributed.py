@@ -30,6 +30,32 @@ from . import ops
 SAMPLES_PER_RANK = 4096
 
 
+class _PhaseTimer:
+    """TE_B200_DIST_TIMING=1: print the wall time of every phase (with device syncs; debugging only)."""
+
+    def __init__(self, dev):
+        import os
+        import time
+
+        self.on = os.environ.get("TE_B200_DIST_TIMING") == "1"
+        self.dev, self.t, self.time, self.rows = dev, None, time, []
+        if self.on:
+            torch.cuda.synchronize(dev) if dev.type == "cuda" else None
+            self.t = time.perf_counter()
+
+    def mark(self, name):
+        if not self.on:
+            return
+        torch.cuda.synchronize(self.dev) if self.dev.type == "cuda" else None
+        now = self.time.perf_counter()
+        self.rows.append((name, (now - self.t) * 1e3))
+        self.t = now
+
+    def done(self, rank):
+        if self.on and rank == 0:
+            print("[sharded_binary_auroc] " + "  ".join(f"{n}={ms:.2f}ms" for n, ms in self.rows), flush=True)
+
+
 class _LocalKernels:
     """Kernel-backed local steps (CUDA tensors in, CUDA tensors out)."""
 
@@ -94,6 +120,7 @@ def sharded_binary_auroc(
     rank = dist.get_rank(group)
     dev = score.device
     n = score.numel()
+    tm = _PhaseTimer(dev)
 
     # --- splitters from regular samples of the raw scores (key space: float bits << 1) -------
     s = SAMPLES_PER_RANK
@@ -114,8 +141,10 @@ def sharded_binary_auroc(
     else:
         splitters = [0] * (world - 1)
 
+    tm.mark("splitters")
     # --- pack (+ bucket sizes), exchange sizes and flags --------------------------------------
     keys, info, counts = _local.pack(score, target, splitters)
+    tm.mark("pack")
     rows = _gather_rows(torch.cat([counts, info[1:2]]), world, group).tolist()
     flags = 0
     for r in rows:
@@ -127,18 +156,24 @@ def sharded_binary_auroc(
     send = [int(c) for c in rows[rank][:world]]
     recv = [int(rows[q][rank]) for q in range(world)]
 
+    tm.mark("sizes")
     # --- partition + all-to-all ----------------------------------------------------------------
     part, _ = _local.partition(keys, splitters, counts)
+    tm.mark("partition")
     inbox = torch.empty(sum(recv), dtype=keys.dtype, device=dev)
     dist.all_to_all_single(inbox, part, recv, send, group=group)
+    tm.mark("all_to_all")
 
     # --- local sort + integrate, then the 3-integer fix-up -------------------------------------
     loc = _local.auroc_from_keys(inbox)
+    tm.mark("local_sort_sweep")
     st = torch.stack([loc[1], loc[2], loc[5], loc[6]]).to(torch.int64)
     stats = []
     for p_r, n_r, hi, lo in _gather_rows(st, world, group).tolist():
         stats.append((int(p_r), int(n_r), (int(hi) << 32) | int(lo)))
     auroc, P, N, u2 = combine_rank_stats(stats)
+    tm.mark("fixup")
+    tm.done(rank)
     return torch.tensor([auroc, P, N, float(u2), 0.0, float(inbox.numel()), 0.0, 0.0], dtype=torch.float64, device=dev)
 
 
