@@ -237,6 +237,16 @@ TE_API size_t te_partition_u32_scratch_bytes(int64_t n);
 TE_API int te_partition_u32(const uint32_t* keys_in, int64_t n, const uint32_t* splitters_host,
                             int32_t num_splitters, const int64_t* counts_in, uint32_t* keys_out,
                             int64_t* counts, void* scratch, size_t scratch_bytes, void* stream);
+/* Partition fused with the exchange: bucket b is not written to a local array but straight to
+ * dest_ptrs_host[b] (HOST array of num_splitters + 1 device addresses), typically the peer-mapped
+ * inbox of rank b (NVLink P2P stores).  dest_ptrs_host[b] must be the address such that
+ * element (exclusive bucket offset of b in a contiguous layout + i) is the i-th key of bucket b,
+ * i.e. inbox_b + slot_of_this_rank - sum(counts[0..b-1]) elements.  The caller synchronises the
+ * ranks before the inboxes are read. */
+TE_API int te_partition_scatter_u32(const uint32_t* keys_in, int64_t n, const uint32_t* splitters_host,
+                                    int32_t num_splitters, const int64_t* counts_in,
+                                    const uint64_t* dest_ptrs_host, int64_t* counts, void* scratch,
+                                    size_t scratch_bytes, void* stream);
 TE_API int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, double* out, void* scratch,
                                      size_t scratch_bytes, void* stream);
 

@@ -49,6 +49,7 @@ SIGNATURES = {
     "te_rank_pack": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
     "te_partition_u32_scratch_bytes": (_sz, [_i64]),
     "te_partition_u32": (C.c_int, [_vp, _i64, _vp, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "te_partition_scatter_u32": (C.c_int, [_vp, _i64, _vp, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
     "te_binary_auroc_from_keys": (C.c_int, [_vp, _i64, _vp, _vp, _sz, _vp]),
     "te_sort_u32_scratch_bytes": (_sz, [_i64, _i32]),
     "te_sort_u32": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _sz, _vp]),

@@ -625,7 +625,7 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   const int block = p.sort_block;
   const size_t smem = block == 256 ? onesweep_smem_bytes<uint32_t, 256>() : onesweep_smem_bytes<uint32_t, 512>();
   using PassFn = void (*)(const uint32_t*, uint32_t*, const uint32_t*, uint32_t*, uint32_t,
-                          const RadixDigit, const uint32_t*, uint32_t*, uint32_t*);
+                          const RadixDigit, const uint32_t*, uint32_t*, uint32_t*, const PeerPtrs);
   PassFn fn = nullptr;
   if (v_in0)
     fn = block == 256 ? onesweep_pass_kernel<uint32_t, true, 256, RadixDigit>
@@ -650,7 +650,7 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
     TE_PROF(v_in0 ? "onesweep_pass_pairs" : "onesweep_pass_keys", st);
     fn<<<p.sort_tiles, block, smem_used, st>>>(kin, kout, vin, vout, p.n, RadixDigit{8 * pass},
                                                hist + pass * kRadix, lbp,
-                                               lbp + (size_t)p.sort_tiles * kRadix);
+                                               lbp + (size_t)p.sort_tiles * kRadix, PeerPtrs{});
     TE_LAUNCH_CHECK();
     kin = kout;
     vin = vout;
@@ -1473,16 +1473,20 @@ extern "C" int te_rank_pack(const float* score, const void* target, int32_t targ
 
 extern "C" size_t te_partition_u32_scratch_bytes(int64_t n) { return te_rank_pack_scratch_bytes(n); }
 
-extern "C" int te_partition_u32(const uint32_t* keys_in, int64_t n, const uint32_t* splitters_host,
-                                int32_t num_splitters, const int64_t* counts_in, uint32_t* keys_out,
-                                int64_t* counts, void* scratch, size_t scratch_bytes, void* stream) {
+static int partition_impl(const uint32_t* keys_in, int64_t n, const uint32_t* splitters_host,
+                          int32_t num_splitters, const int64_t* counts_in, uint32_t* keys_out,
+                          const uint64_t* peer_ptrs_host, int64_t* counts, void* scratch,
+                          size_t scratch_bytes, void* stream) {
   if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
   if (!counts) return TE_ERR_INVALID_ARGUMENT;
-  if (n > 0 && (!keys_in || !keys_out)) return TE_ERR_INVALID_ARGUMENT;
+  if (n > 0 && (!keys_in || (!keys_out && !peer_ptrs_host))) return TE_ERR_INVALID_ARGUMENT;
   if (((uintptr_t)keys_in & 15) != 0) return TE_ERR_INVALID_ARGUMENT;
   SplitterDigit dop;
   const int rs = fill_splitters(dop, splitters_host, num_splitters);
   if (rs) return rs;
+  PeerPtrs pp{};
+  if (peer_ptrs_host)
+    for (int b = 0; b <= num_splitters; ++b) pp.p[b] = peer_ptrs_host[b];
   const RankPlan p = make_plan(n, false, false, false);
   if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
   cudaStream_t st = (cudaStream_t)stream;
@@ -1508,24 +1512,43 @@ extern "C" int te_partition_u32(const uint32_t* keys_in, int64_t n, const uint32
     digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 1);
   }
   TE_LAUNCH_CHECK();
-  TE_PROF("onesweep_partition", st);
+  uint32_t* lb = at<uint32_t>(scratch, p.off_lookback);
+  uint32_t* gp = lb + (size_t)p.sort_tiles * kRadix;
+  const bool peer = peer_ptrs_host != nullptr;
+  TE_PROF(peer ? "onesweep_partition_peer" : "onesweep_partition", st);
+#define TE_LAUNCH_PART(B, PEER)                                                                          \
+  do {                                                                                                   \
+    auto fn = onesweep_pass_kernel<uint32_t, false, B, SplitterDigit, kSortIptDefault, PEER>;            \
+    const size_t smem = onesweep_smem_bytes<uint32_t, B>();                                              \
+    TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
+    fn<<<p.sort_tiles, B, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist, lb, gp, pp);  \
+  } while (0)
+  if (p.sort_ipt != kSortIptDefault) return TE_ERR_UNSUPPORTED;
   if (p.sort_block == 256) {
-    auto fn = onesweep_pass_kernel<uint32_t, false, 256, SplitterDigit>;
-    const size_t smem = onesweep_smem_bytes<uint32_t, 256>();
-    TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    fn<<<p.sort_tiles, 256, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist,
-                                        at<uint32_t>(scratch, p.off_lookback),
-                                        at<uint32_t>(scratch, p.off_lookback) + (size_t)p.sort_tiles * kRadix);
+    if (peer) TE_LAUNCH_PART(256, true); else TE_LAUNCH_PART(256, false);
   } else {
-    auto fn = onesweep_pass_kernel<uint32_t, false, 512, SplitterDigit>;
-    const size_t smem = onesweep_smem_bytes<uint32_t, 512>();
-    TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    fn<<<p.sort_tiles, 512, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist,
-                                        at<uint32_t>(scratch, p.off_lookback),
-                                        at<uint32_t>(scratch, p.off_lookback) + (size_t)p.sort_tiles * kRadix);
+    if (peer) TE_LAUNCH_PART(512, true); else TE_LAUNCH_PART(512, false);
   }
+#undef TE_LAUNCH_PART
   TE_LAUNCH_CHECK();
   return TE_OK;
+}
+
+extern "C" int te_partition_u32(const uint32_t* keys_in, int64_t n, const uint32_t* splitters_host,
+                                int32_t num_splitters, const int64_t* counts_in, uint32_t* keys_out,
+                                int64_t* counts, void* scratch, size_t scratch_bytes, void* stream) {
+  if (n > 0 && !keys_out) return TE_ERR_INVALID_ARGUMENT;
+  return partition_impl(keys_in, n, splitters_host, num_splitters, counts_in, keys_out, nullptr, counts,
+                        scratch, scratch_bytes, stream);
+}
+
+extern "C" int te_partition_scatter_u32(const uint32_t* keys_in, int64_t n, const uint32_t* splitters_host,
+                                        int32_t num_splitters, const int64_t* counts_in,
+                                        const uint64_t* dest_ptrs_host, int64_t* counts, void* scratch,
+                                        size_t scratch_bytes, void* stream) {
+  if (!dest_ptrs_host) return TE_ERR_INVALID_ARGUMENT;
+  return partition_impl(keys_in, n, splitters_host, num_splitters, counts_in, nullptr, dest_ptrs_host, counts,
+                        scratch, scratch_bytes, stream);
 }
 
 extern "C" int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, double* out, void* scratch,

@@ -37,6 +37,12 @@ struct RadixDigit {
 // ... or the index of the range the key falls in, given up to 15 ascending splitters
 // (bucket = #{splitters <= key}): the partition step of the distributed sample sort.
 constexpr int kMaxSplitters = 15;
+// Per-bucket output bases of a partition pass that scatters straight into other GPUs' memory:
+// p[b] is where bucket b's run starts — an address in rank b's peer-mapped inbox, already
+// shifted so that indexing with the pass's own output index lands in this rank's slot there.
+struct PeerPtrs {
+  unsigned long long p[kMaxSplitters + 1];
+};
 struct SplitterDigit {
   uint32_t sp[kMaxSplitters];
   int nsp;
@@ -102,12 +108,13 @@ constexpr size_t onesweep_smem_bytes() {
 // a tile that has not been dispatched.
 constexpr int kLbGroup = 32;
 
-template <typename KeyT, bool HAS_VAL, int kSortBlock, typename DigitOp, int kSortIpt = kSortIptDefault>
+template <typename KeyT, bool HAS_VAL, int kSortBlock, typename DigitOp, int kSortIpt = kSortIptDefault,
+          bool kPeerScatter = false>
 __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / kSortBlock)
     onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                          const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
                          uint32_t n, const DigitOp dop, const uint32_t* __restrict__ digit_base,
-                         uint32_t* lookback, uint32_t* group_prefix) {
+                         uint32_t* lookback, uint32_t* group_prefix, const PeerPtrs peers) {
   static_assert(kSortBlock >= kRadix && kSortBlock % kRadix == 0, "one thread per digit is needed");
   static_assert(kSortIpt % 4 == 0 && 16 * kSortIpt <= 256, "ranks are packed four per register");
   constexpr int GROUPS = kSortBlock / 16;
@@ -288,7 +295,12 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
     const uint32_t p = tid + k * kSortBlock;
     const KeyT kk = s_keys[p];
     const uint32_t d = dop(kk);
-    if (p < valid) keys_out[s_goff[d] + p] = kk;
+    if (p < valid) {
+      if (kPeerScatter)  // the digit is the destination rank: store over NVLink into its inbox
+        reinterpret_cast<KeyT*>(peers.p[d])[s_goff[d] + p] = kk;
+      else
+        keys_out[s_goff[d] + p] = kk;
+    }
     if (HAS_VAL) {
       if ((k & 3) == 0)
         dpack[k >> 2] = d;

@@ -75,6 +75,37 @@ class _LocalKernels:
 _local = _LocalKernels
 
 
+class _PeerInbox:
+    """Peer-mapped receive buffers (torch symmetric memory, CUDA IPC under NVLink/NVSwitch) for
+    the fused partition + exchange: every rank's partition kernel stores bucket b directly into
+    rank b's inbox, so there is no separate all-to-all and no local copy of the partitioned keys.
+    One buffer per (process group, device), grown on demand; allocation is collective."""
+
+    _cache: dict = {}
+    _broken = False
+
+    @classmethod
+    def get(cls, group, dev: torch.device, capacity: int):
+        if cls._broken or dev.type != "cuda":
+            return None
+        key = (id(group) if group is not None else 0, dev.index)
+        ent = cls._cache.get(key)
+        if ent is not None and ent[0] >= capacity:
+            return ent
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+
+            cap = ((int(capacity) + (1 << 20) - 1) >> 20) << 20
+            buf = symm_mem.empty(cap, dtype=torch.int32, device=dev)
+            hdl = symm_mem.rendezvous(buf, group if group is not None else dist.group.WORLD)
+            ent = (cap, buf, hdl, [int(p) for p in hdl.buffer_ptrs])
+            cls._cache[key] = ent
+            return ent
+        except Exception:  # noqa: BLE001 — no peer access on this system: use the NCCL exchange
+            cls._broken = True
+            return None
+
+
 def choose_splitters(samples_sorted, world: int):
     """W-1 ascending splitters from the sorted pool of sampled keys; label bit cleared so that
     both labels of one score compare alike."""
@@ -157,12 +188,31 @@ def sharded_binary_auroc(
     recv = [int(rows[q][rank]) for q in range(world)]
 
     tm.mark("sizes")
-    # --- partition + all-to-all ----------------------------------------------------------------
-    part, _ = _local.partition(keys, splitters, counts)
-    tm.mark("partition")
-    inbox = torch.empty(sum(recv), dtype=keys.dtype, device=dev)
-    dist.all_to_all_single(inbox, part, recv, send, group=group)
-    tm.mark("all_to_all")
+    # --- partition fused with the exchange (P2P stores into peer inboxes), or partition + NCCL ----
+    n_all = [sum(int(v) for v in rows[q][:world]) for q in range(world)]
+    recv_all = [sum(int(rows[q][b]) for q in range(world)) for b in range(world)]
+    peer = None
+    if dev.type == "cuda" and _local is _LocalKernels:
+        peer = _PeerInbox.get(group, dev, max(int(1.3 * max(n_all)) + 65536, 1 << 20))
+        if peer is not None and max(recv_all) > peer[0]:
+            peer = None  # a skewed split does not fit the inboxes: every rank sees that and falls back
+    if peer is not None:
+        _, buf, hdl, ptrs = peer
+        dest, excl = [], 0
+        for b in range(world):
+            slot = sum(int(rows[q][b]) for q in range(rank))  # my keys follow those of lower ranks
+            dest.append(ptrs[b] + 4 * (slot - excl))
+            excl += send[b]
+        ops.partition_scatter_u32(keys, splitters, counts, dest)
+        hdl.barrier()  # every rank's stores have landed before anybody reads its inbox
+        inbox = buf[: recv_all[rank]]
+        tm.mark("partition+p2p")
+    else:
+        part, _ = _local.partition(keys, splitters, counts)
+        tm.mark("partition")
+        inbox = torch.empty(sum(recv), dtype=keys.dtype, device=dev)
+        dist.all_to_all_single(inbox, part, recv, send, group=group)
+        tm.mark("all_to_all")
 
     # --- local sort + integrate, then the 3-integer fix-up -------------------------------------
     loc = _local.auroc_from_keys(inbox)

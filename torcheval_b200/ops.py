@@ -384,6 +384,29 @@ def partition_u32(keys: torch.Tensor, splitters, counts_in: Optional[torch.Tenso
     return out, counts
 
 
+def partition_scatter_u32(keys: torch.Tensor, splitters, counts_in: torch.Tensor, dest_ptrs) -> None:
+    """Partition `keys` by the splitters and store bucket b at device address dest_ptrs[b]
+    (+ the pass's own output index), e.g. into peer-mapped inboxes of other GPUs."""
+    import ctypes
+
+    lib = N.load()
+    dev = _require_cuda(keys, counts_in)
+    keys = keys.contiguous()
+    n = keys.numel()
+    sp, nsp = _host_splitters(splitters)
+    assert len(dest_ptrs) == nsp + 1
+    ptrs = (ctypes.c_uint64 * (nsp + 1))(*[int(p) & 0xFFFFFFFFFFFFFFFF for p in dest_ptrs])
+    counts = torch.zeros(nsp + 1, dtype=torch.int64, device=dev)
+    scratch = _scratch(lib.te_partition_u32_scratch_bytes(n), dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_partition_scatter_u32",
+            lib.te_partition_scatter_u32(keys.data_ptr(), n, ctypes.cast(sp, ctypes.c_void_p), nsp, _ptr(counts_in),
+                                         ctypes.cast(ptrs, ctypes.c_void_p), counts.data_ptr(), scratch.data_ptr(),
+                                         scratch.numel(), _stream_ptr(dev)),
+        )
+
+
 def binary_auroc_from_keys(keys: torch.Tensor) -> torch.Tensor:
     """float64[8] as te_binary_auroc_from_keys: [auroc, P, N, 2U, flags, 2U_hi32, 2U_lo32, n]."""
     lib = N.load()
