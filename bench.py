@@ -48,6 +48,17 @@ def measured_peaks() -> tuple[float, str]:
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(kernel: str, n_records: int):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture, or None when
+    the capture was taken on a different record count than this run."""
+    p = ROOT / "profiles" / "r01_ncu_traffic.json"
+    try:
+        t = json.loads(p.read_text())
+        return int(t[kernel]) if int(t["n_records"]) == int(n_records) else None
+    except Exception:
+        return None
+
+
 # ----------------------------------------------------------------------------------- clocks
 class ClockSampler:
     """Samples SM clock and throttle reasons through NVML while the timed region runs."""
@@ -231,7 +242,7 @@ def run_ours(args) -> dict:
             "peak_source": peak_src,
             "unit": "GB/s",
             "frac": round(achieved / peak_gbs, 4),
-            "traffic": None,
+            "traffic": ncu_traffic(dom, sorted_n),
             "avg_launch_ms": round(avg_ms, 4),
             "algorithmic_bytes_per_launch": 8 * sorted_n,
             "step_share": round(k["total_ms"] / (ms_total), 4),
