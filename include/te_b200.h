@@ -249,6 +249,21 @@ TE_API int te_partition_scatter_u32(const uint32_t* keys_in, int64_t n, const ui
                                     size_t scratch_bytes, void* stream);
 TE_API int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, double* out, void* scratch,
                                      size_t scratch_bytes, void* stream);
+/* Average precision of rank-sharded scores (precision is a ratio of prefix
+ * counts, so the step integral of precision_recall_curve.py:208-231 + tensor_utils.py:12-16 takes
+ * two phases around one exchange of (P_r, N_r)):
+ *  _begin : sort the keys this rank received and count; out[] as te_binary_auroc_from_keys.  The
+ *           sorted keys and the chunk states stay in `scratch`, which the caller must leave
+ *           untouched until _finish (same n, same scratch, same device).
+ *  _finish: out[3] = sum over this rank's positives of precision at their threshold, with
+ *           positives_above / samples_above = positives / samples held by the ranks whose score
+ *           ranges lie above this one (exact integers passed as doubles).  AP = sum over ranks of
+ *           out[3], divided by the global number of positives; out[1], out[2] = local P, N. */
+TE_API int te_binary_auprc_from_keys_begin(const uint32_t* keys, int64_t n, double* out, void* scratch,
+                                           size_t scratch_bytes, void* stream);
+TE_API int te_binary_auprc_from_keys_finish(int64_t n, double positives_above, double samples_above,
+                                            double* out, void* scratch, size_t scratch_bytes,
+                                            void* stream);
 
 /* The sort on its own: ascending, stable, 32-bit keys with an optional 32-bit payload
  * (vals_in/vals_out both NULL or both set).  Replaces torch.sort at auroc.py:121. */

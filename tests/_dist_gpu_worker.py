@@ -20,7 +20,10 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     rank, world = dist.get_rank(), dist.get_world_size()
     from torcheval_b200 import distributed as tdist
-    from torcheval_b200.metrics import BinaryAUROC, BinaryBinnedAUPRC, MulticlassConfusionMatrix
+    from torcheval_b200.metrics import (
+        BinaryAUPRC, BinaryAUROC, BinaryBinnedAUPRC, MulticlassAUPRC, MulticlassAUROC, MulticlassConfusionMatrix,
+        MultilabelAUPRC,
+    )
     from torcheval_b200.metrics import toolkit
 
     res = {}
@@ -40,6 +43,11 @@ def main():
         res[f"sharded/{name}"] = [float(out[0]), want, float(out[1]), tp, float(out[2]), fp]
         m = BinaryAUROC(device=dev).update(xs, ys)
         res[f"sync/{name}"] = [float(toolkit.sync_and_compute(m)), want]
+        out = tdist.sharded_binary_auprc(xs, ys).cpu().numpy()
+        want_ap = oracle.binary_auprc(x, y)
+        res[f"sharded_ap/{name}"] = [float(out[0]), want_ap, float(out[1]), tp, float(out[2]), fp]
+        ma = BinaryAUPRC(device=dev).update(xs, ys)
+        res[f"sync_ap/{name}"] = [float(toolkit.sync_and_compute(ma)), want_ap]
         mh = BinaryAUROC().update(xs.cpu(), ys.cpu())  # host-resident state, NCCL group
         res[f"sync_host/{name}"] = [float(toolkit.sync_and_compute(mh)), want]
     C = 1000
@@ -53,6 +61,20 @@ def main():
     bb = BinaryBinnedAUPRC(threshold=10000, device=dev).update(torch.from_numpy(xb[sl]).to(dev), torch.from_numpy(yb[sl]).to(dev))
     tp_, fp_, fn_ = oracle.binned_update(xb, yb, np.linspace(0, 1, 10000, dtype=np.float32))
     res["sync/binned_auprc"] = [float(toolkit.sync_and_compute(bb)[0][0]), oracle.binned_auprc_from_counts(tp_, fp_, fn_)]
+    # class-sharded transpose (one all-to-all), uneven row shards and column blocks
+    nn, CC = 50021, 13
+    xi, yi = rs.random((nn, CC), dtype=np.float32), rs.integers(0, CC, nn)
+    xi[:, 3] = np.round(xi[:, 3] * 16) / 16
+    li = rs.integers(0, 2, (nn, CC))
+    cut = [0] + [int(nn * (i + 1) / (world * 2)) for i in range(world - 1)] + [nn]
+    sl = slice(cut[rank], cut[rank + 1])
+    xd, yd, ld = torch.from_numpy(xi[sl]).to(dev), torch.from_numpy(yi[sl]).to(dev), torch.from_numpy(li[sl]).to(dev)
+    m1 = MulticlassAUROC(num_classes=CC, average=None, device=dev).update(xd, yd)
+    res["ovr/mc_auroc"] = [toolkit.sync_and_compute(m1).tolist(), oracle.multiclass_auroc(xi, yi).tolist()]
+    m2 = MulticlassAUPRC(num_classes=CC, average=None, device=dev).update(xd, yd)
+    res["ovr/mc_auprc"] = [toolkit.sync_and_compute(m2).tolist(), oracle.multiclass_auprc(xi, yi).tolist()]
+    m3 = MultilabelAUPRC(num_labels=CC, average="macro", device=dev).update(xd, ld)
+    res["ovr/ml_auprc_macro"] = [float(toolkit.sync_and_compute(m3)), float(oracle.multilabel_auprc(xi, li).mean())]
     Path(os.environ["TE_TEST_OUT"] + f".{rank}").write_text(json.dumps(res))
     dist.barrier()
     dist.destroy_process_group()

@@ -29,11 +29,24 @@ def main():
     cpu_backend.install()
     from torcheval_b200 import distributed as tdist
     from torcheval_b200.metrics import (
-        BinaryAUPRC, BinaryAUROC, BinaryBinnedAUPRC, MulticlassAccuracy, MulticlassAUROC, MulticlassConfusionMatrix,
+        BinaryAUPRC, BinaryAUROC, BinaryBinnedAUPRC, MulticlassAccuracy, MulticlassAUPRC, MulticlassAUROC,
+        MulticlassConfusionMatrix, MultilabelAUPRC,
     )
     from torcheval_b200.metrics import toolkit
 
     res = {}
+    calls = {"auprc": 0, "ovr": 0}
+    real_auprc, real_ovr = tdist.sharded_binary_auprc, tdist.class_sharded_one_vs_rest
+
+    def counting_auprc(*a, **k):
+        calls["auprc"] += 1
+        return real_auprc(*a, **k)
+
+    def counting_ovr(*a, **k):
+        calls["ovr"] += 1
+        return real_ovr(*a, **k)
+
+    tdist.sharded_binary_auprc, tdist.class_sharded_one_vs_rest = counting_auprc, counting_ovr
     rs = np.random.default_rng(7)
     n = 20011
     cases = {
@@ -57,6 +70,13 @@ def main():
         m.update(torch.from_numpy(xs[half:]), torch.from_numpy(ys[half:]))
         res[f"sync/{name}"] = [float(toolkit.sync_and_compute(m)), want]
         assert len(m.inputs) == 1  # compacted by _prepare_for_merge_state, data unchanged
+        # average precision over the same shards: two-phase integrate around the (P_r, N_r) exchange
+        out = tdist.sharded_binary_auprc(torch.from_numpy(xs), torch.from_numpy(ys))
+        res[f"sharded_ap/{name}"] = [float(out[0]), oracle.binary_auprc(x, y), float(out[1]), tp, float(out[2]), fp]
+        ma = BinaryAUPRC().update(torch.from_numpy(xs), torch.from_numpy(ys))
+        got = toolkit.sync_and_compute(ma)
+        assert got.dtype == torch.float32 and got.dim() == 0
+        res[f"sync_ap/{name}"] = [float(got), oracle.binary_auprc(x, y)]
     # negative scores: the sharded path declines on every rank, the gather path answers
     x, y = (rs.standard_normal(n) * 2).astype(np.float32), rs.integers(0, 2, n)
     m = BinaryAUROC().update(torch.from_numpy(shard(x, rank, world)), torch.from_numpy(shard(y, rank, world)))
@@ -94,6 +114,31 @@ def main():
         torch.from_numpy(xi[cut[rank]:cut[rank + 1]]), torch.from_numpy(yi[cut[rank]:cut[rank + 1]])
     )
     res["sync/mc_auroc"] = [toolkit.sync_and_compute(mm).tolist(), oracle.multiclass_auroc(xi, yi).tolist()]
+    # class-sharded transpose: more classes than ranks, uneven column blocks, macro and per-class
+    nn, CC = 1203, 7
+    xi, yi = rs.random((nn, CC), dtype=np.float32), rs.integers(0, CC, nn)
+    xi[:, 2] = np.round(xi[:, 2] * 8) / 8  # one heavily tied column
+    li = rs.integers(0, 2, (nn, CC))
+    cut = [0] + [int(nn * (i + 1) / (world * 2)) for i in range(world - 1)] + [nn]
+    sl = slice(cut[rank], cut[rank + 1])
+    for avg in ("macro", None):
+        tag = "macro" if avg else "none"
+        m1 = MulticlassAUROC(num_classes=CC, average=avg).update(torch.from_numpy(xi[sl]), torch.from_numpy(yi[sl]))
+        want = oracle.multiclass_auroc(xi, yi)
+        res[f"ovr/mc_auroc_{tag}"] = [np.atleast_1d(toolkit.sync_and_compute(m1).numpy()).tolist(), np.atleast_1d(want.mean() if avg else want).tolist()]
+        m2 = MulticlassAUPRC(num_classes=CC, average=avg).update(torch.from_numpy(xi[sl]), torch.from_numpy(yi[sl]))
+        want = oracle.multiclass_auprc(xi, yi)
+        res[f"ovr/mc_auprc_{tag}"] = [np.atleast_1d(toolkit.sync_and_compute(m2).numpy()).tolist(), np.atleast_1d(want.mean() if avg else want).tolist()]
+        m3 = MultilabelAUPRC(num_labels=CC, average=avg).update(torch.from_numpy(xi[sl]), torch.from_numpy(li[sl]))
+        want = oracle.multilabel_auprc(xi, li)
+        res[f"ovr/ml_auprc_{tag}"] = [np.atleast_1d(toolkit.sync_and_compute(m3).numpy()).tolist(), np.atleast_1d(want.mean() if avg else want).tolist()]
+    # fewer classes than ranks can happen (C=2, world=3): some rank owns no column
+    x2, y2 = rs.random((300, 2), dtype=np.float32), rs.integers(0, 2, 300)
+    m4 = MulticlassAUROC(num_classes=2, average=None).update(
+        torch.from_numpy(shard(x2, rank, world)), torch.from_numpy(shard(y2, rank, world))
+    )
+    res["ovr/two_classes"] = [toolkit.sync_and_compute(m4).tolist(), oracle.multiclass_auroc(x2, y2).tolist()]
+    res["calls"] = [calls["auprc"], calls["ovr"]]
     # a rank with no data: generic object path still works
     me = BinaryAUROC()
     if rank != 0:

@@ -198,11 +198,34 @@ def binary_auroc_from_keys(keys):
     return binary_auroc_packed(torch.from_numpy(x.copy()), torch.from_numpy(y))
 
 
+def binary_auprc_from_keys_begin(keys):
+    k = np.sort(_np(keys).view(np.uint32))
+    return binary_auroc_from_keys(keys), k
+
+
+def binary_auprc_from_keys_finish(state, positives_above, samples_above):
+    """sum over the local positives of TP/(TP+FP) at their threshold (ascending sorted keys)."""
+    k = state
+    out = torch.zeros(8, dtype=torch.float64)
+    if k.size == 0:
+        return out
+    s, y = k >> np.uint32(1), (k & np.uint32(1)).astype(np.int64)
+    n, P = k.size, int(y.sum())
+    start = np.concatenate([[True], s[1:] != s[:-1]])
+    gp = np.maximum.accumulate(np.where(start, np.arange(n), 0))  # index of my tie group's start
+    pos_before = np.concatenate([[0], np.cumsum(y)[:-1]])[gp]      # positives strictly below my score
+    tp = (P - pos_before + positives_above).astype(np.float64)
+    den = (n - gp + samples_above).astype(np.float64)
+    out[3] = float(np.sum((tp / den)[y == 1]))
+    out[1], out[2] = P, n - P
+    return out
+
+
 _NAMES = [
     "cm_update_", "cm_update_logits_", "class_counts_", "match_count", "binned_hist_update_",
     "binned_hist2d_update_", "binned_counts", "binned_integrate", "binary_auroc_packed",
     "binary_auprc_packed", "binary_auroc_general", "binary_auprc_general", "sort_u32", "rank_pack", "ovr_rank",
-    "partition_u32", "binary_auroc_from_keys",
+    "partition_u32", "binary_auroc_from_keys", "binary_auprc_from_keys_begin", "binary_auprc_from_keys_finish",
 ]
 
 

@@ -32,7 +32,11 @@ def test_sample_sort_and_toolkit_sync(world, port, tmp_path):
         assert results[k] == results[0], "every rank must return the same values"
     res = results[0]
     for key, val in res.items():
-        if key.startswith("sharded/"):
+        if key == "calls":
+            assert val[0] >= 12 and val[1] >= 8, val  # the sharded paths ran, not the gather fallback
+        elif key.startswith("ovr/"):
+            np.testing.assert_allclose(val[0], val[1], rtol=2e-6, err_msg=key)
+        elif key.startswith("sharded/") or key.startswith("sharded_ap/"):
             got, want, P, tp, N, fp = val
             np.testing.assert_allclose(got, want, rtol=1e-12, err_msg=key)
             assert (P, N) == (tp, fp), key

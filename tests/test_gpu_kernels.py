@@ -463,6 +463,75 @@ def test_rank_pack_partition_from_keys(ops):
     assert info.tolist() == [1, 2]
 
 
+@pytest.mark.parametrize("n", [1, 37, 8192, 8193, 123457, 2_000_003])
+def test_partition_scatter_to_separate_buffers(ops, n):
+    """te_partition_scatter_u32 with the buckets going to separate buffers at every 4-byte
+    misalignment (what the peer inboxes look like to the kernel), against the stable CPU partition."""
+    import cpu_backend
+
+    rs = np.random.default_rng(n)
+    x = rs.random(n, dtype=np.float32)
+    y = rs.integers(0, 2, n)
+    keys, _, _ = ops.rank_pack(dev(x), dev(y))
+    wk = keys.cpu()
+    for sp in ([], [int(0.5 * 2**31) & ~1], sorted(int(v) & ~1 for v in rs.integers(0, 2**31, 7)), [4, 4, 2**32 - 2],
+               sorted(int(v) & ~1 for v in rs.integers(0, 2**31, 15))):
+        wp, wc = cpu_backend.partition_u32(wk, sp)
+        wc = wc.tolist()
+        _, _, counts = ops.rank_pack(dev(x), dev(y), sp)
+        for slot in (0, 1, 2, 3, 5):
+            bufs = [torch.full((c + 16,), -1, dtype=torch.int32, device="cuda") for c in wc]
+            dest, excl = [], 0
+            for b, c in enumerate(wc):
+                dest.append(bufs[b].data_ptr() + 4 * (slot + (b % 3) - excl))
+                excl += c
+            ops.partition_scatter_u32(keys, sp, counts, dest)
+            torch.cuda.synchronize()
+            off = 0
+            for b, c in enumerate(wc):
+                o = slot + (b % 3)
+                got = bufs[b].cpu().numpy()
+                np.testing.assert_array_equal(got[o : o + c], wp.numpy()[off : off + c], err_msg=f"{n} {sp} {slot} {b}")
+                assert (got[:o] == -1).all() and (got[o + c :] == -1).all()  # nothing outside the run is touched
+                off += c
+
+
+@pytest.mark.parametrize("n", [1, 5, 4097, 300001, 3_000_001])
+def test_auprc_from_keys_two_phase(ops, n):
+    """te_binary_auprc_from_keys_begin/_finish: whole set == te_binary_auprc; and split at a score
+    boundary into a low and a high part, each finished with what lies above it, the two sums add
+    up to the whole (the decomposition the ranks use)."""
+    import cpu_backend
+
+    rs = np.random.default_rng(n)
+    x = (rs.integers(0, 4000, n) / 4000).astype(np.float32) if n % 2 else rs.random(n, dtype=np.float32)
+    y = rs.integers(0, 2, n)
+    keys, _, _ = ops.rank_pack(dev(x), dev(y))
+    whole = ops.binary_auprc_packed(dev(x), dev(y)).cpu().numpy()
+    loc, st = ops.binary_auprc_from_keys_begin(keys)
+    loc = loc.cpu().numpy()
+    wa = cpu_backend.binary_auroc_from_keys(keys.cpu()).numpy()
+    close(loc[0], wa[0], 1e-12)  # phase 1 also reports the AUROC of the keys
+    assert list(loc[1:3]) == list(whole[1:3])
+    fin = ops.binary_auprc_from_keys_finish(st, 0, 0).cpu().numpy()
+    P = whole[1]
+    close(fin[3] / P if P else -0.0, oracle.binary_auprc(x, y), RTOL64)
+    assert fin[3] == whole[3]  # same kernel, same order of summation
+    if n < 5:
+        return
+    cutv = np.float32(np.median(x))
+    lo, hi = x < cutv, x >= cutv
+    klo, _, _ = ops.rank_pack(dev(x[lo]), dev(y[lo]))
+    khi, _, _ = ops.rank_pack(dev(x[hi]), dev(y[hi]))
+    _, slo = ops.binary_auprc_from_keys_begin(klo)
+    _, shi = ops.binary_auprc_from_keys_begin(khi)
+    f_hi = ops.binary_auprc_from_keys_finish(shi, 0, 0).cpu().numpy()
+    f_lo = ops.binary_auprc_from_keys_finish(slo, int(y[hi].sum()), int(hi.sum())).cpu().numpy()
+    want_lo = cpu_backend.binary_auprc_from_keys_finish(np.sort(klo.cpu().numpy().view(np.uint32)), int(y[hi].sum()), int(hi.sum()))
+    close(f_lo[3], float(want_lo[3]), 1e-12)
+    close(f_lo[3] + f_hi[3], whole[3], 1e-12)
+
+
 # =============================================================================== K2: one-vs-rest
 @pytest.mark.parametrize("n,C", [(1, 3), (257, 17), (5000, 8), (40001, 13), (3000, 1000)])
 def test_ovr_rank_vs_oracle(ops, n, C):

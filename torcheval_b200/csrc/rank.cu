@@ -275,7 +275,8 @@ template <int MODE>
 __global__ void __launch_bounds__(kFinBlock)
     rank_chunk_kernel(const uint32_t* __restrict__ keys, uint32_t n, uint32_t tiles_per_chunk,
                       ChunkRec* rec, const FState* __restrict__ excl_in,
-                      const RankScalars* __restrict__ scal, unsigned long long* partial) {
+                      const RankScalars* __restrict__ scal, unsigned long long* partial,
+                      double pos_above, double cnt_above) {
   __shared__ FState s_warp[kFinBlock / kWarp];
   __shared__ unsigned long long s_red[3][kFinBlock / kWarp];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -285,7 +286,9 @@ __global__ void __launch_bounds__(kFinBlock)
   FState carry = MODE == 1 ? excl_in[chunk] : f_identity();
   unsigned long long accA = 0, accP = 0, accLead = 0;
   double accD = 0.0;
-  const double ptot = MODE == 1 ? (double)scal->positives : 0.0;
+  // pos_above / cnt_above: positives / samples with a score above everything in `keys` that live
+  // on other ranks (0 when `keys` is the whole sample set)
+  const double ptot = MODE == 1 ? (double)scal->positives + pos_above : 0.0;
 
   // register double buffering: the loads of tile t+1 are in flight while tile t is processed
   auto load_tile = [&](uint32_t tl, uint32_t (&dst)[kFinIpt], uint32_t& prev_key) {
@@ -404,7 +407,7 @@ __global__ void __launch_bounds__(kFinBlock)
           if (k[j] & 1u) {
             // precision at this tie group's threshold: TP / (TP + FP), counts of score >= s
             const double tp = ptot - (double)(gp - gs);
-            accD += tp / (double)(n - gp);
+            accD += tp / ((double)(n - gp) + cnt_above);
           } else {
             ++c;
           }
@@ -556,6 +559,14 @@ inline int sort_ipt_from_env() {
   return b;
 }
 
+inline bool unstable_first_pass_from_env() {
+  static const bool b = [] {
+    const char* e = getenv("TE_B200_UNSTABLE_FIRST");
+    return e ? atoi(e) != 0 : true;
+  }();
+  return b;
+}
+
 struct RankPlan {
   uint32_t n;
   int sort_block, sort_ipt;
@@ -643,12 +654,19 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_used));
   const uint32_t* kin = k_in0;
   const uint32_t* vin = v_in0;
+  // keys only: the first pass may hand out ranks in arrival order (see kUnstable)
+  PassFn fn_first = fn;
+  if (!v_in0 && p.sort_ipt == kSortIptDefault && unstable_first_pass_from_env()) {
+    fn_first = block == 256 ? onesweep_pass_kernel<uint32_t, false, 256, RadixDigit, kSortIptDefault, false, true>
+                            : onesweep_pass_kernel<uint32_t, false, 512, RadixDigit, kSortIptDefault, false, true>;
+    TE_CUDA_TRY(cudaFuncSetAttribute(fn_first, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_used));
+  }
   for (int pass = 0; pass < 4; ++pass) {
     uint32_t* kout = (pass & 1) ? k_y : k_x;
     uint32_t* vout = (pass & 1) ? v_y : v_x;
     uint32_t* lbp = lb + (size_t)pass * 2 * p.sort_tiles * kRadix;
-    TE_PROF(v_in0 ? "onesweep_pass_pairs" : "onesweep_pass_keys", st);
-    fn<<<p.sort_tiles, block, smem_used, st>>>(kin, kout, vin, vout, p.n, RadixDigit{8 * pass},
+    TE_PROF(v_in0 ? "onesweep_pass_pairs" : (pass == 0 && fn_first != fn ? "onesweep_pass_keys_first" : "onesweep_pass_keys"), st);
+    (pass == 0 ? fn_first : fn)<<<p.sort_tiles, block, smem_used, st>>>(kin, kout, vin, vout, p.n, RadixDigit{8 * pass},
                                                hist + pass * kRadix, lbp,
                                                lbp + (size_t)p.sort_tiles * kRadix, PeerPtrs{});
     TE_LAUNCH_CHECK();
@@ -713,7 +731,7 @@ int finish_packed(const RankPlan& p, const uint32_t* ka, int mode, double* out, 
   const uint32_t nchunks = n > 0 ? cg.nchunks : 0;
   if (nchunks) {
     TE_PROF("rank_chunk_sweep", st);
-    rank_chunk_kernel<0><<<nchunks, kFinBlock, 0, st>>>(ka, p.n, cg.tiles_per_chunk, rec, nullptr, scal, nullptr);
+    rank_chunk_kernel<0><<<nchunks, kFinBlock, 0, st>>>(ka, p.n, cg.tiles_per_chunk, rec, nullptr, scal, nullptr, 0.0, 0.0);
   }
   TE_LAUNCH_CHECK();
   if (mode == 0) {
@@ -726,7 +744,7 @@ int finish_packed(const RankPlan& p, const uint32_t* ka, int mode, double* out, 
         rank_chunk_scan_kernel<1><<<1, kMaxChunks, 0, st>>>(rec, nchunks, p.n, scal, excl, nullptr);
       }
       TE_PROF("rank_chunk_integrate", st);
-      rank_chunk_kernel<1><<<nchunks, kFinBlock, 0, st>>>(ka, p.n, cg.tiles_per_chunk, nullptr, excl, scal, partial);
+      rank_chunk_kernel<1><<<nchunks, kFinBlock, 0, st>>>(ka, p.n, cg.tiles_per_chunk, nullptr, excl, scal, partial, 0.0, 0.0);
     }
     TE_PROF("rank_reduce", st);
     rank_reduce_kernel<1><<<1, 1024, 0, st>>>(partial, nchunks, p.n, scal, out);
@@ -1485,8 +1503,14 @@ static int partition_impl(const uint32_t* keys_in, int64_t n, const uint32_t* sp
   const int rs = fill_splitters(dop, splitters_host, num_splitters);
   if (rs) return rs;
   PeerPtrs pp{};
-  if (peer_ptrs_host)
+  if (peer_ptrs_host) {
     for (int b = 0; b <= num_splitters; ++b) pp.p[b] = peer_ptrs_host[b];
+    static const int vec = [] {
+      const char* e = getenv("TE_B200_PEER_VEC");
+      return e ? atoi(e) : 1;
+    }();
+    pp.vec = vec;
+  }
   const RankPlan p = make_plan(n, false, false, false);
   if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
   cudaStream_t st = (cudaStream_t)stream;
@@ -1551,8 +1575,10 @@ extern "C" int te_partition_scatter_u32(const uint32_t* keys_in, int64_t n, cons
                         scratch, scratch_bytes, stream);
 }
 
-extern "C" int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, double* out, void* scratch,
-                                         size_t scratch_bytes, void* stream) {
+// mode 0: AUROC of the keys.  mode 1: the same, and the chunk states the AUPRC integrate sweep
+// starts from are left in `scratch` next to the sorted keys (te_binary_auprc_from_keys_finish).
+static int rank_from_keys(const uint32_t* keys, int64_t n, int mode, double* out, void* scratch,
+                          size_t scratch_bytes, void* stream) {
   if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
   if (!out || (n > 0 && !keys)) return TE_ERR_INVALID_ARGUMENT;
   if (((uintptr_t)keys & 15) != 0) return TE_ERR_INVALID_ARGUMENT;
@@ -1570,7 +1596,63 @@ extern "C" int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, double
     rc = run_passes(p, scratch, keys, ka, kb, nullptr, nullptr, nullptr, st);  // sorted keys end in kb
     if (rc) return rc;
   }
-  return finish_packed(p, kb, 0, out, scratch, sms, st);
+  const int rc = finish_packed(p, kb, 0, out, scratch, sms, st);
+  if (rc || mode == 0 || n == 0) return rc;
+  int occ = 0;
+  TE_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, rank_chunk_kernel<1>, kFinBlock, 0));
+  const ChunkGeom cg = chunk_geom(p.fin_tiles, sms, occ);
+  // the count sweep ran with the geometry of rank_chunk_kernel<0>; the integrate sweep needs its own
+  // chunk records when the two kernels' occupancies differ, so recount with that geometry
+  int occ0 = 0;
+  TE_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, rank_chunk_kernel<0>, kFinBlock, 0));
+  ChunkRec* rec = at<ChunkRec>(scratch, p.off_agg);
+  const RankScalars* scal = at<RankScalars>(scratch, p.off_scal);
+  if (chunk_geom(p.fin_tiles, sms, occ0).tiles_per_chunk != cg.tiles_per_chunk) {
+    TE_PROF("rank_chunk_sweep", st);
+    rank_chunk_kernel<0><<<cg.nchunks, kFinBlock, 0, st>>>(kb, p.n, cg.tiles_per_chunk, rec, nullptr, scal, nullptr, 0.0, 0.0);
+  }
+  TE_PROF("rank_chunk_scan", st);
+  rank_chunk_scan_kernel<1><<<1, kMaxChunks, 0, st>>>(rec, cg.nchunks, p.n, scal, at<FState>(scratch, p.off_inc), nullptr);
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+extern "C" int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, double* out, void* scratch,
+                                         size_t scratch_bytes, void* stream) {
+  return rank_from_keys(keys, n, 0, out, scratch, scratch_bytes, stream);
+}
+
+extern "C" int te_binary_auprc_from_keys_begin(const uint32_t* keys, int64_t n, double* out, void* scratch,
+                                               size_t scratch_bytes, void* stream) {
+  return rank_from_keys(keys, n, 1, out, scratch, scratch_bytes, stream);
+}
+
+extern "C" int te_binary_auprc_from_keys_finish(int64_t n, double positives_above, double samples_above,
+                                                double* out, void* scratch, size_t scratch_bytes,
+                                                void* stream) {
+  if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  if (!out || positives_above < 0.0 || samples_above < positives_above) return TE_ERR_INVALID_ARGUMENT;
+  const RankPlan p = make_plan(n, false, true, true);
+  if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  int sms = 0, occ = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  TE_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, rank_chunk_kernel<1>, kFinBlock, 0));
+  const ChunkGeom cg = chunk_geom(p.fin_tiles, sms, occ);
+  const uint32_t nchunks = n > 0 ? cg.nchunks : 0;
+  const uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
+  unsigned long long* partial = at<unsigned long long>(scratch, p.off_partial);
+  const RankScalars* scal = at<RankScalars>(scratch, p.off_scal);
+  if (nchunks) {
+    TE_PROF("rank_chunk_integrate", st);
+    rank_chunk_kernel<1><<<nchunks, kFinBlock, 0, st>>>(kb, p.n, cg.tiles_per_chunk, nullptr,
+                                                        at<FState>(scratch, p.off_inc), scal, partial,
+                                                        positives_above, samples_above);
+  }
+  TE_PROF("rank_reduce", st);
+  rank_reduce_kernel<1><<<1, 1024, 0, st>>>(partial, nchunks, p.n, scal, out);
+  TE_LAUNCH_CHECK();
+  return TE_OK;
 }
 
 extern "C" int te_debug_phase_stats(uint64_t* out8, int reset) {

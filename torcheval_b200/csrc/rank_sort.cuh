@@ -24,7 +24,6 @@ constexpr int kSortBlockDefault = 512;  // 8192 records per CTA; 256 (4096 recor
 //   v      (bit31 == 1)   : v & 0x7fffffff = count over this tile and every tile before it
 // A word carries its own validity, so relaxed loads/stores are enough.  Limits n to 2^31 - 1.
 constexpr uint32_t kLbInclusive = 0x80000000u;
-constexpr int kLbWindowDefault = 8;   // predecessors fetched per look-back round trip
 
 // What a pass sorts by: an 8-bit digit of the key ...
 struct RadixDigit {
@@ -42,6 +41,7 @@ constexpr int kMaxSplitters = 15;
 // shifted so that indexing with the pass's own output index lands in this rank's slot there.
 struct PeerPtrs {
   unsigned long long p[kMaxSplitters + 1];
+  int vec;  // 1: leave each run as 16-byte stores (head / body / tail), 0: one 4-byte store per record
 };
 struct SplitterDigit {
   uint32_t sp[kMaxSplitters];
@@ -93,7 +93,7 @@ constexpr size_t onesweep_stage_bytes() {
 template <typename KeyT, int kSortBlock, int kSortIpt = kSortIptDefault>
 constexpr size_t onesweep_smem_bytes() {
   return onesweep_stage_bytes<KeyT, kSortBlock, kSortIpt>() +
-         sizeof(uint32_t) * ((kSortBlock / 16) * kRadix + 2 * kRadix + kRadix / kWarp + 4);
+         sizeof(uint32_t) * ((kSortBlock / 16) * kRadix + 2 * kRadix + kRadix / kWarp + 4 + 2 * (kMaxSplitters + 1));
 }
 
 // Cross-tile offsets: two-level decoupled look-back.  With ~30-60 million tiles per second per
@@ -108,8 +108,13 @@ constexpr size_t onesweep_smem_bytes() {
 // a tile that has not been dispatched.
 constexpr int kLbGroup = 32;
 
+//
+// kUnstable: ranks inside a round are handed out in arrival order (one ATOMS.ADD with return
+// instead of ATOMS.OR + LDS + STS).  Only valid where the relative order of records with equal
+// digits carries no information: the FIRST pass of a keys-only sort (records that agree in all
+// 32 bits are indistinguishable, and later passes are stable), never for (key, value) pairs.
 template <typename KeyT, bool HAS_VAL, int kSortBlock, typename DigitOp, int kSortIpt = kSortIptDefault,
-          bool kPeerScatter = false>
+          bool kPeerScatter = false, bool kUnstable = false>
 __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / kSortBlock)
     onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                          const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
@@ -127,6 +132,7 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
       smem_raw + onesweep_stage_bytes<KeyT, kSortBlock, kSortIpt>());  // [GROUPS][256]
   uint32_t* s_goff = &s_base[GROUPS][0];       // 2*256 words: also the slice starts of the digit phase
   uint32_t* s_wsum = s_goff + 2 * kRadix;
+  uint32_t* s_runs = s_wsum + kRadix / kWarp + 4;  // peer scatter: tile-local start, count per bucket
 
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   TE_PHASE_BEGIN();
@@ -169,15 +175,21 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
 #pragma unroll
   for (int i = 0; i < kSortIpt; ++i) {
     const uint32_t d = dop(key[i]);
-    atomicOr(gt + d, sub_bit);
-    __syncwarp();
-    const uint32_t e = gt[d];  // count << 16 | lanes of the group holding digit d this round
-    __syncwarp();
-    const uint32_t peers = e & 0xffffu, cnt = e >> 16;
-    const uint32_t below = __popc(peers & sub_lt);
-    if (below == 0) gt[d] = (cnt + __popc(peers)) << 16;  // lowest peer: bump count, clear mask
-    __syncwarp();
-    const uint32_t r = cnt + below;
+    uint32_t r;
+    if (kUnstable) {
+      static_assert(!(kUnstable && HAS_VAL), "payloads need a stable pass");
+      r = atomicAdd(gt + d, 1u << 16) >> 16;
+    } else {
+      atomicOr(gt + d, sub_bit);
+      __syncwarp();
+      const uint32_t e = gt[d];  // count << 16 | lanes of the group holding digit d this round
+      __syncwarp();
+      const uint32_t peers = e & 0xffffu, cnt = e >> 16;
+      const uint32_t below = __popc(peers & sub_lt);
+      if (below == 0) gt[d] = (cnt + __popc(peers)) << 16;  // lowest peer: bump count, clear mask
+      __syncwarp();
+      r = cnt + below;
+    }
     if ((i & 3) == 0)
       rk[i >> 2] = r;
     else
@@ -284,11 +296,40 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
       if (k == kLbGroup - 1)  // last tile of the group: extend the chain of group prefixes
         st_relaxed_u32(group_prefix + (size_t)grp * kRadix + d, kLbInclusive | (excl + my_cnt));
       s_goff[d] = digit_base[d] + excl - my_bin_start;  // output index = s_goff[d] + tile position
+      if (kPeerScatter && d <= (uint32_t)kMaxSplitters) s_runs[d] = my_bin_start, s_runs[kMaxSplitters + 1 + d] = my_cnt;
     }
   }
   __syncthreads();
   TE_PHASE_MARK(6);  // look-back
 
+  if constexpr (kPeerScatter && sizeof(KeyT) == 4 && !HAS_VAL) {
+    // NVLink stores: a bucket's run is contiguous both in s_keys and in its inbox, so it leaves as
+    // 16-byte stores (scalar head up to the first 16-byte boundary of the destination, scalar tail)
+    if (peers.vec) {
+      const int nb = dop.nsp + 1;
+      for (int d = 0; d < nb; ++d) {
+        const uint32_t rs = s_runs[d];
+        if (rs >= valid) break;  // runs are in tile order; padding sits at the very end
+        const uint32_t rc = min(s_runs[kMaxSplitters + 1 + d], valid - rs);
+        if (rc == 0) continue;
+        uint32_t* dst = reinterpret_cast<uint32_t*>(peers.p[d]) + s_goff[d];  // dst[p], p = tile position
+        const uint32_t mis = (uint32_t)((reinterpret_cast<uintptr_t>(dst + rs) >> 2) & 3u);
+        const uint32_t head = min(rc, (4u - mis) & 3u);
+        if (tid < head) dst[rs + tid] = s_keys[rs + tid];
+        const uint32_t body = (rc - head) >> 2;
+        for (uint32_t q = tid; q < body; q += kSortBlock) {
+          const uint32_t p = rs + head + 4 * q;
+          uint4 v;
+          v.x = s_keys[p], v.y = s_keys[p + 1], v.z = s_keys[p + 2], v.w = s_keys[p + 3];
+          *reinterpret_cast<uint4*>(dst + p) = v;
+        }
+        const uint32_t done = head + 4 * body;
+        if (tid < rc - done) dst[rs + done + tid] = s_keys[rs + done + tid];
+      }
+      TE_PHASE_MARK(7);
+      return;
+    }
+  }
   uint32_t dpack[kSortIpt / 4];  // digit of tile position tid + k*BLOCK, four per register
 #pragma unroll
   for (int k = 0; k < kSortIpt; ++k) {

@@ -71,6 +71,14 @@ class _LocalKernels:
     def auroc_from_keys(keys: torch.Tensor) -> torch.Tensor:
         return ops.binary_auroc_from_keys(keys)
 
+    @staticmethod
+    def auprc_begin(keys: torch.Tensor):
+        return ops.binary_auprc_from_keys_begin(keys)
+
+    @staticmethod
+    def auprc_finish(state, positives_above: int, samples_above: int) -> torch.Tensor:
+        return ops.binary_auprc_from_keys_finish(state, positives_above, samples_above)
+
 
 _local = _LocalKernels
 
@@ -140,18 +148,15 @@ def _gather_rows(t: torch.Tensor, world: int, group) -> torch.Tensor:
     return out
 
 
-def sharded_binary_auroc(
-    score: torch.Tensor, target: torch.Tensor, group: Optional[dist.ProcessGroup] = None
-) -> torch.Tensor:
-    """AUROC of the union of all ranks' (score, target) shards; float64[8] on score.device:
-    [auroc, P, N, 2U, flags, n_received_here, 0, 0].  flags != 0 (negative scores / soft labels
-    somewhere) means the packed representation does not apply and [0] is not valid.
-    Three host round trips in total: splitters, bucket sizes, per-rank statistics."""
+def _exchange_keys(score: torch.Tensor, target: torch.Tensor, group, tm: _PhaseTimer):
+    """Steps 1-4: returns (inbox, flags).  inbox = the packed keys of the score range this rank
+    owns (rank order = ascending score order), None when flags != 0 (negative scores / soft labels
+    on some rank: the packed representation does not apply; every rank sees the same flags).
+    Two host round trips: splitters, bucket sizes."""
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = score.device
     n = score.numel()
-    tm = _PhaseTimer(dev)
 
     # --- splitters from regular samples of the raw scores (key space: float bits << 1) -------
     s = SAMPLES_PER_RANK
@@ -181,9 +186,7 @@ def sharded_binary_auroc(
     for r in rows:
         flags |= int(r[world])
     if flags:
-        out = torch.zeros(8, dtype=torch.float64, device=dev)
-        out[4] = float(flags)
-        return out
+        return None, flags
     send = [int(c) for c in rows[rank][:world]]
     recv = [int(rows[q][rank]) for q in range(world)]
 
@@ -213,6 +216,29 @@ def sharded_binary_auroc(
         inbox = torch.empty(sum(recv), dtype=keys.dtype, device=dev)
         dist.all_to_all_single(inbox, part, recv, send, group=group)
         tm.mark("all_to_all")
+    return inbox, 0
+
+
+def _flags_only(flags: int, dev) -> torch.Tensor:
+    out = torch.zeros(8, dtype=torch.float64, device=dev)
+    out[4] = float(flags)
+    return out
+
+
+def sharded_binary_auroc(
+    score: torch.Tensor, target: torch.Tensor, group: Optional[dist.ProcessGroup] = None
+) -> torch.Tensor:
+    """AUROC of the union of all ranks' (score, target) shards; float64[8] on score.device:
+    [auroc, P, N, 2U, flags, n_received_here, 0, 0].  flags != 0 (negative scores / soft labels
+    somewhere) means the packed representation does not apply and [0] is not valid.
+    Three host round trips in total: splitters, bucket sizes, per-rank statistics."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    dev = score.device
+    tm = _PhaseTimer(dev)
+    inbox, flags = _exchange_keys(score, target, group, tm)
+    if flags:
+        return _flags_only(flags, dev)
 
     # --- local sort + integrate, then the 3-integer fix-up -------------------------------------
     loc = _local.auroc_from_keys(inbox)
@@ -227,42 +253,164 @@ def sharded_binary_auroc(
     return torch.tensor([auroc, P, N, float(u2), 0.0, float(inbox.numel()), 0.0, 0.0], dtype=torch.float64, device=dev)
 
 
-def try_sharded_compute(metric, group: Optional[dist.ProcessGroup] = None):
-    """Fast path of ``toolkit.sync_and_compute``: exact BinaryAUROC (one task, no weights) held
-    as rank-local shards.  Returns the metric value, or None if the metric / its state does not
-    qualify on some rank (every rank then takes the generic path together)."""
-    from .metrics.classification.auroc import BinaryAUROC, _resolve_weights
-    from ._ranking import _as_f32_scores, compute_device, stage
+def combine_rank_ap(sums, positives):
+    """sums[r] = sum over rank r's positives of the precision at their threshold (float),
+    positives[r] = P_r.  AP of the union; no positives anywhere -> -0.0 like the reference
+    (precision_recall_curve.py:227-229)."""
+    P = sum(int(p) for p in positives)
+    if P == 0:
+        return -0.0
+    total = 0.0
+    for v in sums:  # fixed rank order: the same bits on every rank and every run
+        total += float(v)
+    return total / P
 
-    if not isinstance(metric, BinaryAUROC):
-        return None
+
+def sharded_binary_auprc(
+    score: torch.Tensor, target: torch.Tensor, group: Optional[dist.ProcessGroup] = None
+) -> torch.Tensor:
+    """Average precision (step integral, functional/classification/auprc.py:239-251) of the union
+    of all ranks' shards; float64[8]: [ap, P, N, sum, flags, n_received_here, 0, 0].
+    Precision is a ratio of prefix counts, so after the exchange the work is two-phase:
+    sort + count locally -> all_gather (P_r, N_r) -> integrate with what the ranks above hold ->
+    all_gather the per-rank sums.  Four host round trips in total."""
     world = dist.get_world_size(group)
-    ok = (
-        metric.num_tasks == 1
-        and len(metric.inputs) > 0
-        and _resolve_weights(metric.inputs, metric.weights) is None
-        and metric.inputs[0].dim() == 1
-    )
-    from .metrics.toolkit import _comm_device
+    rank = dist.get_rank(group)
+    dev = score.device
+    tm = _PhaseTimer(dev)
+    inbox, flags = _exchange_keys(score, target, group, tm)
+    if flags:
+        return _flags_only(flags, dev)
 
-    cdev = _comm_device(metric.device, group)
+    loc, state = _local.auprc_begin(inbox)
+    tm.mark("local_sort_count")
+    pn = _gather_rows(torch.stack([loc[1], loc[2]]).to(torch.int64), world, group).tolist()
+    pos_above = sum(int(pn[q][0]) for q in range(rank + 1, world))
+    all_above = sum(int(pn[q][0]) + int(pn[q][1]) for q in range(rank + 1, world))
+    part = _local.auprc_finish(state, pos_above, all_above)
+    tm.mark("integrate")
+    sums = _gather_rows(part[3:4].clone(), world, group).reshape(-1).tolist()
+    ap = combine_rank_ap(sums, [r[0] for r in pn])
+    P = sum(int(r[0]) for r in pn)
+    Nn = sum(int(r[1]) for r in pn)
+    tm.mark("fixup")
+    tm.done(rank)
+    return torch.tensor([ap, P, Nn, sum(sums), 0.0, float(inbox.numel()), 0.0, 0.0], dtype=torch.float64, device=dev)
+
+
+def _column_bounds(num_columns: int, world: int):
+    return [(q * num_columns) // world for q in range(world + 1)]
+
+
+def class_sharded_one_vs_rest(
+    input: torch.Tensor,
+    target: torch.Tensor,
+    *,
+    auprc: bool,
+    multilabel: bool,
+    group: Optional[dist.ProcessGroup] = None,
+) -> torch.Tensor:
+    """Per-class (per-label) one-vs-rest AUROC / average precision over sample-sharded
+    (n_r, C) scores: float64 (C,), the same on every rank.
+
+    Classes are independent, so instead of gathering all N x C scores everywhere (the reference:
+    toolkit.py:371-391 then auroc.py:206-235 / auprc.py:279-347 on the concatenation) the ranks
+    transpose the sharding with ONE all-to-all: rank q ends up with all N rows of its C/W columns,
+    ranks them locally with the batched one-vs-rest kernels, and the C values are all-gathered.
+    No splitters, perfectly balanced, and no rank holds more than N*C/W scores."""
+    from . import _ranking
+
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    dev = input.device
+    n_r, C = int(input.shape[0]), int(input.shape[1])
+    bounds = _column_bounds(C, world)
+    width = bounds[rank + 1] - bounds[rank]
+    ns = [int(v) for v in _gather_rows(torch.tensor([n_r], dtype=torch.int64, device=dev), world, group).reshape(-1).tolist()]
+    n_all = sum(ns)
+
+    def transpose_sharding(t: torch.Tensor) -> torch.Tensor:
+        send = torch.cat([t[:, bounds[q] : bounds[q + 1]].reshape(-1) for q in range(world)])
+        send_sizes = [n_r * (bounds[q + 1] - bounds[q]) for q in range(world)]
+        recv_sizes = [ns[q] * width for q in range(world)]
+        recv = torch.empty(sum(recv_sizes), dtype=t.dtype, device=dev)
+        dist.all_to_all_single(recv, send, recv_sizes, send_sizes, group=group)
+        return recv.view(n_all, width)  # blocks arrive in rank order = row order of the union
+
+    x_loc = transpose_sharding(input)
+    if multilabel:
+        t_loc = transpose_sharding(target)
+    else:
+        # every rank needs all N class labels; shifted so that local column j is class j
+        pad = torch.zeros(max(ns), dtype=torch.int64, device=dev)
+        pad[:n_r] = target.to(torch.int64)
+        rows = _gather_rows(pad, world, group)
+        t_loc = torch.cat([rows[q, : ns[q]] for q in range(world)]) - bounds[rank]
+    if width > 0 and n_all > 0:
+        vals = _ranking._one_vs_rest(x_loc, t_loc, auprc, multilabel).to(torch.float64).to(dev)
+    else:
+        vals = torch.zeros(width, dtype=torch.float64, device=dev)
+    wmax = max(bounds[q + 1] - bounds[q] for q in range(world))
+    pad = torch.zeros(wmax, dtype=torch.float64, device=dev)
+    pad[:width] = vals
+    rows = _gather_rows(pad, world, group)
+    return torch.cat([rows[q, : bounds[q + 1] - bounds[q]] for q in range(world)])
+
+
+def _agree(ok: bool, cdev: torch.device, group) -> bool:
     flag = torch.tensor([1 if ok else 0], dtype=torch.int64, device=cdev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
-    if int(flag.item()) == 0:
+    return int(flag.item()) == 1
+
+
+def try_sharded_compute(metric, group: Optional[dist.ProcessGroup] = None):
+    """Fast paths of ``toolkit.sync_and_compute`` for the sample-keeping metrics held as rank-local
+    shards: exact BinaryAUROC / BinaryAUPRC (one task, no weights) as a distributed sample sort,
+    MulticlassAUROC / MulticlassAUPRC / MultilabelAUPRC as a class-sharded transpose.  Returns
+    the metric value, or None if the metric / its state does not qualify on some rank (every
+    rank then takes the generic path together)."""
+    from .metrics.classification.auprc import BinaryAUPRC, MulticlassAUPRC, MultilabelAUPRC
+    from .metrics.classification.auroc import BinaryAUROC, MulticlassAUROC, _resolve_weights
+    from ._ranking import _as_f32_scores, compute_device, stage
+    from .metrics.toolkit import _comm_device
+
+    is_auroc = isinstance(metric, BinaryAUROC)
+    is_auprc = isinstance(metric, BinaryAUPRC)
+    is_ovr = isinstance(metric, (MulticlassAUROC, MulticlassAUPRC, MultilabelAUPRC))
+    if not (is_auroc or is_auprc or is_ovr):
+        return None
+    cdev = _comm_device(metric.device, group)
+    ok = len(metric.inputs) > 0
+    if is_auroc or is_auprc:
+        ok = ok and metric.num_tasks == 1 and metric.inputs[0].dim() == 1
+        if is_auroc:
+            ok = ok and _resolve_weights(metric.inputs, metric.weights) is None
+    if not _agree(ok, cdev, group):
         return None
     metric._prepare_for_merge_state()
     x, t = metric.inputs[0], metric.targets[0]
     dev = cdev if cdev.type == "cuda" else compute_device(x)
     try:
         xs = _as_f32_scores(stage(x, dev))
-        representable = 1
+        representable = True
     except NotImplementedError:
-        xs, representable = None, 0
-    flag = torch.tensor([representable], dtype=torch.int64, device=cdev)
-    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
-    if int(flag.item()) == 0:
+        xs, representable = None, False
+    if not _agree(representable, cdev, group):
         return None
-    out = sharded_binary_auroc(xs, stage(t, dev), group)
+    ts = stage(t, dev)
+    if is_ovr:
+        multilabel = isinstance(metric, MultilabelAUPRC)
+        vals = class_sharded_one_vs_rest(
+            xs, ts, auprc=not isinstance(metric, MulticlassAUROC), multilabel=multilabel, group=group
+        )
+        vals = vals.to(torch.float32).to(metric.device)
+        return vals.mean() if metric.average == "macro" else vals
+    if is_auroc:
+        out = sharded_binary_auroc(xs, ts, group)
+        if int(out[4].item()) != 0:
+            return None  # same answer on every rank (flags were all-gathered)
+        return out[0].clone().to(metric.device)
+    out = sharded_binary_auprc(xs, ts, group)
     if int(out[4].item()) != 0:
-        return None  # same answer on every rank (flags were all-gathered)
-    return out[0].clone().to(metric.device)
+        return None
+    return out[0].to(torch.float32).to(metric.device)

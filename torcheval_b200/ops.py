@@ -421,3 +421,41 @@ def binary_auroc_from_keys(keys: torch.Tensor) -> torch.Tensor:
             lib.te_binary_auroc_from_keys(keys.data_ptr(), n, out.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
         )
     return out
+
+
+def binary_auprc_from_keys_begin(keys: torch.Tensor):
+    """Phase 1 of the rank-sharded average precision: sort + count.  Returns (out, state) where
+    out is float64[8] like ``binary_auroc_from_keys`` and ``state`` must be handed, untouched, to
+    ``binary_auprc_from_keys_finish``."""
+    lib = N.load()
+    dev = _require_cuda(keys)
+    keys = keys.contiguous()
+    n = keys.numel()
+    out = torch.empty(8, dtype=torch.float64, device=dev)
+    scratch = _scratch(lib.te_binary_rank_scratch_bytes(n), dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_binary_auprc_from_keys_begin",
+            lib.te_binary_auprc_from_keys_begin(
+                keys.data_ptr(), n, out.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)
+            ),
+        )
+    return out, (n, scratch)
+
+
+def binary_auprc_from_keys_finish(state, positives_above: int, samples_above: int) -> torch.Tensor:
+    """Phase 2: float64[8]; [3] = sum over the local positives of the precision at their
+    threshold, given what the ranks holding higher scores contain."""
+    lib = N.load()
+    n, scratch = state
+    dev = scratch.device
+    out = torch.zeros(8, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_binary_auprc_from_keys_finish",
+            lib.te_binary_auprc_from_keys_finish(
+                n, float(positives_above), float(samples_above), out.data_ptr(), scratch.data_ptr(),
+                scratch.numel(), _stream_ptr(dev),
+            ),
+        )
+    return out
