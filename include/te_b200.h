@@ -233,6 +233,12 @@ TE_API size_t te_rank_pack_scratch_bytes(int64_t n);
 TE_API int te_rank_pack(const float* score, const void* target, int32_t target_dtype, int64_t n,
                         const uint32_t* splitters_host, int32_t num_splitters, uint32_t* keys_out,
                         int64_t* info, int64_t* counts, void* scratch, size_t scratch_bytes, void* stream);
+/* te_rank_pack with the splitters in DEVICE memory (uint32[num_splitters], ascending: not
+ * checked), for callers that pick them on the device and do not want a host round trip. */
+TE_API int te_rank_pack_dsplit(const float* score, const void* target, int32_t target_dtype, int64_t n,
+                               const uint32_t* splitters_dev, int32_t num_splitters, uint32_t* keys_out,
+                               int64_t* info, int64_t* counts, void* scratch, size_t scratch_bytes,
+                               void* stream);
 TE_API size_t te_partition_u32_scratch_bytes(int64_t n);
 TE_API int te_partition_u32(const uint32_t* keys_in, int64_t n, const uint32_t* splitters_host,
                             int32_t num_splitters, const int64_t* counts_in, uint32_t* keys_out,
@@ -257,13 +263,15 @@ TE_API int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, double* ou
  *           untouched until _finish (same n, same scratch, same device).
  *  _finish: out[3] = sum over this rank's positives of precision at their threshold, with
  *           positives_above / samples_above = positives / samples held by the ranks whose score
- *           ranges lie above this one (exact integers passed as doubles).  AP = sum over ranks of
- *           out[3], divided by the global number of positives; out[1], out[2] = local P, N. */
+ *           ranges lie above this one (exact integers passed as doubles; if above_dev is not
+ *           NULL the two numbers are read from that device array instead, so that they can come
+ *           straight out of a collective).  AP = sum over ranks of out[3], divided by the global
+ *           number of positives; out[1], out[2] = local P, N. */
 TE_API int te_binary_auprc_from_keys_begin(const uint32_t* keys, int64_t n, double* out, void* scratch,
                                            size_t scratch_bytes, void* stream);
 TE_API int te_binary_auprc_from_keys_finish(int64_t n, double positives_above, double samples_above,
-                                            double* out, void* scratch, size_t scratch_bytes,
-                                            void* stream);
+                                            const double* above_dev, double* out, void* scratch,
+                                            size_t scratch_bytes, void* stream);
 
 /* The sort on its own: ascending, stable, 32-bit keys with an optional 32-bit payload
  * (vals_in/vals_out both NULL or both set).  Replaces torch.sort at auroc.py:121. */

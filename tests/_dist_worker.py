@@ -36,7 +36,7 @@ def main():
 
     res = {}
     calls = {"auprc": 0, "ovr": 0}
-    real_auprc, real_ovr = tdist.sharded_binary_auprc, tdist.class_sharded_one_vs_rest
+    real_auprc, real_ovr = tdist._sharded_binary_auprc, tdist.class_sharded_one_vs_rest
 
     def counting_auprc(*a, **k):
         calls["auprc"] += 1
@@ -46,7 +46,7 @@ def main():
         calls["ovr"] += 1
         return real_ovr(*a, **k)
 
-    tdist.sharded_binary_auprc, tdist.class_sharded_one_vs_rest = counting_auprc, counting_ovr
+    tdist._sharded_binary_auprc, tdist.class_sharded_one_vs_rest = counting_auprc, counting_ovr
     rs = np.random.default_rng(7)
     n = 20011
     cases = {

@@ -170,6 +170,8 @@ def sort_u32(keys, vals=None):
 
 
 def rank_pack(score, target, splitters=()):
+    if isinstance(splitters, torch.Tensor):  # "device" splitters: int32 bit patterns
+        splitters = [int(v) & 0xFFFFFFFF for v in splitters.tolist()]
     x = _np(score).astype(np.float32).copy()
     bits = x.view(np.uint32).copy()
     bits[bits == 0x80000000] = 0
@@ -203,8 +205,10 @@ def binary_auprc_from_keys_begin(keys):
     return binary_auroc_from_keys(keys), k
 
 
-def binary_auprc_from_keys_finish(state, positives_above, samples_above):
+def binary_auprc_from_keys_finish(state, positives_above, samples_above=None):
     """sum over the local positives of TP/(TP+FP) at their threshold (ascending sorted keys)."""
+    if isinstance(positives_above, torch.Tensor):
+        positives_above, samples_above = (int(v) for v in positives_above.tolist())
     k = state
     out = torch.zeros(8, dtype=torch.float64)
     if k.size == 0:

@@ -57,6 +57,20 @@ def test_combine_rank_stats_and_splitters():
     assert u2 == 2 + 2 + 2 * 2 * 2  # each high positive also beats both low negatives
     assert auroc == u2 / (2 * 9)
     assert combine_rank_stats([(0, 5, 0), (0, 3, 0)])[0] == 0.5
+    import torch
+    from torcheval_b200.distributed import combine_rank_stats_tensor
+
+    rs = np.random.default_rng(3)
+    for _ in range(20):
+        w = int(rs.integers(1, 9))
+        p_, n_ = rs.integers(0, 2**28, w), rs.integers(0, 2**28, w)
+        u2 = [int(rs.integers(0, 2 * int(a) * int(b) + 1)) for a, b in zip(p_, n_)]
+        want = combine_rank_stats([(int(a), int(b), c) for a, b, c in zip(p_, n_, u2)])
+        st = torch.tensor([[int(a), int(b), c >> 32, c & 0xFFFFFFFF] for a, b, c in zip(p_, n_, u2)], dtype=torch.int64)
+        got = combine_rank_stats_tensor(st)
+        assert (int(got[1]), int(got[2]), int(got[3])) == want[1:]
+        np.testing.assert_allclose(float(got[0]), want[0], rtol=1e-15)
+    assert float(combine_rank_stats_tensor(torch.tensor([[0, 5, 0, 0], [0, 3, 0, 0]]))[0]) == 0.5
     sp = choose_splitters(sorted([5, 9, 9, 9, 9, 13, 21, 40]), 4)
     assert sp == sorted(sp) and all(v % 2 == 0 for v in sp) and len(sp) == 3
     assert choose_splitters([], 2) == [0]

@@ -451,6 +451,9 @@ def test_rank_pack_partition_from_keys(ops):
             wp, wc = cpu_backend.partition_u32(wk, sp)
             k2, _, c2 = ops.rank_pack(dev(x), dev(y), sp)  # bucket sizes straight from the pack pass
             assert c2.tolist() == wc.tolist(), (n, sp)
+            sp_dev = torch.tensor(sp, dtype=torch.int64, device="cuda").to(torch.int32)  # bit patterns
+            k3, _, c3 = ops.rank_pack(dev(x), dev(y), sp_dev)  # splitters read from device memory
+            assert c3.tolist() == wc.tolist() and torch.equal(k3, k2), (n, sp)
             for known in (None, c2):
                 part, counts = ops.partition_u32(k2, sp, known)
                 assert counts.tolist() == wc.tolist(), (n, sp)
@@ -529,6 +532,8 @@ def test_auprc_from_keys_two_phase(ops, n):
     f_lo = ops.binary_auprc_from_keys_finish(slo, int(y[hi].sum()), int(hi.sum())).cpu().numpy()
     want_lo = cpu_backend.binary_auprc_from_keys_finish(np.sort(klo.cpu().numpy().view(np.uint32)), int(y[hi].sum()), int(hi.sum()))
     close(f_lo[3], float(want_lo[3]), 1e-12)
+    above = torch.tensor([float(y[hi].sum()), float(hi.sum())], dtype=torch.float64, device="cuda")
+    assert ops.binary_auprc_from_keys_finish(slo, above).cpu().numpy()[3] == f_lo[3]  # same numbers from device memory
     close(f_lo[3] + f_hi[3], whole[3], 1e-12)
 
 

@@ -276,7 +276,7 @@ __global__ void __launch_bounds__(kFinBlock)
     rank_chunk_kernel(const uint32_t* __restrict__ keys, uint32_t n, uint32_t tiles_per_chunk,
                       ChunkRec* rec, const FState* __restrict__ excl_in,
                       const RankScalars* __restrict__ scal, unsigned long long* partial,
-                      double pos_above, double cnt_above) {
+                      double pos_above, double cnt_above, const double* __restrict__ above_dev) {
   __shared__ FState s_warp[kFinBlock / kWarp];
   __shared__ unsigned long long s_red[3][kFinBlock / kWarp];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -288,6 +288,8 @@ __global__ void __launch_bounds__(kFinBlock)
   double accD = 0.0;
   // pos_above / cnt_above: positives / samples with a score above everything in `keys` that live
   // on other ranks (0 when `keys` is the whole sample set)
+  // (above_dev, if given, holds the same two numbers in device memory)
+  if (MODE == 1 && above_dev) pos_above = above_dev[0], cnt_above = above_dev[1];
   const double ptot = MODE == 1 ? (double)scal->positives + pos_above : 0.0;
 
   // register double buffering: the loads of tile t+1 are in flight while tile t is processed
@@ -731,7 +733,7 @@ int finish_packed(const RankPlan& p, const uint32_t* ka, int mode, double* out, 
   const uint32_t nchunks = n > 0 ? cg.nchunks : 0;
   if (nchunks) {
     TE_PROF("rank_chunk_sweep", st);
-    rank_chunk_kernel<0><<<nchunks, kFinBlock, 0, st>>>(ka, p.n, cg.tiles_per_chunk, rec, nullptr, scal, nullptr, 0.0, 0.0);
+    rank_chunk_kernel<0><<<nchunks, kFinBlock, 0, st>>>(ka, p.n, cg.tiles_per_chunk, rec, nullptr, scal, nullptr, 0.0, 0.0, nullptr);
   }
   TE_LAUNCH_CHECK();
   if (mode == 0) {
@@ -744,7 +746,7 @@ int finish_packed(const RankPlan& p, const uint32_t* ka, int mode, double* out, 
         rank_chunk_scan_kernel<1><<<1, kMaxChunks, 0, st>>>(rec, nchunks, p.n, scal, excl, nullptr);
       }
       TE_PROF("rank_chunk_integrate", st);
-      rank_chunk_kernel<1><<<nchunks, kFinBlock, 0, st>>>(ka, p.n, cg.tiles_per_chunk, nullptr, excl, scal, partial, 0.0, 0.0);
+      rank_chunk_kernel<1><<<nchunks, kFinBlock, 0, st>>>(ka, p.n, cg.tiles_per_chunk, nullptr, excl, scal, partial, 0.0, 0.0, nullptr);
     }
     TE_PROF("rank_reduce", st);
     rank_reduce_kernel<1><<<1, 1024, 0, st>>>(partial, nchunks, p.n, scal, out);
@@ -1156,12 +1158,23 @@ __global__ void rank_info_kernel(const RankScalars* __restrict__ scal, long long
 template <typename TargetT>
 __global__ void __launch_bounds__(1024)
     pack_bucket_kernel(const float* __restrict__ score, const TargetT* __restrict__ target, uint32_t n,
-                       bool vec_ok, const SplitterDigit dop, uint32_t* __restrict__ keys_out, uint32_t* hist,
-                       RankScalars* scal) {
+                       bool vec_ok, const SplitterDigit dop_in, const uint32_t* __restrict__ splitters_dev,
+                       uint32_t* __restrict__ keys_out, uint32_t* hist, RankScalars* scal) {
   __shared__ uint32_t sh[16 * kWarp];
+  __shared__ uint32_t s_sp[kMaxSplitters + 1];
   const unsigned tid = threadIdx.x, lane = tid & 31;
   if (tid < 16 * kWarp) sh[tid] = 0;
+  // splitters either came with the launch (host array) or are read from device memory, so that a
+  // caller can choose them on the device without a round trip through the host
+  if (tid < (unsigned)dop_in.nsp) s_sp[tid] = splitters_dev ? splitters_dev[tid] : dop_in.sp[tid];
   __syncthreads();
+  const int nsp = dop_in.nsp;
+  auto dop = [&](uint32_t k) {
+    uint32_t b = 0;
+#pragma unroll 1
+    for (int i = 0; i < nsp; ++i) b += s_sp[i] <= k ? 1u : 0u;
+    return b;
+  };
   uint32_t npos = 0, bad_label = 0, neg_score = 0;
   const uint32_t ngroups = (n + 3) / 4;
   for (uint32_t g = blockIdx.x * blockDim.x + tid; g < ngroups; g += gridDim.x * blockDim.x) {
@@ -1445,26 +1458,33 @@ static int fill_splitters(SplitterDigit& dop, const uint32_t* splitters_host, in
 
 template <typename TargetT>
 static void launch_pack(const float* score, const void* target, const RankPlan& p, const SplitterDigit& dop,
-                        uint32_t* keys_out, void* scratch, int sms, cudaStream_t st) {
+                        const uint32_t* splitters_dev, uint32_t* keys_out, void* scratch, int sms,
+                        cudaStream_t st) {
   const uint32_t ngroups = (p.n + 3) / 4;
   uint32_t grid = (ngroups + 1023) / 1024;
   if (grid > (uint32_t)sms * 2) grid = sms * 2;
   const bool vec_ok = ((((uintptr_t)score) | ((uintptr_t)target)) & 15) == 0;
-  pack_bucket_kernel<TargetT><<<grid, 1024, 0, st>>>(score, (const TargetT*)target, p.n, vec_ok, dop, keys_out,
-                                                     at<uint32_t>(scratch, p.off_hist),
+  pack_bucket_kernel<TargetT><<<grid, 1024, 0, st>>>(score, (const TargetT*)target, p.n, vec_ok, dop, splitters_dev,
+                                                     keys_out, at<uint32_t>(scratch, p.off_hist),
                                                      at<RankScalars>(scratch, p.off_scal));
 }
 
-extern "C" int te_rank_pack(const float* score, const void* target, int32_t target_dtype, int64_t n,
-                            const uint32_t* splitters_host, int32_t num_splitters, uint32_t* keys_out,
-                            int64_t* info, int64_t* counts, void* scratch, size_t scratch_bytes,
-                            void* stream) {
+static int rank_pack_impl(const float* score, const void* target, int32_t target_dtype, int64_t n,
+                          const uint32_t* splitters_host, const uint32_t* splitters_dev, int32_t num_splitters,
+                          uint32_t* keys_out, int64_t* info, int64_t* counts, void* scratch,
+                          size_t scratch_bytes, void* stream) {
   if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
   if (!info || !counts || (n > 0 && (!score || !target || !keys_out))) return TE_ERR_INVALID_ARGUMENT;
   if (((uintptr_t)keys_out & 15) != 0) return TE_ERR_INVALID_ARGUMENT;
   SplitterDigit dop;
-  const int rs = fill_splitters(dop, splitters_host, num_splitters);
-  if (rs) return rs;
+  if (splitters_dev) {
+    if (num_splitters < 0 || num_splitters > kMaxSplitters) return TE_ERR_INVALID_ARGUMENT;
+    dop = SplitterDigit{};
+    dop.nsp = num_splitters;
+  } else {
+    const int rs = fill_splitters(dop, splitters_host, num_splitters);
+    if (rs) return rs;
+  }
   const RankPlan p = make_plan(n, false, false, false);
   if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
   cudaStream_t st = (cudaStream_t)stream;
@@ -1474,11 +1494,11 @@ extern "C" int te_rank_pack(const float* score, const void* target, int32_t targ
   if (n > 0) {
     TE_PROF("pack_bucket", st);
     switch (target_dtype) {
-      case TE_DTYPE_I64: launch_pack<long long>(score, target, p, dop, keys_out, scratch, sms, st); break;
-      case TE_DTYPE_I32: launch_pack<int>(score, target, p, dop, keys_out, scratch, sms, st); break;
-      case TE_DTYPE_U8: launch_pack<unsigned char>(score, target, p, dop, keys_out, scratch, sms, st); break;
-      case TE_DTYPE_F32: launch_pack<float>(score, target, p, dop, keys_out, scratch, sms, st); break;
-      case TE_DTYPE_F64: launch_pack<double>(score, target, p, dop, keys_out, scratch, sms, st); break;
+      case TE_DTYPE_I64: launch_pack<long long>(score, target, p, dop, splitters_dev, keys_out, scratch, sms, st); break;
+      case TE_DTYPE_I32: launch_pack<int>(score, target, p, dop, splitters_dev, keys_out, scratch, sms, st); break;
+      case TE_DTYPE_U8: launch_pack<unsigned char>(score, target, p, dop, splitters_dev, keys_out, scratch, sms, st); break;
+      case TE_DTYPE_F32: launch_pack<float>(score, target, p, dop, splitters_dev, keys_out, scratch, sms, st); break;
+      case TE_DTYPE_F64: launch_pack<double>(score, target, p, dop, splitters_dev, keys_out, scratch, sms, st); break;
       default: return TE_ERR_INVALID_ARGUMENT;
     }
     TE_LAUNCH_CHECK();
@@ -1487,6 +1507,24 @@ extern "C" int te_rank_pack(const float* score, const void* target, int32_t targ
   copy_counts_kernel<<<1, 32, 0, st>>>(at<uint32_t>(scratch, p.off_hist), (long long*)counts, num_splitters + 1);
   TE_LAUNCH_CHECK();
   return TE_OK;
+}
+
+extern "C" int te_rank_pack(const float* score, const void* target, int32_t target_dtype, int64_t n,
+                            const uint32_t* splitters_host, int32_t num_splitters, uint32_t* keys_out,
+                            int64_t* info, int64_t* counts, void* scratch, size_t scratch_bytes,
+                            void* stream) {
+  return rank_pack_impl(score, target, target_dtype, n, splitters_host, nullptr, num_splitters, keys_out, info,
+                        counts, scratch, scratch_bytes, stream);
+}
+
+extern "C" int te_rank_pack_dsplit(const float* score, const void* target, int32_t target_dtype, int64_t n,
+                                   const uint32_t* splitters_dev, int32_t num_splitters, uint32_t* keys_out,
+                                   int64_t* info, int64_t* counts, void* scratch, size_t scratch_bytes,
+                                   void* stream) {
+  if (num_splitters > 0 && !splitters_dev) return TE_ERR_INVALID_ARGUMENT;
+  static const uint32_t none = 0;  // num_splitters == 0: nothing is read through the pointer
+  return rank_pack_impl(score, target, target_dtype, n, nullptr, splitters_dev ? splitters_dev : &none,
+                        num_splitters, keys_out, info, counts, scratch, scratch_bytes, stream);
 }
 
 extern "C" size_t te_partition_u32_scratch_bytes(int64_t n) { return te_rank_pack_scratch_bytes(n); }
@@ -1609,7 +1647,7 @@ static int rank_from_keys(const uint32_t* keys, int64_t n, int mode, double* out
   const RankScalars* scal = at<RankScalars>(scratch, p.off_scal);
   if (chunk_geom(p.fin_tiles, sms, occ0).tiles_per_chunk != cg.tiles_per_chunk) {
     TE_PROF("rank_chunk_sweep", st);
-    rank_chunk_kernel<0><<<cg.nchunks, kFinBlock, 0, st>>>(kb, p.n, cg.tiles_per_chunk, rec, nullptr, scal, nullptr, 0.0, 0.0);
+    rank_chunk_kernel<0><<<cg.nchunks, kFinBlock, 0, st>>>(kb, p.n, cg.tiles_per_chunk, rec, nullptr, scal, nullptr, 0.0, 0.0, nullptr);
   }
   TE_PROF("rank_chunk_scan", st);
   rank_chunk_scan_kernel<1><<<1, kMaxChunks, 0, st>>>(rec, cg.nchunks, p.n, scal, at<FState>(scratch, p.off_inc), nullptr);
@@ -1628,10 +1666,11 @@ extern "C" int te_binary_auprc_from_keys_begin(const uint32_t* keys, int64_t n, 
 }
 
 extern "C" int te_binary_auprc_from_keys_finish(int64_t n, double positives_above, double samples_above,
-                                                double* out, void* scratch, size_t scratch_bytes,
-                                                void* stream) {
+                                                const double* above_dev, double* out, void* scratch,
+                                                size_t scratch_bytes, void* stream) {
   if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
-  if (!out || positives_above < 0.0 || samples_above < positives_above) return TE_ERR_INVALID_ARGUMENT;
+  if (!out) return TE_ERR_INVALID_ARGUMENT;
+  if (!above_dev && (positives_above < 0.0 || samples_above < positives_above)) return TE_ERR_INVALID_ARGUMENT;
   const RankPlan p = make_plan(n, false, true, true);
   if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
   cudaStream_t st = (cudaStream_t)stream;
@@ -1647,7 +1686,7 @@ extern "C" int te_binary_auprc_from_keys_finish(int64_t n, double positives_abov
     TE_PROF("rank_chunk_integrate", st);
     rank_chunk_kernel<1><<<nchunks, kFinBlock, 0, st>>>(kb, p.n, cg.tiles_per_chunk, nullptr,
                                                         at<FState>(scratch, p.off_inc), scal, partial,
-                                                        positives_above, samples_above);
+                                                        positives_above, samples_above, above_dev);
   }
   TE_PROF("rank_reduce", st);
   rank_reduce_kernel<1><<<1, 1024, 0, st>>>(partial, nchunks, p.n, scal, out);

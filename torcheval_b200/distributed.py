@@ -76,8 +76,8 @@ class _LocalKernels:
         return ops.binary_auprc_from_keys_begin(keys)
 
     @staticmethod
-    def auprc_finish(state, positives_above: int, samples_above: int) -> torch.Tensor:
-        return ops.binary_auprc_from_keys_finish(state, positives_above, samples_above)
+    def auprc_finish(state, above: torch.Tensor) -> torch.Tensor:
+        return ops.binary_auprc_from_keys_finish(state, above)
 
 
 _local = _LocalKernels
@@ -148,45 +148,49 @@ def _gather_rows(t: torch.Tensor, world: int, group) -> torch.Tensor:
     return out
 
 
+_NO_SAMPLE = 1 << 33  # above every 32-bit key: what a rank without data contributes to the pool
+
+
+def device_splitters(score: torch.Tensor, world: int, group) -> torch.Tensor:
+    """W-1 ascending splitters (int64 key values, label bit cleared) chosen from regular samples
+    of every rank's scores; computed with device ops only, identical on every rank."""
+    dev = score.device
+    n = score.numel()
+    s = SAMPLES_PER_RANK
+    if n > 0:
+        idx = torch.div(torch.arange(s, device=dev, dtype=torch.int64) * n, s, rounding_mode="floor")
+        bits = score.contiguous().view(torch.int32)[idx].to(torch.int64)
+        smp = (bits << 1) & 0xFFFFFFFE
+    else:
+        smp = torch.full((s,), _NO_SAMPLE, dtype=torch.int64, device=dev)
+    pool, _ = torch.sort(_gather_rows(smp, world, group).reshape(-1))
+    m = (pool < _NO_SAMPLE).sum()
+    i = torch.arange(1, world, device=dev, dtype=torch.int64)
+    pick = torch.minimum(torch.div(i * m, world, rounding_mode="floor"), (m - 1).clamp(min=0))
+    return pool[pick] & 0xFFFFFFFE  # no data anywhere: the sentinel masks to 0
+
+
 def _exchange_keys(score: torch.Tensor, target: torch.Tensor, group, tm: _PhaseTimer):
     """Steps 1-4: returns (inbox, flags).  inbox = the packed keys of the score range this rank
     owns (rank order = ascending score order), None when flags != 0 (negative scores / soft labels
     on some rank: the packed representation does not apply; every rank sees the same flags).
-    Two host round trips: splitters, bucket sizes."""
+    ONE host read: bucket sizes, flags and the splitters come back together."""
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = score.device
-    n = score.numel()
 
-    # --- splitters from regular samples of the raw scores (key space: float bits << 1) -------
-    s = SAMPLES_PER_RANK
-    if n > 0:
-        idx = torch.div(torch.arange(s, device=dev, dtype=torch.int64) * n, s, rounding_mode="floor")
-        bits = score.contiguous().view(torch.int32)[idx].to(torch.int64) & 0xFFFFFFFF
-        smp = (bits << 1) & 0xFFFFFFFF
-    else:
-        smp = torch.zeros(s, dtype=torch.int64, device=dev)
-    msg = torch.cat([torch.tensor([n], dtype=torch.int64, device=dev), smp])
-    rows = _gather_rows(msg, world, group)
-    pool = rows[rows[:, 0] > 0][:, 1:].reshape(-1)
-    pool, _ = torch.sort(pool)
-    m = pool.numel()
-    if m:
-        pick = torch.tensor([min(m - 1, (i * m) // world) for i in range(1, world)], dtype=torch.int64, device=dev)
-        splitters = [int(v) & 0xFFFFFFFE for v in pool[pick].tolist()]
-    else:
-        splitters = [0] * (world - 1)
-
+    sp_dev = device_splitters(score, world, group)
     tm.mark("splitters")
-    # --- pack (+ bucket sizes), exchange sizes and flags --------------------------------------
-    keys, info, counts = _local.pack(score, target, splitters)
+    # --- pack (+ bucket sizes) with the splitters still on the device --------------------------
+    keys, info, counts = _local.pack(score, target, sp_dev.to(torch.int32))
     tm.mark("pack")
-    rows = _gather_rows(torch.cat([counts, info[1:2]]), world, group).tolist()
+    rows = _gather_rows(torch.cat([counts, info[1:2], sp_dev]), world, group).tolist()
     flags = 0
     for r in rows:
         flags |= int(r[world])
     if flags:
         return None, flags
+    splitters = [int(v) for v in rows[rank][world + 1 :]]
     send = [int(c) for c in rows[rank][:world]]
     recv = [int(rows[q][rank]) for q in range(world)]
 
@@ -225,32 +229,50 @@ def _flags_only(flags: int, dev) -> torch.Tensor:
     return out
 
 
-def sharded_binary_auroc(
-    score: torch.Tensor, target: torch.Tensor, group: Optional[dist.ProcessGroup] = None
-) -> torch.Tensor:
-    """AUROC of the union of all ranks' (score, target) shards; float64[8] on score.device:
-    [auroc, P, N, 2U, flags, n_received_here, 0, 0].  flags != 0 (negative scores / soft labels
-    somewhere) means the packed representation does not apply and [0] is not valid.
-    Three host round trips in total: splitters, bucket sizes, per-rank statistics."""
+def combine_rank_stats_tensor(st: torch.Tensor):
+    """st: int64 (W, 4) rows {P_r, N_r, 2U_r >> 32, 2U_r & 0xffffffff}, ranks in ascending score
+    order.  Returns (auroc float64, P, N, 2U int64) as 0-d tensors on st.device, no host read:
+        2U = sum_r ( 2U_r + 2 * P_r * sum_{q<r} N_q )        (fits int64 for N_total < 2^31)."""
+    p, nn = st[:, 0], st[:, 1]
+    u2r = (st[:, 2] << 32) | st[:, 3]
+    neg_below = torch.cumsum(nn, 0) - nn
+    u2 = (u2r + 2 * p * neg_below).sum()
+    P, Nn = p.sum(), nn.sum()
+    den = 2.0 * P.to(torch.float64) * Nn.to(torch.float64)
+    auroc = torch.where(den == 0, torch.full_like(den, 0.5), u2.to(torch.float64) / den.clamp(min=1.0))
+    return auroc, P, Nn, u2
+
+
+def _sharded_binary_auroc(score, target, group):
+    """(float64[8] result, flags as a host int)."""
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = score.device
     tm = _PhaseTimer(dev)
     inbox, flags = _exchange_keys(score, target, group, tm)
     if flags:
-        return _flags_only(flags, dev)
-
-    # --- local sort + integrate, then the 3-integer fix-up -------------------------------------
+        return _flags_only(flags, dev), flags
+    # --- local sort + integrate, then the fix-up of three integers per rank, on the device -------
     loc = _local.auroc_from_keys(inbox)
     tm.mark("local_sort_sweep")
     st = torch.stack([loc[1], loc[2], loc[5], loc[6]]).to(torch.int64)
-    stats = []
-    for p_r, n_r, hi, lo in _gather_rows(st, world, group).tolist():
-        stats.append((int(p_r), int(n_r), (int(hi) << 32) | int(lo)))
-    auroc, P, N, u2 = combine_rank_stats(stats)
+    auroc, P, Nn, u2 = combine_rank_stats_tensor(_gather_rows(st, world, group))
+    out = torch.zeros(8, dtype=torch.float64, device=dev)
+    out[:4] = torch.stack([auroc, P.to(torch.float64), Nn.to(torch.float64), u2.to(torch.float64)])
+    out[5] = float(inbox.numel())
     tm.mark("fixup")
     tm.done(rank)
-    return torch.tensor([auroc, P, N, float(u2), 0.0, float(inbox.numel()), 0.0, 0.0], dtype=torch.float64, device=dev)
+    return out, 0
+
+
+def sharded_binary_auroc(
+    score: torch.Tensor, target: torch.Tensor, group: Optional[dist.ProcessGroup] = None
+) -> torch.Tensor:
+    """AUROC of the union of all ranks' (score, target) shards; float64[8] on score.device:
+    [auroc, P, N, 2U, flags, n_received_here, 0, 0].  flags != 0 (negative scores / soft labels
+    somewhere) means the packed representation does not apply and [0] is not valid.
+    One host read in total (bucket sizes); everything else stays on the device."""
+    return _sharded_binary_auroc(score, target, group)[0]
 
 
 def combine_rank_ap(sums, positives):
@@ -266,6 +288,33 @@ def combine_rank_ap(sums, positives):
     return total / P
 
 
+def _sharded_binary_auprc(score, target, group):
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    dev = score.device
+    tm = _PhaseTimer(dev)
+    inbox, flags = _exchange_keys(score, target, group, tm)
+    if flags:
+        return _flags_only(flags, dev), flags
+    loc, state = _local.auprc_begin(inbox)
+    tm.mark("local_sort_count")
+    pn = _gather_rows(loc[1:3].clone(), world, group)  # (W, 2) float64 {P_r, N_r}, exact integers
+    above = pn[rank + 1 :].sum(0)                      # what the ranks with higher scores hold
+    above = torch.stack([above[0], above[0] + above[1]])
+    part = _local.auprc_finish(state, above)
+    tm.mark("integrate")
+    sums = _gather_rows(part[3:4].clone(), world, group).reshape(-1)
+    total = sums.sum()
+    P, Nn = pn[:, 0].sum(), pn[:, 1].sum()
+    ap = torch.where(P == 0, torch.full_like(total, -0.0), total / P.clamp(min=1.0))
+    out = torch.zeros(8, dtype=torch.float64, device=dev)
+    out[:4] = torch.stack([ap, P, Nn, total])
+    out[5] = float(inbox.numel())
+    tm.mark("fixup")
+    tm.done(rank)
+    return out, 0
+
+
 def sharded_binary_auprc(
     score: torch.Tensor, target: torch.Tensor, group: Optional[dist.ProcessGroup] = None
 ) -> torch.Tensor:
@@ -273,29 +322,8 @@ def sharded_binary_auprc(
     of all ranks' shards; float64[8]: [ap, P, N, sum, flags, n_received_here, 0, 0].
     Precision is a ratio of prefix counts, so after the exchange the work is two-phase:
     sort + count locally -> all_gather (P_r, N_r) -> integrate with what the ranks above hold ->
-    all_gather the per-rank sums.  Four host round trips in total."""
-    world = dist.get_world_size(group)
-    rank = dist.get_rank(group)
-    dev = score.device
-    tm = _PhaseTimer(dev)
-    inbox, flags = _exchange_keys(score, target, group, tm)
-    if flags:
-        return _flags_only(flags, dev)
-
-    loc, state = _local.auprc_begin(inbox)
-    tm.mark("local_sort_count")
-    pn = _gather_rows(torch.stack([loc[1], loc[2]]).to(torch.int64), world, group).tolist()
-    pos_above = sum(int(pn[q][0]) for q in range(rank + 1, world))
-    all_above = sum(int(pn[q][0]) + int(pn[q][1]) for q in range(rank + 1, world))
-    part = _local.auprc_finish(state, pos_above, all_above)
-    tm.mark("integrate")
-    sums = _gather_rows(part[3:4].clone(), world, group).reshape(-1).tolist()
-    ap = combine_rank_ap(sums, [r[0] for r in pn])
-    P = sum(int(r[0]) for r in pn)
-    Nn = sum(int(r[1]) for r in pn)
-    tm.mark("fixup")
-    tm.done(rank)
-    return torch.tensor([ap, P, Nn, sum(sums), 0.0, float(inbox.numel()), 0.0, 0.0], dtype=torch.float64, device=dev)
+    all_gather the per-rank sums; both gathers feed device code directly, no host read."""
+    return _sharded_binary_auprc(score, target, group)[0]
 
 
 def _column_bounds(num_columns: int, world: int):
@@ -385,17 +413,16 @@ def try_sharded_compute(metric, group: Optional[dist.ProcessGroup] = None):
         ok = ok and metric.num_tasks == 1 and metric.inputs[0].dim() == 1
         if is_auroc:
             ok = ok and _resolve_weights(metric.inputs, metric.weights) is None
-    if not _agree(ok, cdev, group):
-        return None
-    metric._prepare_for_merge_state()
-    x, t = metric.inputs[0], metric.targets[0]
-    dev = cdev if cdev.type == "cuda" else compute_device(x)
-    try:
-        xs = _as_f32_scores(stage(x, dev))
-        representable = True
-    except NotImplementedError:
-        xs, representable = None, False
-    if not _agree(representable, cdev, group):
+    xs = None
+    if ok:
+        metric._prepare_for_merge_state()
+        x, t = metric.inputs[0], metric.targets[0]
+        dev = cdev if cdev.type == "cuda" else compute_device(x)
+        try:
+            xs = _as_f32_scores(stage(x, dev))
+        except NotImplementedError:
+            ok = False
+    if not _agree(ok, cdev, group):  # one agreement round: every rank qualifies, or none takes this path
         return None
     ts = stage(t, dev)
     if is_ovr:
@@ -406,11 +433,11 @@ def try_sharded_compute(metric, group: Optional[dist.ProcessGroup] = None):
         vals = vals.to(torch.float32).to(metric.device)
         return vals.mean() if metric.average == "macro" else vals
     if is_auroc:
-        out = sharded_binary_auroc(xs, ts, group)
-        if int(out[4].item()) != 0:
+        out, flags = _sharded_binary_auroc(xs, ts, group)
+        if flags:
             return None  # same answer on every rank (flags were all-gathered)
         return out[0].clone().to(metric.device)
-    out = sharded_binary_auprc(xs, ts, group)
-    if int(out[4].item()) != 0:
+    out, flags = _sharded_binary_auprc(xs, ts, group)
+    if flags:
         return None
     return out[0].to(torch.float32).to(metric.device)

@@ -339,7 +339,8 @@ def _host_splitters(splitters):
 
 def rank_pack(score: torch.Tensor, target: torch.Tensor, splitters=()):
     """(packed keys as int32 tensor [n], info int64[2] = {#positives, flags}, bucket sizes
-    int64[len(splitters) + 1])."""
+    int64[len(splitters) + 1]).  `splitters`: ascending key values, either a host sequence of ints
+    or an int32 DEVICE tensor holding their bit patterns (no host round trip to choose them)."""
     import ctypes
 
     lib = N.load()
@@ -347,18 +348,32 @@ def rank_pack(score: torch.Tensor, target: torch.Tensor, splitters=()):
     assert score.dim() == 1 and score.shape == target.shape and score.dtype == torch.float32
     score, target = score.contiguous(), target.contiguous()
     n = score.numel()
-    sp, nsp = _host_splitters(splitters)
+    on_device = isinstance(splitters, torch.Tensor)
+    if on_device:
+        assert splitters.dtype == torch.int32 and splitters.device == dev and splitters.dim() == 1
+        splitters = splitters.contiguous()
+        nsp = splitters.numel()
+    else:
+        sp, nsp = _host_splitters(splitters)
     keys = torch.empty(n, dtype=torch.int32, device=dev)
     info = torch.zeros(2, dtype=torch.int64, device=dev)
     counts = torch.zeros(nsp + 1, dtype=torch.int64, device=dev)
     scratch = _scratch(lib.te_rank_pack_scratch_bytes(n), dev)
     with torch.cuda.device(dev):
-        N.check(
-            "te_rank_pack",
-            lib.te_rank_pack(score.data_ptr(), target.data_ptr(), _DTYPE_CODE[target.dtype], n,
-                             ctypes.cast(sp, ctypes.c_void_p), nsp, keys.data_ptr(), info.data_ptr(),
-                             counts.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
-        )
+        if on_device:
+            N.check(
+                "te_rank_pack_dsplit",
+                lib.te_rank_pack_dsplit(score.data_ptr(), target.data_ptr(), _DTYPE_CODE[target.dtype], n,
+                                        splitters.data_ptr() if nsp else None, nsp, keys.data_ptr(), info.data_ptr(),
+                                        counts.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
+            )
+        else:
+            N.check(
+                "te_rank_pack",
+                lib.te_rank_pack(score.data_ptr(), target.data_ptr(), _DTYPE_CODE[target.dtype], n,
+                                 ctypes.cast(sp, ctypes.c_void_p), nsp, keys.data_ptr(), info.data_ptr(),
+                                 counts.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
+            )
     return keys, info, counts
 
 
@@ -443,19 +458,25 @@ def binary_auprc_from_keys_begin(keys: torch.Tensor):
     return out, (n, scratch)
 
 
-def binary_auprc_from_keys_finish(state, positives_above: int, samples_above: int) -> torch.Tensor:
+def binary_auprc_from_keys_finish(state, positives_above, samples_above=None) -> torch.Tensor:
     """Phase 2: float64[8]; [3] = sum over the local positives of the precision at their
-    threshold, given what the ranks holding higher scores contain."""
+    threshold, given what the ranks holding higher scores contain: two Python ints, or ONE
+    float64[2] device tensor {positives_above, samples_above} (no host read needed)."""
     lib = N.load()
     n, scratch = state
     dev = scratch.device
     out = torch.zeros(8, dtype=torch.float64, device=dev)
+    if isinstance(positives_above, torch.Tensor):
+        above = positives_above.contiguous()
+        assert above.dtype == torch.float64 and above.numel() == 2 and above.device == dev
+        args = (0.0, 0.0, above.data_ptr())
+    else:
+        args = (float(positives_above), float(samples_above), None)
     with torch.cuda.device(dev):
         N.check(
             "te_binary_auprc_from_keys_finish",
             lib.te_binary_auprc_from_keys_finish(
-                n, float(positives_above), float(samples_above), out.data_ptr(), scratch.data_ptr(),
-                scratch.numel(), _stream_ptr(dev),
+                n, args[0], args[1], args[2], out.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)
             ),
         )
     return out
