@@ -561,6 +561,14 @@ inline int sort_ipt_from_env() {
   return b;
 }
 
+inline bool hot_digits_from_env() {
+  static const bool b = [] {
+    const char* e = getenv("TE_B200_HOT_DIGITS");
+    return e ? atoi(e) != 0 : false;  // measured a wash once the bank rotation is in (profiles/r01_skew_bench.txt)
+  }();
+  return b;
+}
+
 inline bool unstable_first_pass_from_env() {
   static const bool b = [] {
     const char* e = getenv("TE_B200_UNSTABLE_FIRST");
@@ -577,6 +585,7 @@ struct RankPlan {
   size_t off_zero;      // start of the region that must be zero before launch
   size_t off_hist;      // 4*256 u32
   size_t off_ticket;    // 8 u32
+  size_t off_hot;       // 8 u32
   size_t off_scal;      // RankScalars
   size_t off_lookback;  // 4 passes * sort_tiles * 256 u32
   size_t off_agg, off_inc;
@@ -609,6 +618,7 @@ RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final)
   p.off_zero = o;
   p.off_hist = take(4 * kRadix * 4);
   p.off_ticket = take(8 * 4);
+  p.off_hot = take(8 * 4);  // hot digits: 2 per pass
   p.off_scal = take(sizeof(RankScalars));
   p.off_lookback = take((size_t)4 * 2 * p.sort_tiles * kRadix * 4);  // counts + prefixes, 4 passes
   p.off_agg = take(with_final ? (size_t)kMaxChunks * sizeof(ChunkRec) : 0);
@@ -628,17 +638,18 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
                const uint32_t* v_in0, uint32_t* v_x, uint32_t* v_y, cudaStream_t st) {
   // 4 passes: in0 -> x -> y -> x -> y
   uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
-  uint32_t* ticket = at<uint32_t>(scratch, p.off_ticket);
+  uint32_t* hot = hot_digits_from_env() ? at<uint32_t>(scratch, p.off_hot) : nullptr;
   uint32_t* lb = at<uint32_t>(scratch, p.off_lookback);
   {
     TE_PROF("digit_scan", st);
-    digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 4);
+    digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 4, hot);
   }
   TE_LAUNCH_CHECK();
   const int block = p.sort_block;
   const size_t smem = block == 256 ? onesweep_smem_bytes<uint32_t, 256>() : onesweep_smem_bytes<uint32_t, 512>();
   using PassFn = void (*)(const uint32_t*, uint32_t*, const uint32_t*, uint32_t*, uint32_t,
-                          const RadixDigit, const uint32_t*, uint32_t*, uint32_t*, const PeerPtrs);
+                          const RadixDigit, const uint32_t*, uint32_t*, uint32_t*, const PeerPtrs,
+                          const uint32_t*);
   PassFn fn = nullptr;
   if (v_in0)
     fn = block == 256 ? onesweep_pass_kernel<uint32_t, true, 256, RadixDigit>
@@ -670,7 +681,8 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
     TE_PROF(v_in0 ? "onesweep_pass_pairs" : (pass == 0 && fn_first != fn ? "onesweep_pass_keys_first" : "onesweep_pass_keys"), st);
     (pass == 0 ? fn_first : fn)<<<p.sort_tiles, block, smem_used, st>>>(kin, kout, vin, vout, p.n, RadixDigit{8 * pass},
                                                hist + pass * kRadix, lbp,
-                                               lbp + (size_t)p.sort_tiles * kRadix, PeerPtrs{});
+                                               lbp + (size_t)p.sort_tiles * kRadix, PeerPtrs{},
+                                               hot ? hot + 2 * pass : nullptr);
     TE_LAUNCH_CHECK();
     kin = kout;
     vin = vout;
@@ -1556,6 +1568,7 @@ static int partition_impl(const uint32_t* keys_in, int64_t n, const uint32_t* sp
   TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
   TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
   uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
+  uint32_t* hot = hot_digits_from_env() ? at<uint32_t>(scratch, p.off_hot) : nullptr;
   if (counts_in) {  // bucket sizes already known (te_rank_pack computed them)
     counts_to_hist_kernel<<<1, 32, 0, st>>>((const long long*)counts_in, hist, num_splitters + 1);
   } else if (n > 0) {
@@ -1571,7 +1584,7 @@ static int partition_impl(const uint32_t* keys_in, int64_t n, const uint32_t* sp
   if (n == 0) return TE_OK;
   {
     TE_PROF("digit_scan", st);
-    digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 1);
+    digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 1, hot);
   }
   TE_LAUNCH_CHECK();
   uint32_t* lb = at<uint32_t>(scratch, p.off_lookback);
@@ -1583,7 +1596,7 @@ static int partition_impl(const uint32_t* keys_in, int64_t n, const uint32_t* sp
     auto fn = onesweep_pass_kernel<uint32_t, false, B, SplitterDigit, kSortIptDefault, PEER>;            \
     const size_t smem = onesweep_smem_bytes<uint32_t, B>();                                              \
     TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
-    fn<<<p.sort_tiles, B, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist, lb, gp, pp);  \
+    fn<<<p.sort_tiles, B, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist, lb, gp, pp, hot); \
   } while (0)
   if (p.sort_ipt != kSortIptDefault) return TE_ERR_UNSUPPORTED;
   if (p.sort_block == 256) {

@@ -27,6 +27,7 @@ constexpr uint32_t kLbInclusive = 0x80000000u;
 
 // What a pass sorts by: an 8-bit digit of the key ...
 struct RadixDigit {
+  static constexpr bool kCached = false;  // one shift + mask: recomputed wherever it is needed
   int shift;
   template <typename KeyT>
   __device__ __forceinline__ uint32_t operator()(KeyT k) const {
@@ -44,6 +45,9 @@ struct PeerPtrs {
   int vec;  // 1: leave each run as 16-byte stores (head / body / tail), 0: one 4-byte store per record
 };
 struct SplitterDigit {
+  // a compare per splitter against an array that lives in local memory: the pass evaluates it
+  // once per record and keeps the 4-bit result in registers
+  static constexpr bool kCached = true;
   uint32_t sp[kMaxSplitters];
   int nsp;
   __device__ __forceinline__ uint32_t operator()(uint32_t k) const {
@@ -107,6 +111,7 @@ constexpr size_t onesweep_smem_bytes() {
 // advances 32 tiles per round trip.  Tile order = block order (see below), so nothing waits on
 // a tile that has not been dispatched.
 constexpr int kLbGroup = 32;
+constexpr uint32_t kNoHotDigit = 0xffffffffu;
 
 //
 // kUnstable: ranks inside a round are handed out in arrival order (one ATOMS.ADD with return
@@ -119,7 +124,8 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
     onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                          const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
                          uint32_t n, const DigitOp dop, const uint32_t* __restrict__ digit_base,
-                         uint32_t* lookback, uint32_t* group_prefix, const PeerPtrs peers) {
+                         uint32_t* lookback, uint32_t* group_prefix, const PeerPtrs peers,
+                         const uint32_t* __restrict__ hot_info) {
   static_assert(kSortBlock >= kRadix && kSortBlock % kRadix == 0, "one thread per digit is needed");
   static_assert(kSortIpt % 4 == 0 && 16 * kSortIpt <= 256, "ranks are packed four per register");
   constexpr int GROUPS = kSortBlock / 16;
@@ -169,31 +175,95 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
 #endif
 
   // ---- rank inside the group: ranks are group-relative (< 256), four per register ----
+  // Odd groups index their table with bit 4 of the digit flipped: the two half-warps of a warp
+  // then hit different banks for the same digit, which matters when one digit dominates.
+  const uint32_t rot = (group & 1u) << 4;
   uint32_t* gt = s_rank + group * kRadix;
   const uint32_t sub_bit = 1u << sub, sub_lt = sub_bit - 1u;
   uint32_t rk[kSortIpt / 4];
-#pragma unroll
-  for (int i = 0; i < kSortIpt; ++i) {
-    const uint32_t d = dop(key[i]);
-    uint32_t r;
-    if (kUnstable) {
-      static_assert(!(kUnstable && HAS_VAL), "payloads need a stable pass");
-      r = atomicAdd(gt + d, 1u << 16) >> 16;
-    } else {
-      atomicOr(gt + d, sub_bit);
-      __syncwarp();
-      const uint32_t e = gt[d];  // count << 16 | lanes of the group holding digit d this round
-      __syncwarp();
-      const uint32_t peers = e & 0xffffu, cnt = e >> 16;
-      const uint32_t below = __popc(peers & sub_lt);
-      if (below == 0) gt[d] = (cnt + __popc(peers)) << 16;  // lowest peer: bump count, clear mask
-      __syncwarp();
-      r = cnt + below;
+  // Skewed digits (constant exponent bits after a range partition, label-only low digits of
+  // half-precision scores, two destination ranks): same-address shared atomics serialise, up to 16
+  // deep.  digit_scan_kernel names up to two digits that hold >= 1/8 of the keys of this pass;
+  // records with those digits are ranked with a ballot and a register counter instead.
+  const uint32_t hot0 = hot_info ? hot_info[0] : kNoHotDigit;
+  const uint32_t hot1 = hot_info ? hot_info[1] : kNoHotDigit;
+  uint32_t dcache[DigitOp::kCached ? kSortIpt / 8 : 1];  // digits < 16, eight per register
+  auto remember = [&](int i, uint32_t dd) {
+    if (DigitOp::kCached) {
+      if ((i & 7) == 0)
+        dcache[i >> 3] = dd;
+      else
+        dcache[i >> 3] |= dd << (4 * (i & 7));
     }
-    if ((i & 3) == 0)
-      rk[i >> 2] = r;
-    else
-      rk[i >> 2] |= r << (8 * (i & 3));
+  };
+  auto digit_of = [&](int i) -> uint32_t {
+    return DigitOp::kCached ? (dcache[i >> 3] >> (4 * (i & 7))) & 15u : dop(key[i]);
+  };
+  if (hot0 == kNoHotDigit) {
+#pragma unroll
+    for (int i = 0; i < kSortIpt; ++i) {
+      const uint32_t dd0 = dop(key[i]);
+      remember(i, dd0);
+      const uint32_t d = dd0 ^ rot;
+      uint32_t r;
+      if (kUnstable) {
+        static_assert(!(kUnstable && HAS_VAL), "payloads need a stable pass");
+        r = atomicAdd(gt + d, 1u << 16) >> 16;
+      } else {
+        atomicOr(gt + d, sub_bit);
+        __syncwarp();
+        const uint32_t e = gt[d];  // count << 16 | lanes of the group holding digit d this round
+        __syncwarp();
+        const uint32_t peers = e & 0xffffu, cnt = e >> 16;
+        const uint32_t below = __popc(peers & sub_lt);
+        if (below == 0) gt[d] = (cnt + __popc(peers)) << 16;  // lowest peer: bump count, clear mask
+        __syncwarp();
+        r = cnt + below;
+      }
+      if ((i & 3) == 0)
+        rk[i >> 2] = r;
+      else
+        rk[i >> 2] |= r << (8 * (i & 3));
+    }
+  } else {
+    uint32_t hc0 = 0, hc1 = 0;  // records of the group seen so far with digit hot0 / hot1
+    const uint32_t hshift = lane & 16u;
+#pragma unroll
+    for (int i = 0; i < kSortIpt; ++i) {
+      const uint32_t dd = dop(key[i]);
+      remember(i, dd);
+      const bool h0 = dd == hot0, h1 = dd == hot1;
+      const uint32_t b0 = (__ballot_sync(kFull, h0) >> hshift) & 0xffffu;
+      const uint32_t b1 = (__ballot_sync(kFull, h1) >> hshift) & 0xffffu;
+      const bool cold = !(h0 || h1);
+      const uint32_t d = dd ^ rot;
+      uint32_t r = 0;
+      if (kUnstable) {
+        if (cold) r = atomicAdd(gt + d, 1u << 16) >> 16;
+      } else {
+        if (cold) atomicOr(gt + d, sub_bit);
+        __syncwarp();
+        const uint32_t e = cold ? gt[d] : 0u;
+        __syncwarp();
+        const uint32_t peers = e & 0xffffu, cnt = e >> 16;
+        const uint32_t below = __popc(peers & sub_lt);
+        if (cold && below == 0) gt[d] = (cnt + __popc(peers)) << 16;
+        __syncwarp();
+        r = cnt + below;
+      }
+      if (h0) r = hc0 + __popc(b0 & sub_lt);
+      if (h1) r = hc1 + __popc(b1 & sub_lt);
+      hc0 += __popc(b0);
+      hc1 += __popc(b1);
+      if ((i & 3) == 0)
+        rk[i >> 2] = r;
+      else
+        rk[i >> 2] |= r << (8 * (i & 3));
+    }
+    if (sub == 0) {  // nobody touched the hot digits' table entries: they get their counts now
+      gt[hot0 ^ rot] = hc0 << 16;
+      if (hot1 != kNoHotDigit) gt[hot1 ^ rot] = hc1 << 16;
+    }
   }
   TE_PHASE_MARK(2);  // rank (thread 0's warp)
   __syncthreads();
@@ -210,8 +280,9 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
   {
     const uint32_t d = tid & (kRadix - 1), h = tid >> 8;
     uint32_t part = 0;
+    static_assert(GPS % 2 == 0, "group parity must follow the loop index");
 #pragma unroll
-    for (int g = 0; g < GPS; ++g) part += s_rank[(h * GPS + g) * kRadix + d] >> 16;
+    for (int g = 0; g < GPS; ++g) part += s_rank[(h * GPS + g) * kRadix + (d ^ ((g & 1) << 4))] >> 16;
     if (SLICES > 1 && h > 0) s_base[GROUPS - 1][d] = part;  // parked in the last row, rewritten below
     __syncthreads();
     uint32_t cnt = part;
@@ -244,7 +315,7 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
 #pragma unroll
     for (int g = 0; g < GPS; ++g) {
       s_base[h * GPS + g][d] = run;
-      run += s_rank[(h * GPS + g) * kRadix + d] >> 16;
+      run += s_rank[(h * GPS + g) * kRadix + (d ^ ((g & 1) << 4))] >> 16;
     }
   }
   __syncthreads();
@@ -255,7 +326,7 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
   uint32_t pos[HAS_VAL ? kSortIpt / 2 : 1];  // tile positions, two per register (pairs only)
 #pragma unroll
   for (int i = 0; i < kSortIpt; ++i) {
-    const uint32_t d = dop(key[i]);
+    const uint32_t d = digit_of(i);
     const uint32_t r = (rk[i >> 2] >> (8 * (i & 3))) & 0xffu;
     const uint32_t p = gb[d] + r;
     s_keys[p] = key[i];
@@ -375,9 +446,12 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
   }
 }
 
-// Exclusive scan of the four 256-bin digit histograms, in place (one warp-scan chain per pass).
-__global__ void __launch_bounds__(1024) digit_scan_kernel(uint32_t* hist, int passes) {
+// Exclusive scan of the four 256-bin digit histograms, in place (one warp-scan chain per pass),
+// and the up-to-two "hot" digits of every pass: hot[2 * pass + {0, 1}] = digit holding at least
+// 1/8 of the keys (largest first), kNoHotDigit otherwise.
+__global__ void __launch_bounds__(1024) digit_scan_kernel(uint32_t* hist, int passes, uint32_t* hot) {
   __shared__ uint32_t ws[32];
+  __shared__ unsigned long long wmax[32];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int pass = tid >> 8;
   uint32_t v = pass < passes ? hist[tid] : 0u;
@@ -389,10 +463,37 @@ __global__ void __launch_bounds__(1024) digit_scan_kernel(uint32_t* hist, int pa
   }
   if (lane == 31) ws[warp] = incl;
   __syncthreads();
-  uint32_t wb = 0;
+  uint32_t wb = 0, total = 0;
   const unsigned w0 = (unsigned)pass * 8;  // first warp of this pass
-  for (unsigned w = w0; w < warp; ++w) wb += ws[w];
+  for (unsigned w = w0; w < w0 + 8; ++w) {
+    if (w < warp) wb += ws[w];
+    total += ws[w];
+  }
   if (pass < passes) hist[tid] = wb + incl - v;
+  if (!hot) return;
+  // top two bins of each pass: max-reduce (count << 8 | digit), twice
+  unsigned long long mine = ((unsigned long long)v << 8) | (tid & 255u);
+  unsigned long long first = 0;
+  for (int round = 0; round < 2; ++round) {
+    unsigned long long m = mine;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const unsigned long long u = __shfl_xor_sync(kFull, m, o);
+      m = u > m ? u : m;
+    }
+    __syncthreads();
+    if (lane == 0) wmax[warp] = m;
+    __syncthreads();
+    unsigned long long best = 0;
+    for (unsigned w = w0; w < w0 + 8; ++w) best = wmax[w] > best ? wmax[w] : best;
+    const uint32_t cnt = (uint32_t)(best >> 8), dig = (uint32_t)(best & 255u);
+    const bool is_hot = pass < passes && total > 0 && cnt >= (total + 7) / 8 && (round == 0 || first != 0);
+    if ((tid & 255u) == 0 && pass < passes) hot[2 * pass + round] = is_hot ? dig : kNoHotDigit;
+    if (round == 0) {
+      first = is_hot ? 1 : 0;
+      if ((tid & 255u) == dig) mine = 0;  // leave the winner out of the second round
+    }
+  }
 }
 
 }  // namespace te

@@ -37,7 +37,8 @@ class _PhaseTimer:
         import os
         import time
 
-        self.on = os.environ.get("TE_B200_DIST_TIMING") == "1"
+        self.level = os.environ.get("TE_B200_DIST_TIMING", "0")
+        self.on = self.level in ("1", "2")  # 2: every rank prints
         self.dev, self.t, self.time, self.rows = dev, None, time, []
         if self.on:
             torch.cuda.synchronize(dev) if dev.type == "cuda" else None
@@ -52,8 +53,8 @@ class _PhaseTimer:
         self.t = now
 
     def done(self, rank):
-        if self.on and rank == 0:
-            print("[sharded_binary_auroc] " + "  ".join(f"{n}={ms:.2f}ms" for n, ms in self.rows), flush=True)
+        if self.on and (rank == 0 or self.level == "2"):
+            print(f"[sharded r{rank}] " + "  ".join(f"{n}={ms:.2f}ms" for n, ms in self.rows), flush=True)
 
 
 class _LocalKernels:
@@ -256,11 +257,14 @@ def _sharded_binary_auroc(score, target, group):
     loc = _local.auroc_from_keys(inbox)
     tm.mark("local_sort_sweep")
     st = torch.stack([loc[1], loc[2], loc[5], loc[6]]).to(torch.int64)
-    auroc, P, Nn, u2 = combine_rank_stats_tensor(_gather_rows(st, world, group))
+    tm.mark("fix:stack")
+    rows = _gather_rows(st, world, group)
+    tm.mark("fix:gather")
+    auroc, P, Nn, u2 = combine_rank_stats_tensor(rows)
     out = torch.zeros(8, dtype=torch.float64, device=dev)
     out[:4] = torch.stack([auroc, P.to(torch.float64), Nn.to(torch.float64), u2.to(torch.float64)])
     out[5] = float(inbox.numel())
-    tm.mark("fixup")
+    tm.mark(f"fixup(n_recv={inbox.numel()})")
     tm.done(rank)
     return out, 0
 
