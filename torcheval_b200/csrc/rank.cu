@@ -1178,15 +1178,10 @@ __global__ void __launch_bounds__(1024)
   if (tid < 16 * kWarp) sh[tid] = 0;
   // splitters either came with the launch (host array) or are read from device memory, so that a
   // caller can choose them on the device without a round trip through the host
-  if (tid < (unsigned)dop_in.nsp) s_sp[tid] = splitters_dev ? splitters_dev[tid] : dop_in.sp[tid];
+  if (tid < kMaxSplitters + 1)
+    s_sp[tid] = (int)tid < dop_in.nsp ? (splitters_dev ? splitters_dev[tid] : dop_in.sp[tid]) : 0xffffffffu;
   __syncthreads();
-  const int nsp = dop_in.nsp;
-  auto dop = [&](uint32_t k) {
-    uint32_t b = 0;
-#pragma unroll 1
-    for (int i = 0; i < nsp; ++i) b += s_sp[i] <= k ? 1u : 0u;
-    return b;
-  };
+  auto dop = [&](uint32_t k) { return dop_in.eval(k, s_sp); };
   uint32_t npos = 0, bad_label = 0, neg_score = 0;
   const uint32_t ngroups = (n + 3) / 4;
   for (uint32_t g = blockIdx.x * blockDim.x + tid; g < ngroups; g += gridDim.x * blockDim.x) {

@@ -33,6 +33,11 @@ struct RadixDigit {
   __device__ __forceinline__ uint32_t operator()(KeyT k) const {
     return (uint32_t)(k >> shift) & (kRadix - 1);
   }
+  __device__ __forceinline__ void stage(uint32_t*, unsigned) const {}
+  template <typename KeyT>
+  __device__ __forceinline__ uint32_t eval(KeyT k, const uint32_t*) const {
+    return (*this)(k);
+  }
 };
 // ... or the index of the range the key falls in, given up to 15 ascending splitters
 // (bucket = #{splitters <= key}): the partition step of the distributed sample sort.
@@ -55,6 +60,24 @@ struct SplitterDigit {
 #pragma unroll 1
     for (int i = 0; i < nsp; ++i) b += sp[i] <= k ? 1u : 0u;  // nsp = ranks - 1, usually 1..7
     return b;
+  }
+  // The pass kernel stages the splitters in shared memory (padded to 16 words with 0xffffffff) and
+  // finds the bucket with a branch-free binary search: log2 steps, every step one shared load that
+  // is conflict-free (<= 15 consecutive words, equal addresses broadcast).  The linear scan above
+  // made the partition pass 2-4x slower than a radix pass at 8-16 ranks
+  // (profiles/r01_part_bench.txt).
+  __device__ __forceinline__ void stage(uint32_t* s, unsigned tid) const {
+    if (tid < 16) s[tid] = (int)tid < nsp ? sp[tid] : 0xffffffffu;
+  }
+  __device__ __forceinline__ uint32_t eval(uint32_t k, const uint32_t* s) const {
+    uint32_t b = 0;
+#pragma unroll
+    for (int step = 8; step >= 1; step >>= 1) {
+      if (step <= nsp) {  // uniform: 1 step for 2 ranks, 3 for 8, 4 for 16
+        if (s[b + step - 1] <= k) b += step;
+      }
+    }
+    return min(b, (uint32_t)nsp);  // (a padding word compares equal only to the key 0xffffffff)
   }
 };
 
@@ -97,7 +120,7 @@ constexpr size_t onesweep_stage_bytes() {
 template <typename KeyT, int kSortBlock, int kSortIpt = kSortIptDefault>
 constexpr size_t onesweep_smem_bytes() {
   return onesweep_stage_bytes<KeyT, kSortBlock, kSortIpt>() +
-         sizeof(uint32_t) * ((kSortBlock / 16) * kRadix + 2 * kRadix + kRadix / kWarp + 4 + 2 * (kMaxSplitters + 1));
+         sizeof(uint32_t) * ((kSortBlock / 16) * kRadix + 2 * kRadix + kRadix / kWarp + 4 + 2 * (kMaxSplitters + 1) + 16 + 2 * (kMaxSplitters + 1));
 }
 
 // Cross-tile offsets: two-level decoupled look-back.  With ~30-60 million tiles per second per
@@ -139,6 +162,8 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
   uint32_t* s_goff = &s_base[GROUPS][0];       // 2*256 words: also the slice starts of the digit phase
   uint32_t* s_wsum = s_goff + 2 * kRadix;
   uint32_t* s_runs = s_wsum + kRadix / kWarp + 4;  // peer scatter: tile-local start, count per bucket
+  uint32_t* s_sp = s_runs + 2 * (kMaxSplitters + 1);  // splitters (partition passes)
+  unsigned long long* s_peer = reinterpret_cast<unsigned long long*>(s_sp + 16);  // inbox bases
 
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   TE_PHASE_BEGIN();
@@ -162,6 +187,8 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
     key[i] = r < valid ? keys_in[base + r] : ~(KeyT)0;  // padding sorts last, is never written
   }
   for (int i = tid; i < GROUPS * kRadix; i += kSortBlock) s_rank[i] = 0u;
+  dop.stage(s_sp, tid);
+  if (kPeerScatter && tid <= (unsigned)kMaxSplitters) s_peer[tid] = peers.p[tid];
   __syncthreads();
   TE_PHASE_MARK(0);  // setup
 #ifdef TE_PHASE_STATS
@@ -197,12 +224,12 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
     }
   };
   auto digit_of = [&](int i) -> uint32_t {
-    return DigitOp::kCached ? (dcache[i >> 3] >> (4 * (i & 7))) & 15u : dop(key[i]);
+    return DigitOp::kCached ? (dcache[i >> 3] >> (4 * (i & 7))) & 15u : dop.eval(key[i], s_sp);
   };
   if (hot0 == kNoHotDigit) {
 #pragma unroll
     for (int i = 0; i < kSortIpt; ++i) {
-      const uint32_t dd0 = dop(key[i]);
+      const uint32_t dd0 = dop.eval(key[i], s_sp);
       remember(i, dd0);
       const uint32_t d = dd0 ^ rot;
       uint32_t r;
@@ -230,7 +257,7 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
     const uint32_t hshift = lane & 16u;
 #pragma unroll
     for (int i = 0; i < kSortIpt; ++i) {
-      const uint32_t dd = dop(key[i]);
+      const uint32_t dd = dop.eval(key[i], s_sp);
       remember(i, dd);
       const bool h0 = dd == hot0, h1 = dd == hot1;
       const uint32_t b0 = (__ballot_sync(kFull, h0) >> hshift) & 0xffffu;
@@ -377,25 +404,32 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
     // NVLink stores: a bucket's run is contiguous both in s_keys and in its inbox, so it leaves as
     // 16-byte stores (scalar head up to the first 16-byte boundary of the destination, scalar tail)
     if (peers.vec) {
-      const int nb = dop.nsp + 1;
-      for (int d = 0; d < nb; ++d) {
+      // the 16 warps are dealt out over the buckets (16 / buckets warps each); a warp walks its
+      // share of the run with one 16-byte store per lane and step
+      const uint32_t nb = (uint32_t)dop.nsp + 1u;
+      constexpr uint32_t kWarps = kSortBlock / kWarp;
+      const uint32_t wpr = nb < kWarps ? kWarps / nb : 1u;  // warps per run
+      for (uint32_t d = warp / wpr; d < nb; d += kWarps / wpr) {
+        const uint32_t j = warp % wpr;
         const uint32_t rs = s_runs[d];
         if (rs >= valid) break;  // runs are in tile order; padding sits at the very end
         const uint32_t rc = min(s_runs[kMaxSplitters + 1 + d], valid - rs);
         if (rc == 0) continue;
-        uint32_t* dst = reinterpret_cast<uint32_t*>(peers.p[d]) + s_goff[d];  // dst[p], p = tile position
+        uint32_t* dst = reinterpret_cast<uint32_t*>(s_peer[d]) + s_goff[d];  // dst[p], p = tile position
         const uint32_t mis = (uint32_t)((reinterpret_cast<uintptr_t>(dst + rs) >> 2) & 3u);
         const uint32_t head = min(rc, (4u - mis) & 3u);
-        if (tid < head) dst[rs + tid] = s_keys[rs + tid];
         const uint32_t body = (rc - head) >> 2;
-        for (uint32_t q = tid; q < body; q += kSortBlock) {
+        const uint32_t done = head + 4 * body;
+        if (j == 0) {  // scalar head and tail (<= 3 records each)
+          if (lane < head) dst[rs + lane] = s_keys[rs + lane];
+          if (lane >= 8 && lane - 8 < rc - done) dst[rs + done + lane - 8] = s_keys[rs + done + lane - 8];
+        }
+        for (uint32_t q = j * kWarp + lane; q < body; q += wpr * kWarp) {
           const uint32_t p = rs + head + 4 * q;
           uint4 v;
           v.x = s_keys[p], v.y = s_keys[p + 1], v.z = s_keys[p + 2], v.w = s_keys[p + 3];
           *reinterpret_cast<uint4*>(dst + p) = v;
         }
-        const uint32_t done = head + 4 * body;
-        if (tid < rc - done) dst[rs + done + tid] = s_keys[rs + done + tid];
       }
       TE_PHASE_MARK(7);
       return;
@@ -406,10 +440,10 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
   for (int k = 0; k < kSortIpt; ++k) {
     const uint32_t p = tid + k * kSortBlock;
     const KeyT kk = s_keys[p];
-    const uint32_t d = dop(kk);
+    const uint32_t d = dop.eval(kk, s_sp);
     if (p < valid) {
       if (kPeerScatter)  // the digit is the destination rank: store over NVLink into its inbox
-        reinterpret_cast<KeyT*>(peers.p[d])[s_goff[d] + p] = kk;
+        reinterpret_cast<KeyT*>(s_peer[d])[s_goff[d] + p] = kk;
       else
         keys_out[s_goff[d] + p] = kk;
     }
