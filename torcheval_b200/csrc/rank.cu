@@ -218,8 +218,9 @@ __global__ void __launch_bounds__(kIngestBlock, 1)
 // ------------------------------------------------------------------------------------------
 constexpr int kFinBlock = 256;
 constexpr int kFinIpt = 16;
-constexpr int kFinTile = kFinBlock * kFinIpt;
-constexpr int kMaxChunks = 1024;
+constexpr int kFinStep = kWarp * kFinIpt;  // records a warp takes per step
+constexpr int kFinWarpsPerSm = 32;         // chunks (= warps) per SM the sweep is cut into
+constexpr int kMaxChunks = 8192;
 
 struct FState {
   uint32_t S;   // negatives in the segment
@@ -236,12 +237,22 @@ __device__ __forceinline__ FState f_combine(const FState& a, const FState& b) { 
   r.Mp = b.F ? b.Mp : a.Mp;
   return r;
 }
+template <bool WITH_POS>
 __device__ __forceinline__ FState f_shfl_up(const FState& v, int o) {
   FState u;
   u.S = __shfl_up_sync(kFull, v.S, o);
   u.M = __shfl_up_sync(kFull, v.M, o);
-  u.Mp = __shfl_up_sync(kFull, v.Mp, o);
+  u.Mp = WITH_POS ? __shfl_up_sync(kFull, v.Mp, o) : 0u;
   u.F = __shfl_up_sync(kFull, v.F, o);
+  return u;
+}
+template <bool WITH_POS>
+__device__ __forceinline__ FState f_shfl(const FState& v, int src) {
+  FState u;
+  u.S = __shfl_sync(kFull, v.S, src);
+  u.M = __shfl_sync(kFull, v.M, src);
+  u.Mp = WITH_POS ? __shfl_sync(kFull, v.Mp, src) : 0u;
+  u.F = __shfl_sync(kFull, v.F, src);
   return u;
 }
 
@@ -253,51 +264,61 @@ struct alignas(16) ChunkRec {
   unsigned long long pad;
 };
 
+// The sorted array is cut into nchunks contiguous chunks of steps_per_chunk * 512 records, one per
+// WARP: a warp carries its running state in registers from step to step, the only communication
+// inside a step is one warp scan, and nothing is shared between warps (no shared memory, no
+// block barrier).  The geometry depends on n and the SM count only, so separate launches (count
+// sweep, integrate sweep, the two halves of the rank-sharded AUPRC) agree on it.
 struct ChunkGeom {
-  uint32_t nchunks, tiles_per_chunk;
+  uint32_t nchunks, steps_per_chunk;
 };
-inline ChunkGeom chunk_geom(uint32_t fin_tiles, int sms, int ctas_per_sm) {
+inline ChunkGeom chunk_geom(uint32_t n, int sms) {
   ChunkGeom g;
-  uint32_t want = (uint32_t)sms * (uint32_t)(ctas_per_sm > 0 ? ctas_per_sm : 1);
+  uint32_t steps = (n + kFinStep - 1) / kFinStep;
+  if (steps < 1) steps = 1;
+  uint32_t want = (uint32_t)sms * (uint32_t)kFinWarpsPerSm;
   if (want > (uint32_t)kMaxChunks) want = kMaxChunks;
-  if (want > fin_tiles) want = fin_tiles;
+  if (want > steps) want = steps;
   if (want < 1) want = 1;
-  g.tiles_per_chunk = (fin_tiles + want - 1) / want;
-  if (g.tiles_per_chunk < 1) g.tiles_per_chunk = 1;
-  g.nchunks = (fin_tiles + g.tiles_per_chunk - 1) / g.tiles_per_chunk;
-  if (g.nchunks < 1) g.nchunks = 1;
+  g.steps_per_chunk = (steps + want - 1) / want;
+  g.nchunks = (steps + g.steps_per_chunk - 1) / g.steps_per_chunk;
   return g;
 }
 
 // MODE 0: counting / AUROC sweep -> rec[chunk].   MODE 1: AUPRC integrate sweep, starts from
 // excl[chunk] (global state before the chunk) -> partial[chunk] (double bits).
-template <int MODE>
-__global__ void __launch_bounds__(kFinBlock)
-    rank_chunk_kernel(const uint32_t* __restrict__ keys, uint32_t n, uint32_t tiles_per_chunk,
-                      ChunkRec* rec, const FState* __restrict__ excl_in,
+template <int MODE, bool POS = (MODE == 1)>
+__global__ void __launch_bounds__(kFinBlock, kFinWarpsPerSm / (kFinBlock / kWarp))
+    rank_chunk_kernel(const uint32_t* __restrict__ keys, uint32_t n, uint32_t steps_per_chunk,
+                      uint32_t nchunks, ChunkRec* rec, const FState* __restrict__ excl_in,
                       const RankScalars* __restrict__ scal, unsigned long long* partial,
                       double pos_above, double cnt_above, const double* __restrict__ above_dev) {
-  __shared__ FState s_warp[kFinBlock / kWarp];
-  __shared__ unsigned long long s_red[3][kFinBlock / kWarp];
-  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const uint32_t chunk = blockIdx.x;
-  const uint32_t tile0 = chunk * tiles_per_chunk;
+  // POS: also track WHERE the current tie group started (needed by the AUPRC integrate sweep and
+  // by the count sweep that feeds it; plain AUROC leaves it out)
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t chunk = blockIdx.x * (kFinBlock / kWarp) + (threadIdx.x >> 5);
+  if (chunk >= nchunks) return;
+  const uint64_t begin64 = (uint64_t)chunk * steps_per_chunk * kFinStep;
+  if (begin64 >= n) return;
+  const uint32_t begin = (uint32_t)begin64;
+  const uint32_t end = (uint32_t)min((uint64_t)n, begin64 + (uint64_t)steps_per_chunk * kFinStep);
 
   FState carry = MODE == 1 ? excl_in[chunk] : f_identity();
   unsigned long long accA = 0, accP = 0, accLead = 0;
   double accD = 0.0;
   // pos_above / cnt_above: positives / samples with a score above everything in `keys` that live
-  // on other ranks (0 when `keys` is the whole sample set)
-  // (above_dev, if given, holds the same two numbers in device memory)
+  // on other ranks (0 when `keys` is the whole sample set); above_dev, if given, holds the same
+  // two numbers in device memory
   if (MODE == 1 && above_dev) pos_above = above_dev[0], cnt_above = above_dev[1];
   const double ptot = MODE == 1 ? (double)scal->positives + pos_above : 0.0;
 
-  // register double buffering: the loads of tile t+1 are in flight while tile t is processed
-  auto load_tile = [&](uint32_t tl, uint32_t (&dst)[kFinIpt], uint32_t& prev_key) {
-    const uint64_t b = (uint64_t)(tile0 + tl) * kFinTile;
-    if (tl >= tiles_per_chunk || b >= n) return;
-    const uint32_t j0 = (uint32_t)b + tid * kFinIpt;
-    if (j0 + kFinIpt <= n) {
+  // score of the record just before this lane's 16 (lane 0: carried from the previous step)
+  uint32_t last = begin > 0 ? keys[begin - 1] >> 1 : 0u;
+
+  auto load_step = [&](uint32_t at, uint32_t (&dst)[kFinIpt]) {
+    if (at >= end) return;
+    const uint32_t j0 = at + lane * kFinIpt;
+    if (at + kFinStep <= end) {
 #pragma unroll
       for (int q = 0; q < kFinIpt / 4; ++q) {
         const int4 a = ld_stream_v4(keys + j0 + 4 * q);
@@ -305,28 +326,29 @@ __global__ void __launch_bounds__(kFinBlock)
       }
     } else {
 #pragma unroll
-      for (int j = 0; j < kFinIpt; ++j) dst[j] = (j0 + j < n) ? keys[j0 + j] : 0u;
+      for (int j = 0; j < kFinIpt; ++j) dst[j] = (j0 + j < end) ? keys[j0 + j] : 0u;
     }
-    prev_key = (j0 > 0 && j0 < n) ? keys[j0 - 1] : 0u;
   };
-  uint32_t knext[kFinIpt], prev_next = 0;
-  load_tile(0, knext, prev_next);
+  uint32_t knext[kFinIpt];
+  load_step(begin, knext);
 
-  for (uint32_t tl = 0; tl < tiles_per_chunk; ++tl) {
-    const uint64_t base64 = (uint64_t)(tile0 + tl) * kFinTile;
-    if (base64 >= n) break;
-    const uint32_t i0 = (uint32_t)base64 + tid * kFinIpt;
-
+  for (uint32_t at = begin; at < end; at += kFinStep) {
     uint32_t k[kFinIpt];
 #pragma unroll
     for (int j = 0; j < kFinIpt; ++j) k[j] = knext[j];
-    uint32_t prev = prev_next >> 1;
-    load_tile(tl + 1, knext, prev_next);
-    const uint32_t cnt = i0 < n ? min((uint32_t)kFinIpt, n - i0) : 0u;
+    load_step(at + kFinStep, knext);  // in flight while this step is processed
+    const uint32_t i0 = at + lane * kFinIpt;
+    const uint32_t cnt = i0 < end ? min((uint32_t)kFinIpt, end - i0) : 0u;
 
-    // phase 1: thread aggregate + group-start mask
-    // one local pass: thread aggregate, group-start mask and (MODE 0) the local sums of the
-    // AUROC integrand, all relative to the start of this thread's 16 keys and in 32-bit
+    // score before my first record: the previous lane's last one (a lane with fewer than 16
+    // records is followed only by empty lanes, so its k[15] is never looked at)
+    uint32_t prev = __shfl_up_sync(kFull, k[kFinIpt - 1] >> 1, 1);
+    if (lane == 0) prev = last;
+    const uint32_t tail = (end - at >= (uint32_t)kFinStep) ? k[kFinIpt - 1] >> 1 : 0u;
+    last = __shfl_sync(kFull, tail, 31);  // only used if a full step follows, i.e. this one was full
+
+    // one local pass: lane aggregate, group-start mask and (MODE 0) the local sums of the AUROC
+    // integrand, all relative to the start of this lane's 16 records and in 32-bit
     FState mine = f_identity();
     uint32_t starts = 0;
     uint32_t n_pre = 0, n_post = 0;  // positives before / after the first group start seen here
@@ -336,14 +358,14 @@ __global__ void __launch_bounds__(kFinBlock)
 #pragma unroll
     for (int j = 0; j < kFinIpt; ++j) {
       if (j < (int)cnt) {
-        const uint32_t s = k[j] >> 1;
-        const bool st = (j == 0 && i0 == 0) || s != prev;
-        prev = s;
+        const uint32_t sc = k[j] >> 1;
+        const bool st = (j == 0 && i0 == 0) || sc != prev;
+        prev = sc;
         if (st) {
           starts |= 1u << j;
           mine.F = 1;
           mine.M = mine.S;
-          mine.Mp = i0 + j;
+          if (POS) mine.Mp = i0 + j;
           lgs = mine.S;
         }
         if (k[j] & 1u) {
@@ -362,30 +384,21 @@ __global__ void __launch_bounds__(kFinBlock)
       }
     }
 
-    // block exclusive scan of the thread aggregates
+    // warp scan of the lane aggregates
     FState incl = mine;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      const FState u = f_shfl_up(incl, o);
+      const FState u = f_shfl_up<POS>(incl, o);
       if (lane >= (unsigned)o) incl = f_combine(u, incl);
     }
-    if (lane == 31) s_warp[warp] = incl;
-    FState excl = f_shfl_up(incl, 1);
+    FState excl = f_shfl_up<POS>(incl, 1);
     if (lane == 0) excl = f_identity();
-    __syncthreads();
-    FState wprefix = f_identity(), tile_agg = f_identity();
-#pragma unroll
-    for (int w = 0; w < kFinBlock / kWarp; ++w) {
-      const FState x = s_warp[w];
-      if (w < (int)warp) wprefix = f_combine(wprefix, x);
-      tile_agg = f_combine(tile_agg, x);
-    }
-    __syncthreads();  // s_warp is rewritten by the next tile
-    const FState g = f_combine(carry, f_combine(wprefix, excl));
+    const FState step_agg = f_shfl<POS>(incl, 31);
+    const FState g = f_combine(carry, excl);
 
     if (MODE == 0) {
       // a positive contributes (#neg before it) + (#neg before its tie group): with g = state
-      // of everything before this thread inside the chunk,
+      // of everything before this lane inside the chunk,
       //   "post" positives: (g.S + lc) + (g.S + lgs)
       //   "pre"  positives: (g.S + lc) + g.M      (group known inside the chunk: g.F)
       //                     (g.S + lc) + [E.M]    (group older than the chunk: counted in lead)
@@ -416,72 +429,74 @@ __global__ void __launch_bounds__(kFinBlock)
         }
       }
     }
-    carry = f_combine(carry, tile_agg);
+    carry = f_combine(carry, step_agg);
   }
 
   if (MODE == 0) {
     accA = warp_sum(accA);
     accP = warp_sum(accP);
     accLead = warp_sum(accLead);
-    if (lane == 0) s_red[0][warp] = accA, s_red[1][warp] = accP, s_red[2][warp] = accLead;
-    __syncthreads();
-    if (tid == 0) {
+    if (lane == 0) {
       ChunkRec r;
       r.st = carry;
-      r.A = r.P = r.lead = r.pad = 0;
-      for (int w = 0; w < kFinBlock / kWarp; ++w) r.A += s_red[0][w], r.P += s_red[1][w], r.lead += s_red[2][w];
+      r.A = accA, r.P = accP, r.lead = accLead, r.pad = 0;
       rec[chunk] = r;
     }
   } else {
-    accD = warp_sum(accD);
-    if (lane == 0) s_red[0][warp] = (unsigned long long)__double_as_longlong(accD);
-    __syncthreads();
-    if (tid == 0) {
-      double t = 0.0;
-      for (int w = 0; w < kFinBlock / kWarp; ++w) t += __longlong_as_double((long long)s_red[0][w]);
-      partial[chunk] = (unsigned long long)__double_as_longlong(t);
-    }
+    accD = warp_sum(accD);  // butterfly: the same bits in every lane, every run
+    if (lane == 0) partial[chunk] = (unsigned long long)__double_as_longlong(accD);
   }
 }
 
-// One CTA: exclusive scan of the chunk states.  MODE 0 finishes AUROC (out[] as documented at
-// te_binary_auroc); MODE 1 publishes excl[chunk] for the AUPRC integrate sweep.
+// One CTA: exclusive scan of the chunk states, 1024 at a time.  MODE 0 finishes AUROC (out[] as
+// documented at te_binary_auroc); MODE 1 publishes excl[chunk] for the AUPRC integrate sweep.
 template <int MODE>
-__global__ void __launch_bounds__(kMaxChunks)
+__global__ void __launch_bounds__(1024)
     rank_chunk_scan_kernel(const ChunkRec* __restrict__ rec, uint32_t nchunks, uint32_t n,
                            const RankScalars* __restrict__ scal, FState* excl_out, double* out) {
-  __shared__ FState s_warp[kMaxChunks / kWarp];
-  __shared__ unsigned long long s_u[kMaxChunks / kWarp];
+  __shared__ FState s_warp[32];
+  __shared__ unsigned long long s_u[32];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  ChunkRec r;
-  r.st = f_identity();
-  r.A = r.P = r.lead = 0;
-  if (tid < nchunks) r = rec[tid];
-  FState incl = r.st;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const FState u = f_shfl_up(incl, o);
-    if (lane >= (unsigned)o) incl = f_combine(u, incl);
-  }
-  if (lane == 31) s_warp[warp] = incl;
-  FState excl = f_shfl_up(incl, 1);
-  if (lane == 0) excl = f_identity();
-  __syncthreads();
-  FState wprefix = f_identity();
-  for (int w = 0; w < (int)warp; ++w) wprefix = f_combine(wprefix, s_warp[w]);
-  excl = f_combine(wprefix, excl);
-  if (MODE == 1) {
-    if (tid < nchunks) excl_out[tid] = excl;
-    return;
-  }
+  FState carry = f_identity();
   unsigned long long u2 = 0;
-  if (tid < nchunks) u2 = r.A + (unsigned long long)excl.S * (2ull * r.P - r.lead) + (unsigned long long)excl.M * r.lead;
+  for (uint32_t base = 0; base < nchunks; base += 1024) {
+    const uint32_t i = base + tid;
+    ChunkRec r;
+    r.st = f_identity();
+    r.A = r.P = r.lead = 0;
+    if (i < nchunks) r = rec[i];
+    FState incl = r.st;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const FState u = f_shfl_up<true>(incl, o);
+      if (lane >= (unsigned)o) incl = f_combine(u, incl);
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    FState excl = f_shfl_up<true>(incl, 1);
+    if (lane == 0) excl = f_identity();
+    __syncthreads();
+    FState wprefix = f_identity(), strip = f_identity();
+    for (int w = 0; w < 32; ++w) {
+      const FState x = s_warp[w];
+      if (w < (int)warp) wprefix = f_combine(wprefix, x);
+      strip = f_combine(strip, x);
+    }
+    excl = f_combine(carry, f_combine(wprefix, excl));
+    if (MODE == 1) {
+      if (i < nchunks) excl_out[i] = excl;
+    } else if (i < nchunks) {
+      u2 += r.A + (unsigned long long)excl.S * (2ull * r.P - r.lead) + (unsigned long long)excl.M * r.lead;
+    }
+    carry = f_combine(carry, strip);
+    __syncthreads();  // s_warp is rewritten by the next strip
+  }
+  if (MODE == 1) return;
   u2 = warp_sum(u2);
   if (lane == 0) s_u[warp] = u2;
   __syncthreads();
   if (tid == 0) {
     unsigned long long tu = 0;
-    for (int w = 0; w < kMaxChunks / kWarp; ++w) tu += s_u[w];
+    for (int w = 0; w < 32; ++w) tu += s_u[w];
     const double P = (double)scal->positives, N = (double)n - P;
     out[0] = (P * N == 0.0) ? 0.5 : ((double)tu * 0.5) / (P * N);
     out[1] = P;
@@ -580,7 +595,7 @@ inline bool unstable_first_pass_from_env() {
 struct RankPlan {
   uint32_t n;
   int sort_block, sort_ipt;
-  uint32_t sort_tiles, fin_tiles;
+  uint32_t sort_tiles;
   size_t off_keys_a, off_keys_b, off_vals_a, off_vals_b;
   size_t off_zero;      // start of the region that must be zero before launch
   size_t off_hist;      // 4*256 u32
@@ -601,9 +616,7 @@ RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final)
   p.sort_ipt = sort_ipt_from_env();
   const int64_t sort_tile = (int64_t)p.sort_block * p.sort_ipt;
   p.sort_tiles = (uint32_t)((n64 + sort_tile - 1) / sort_tile);
-  p.fin_tiles = (uint32_t)((n64 + kFinTile - 1) / kFinTile);
   if (p.sort_tiles == 0) p.sort_tiles = 1;
-  if (p.fin_tiles == 0) p.fin_tiles = 1;
   size_t o = 0;
   auto take = [&](size_t bytes) {
     const size_t at = o;
@@ -732,33 +745,37 @@ int launch_ingest_dtype(const float* score, const void* target, int32_t dt, cons
 
 // fused scan / integrate over the sorted packed keys + final division (both modes)
 int finish_packed(const RankPlan& p, const uint32_t* ka, int mode, double* out, void* scratch, int sms,
-                  cudaStream_t st) {
+                  cudaStream_t st, bool track_pos = false) {
   const int64_t n = p.n;
   ChunkRec* rec = at<ChunkRec>(scratch, p.off_agg);
   FState* excl = at<FState>(scratch, p.off_inc);
   unsigned long long* partial = at<unsigned long long>(scratch, p.off_partial);
   const RankScalars* scal = at<RankScalars>(scratch, p.off_scal);
-  int occ = 0;  // one resident wave: every chunk runs concurrently, all the same length
-  TE_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-      &occ, mode == 0 ? rank_chunk_kernel<0> : rank_chunk_kernel<1>, kFinBlock, 0));
-  const ChunkGeom cg = chunk_geom(p.fin_tiles, sms, occ);
+  const ChunkGeom cg = chunk_geom(p.n, sms);
   const uint32_t nchunks = n > 0 ? cg.nchunks : 0;
+  const uint32_t grid = (nchunks + kFinBlock / kWarp - 1) / (kFinBlock / kWarp);
   if (nchunks) {
     TE_PROF("rank_chunk_sweep", st);
-    rank_chunk_kernel<0><<<nchunks, kFinBlock, 0, st>>>(ka, p.n, cg.tiles_per_chunk, rec, nullptr, scal, nullptr, 0.0, 0.0, nullptr);
+    if (mode == 1 || track_pos)
+      rank_chunk_kernel<0, true><<<grid, kFinBlock, 0, st>>>(ka, p.n, cg.steps_per_chunk, nchunks, rec, nullptr,
+                                                             scal, nullptr, 0.0, 0.0, nullptr);
+    else
+      rank_chunk_kernel<0><<<grid, kFinBlock, 0, st>>>(ka, p.n, cg.steps_per_chunk, nchunks, rec, nullptr, scal,
+                                                       nullptr, 0.0, 0.0, nullptr);
   }
   TE_LAUNCH_CHECK();
   if (mode == 0) {
     TE_PROF("rank_chunk_scan", st);
-    rank_chunk_scan_kernel<0><<<1, kMaxChunks, 0, st>>>(rec, nchunks, p.n, scal, nullptr, out);
+    rank_chunk_scan_kernel<0><<<1, 1024, 0, st>>>(rec, nchunks, p.n, scal, nullptr, out);
   } else {
     if (nchunks) {
       {
         TE_PROF("rank_chunk_scan", st);
-        rank_chunk_scan_kernel<1><<<1, kMaxChunks, 0, st>>>(rec, nchunks, p.n, scal, excl, nullptr);
+        rank_chunk_scan_kernel<1><<<1, 1024, 0, st>>>(rec, nchunks, p.n, scal, excl, nullptr);
       }
       TE_PROF("rank_chunk_integrate", st);
-      rank_chunk_kernel<1><<<nchunks, kFinBlock, 0, st>>>(ka, p.n, cg.tiles_per_chunk, nullptr, excl, scal, partial, 0.0, 0.0, nullptr);
+      rank_chunk_kernel<1><<<grid, kFinBlock, 0, st>>>(ka, p.n, cg.steps_per_chunk, nchunks, nullptr, excl, scal,
+                                                       partial, 0.0, 0.0, nullptr);
     }
     TE_PROF("rank_reduce", st);
     rank_reduce_kernel<1><<<1, 1024, 0, st>>>(partial, nchunks, p.n, scal, out);
@@ -1642,23 +1659,13 @@ static int rank_from_keys(const uint32_t* keys, int64_t n, int mode, double* out
     rc = run_passes(p, scratch, keys, ka, kb, nullptr, nullptr, nullptr, st);  // sorted keys end in kb
     if (rc) return rc;
   }
-  const int rc = finish_packed(p, kb, 0, out, scratch, sms, st);
+  const int rc = finish_packed(p, kb, 0, out, scratch, sms, st, mode == 1);
   if (rc || mode == 0 || n == 0) return rc;
-  int occ = 0;
-  TE_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, rank_chunk_kernel<1>, kFinBlock, 0));
-  const ChunkGeom cg = chunk_geom(p.fin_tiles, sms, occ);
-  // the count sweep ran with the geometry of rank_chunk_kernel<0>; the integrate sweep needs its own
-  // chunk records when the two kernels' occupancies differ, so recount with that geometry
-  int occ0 = 0;
-  TE_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, rank_chunk_kernel<0>, kFinBlock, 0));
-  ChunkRec* rec = at<ChunkRec>(scratch, p.off_agg);
-  const RankScalars* scal = at<RankScalars>(scratch, p.off_scal);
-  if (chunk_geom(p.fin_tiles, sms, occ0).tiles_per_chunk != cg.tiles_per_chunk) {
-    TE_PROF("rank_chunk_sweep", st);
-    rank_chunk_kernel<0><<<cg.nchunks, kFinBlock, 0, st>>>(kb, p.n, cg.tiles_per_chunk, rec, nullptr, scal, nullptr, 0.0, 0.0, nullptr);
-  }
+  const ChunkGeom cg = chunk_geom(p.n, sms);
   TE_PROF("rank_chunk_scan", st);
-  rank_chunk_scan_kernel<1><<<1, kMaxChunks, 0, st>>>(rec, cg.nchunks, p.n, scal, at<FState>(scratch, p.off_inc), nullptr);
+  rank_chunk_scan_kernel<1><<<1, 1024, 0, st>>>(at<ChunkRec>(scratch, p.off_agg), cg.nchunks, p.n,
+                                                at<RankScalars>(scratch, p.off_scal),
+                                                at<FState>(scratch, p.off_inc), nullptr);
   TE_LAUNCH_CHECK();
   return TE_OK;
 }
@@ -1682,19 +1689,18 @@ extern "C" int te_binary_auprc_from_keys_finish(int64_t n, double positives_abov
   const RankPlan p = make_plan(n, false, true, true);
   if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
   cudaStream_t st = (cudaStream_t)stream;
-  int sms = 0, occ = 0;
+  int sms = 0;
   TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
-  TE_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, rank_chunk_kernel<1>, kFinBlock, 0));
-  const ChunkGeom cg = chunk_geom(p.fin_tiles, sms, occ);
+  const ChunkGeom cg = chunk_geom(p.n, sms);
   const uint32_t nchunks = n > 0 ? cg.nchunks : 0;
   const uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
   unsigned long long* partial = at<unsigned long long>(scratch, p.off_partial);
   const RankScalars* scal = at<RankScalars>(scratch, p.off_scal);
   if (nchunks) {
     TE_PROF("rank_chunk_integrate", st);
-    rank_chunk_kernel<1><<<nchunks, kFinBlock, 0, st>>>(kb, p.n, cg.tiles_per_chunk, nullptr,
-                                                        at<FState>(scratch, p.off_inc), scal, partial,
-                                                        positives_above, samples_above, above_dev);
+    rank_chunk_kernel<1><<<(nchunks + kFinBlock / kWarp - 1) / (kFinBlock / kWarp), kFinBlock, 0, st>>>(
+        kb, p.n, cg.steps_per_chunk, nchunks, nullptr, at<FState>(scratch, p.off_inc), scal, partial,
+        positives_above, samples_above, above_dev);
   }
   TE_PROF("rank_reduce", st);
   rank_reduce_kernel<1><<<1, 1024, 0, st>>>(partial, nchunks, p.n, scal, out);
