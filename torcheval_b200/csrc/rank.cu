@@ -602,7 +602,9 @@ struct RankPlan {
   size_t off_ticket;    // 8 u32
   size_t off_hot;       // 8 u32
   size_t off_scal;      // RankScalars
-  size_t off_lookback;  // 4 passes * sort_tiles * 256 u32
+  size_t off_lookback;  // look-back counts of the first pass: sort_tiles * 256 u32 (zeroed by memset)
+  size_t off_gprefix;   // group prefixes, 4 passes * ceil(sort_tiles / 32) * 256 u32 (zeroed by memset)
+  size_t off_lookback_rest;  // counts of passes 1..3: each pass clears the rows of the next one
   size_t off_agg, off_inc;
   size_t zero_bytes;
   size_t off_partial;
@@ -633,10 +635,13 @@ RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final)
   p.off_ticket = take(8 * 4);
   p.off_hot = take(8 * 4);  // hot digits: 2 per pass
   p.off_scal = take(sizeof(RankScalars));
-  p.off_lookback = take((size_t)4 * 2 * p.sort_tiles * kRadix * 4);  // counts + prefixes, 4 passes
+  const size_t lb_groups = (p.sort_tiles + kLbGroup - 1) / kLbGroup;
+  p.off_lookback = take((size_t)p.sort_tiles * kRadix * 4);
+  p.off_gprefix = take((size_t)4 * lb_groups * kRadix * 4);
   p.off_agg = take(with_final ? (size_t)kMaxChunks * sizeof(ChunkRec) : 0);
   p.off_inc = take(with_final ? (size_t)kMaxChunks * sizeof(FState) : 0);
   p.zero_bytes = o - p.off_zero;
+  p.off_lookback_rest = take((size_t)3 * p.sort_tiles * kRadix * 4);
   p.off_partial = take(with_final ? (size_t)kMaxChunks * 8 : 0);
   p.total = o;
   return p;
@@ -652,7 +657,11 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   // 4 passes: in0 -> x -> y -> x -> y
   uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
   uint32_t* hot = hot_digits_from_env() ? at<uint32_t>(scratch, p.off_hot) : nullptr;
-  uint32_t* lb = at<uint32_t>(scratch, p.off_lookback);
+  const size_t lb_groups = (p.sort_tiles + kLbGroup - 1) / kLbGroup;
+  auto lb_counts = [&](int pass) {
+    return pass == 0 ? at<uint32_t>(scratch, p.off_lookback)
+                     : at<uint32_t>(scratch, p.off_lookback_rest) + (size_t)(pass - 1) * p.sort_tiles * kRadix;
+  };
   {
     TE_PROF("digit_scan", st);
     digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 4, hot);
@@ -662,7 +671,7 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   const size_t smem = block == 256 ? onesweep_smem_bytes<uint32_t, 256>() : onesweep_smem_bytes<uint32_t, 512>();
   using PassFn = void (*)(const uint32_t*, uint32_t*, const uint32_t*, uint32_t*, uint32_t,
                           const RadixDigit, const uint32_t*, uint32_t*, uint32_t*, const PeerPtrs,
-                          const uint32_t*);
+                          const uint32_t*, uint32_t*);
   PassFn fn = nullptr;
   if (v_in0)
     fn = block == 256 ? onesweep_pass_kernel<uint32_t, true, 256, RadixDigit>
@@ -690,12 +699,13 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   for (int pass = 0; pass < 4; ++pass) {
     uint32_t* kout = (pass & 1) ? k_y : k_x;
     uint32_t* vout = (pass & 1) ? v_y : v_x;
-    uint32_t* lbp = lb + (size_t)pass * 2 * p.sort_tiles * kRadix;
+    uint32_t* lbp = lb_counts(pass);
+    uint32_t* gpp = at<uint32_t>(scratch, p.off_gprefix) + (size_t)pass * lb_groups * kRadix;
     TE_PROF(v_in0 ? "onesweep_pass_pairs" : (pass == 0 && fn_first != fn ? "onesweep_pass_keys_first" : "onesweep_pass_keys"), st);
     (pass == 0 ? fn_first : fn)<<<p.sort_tiles, block, smem_used, st>>>(kin, kout, vin, vout, p.n, RadixDigit{8 * pass},
-                                               hist + pass * kRadix, lbp,
-                                               lbp + (size_t)p.sort_tiles * kRadix, PeerPtrs{},
-                                               hot ? hot + 2 * pass : nullptr);
+                                               hist + pass * kRadix, lbp, gpp, PeerPtrs{},
+                                               hot ? hot + 2 * pass : nullptr,
+                                               pass < 3 ? lb_counts(pass + 1) : nullptr);
     TE_LAUNCH_CHECK();
     kin = kout;
     vin = vout;
@@ -1600,7 +1610,7 @@ static int partition_impl(const uint32_t* keys_in, int64_t n, const uint32_t* sp
   }
   TE_LAUNCH_CHECK();
   uint32_t* lb = at<uint32_t>(scratch, p.off_lookback);
-  uint32_t* gp = lb + (size_t)p.sort_tiles * kRadix;
+  uint32_t* gp = at<uint32_t>(scratch, p.off_gprefix);
   const bool peer = peer_ptrs_host != nullptr;
   TE_PROF(peer ? "onesweep_partition_peer" : "onesweep_partition", st);
 #define TE_LAUNCH_PART(B, PEER)                                                                          \
@@ -1608,7 +1618,8 @@ static int partition_impl(const uint32_t* keys_in, int64_t n, const uint32_t* sp
     auto fn = onesweep_pass_kernel<uint32_t, false, B, SplitterDigit, kSortIptDefault, PEER>;            \
     const size_t smem = onesweep_smem_bytes<uint32_t, B>();                                              \
     TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
-    fn<<<p.sort_tiles, B, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist, lb, gp, pp, hot); \
+    fn<<<p.sort_tiles, B, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist, lb, gp, pp, hot, \
+                                      nullptr);                                                          \
   } while (0)
   if (p.sort_ipt != kSortIptDefault) return TE_ERR_UNSUPPORTED;
   if (p.sort_block == 256) {

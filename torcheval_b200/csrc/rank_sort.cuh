@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
                          const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
                          uint32_t n, const DigitOp dop, const uint32_t* __restrict__ digit_base,
                          uint32_t* lookback, uint32_t* group_prefix, const PeerPtrs peers,
-                         const uint32_t* __restrict__ hot_info) {
+                         const uint32_t* __restrict__ hot_info, uint32_t* __restrict__ zero_next) {
   static_assert(kSortBlock >= kRadix && kSortBlock % kRadix == 0, "one thread per digit is needed");
   static_assert(kSortIpt % 4 == 0 && 16 * kSortIpt <= 256, "ranks are packed four per register");
   constexpr int GROUPS = kSortBlock / 16;
@@ -187,6 +187,9 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
     key[i] = r < valid ? keys_in[base + r] : ~(KeyT)0;  // padding sorts last, is never written
   }
   for (int i = tid; i < GROUPS * kRadix; i += kSortBlock) s_rank[i] = 0u;
+  // the next pass's look-back row of this tile must read as "not published": clearing it here
+  // (1 KB per tile, the pass has HBM bandwidth to spare) replaces a memset of the whole array
+  if (zero_next && tid < kRadix) zero_next[(size_t)tile * kRadix + tid] = 0u;
   dop.stage(s_sp, tid);
   if (kPeerScatter && tid <= (unsigned)kMaxSplitters) s_peer[tid] = peers.p[tid];
   __syncthreads();
