@@ -73,10 +73,16 @@ enum {
   TE_CM_GLOBAL32 = 2,  /* RED.ADD.32 into scratch bins, folded into `cm`         */
   TE_CM_SMEM_REPL = 3, /* per-CTA smem bins, replicated per lane (tiny C)        */
   TE_CM_SMEM = 4,      /* per-CTA smem bins (C*C*4 bytes must fit in smem)       */
-  TE_CM_CLUSTER = 5    /* bins spread over the distributed smem of a 16/8-CTA cluster */
+  TE_CM_CLUSTER = 5,   /* bins spread over the distributed smem of a 16/8-CTA cluster */
+  TE_CM_BUCKETED = 6   /* two passes: route 16-bit indices by matrix slice, count in smem  */
 };
 
 TE_API size_t te_cm_scratch_bytes(int32_t num_classes, int32_t variant);
+/* Scratch for n samples.  TE_CM_BUCKETED (and TE_CM_AUTO, which picks it for large num_classes
+ * and n >= 2^22 when the scratch passed to te_cm_update is at least this big) needs ~2 bytes per
+ * sample; every other variant needs what te_cm_scratch_bytes says.  0 for TE_CM_BUCKETED means
+ * the variant does not apply (num_classes^2 / 31 slices must fit 50 000 bins: num_classes <= 1240). */
+TE_API size_t te_cm_scratch_bytes_n(int32_t num_classes, int32_t variant, int64_t n);
 
 /* cm[target[i] * C + pred[i]] += 1 for i < n.
  * range[4] is overwritten with {min_pred, max_pred, min_target, max_target} taken over the

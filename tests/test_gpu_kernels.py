@@ -49,6 +49,8 @@ def cm_variants(C):
         v.append(4)
     if C >= 300:
         v.append(5)  # cluster / distributed-smem bins
+    if C <= 1240:
+        v.append(6)  # bucketed two-pass (route by matrix slice, count in shared memory)
     return v
 
 
@@ -82,9 +84,47 @@ def test_cm_skewed_diagonal(ops):
     p[: n // 4] = 7
     t[: n // 4] = 7  # one very hot bin
     want, _, _ = oracle.confusion_matrix(p, t, C)
-    for v in (1, 2, 5):
+    for v in (1, 2, 5, 6):
         cm, _ = run_cm(ops, dev(p), dev(t), C, v)
         np.testing.assert_array_equal(cm, want)
+    # every sample in ONE slice of the matrix (a single target class): the count pass deals all
+    # CTAs onto that slice
+    t2 = np.full(n, 993)
+    want2, _, _ = oracle.confusion_matrix(p, t2, C)
+    cm, _ = run_cm(ops, dev(p), dev(t2), C, 6)
+    np.testing.assert_array_equal(cm, want2)
+
+
+def test_cm_bucketed_unaligned_tail_and_accumulate(ops):
+    rs = np.random.default_rng(12)
+    C, n = 1000, (1 << 22) + 4099
+    p, t = rs.integers(0, C, n), rs.integers(0, C, n)
+    p[5], t[9], p[n - 1] = C, -2, 12345  # out of range: reported, not counted
+    P, T = dev(p), dev(t)
+    cm = torch.zeros((C, C), dtype=torch.int64, device="cuda")
+    r1 = ops.cm_update_(cm, P[1:], T[1:], C, 6)   # 8-byte aligned only -> scalar loads
+    r2 = ops.cm_update_(cm, P, T, C)              # AUTO: n >= 2^22 and C = 1000 -> bucketed
+    torch.cuda.synchronize()
+    want, bad, _ = oracle.confusion_matrix(p, t, C)
+    want1, _, _ = oracle.confusion_matrix(p[1:], t[1:], C)
+    assert bad
+    np.testing.assert_array_equal(cm.cpu().numpy(), want + want1)
+    assert r1.tolist() == [C, 12345, -2, -2] and r2.tolist() == [C, 12345, -2, -2]
+
+
+def test_cm_full_size_checksums(ops):
+    """BASELINE config 2 at full size (N = 2^28, C = 1000): the matrix against torch.bincount of
+    target * C + pred on the same device data, for the bucketed path (what AUTO picks) and RED."""
+    n, C = 1 << 28, 1000
+    g = torch.Generator(device="cuda").manual_seed(20261106)
+    p = torch.randint(0, C, (n,), device="cuda", generator=g)
+    t = torch.randint(0, C, (n,), device="cuda", generator=g)
+    want = torch.bincount(t * C + p, minlength=C * C).view(C, C)
+    for v in (0, 1):
+        cm = torch.zeros((C, C), dtype=torch.int64, device="cuda")
+        ops.cm_update_(cm, p, t, C, v)
+        assert torch.equal(cm, want), v
+    assert int(want.sum()) == n
 
 
 def test_cm_unaligned_views_and_accumulate(ops):

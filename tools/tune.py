@@ -28,18 +28,41 @@ def timeit(fn, reps=5):
     return best
 
 
+def kernel_times(fn):
+    """{kernel: (total ms, launches)} of one call, from the library's own CUDA-event profile."""
+    import ctypes
+
+    from torcheval_b200 import _native
+
+    lib = _native.load()
+    lib.te_profile_enable(1)
+    fn()
+    torch.cuda.synchronize()
+    names = ctypes.create_string_buffer(8192)
+    ms = (ctypes.c_double * 64)()
+    cnt = (ctypes.c_int64 * 64)()
+    k = lib.te_profile_read(names, 8192, ctypes.cast(ms, ctypes.c_void_p), ctypes.cast(cnt, ctypes.c_void_p), 64)
+    lib.te_profile_enable(0)
+    out = {}
+    for i, nm in enumerate(names.value.decode().split("\n")[:k]):
+        out[nm] = (ms[i], cnt[i])
+    return out
+
+
 def cm():
     for C, logn in [(1000, 28), (1000, 24), (500, 26), (1500, 26), (100, 26), (10, 26), (2, 26), (32, 26)]:
         n = 1 << logn
         p = torch.randint(0, C, (n,), device="cuda")
         t = torch.randint(0, C, (n,), device="cuda")
         cmx = torch.zeros((C, C), dtype=torch.int64, device="cuda")
-        for v, name in [(1, "global64"), (2, "global32"), (3, "smem_repl"), (4, "smem"), (5, "cluster")]:
+        for v, name in [(1, "global64"), (2, "global32"), (3, "smem_repl"), (4, "smem"), (5, "cluster"), (6, "bucketed")]:
             if v == 3 and C * C * 128 > 200 * 1024:
                 continue
             if v == 4 and C * C * 4 > 200 * 1024:
                 continue
             if v == 5 and C < 300:
+                continue
+            if v == 6 and (C > 1240 or C < 100):
                 continue
             try:
                 ms = timeit(lambda: ops.cm_update_(cmx, p, t, C, v))
@@ -48,6 +71,9 @@ def cm():
                 continue
             gbs = 16 * n / ms / 1e6
             print(f"C={C:5d} n=2^{logn} {name:10s} {ms:8.3f} ms  {gbs:7.1f} GB/s  {gbs / PEAK:5.1%}  {n / ms / 1e6:6.1f} G/s", flush=True)
+            if v == 6:
+                for kname, (kms, kn) in kernel_times(lambda: ops.cm_update_(cmx, p, t, C, v)).items():
+                    print(f"        {kname:12s} {kms / max(kn, 1):8.3f} ms")
         del p, t
 
 

@@ -12,7 +12,7 @@ from pathlib import Path
 _LIB_PATH = Path(__file__).resolve().parent / "lib" / "libte_b200.so"
 
 TE_OK = 0
-TE_CM_AUTO, TE_CM_GLOBAL64, TE_CM_GLOBAL32, TE_CM_SMEM_REPL, TE_CM_SMEM, TE_CM_CLUSTER = range(6)
+TE_CM_AUTO, TE_CM_GLOBAL64, TE_CM_GLOBAL32, TE_CM_SMEM_REPL, TE_CM_SMEM, TE_CM_CLUSTER, TE_CM_BUCKETED = range(7)
 TE_BINNED_AUROC, TE_BINNED_AUPRC = 0, 1
 TE_DTYPE_I64, TE_DTYPE_I32, TE_DTYPE_U8, TE_DTYPE_F32, TE_DTYPE_F64 = range(5)
 TE_RANK_FLAG_BAD_LABEL, TE_RANK_FLAG_NEGATIVE_SCORE = 1, 2
@@ -27,6 +27,7 @@ SIGNATURES = {
     "te_profile_read": (C.c_int, [C.c_char_p, _sz, _vp, _vp, _i32]),
     "te_debug_phase_stats": (C.c_int, [_vp, C.c_int]),
     "te_cm_scratch_bytes": (_sz, [_i32, _i32]),
+    "te_cm_scratch_bytes_n": (_sz, [_i32, _i32, _i64]),
     "te_cm_update": (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _vp, _sz, _i32, _vp]),
     "te_cm_update_noalloc": (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _vp]),
     "te_cm_update_logits": (C.c_int, [_vp, _i64, _vp, _i64, _i32, _vp, _vp, _vp]),

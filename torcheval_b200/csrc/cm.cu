@@ -451,6 +451,240 @@ __global__ void __launch_bounds__(kCmBlock)
   if (threadIdx.x == 0 && tot) atomicAdd(out, tot);
 }
 
+// ---- TE_CM_BUCKETED: two passes, every increment is a SHARED-memory atomic ------------------
+// 10^6 bins (C = 1000) do not fit one SM, and one RED per sample into L2 is capped by the SM<->L2
+// request rate at ~146 G samples/s = 36 % of the HBM roofline (profiles/r01_tune_cm_v2.txt).  But a
+// SLICE of the matrix — R consecutive target rows, R*C <= 50 000 bins — does fit.  So:
+//   pass 1 (route)  streams the int64 pairs once (16 B/sample), turns every sample into a 16-bit
+//                   index inside its slice (local_row * C + pred) and writes the indices back
+//                   grouped by slice WITHIN each 8192-sample tile (unordered multisplit over <= 31
+//                   slices: ballots + one shared atomic per distinct slice and warp round), plus a
+//                   33-entry offset table per tile and global per-slice totals;
+//   pass 2 (count)  one CTA per SM holds one slice's bins in shared memory (int32), walks the
+//                   runs of that slice tile by tile (2 B/sample) with shared atomics, and adds
+//                   its bins into the int64 matrix at the end.  CTAs are dealt out over the
+//                   slices in proportion to the slice totals, so a skewed class distribution
+//                   still keeps every SM busy.
+// Traffic: 16 + 2 + 2 = 20 B/sample instead of 16 B + one L2 atomic.
+constexpr int kRtBlock = 512;
+constexpr int kRtIpt = 16;
+constexpr int kRtTile = kRtBlock * kRtIpt;  // 8192 samples
+constexpr int kRtMaxSlices = 31;            // slice 31 = "not counted" (out of range / past the end)
+constexpr uint32_t kRtMaxSliceBins = 50000; // 200 KB of int32 bins per CTA
+constexpr int kCtBlock = 1024;
+
+struct BucketGeom {
+  uint32_t rows, slices;  // target rows per slice, number of slices
+};
+inline bool bucket_geom(int32_t C, BucketGeom* g) {
+  if (C < 1 || (uint32_t)C > kRtMaxSliceBins) return false;
+  const uint32_t rows = kRtMaxSliceBins / (uint32_t)C;
+  const uint32_t slices = ((uint32_t)C + rows - 1) / rows;
+  if (rows < 1 || slices > (uint32_t)kRtMaxSlices || rows * (uint32_t)C > 65536u) return false;
+  g->rows = rows;
+  g->slices = slices;
+  return true;
+}
+struct BucketPlan {
+  uint64_t tiles;
+  size_t off_keys, off_table, off_totals, total;
+};
+inline BucketPlan bucket_plan(int64_t n) {
+  BucketPlan p{};
+  p.tiles = ((uint64_t)n + kRtTile - 1) / kRtTile;
+  if (p.tiles == 0) p.tiles = 1;
+  size_t o = 0;
+  p.off_keys = o;
+  o += align_up((size_t)p.tiles * kRtTile * 2, 256);
+  p.off_table = o;
+  o += align_up((size_t)p.tiles * 32 * 2, 256);  // 32 x uint16 run starts per tile
+  p.off_totals = o;
+  o += 256;  // 32 x uint64 slice totals (zeroed per call)
+  p.total = o;
+  return p;
+}
+
+constexpr int kRtParts = 4;  // slice counters are split over 4 interleaved thread classes
+
+__global__ void __launch_bounds__(kRtBlock)
+    cm_route_kernel(const long long* __restrict__ pred, const long long* __restrict__ target, int64_t n,
+                    uint32_t C, uint32_t rows, uint32_t inv_rows, bool vec_ok,
+                    uint16_t* __restrict__ keys, uint16_t* __restrict__ table,
+                    unsigned long long* __restrict__ totals, long long* range) {
+  __shared__ __align__(16) uint16_t s_keys[kRtTile];
+  // position counters: [slice][part]; a thread uses part = tid % 4, so the lanes of a warp that
+  // hit the same slice are spread over four addresses (the ranking is unordered: ANY position
+  // inside the slice's run will do, so one shared atomic with return per sample is all it takes)
+  __shared__ uint32_t s_cnt[32 * kRtParts];
+  const unsigned tid = threadIdx.x, lane = tid & 31;
+  const uint64_t tile = blockIdx.x;
+  const int64_t base = (int64_t)(tile * kRtTile);
+  if (tid < 32 * kRtParts) s_cnt[tid] = 0;
+  __syncthreads();
+  RangeReport rr{range};
+  const uint32_t part = tid & (kRtParts - 1);
+  uint32_t rec[kRtIpt];      // (slice * 4 + part) << 16 | index inside the slice
+  uint32_t rk[kRtIpt / 2];   // arrival number inside (slice, part), two per register
+  const bool full = vec_ok && base + kRtTile <= n;
+#pragma unroll
+  for (int h = 0; h < kRtIpt / 4; ++h) {
+    // 4 samples: two 128-bit loads per stream; sample 2*(tid + k*512) + v of the tile
+    int4 a[2], b[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int64_t i = base + 2 * ((int64_t)tid + (int64_t)(2 * h + k) * kRtBlock);
+      if (full) {
+        a[k] = ld_stream_v4(pred + i);
+        b[k] = ld_stream_v4(target + i);
+      } else {
+        long long pv[2], tv[2];
+#pragma unroll
+        for (int v = 0; v < 2; ++v) {
+          pv[v] = i + v < n ? pred[i + v] : -1;  // -1: past the end, never reported (see below)
+          tv[v] = i + v < n ? target[i + v] : -1;
+        }
+        a[k] = make_int4((int)(uint32_t)pv[0], (int)(pv[0] >> 32), (int)(uint32_t)pv[1], (int)(pv[1] >> 32));
+        b[k] = make_int4((int)(uint32_t)tv[0], (int)(tv[0] >> 32), (int)(uint32_t)tv[1], (int)(tv[1] >> 32));
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int s = 4 * h + j;
+      const int4 pa = a[j >> 1], ta = b[j >> 1];
+      const uint32_t plo = (j & 1) ? (uint32_t)pa.z : (uint32_t)pa.x, phi = (j & 1) ? (uint32_t)pa.w : (uint32_t)pa.y;
+      const uint32_t tlo = (j & 1) ? (uint32_t)ta.z : (uint32_t)ta.x, thi = (j & 1) ? (uint32_t)ta.w : (uint32_t)ta.y;
+      uint32_t sp = 31u * kRtParts, idx = 0u, r = 0u;
+      if ((phi | thi) == 0u && plo < C && tlo < C) {
+        const uint32_t slice = __umulhi(tlo, inv_rows);
+        idx = (tlo - slice * rows) * C + plo;
+        sp = slice * kRtParts + part;
+        r = atomicAdd(&s_cnt[sp], 1u);
+      } else if (full || base + 2 * ((int64_t)tid + (int64_t)(2 * h + (j >> 1)) * kRtBlock) + (j & 1) < n) {
+        rr.bad((long long)(((unsigned long long)phi << 32) | plo), (long long)(((unsigned long long)thi << 32) | tlo), C);
+      }
+      rec[s] = (sp << 16) | idx;
+      if ((s & 1) == 0)
+        rk[s >> 1] = r;
+      else
+        rk[s >> 1] |= r << 16;
+    }
+  }
+  __syncthreads();
+  // exclusive scan over the 31 * 4 (slice, part) counters in slice-major order -> run starts
+  if (tid < 32 * kRtParts) {
+    const uint32_t c = tid < 31 * kRtParts ? s_cnt[tid] : 0u;
+    uint32_t incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t u = __shfl_up_sync(kFull, incl, o);
+      if (lane >= (unsigned)o) incl += u;
+    }
+    __shared__ uint32_t s_w[kRtParts];
+    if (lane == 31) s_w[tid >> 5] = incl;
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    uint32_t wb = 0;
+    for (unsigned w = 0; w < (tid >> 5); ++w) wb += s_w[w];
+    const uint32_t excl = wb + incl - c;
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    s_cnt[tid] = excl;  // now the start of (slice, part) inside the tile
+    if ((tid & (kRtParts - 1)) == 0) table[tile * 32 + tid / kRtParts] = (uint16_t)excl;  // entry 31 = counted total
+  }
+  __syncthreads();
+  if (tid < 31) {  // slice totals for the count pass's work split
+    const uint32_t c = s_cnt[(tid + 1) * kRtParts] - s_cnt[tid * kRtParts];
+    if (c) atomicAdd(totals + tid, (unsigned long long)c);
+  }
+#pragma unroll
+  for (int s = 0; s < kRtIpt; ++s) {
+    const uint32_t sp = rec[s] >> 16;
+    const uint32_t r = (s & 1) ? (rk[s >> 1] >> 16) : (rk[s >> 1] & 0xffffu);
+    if (sp < 31u * kRtParts) s_keys[s_cnt[sp] + r] = (uint16_t)(rec[s] & 0xffffu);
+  }
+  __syncthreads();
+  // the tile's indices, grouped by slice, as 16-byte stores (positions past the counted total
+  // are never read)
+  int4* dst = reinterpret_cast<int4*>(keys + tile * kRtTile);
+  const int4* src = reinterpret_cast<const int4*>(s_keys);
+#pragma unroll
+  for (int k = 0; k < kRtTile * 2 / 16 / kRtBlock; ++k) dst[tid + k * kRtBlock] = src[tid + k * kRtBlock];
+}
+
+__global__ void __launch_bounds__(kCtBlock, 1)
+    cm_count_kernel(const uint16_t* __restrict__ keys, const uint16_t* __restrict__ table,
+                    const unsigned long long* __restrict__ totals, uint64_t tiles, uint32_t C,
+                    uint32_t rows, uint32_t slices, unsigned long long* cm) {
+  extern __shared__ uint32_t sh_bins[];
+  __shared__ unsigned long long s_cum[33];
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) {
+    unsigned long long c = 0;
+    for (uint32_t b = 0; b < 32; ++b) {
+      s_cum[b] = c;
+      c += b < slices ? totals[b] : 0ull;
+    }
+    s_cum[32] = c;
+  }
+  __syncthreads();
+  const unsigned long long total = s_cum[32];
+  if (total == 0) return;
+  // this CTA's share of the counted samples, in slice-major order
+  const unsigned long long lo = total * blockIdx.x / gridDim.x, hi = total * (blockIdx.x + 1) / gridDim.x;
+  for (uint32_t b = 0; b < slices; ++b) {
+    const unsigned long long c0 = s_cum[b], c1 = s_cum[b + 1];
+    if (c1 <= lo || c0 >= hi || c1 == c0) continue;
+    // the part of slice b that is mine, mapped onto a range of tiles (consecutive CTAs share the
+    // boundary value, so the tiles of a slice are partitioned exactly)
+    const unsigned long long a0 = (lo > c0 ? lo - c0 : 0ull), a1 = (hi < c1 ? hi : c1) - c0, cnt = c1 - c0;
+    const uint64_t t0 = (uint64_t)((__uint128_t)a0 * tiles / cnt);
+    const uint64_t t1 = a1 == cnt ? tiles : (uint64_t)((__uint128_t)a1 * tiles / cnt);
+    if (t1 <= t0) continue;
+    const uint32_t row0 = b * rows;
+    const uint32_t nbins = (min(row0 + rows, C) - row0) * C;
+    for (uint32_t i = tid; i < nbins; i += kCtBlock) sh_bins[i] = 0u;
+    __syncthreads();
+    for (uint64_t t = t0 + warp; t < t1; t += kCtBlock / kWarp) {
+      const uint32_t s = table[t * 32 + b], e = table[t * 32 + b + 1];
+      const uint16_t* run = keys + t * kRtTile;
+      for (uint32_t k = s + lane; k < e; k += kWarp) atomicAdd(&sh_bins[run[k]], 1u);
+    }
+    __syncthreads();
+    unsigned long long* out = cm + (size_t)row0 * C;
+    for (uint32_t i = tid; i < nbins; i += kCtBlock) {
+      const uint32_t v = sh_bins[i];
+      if (v) atomicAdd(out + i, (unsigned long long)v);
+    }
+    __syncthreads();
+  }
+}
+
+int cm_bucketed(const long long* pred, const long long* target, int64_t n, int32_t C,
+                unsigned long long* cm, long long* range, void* scratch, int sms, cudaStream_t st) {
+  BucketGeom g;
+  if (!bucket_geom(C, &g)) return TE_ERR_UNSUPPORTED;
+  const BucketPlan p = bucket_plan(n);
+  char* base = static_cast<char*>(scratch);
+  uint16_t* keys = reinterpret_cast<uint16_t*>(base + p.off_keys);
+  uint16_t* table = reinterpret_cast<uint16_t*>(base + p.off_table);
+  unsigned long long* totals = reinterpret_cast<unsigned long long*>(base + p.off_totals);
+  TE_CUDA_TRY(cudaMemsetAsync(totals, 0, 256, st));
+  const uint32_t inv_rows = (uint32_t)((((uint64_t)1 << 32) + g.rows - 1) / g.rows);
+  const bool vec_ok = (((uintptr_t)pred | (uintptr_t)target) & 15) == 0;
+  {
+    TE_PROF("cm_route", st);
+    cm_route_kernel<<<(unsigned)p.tiles, kRtBlock, 0, st>>>(pred, target, n, (uint32_t)C, g.rows, inv_rows, vec_ok,
+                                                            keys, table, totals, range);
+  }
+  TE_LAUNCH_CHECK();
+  const size_t sh = (size_t)g.rows * C * 4;
+  TE_CUDA_TRY(cudaFuncSetAttribute(cm_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
+  TE_PROF("cm_count", st);
+  cm_count_kernel<<<sms, kCtBlock, sh, st>>>(keys, table, totals, p.tiles, (uint32_t)C, g.rows, g.slices, cm);
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+constexpr int64_t kBucketedMinN = (int64_t)1 << 22;  // below this the extra pass does not pay
+
 int pick_variant(int32_t C, int32_t variant) {
   if (variant != TE_CM_AUTO) return variant;
   const int64_t nbins = (int64_t)C * C;
@@ -469,6 +703,16 @@ extern "C" size_t te_cm_scratch_bytes(int32_t num_classes, int32_t variant) {
   const int v = pick_variant(num_classes, variant);
   if (v == TE_CM_GLOBAL32) return align_up((size_t)num_classes * num_classes * 4, 256);
   return 0;
+}
+
+extern "C" size_t te_cm_scratch_bytes_n(int32_t num_classes, int32_t variant, int64_t n) {
+  if (num_classes < 1 || n < 0) return 0;
+  BucketGeom g;
+  const bool can = bucket_geom(num_classes, &g) && n < ((int64_t)1 << 32);
+  if (variant == TE_CM_BUCKETED) return can ? bucket_plan(n).total : 0;
+  if (variant == TE_CM_AUTO && can && pick_variant(num_classes, variant) == TE_CM_GLOBAL64 && n >= kBucketedMinN)
+    return bucket_plan(n).total;
+  return te_cm_scratch_bytes(num_classes, variant);
 }
 
 template <int VEC>
@@ -573,11 +817,22 @@ extern "C" int te_cm_update(const int64_t* pred, const int64_t* target, int64_t 
                             size_t scratch_bytes, int32_t variant, void* stream) {
   if (n < 0 || num_classes < 1 || num_classes > 46340 || !cm || !range) return TE_ERR_INVALID_ARGUMENT;
   if (n > 0 && (!pred || !target)) return TE_ERR_INVALID_ARGUMENT;
-  const int v = pick_variant(num_classes, variant);
+  int v = pick_variant(num_classes, variant);
+  {
+    // large C: the bucketed two-pass variant when the caller's scratch has room for it
+    // (te_cm_scratch_bytes_n), else RED into L2
+    BucketGeom g;
+    const bool can = bucket_geom(num_classes, &g) && n < ((int64_t)1 << 32);
+    if (variant == TE_CM_BUCKETED && !can) return TE_ERR_UNSUPPORTED;
+    if (variant == TE_CM_AUTO && v == TE_CM_GLOBAL64 && can && n >= kBucketedMinN && scratch &&
+        scratch_bytes >= bucket_plan(n).total)
+      v = TE_CM_BUCKETED;
+    if (v == TE_CM_BUCKETED && (!scratch || scratch_bytes < bucket_plan(n).total)) return TE_ERR_SCRATCH_TOO_SMALL;
+  }
   if ((v == TE_CM_SMEM_REPL && (size_t)num_classes * num_classes * 128 > 200 * 1024) ||
       (v == TE_CM_SMEM && (size_t)num_classes * num_classes * 4 > 200 * 1024))
     return TE_ERR_INVALID_ARGUMENT;
-  if (scratch_bytes < te_cm_scratch_bytes(num_classes, v) || (v == TE_CM_GLOBAL32 && !scratch))
+  if (v != TE_CM_BUCKETED && (scratch_bytes < te_cm_scratch_bytes(num_classes, v) || (v == TE_CM_GLOBAL32 && !scratch)))
     return TE_ERR_SCRATCH_TOO_SMALL;
   cudaStream_t st = (cudaStream_t)stream;
   int sms = 0;
@@ -585,6 +840,9 @@ extern "C" int te_cm_update(const int64_t* pred, const int64_t* target, int64_t 
   cm_init_range_kernel<<<1, 32, 0, st>>>((long long*)range);
   TE_LAUNCH_CHECK();
   if (n == 0) return TE_OK;
+  if (v == TE_CM_BUCKETED)
+    return cm_bucketed((const long long*)pred, (const long long*)target, n, num_classes,
+                       (unsigned long long*)cm, (long long*)range, scratch, sms, st);
   const bool aligned = (((uintptr_t)pred | (uintptr_t)target) & 15) == 0;
   if (aligned)
     return cm_launch<2>((const long long*)pred, (const long long*)target, n, num_classes,

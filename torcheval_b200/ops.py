@@ -68,7 +68,9 @@ def cm_update_(
     assert pred.dtype == torch.int64 and target.dtype == torch.int64
     pred, target = pred.contiguous(), target.contiguous()
     rng = torch.empty(4, dtype=torch.int64, device=dev)
-    sb = lib.te_cm_scratch_bytes(num_classes, variant)
+    sb = lib.te_cm_scratch_bytes_n(num_classes, variant, pred.numel())
+    if variant == N.TE_CM_BUCKETED and sb == 0:
+        raise ValueError(f"TE_CM_BUCKETED does not apply to num_classes={num_classes}")
     scratch = _scratch(sb, dev)
     with torch.cuda.device(dev):
         N.check(
