@@ -66,6 +66,47 @@ def test_functional_exact(backend, golden):
         close(F.multilabel_auprc(T(c["x"]), T(c["y"])), c["auprc_macro"], 1e-4)
 
 
+def test_float64_and_integer_scores(backend):
+    """Scores float32 cannot hold (float64 probabilities 1e-9 apart, int64 beyond 2^24): the
+    reference ranks them as they are (auroc.py:121 sorts whatever dtype it is given); here they
+    go through the dense-rank transform (ranking) or are floored to float32 (threshold counts)."""
+    import oracle
+    from torcheval_b200.metrics import functional as F
+
+    rs = np.random.default_rng(99)
+    n = 20001
+    y = rs.integers(0, 2, n)
+    x64 = 0.5 + rs.integers(0, 4000, n) * 1e-9  # distinct in float64, 2 values in float32
+    assert np.unique(x64.astype(np.float32)).size < 100 < np.unique(x64).size
+
+    def ranks(a):  # the oracle takes float32 scores: hand it small integers with the same order and ties
+        return np.unique(a, return_inverse=True)[1].reshape(a.shape).astype(np.float32)
+
+    close(F.binary_auroc(T(x64), T(y)), oracle.binary_auroc(ranks(x64), y)[0])
+    close(F.binary_auprc(T(x64), T(y)), oracle.binary_auprc(ranks(x64), y), 1e-4)
+    w = rs.random(n) + 0.5
+    close(F.binary_auroc(T(x64), T(y), weight=T(w)), oracle.binary_auroc(ranks(x64), y, w)[0])
+    xi = (1 << 40) + rs.integers(0, 50, n)  # int64 scores that collapse in float32
+    close(F.binary_auroc(T(xi), T(y)), oracle.binary_auroc(ranks(xi), y)[0])
+    C = 5
+    xm = 0.25 + rs.integers(0, 1000, (n, C)) * 1e-10
+    ym = rs.integers(0, C, n)
+    close(F.multiclass_auroc(T(xm), T(ym), num_classes=C, average=None), oracle.multiclass_auroc(ranks(xm), ym), 1e-4)
+    # threshold counting: a float64 score just below a float32 threshold must stay below it
+    thr = np.linspace(0, 1, 11, dtype=np.float32)
+    xb = np.concatenate([thr.astype(np.float64) - 1e-12, thr.astype(np.float64) + 1e-12, thr.astype(np.float64)])
+    xb = np.clip(xb, 0.0, 1.0)
+    yb = rs.integers(0, 2, xb.size)
+    from torcheval_b200.metrics.functional.classification.binned_precision_recall_curve import (
+        _binary_binned_precision_recall_curve_update,
+    )
+
+    tp, fp, fn = _binary_binned_precision_recall_curve_update(T(xb), T(yb), T(thr))
+    ge = xb[None, :] >= thr.astype(np.float64)[:, None]
+    np.testing.assert_array_equal(tp.numpy(), (ge & (yb == 1)[None, :]).sum(1))
+    np.testing.assert_array_equal(fp.numpy(), (ge & (yb == 0)[None, :]).sum(1))
+
+
 def test_functional_binned(backend, golden):
     from torcheval_b200.metrics import functional as F
     from torcheval_b200.metrics.functional.classification.binned_precision_recall_curve import (

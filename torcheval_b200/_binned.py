@@ -8,7 +8,7 @@ import torch
 
 from . import _native as N
 from . import ops
-from ._ranking import _as_f32_scores, compute_device, stage
+from ._ranking import _floor_f32_scores, compute_device, stage
 
 
 def _labels_i64(t: torch.Tensor) -> torch.Tensor:
@@ -22,7 +22,7 @@ def _thr_f32(threshold: torch.Tensor, dev: torch.device) -> torch.Tensor:
 def binary_counts(input: torch.Tensor, target: torch.Tensor, threshold: torch.Tensor):
     """(num_tp, num_fp, num_fn): int64 (tasks, T) on the compute device; input is (n,) or (tasks, n)."""
     dev = compute_device(input)
-    x = _as_f32_scores(stage(input, dev))
+    x = _floor_f32_scores(stage(input, dev))
     t = _labels_i64(stage(target, dev))
     thr = _thr_f32(threshold, dev)
     T = thr.numel()
@@ -35,7 +35,7 @@ def binary_counts(input: torch.Tensor, target: torch.Tensor, threshold: torch.Te
 def counts_2d(input: torch.Tensor, target: torch.Tensor, threshold: torch.Tensor, multilabel: bool):
     """(num_tp, num_fp, num_fn): int64 (C, T) for (n, C) scores, one-vs-rest per class / per label."""
     dev = compute_device(input)
-    x = _as_f32_scores(stage(input, dev))
+    x = _floor_f32_scores(stage(input, dev))
     t = _labels_i64(stage(target, dev))
     thr = _thr_f32(threshold, dev)
     T, C = thr.numel(), x.shape[1]

@@ -31,6 +31,9 @@ def stage(t: torch.Tensor, dev: torch.device, dtype: Optional[torch.dtype] = Non
 
 
 def _as_f32_scores(x: torch.Tensor) -> torch.Tensor:
+    """`x` as float32 if that is exact, else NotImplementedError (callers decide what to do:
+    `_rank_scores` for ranking, `_floor_f32_scores` for threshold counting, the generic gather
+    path for rank-sharded scores, whose ranks would have to agree across ranks)."""
     if x.dtype == torch.float32:
         return x
     if x.dtype in (torch.float16, torch.bfloat16):
@@ -38,15 +41,42 @@ def _as_f32_scores(x: torch.Tensor) -> torch.Tensor:
     y = x.float()
     if not bool((y.to(x.dtype) == x).all()):
         raise NotImplementedError(
-            f"scores of dtype {x.dtype} that are not exactly representable in float32 are not supported yet"
+            f"scores of dtype {x.dtype} that are not exactly representable in float32"
         )
     return y
+
+
+def _floor_f32_scores(x: torch.Tensor) -> torch.Tensor:
+    """Largest float32 <= x.  For float32 thresholds t: t <= x  <=>  t <= floor32(x), so counting
+    scores against thresholds is unchanged by this rounding (unlike round-to-nearest)."""
+    try:
+        return _as_f32_scores(x)
+    except NotImplementedError:
+        y = x.float()
+        above = y.to(x.dtype) > x
+        return torch.where(above, torch.nextafter(y, torch.full_like(y, float("-inf"))), y)
+
+
+def _rank_scores(x: torch.Tensor) -> torch.Tensor:
+    """A float32 tensor with the same order and the same ties as `x` — all the ranking kernels
+    look at.  Scores that float32 holds exactly are passed through; anything else (float64
+    probabilities, large integers) is replaced by its dense rank, stored as the float whose BIT
+    PATTERN is the rank: non-negative floats order like their bit patterns, and the kernels only
+    ever compare and sort the bits.  (The rank transform is a library sort, torch.unique; it is
+    the slow road for inputs the packed 32-bit key cannot hold.)"""
+    try:
+        return _as_f32_scores(x)
+    except NotImplementedError:
+        _, inv = torch.unique(x, sorted=True, return_inverse=True)
+        if inv.numel() and int(inv.max()) >= 0x7F800000:
+            raise
+        return inv.to(torch.int32).view(torch.float32)
 
 
 def binary_auroc(input: torch.Tensor, target: torch.Tensor, weight: Optional[torch.Tensor] = None) -> torch.Tensor:
     out_dev = input.device
     dev = compute_device(input)
-    x = _as_f32_scores(stage(input, dev))
+    x = _rank_scores(stage(input, dev))
     t = stage(target, dev)
     w = None if weight is None else stage(weight, dev, torch.float64)
     rows = [(x, t, w)] if x.dim() == 1 else [(x[k], t[k], None if w is None else w[k]) for k in range(x.shape[0])]
@@ -79,7 +109,7 @@ def binary_auprc(input: torch.Tensor, target: torch.Tensor, num_tasks: int = 1) 
     otherwise (num_tasks,)."""
     out_dev = input.device
     dev = compute_device(input)
-    x = _as_f32_scores(stage(input, dev))
+    x = _rank_scores(stage(input, dev))
     t = stage(target, dev)
     if num_tasks == 1 and x.dim() == 1:
         return _binary_auprc_row(x, t).to(torch.float32).to(out_dev)
@@ -92,7 +122,7 @@ def _one_vs_rest(input: torch.Tensor, target: torch.Tensor, auprc: bool, multila
     kernels do all columns; a column the packed representation cannot take (negative scores) is
     redone on its own through the general path."""
     dev = compute_device(input)
-    x = _as_f32_scores(stage(input, dev))
+    x = _rank_scores(stage(input, dev))
     t = stage(target, dev)
     if t.dtype != torch.int64:
         t = t.to(torch.int64)
