@@ -184,6 +184,36 @@ def main() -> None:
         f1_none=F.multiclass_f1_score(p, t, num_classes=5, average=None),
     )
 
+    # ---------------- precision / recall -------------------------------
+    p, t = randint(0, 6, (901,)), randint(0, 5, (901,))  # class 5 is predicted but never true
+    p[p == 2] = 1                                         # class 2 is true but never predicted
+    rec = dict(pred=p, target=t)
+    for avg, tag in (("micro", "micro"), ("macro", "macro"), ("weighted", "weighted"), (None, "none")):
+        nc = None if avg == "micro" else 7                # class 6 occurs nowhere
+        rec[f"precision_{tag}"] = F.multiclass_precision(p, t, num_classes=nc, average=avg)
+        # (the reference's recall masks num_tp but not num_labels for macro/weighted and raises a
+        # shape error when a class is absent from both pred and target: 6 classes there)
+        rec[f"recall_{tag}"] = F.multiclass_recall(p, t, num_classes=None if avg == "micro" else 6, average=avg)
+    put("prec_rec/c7", **rec)
+    logits, t = rand(500, 4), randint(0, 4, (500,))
+    put(
+        "prec_rec/logits4",
+        logits=logits,
+        target=t,
+        precision_macro=F.multiclass_precision(logits, t, num_classes=4, average="macro"),
+        recall_none=F.multiclass_recall(logits, t, num_classes=4, average=None),
+    )
+    xb4, t = rand(1201), randint(0, 2, (1201,))
+    put(
+        "prec_rec/binary",
+        x=xb4,
+        target=t,
+        precision_05=F.binary_precision(xb4, t),
+        precision_07=F.binary_precision(xb4, t, threshold=0.7),
+        recall_05=F.binary_recall(xb4, t),
+        recall_03=F.binary_recall(xb4, t, threshold=0.3),
+    )
+
     OUT.parent.mkdir(parents=True, exist_ok=True)
     np.savez_compressed(OUT, **store)
     print(f"wrote {OUT} ({OUT.stat().st_size / 1024:.0f} KiB, {len(store)} arrays)")

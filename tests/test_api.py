@@ -187,6 +187,49 @@ def test_functional_counting(backend, golden):
     close(F.multiclass_accuracy(T([[0.9, 0.1, 0], [0.1, 0.2, 0.7], [0.3, 0.4, 0.3]]), T([0, 1, 1]), k=2), 1.0)
 
 
+def test_functional_precision_recall(backend, golden):
+    """SURVEY.md section 8f #3: precision / recall on the class-count kernel, against the reference."""
+    from torcheval_b200.metrics import functional as F
+
+    c = golden.case("prec_rec/c7")
+    p, t = T(c["pred"]), T(c["target"])
+    for avg, tag in (("micro", "micro"), ("macro", "macro"), ("weighted", "weighted"), (None, "none")):
+        got = F.multiclass_precision(p, t, num_classes=None if avg == "micro" else 7, average=avg)
+        assert got.dtype == torch.float32
+        close(got, c[f"precision_{tag}"])
+        got = F.multiclass_recall(p, t, num_classes=None if avg == "micro" else 6, average=avg)
+        assert got.dtype == torch.float32
+        close(got, c[f"recall_{tag}"])
+    # a class absent from predictions AND targets: ignored by macro / weighted (the reference's
+    # recall raises a shape error here, see functional/classification/recall.py)
+    r7 = F.multiclass_recall(p, t, num_classes=7, average="macro")
+    close(r7, c["recall_macro"])
+    c = golden.case("prec_rec/logits4")
+    close(F.multiclass_precision(T(c["logits"]), T(c["target"]), num_classes=4, average="macro"), c["precision_macro"])
+    close(F.multiclass_recall(T(c["logits"]), T(c["target"]), num_classes=4, average=None), c["recall_none"])
+    c = golden.case("prec_rec/binary")
+    close(F.binary_precision(T(c["x"]), T(c["target"])), c["precision_05"])
+    close(F.binary_precision(T(c["x"]), T(c["target"]), threshold=0.7), c["precision_07"])
+    close(F.binary_recall(T(c["x"]), T(c["target"])), c["recall_05"])
+    close(F.binary_recall(T(c["x"]), T(c["target"]), threshold=0.3), c["recall_03"])
+    # docstring examples of the reference (precision.py:29-40, recall.py:31-38)
+    close(F.binary_precision(T([0, 0, 1, 1]), T([1, 0, 1, 1])), 1.0)
+    close(F.binary_precision(T([0, 0.8, 0.6, 0.7]), T([1, 0, 1, 1]), threshold=0.7), 0.5)
+    close(F.multiclass_precision(T([0, 2, 1, 3]), T([0, 1, 2, 3]), average=None, num_classes=4), [1.0, 0.0, 0.0, 1.0])
+    close(F.binary_recall(T([0, 0, 1, 1]), T([1, 0, 1, 1])), 2 / 3)
+    close(F.binary_recall(T([0.2, 0.3]), T([0, 0])), 0.0)  # no positives: NaN -> 0
+    with pytest.raises(ValueError, match="`average` was not in the allowed value of"):
+        F.multiclass_precision(p, t, average="gamma")
+    with pytest.raises(ValueError, match="num_classes should be a positive number when average=macro"):
+        F.multiclass_precision(p, t, average="macro")
+    with pytest.raises(ValueError, match="`num_classes` should be a positive number when average=None"):
+        F.multiclass_recall(p, t, average=None)
+    with pytest.raises(ValueError, match="should have the same first dimension"):
+        F.multiclass_recall(p[:5], t, num_classes=7, average="macro")
+    with pytest.raises(ValueError, match="target should be a one-dimensional tensor"):
+        F.binary_precision(torch.rand(2, 2), torch.rand(2, 2))
+
+
 def test_error_messages(backend):
     from torcheval_b200.metrics import functional as F
 
@@ -408,6 +451,18 @@ def test_class_counting(backend, golden):
     check_lifecycle(MulticlassF1Score, feed, lambda r: close(r, a["f1_micro"]), {"num_tp", "num_label", "num_prediction"})
     ba = BinaryAccuracy().update(T([0.1, 0.9, 0.6, 0.2]), T([0, 1, 0, 0]))
     close(ba.compute(), 0.75)
+    from torcheval_b200.metrics import BinaryPrecision, BinaryRecall, MulticlassPrecision, MulticlassRecall
+
+    pr = golden.case("prec_rec/c7")
+    feed = lambda: [(T(p), T(t)) for p, t in zip(_split(pr["pred"], 3), _split(pr["target"], 3))]  # noqa: E731
+    check_lifecycle(MulticlassPrecision, feed, lambda r: close(r, pr["precision_micro"]), {"num_tp", "num_fp", "num_label"})
+    check_lifecycle(lambda: MulticlassPrecision(num_classes=7, average="weighted"), feed, lambda r: close(r, pr["precision_weighted"]), {"num_tp", "num_fp", "num_label"})
+    check_lifecycle(lambda: MulticlassRecall(num_classes=6, average="macro"), feed, lambda r: close(r, pr["recall_macro"]), {"num_tp", "num_labels", "num_predictions"})
+    check_lifecycle(lambda: MulticlassRecall(num_classes=6, average=None), feed, lambda r: close(r, pr["recall_none"]), {"num_tp", "num_labels", "num_predictions"})
+    pb = golden.case("prec_rec/binary")
+    feed = lambda: [(T(x), T(t)) for x, t in zip(_split(pb["x"], 4), _split(pb["target"], 4))]  # noqa: E731
+    check_lifecycle(lambda: BinaryPrecision(threshold=0.7), feed, lambda r: close(r, pb["precision_07"]), {"num_tp", "num_fp", "num_label"})
+    check_lifecycle(lambda: BinaryRecall(threshold=0.3), feed, lambda r: close(r, pb["recall_03"]), {"num_tp", "num_true_labels"})
     bf = BinaryF1Score().update(T([0.1, 0.9, 0.6, 0.2]), T([0, 1, 0, 0]))
     close(bf.compute(), 2 / 3)
     assert torch.isnan(MulticlassAccuracy().compute())

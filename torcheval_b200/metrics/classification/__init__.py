@@ -10,6 +10,8 @@ from .binned_precision_recall_curve import (
 )
 from .confusion_matrix import BinaryConfusionMatrix, MulticlassConfusionMatrix
 from .f1_score import BinaryF1Score, MulticlassF1Score
+from .precision import BinaryPrecision, MulticlassPrecision
+from .recall import BinaryRecall, MulticlassRecall
 
 __all__ = [
     "BinaryAccuracy",
@@ -20,6 +22,8 @@ __all__ = [
     "BinaryBinnedPrecisionRecallCurve",
     "BinaryConfusionMatrix",
     "BinaryF1Score",
+    "BinaryPrecision",
+    "BinaryRecall",
     "MulticlassAccuracy",
     "MulticlassAUPRC",
     "MulticlassAUROC",
@@ -28,6 +32,8 @@ __all__ = [
     "MulticlassBinnedPrecisionRecallCurve",
     "MulticlassConfusionMatrix",
     "MulticlassF1Score",
+    "MulticlassPrecision",
+    "MulticlassRecall",
     "MultilabelAUPRC",
     "MultilabelBinnedAUPRC",
     "MultilabelBinnedPrecisionRecallCurve",

@@ -13,6 +13,8 @@ from .classification.binned_precision_recall_curve import (
 )
 from .classification.confusion_matrix import binary_confusion_matrix, multiclass_confusion_matrix
 from .classification.f1_score import binary_f1_score, multiclass_f1_score
+from .classification.precision import binary_precision, multiclass_precision
+from .classification.recall import binary_recall, multiclass_recall
 
 __all__ = [
     "binary_accuracy",
@@ -23,6 +25,8 @@ __all__ = [
     "binary_binned_precision_recall_curve",
     "binary_confusion_matrix",
     "binary_f1_score",
+    "binary_precision",
+    "binary_recall",
     "multiclass_accuracy",
     "multiclass_auprc",
     "multiclass_auroc",
@@ -31,6 +35,8 @@ __all__ = [
     "multiclass_binned_precision_recall_curve",
     "multiclass_confusion_matrix",
     "multiclass_f1_score",
+    "multiclass_precision",
+    "multiclass_recall",
     "multilabel_auprc",
     "multilabel_binned_auprc",
     "multilabel_binned_precision_recall_curve",
