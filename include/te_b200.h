@@ -279,6 +279,21 @@ TE_API int te_binary_auprc_from_keys_finish(int64_t n, double positives_above, d
                                             const double* above_dev, double* out, void* scratch,
                                             size_t scratch_bytes, void* stream);
 
+/* Exact precision-recall curve of (score, target == 1) — precision_recall_curve.py:208-231
+ * (_compute_for_each_class: sort, tie mask, cumsum, flip, append (1, 0)).  Two calls around one
+ * host read, because the number of points K (= distinct scores) sizes the outputs:
+ *  _begin : sort + count; out[0] = K, out[1] = #positives, out[2] = #negatives,
+ *           out[4] = TE_RANK_FLAG_* (non-zero: the packed representation does not apply, see
+ *           te_binary_auroc).  `scratch` (te_binary_rank_scratch_bytes(n)) keeps the sorted keys and
+ *           must reach _finish untouched.
+ *  _finish: precision[K + 1], recall[K + 1], thresholds[K] (float32, device), thresholds ascending,
+ *           closing point (precision 1, recall 0) last; recall is 1 where there are no positives. */
+TE_API int te_binary_pr_curve_begin(const float* score, const void* target, int32_t target_dtype,
+                                    int64_t n, double* out, void* scratch, size_t scratch_bytes,
+                                    void* stream);
+TE_API int te_binary_pr_curve_finish(int64_t n, float* precision, float* recall, float* thresholds,
+                                     void* scratch, size_t scratch_bytes, void* stream);
+
 /* The sort on its own: ascending, stable, 32-bit keys with an optional 32-bit payload
  * (vals_in/vals_out both NULL or both set).  Replaces torch.sort at auroc.py:121. */
 TE_API size_t te_sort_u32_scratch_bytes(int64_t n, int32_t with_values);

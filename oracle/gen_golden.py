@@ -214,6 +214,36 @@ def main() -> None:
         recall_03=F.binary_recall(xb4, t, threshold=0.3),
     )
 
+    # ---------------- exact precision-recall curves, recall at fixed precision (section 8f #1) ------
+    for name, x, y in (
+        ("ties", (randint(0, 40, (3001,)).float() / 40), randint(0, 2, (3001,))),
+        ("distinct", rand(2000), randint(0, 2, (2000,))),
+        ("no_pos", rand(300), torch.zeros(300, dtype=torch.int64)),
+        ("logits", torch.randn(1500, generator=g) * 3, randint(0, 2, (1500,))),
+        ("doc", torch.tensor([0.1, 0.5, 0.7, 0.8]), torch.tensor([0, 0, 1, 1])),
+    ):
+        pr, rc, th = F.binary_precision_recall_curve(x, y)
+        rec = dict(x=x, y=y, precision=pr, recall=rc, thresholds=th)
+        for mp in (0.0, 0.5, 0.9, 1.0):
+            r, t = F.binary_recall_at_fixed_precision(x, y, min_precision=mp)
+            rec[f"rafp_{int(mp * 100)}"] = torch.stack([r, t.to(r.dtype)])
+        put(f"pr_curve/{name}", **rec)
+    inp, tgt = rand(700, 4), randint(0, 4, (700,))
+    inp[:, 1] = (inp[:, 1] * 10).round() / 10
+    pr, rc, th = F.multiclass_precision_recall_curve(inp, tgt, num_classes=4)
+    rec = dict(x=inp, y=tgt)
+    for c in range(4):
+        rec[f"precision_{c}"], rec[f"recall_{c}"], rec[f"thresholds_{c}"] = pr[c], rc[c], th[c]
+    put("pr_curve_multiclass/c4", **rec)
+    ml = randint(0, 2, (700, 4))
+    pr, rc, th = F.multilabel_precision_recall_curve(inp, ml, num_labels=4)
+    rec = dict(x=inp, y=ml)
+    for c in range(4):
+        rec[f"precision_{c}"], rec[f"recall_{c}"], rec[f"thresholds_{c}"] = pr[c], rc[c], th[c]
+    r, t = F.multilabel_recall_at_fixed_precision(inp, ml, num_labels=4, min_precision=0.5)
+    rec["rafp_50"] = torch.stack([torch.stack(r), torch.stack(t)])
+    put("pr_curve_multilabel/l4", **rec)
+
     OUT.parent.mkdir(parents=True, exist_ok=True)
     np.savez_compressed(OUT, **store)
     print(f"wrote {OUT} ({OUT.stat().st_size / 1024:.0f} KiB, {len(store)} arrays)")

@@ -225,11 +225,34 @@ def binary_auprc_from_keys_finish(state, positives_above, samples_above=None):
     return out
 
 
+def binary_pr_curve(score, target):
+    """Ascending thresholds; one point per distinct score + the closing (1, 0)."""
+    f = _flags(score, target)
+    if f:
+        return None, f
+    x, y = _np(score).astype(np.float32), _np(target).astype(np.int64)
+    x = np.where(x == 0, np.float32(0.0), x)  # -0.0 ties with +0.0
+    order = np.argsort(x, kind="stable")
+    xs, ys = x[order], y[order]
+    n, P = xs.size, int(ys.sum())
+    if n == 0:
+        return (torch.ones(1), torch.zeros(1), torch.zeros(0)), 0
+    start = np.concatenate([[True], xs[1:] != xs[:-1]])
+    gp = np.nonzero(start)[0]
+    pos_before = np.concatenate([[0], np.cumsum(ys)[:-1]])[gp]
+    tp = (P - pos_before).astype(np.float64)
+    prec = (tp / (n - gp)).astype(np.float32)
+    rec = (tp / P).astype(np.float32) if P else np.ones(gp.size, dtype=np.float32)
+    prec = np.concatenate([prec, np.ones(1, dtype=np.float32)])
+    rec = np.concatenate([rec, np.zeros(1, dtype=np.float32)])
+    return (torch.from_numpy(prec), torch.from_numpy(rec), torch.from_numpy(xs[gp].copy())), 0
+
+
 _NAMES = [
     "cm_update_", "cm_update_logits_", "class_counts_", "match_count", "binned_hist_update_",
     "binned_hist2d_update_", "binned_counts", "binned_integrate", "binary_auroc_packed",
     "binary_auprc_packed", "binary_auroc_general", "binary_auprc_general", "sort_u32", "rank_pack", "ovr_rank",
-    "partition_u32", "binary_auroc_from_keys", "binary_auprc_from_keys_begin", "binary_auprc_from_keys_finish",
+    "partition_u32", "binary_auroc_from_keys", "binary_auprc_from_keys_begin", "binary_auprc_from_keys_finish", "binary_pr_curve",
 ]
 
 

@@ -230,6 +230,71 @@ def test_functional_precision_recall(backend, golden):
         F.binary_precision(torch.rand(2, 2), torch.rand(2, 2))
 
 
+def test_precision_recall_curves(backend, golden):
+    """SURVEY.md section 8f #1: exact PR curves + recall at fixed precision against the reference."""
+    from torcheval_b200.metrics import (
+        BinaryPrecisionRecallCurve, BinaryRecallAtFixedPrecision, MulticlassPrecisionRecallCurve,
+        MultilabelPrecisionRecallCurve, MultilabelRecallAtFixedPrecision,
+    )
+    from torcheval_b200.metrics import functional as F
+
+    for name in golden.cases("pr_curve"):
+        c = golden.case(f"pr_curve/{name}")
+        pr, rc, th = F.binary_precision_recall_curve(T(c["x"]), T(c["y"]))
+        assert pr.dtype == torch.float32 and rc.dtype == torch.float32 and th.dtype == torch.float32
+        assert pr.shape == c["precision"].shape and th.shape == c["thresholds"].shape, name
+        np.testing.assert_array_equal(th.numpy(), c["thresholds"])  # thresholds are the scores themselves
+        close(pr, c["precision"], 1e-6)
+        close(rc, c["recall"], 1e-6)
+        for mp in (0.0, 0.5, 0.9, 1.0):
+            r, t = F.binary_recall_at_fixed_precision(T(c["x"]), T(c["y"]), min_precision=mp)
+            close(torch.stack([r, t]), c[f"rafp_{int(mp * 100)}"], 1e-6)
+    c = golden.case("pr_curve/ties")
+    feed = lambda: [(T(x), T(y)) for x, y in zip(_split(c["x"], 3), _split(c["y"], 3))]  # noqa: E731
+
+    def curve_ok(r):
+        close(r[0], c["precision"], 1e-6)
+        close(r[1], c["recall"], 1e-6)
+        np.testing.assert_array_equal(r[2].numpy(), c["thresholds"])
+
+    check_lifecycle(BinaryPrecisionRecallCurve, feed, curve_ok, {"inputs", "targets"})
+    check_lifecycle(lambda: BinaryRecallAtFixedPrecision(min_precision=0.5), feed,
+                    lambda r: close(torch.stack(list(r)), c["rafp_50"], 1e-6), {"inputs", "targets"})
+    # int64 scores and labels other than 0 / 1 (they count as negatives)
+    pr, rc, th = F.binary_precision_recall_curve(T([1, 5, 7, 8]), T([0, 3, 1, 1]))
+    assert th.dtype == torch.int64 and th.tolist() == [1, 5, 7, 8]
+    close(pr, [0.5, 2 / 3, 1.0, 1.0, 1.0], 1e-6)
+    close(rc, [1.0, 1.0, 1.0, 0.5, 0.0], 1e-6)
+    c = golden.case("pr_curve_multiclass/c4")
+    pr, rc, th = F.multiclass_precision_recall_curve(T(c["x"]), T(c["y"]), num_classes=4)
+    m = MulticlassPrecisionRecallCurve(num_classes=4).update(T(c["x"][:300]), T(c["y"][:300])).update(T(c["x"][300:]), T(c["y"][300:]))
+    mp_, mr_, mt_ = m.compute()
+    for k in range(4):
+        close(pr[k], c[f"precision_{k}"], 1e-6)
+        close(rc[k], c[f"recall_{k}"], 1e-6)
+        np.testing.assert_array_equal(th[k].numpy(), c[f"thresholds_{k}"])
+        close(mp_[k], c[f"precision_{k}"], 1e-6)
+        np.testing.assert_array_equal(mt_[k].numpy(), c[f"thresholds_{k}"])
+    c = golden.case("pr_curve_multilabel/l4")
+    pr, rc, th = F.multilabel_precision_recall_curve(T(c["x"]), T(c["y"]), num_labels=4)
+    for k in range(4):
+        close(pr[k], c[f"precision_{k}"], 1e-6)
+        close(rc[k], c[f"recall_{k}"], 1e-6)
+        np.testing.assert_array_equal(th[k].numpy(), c[f"thresholds_{k}"])
+    r, t = F.multilabel_recall_at_fixed_precision(T(c["x"]), T(c["y"]), num_labels=4, min_precision=0.5)
+    close(torch.stack([torch.stack(r), torch.stack(t)]), c["rafp_50"], 1e-6)
+    ml = MultilabelPrecisionRecallCurve(num_labels=4).update(T(c["x"]), T(c["y"]))
+    close(ml.compute()[1][2], c["recall_2"], 1e-6)
+    mr = MultilabelRecallAtFixedPrecision(num_labels=4, min_precision=0.5).update(T(c["x"]), T(c["y"]))
+    close(torch.stack(mr.compute()[0]), c["rafp_50"][0], 1e-6)
+    with pytest.raises(ValueError, match="input should be a one-dimensional tensor"):
+        F.binary_precision_recall_curve(torch.rand(2, 2), torch.rand(2, 2))
+    with pytest.raises(ValueError, match="Expected min_precision to be a float in the"):
+        F.binary_recall_at_fixed_precision(torch.rand(4), torch.ones(4), min_precision=2.0)
+    with pytest.raises(ValueError, match="input should have shape of \\(num_sample, num_classes\\)"):
+        F.multiclass_precision_recall_curve(torch.rand(4, 3), torch.zeros(4, dtype=torch.int64), num_classes=2)
+
+
 def test_error_messages(backend):
     from torcheval_b200.metrics import functional as F
 

@@ -577,6 +577,34 @@ def test_auprc_from_keys_two_phase(ops, n):
     close(f_lo[3] + f_hi[3], whole[3], 1e-12)
 
 
+@pytest.mark.parametrize("n", [1, 2, 511, 513, 40000, 300001, 3_000_001])
+def test_pr_curve_vs_cpu(ops, n):
+    """te_binary_pr_curve_begin/_finish against the numpy restatement of
+    precision_recall_curve.py:208-231 (tests/cpu_backend.py), thresholds bit-exact."""
+    import cpu_backend
+
+    rs = np.random.default_rng(n)
+    for kind in ("ties", "distinct", "no_pos", "all_pos", "constant"):
+        x = rs.random(n, dtype=np.float32)
+        y = rs.integers(0, 2, n)
+        if kind == "ties":
+            x = (rs.integers(0, 300, n) / 300).astype(np.float32)
+        elif kind == "no_pos":
+            y[:] = 0
+        elif kind == "all_pos":
+            y[:] = 1
+        elif kind == "constant":
+            x[:] = 0.25
+        (p, r, t), flags = ops.binary_pr_curve(dev(x), dev(y))
+        (wp, wr, wt), _ = cpu_backend.binary_pr_curve(torch.from_numpy(x), torch.from_numpy(y))
+        assert flags == 0 and t.shape == wt.shape, (n, kind)
+        np.testing.assert_array_equal(t.cpu().numpy(), wt.numpy())
+        np.testing.assert_allclose(p.cpu().numpy(), wp.numpy(), rtol=2e-7, atol=0)
+        np.testing.assert_allclose(r.cpu().numpy(), wr.numpy(), rtol=2e-7, atol=0)
+    curve, flags = ops.binary_pr_curve(dev(np.array([0.5, -1.0], dtype=np.float32)), dev(np.array([0, 1])))
+    assert curve is None and flags == 2
+
+
 # =============================================================================== K2: one-vs-rest
 @pytest.mark.parametrize("n,C", [(1, 3), (257, 17), (5000, 8), (40001, 13), (3000, 1000)])
 def test_ovr_rank_vs_oracle(ops, n, C):

@@ -146,3 +146,33 @@ def multiclass_auprc(input: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
 
 def multilabel_auprc(input: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
     return _one_vs_rest(input, target, auprc=True, multilabel=True)
+
+
+def binary_precision_recall_curve(input: torch.Tensor, target: torch.Tensor, pos_label: int = 1):
+    """(precision, recall, thresholds) of the reference's ``_compute_for_each_class``
+    (precision_recall_curve.py:208-231): thresholds = distinct scores, ascending, in the input's
+    dtype; precision / recall float32 with the closing (1, 0) appended; on input.device.
+    Positives are ``target == pos_label``; anything else counts as a negative."""
+    out_dev = input.device
+    dev = compute_device(input)
+    x = stage(input, dev)
+    t = stage(target, dev)
+    lab = t if (pos_label == 1 and t.dtype in ops._DTYPE_CODE) else (t == pos_label).to(torch.uint8)
+    curve, flags = None, N.TE_RANK_FLAG_NEGATIVE_SCORE
+    values = None
+    if x.dtype in (torch.float32, torch.float16, torch.bfloat16):
+        curve, flags = ops.binary_pr_curve(x.float(), lab)
+        if flags & N.TE_RANK_FLAG_BAD_LABEL:  # labels other than 0 / 1 are negatives here, not an error
+            lab = (t == pos_label).to(torch.uint8)
+            curve, flags = ops.binary_pr_curve(x.float(), lab)
+    if flags:
+        # negative scores, or a dtype float32 cannot hold: dense ranks go through the kernel (they
+        # order and tie like the scores), the thresholds are the distinct score values themselves
+        values, inv = torch.unique(x, sorted=True, return_inverse=True)
+        if lab.dtype != torch.uint8:
+            lab = (t == pos_label).to(torch.uint8)
+        curve, flags = ops.binary_pr_curve(inv.to(torch.int32).view(torch.float32), lab)
+        assert flags == 0
+    precision, recall, thresholds = curve
+    thresholds = values if values is not None else thresholds.to(input.dtype)
+    return precision.to(out_dev), recall.to(out_dev), thresholds.to(out_dev)

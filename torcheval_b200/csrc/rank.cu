@@ -261,7 +261,7 @@ struct alignas(16) ChunkRec {
   unsigned long long A;      // AUROC: local part of 2U
   unsigned long long P;      // positives in the chunk
   unsigned long long lead;   // positives whose tie group started before the chunk
-  unsigned long long pad;
+  unsigned long long starts; // tie groups that start inside the chunk (counted when POS)
 };
 
 // The sorted array is cut into nchunks contiguous chunks of steps_per_chunk * 512 records, one per
@@ -305,6 +305,7 @@ __global__ void __launch_bounds__(kFinBlock, kFinWarpsPerSm / (kFinBlock / kWarp
 
   FState carry = MODE == 1 ? excl_in[chunk] : f_identity();
   unsigned long long accA = 0, accP = 0, accLead = 0;
+  uint32_t accStarts = 0;
   double accD = 0.0;
   // pos_above / cnt_above: positives / samples with a score above everything in `keys` that live
   // on other ranks (0 when `keys` is the whole sample set); above_dev, if given, holds the same
@@ -403,6 +404,7 @@ __global__ void __launch_bounds__(kFinBlock, kFinWarpsPerSm / (kFinBlock / kWarp
       //   "pre"  positives: (g.S + lc) + g.M      (group known inside the chunk: g.F)
       //                     (g.S + lc) + [E.M]    (group older than the chunk: counted in lead)
       const uint32_t npos = n_pre + n_post;
+      if (POS) accStarts += __popc(starts);
       accP += npos;
       accA += (unsigned long long)g.S * (npos + n_post) + s_lc + s_lgs;
       if (g.F)
@@ -436,10 +438,11 @@ __global__ void __launch_bounds__(kFinBlock, kFinWarpsPerSm / (kFinBlock / kWarp
     accA = warp_sum(accA);
     accP = warp_sum(accP);
     accLead = warp_sum(accLead);
+    const unsigned long long nst = warp_sum((unsigned long long)accStarts);
     if (lane == 0) {
       ChunkRec r;
       r.st = carry;
-      r.A = accA, r.P = accP, r.lead = accLead, r.pad = 0;
+      r.A = accA, r.P = accP, r.lead = accLead, r.starts = nst;
       rec[chunk] = r;
     }
   } else {
@@ -453,44 +456,58 @@ __global__ void __launch_bounds__(kFinBlock, kFinWarpsPerSm / (kFinBlock / kWarp
 template <int MODE>
 __global__ void __launch_bounds__(1024)
     rank_chunk_scan_kernel(const ChunkRec* __restrict__ rec, uint32_t nchunks, uint32_t n,
-                           const RankScalars* __restrict__ scal, FState* excl_out, double* out) {
+                           const RankScalars* __restrict__ scal, FState* excl_out, double* out,
+                           uint32_t* starts_out = nullptr) {
   __shared__ FState s_warp[32];
   __shared__ unsigned long long s_u[32];
+  __shared__ uint32_t s_ns[32];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   FState carry = f_identity();
   unsigned long long u2 = 0;
+  uint32_t starts_carry = 0;  // tie groups that start before the current strip
   for (uint32_t base = 0; base < nchunks; base += 1024) {
     const uint32_t i = base + tid;
     ChunkRec r;
     r.st = f_identity();
-    r.A = r.P = r.lead = 0;
+    r.A = r.P = r.lead = r.starts = 0;
     if (i < nchunks) r = rec[i];
     FState incl = r.st;
+    uint32_t ns_incl = (uint32_t)r.starts;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       const FState u = f_shfl_up<true>(incl, o);
-      if (lane >= (unsigned)o) incl = f_combine(u, incl);
+      const uint32_t un = __shfl_up_sync(kFull, ns_incl, o);
+      if (lane >= (unsigned)o) incl = f_combine(u, incl), ns_incl += un;
     }
-    if (lane == 31) s_warp[warp] = incl;
+    if (lane == 31) s_warp[warp] = incl, s_ns[warp] = ns_incl;
     FState excl = f_shfl_up<true>(incl, 1);
     if (lane == 0) excl = f_identity();
     __syncthreads();
     FState wprefix = f_identity(), strip = f_identity();
+    uint32_t ns_prefix = 0, ns_strip = 0;
     for (int w = 0; w < 32; ++w) {
       const FState x = s_warp[w];
-      if (w < (int)warp) wprefix = f_combine(wprefix, x);
+      if (w < (int)warp) wprefix = f_combine(wprefix, x), ns_prefix += s_ns[w];
       strip = f_combine(strip, x);
+      ns_strip += s_ns[w];
     }
     excl = f_combine(carry, f_combine(wprefix, excl));
     if (MODE == 1) {
-      if (i < nchunks) excl_out[i] = excl;
+      if (i < nchunks) {
+        excl_out[i] = excl;
+        if (starts_out) starts_out[i] = starts_carry + ns_prefix + ns_incl - (uint32_t)r.starts;
+      }
     } else if (i < nchunks) {
       u2 += r.A + (unsigned long long)excl.S * (2ull * r.P - r.lead) + (unsigned long long)excl.M * r.lead;
     }
     carry = f_combine(carry, strip);
+    starts_carry += ns_strip;
     __syncthreads();  // s_warp is rewritten by the next strip
   }
-  if (MODE == 1) return;
+  if (MODE == 1) {
+    if (starts_out && tid == 0) starts_out[nchunks] = starts_carry;  // number of distinct scores
+    return;
+  }
   u2 = warp_sum(u2);
   if (lane == 0) s_u[warp] = u2;
   __syncthreads();
@@ -506,6 +523,102 @@ __global__ void __launch_bounds__(1024)
     out[5] = (double)(tu >> 32);           // 2U exactly, as two 32-bit halves
     out[6] = (double)(tu & 0xffffffffull);
     out[7] = (double)n;
+  }
+}
+
+// Precision-recall curve (precision_recall_curve.py:208-231): one point per distinct score, in
+// ascending-threshold order — which is the order the keys are sorted in, so the "flip" of the
+// reference costs nothing.  For the tie group that starts at sorted position gp, with gs
+// negatives before it: TP = P - (gp - gs) samples are positive with score >= threshold, out of
+// n - gp samples with score >= threshold.  The output index of a group is the number of groups
+// that start before it: chunk offset (starts_excl) + a warp scan inside the step.
+__global__ void __launch_bounds__(kFinBlock, kFinWarpsPerSm / (kFinBlock / kWarp))
+    rank_pr_curve_kernel(const uint32_t* __restrict__ keys, uint32_t n, uint32_t steps_per_chunk,
+                         uint32_t nchunks, const FState* __restrict__ excl_in,
+                         const uint32_t* __restrict__ starts_excl, const RankScalars* __restrict__ scal,
+                         float* __restrict__ precision, float* __restrict__ recall,
+                         float* __restrict__ thresholds) {
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t chunk = blockIdx.x * (kFinBlock / kWarp) + (threadIdx.x >> 5);
+  if (chunk >= nchunks) return;
+  const uint64_t begin64 = (uint64_t)chunk * steps_per_chunk * kFinStep;
+  if (begin64 >= n) return;
+  const uint32_t begin = (uint32_t)begin64;
+  const uint32_t end = (uint32_t)min((uint64_t)n, begin64 + (uint64_t)steps_per_chunk * kFinStep);
+  const double ptot = (double)scal->positives;
+  if (chunk == 0 && lane == 0) {  // the closing point without a threshold
+    const uint32_t K = starts_excl[nchunks];
+    precision[K] = 1.0f;
+    recall[K] = 0.0f;
+  }
+  FState carry = excl_in[chunk];
+  uint32_t out_at = starts_excl[chunk];
+  uint32_t last = begin > 0 ? keys[begin - 1] >> 1 : 0u;
+  for (uint32_t at = begin; at < end; at += kFinStep) {
+    const uint32_t i0 = at + lane * kFinIpt;
+    const uint32_t cnt = i0 < end ? min((uint32_t)kFinIpt, end - i0) : 0u;
+    uint32_t k[kFinIpt];
+    if (at + kFinStep <= end) {
+#pragma unroll
+      for (int q = 0; q < kFinIpt / 4; ++q) {
+        const int4 a = ld_stream_v4(keys + i0 + 4 * q);
+        k[4 * q] = a.x, k[4 * q + 1] = a.y, k[4 * q + 2] = a.z, k[4 * q + 3] = a.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < kFinIpt; ++j) k[j] = (i0 + j < end) ? keys[i0 + j] : 0u;
+    }
+    uint32_t prev = __shfl_up_sync(kFull, k[kFinIpt - 1] >> 1, 1);
+    if (lane == 0) prev = last;
+    const uint32_t tail = (end - at >= (uint32_t)kFinStep) ? k[kFinIpt - 1] >> 1 : 0u;
+    last = __shfl_sync(kFull, tail, 31);
+    FState mine = f_identity();
+    uint32_t starts = 0;
+#pragma unroll
+    for (int j = 0; j < kFinIpt; ++j) {
+      if (j < (int)cnt) {
+        const uint32_t sc = k[j] >> 1;
+        const bool st = (j == 0 && i0 == 0) || sc != prev;
+        prev = sc;
+        if (st) {
+          starts |= 1u << j;
+          mine.F = 1;
+          mine.M = mine.S;
+          mine.Mp = i0 + j;
+        }
+        if (!(k[j] & 1u)) ++mine.S;
+      }
+    }
+    FState incl = mine;
+    uint32_t ns_incl = __popc(starts);
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const FState u = f_shfl_up<true>(incl, o);
+      const uint32_t un = __shfl_up_sync(kFull, ns_incl, o);
+      if (lane >= (unsigned)o) incl = f_combine(u, incl), ns_incl += un;
+    }
+    FState excl = f_shfl_up<true>(incl, 1);
+    if (lane == 0) excl = f_identity();
+    const FState step_agg = f_shfl<true>(incl, 31);
+    const uint32_t step_starts = __shfl_sync(kFull, ns_incl, 31);
+    const FState g = f_combine(carry, excl);
+    uint32_t c = g.S, o = out_at + ns_incl - __popc(starts);
+#pragma unroll
+    for (int j = 0; j < kFinIpt; ++j) {
+      if (j < (int)cnt) {
+        if (starts & (1u << j)) {
+          const uint32_t gp = i0 + j;
+          const double tp = ptot - (double)(gp - c);
+          precision[o] = (float)(tp / (double)(n - gp));
+          recall[o] = ptot == 0.0 ? 1.0f : (float)(tp / ptot);  // no positives: NaN -> 1.0 (:228-229)
+          thresholds[o] = __uint_as_float(k[j] >> 1);
+          ++o;
+        }
+        if (!(k[j] & 1u)) ++c;
+      }
+    }
+    carry = f_combine(carry, step_agg);
+    out_at += step_starts;
   }
 }
 
@@ -606,6 +719,7 @@ struct RankPlan {
   size_t off_gprefix;   // group prefixes, 4 passes * ceil(sort_tiles / 32) * 256 u32 (zeroed by memset)
   size_t off_lookback_rest;  // counts of passes 1..3: each pass clears the rows of the next one
   size_t off_agg, off_inc;
+  size_t off_starts;    // exclusive count of tie-group starts per chunk (+ total): PR curve
   size_t zero_bytes;
   size_t off_partial;
   size_t total;
@@ -640,6 +754,7 @@ RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final)
   p.off_gprefix = take((size_t)4 * lb_groups * kRadix * 4);
   p.off_agg = take(with_final ? (size_t)kMaxChunks * sizeof(ChunkRec) : 0);
   p.off_inc = take(with_final ? (size_t)kMaxChunks * sizeof(FState) : 0);
+  p.off_starts = take(with_final ? (size_t)(kMaxChunks + 1) * 4 : 0);
   p.zero_bytes = o - p.off_zero;
   p.off_lookback_rest = take((size_t)3 * p.sort_tiles * kRadix * 4);
   p.off_partial = take(with_final ? (size_t)kMaxChunks * 8 : 0);
@@ -1715,6 +1830,66 @@ extern "C" int te_binary_auprc_from_keys_finish(int64_t n, double positives_abov
   }
   TE_PROF("rank_reduce", st);
   rank_reduce_kernel<1><<<1, 1024, 0, st>>>(partial, nchunks, p.n, scal, out);
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+__global__ void pr_info_kernel(const uint32_t* starts, uint32_t nchunks, double* out) {
+  if (threadIdx.x == 0) out[0] = (double)starts[nchunks];
+}
+
+extern "C" int te_binary_pr_curve_begin(const float* score, const void* target, int32_t target_dtype,
+                                        int64_t n, double* out, void* scratch, size_t scratch_bytes,
+                                        void* stream) {
+  if (!out || (n > 0 && (!score || !target))) return TE_ERR_INVALID_ARGUMENT;
+  if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  const RankPlan p = make_plan(n, false, true, true);
+  if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
+  uint32_t* ka = at<uint32_t>(scratch, p.off_keys_a);
+  uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
+  if (n > 0) {
+    int rc = launch_ingest_dtype<kPacked>(score, target, target_dtype, p, ka, nullptr, scratch, sms, st);
+    if (rc) return rc;
+    rc = run_passes(p, scratch, ka, kb, ka, nullptr, nullptr, nullptr, st);  // sorted keys end in ka
+    if (rc) return rc;
+  }
+  const int rc = finish_packed(p, ka, 0, out, scratch, sms, st, true);  // out[] as te_binary_auroc
+  if (rc) return rc;
+  const ChunkGeom cg = chunk_geom(p.n, sms);
+  const uint32_t nchunks = n > 0 ? cg.nchunks : 0;
+  uint32_t* starts = at<uint32_t>(scratch, p.off_starts);
+  rank_chunk_scan_kernel<1><<<1, 1024, 0, st>>>(at<ChunkRec>(scratch, p.off_agg), nchunks, p.n,
+                                                at<RankScalars>(scratch, p.off_scal),
+                                                at<FState>(scratch, p.off_inc), nullptr, starts);
+  pr_info_kernel<<<1, 32, 0, st>>>(starts, nchunks, out);
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+extern "C" int te_binary_pr_curve_finish(int64_t n, float* precision, float* recall, float* thresholds,
+                                         void* scratch, size_t scratch_bytes, void* stream) {
+  if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  if (!precision || !recall || (n > 0 && !thresholds)) return TE_ERR_INVALID_ARGUMENT;
+  const RankPlan p = make_plan(n, false, true, true);
+  if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  if (n == 0) {  // no scores: the curve is the closing point alone
+    const float one = 1.0f, zero = 0.0f;
+    TE_CUDA_TRY(cudaMemcpyAsync(precision, &one, 4, cudaMemcpyHostToDevice, st));
+    TE_CUDA_TRY(cudaMemcpyAsync(recall, &zero, 4, cudaMemcpyHostToDevice, st));
+    return TE_OK;
+  }
+  const ChunkGeom cg = chunk_geom(p.n, sms);
+  TE_PROF("rank_pr_curve", st);
+  rank_pr_curve_kernel<<<(cg.nchunks + kFinBlock / kWarp - 1) / (kFinBlock / kWarp), kFinBlock, 0, st>>>(
+      at<uint32_t>(scratch, p.off_keys_a), p.n, cg.steps_per_chunk, cg.nchunks, at<FState>(scratch, p.off_inc),
+      at<uint32_t>(scratch, p.off_starts), at<RankScalars>(scratch, p.off_scal), precision, recall, thresholds);
   TE_LAUNCH_CHECK();
   return TE_OK;
 }

@@ -11,7 +11,13 @@ from .binned_precision_recall_curve import (
 from .confusion_matrix import BinaryConfusionMatrix, MulticlassConfusionMatrix
 from .f1_score import BinaryF1Score, MulticlassF1Score
 from .precision import BinaryPrecision, MulticlassPrecision
+from .precision_recall_curve import (
+    BinaryPrecisionRecallCurve,
+    MulticlassPrecisionRecallCurve,
+    MultilabelPrecisionRecallCurve,
+)
 from .recall import BinaryRecall, MulticlassRecall
+from .recall_at_fixed_precision import BinaryRecallAtFixedPrecision, MultilabelRecallAtFixedPrecision
 
 __all__ = [
     "BinaryAccuracy",
@@ -23,7 +29,9 @@ __all__ = [
     "BinaryConfusionMatrix",
     "BinaryF1Score",
     "BinaryPrecision",
+    "BinaryPrecisionRecallCurve",
     "BinaryRecall",
+    "BinaryRecallAtFixedPrecision",
     "MulticlassAccuracy",
     "MulticlassAUPRC",
     "MulticlassAUROC",
@@ -33,8 +41,11 @@ __all__ = [
     "MulticlassConfusionMatrix",
     "MulticlassF1Score",
     "MulticlassPrecision",
+    "MulticlassPrecisionRecallCurve",
     "MulticlassRecall",
     "MultilabelAUPRC",
     "MultilabelBinnedAUPRC",
     "MultilabelBinnedPrecisionRecallCurve",
+    "MultilabelPrecisionRecallCurve",
+    "MultilabelRecallAtFixedPrecision",
 ]

@@ -14,7 +14,16 @@ from .classification.binned_precision_recall_curve import (
 from .classification.confusion_matrix import binary_confusion_matrix, multiclass_confusion_matrix
 from .classification.f1_score import binary_f1_score, multiclass_f1_score
 from .classification.precision import binary_precision, multiclass_precision
+from .classification.precision_recall_curve import (
+    binary_precision_recall_curve,
+    multiclass_precision_recall_curve,
+    multilabel_precision_recall_curve,
+)
 from .classification.recall import binary_recall, multiclass_recall
+from .classification.recall_at_fixed_precision import (
+    binary_recall_at_fixed_precision,
+    multilabel_recall_at_fixed_precision,
+)
 
 __all__ = [
     "binary_accuracy",
@@ -26,7 +35,9 @@ __all__ = [
     "binary_confusion_matrix",
     "binary_f1_score",
     "binary_precision",
+    "binary_precision_recall_curve",
     "binary_recall",
+    "binary_recall_at_fixed_precision",
     "multiclass_accuracy",
     "multiclass_auprc",
     "multiclass_auroc",
@@ -36,8 +47,11 @@ __all__ = [
     "multiclass_confusion_matrix",
     "multiclass_f1_score",
     "multiclass_precision",
+    "multiclass_precision_recall_curve",
     "multiclass_recall",
     "multilabel_auprc",
     "multilabel_binned_auprc",
     "multilabel_binned_precision_recall_curve",
+    "multilabel_precision_recall_curve",
+    "multilabel_recall_at_fixed_precision",
 ]

@@ -482,3 +482,37 @@ def binary_auprc_from_keys_finish(state, positives_above, samples_above=None) ->
             ),
         )
     return out
+
+
+def binary_pr_curve(score: torch.Tensor, target: torch.Tensor):
+    """Exact precision-recall curve of (score, target == 1): ((precision[K+1], recall[K+1],
+    thresholds[K]) float32 on the device, thresholds ascending), flags.  flags != 0: the packed
+    representation does not apply (negative scores / labels outside {0, 1}) and the curve is None.
+    One host read (K sizes the outputs)."""
+    lib = N.load()
+    dev = _require_cuda(score, target)
+    assert score.dim() == 1 and score.shape == target.shape and score.dtype == torch.float32
+    score, target = score.contiguous(), target.contiguous()
+    n = score.numel()
+    out = torch.zeros(8, dtype=torch.float64, device=dev)
+    scratch = _scratch(lib.te_binary_rank_scratch_bytes(n), dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_binary_pr_curve_begin",
+            lib.te_binary_pr_curve_begin(score.data_ptr(), target.data_ptr(), _DTYPE_CODE[target.dtype], n,
+                                         out.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
+        )
+        info = out.tolist()
+        flags = int(info[4])
+        if flags:
+            return None, flags
+        k = int(info[0])
+        precision = torch.empty(k + 1, dtype=torch.float32, device=dev)
+        recall = torch.empty(k + 1, dtype=torch.float32, device=dev)
+        thresholds = torch.empty(k, dtype=torch.float32, device=dev)
+        N.check(
+            "te_binary_pr_curve_finish",
+            lib.te_binary_pr_curve_finish(n, precision.data_ptr(), recall.data_ptr(), thresholds.data_ptr(),
+                                          scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
+        )
+    return (precision, recall, thresholds), 0
