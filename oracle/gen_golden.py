@@ -244,6 +244,28 @@ def main() -> None:
     rec["rafp_50"] = torch.stack([torch.stack(r), torch.stack(t)])
     put("pr_curve_multilabel/l4", **rec)
 
+    # ---------------- WindowedBinaryAUROC (section 8f #2) ------------------------------------------
+    from torcheval.metrics import WindowedBinaryAUROC
+
+    xs, ys = rand(2, 57) + 0.01, randint(0, 2, (2, 57))
+    ws = rand(2, 57) + 0.5
+    m = WindowedBinaryAUROC(num_tasks=2, max_num_samples=20)
+    outs, cuts = [], [0, 7, 15, 26, 31, 57]
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        m.update(xs[:, a:b], ys[:, a:b], ws[:, a:b] if a >= 15 else None)
+        outs.append(m.compute())
+    m2 = WindowedBinaryAUROC(num_tasks=2, max_num_samples=10).update(xs[:, :9], ys[:, :9])
+    m3 = WindowedBinaryAUROC(num_tasks=2, max_num_samples=10).update(xs[:, 9:33], ys[:, 9:33])
+    m2.merge_state([m3])
+    x1, y1 = rand(33) + 0.01, randint(0, 2, (33,))
+    m1 = WindowedBinaryAUROC(max_num_samples=25).update(x1, y1)
+    put(
+        "windowed_auroc/t2",
+        x=xs, y=ys, w=ws, cuts=torch.tensor(cuts), auroc_steps=torch.stack(outs),
+        merged=m2.compute(), merged_cap=torch.tensor(m2.max_num_samples), merged_next=torch.tensor(m2.next_inserted),
+        x1=x1, y1=y1, single=m1.compute(),
+    )
+
     OUT.parent.mkdir(parents=True, exist_ok=True)
     np.savez_compressed(OUT, **store)
     print(f"wrote {OUT} ({OUT.stat().st_size / 1024:.0f} KiB, {len(store)} arrays)")

@@ -295,6 +295,39 @@ def test_precision_recall_curves(backend, golden):
         F.multiclass_precision_recall_curve(torch.rand(4, 3), torch.zeros(4, dtype=torch.int64), num_classes=2)
 
 
+def test_windowed_binary_auroc(backend, golden):
+    """SURVEY.md section 8f #2: ring-buffer window semantics + merge against the reference."""
+    from torcheval_b200.metrics import WindowedBinaryAUROC
+
+    c = golden.case("windowed_auroc/t2")
+    xs, ys, ws, cuts = T(c["x"]), T(c["y"]), T(c["w"]), c["cuts"].tolist()
+    m = WindowedBinaryAUROC(num_tasks=2, max_num_samples=20)
+    for k, (a, b) in enumerate(zip(cuts[:-1], cuts[1:])):
+        m.update(xs[:, a:b], ys[:, a:b], ws[:, a:b] if a >= 15 else None)
+        got = m.compute()
+        assert got.dtype == torch.float64 and got.shape == (2,)
+        close(got, c["auroc_steps"][k])
+    assert m.total_samples == 57 and m.inputs.shape == (2, 20) and m.inputs.dtype == torch.float32
+    m2 = WindowedBinaryAUROC(num_tasks=2, max_num_samples=10).update(xs[:, :9], ys[:, :9])
+    m3 = WindowedBinaryAUROC(num_tasks=2, max_num_samples=10).update(xs[:, 9:33], ys[:, 9:33])
+    m2.merge_state([m3])
+    close(m2.compute(), c["merged"])
+    assert m2.max_num_samples == int(c["merged_cap"]) and m2.next_inserted == int(c["merged_next"])
+    m1 = WindowedBinaryAUROC(max_num_samples=25).update(T(c["x1"]), T(c["y1"]))
+    assert m1.compute().shape == ()
+    close(m1.compute(), c["single"])
+    sd = m1.state_dict()
+    assert set(sd) == {"max_num_samples", "total_samples", "inputs", "targets", "weights"}
+    m4 = WindowedBinaryAUROC(max_num_samples=25)
+    m4.load_state_dict(sd)
+    m4.next_inserted = m1.next_inserted
+    close(m4.compute(), c["single"])
+    m1.reset()
+    assert float(m1.inputs.abs().sum()) == 0  # (int states keep their value across reset, like the reference)
+    with pytest.raises(ValueError, match="`max_num_samples` value should be greater than and equal to 1"):
+        WindowedBinaryAUROC(max_num_samples=0)
+
+
 def test_error_messages(backend):
     from torcheval_b200.metrics import functional as F
 

@@ -10,5 +10,6 @@ from . import functional
 from .classification import *  # noqa: F401,F403
 from .classification import __all__ as _classification_all
 from .metric import Metric
+from .window import WindowedBinaryAUROC
 
-__all__ = ["Metric", "functional", *_classification_all]
+__all__ = ["Metric", "functional", "WindowedBinaryAUROC", *_classification_all]
