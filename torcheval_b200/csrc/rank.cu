@@ -289,10 +289,16 @@ inline ChunkGeom chunk_geom(uint32_t n, int sms) {
 // excl[chunk] (global state before the chunk) -> partial[chunk] (double bits).
 template <int MODE, bool POS = (MODE == 1)>
 __global__ void __launch_bounds__(kFinBlock, kFinWarpsPerSm / (kFinBlock / kWarp))
-    rank_chunk_kernel(const uint32_t* __restrict__ keys, uint32_t n, uint32_t steps_per_chunk,
-                      uint32_t nchunks, ChunkRec* rec, const FState* __restrict__ excl_in,
-                      const RankScalars* __restrict__ scal, unsigned long long* partial,
-                      double pos_above, double cnt_above, const double* __restrict__ above_dev) {
+    rank_chunk_kernel(const uint32_t* __restrict__ keys_, uint32_t n, uint32_t steps_per_chunk,
+                      uint32_t nchunks, ChunkRec* rec_, const FState* __restrict__ excl_in_,
+                      const RankScalars* __restrict__ scal_, unsigned long long* partial_,
+                      double pos_above, double cnt_above, const double* __restrict__ above_dev,
+                      size_t bstride) {
+  const uint32_t* __restrict__ keys = batch_ptr(keys_, bstride);
+  ChunkRec* rec = batch_ptr(rec_, bstride);
+  const FState* __restrict__ excl_in = batch_ptr(excl_in_, bstride);
+  const RankScalars* __restrict__ scal = batch_ptr(scal_, bstride);
+  unsigned long long* partial = batch_ptr(partial_, bstride);
   // POS: also track WHERE the current tie group started (needed by the AUPRC integrate sweep and
   // by the count sweep that feeds it; plain AUROC leaves it out)
   const unsigned lane = threadIdx.x & 31;
@@ -455,9 +461,14 @@ __global__ void __launch_bounds__(kFinBlock, kFinWarpsPerSm / (kFinBlock / kWarp
 // documented at te_binary_auroc); MODE 1 publishes excl[chunk] for the AUPRC integrate sweep.
 template <int MODE>
 __global__ void __launch_bounds__(1024)
-    rank_chunk_scan_kernel(const ChunkRec* __restrict__ rec, uint32_t nchunks, uint32_t n,
-                           const RankScalars* __restrict__ scal, FState* excl_out, double* out,
-                           uint32_t* starts_out = nullptr) {
+    rank_chunk_scan_kernel(const ChunkRec* __restrict__ rec_, uint32_t nchunks, uint32_t n,
+                           const RankScalars* __restrict__ scal_, FState* excl_out_, double* out,
+                           uint32_t* starts_out_ = nullptr, size_t bstride = 0) {
+  const ChunkRec* __restrict__ rec = batch_ptr(rec_, bstride);
+  const RankScalars* __restrict__ scal = batch_ptr(scal_, bstride);
+  FState* excl_out = batch_ptr(excl_out_, bstride);
+  uint32_t* starts_out = batch_ptr(starts_out_, bstride);
+  if (out) out += 8 * (size_t)blockIdx.y;
   __shared__ FState s_warp[32];
   __shared__ unsigned long long s_u[32];
   __shared__ uint32_t s_ns[32];
@@ -627,8 +638,11 @@ __global__ void __launch_bounds__(kFinBlock, kFinWarpsPerSm / (kFinBlock / kWarp
 //   out[4] = TE_RANK_FLAG_* seen by the ingest kernel (non-zero: out[0] is not valid)
 template <int MODE>
 __global__ void __launch_bounds__(1024)
-    rank_reduce_kernel(const unsigned long long* __restrict__ partial, uint32_t ntiles, uint32_t n,
-                       const RankScalars* __restrict__ scal, double* out) {
+    rank_reduce_kernel(const unsigned long long* __restrict__ partial_, uint32_t ntiles, uint32_t n,
+                       const RankScalars* __restrict__ scal_, double* out, size_t bstride = 0) {
+  const unsigned long long* __restrict__ partial = batch_ptr(partial_, bstride);
+  const RankScalars* __restrict__ scal = batch_ptr(scal_, bstride);
+  out += 8 * (size_t)blockIdx.y;
   __shared__ unsigned long long s_u[32];
   __shared__ double s_d[32];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -767,8 +781,11 @@ T* at(void* base, size_t off) {
   return reinterpret_cast<T*>(static_cast<char*>(base) + off);
 }
 
+// nb > 1: nb independent sorts of the same length whose scratch blocks (and key arrays) lie
+// bstride bytes apart, done by the same launches (grid.y = nb).
 int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t* k_x, uint32_t* k_y,
-               const uint32_t* v_in0, uint32_t* v_x, uint32_t* v_y, cudaStream_t st) {
+               const uint32_t* v_in0, uint32_t* v_x, uint32_t* v_y, cudaStream_t st, int nb = 1,
+               size_t bstride = 0) {
   // 4 passes: in0 -> x -> y -> x -> y
   uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
   uint32_t* hot = hot_digits_from_env() ? at<uint32_t>(scratch, p.off_hot) : nullptr;
@@ -779,14 +796,14 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   };
   {
     TE_PROF("digit_scan", st);
-    digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 4, hot);
+    digit_scan_kernel<<<dim3(1, nb), 1024, 0, st>>>(hist, 4, hot, bstride);
   }
   TE_LAUNCH_CHECK();
   const int block = p.sort_block;
   const size_t smem = block == 256 ? onesweep_smem_bytes<uint32_t, 256>() : onesweep_smem_bytes<uint32_t, 512>();
   using PassFn = void (*)(const uint32_t*, uint32_t*, const uint32_t*, uint32_t*, uint32_t,
                           const RadixDigit, const uint32_t*, uint32_t*, uint32_t*, const PeerPtrs,
-                          const uint32_t*, uint32_t*);
+                          const uint32_t*, uint32_t*, size_t);
   PassFn fn = nullptr;
   if (v_in0)
     fn = block == 256 ? onesweep_pass_kernel<uint32_t, true, 256, RadixDigit>
@@ -817,10 +834,10 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
     uint32_t* lbp = lb_counts(pass);
     uint32_t* gpp = at<uint32_t>(scratch, p.off_gprefix) + (size_t)pass * lb_groups * kRadix;
     TE_PROF(v_in0 ? "onesweep_pass_pairs" : (pass == 0 && fn_first != fn ? "onesweep_pass_keys_first" : "onesweep_pass_keys"), st);
-    (pass == 0 ? fn_first : fn)<<<p.sort_tiles, block, smem_used, st>>>(kin, kout, vin, vout, p.n, RadixDigit{8 * pass},
+    (pass == 0 ? fn_first : fn)<<<dim3(p.sort_tiles, nb), block, smem_used, st>>>(kin, kout, vin, vout, p.n, RadixDigit{8 * pass},
                                                hist + pass * kRadix, lbp, gpp, PeerPtrs{},
                                                hot ? hot + 2 * pass : nullptr,
-                                               pass < 3 ? lb_counts(pass + 1) : nullptr);
+                                               pass < 3 ? lb_counts(pass + 1) : nullptr, bstride);
     TE_LAUNCH_CHECK();
     kin = kout;
     vin = vout;
@@ -870,7 +887,7 @@ int launch_ingest_dtype(const float* score, const void* target, int32_t dt, cons
 
 // fused scan / integrate over the sorted packed keys + final division (both modes)
 int finish_packed(const RankPlan& p, const uint32_t* ka, int mode, double* out, void* scratch, int sms,
-                  cudaStream_t st, bool track_pos = false) {
+                  cudaStream_t st, bool track_pos = false, int nb = 1, size_t bstride = 0) {
   const int64_t n = p.n;
   ChunkRec* rec = at<ChunkRec>(scratch, p.off_agg);
   FState* excl = at<FState>(scratch, p.off_inc);
@@ -878,32 +895,32 @@ int finish_packed(const RankPlan& p, const uint32_t* ka, int mode, double* out, 
   const RankScalars* scal = at<RankScalars>(scratch, p.off_scal);
   const ChunkGeom cg = chunk_geom(p.n, sms);
   const uint32_t nchunks = n > 0 ? cg.nchunks : 0;
-  const uint32_t grid = (nchunks + kFinBlock / kWarp - 1) / (kFinBlock / kWarp);
+  const dim3 grid((nchunks + kFinBlock / kWarp - 1) / (kFinBlock / kWarp), nb);
   if (nchunks) {
     TE_PROF("rank_chunk_sweep", st);
     if (mode == 1 || track_pos)
       rank_chunk_kernel<0, true><<<grid, kFinBlock, 0, st>>>(ka, p.n, cg.steps_per_chunk, nchunks, rec, nullptr,
-                                                             scal, nullptr, 0.0, 0.0, nullptr);
+                                                             scal, nullptr, 0.0, 0.0, nullptr, bstride);
     else
       rank_chunk_kernel<0><<<grid, kFinBlock, 0, st>>>(ka, p.n, cg.steps_per_chunk, nchunks, rec, nullptr, scal,
-                                                       nullptr, 0.0, 0.0, nullptr);
+                                                       nullptr, 0.0, 0.0, nullptr, bstride);
   }
   TE_LAUNCH_CHECK();
   if (mode == 0) {
     TE_PROF("rank_chunk_scan", st);
-    rank_chunk_scan_kernel<0><<<1, 1024, 0, st>>>(rec, nchunks, p.n, scal, nullptr, out);
+    rank_chunk_scan_kernel<0><<<dim3(1, nb), 1024, 0, st>>>(rec, nchunks, p.n, scal, nullptr, out, nullptr, bstride);
   } else {
     if (nchunks) {
       {
         TE_PROF("rank_chunk_scan", st);
-        rank_chunk_scan_kernel<1><<<1, 1024, 0, st>>>(rec, nchunks, p.n, scal, excl, nullptr);
+        rank_chunk_scan_kernel<1><<<dim3(1, nb), 1024, 0, st>>>(rec, nchunks, p.n, scal, excl, nullptr, nullptr, bstride);
       }
       TE_PROF("rank_chunk_integrate", st);
       rank_chunk_kernel<1><<<grid, kFinBlock, 0, st>>>(ka, p.n, cg.steps_per_chunk, nchunks, nullptr, excl, scal,
-                                                       partial, 0.0, 0.0, nullptr);
+                                                       partial, 0.0, 0.0, nullptr, bstride);
     }
     TE_PROF("rank_reduce", st);
-    rank_reduce_kernel<1><<<1, 1024, 0, st>>>(partial, nchunks, p.n, scal, out);
+    rank_reduce_kernel<1><<<dim3(1, nb), 1024, 0, st>>>(partial, nchunks, p.n, scal, out, bstride);
   }
   TE_LAUNCH_CHECK();
   return TE_OK;
@@ -1721,7 +1738,7 @@ static int partition_impl(const uint32_t* keys_in, int64_t n, const uint32_t* sp
   if (n == 0) return TE_OK;
   {
     TE_PROF("digit_scan", st);
-    digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 1, hot);
+    digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 1, hot, 0);
   }
   TE_LAUNCH_CHECK();
   uint32_t* lb = at<uint32_t>(scratch, p.off_lookback);
@@ -1734,7 +1751,7 @@ static int partition_impl(const uint32_t* keys_in, int64_t n, const uint32_t* sp
     const size_t smem = onesweep_smem_bytes<uint32_t, B>();                                              \
     TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
     fn<<<p.sort_tiles, B, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist, lb, gp, pp, hot, \
-                                      nullptr);                                                          \
+                                      nullptr, 0);                                                       \
   } while (0)
   if (p.sort_ipt != kSortIptDefault) return TE_ERR_UNSUPPORTED;
   if (p.sort_block == 256) {
@@ -1826,7 +1843,7 @@ extern "C" int te_binary_auprc_from_keys_finish(int64_t n, double positives_abov
     TE_PROF("rank_chunk_integrate", st);
     rank_chunk_kernel<1><<<(nchunks + kFinBlock / kWarp - 1) / (kFinBlock / kWarp), kFinBlock, 0, st>>>(
         kb, p.n, cg.steps_per_chunk, nchunks, nullptr, at<FState>(scratch, p.off_inc), scal, partial,
-        positives_above, samples_above, above_dev);
+        positives_above, samples_above, above_dev, 0);
   }
   TE_PROF("rank_reduce", st);
   rank_reduce_kernel<1><<<1, 1024, 0, st>>>(partial, nchunks, p.n, scal, out);
@@ -1929,8 +1946,7 @@ extern "C" int te_ovr_rank(const float* input, int64_t ld, const int64_t* target
   char* base = static_cast<char*>(scratch);
   for (int c0 = 0; c0 < num_classes; c0 += kOvrBatch) {
     const int nb = num_classes - c0 < kOvrBatch ? num_classes - c0 : kOvrBatch;
-    for (int j = 0; j < nb; ++j)
-      TE_CUDA_TRY(cudaMemsetAsync(base + (size_t)j * stride + p.off_zero, 0, p.zero_bytes, st));
+    TE_CUDA_TRY(cudaMemset2DAsync(base + p.off_zero, stride, 0, p.zero_bytes, nb, st));  // every slab's control block
     if (n > 0) {
       const bool vec_ok = (((uintptr_t)input) & 15) == 0 && (ld % 4) == 0 && (c0 % 4) == 0;
       int64_t want = (n + kOvrBlock - 1) / kOvrBlock;
@@ -1947,17 +1963,15 @@ extern "C" int te_ovr_rank(const float* input, int64_t ld, const int64_t* target
       }
       TE_LAUNCH_CHECK();
     }
-    for (int j = 0; j < nb; ++j) {
-      void* sj = base + (size_t)j * stride;
-      uint32_t* ka = at<uint32_t>(sj, p.off_keys_a);
-      uint32_t* kb = at<uint32_t>(sj, p.off_keys_b);
-      if (n > 0) {
-        const int rc = run_passes(p, sj, ka, kb, ka, nullptr, nullptr, nullptr, st);
-        if (rc) return rc;
-      }
-      const int rc = finish_packed(p, ka, mode, out + (size_t)(c0 + j) * 8, sj, sms, st);
+    // the nb classes of the batch are sorted and swept by the same launches (grid.y = nb)
+    uint32_t* ka = at<uint32_t>(base, p.off_keys_a);
+    uint32_t* kb = at<uint32_t>(base, p.off_keys_b);
+    if (n > 0) {
+      const int rc = run_passes(p, base, ka, kb, ka, nullptr, nullptr, nullptr, st, nb, stride);
       if (rc) return rc;
     }
+    const int rc = finish_packed(p, ka, mode, out + (size_t)c0 * 8, base, sms, st, false, nb, stride);
+    if (rc) return rc;
   }
   return TE_OK;
 }

@@ -8,6 +8,8 @@
 // kernel, so each pass reads and writes every record exactly once (2*r bytes per record, the
 // "bytes moved per sort pass" of BASELINE.json).
 #pragma once
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace te {
@@ -133,6 +135,15 @@ constexpr size_t onesweep_smem_bytes() {
 // the last tile of the previous group publishes.  Only those last tiles form a chain, and it
 // advances 32 tiles per round trip.  Tile order = block order (see below), so nothing waits on
 // a tile that has not been dispatched.
+// Batched launches (one-vs-rest: several independent sorts of the same length in one grid):
+// blockIdx.y selects the problem, every scratch-resident pointer moves by blockIdx.y * bstride bytes.
+template <typename T>
+__device__ __forceinline__ T* batch_ptr(T* p, size_t bstride) {
+  return p ? reinterpret_cast<T*>(reinterpret_cast<char*>(const_cast<typename std::remove_const<T>::type*>(p)) +
+                                  (size_t)blockIdx.y * bstride)
+           : p;
+}
+
 constexpr int kLbGroup = 32;
 constexpr uint32_t kNoHotDigit = 0xffffffffu;
 
@@ -144,11 +155,19 @@ constexpr uint32_t kNoHotDigit = 0xffffffffu;
 template <typename KeyT, bool HAS_VAL, int kSortBlock, typename DigitOp, int kSortIpt = kSortIptDefault,
           bool kPeerScatter = false, bool kUnstable = false>
 __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / kSortBlock)
-    onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
+    onesweep_pass_kernel(const KeyT* __restrict__ keys_in_, KeyT* __restrict__ keys_out_,
                          const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
-                         uint32_t n, const DigitOp dop, const uint32_t* __restrict__ digit_base,
-                         uint32_t* lookback, uint32_t* group_prefix, const PeerPtrs peers,
-                         const uint32_t* __restrict__ hot_info, uint32_t* __restrict__ zero_next) {
+                         uint32_t n, const DigitOp dop, const uint32_t* __restrict__ digit_base_,
+                         uint32_t* lookback_, uint32_t* group_prefix_, const PeerPtrs peers,
+                         const uint32_t* __restrict__ hot_info_, uint32_t* __restrict__ zero_next_,
+                         size_t bstride) {
+  const KeyT* __restrict__ keys_in = batch_ptr(keys_in_, bstride);
+  KeyT* __restrict__ keys_out = batch_ptr(keys_out_, bstride);
+  const uint32_t* __restrict__ digit_base = batch_ptr(digit_base_, bstride);
+  uint32_t* lookback = batch_ptr(lookback_, bstride);
+  uint32_t* group_prefix = batch_ptr(group_prefix_, bstride);
+  const uint32_t* __restrict__ hot_info = batch_ptr(hot_info_, bstride);
+  uint32_t* __restrict__ zero_next = batch_ptr(zero_next_, bstride);
   static_assert(kSortBlock >= kRadix && kSortBlock % kRadix == 0, "one thread per digit is needed");
   static_assert(kSortIpt % 4 == 0 && 16 * kSortIpt <= 256, "ranks are packed four per register");
   constexpr int GROUPS = kSortBlock / 16;
@@ -486,7 +505,10 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
 // Exclusive scan of the four 256-bin digit histograms, in place (one warp-scan chain per pass),
 // and the up-to-two "hot" digits of every pass: hot[2 * pass + {0, 1}] = digit holding at least
 // 1/8 of the keys (largest first), kNoHotDigit otherwise.
-__global__ void __launch_bounds__(1024) digit_scan_kernel(uint32_t* hist, int passes, uint32_t* hot) {
+__global__ void __launch_bounds__(1024) digit_scan_kernel(uint32_t* hist_, int passes, uint32_t* hot_,
+                                                          size_t bstride) {
+  uint32_t* hist = batch_ptr(hist_, bstride);
+  uint32_t* hot = batch_ptr(hot_, bstride);
   __shared__ uint32_t ws[32];
   __shared__ unsigned long long wmax[32];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
