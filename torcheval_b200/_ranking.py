@@ -79,12 +79,18 @@ def binary_auroc(input: torch.Tensor, target: torch.Tensor, weight: Optional[tor
     x = _rank_scores(stage(input, dev))
     t = stage(target, dev)
     w = None if weight is None else stage(weight, dev, torch.float64)
-    rows = [(x, t, w)] if x.dim() == 1 else [(x[k], t[k], None if w is None else w[k]) for k in range(x.shape[0])]
-    vals = []
-    for xr, tr, wr in rows:
-        vals.append(_binary_auroc_row(xr, tr, wr))
-    res = vals[0] if x.dim() == 1 else torch.stack(vals)
-    return res.to(out_dev)
+    if x.dim() == 1:
+        return _binary_auroc_row(x, t, w).to(out_dev)
+    if w is None and x.shape[0] > 1 and not t.is_floating_point() and bool(((t == 0) | (t == 1)).all()):
+        # (tasks, n) without weights: the tasks are independent rankings of equal length, i.e. the
+        # multilabel one-vs-rest problem on the transposed arrays — eight tasks per launch
+        out = ops.ovr_rank(x.t().contiguous(), t.t().contiguous().to(torch.int64), True, 0)
+        vals = out[:, 0].clone()
+        for k in torch.nonzero(out[:, 4] != 0).flatten().tolist():  # negative scores / soft labels
+            vals[k] = ops.binary_auroc_general(x[k], t[k], None)[0]
+        return vals.to(out_dev)
+    vals = [_binary_auroc_row(x[k], t[k], None if w is None else w[k]) for k in range(x.shape[0])]
+    return torch.stack(vals).to(out_dev)
 
 
 def _binary_auroc_row(x: torch.Tensor, t: torch.Tensor, w: Optional[torch.Tensor]) -> torch.Tensor:
