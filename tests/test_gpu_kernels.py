@@ -383,6 +383,34 @@ def test_rank_target_dtypes_and_flags(ops):
     close(a[0], oracle.binary_auroc(x2, y)[0], 1e-12)
 
 
+@pytest.mark.parametrize("n", [3, 8192, 100003, 2_000_001])
+def test_rank_constant_digit_passes(ops, n):
+    """Score sets whose keys are constant in one or more radix digits (those passes are skipped
+    on the device): bf16-valued scores (low 16 key bits = label only), one binade (top byte
+    constant), a single value, and a (key, value) sort whose keys have two constant bytes."""
+    rs = np.random.default_rng(n)
+    y = rs.integers(0, 2, n)
+    u = rs.random(n, dtype=np.float32)
+    bf16 = (u.view(np.uint32) & np.uint32(0xFFFF0000)).view(np.float32)
+    cases = {"bf16": bf16, "binade": (0.5 + 0.5 * u).astype(np.float32), "constant": np.full(n, 0.375, dtype=np.float32),
+             "two_values": np.where(u < 0.3, np.float32(0.25), np.float32(0.75))}
+    for name, x in cases.items():
+        out = ops.binary_auroc_packed(dev(x), dev(y)).cpu().numpy()
+        want, tp, fp = oracle.binary_auroc(x, y)
+        assert out[4] == 0
+        close(out[0], want, RTOL64)
+        assert (out[1], out[2]) == (tp, fp), name
+        ap = ops.binary_auprc_packed(dev(x), dev(y)).cpu().numpy()
+        close(ap[0], oracle.binary_auprc(x, y), RTOL64)
+    keys = (rs.integers(0, 256, n).astype(np.uint32) << np.uint32(8)) | np.uint32(0x5A000000) | rs.integers(0, 4, n).astype(np.uint32) << np.uint32(16)
+    keys = keys & np.uint32(0xFF03FF00)  # byte 0 constant (0), byte 2 has 4 values, byte 3 constant
+    vals = np.arange(n, dtype=np.int32)
+    ok, ov = ops.sort_u32(dev(keys.view(np.int32)), dev(vals))
+    order = np.argsort(keys, kind="stable")
+    np.testing.assert_array_equal(ok.cpu().numpy().view(np.uint32), keys[order])
+    np.testing.assert_array_equal(ov.cpu().numpy(), vals[order])  # stable: payload order is fixed
+
+
 def test_rank_large_closed_form(ops):
     """Size-independent property at a size the sort-based oracle cannot afford: scores on a grid
     of G levels -> AUROC in closed form from the (level, label) histogram."""

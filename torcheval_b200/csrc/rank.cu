@@ -711,6 +711,14 @@ inline bool hot_digits_from_env() {
   return b;
 }
 
+inline bool skip_passes_from_env() {
+  static const bool b = [] {
+    const char* e = getenv("TE_B200_SKIP_PASSES");
+    return e ? atoi(e) != 0 : true;
+  }();
+  return b;
+}
+
 inline bool unstable_first_pass_from_env() {
   static const bool b = [] {
     const char* e = getenv("TE_B200_UNSTABLE_FIRST");
@@ -789,6 +797,8 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   // 4 passes: in0 -> x -> y -> x -> y
   uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
   uint32_t* hot = hot_digits_from_env() ? at<uint32_t>(scratch, p.off_hot) : nullptr;
+  // words 0..3 of the (zeroed) ticket block: "pass p is a no-op" flags, set by digit_scan_kernel
+  uint32_t* skip = skip_passes_from_env() ? at<uint32_t>(scratch, p.off_ticket) : nullptr;
   const size_t lb_groups = (p.sort_tiles + kLbGroup - 1) / kLbGroup;
   auto lb_counts = [&](int pass) {
     return pass == 0 ? at<uint32_t>(scratch, p.off_lookback)
@@ -796,14 +806,14 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   };
   {
     TE_PROF("digit_scan", st);
-    digit_scan_kernel<<<dim3(1, nb), 1024, 0, st>>>(hist, 4, hot, bstride);
+    digit_scan_kernel<<<dim3(1, nb), 1024, 0, st>>>(hist, 4, hot, bstride, skip);
   }
   TE_LAUNCH_CHECK();
   const int block = p.sort_block;
   const size_t smem = block == 256 ? onesweep_smem_bytes<uint32_t, 256>() : onesweep_smem_bytes<uint32_t, 512>();
   using PassFn = void (*)(const uint32_t*, uint32_t*, const uint32_t*, uint32_t*, uint32_t,
                           const RadixDigit, const uint32_t*, uint32_t*, uint32_t*, const PeerPtrs,
-                          const uint32_t*, uint32_t*, size_t);
+                          const uint32_t*, uint32_t*, size_t, const uint32_t*);
   PassFn fn = nullptr;
   if (v_in0)
     fn = block == 256 ? onesweep_pass_kernel<uint32_t, true, 256, RadixDigit>
@@ -837,7 +847,8 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
     (pass == 0 ? fn_first : fn)<<<dim3(p.sort_tiles, nb), block, smem_used, st>>>(kin, kout, vin, vout, p.n, RadixDigit{8 * pass},
                                                hist + pass * kRadix, lbp, gpp, PeerPtrs{},
                                                hot ? hot + 2 * pass : nullptr,
-                                               pass < 3 ? lb_counts(pass + 1) : nullptr, bstride);
+                                               pass < 3 ? lb_counts(pass + 1) : nullptr, bstride,
+                                               skip ? skip + pass : nullptr);
     TE_LAUNCH_CHECK();
     kin = kout;
     vin = vout;
@@ -1751,7 +1762,7 @@ static int partition_impl(const uint32_t* keys_in, int64_t n, const uint32_t* sp
     const size_t smem = onesweep_smem_bytes<uint32_t, B>();                                              \
     TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
     fn<<<p.sort_tiles, B, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist, lb, gp, pp, hot, \
-                                      nullptr, 0);                                                       \
+                                      nullptr, 0, nullptr);                                              \
   } while (0)
   if (p.sort_ipt != kSortIptDefault) return TE_ERR_UNSUPPORTED;
   if (p.sort_block == 256) {

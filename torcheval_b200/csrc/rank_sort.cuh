@@ -160,7 +160,8 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
                          uint32_t n, const DigitOp dop, const uint32_t* __restrict__ digit_base_,
                          uint32_t* lookback_, uint32_t* group_prefix_, const PeerPtrs peers,
                          const uint32_t* __restrict__ hot_info_, uint32_t* __restrict__ zero_next_,
-                         size_t bstride) {
+                         size_t bstride, const uint32_t* __restrict__ skip_flag_ = nullptr) {
+  const uint32_t* __restrict__ skip_flag = batch_ptr(skip_flag_, bstride);
   const KeyT* __restrict__ keys_in = batch_ptr(keys_in_, bstride);
   KeyT* __restrict__ keys_out = batch_ptr(keys_out_, bstride);
   const uint32_t* __restrict__ digit_base = batch_ptr(digit_base_, bstride);
@@ -196,6 +197,19 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
   const uint32_t sub = lane & 15u;
   const uint32_t group = tid >> 4;
   const uint32_t gbase = group * kGroupKeys;  // tile-relative start of this half-warp's records
+
+  // ---- a digit that is the same for every key (digit_scan_kernel found one full bin: low bits of
+  //      bf16-valued scores, the exponent byte of one binade, constant scores) leaves the order
+  //      as it is: the tile is copied through, no ranking, no look-back ----
+  if (skip_flag && *skip_flag) {
+    if (zero_next && tid < kRadix) zero_next[(size_t)tile * kRadix + tid] = 0u;
+#pragma unroll 4
+    for (uint32_t r = tid; r < valid; r += kSortBlock) {
+      keys_out[base + r] = keys_in[base + r];
+      if (HAS_VAL) vals_out[base + r] = vals_in[base + r];
+    }
+    return;
+  }
 
   // ---- load: a warp instruction fetches two 64-byte runs, one per half-warp.  The loads are
   //      issued first; the ranking tables are cleared while they are in flight. ----
@@ -506,9 +520,10 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
 // and the up-to-two "hot" digits of every pass: hot[2 * pass + {0, 1}] = digit holding at least
 // 1/8 of the keys (largest first), kNoHotDigit otherwise.
 __global__ void __launch_bounds__(1024) digit_scan_kernel(uint32_t* hist_, int passes, uint32_t* hot_,
-                                                          size_t bstride) {
+                                                          size_t bstride, uint32_t* skip_ = nullptr) {
   uint32_t* hist = batch_ptr(hist_, bstride);
   uint32_t* hot = batch_ptr(hot_, bstride);
+  uint32_t* skip = batch_ptr(skip_, bstride);  // skip[pass] = 1: one bin holds every key
   __shared__ uint32_t ws[32];
   __shared__ unsigned long long wmax[32];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -529,6 +544,7 @@ __global__ void __launch_bounds__(1024) digit_scan_kernel(uint32_t* hist_, int p
     total += ws[w];
   }
   if (pass < passes) hist[tid] = wb + incl - v;
+  if (skip && pass < passes && v == total && total > 0) skip[pass] = 1u;  // (zero-initialised by the caller)
   if (!hot) return;
   // top two bins of each pass: max-reduce (count << 8 | digit), twice
   unsigned long long mine = ((unsigned long long)v << 8) | (tid & 255u);
