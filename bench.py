@@ -260,6 +260,8 @@ def run_ours(args) -> dict:
     binned = None
     if world == 1:
         binned = binned_bench(args, x, y, peak_gbs, peak_src)
+    else:
+        binned = binned_sync_bench(args, x, y, world, device)
     if world == 1:
         xh = torch.empty(n_local, dtype=torch.float32, pin_memory=True)
         yh = torch.empty(n_local, dtype=torch.int64, pin_memory=True)
@@ -436,6 +438,45 @@ def binned_bench(args, x, y, peak_gbs, peak_src) -> dict:
             "frac": round(kgbs / peak_gbs, 4),
             "traffic": None,
             "avg_launch_ms": round(kavg, 4),
+        },
+    }
+
+
+def binned_sync_bench(args, x, y, world, device) -> dict:
+    """configs[2] at N GPUs: every rank counts its shard of the 2^30 scores into the 10k-threshold
+    histogram state of BinaryBinnedAUPRC (kernel), then toolkit.sync_and_compute all-reduces the
+    int64 counters over NCCL and integrates.  One step = update + sync_and_compute."""
+    from torcheval_b200.metrics import BinaryBinnedAUPRC
+    from torcheval_b200.metrics.toolkit import sync_and_compute
+
+    T = 10_000
+
+    def step():
+        m = BinaryBinnedAUPRC(threshold=T, device=device)
+        m.update(x, y)
+        return sync_and_compute(m)
+
+    for _ in range(3):
+        out = step()
+    barrier(world)
+    steps = max(args.steps, 5)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(steps):
+        out = step()
+    ev1.record()
+    barrier(world)
+    ms = max_over_ranks(ev0.elapsed_time(ev1), world, device) / steps
+    n_total = x.numel() * world
+    return {
+        "metric": "binary_binned_auprc_update_sync_scores_per_sec",
+        "value": n_total / (ms * 1e-3),
+        "unit": "scores/s",
+        "ms_per_step": ms,
+        "scaling": "strong",
+        "config": {
+            "workload": f"BinaryBinnedAUPRC update + sync_and_compute, T={T} thresholds, N=2^{n_total.bit_length() - 1} scores over {world} GPUs, int64 counter all-reduce",
+            "binned_auprc": float(out[0].item()),
         },
     }
 

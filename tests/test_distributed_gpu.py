@@ -13,16 +13,19 @@ pytestmark = pytest.mark.gpu
 ROOT = Path(__file__).resolve().parent.parent
 
 
-def test_nccl_sample_sort_and_sync(tmp_path):
+@pytest.mark.parametrize("no_peer", ["0", "1"])
+def test_nccl_sample_sort_and_sync(tmp_path, no_peer):
+    """no_peer=0: partition fused with the exchange (P2P stores into peer inboxes);
+    no_peer=1: the fallback, local partition + NCCL all_to_all_single."""
     world = torch.cuda.device_count()
     if world < 2:
         pytest.skip("needs at least 2 GPUs")
     world = min(world, 8)
     out = tmp_path / "res"
-    env = dict(os.environ, TE_TEST_OUT=str(out))
+    env = dict(os.environ, TE_TEST_OUT=str(out), TE_B200_NO_PEER=no_peer)
     cmd = [
         sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
-        "--master-addr", "127.0.0.1", "--master-port", "29655", str(ROOT / "tests" / "_dist_gpu_worker.py"),
+        "--master-addr", "127.0.0.1", "--master-port", "29655" if no_peer == "0" else "29657", str(ROOT / "tests" / "_dist_gpu_worker.py"),
     ]
     r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]

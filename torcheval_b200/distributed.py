@@ -95,8 +95,10 @@ class _PeerInbox:
 
     @classmethod
     def get(cls, group, dev: torch.device, capacity: int):
-        if cls._broken or dev.type != "cuda":
-            return None
+        import os
+
+        if cls._broken or dev.type != "cuda" or os.environ.get("TE_B200_NO_PEER") == "1":
+            return None  # (TE_B200_NO_PEER=1: exercise the NCCL all_to_all_single exchange)
         key = (id(group) if group is not None else 0, dev.index)
         ent = cls._cache.get(key)
         if ent is not None and ent[0] >= capacity:
