@@ -72,6 +72,7 @@ struct SplitterDigit {
     if (tid < 16) s[tid] = (int)tid < nsp ? sp[tid] : 0xffffffffu;
   }
   __device__ __forceinline__ uint32_t eval(uint32_t k, const uint32_t* s) const {
+    if (nsp == 1) return sp[0] <= k ? 1u : 0u;  // two ranks: one compare against a launch constant
     uint32_t b = 0;
 #pragma unroll
     for (int step = 8; step >= 1; step >>= 1) {
