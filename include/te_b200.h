@@ -230,6 +230,11 @@ TE_API int te_ovr_rank(const float* input, int64_t ld, const int64_t* target, in
  *    = {#positives, TE_RANK_FLAG_*}; counts (int64[num_splitters + 1], device) = sizes of the
  *    buckets the keys fall in, bucket = #{splitters <= key}, for up to 15 ascending splitters
  *    given in HOST memory (num_splitters may be 0).  keys_out must be 16-byte aligned.
+ *    digit_hist (device, may be NULL): uint32[num_splitters + 1][4][256], the four radix-digit
+ *    histograms of the keys of every bucket; the rank that receives bucket b sums the rows b of all
+ *    senders and hands the result to te_binary_auroc_from_keys / te_binary_auprc_from_keys_begin as
+ *    digit_hist (uint32[4][256]; NULL there = histogram the keys first), which saves one read of
+ *    the received keys.
  *  te_partition_u32: stable partition of keys by the same kind of splitters; counts_in (device,
  *    may be NULL) are bucket sizes already known from te_rank_pack, counts receives them again,
  *    keys_out the keys grouped by bucket.
@@ -238,13 +243,14 @@ TE_API int te_ovr_rank(const float* input, int64_t ld, const int64_t* target, in
 TE_API size_t te_rank_pack_scratch_bytes(int64_t n);
 TE_API int te_rank_pack(const float* score, const void* target, int32_t target_dtype, int64_t n,
                         const uint32_t* splitters_host, int32_t num_splitters, uint32_t* keys_out,
-                        int64_t* info, int64_t* counts, void* scratch, size_t scratch_bytes, void* stream);
+                        int64_t* info, int64_t* counts, uint32_t* digit_hist, void* scratch,
+                        size_t scratch_bytes, void* stream);
 /* te_rank_pack with the splitters in DEVICE memory (uint32[num_splitters], ascending: not
  * checked), for callers that pick them on the device and do not want a host round trip. */
 TE_API int te_rank_pack_dsplit(const float* score, const void* target, int32_t target_dtype, int64_t n,
                                const uint32_t* splitters_dev, int32_t num_splitters, uint32_t* keys_out,
-                               int64_t* info, int64_t* counts, void* scratch, size_t scratch_bytes,
-                               void* stream);
+                               int64_t* info, int64_t* counts, uint32_t* digit_hist, void* scratch,
+                               size_t scratch_bytes, void* stream);
 TE_API size_t te_partition_u32_scratch_bytes(int64_t n);
 TE_API int te_partition_u32(const uint32_t* keys_in, int64_t n, const uint32_t* splitters_host,
                             int32_t num_splitters, const int64_t* counts_in, uint32_t* keys_out,
@@ -259,8 +265,8 @@ TE_API int te_partition_scatter_u32(const uint32_t* keys_in, int64_t n, const ui
                                     int32_t num_splitters, const int64_t* counts_in,
                                     const uint64_t* dest_ptrs_host, int64_t* counts, void* scratch,
                                     size_t scratch_bytes, void* stream);
-TE_API int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, double* out, void* scratch,
-                                     size_t scratch_bytes, void* stream);
+TE_API int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, const uint32_t* digit_hist,
+                                     double* out, void* scratch, size_t scratch_bytes, void* stream);
 /* Average precision of rank-sharded scores (precision is a ratio of prefix
  * counts, so the step integral of precision_recall_curve.py:208-231 + tensor_utils.py:12-16 takes
  * two phases around one exchange of (P_r, N_r)):
@@ -273,8 +279,8 @@ TE_API int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, double* ou
  *           NULL the two numbers are read from that device array instead, so that they can come
  *           straight out of a collective).  AP = sum over ranks of out[3], divided by the global
  *           number of positives; out[1], out[2] = local P, N. */
-TE_API int te_binary_auprc_from_keys_begin(const uint32_t* keys, int64_t n, double* out, void* scratch,
-                                           size_t scratch_bytes, void* stream);
+TE_API int te_binary_auprc_from_keys_begin(const uint32_t* keys, int64_t n, const uint32_t* digit_hist,
+                                           double* out, void* scratch, size_t scratch_bytes, void* stream);
 TE_API int te_binary_auprc_from_keys_finish(int64_t n, double positives_above, double samples_above,
                                             const double* above_dev, double* out, void* scratch,
                                             size_t scratch_bytes, void* stream);

@@ -169,7 +169,12 @@ def sort_u32(keys, vals=None):
     return ok, (None if vals is None else vals[torch.from_numpy(order)])
 
 
-def rank_pack(score, target, splitters=()):
+def _digit_hist(k):
+    """int32[1024]: the four 8-bit digit histograms of uint32 keys (pass-major)."""
+    return np.concatenate([np.bincount((k >> np.uint32(8 * p)) & np.uint32(255), minlength=256) for p in range(4)]).astype(np.int32)
+
+
+def rank_pack(score, target, splitters=(), want_hist=False):
     if isinstance(splitters, torch.Tensor):  # "device" splitters: int32 bit patterns
         splitters = [int(v) & 0xFFFFFFFF for v in splitters.tolist()]
     x = _np(score).astype(np.float32).copy()
@@ -180,8 +185,14 @@ def rank_pack(score, target, splitters=()):
     keys = ((bits << np.uint32(1)) | lab).astype(np.uint32)
     info = torch.tensor([int(lab.sum()), _flags(score, target)], dtype=torch.int64)
     kt = torch.from_numpy(keys.view(np.int32).copy())
-    _, counts = partition_u32(kt, splitters)
-    return kt, info, counts
+    part, counts = partition_u32(kt, splitters)
+    if not want_hist:
+        return kt, info, counts
+    pk, off, rows = part.numpy().view(np.uint32), 0, []
+    for c in counts.tolist():
+        rows.append(_digit_hist(pk[off : off + c]))
+        off += c
+    return kt, info, counts, torch.from_numpy(np.stack(rows))
 
 
 def partition_u32(keys, splitters, counts_in=None):
@@ -193,16 +204,18 @@ def partition_u32(keys, splitters, counts_in=None):
     return torch.from_numpy(k[order].view(np.int32).copy()), torch.from_numpy(counts)
 
 
-def binary_auroc_from_keys(keys):
+def binary_auroc_from_keys(keys, hist=None):
     k = _np(keys).view(np.uint32)
+    if hist is not None:  # histograms that travelled with the keys must be THE histograms of the keys
+        assert np.array_equal(_np(hist), _digit_hist(k)), "digit histograms do not match the received keys"
     x = (k >> np.uint32(1)).astype(np.uint32).view(np.float32)
     y = (k & np.uint32(1)).astype(np.int64)
     return binary_auroc_packed(torch.from_numpy(x.copy()), torch.from_numpy(y))
 
 
-def binary_auprc_from_keys_begin(keys):
+def binary_auprc_from_keys_begin(keys, hist=None):
     k = np.sort(_np(keys).view(np.uint32))
-    return binary_auroc_from_keys(keys), k
+    return binary_auroc_from_keys(keys, hist), k
 
 
 def binary_auprc_from_keys_finish(state, positives_above, samples_above=None):

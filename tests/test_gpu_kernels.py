@@ -522,6 +522,11 @@ def test_rank_pack_partition_from_keys(ops):
             sp_dev = torch.tensor(sp, dtype=torch.int64, device="cuda").to(torch.int32)  # bit patterns
             k3, _, c3 = ops.rank_pack(dev(x), dev(y), sp_dev)  # splitters read from device memory
             assert c3.tolist() == wc.tolist() and torch.equal(k3, k2), (n, sp)
+            # per-bucket radix-digit histograms computed while packing
+            k4, _, c4, h4 = ops.rank_pack(dev(x), dev(y), sp_dev, want_hist=True)
+            _, _, _, wh = cpu_backend.rank_pack(torch.from_numpy(x), torch.from_numpy(y), sp, want_hist=True)
+            assert torch.equal(k4, k2) and c4.tolist() == wc.tolist()
+            np.testing.assert_array_equal(h4.cpu().numpy(), wh.numpy(), err_msg=f"{n} {sp}")
             for known in (None, c2):
                 part, counts = ops.partition_u32(k2, sp, known)
                 assert counts.tolist() == wc.tolist(), (n, sp)
@@ -530,6 +535,14 @@ def test_rank_pack_partition_from_keys(ops):
         want = cpu_backend.binary_auroc_from_keys(wk).numpy()
         close(out[0], want[0], 1e-12)
         assert list(out[1:4]) == list(want[1:4]) and list(out[5:8]) == list(want[5:8])
+        # the same with the digit histograms handed in instead of recomputed from the keys
+        _, _, _, h0 = ops.rank_pack(dev(x), dev(y), [], want_hist=True)
+        out_h = ops.binary_auroc_from_keys(keys, h0[0].contiguous()).cpu().numpy()
+        np.testing.assert_array_equal(out_h, out)
+        a1, st1 = ops.binary_auprc_from_keys_begin(keys, h0[0].contiguous())
+        a0, st0 = ops.binary_auprc_from_keys_begin(keys)
+        assert torch.equal(a1, a0)
+        assert torch.equal(ops.binary_auprc_from_keys_finish(st1, 0, 0), ops.binary_auprc_from_keys_finish(st0, 0, 0))
     _, info, _ = ops.rank_pack(dev(np.array([0.5, -1.0], dtype=np.float32)), dev(np.array([0, 1])))
     assert info.tolist() == [1, 2]
 

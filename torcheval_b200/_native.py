@@ -47,13 +47,13 @@ SIGNATURES = {
     "te_ovr_rank_scratch_bytes": (_sz, [_i64]),
     "te_ovr_rank": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i32, _i32, _i32, _vp, _vp, _sz, _vp]),
     "te_rank_pack_scratch_bytes": (_sz, [_i64]),
-    "te_rank_pack": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
-    "te_rank_pack_dsplit": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "te_rank_pack": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "te_rank_pack_dsplit": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "te_partition_u32_scratch_bytes": (_sz, [_i64]),
     "te_partition_u32": (C.c_int, [_vp, _i64, _vp, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
     "te_partition_scatter_u32": (C.c_int, [_vp, _i64, _vp, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
-    "te_binary_auroc_from_keys": (C.c_int, [_vp, _i64, _vp, _vp, _sz, _vp]),
-    "te_binary_auprc_from_keys_begin": (C.c_int, [_vp, _i64, _vp, _vp, _sz, _vp]),
+    "te_binary_auroc_from_keys": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _sz, _vp]),
+    "te_binary_auprc_from_keys_begin": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _sz, _vp]),
     "te_binary_auprc_from_keys_finish": (C.c_int, [_i64, C.c_double, C.c_double, _vp, _vp, _vp, _sz, _vp]),
     "te_binary_pr_curve_begin": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp, _sz, _vp]),
     "te_binary_pr_curve_finish": (C.c_int, [_i64, _vp, _vp, _vp, _vp, _sz, _vp]),

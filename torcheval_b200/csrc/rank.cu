@@ -1335,17 +1335,28 @@ __global__ void rank_info_kernel(const RankScalars* __restrict__ scal, long long
 
 // pack for the distributed path: (score, target) -> packed keys, #positives, flags, and — the
 // splitters are already known — the sizes of the destination buckets, all in one streaming pass
-// (12 B read + 4 B written per score; no radix histograms, the keys are re-histogrammed after the
-// exchange).
-template <typename TargetT>
+// (12 B read + 4 B written per score).
+// HIST: also the four radix-digit histograms of every destination bucket's keys, so that the
+// receiving rank can start sorting without reading its inbox once more (the ranks sum the
+// rows they are sent).  Bins per bucket in shared memory: digits 0-2 plain (uniform mantissa
+// bits), digit 3 — the exponent byte, where half of the keys share a value — replicated 8 ways
+// by lane so that a warp's same-address atomics stay short.
+constexpr int kPackTopRepl = 8;
+constexpr int kPackBinsPerBucket = 3 * kRadix + kRadix * kPackTopRepl;  // 2816 words = 11 KB
+
+template <typename TargetT, bool HIST>
 __global__ void __launch_bounds__(1024)
     pack_bucket_kernel(const float* __restrict__ score, const TargetT* __restrict__ target, uint32_t n,
                        bool vec_ok, const SplitterDigit dop_in, const uint32_t* __restrict__ splitters_dev,
-                       uint32_t* __restrict__ keys_out, uint32_t* hist, RankScalars* scal) {
+                       uint32_t* __restrict__ keys_out, uint32_t* hist, RankScalars* scal,
+                       uint32_t* __restrict__ digit_hist) {
   __shared__ uint32_t sh[16 * kWarp];
   __shared__ uint32_t s_sp[kMaxSplitters + 1];
+  extern __shared__ uint32_t s_dh[];  // HIST: [buckets][kPackBinsPerBucket]
   const unsigned tid = threadIdx.x, lane = tid & 31;
   if (tid < 16 * kWarp) sh[tid] = 0;
+  if (HIST)
+    for (uint32_t i = tid; i < (uint32_t)(dop_in.nsp + 1) * kPackBinsPerBucket; i += blockDim.x) s_dh[i] = 0;
   // splitters either came with the launch (host array) or are read from device memory, so that a
   // caller can choose them on the device without a round trip through the host
   if (tid < kMaxSplitters + 1)
@@ -1393,7 +1404,15 @@ __global__ void __launch_bounds__(1024)
       k[j] = (b << 1) | lab[j];
       if (j < (int)cnt) {
         npos += lab[j];
-        atomicAdd(sh + dop(k[j]) * kWarp + lane, 1u);
+        const uint32_t bkt = dop(k[j]);
+        atomicAdd(sh + bkt * kWarp + lane, 1u);
+        if (HIST) {
+          uint32_t* bins = s_dh + bkt * kPackBinsPerBucket;
+          atomicAdd(bins + (k[j] & 255u), 1u);
+          atomicAdd(bins + kRadix + ((k[j] >> 8) & 255u), 1u);
+          atomicAdd(bins + 2 * kRadix + ((k[j] >> 16) & 255u), 1u);
+          atomicAdd(bins + 3 * kRadix + (k[j] >> 24) * kPackTopRepl + (lane & (kPackTopRepl - 1)), 1u);
+        }
       }
     }
     if (cnt == 4) {
@@ -1408,6 +1427,22 @@ __global__ void __launch_bounds__(1024)
     for (int r = 0; r < kWarp; ++r) s += sh[tid * kWarp + r];
     if (s) atomicAdd(hist + tid, s);
   }
+  if (HIST) {  // digit_hist[bucket][pass][digit]
+    const uint32_t total = (uint32_t)(dop_in.nsp + 1) * 4 * kRadix;
+    for (uint32_t i = tid; i < total; i += blockDim.x) {
+      const uint32_t bkt = i / (4 * kRadix), r = i % (4 * kRadix);
+      const uint32_t* bins = s_dh + bkt * kPackBinsPerBucket;
+      uint32_t v;
+      if (r < 3 * kRadix) {
+        v = bins[r];
+      } else {
+        v = 0;
+#pragma unroll
+        for (int q = 0; q < kPackTopRepl; ++q) v += bins[3 * kRadix + (r - 3 * kRadix) * kPackTopRepl + q];
+      }
+      if (v) atomicAdd(digit_hist + i, v);
+    }
+  }
   npos = warp_sum(npos);
   const uint32_t anybad = __any_sync(kFull, bad_label != 0);
   const uint32_t anyneg = __any_sync(kFull, neg_score != 0);
@@ -1416,6 +1451,18 @@ __global__ void __launch_bounds__(1024)
     const uint32_t f = (anybad ? TE_RANK_FLAG_BAD_LABEL : 0) | (anyneg ? TE_RANK_FLAG_NEGATIVE_SCORE : 0);
     if (f) atomicOr(&scal->flags, f);
   }
+}
+
+// A rank's digit histograms came with the keys (te_rank_pack digit_hist rows, summed over the
+// senders): install them and derive the number of positives (bit 0 of the key = odd digit 0).
+__global__ void __launch_bounds__(1024)
+    install_hist_kernel(const uint32_t* __restrict__ hist_in, uint32_t* __restrict__ hist, RankScalars* scal) {
+  const unsigned tid = threadIdx.x;
+  const uint32_t v = hist_in[tid];
+  hist[tid] = v;
+  unsigned long long odd = (tid < (unsigned)kRadix && (tid & 1u)) ? v : 0u;
+  odd = warp_sum(odd);
+  if ((tid & 31) == 0 && odd) atomicAdd(&scal->positives, odd);
 }
 
 __global__ void counts_to_hist_kernel(const long long* __restrict__ counts, uint32_t* hist, int nb) {
@@ -1636,20 +1683,29 @@ static int fill_splitters(SplitterDigit& dop, const uint32_t* splitters_host, in
 template <typename TargetT>
 static void launch_pack(const float* score, const void* target, const RankPlan& p, const SplitterDigit& dop,
                         const uint32_t* splitters_dev, uint32_t* keys_out, void* scratch, int sms,
-                        cudaStream_t st) {
+                        cudaStream_t st, uint32_t* digit_hist) {
   const uint32_t ngroups = (p.n + 3) / 4;
   uint32_t grid = (ngroups + 1023) / 1024;
   if (grid > (uint32_t)sms * 2) grid = sms * 2;
   const bool vec_ok = ((((uintptr_t)score) | ((uintptr_t)target)) & 15) == 0;
-  pack_bucket_kernel<TargetT><<<grid, 1024, 0, st>>>(score, (const TargetT*)target, p.n, vec_ok, dop, splitters_dev,
-                                                     keys_out, at<uint32_t>(scratch, p.off_hist),
-                                                     at<RankScalars>(scratch, p.off_scal));
+  if (digit_hist) {
+    const size_t smem = (size_t)(dop.nsp + 1) * kPackBinsPerBucket * sizeof(uint32_t);
+    cudaFuncSetAttribute(pack_bucket_kernel<TargetT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 100 * 1024 && grid > (uint32_t)sms) grid = sms;  // one CTA per SM fits then
+    pack_bucket_kernel<TargetT, true><<<grid, 1024, smem, st>>>(score, (const TargetT*)target, p.n, vec_ok, dop,
+                                                                splitters_dev, keys_out, at<uint32_t>(scratch, p.off_hist),
+                                                                at<RankScalars>(scratch, p.off_scal), digit_hist);
+  } else {
+    pack_bucket_kernel<TargetT, false><<<grid, 1024, 0, st>>>(score, (const TargetT*)target, p.n, vec_ok, dop,
+                                                              splitters_dev, keys_out, at<uint32_t>(scratch, p.off_hist),
+                                                              at<RankScalars>(scratch, p.off_scal), nullptr);
+  }
 }
 
 static int rank_pack_impl(const float* score, const void* target, int32_t target_dtype, int64_t n,
                           const uint32_t* splitters_host, const uint32_t* splitters_dev, int32_t num_splitters,
-                          uint32_t* keys_out, int64_t* info, int64_t* counts, void* scratch,
-                          size_t scratch_bytes, void* stream) {
+                          uint32_t* keys_out, int64_t* info, int64_t* counts, uint32_t* digit_hist,
+                          void* scratch, size_t scratch_bytes, void* stream) {
   if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
   if (!info || !counts || (n > 0 && (!score || !target || !keys_out))) return TE_ERR_INVALID_ARGUMENT;
   if (((uintptr_t)keys_out & 15) != 0) return TE_ERR_INVALID_ARGUMENT;
@@ -1668,14 +1724,16 @@ static int rank_pack_impl(const float* score, const void* target, int32_t target
   int sms = 0;
   TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
   TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.off_scal + 256 - p.off_zero, st));
+  if (digit_hist)
+    TE_CUDA_TRY(cudaMemsetAsync(digit_hist, 0, (size_t)(num_splitters + 1) * 4 * kRadix * sizeof(uint32_t), st));
   if (n > 0) {
     TE_PROF("pack_bucket", st);
     switch (target_dtype) {
-      case TE_DTYPE_I64: launch_pack<long long>(score, target, p, dop, splitters_dev, keys_out, scratch, sms, st); break;
-      case TE_DTYPE_I32: launch_pack<int>(score, target, p, dop, splitters_dev, keys_out, scratch, sms, st); break;
-      case TE_DTYPE_U8: launch_pack<unsigned char>(score, target, p, dop, splitters_dev, keys_out, scratch, sms, st); break;
-      case TE_DTYPE_F32: launch_pack<float>(score, target, p, dop, splitters_dev, keys_out, scratch, sms, st); break;
-      case TE_DTYPE_F64: launch_pack<double>(score, target, p, dop, splitters_dev, keys_out, scratch, sms, st); break;
+      case TE_DTYPE_I64: launch_pack<long long>(score, target, p, dop, splitters_dev, keys_out, scratch, sms, st, digit_hist); break;
+      case TE_DTYPE_I32: launch_pack<int>(score, target, p, dop, splitters_dev, keys_out, scratch, sms, st, digit_hist); break;
+      case TE_DTYPE_U8: launch_pack<unsigned char>(score, target, p, dop, splitters_dev, keys_out, scratch, sms, st, digit_hist); break;
+      case TE_DTYPE_F32: launch_pack<float>(score, target, p, dop, splitters_dev, keys_out, scratch, sms, st, digit_hist); break;
+      case TE_DTYPE_F64: launch_pack<double>(score, target, p, dop, splitters_dev, keys_out, scratch, sms, st, digit_hist); break;
       default: return TE_ERR_INVALID_ARGUMENT;
     }
     TE_LAUNCH_CHECK();
@@ -1688,20 +1746,20 @@ static int rank_pack_impl(const float* score, const void* target, int32_t target
 
 extern "C" int te_rank_pack(const float* score, const void* target, int32_t target_dtype, int64_t n,
                             const uint32_t* splitters_host, int32_t num_splitters, uint32_t* keys_out,
-                            int64_t* info, int64_t* counts, void* scratch, size_t scratch_bytes,
-                            void* stream) {
+                            int64_t* info, int64_t* counts, uint32_t* digit_hist, void* scratch,
+                            size_t scratch_bytes, void* stream) {
   return rank_pack_impl(score, target, target_dtype, n, splitters_host, nullptr, num_splitters, keys_out, info,
-                        counts, scratch, scratch_bytes, stream);
+                        counts, digit_hist, scratch, scratch_bytes, stream);
 }
 
 extern "C" int te_rank_pack_dsplit(const float* score, const void* target, int32_t target_dtype, int64_t n,
                                    const uint32_t* splitters_dev, int32_t num_splitters, uint32_t* keys_out,
-                                   int64_t* info, int64_t* counts, void* scratch, size_t scratch_bytes,
-                                   void* stream) {
+                                   int64_t* info, int64_t* counts, uint32_t* digit_hist, void* scratch,
+                                   size_t scratch_bytes, void* stream) {
   if (num_splitters > 0 && !splitters_dev) return TE_ERR_INVALID_ARGUMENT;
   static const uint32_t none = 0;  // num_splitters == 0: nothing is read through the pointer
   return rank_pack_impl(score, target, target_dtype, n, nullptr, splitters_dev ? splitters_dev : &none,
-                        num_splitters, keys_out, info, counts, scratch, scratch_bytes, stream);
+                        num_splitters, keys_out, info, counts, digit_hist, scratch, scratch_bytes, stream);
 }
 
 extern "C" size_t te_partition_u32_scratch_bytes(int64_t n) { return te_rank_pack_scratch_bytes(n); }
@@ -1794,8 +1852,8 @@ extern "C" int te_partition_scatter_u32(const uint32_t* keys_in, int64_t n, cons
 
 // mode 0: AUROC of the keys.  mode 1: the same, and the chunk states the AUPRC integrate sweep
 // starts from are left in `scratch` next to the sorted keys (te_binary_auprc_from_keys_finish).
-static int rank_from_keys(const uint32_t* keys, int64_t n, int mode, double* out, void* scratch,
-                          size_t scratch_bytes, void* stream) {
+static int rank_from_keys(const uint32_t* keys, int64_t n, int mode, const uint32_t* digit_hist, double* out,
+                          void* scratch, size_t scratch_bytes, void* stream) {
   if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
   if (!out || (n > 0 && !keys)) return TE_ERR_INVALID_ARGUMENT;
   if (((uintptr_t)keys & 15) != 0) return TE_ERR_INVALID_ARGUMENT;
@@ -1808,7 +1866,14 @@ static int rank_from_keys(const uint32_t* keys, int64_t n, int mode, double* out
   uint32_t* ka = at<uint32_t>(scratch, p.off_keys_a);
   uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
   if (n > 0) {
-    int rc = launch_ingest<kRawKeys, long long>(nullptr, nullptr, keys, p, nullptr, nullptr, scratch, sms, st);
+    int rc = TE_OK;
+    if (digit_hist) {  // the histograms travelled with the keys: no extra read of the inbox
+      TE_PROF("install_hist", st);
+      install_hist_kernel<<<1, 4 * kRadix, 0, st>>>(digit_hist, at<uint32_t>(scratch, p.off_hist),
+                                                    at<RankScalars>(scratch, p.off_scal));
+    } else {
+      rc = launch_ingest<kRawKeys, long long>(nullptr, nullptr, keys, p, nullptr, nullptr, scratch, sms, st);
+    }
     if (rc) return rc;
     rc = run_passes(p, scratch, keys, ka, kb, nullptr, nullptr, nullptr, st);  // sorted keys end in kb
     if (rc) return rc;
@@ -1824,14 +1889,15 @@ static int rank_from_keys(const uint32_t* keys, int64_t n, int mode, double* out
   return TE_OK;
 }
 
-extern "C" int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, double* out, void* scratch,
-                                         size_t scratch_bytes, void* stream) {
-  return rank_from_keys(keys, n, 0, out, scratch, scratch_bytes, stream);
+extern "C" int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, const uint32_t* digit_hist,
+                                         double* out, void* scratch, size_t scratch_bytes, void* stream) {
+  return rank_from_keys(keys, n, 0, digit_hist, out, scratch, scratch_bytes, stream);
 }
 
-extern "C" int te_binary_auprc_from_keys_begin(const uint32_t* keys, int64_t n, double* out, void* scratch,
-                                               size_t scratch_bytes, void* stream) {
-  return rank_from_keys(keys, n, 1, out, scratch, scratch_bytes, stream);
+extern "C" int te_binary_auprc_from_keys_begin(const uint32_t* keys, int64_t n, const uint32_t* digit_hist,
+                                               double* out, void* scratch, size_t scratch_bytes,
+                                               void* stream) {
+  return rank_from_keys(keys, n, 1, digit_hist, out, scratch, scratch_bytes, stream);
 }
 
 extern "C" int te_binary_auprc_from_keys_finish(int64_t n, double positives_above, double samples_above,

@@ -72,7 +72,8 @@ struct SplitterDigit {
     if (tid < 16) s[tid] = (int)tid < nsp ? sp[tid] : 0xffffffffu;
   }
   __device__ __forceinline__ uint32_t eval(uint32_t k, const uint32_t* s) const {
-    if (nsp == 1) return sp[0] <= k ? 1u : 0u;  // two ranks: one compare against a launch constant
+    if (nsp == 1) return s[0] <= k ? 1u : 0u;  // two ranks: one compare (the staged copy: the
+                                               // splitters may have come from device memory)
     uint32_t b = 0;
 #pragma unroll
     for (int step = 8; step >= 1; step >>= 1) {

@@ -62,19 +62,19 @@ class _LocalKernels:
 
     @staticmethod
     def pack(score: torch.Tensor, target: torch.Tensor, splitters):
-        return ops.rank_pack(score, target, splitters)
+        return ops.rank_pack(score, target, splitters, want_hist=True)
 
     @staticmethod
     def partition(keys: torch.Tensor, splitters, counts):
         return ops.partition_u32(keys, splitters, counts)
 
     @staticmethod
-    def auroc_from_keys(keys: torch.Tensor) -> torch.Tensor:
-        return ops.binary_auroc_from_keys(keys)
+    def auroc_from_keys(keys: torch.Tensor, hist=None) -> torch.Tensor:
+        return ops.binary_auroc_from_keys(keys, hist)
 
     @staticmethod
-    def auprc_begin(keys: torch.Tensor):
-        return ops.binary_auprc_from_keys_begin(keys)
+    def auprc_begin(keys: torch.Tensor, hist=None):
+        return ops.binary_auprc_from_keys_begin(keys, hist)
 
     @staticmethod
     def auprc_finish(state, above: torch.Tensor) -> torch.Tensor:
@@ -174,9 +174,12 @@ def device_splitters(score: torch.Tensor, world: int, group) -> torch.Tensor:
 
 
 def _exchange_keys(score: torch.Tensor, target: torch.Tensor, group, tm: _PhaseTimer):
-    """Steps 1-4: returns (inbox, flags).  inbox = the packed keys of the score range this rank
-    owns (rank order = ascending score order), None when flags != 0 (negative scores / soft labels
-    on some rank: the packed representation does not apply; every rank sees the same flags).
+    """Steps 1-4: returns (inbox, flags, hist).  inbox = the packed keys of the score range this
+    rank owns (rank order = ascending score order), None when flags != 0 (negative scores / soft
+    labels on some rank: the packed representation does not apply; every rank sees the same
+    flags).  hist = int32[1024], the radix-digit histograms of the inbox: every sender histograms
+    what it sends while packing, and the rows are summed across the senders (one reduce-scatter), so
+    the receiver never reads its inbox just to count digits.
     ONE host read: bucket sizes, flags and the splitters come back together."""
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
@@ -185,14 +188,15 @@ def _exchange_keys(score: torch.Tensor, target: torch.Tensor, group, tm: _PhaseT
     sp_dev = device_splitters(score, world, group)
     tm.mark("splitters")
     # --- pack (+ bucket sizes) with the splitters still on the device --------------------------
-    keys, info, counts = _local.pack(score, target, sp_dev.to(torch.int32))
+    keys, info, counts, send_hist = _local.pack(score, target, sp_dev.to(torch.int32))
+    my_hist = _sum_rows_to_owner(send_hist, world, rank, group)
     tm.mark("pack")
     rows = _gather_rows(torch.cat([counts, info[1:2], sp_dev]), world, group).tolist()
     flags = 0
     for r in rows:
         flags |= int(r[world])
     if flags:
-        return None, flags
+        return None, flags, None
     splitters = [int(v) for v in rows[rank][world + 1 :]]
     send = [int(c) for c in rows[rank][:world]]
     recv = [int(rows[q][rank]) for q in range(world)]
@@ -223,7 +227,20 @@ def _exchange_keys(score: torch.Tensor, target: torch.Tensor, group, tm: _PhaseT
         inbox = torch.empty(sum(recv), dtype=keys.dtype, device=dev)
         dist.all_to_all_single(inbox, part, recv, send, group=group)
         tm.mark("all_to_all")
-    return inbox, 0
+    return inbox, 0, my_hist
+
+
+def _sum_rows_to_owner(rows: torch.Tensor, world: int, rank: int, group) -> torch.Tensor:
+    """rows: (W, k) on every rank; returns sum over ranks of row[rank] — a reduce-scatter (NCCL),
+    or an all-reduce + slice where the backend has no reduce-scatter (gloo)."""
+    rows = rows.contiguous()
+    if rows.is_cuda:
+        out = torch.empty(rows.shape[1], dtype=rows.dtype, device=rows.device)
+        dist.reduce_scatter_tensor(out, rows.view(-1), op=dist.ReduceOp.SUM, group=group)
+        return out
+    total = rows.clone()
+    dist.all_reduce(total, op=dist.ReduceOp.SUM, group=group)
+    return total[rank].contiguous()
 
 
 def _flags_only(flags: int, dev) -> torch.Tensor:
@@ -252,11 +269,11 @@ def _sharded_binary_auroc(score, target, group):
     rank = dist.get_rank(group)
     dev = score.device
     tm = _PhaseTimer(dev)
-    inbox, flags = _exchange_keys(score, target, group, tm)
+    inbox, flags, hist = _exchange_keys(score, target, group, tm)
     if flags:
         return _flags_only(flags, dev), flags
     # --- local sort + integrate, then the fix-up of three integers per rank, on the device -------
-    loc = _local.auroc_from_keys(inbox)
+    loc = _local.auroc_from_keys(inbox, hist)
     tm.mark("local_sort_sweep")
     st = torch.stack([loc[1], loc[2], loc[5], loc[6]]).to(torch.int64)
     tm.mark("fix:stack")
@@ -299,10 +316,10 @@ def _sharded_binary_auprc(score, target, group):
     rank = dist.get_rank(group)
     dev = score.device
     tm = _PhaseTimer(dev)
-    inbox, flags = _exchange_keys(score, target, group, tm)
+    inbox, flags, hist = _exchange_keys(score, target, group, tm)
     if flags:
         return _flags_only(flags, dev), flags
-    loc, state = _local.auprc_begin(inbox)
+    loc, state = _local.auprc_begin(inbox, hist)
     tm.mark("local_sort_count")
     pn = _gather_rows(loc[1:3].clone(), world, group)  # (W, 2) float64 {P_r, N_r}, exact integers
     above = pn[rank + 1 :].sum(0)                      # what the ranks with higher scores hold

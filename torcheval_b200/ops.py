@@ -339,10 +339,12 @@ def _host_splitters(splitters):
     return (ctypes.c_uint32 * max(nsp, 1))(*[int(v) & 0xFFFFFFFF for v in splitters]), nsp
 
 
-def rank_pack(score: torch.Tensor, target: torch.Tensor, splitters=()):
+def rank_pack(score: torch.Tensor, target: torch.Tensor, splitters=(), want_hist: bool = False):
     """(packed keys as int32 tensor [n], info int64[2] = {#positives, flags}, bucket sizes
     int64[len(splitters) + 1]).  `splitters`: ascending key values, either a host sequence of ints
-    or an int32 DEVICE tensor holding their bit patterns (no host round trip to choose them)."""
+    or an int32 DEVICE tensor holding their bit patterns (no host round trip to choose them).
+    want_hist: a fourth result, int32 [buckets, 4 * 256] — the radix-digit histograms of every
+    bucket's keys (what the receiver of a bucket needs to start sorting it)."""
     import ctypes
 
     lib = N.load()
@@ -360,6 +362,7 @@ def rank_pack(score: torch.Tensor, target: torch.Tensor, splitters=()):
     keys = torch.empty(n, dtype=torch.int32, device=dev)
     info = torch.zeros(2, dtype=torch.int64, device=dev)
     counts = torch.zeros(nsp + 1, dtype=torch.int64, device=dev)
+    hist = torch.empty((nsp + 1, 1024), dtype=torch.int32, device=dev) if want_hist else None
     scratch = _scratch(lib.te_rank_pack_scratch_bytes(n), dev)
     with torch.cuda.device(dev):
         if on_device:
@@ -367,16 +370,17 @@ def rank_pack(score: torch.Tensor, target: torch.Tensor, splitters=()):
                 "te_rank_pack_dsplit",
                 lib.te_rank_pack_dsplit(score.data_ptr(), target.data_ptr(), _DTYPE_CODE[target.dtype], n,
                                         splitters.data_ptr() if nsp else None, nsp, keys.data_ptr(), info.data_ptr(),
-                                        counts.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
+                                        counts.data_ptr(), _ptr(hist), scratch.data_ptr(), scratch.numel(),
+                                        _stream_ptr(dev)),
             )
         else:
             N.check(
                 "te_rank_pack",
                 lib.te_rank_pack(score.data_ptr(), target.data_ptr(), _DTYPE_CODE[target.dtype], n,
                                  ctypes.cast(sp, ctypes.c_void_p), nsp, keys.data_ptr(), info.data_ptr(),
-                                 counts.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
+                                 counts.data_ptr(), _ptr(hist), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
             )
-    return keys, info, counts
+    return (keys, info, counts, hist) if want_hist else (keys, info, counts)
 
 
 def partition_u32(keys: torch.Tensor, splitters, counts_in: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
@@ -424,8 +428,16 @@ def partition_scatter_u32(keys: torch.Tensor, splitters, counts_in: torch.Tensor
         )
 
 
-def binary_auroc_from_keys(keys: torch.Tensor) -> torch.Tensor:
-    """float64[8] as te_binary_auroc_from_keys: [auroc, P, N, 2U, flags, 2U_hi32, 2U_lo32, n]."""
+def _hist_ptr(hist: Optional[torch.Tensor], dev) -> Optional[int]:
+    if hist is None:
+        return None
+    assert hist.dtype == torch.int32 and hist.numel() == 1024 and hist.device == dev and hist.is_contiguous()
+    return hist.data_ptr()
+
+
+def binary_auroc_from_keys(keys: torch.Tensor, hist: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """float64[8] as te_binary_auroc_from_keys: [auroc, P, N, 2U, flags, 2U_hi32, 2U_lo32, n].
+    hist: int32[4 * 256] radix-digit histograms of `keys` if they are already known."""
     lib = N.load()
     dev = _require_cuda(keys)
     keys = keys.contiguous()
@@ -435,12 +447,13 @@ def binary_auroc_from_keys(keys: torch.Tensor) -> torch.Tensor:
     with torch.cuda.device(dev):
         N.check(
             "te_binary_auroc_from_keys",
-            lib.te_binary_auroc_from_keys(keys.data_ptr(), n, out.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
+            lib.te_binary_auroc_from_keys(keys.data_ptr(), n, _hist_ptr(hist, dev), out.data_ptr(), scratch.data_ptr(),
+                                          scratch.numel(), _stream_ptr(dev)),
         )
     return out
 
 
-def binary_auprc_from_keys_begin(keys: torch.Tensor):
+def binary_auprc_from_keys_begin(keys: torch.Tensor, hist: Optional[torch.Tensor] = None):
     """Phase 1 of the rank-sharded average precision: sort + count.  Returns (out, state) where
     out is float64[8] like ``binary_auroc_from_keys`` and ``state`` must be handed, untouched, to
     ``binary_auprc_from_keys_finish``."""
@@ -454,7 +467,8 @@ def binary_auprc_from_keys_begin(keys: torch.Tensor):
         N.check(
             "te_binary_auprc_from_keys_begin",
             lib.te_binary_auprc_from_keys_begin(
-                keys.data_ptr(), n, out.data_ptr(), scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)
+                keys.data_ptr(), n, _hist_ptr(hist, dev), out.data_ptr(), scratch.data_ptr(), scratch.numel(),
+                _stream_ptr(dev)
             ),
         )
     return out, (n, scratch)
