@@ -285,6 +285,19 @@ TE_API int te_binary_auprc_from_keys_finish(int64_t n, double positives_above, d
                                             const double* above_dev, double* out, void* scratch,
                                             size_t scratch_bytes, void* stream);
 
+/* Two one-CTA helpers of the distributed sample sort (no counterpart in the reference, which has no
+ * sharded path: toolkit.py:371-391 gathers everything everywhere).
+ *  te_select_splitters: `samples` = int32[total] float bit patterns of sampled scores from all
+ *    ranks (negative = no sample), total <= 32768; writes the world - 1 quantile splitters in key
+ *    space ((bits << 1), ascending) as uint32 and as int64.  world <= 16.
+ *  te_combine_auroc_stats: `rows` = float64[world][8], the te_binary_auroc_from_keys results of
+ *    the ranks in ascending score-range order; out[] = [auroc, P, N, 2U, 0, n_received, 0, 0] with
+ *    2U = sum_r (2U_r + 2 P_r sum_{q<r} N_q) in exact 64-bit integers. */
+TE_API int te_select_splitters(const int32_t* samples, int64_t total, int32_t world, uint32_t* splitters,
+                               int64_t* splitters_i64, void* stream);
+TE_API int te_combine_auroc_stats(const double* rows, int32_t world, double n_received, double* out,
+                                  void* stream);
+
 /* Exact precision-recall curve of (score, target == 1) — precision_recall_curve.py:208-231
  * (_compute_for_each_class: sort, tie mask, cumsum, flip, append (1, 0)).  Two calls around one
  * host read, because the number of points K (= distinct scores) sizes the outputs:

@@ -547,6 +547,36 @@ def test_rank_pack_partition_from_keys(ops):
     assert info.tolist() == [1, 2]
 
 
+def test_select_splitters_and_combine_stats(ops):
+    """The two one-CTA helpers of the sample sort against their Python restatements."""
+    from torcheval_b200.distributed import combine_rank_stats
+
+    rs = np.random.default_rng(77)
+    for world, s, empty in [(2, 4096, ()), (8, 4096, ()), (3, 1000, (1,)), (16, 2048, (0, 5)), (4, 7, ()), (2, 1, (0, 1))]:
+        bits = rs.random((world, s), dtype=np.float32).view(np.int32).copy()
+        bits[:, ::5] = bits[:, :1]  # duplicates
+        for r in empty:
+            bits[r] = -1
+        sp32, sp64 = ops.select_splitters(dev(bits), world)
+        pool = np.sort(bits[bits >= 0].astype(np.int64))
+        m = pool.size
+        want = [int((pool[min(m - 1, (i * m) // world)] << 1) & 0xFFFFFFFE) if m else 0 for i in range(1, world)]
+        assert sp64.tolist() == want, (world, s)
+        assert [v & 0xFFFFFFFF for v in sp32.tolist()] == want
+    for world in (1, 2, 8):
+        rows = np.zeros((world, 8))
+        stats = []
+        for r in range(world):
+            p_, n_ = int(rs.integers(0, 2**28)), int(rs.integers(0, 2**28))
+            u2 = int(rs.integers(0, 2 * p_ * n_ + 1))
+            rows[r, 1], rows[r, 2], rows[r, 5], rows[r, 6] = p_, n_, u2 >> 32, u2 & 0xFFFFFFFF
+            stats.append((p_, n_, u2))
+        out = ops.combine_auroc_stats(dev(rows), 1234).cpu().numpy()
+        auroc, P, N_, u2 = combine_rank_stats(stats)
+        close(out[0], auroc, 1e-15)
+        assert (int(out[1]), int(out[2]), out[5]) == (P, N_, 1234.0) and out[3] == float(u2)
+
+
 @pytest.mark.parametrize("n", [1, 37, 8192, 8193, 123457, 2_000_003])
 def test_partition_scatter_to_separate_buffers(ops, n):
     """te_partition_scatter_u32 with the buckets going to separate buffers at every 4-byte

@@ -55,6 +55,8 @@ SIGNATURES = {
     "te_binary_auroc_from_keys": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _sz, _vp]),
     "te_binary_auprc_from_keys_begin": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _sz, _vp]),
     "te_binary_auprc_from_keys_finish": (C.c_int, [_i64, C.c_double, C.c_double, _vp, _vp, _vp, _sz, _vp]),
+    "te_select_splitters": (C.c_int, [_vp, _i64, _i32, _vp, _vp, _vp]),
+    "te_combine_auroc_stats": (C.c_int, [_vp, _i32, C.c_double, _vp, _vp]),
     "te_binary_pr_curve_begin": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp, _sz, _vp]),
     "te_binary_pr_curve_finish": (C.c_int, [_i64, _vp, _vp, _vp, _vp, _sz, _vp]),
     "te_sort_u32_scratch_bytes": (_sz, [_i64, _i32]),

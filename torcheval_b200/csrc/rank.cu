@@ -2052,3 +2052,107 @@ extern "C" int te_ovr_rank(const float* input, int64_t ld, const int64_t* target
   }
   return TE_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// Small single-CTA helpers of the distributed sample sort.  Each replaces a dozen or more tiny
+// framework kernels whose launch gaps, not their work, were 10 % of an 8-GPU step
+// (profiles/r01_dist_trace_4gpu.txt).
+// ------------------------------------------------------------------------------------------
+namespace te {
+namespace {
+
+// samples: float bit patterns of regularly sampled scores from every rank (negative = "this rank
+// has no data").  Bitonic sort in shared memory, then W-1 quantile splitters in KEY space
+// ((bits << 1), label bit clear), as uint32 and again as int64 (for the host message).
+__global__ void __launch_bounds__(1024)
+    select_splitters_kernel(const int32_t* __restrict__ samples, uint32_t total, uint32_t padded, int world,
+                            uint32_t* __restrict__ sp32, long long* __restrict__ sp64) {
+  extern __shared__ uint32_t s_pool[];
+  __shared__ uint32_t s_valid;
+  const unsigned tid = threadIdx.x;
+  if (tid == 0) s_valid = 0;
+  __syncthreads();
+  uint32_t mine = 0;
+  for (uint32_t i = tid; i < padded; i += blockDim.x) {
+    const int32_t v = i < total ? samples[i] : -1;
+    s_pool[i] = v >= 0 ? (uint32_t)v : 0xffffffffu;
+    mine += v >= 0 ? 1u : 0u;
+  }
+  mine = (uint32_t)warp_sum((unsigned long long)mine);
+  if ((tid & 31) == 0 && mine) atomicAdd(&s_valid, mine);
+  __syncthreads();
+  for (uint32_t k = 2; k <= padded; k <<= 1) {
+    for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+      for (uint32_t t = tid; t < padded / 2; t += blockDim.x) {
+        const uint32_t i = 2 * t - (t & (j - 1));  // element whose partner is i + j
+        const uint32_t a = s_pool[i], b = s_pool[i + j];
+        const bool up = (i & k) == 0;
+        if ((a > b) == up) s_pool[i] = b, s_pool[i + j] = a;
+      }
+      __syncthreads();
+    }
+  }
+  const uint32_t m = s_valid;
+  if (tid + 1 < (unsigned)world) {
+    uint32_t v = 0;
+    if (m) {
+      uint32_t at = (uint32_t)(((unsigned long long)(tid + 1) * m) / (unsigned)world);
+      if (at > m - 1) at = m - 1;
+      v = (s_pool[at] << 1) & 0xfffffffeu;
+    }
+    sp32[tid] = v;
+    sp64[tid] = (long long)v;
+  }
+}
+
+// rows: the float64[8] results of te_binary_auroc_from_keys of every rank, in rank (= ascending
+// score range) order.  2U = sum_r (2U_r + 2 P_r sum_{q<r} N_q), exact in uint64.
+__global__ void combine_auroc_kernel(const double* __restrict__ rows, int world, double n_recv, double* out) {
+  if (threadIdx.x != 0) return;
+  unsigned long long u2 = 0, neg_below = 0, P = 0, N = 0;
+  for (int r = 0; r < world; ++r) {
+    const double* w = rows + 8 * r;
+    const unsigned long long p = (unsigned long long)w[1], n = (unsigned long long)w[2];
+    const unsigned long long u = ((unsigned long long)w[5] << 32) | (unsigned long long)w[6];
+    u2 += u + 2ull * p * neg_below;
+    neg_below += n;
+    P += p;
+    N += n;
+  }
+  out[0] = (P == 0 || N == 0) ? 0.5 : ((double)u2 * 0.5) / ((double)P * (double)N);
+  out[1] = (double)P;
+  out[2] = (double)N;
+  out[3] = (double)u2;
+  out[4] = 0.0;
+  out[5] = n_recv;
+  out[6] = 0.0;
+  out[7] = 0.0;
+}
+
+}  // namespace
+}  // namespace te
+
+extern "C" int te_select_splitters(const int32_t* samples, int64_t total, int32_t world, uint32_t* splitters,
+                                   int64_t* splitters_i64, void* stream) {
+  if (world < 1 || world > kMaxSplitters + 1 || total < 0 || total > 32768) return TE_ERR_INVALID_ARGUMENT;
+  if (world > 1 && (!splitters || !splitters_i64 || (total > 0 && !samples))) return TE_ERR_INVALID_ARGUMENT;
+  if (world == 1) return TE_OK;
+  uint32_t padded = 2;
+  while (padded < (uint32_t)total) padded <<= 1;
+  const size_t smem = (size_t)padded * sizeof(uint32_t);
+  TE_CUDA_TRY(cudaFuncSetAttribute(select_splitters_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaStream_t st = (cudaStream_t)stream;
+  TE_PROF("select_splitters", st);
+  select_splitters_kernel<<<1, 1024, smem, st>>>(samples, (uint32_t)total, padded, world, splitters,
+                                                 (long long*)splitters_i64);
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+extern "C" int te_combine_auroc_stats(const double* rows, int32_t world, double n_received, double* out,
+                                      void* stream) {
+  if (!rows || !out || world < 1) return TE_ERR_INVALID_ARGUMENT;
+  combine_auroc_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(rows, world, n_received, out);
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}

@@ -154,23 +154,42 @@ def _gather_rows(t: torch.Tensor, world: int, group) -> torch.Tensor:
 _NO_SAMPLE = 1 << 33  # above every 32-bit key: what a rank without data contributes to the pool
 
 
-def device_splitters(score: torch.Tensor, world: int, group) -> torch.Tensor:
-    """W-1 ascending splitters (int64 key values, label bit cleared) chosen from regular samples
-    of every rank's scores; computed with device ops only, identical on every rank."""
+_SAMPLE_INDEX_CACHE: dict = {}
+
+
+def _sample_index(n: int, s: int, dev: torch.device) -> torch.Tensor:
+    key = (n, s, str(dev))
+    idx = _SAMPLE_INDEX_CACHE.get(key)
+    if idx is None:
+        if len(_SAMPLE_INDEX_CACHE) > 64:
+            _SAMPLE_INDEX_CACHE.clear()
+        idx = torch.div(torch.arange(s, device=dev, dtype=torch.int64) * n, s, rounding_mode="floor")
+        _SAMPLE_INDEX_CACHE[key] = idx
+    return idx
+
+
+def device_splitters(score: torch.Tensor, world: int, group):
+    """(int32[W-1] splitter bit patterns for the pack kernel, int64[W-1] the same values) chosen
+    from regular samples of every rank's scores; never leaves the device, identical on every rank.
+    Splitters are key values with the label bit cleared.  On CUDA: one gather of the sampled bit
+    patterns, one all_gather, ONE kernel (shared-memory bitonic sort + quantile pick); the torch
+    op chain it replaces cost 0.6 ms of launch gaps per call (profiles/r01_dist_trace_4gpu.txt)."""
     dev = score.device
     n = score.numel()
-    s = SAMPLES_PER_RANK
+    s = min(SAMPLES_PER_RANK, 32768 // world)
     if n > 0:
-        idx = torch.div(torch.arange(s, device=dev, dtype=torch.int64) * n, s, rounding_mode="floor")
-        bits = score.contiguous().view(torch.int32)[idx].to(torch.int64)
-        smp = (bits << 1) & 0xFFFFFFFE
+        smp = score.contiguous().view(torch.int32)[_sample_index(n, s, dev)]
     else:
-        smp = torch.full((s,), _NO_SAMPLE, dtype=torch.int64, device=dev)
-    pool, _ = torch.sort(_gather_rows(smp, world, group).reshape(-1))
+        smp = torch.full((s,), -1, dtype=torch.int32, device=dev)
+    pool = _gather_rows(smp, world, group)  # negative bit patterns (negative scores, no data) are not samples
+    if dev.type == "cuda" and _local is _LocalKernels:
+        return ops.select_splitters(pool, world)
+    pool, _ = torch.sort(torch.where(pool >= 0, pool.to(torch.int64), torch.full_like(pool, _NO_SAMPLE, dtype=torch.int64)).reshape(-1))
     m = (pool < _NO_SAMPLE).sum()
     i = torch.arange(1, world, device=dev, dtype=torch.int64)
     pick = torch.minimum(torch.div(i * m, world, rounding_mode="floor"), (m - 1).clamp(min=0))
-    return pool[pick] & 0xFFFFFFFE  # no data anywhere: the sentinel masks to 0
+    sp = torch.where(m > 0, (pool[pick] << 1) & 0xFFFFFFFE, torch.zeros_like(pick))
+    return sp.to(torch.int32), sp
 
 
 def _exchange_keys(score: torch.Tensor, target: torch.Tensor, group, tm: _PhaseTimer):
@@ -185,10 +204,10 @@ def _exchange_keys(score: torch.Tensor, target: torch.Tensor, group, tm: _PhaseT
     rank = dist.get_rank(group)
     dev = score.device
 
-    sp_dev = device_splitters(score, world, group)
+    sp32, sp_dev = device_splitters(score, world, group)
     tm.mark("splitters")
     # --- pack (+ bucket sizes) with the splitters still on the device --------------------------
-    keys, info, counts, send_hist = _local.pack(score, target, sp_dev.to(torch.int32))
+    keys, info, counts, send_hist = _local.pack(score, target, sp32)
     my_hist = _sum_rows_to_owner(send_hist, world, rank, group)
     tm.mark("pack")
     rows = _gather_rows(torch.cat([counts, info[1:2], sp_dev]), world, group).tolist()
@@ -275,14 +294,16 @@ def _sharded_binary_auroc(score, target, group):
     # --- local sort + integrate, then the fix-up of three integers per rank, on the device -------
     loc = _local.auroc_from_keys(inbox, hist)
     tm.mark("local_sort_sweep")
-    st = torch.stack([loc[1], loc[2], loc[5], loc[6]]).to(torch.int64)
-    tm.mark("fix:stack")
-    rows = _gather_rows(st, world, group)
+    rows = _gather_rows(loc, world, group)  # (W, 8) float64
     tm.mark("fix:gather")
-    auroc, P, Nn, u2 = combine_rank_stats_tensor(rows)
-    out = torch.zeros(8, dtype=torch.float64, device=dev)
-    out[:4] = torch.stack([auroc, P.to(torch.float64), Nn.to(torch.float64), u2.to(torch.float64)])
-    out[5] = float(inbox.numel())
+    if dev.type == "cuda" and _local is _LocalKernels:
+        out = ops.combine_auroc_stats(rows, inbox.numel())  # one kernel, exact 64-bit integers
+    else:
+        st = torch.stack([rows[:, 1], rows[:, 2], rows[:, 5], rows[:, 6]], dim=1).to(torch.int64)
+        auroc, P, Nn, u2 = combine_rank_stats_tensor(st)
+        out = torch.zeros(8, dtype=torch.float64, device=dev)
+        out[:4] = torch.stack([auroc, P.to(torch.float64), Nn.to(torch.float64), u2.to(torch.float64)])
+        out[5] = float(inbox.numel())
     tm.mark(f"fixup(n_recv={inbox.numel()})")
     tm.done(rank)
     return out, 0

@@ -530,3 +530,37 @@ def binary_pr_curve(score: torch.Tensor, target: torch.Tensor):
                                           scratch.data_ptr(), scratch.numel(), _stream_ptr(dev)),
         )
     return (precision, recall, thresholds), 0
+
+
+def select_splitters(samples: torch.Tensor, world: int):
+    """samples: int32 [world * s] float bit patterns of sampled scores (negative = none), at most
+    32768 of them.  Returns (int32[world - 1] splitter bit patterns in key space, int64 copy)."""
+    lib = N.load()
+    dev = _require_cuda(samples)
+    samples = samples.contiguous().view(-1)
+    assert samples.dtype == torch.int32 and samples.numel() <= 32768
+    sp32 = torch.empty(max(world - 1, 0), dtype=torch.int32, device=dev)
+    sp64 = torch.empty(max(world - 1, 0), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_select_splitters",
+            lib.te_select_splitters(samples.data_ptr(), samples.numel(), world, _ptr(sp32) if world > 1 else None,
+                                    _ptr(sp64) if world > 1 else None, _stream_ptr(dev)),
+        )
+    return sp32, sp64
+
+
+def combine_auroc_stats(rows: torch.Tensor, n_received: int) -> torch.Tensor:
+    """rows: float64 [world, 8] gathered te_binary_auroc_from_keys results (rank order = ascending
+    score ranges) -> float64[8] [auroc, P, N, 2U, 0, n_received, 0, 0]."""
+    lib = N.load()
+    dev = _require_cuda(rows)
+    rows = rows.contiguous()
+    assert rows.dtype == torch.float64 and rows.dim() == 2 and rows.shape[1] == 8
+    out = torch.empty(8, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_combine_auroc_stats",
+            lib.te_combine_auroc_stats(rows.data_ptr(), rows.shape[0], float(n_received), out.data_ptr(), _stream_ptr(dev)),
+        )
+    return out
