@@ -28,6 +28,10 @@ import torch.distributed as dist
 from . import ops
 
 SAMPLES_PER_RANK = 4096
+# All samples are sorted by ONE thread block (te_select_splitters, bitonic in shared memory:
+# 0.05 ms for 8192 keys, 0.3 ms for 32768), so the pool is capped; 8192 samples put the quantile
+# error of a splitter at ~0.4 % of the total, i.e. ~3 % of a rank's share at 8 ranks.
+SAMPLE_POOL = 8192
 
 
 class _PhaseTimer:
@@ -176,7 +180,7 @@ def device_splitters(score: torch.Tensor, world: int, group):
     op chain it replaces cost 0.6 ms of launch gaps per call (profiles/r01_dist_trace_4gpu.txt)."""
     dev = score.device
     n = score.numel()
-    s = min(SAMPLES_PER_RANK, 32768 // world)
+    s = min(SAMPLES_PER_RANK, SAMPLE_POOL // world)
     if n > 0:
         smp = score.contiguous().view(torch.int32)[_sample_index(n, s, dev)]
     else:
