@@ -426,6 +426,42 @@ def test_rank_large_closed_form(ops):
     close(a[0], oracle.auroc_from_level_hist(neg, pos), 1e-9)
 
 
+def test_full_size_2p30_closed_forms(ops):
+    """BASELINE configs 3 and 4 at their full size, N = 2^30 scores on one GPU, through
+    size-independent properties: scores on a grid of G levels, so that
+      * exact AUROC / AUPRC follow in closed form from the (level, label) histogram,
+      * 2U is an exact integer that must match digit for digit,
+      * the 10k-threshold binned counts are prefix sums of the same histogram."""
+    n, G, T = 1 << 30, 1 << 12, 10_000
+    g = torch.Generator(device="cuda").manual_seed(2030)
+    lev = torch.randint(0, G, (n,), device="cuda", generator=g)
+    y = (torch.rand(n, device="cuda", generator=g) < 0.25).long()
+    x = lev.float() / G  # exact in float32
+    neg = torch.bincount(lev[y == 0], minlength=G).cpu().numpy().astype(np.int64)
+    pos = torch.bincount(lev[y == 1], minlength=G).cpu().numpy().astype(np.int64)
+    del lev
+    a = ops.binary_auroc_packed(x, y).cpu().numpy()
+    assert a[4] == 0 and a[1] == pos.sum() and a[2] == neg.sum()
+    below = np.concatenate([[0], np.cumsum(neg)[:-1]])
+    u2 = int(np.sum(pos.astype(object) * (2 * below.astype(object) + neg.astype(object))))
+    assert (int(a[5]) << 32) | int(a[6]) == u2  # exact integer Mann-Whitney statistic
+    close(a[0], oracle.auroc_from_level_hist(neg, pos), 1e-12)
+    ap = ops.binary_auprc_packed(x, y).cpu().numpy()
+    tp_ge = np.cumsum(pos[::-1])[::-1].astype(np.float64)
+    all_ge = np.cumsum((pos + neg)[::-1])[::-1].astype(np.float64)
+    want_ap = float(np.sum(pos * (tp_ge / np.maximum(all_ge, 1))) / pos.sum())
+    close(ap[0], want_ap, 1e-9)
+    thr = torch.linspace(0, 1, T, device="cuda")
+    hist = torch.zeros((1, T + 1, 2), dtype=torch.int64, device="cuda")
+    ops.binned_hist_update_(hist, x, y, thr)
+    tp, fp, fn = ops.binned_counts(hist, T)
+    levels = (np.arange(G, dtype=np.float32) / np.float32(G))
+    ge = levels[None, :] >= thr.cpu().numpy()[:, None]          # (T, G)
+    np.testing.assert_array_equal(tp.cpu().numpy()[0], ge.astype(np.int64) @ pos)
+    np.testing.assert_array_equal(fp.cpu().numpy()[0], ge.astype(np.int64) @ neg)
+    assert int(hist.sum()) == n
+
+
 # =============================================================================== K1: general path
 def run_general(ops, x, y, w=None, ydtype=None):
     X = dev(x, torch.float32)
@@ -717,3 +753,43 @@ def test_functional_multiclass_with_negative_columns(ops):
     close(got.cpu().numpy(), oracle.multiclass_auroc(x, y), RTOL32)
     got = F.multiclass_auprc(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda(), average=None)
     close(got.cpu().numpy(), oracle.multiclass_auprc(x, y), RTOL32)
+
+
+# =============================================================================== edge-size sweep
+def test_edge_size_sweep_all_kernels(ops):
+    """Sizes around every tile / step / vector boundary of the kernels (0, 1, 3, 4, 5, 511..513,
+    4095..4097, 8191..8193, 16383..16385) with heavy ties, through every kernel family."""
+    import cpu_backend
+
+    rs = np.random.default_rng(123)
+    sizes = [0, 1, 2, 3, 4, 5, 31, 32, 33, 511, 512, 513, 1023, 1025, 4095, 4096, 4097, 8191, 8192, 8193, 16383, 16385, 24577]
+    thr = np.linspace(0, 1, 33, dtype=np.float32)
+    for n in sizes:
+        x = (rs.integers(0, 64, n) / 64).astype(np.float32)
+        y = rs.integers(0, 2, n)
+        a = ops.binary_auroc_packed(dev(x), dev(y)).cpu().numpy()
+        want, tp, fp = oracle.binary_auroc(x, y) if n else (0.5, 0.0, 0.0)
+        assert a[4] == 0 and (a[1], a[2]) == (tp, fp), n
+        close(a[0], want, RTOL64)
+        if n:
+            p = ops.binary_auprc_packed(dev(x), dev(y)).cpu().numpy()
+            close(p[0], oracle.binary_auprc(x, y), RTOL64)
+            (pr, rc, th), flags = ops.binary_pr_curve(dev(x), dev(y))
+            (wp, wr, wt), _ = cpu_backend.binary_pr_curve(torch.from_numpy(x), torch.from_numpy(y))
+            np.testing.assert_array_equal(th.cpu().numpy(), wt.numpy())
+            np.testing.assert_allclose(pr.cpu().numpy(), wp.numpy(), rtol=2e-7)
+            np.testing.assert_allclose(rc.cpu().numpy(), wr.numpy(), rtol=2e-7)
+            g = ops.binary_auroc_general(dev(x - 0.5), dev(y), None).cpu().numpy()
+            close(g[0], want, RTOL64)
+        for C in (3, 1000):
+            pc, tc = rs.integers(0, C, n), rs.integers(0, C, n)
+            wantcm, _, _ = oracle.confusion_matrix(pc, tc, C)
+            for v in (0, 6):
+                cm, _ = run_cm(ops, dev(pc), dev(tc), C, v)
+                np.testing.assert_array_equal(cm, wantcm, err_msg=f"n={n} C={C} v={v}")
+        hist = torch.zeros((1, thr.size + 1, 2), dtype=torch.int64, device="cuda")
+        ops.binned_hist_update_(hist, dev(x), dev(y), dev(thr))
+        np.testing.assert_array_equal(hist.cpu().numpy()[0], oracle.binned_hist(x, y, thr))
+        keys = rs.integers(0, 2**32, n, dtype=np.uint64).astype(np.uint32)
+        ok, _ = ops.sort_u32(dev(keys.view(np.int32)))
+        np.testing.assert_array_equal(ok.cpu().numpy().view(np.uint32), np.sort(keys))
