@@ -148,6 +148,50 @@ def main():
         res["sync/empty_rank_ok"] = bool(np.isfinite(v))
     except Exception as e:  # noqa: BLE001
         res["sync/empty_rank_ok"] = f"raised {type(e).__name__}: {e}"
+    # a user-defined metric with every kind of state (tensor, list, dict, int): the generic path
+    from torcheval_b200.metrics import Metric, WindowedBinaryAUROC
+
+    class Toy(Metric):
+        def __init__(self):
+            super().__init__()
+            self._add_state("total", torch.zeros(3, dtype=torch.float64))
+            self._add_state("chunks", [])
+            self._add_state("per_key", {})
+            self._add_state("count", 0)
+
+        def update(self, v):
+            self.total += v.sum(0)
+            self.chunks.append(v)
+            self.per_key[f"r{int(v[0, 0])}"] = v.mean()
+            self.count += v.shape[0]
+            return self
+
+        def compute(self):
+            return self.total, torch.cat(self.chunks).shape[0] if self.chunks else 0, dict(self.per_key), self.count
+
+        def merge_state(self, metrics):
+            for m in metrics:
+                self.total += m.total
+                self.chunks.extend(m.chunks)
+                self.per_key.update(m.per_key)
+                self.count += m.count
+            return self
+
+    toy = Toy()
+    if rank != 1:  # rank 1 stays empty: empty list / dict states must travel too
+        toy.update(torch.full((rank + 2, 3), float(rank), dtype=torch.float64))
+    total, rows, keys, count = toolkit.sync_and_compute(toy)
+    want_rows = sum(r + 2 for r in range(world) if r != 1)
+    res["generic/toy"] = [
+        total.tolist(), [float(sum(r * (r + 2) for r in range(world) if r != 1))] * 3,
+    ]
+    res["generic/toy_meta"] = [[rows, count, sorted(keys)], [want_rows, want_rows, sorted(f"r{r}" for r in range(world) if r != 1)]]
+    assert toy.count == (0 if rank == 1 else rank + 2)  # the local object is left alone
+    wx, wy = rs.random((world, 30), dtype=np.float32) + 0.01, rs.integers(0, 2, (world, 30))
+    wm = WindowedBinaryAUROC(max_num_samples=20).update(torch.from_numpy(wx[rank]), torch.from_numpy(wy[rank]))
+    wv = float(toolkit.sync_and_compute(wm))
+    # merged window = the last 20 samples of every rank, concatenated
+    res["generic/windowed"] = [wv, oracle.binary_auroc(np.concatenate([wx[r, 10:] for r in range(world)]), np.concatenate([wy[r, 10:] for r in range(world)]))[0]]
     Path(os.environ["TE_TEST_OUT"] + f".{rank}").write_text(json.dumps(res))
     dist.barrier()
     dist.destroy_process_group()

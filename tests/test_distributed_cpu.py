@@ -42,6 +42,8 @@ def test_sample_sort_and_toolkit_sync(world, port, tmp_path):
             assert (P, N) == (tp, fp), key
         elif key in ("sync/cm_equal", "sync/cm_input_unchanged", "sync/empty_rank_ok"):
             assert val is True, (key, val)
+        elif key == "generic/toy_meta":
+            assert val[0] == val[1], val
         elif key == "sd/cm_total":
             assert val[0] == val[1]
         else:

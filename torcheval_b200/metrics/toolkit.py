@@ -11,8 +11,9 @@ through ``dist.all_gather_object`` and re-merges them on every rank.  Here
 * exact binary AUROC over rank-sharded samples runs as a distributed sample sort
   (``torcheval_b200.distributed``): no rank ever holds more than its share of the samples;
 * sample-keeping metrics are merged with tensor all-gathers (no pickle);
-* anything else (user-defined metrics with arbitrary states) falls back to the reference's
-  object all-gather, so the contract "every Metric syncs" still holds.
+* anything else (user-defined metrics with arbitrary tensor / list / dict / int states) moves its
+  tensors as ONE flat byte buffer through a padded all-gather; only the table of dtypes and shapes
+  is pickled, so the contract "every Metric syncs" still holds.
 
 Every rank of the group must call these functions in the same order, as with the reference.
 """
@@ -141,16 +142,82 @@ def _gather_sample_store(metric: Metric, process_group) -> Optional[Metric]:
     return merged
 
 
-def _sync_metric_object(metric: Any, process_group, world_size: int) -> List[Any]:
-    """The reference's generic path (toolkit.py:371-391): pickle + all_gather_object."""
-    if isinstance(metric, Metric):
-        metric._prepare_for_merge_state()
-    else:
-        for m in metric.values():
-            m._prepare_for_merge_state()
-    gathered = [None] * world_size
-    dist.all_gather_object(gathered, metric, group=process_group)
-    return gathered
+def _flatten_states(metrics: List[Metric], dev: torch.device):
+    """(meta, payload): every tensor of every registered state of `metrics`, in a fixed traversal
+    order, as ONE uint8 buffer on `dev` (16-byte aligned pieces); meta holds what is needed to
+    rebuild them (dtype, shape, offset) plus the int / float states — no tensor data."""
+    meta, pieces, off = [], [], 0
+
+    def add(t: torch.Tensor):
+        nonlocal off
+        raw = t.detach().contiguous().reshape(-1).view(torch.uint8).to(dev)
+        entry = (str(t.dtype).replace("torch.", ""), tuple(t.shape), off, raw.numel())
+        pad = (-raw.numel()) % 16
+        pieces.append(raw)
+        if pad:
+            pieces.append(torch.zeros(pad, dtype=torch.uint8, device=dev))
+        off += raw.numel() + pad
+        return entry
+
+    for m in metrics:
+        m._prepare_for_merge_state()
+        states = {}
+        for name in sorted(m._state_name_to_default):
+            v = getattr(m, name)
+            if isinstance(v, torch.Tensor):
+                states[name] = ("tensor", add(v))
+            elif isinstance(v, list):
+                states[name] = ("list", [add(t) for t in v])
+            elif isinstance(v, dict):
+                states[name] = ("dict", [(k, add(t)) for k, t in v.items()])
+            else:
+                states[name] = ("value", v)
+        meta.append(states)
+    payload = torch.cat(pieces) if pieces else torch.zeros(0, dtype=torch.uint8, device=dev)
+    return meta, payload
+
+
+def _unflatten_states(template: Metric, states: dict, payload: torch.Tensor) -> Metric:
+    """A clone of `template` carrying the states described by `states` / `payload`."""
+
+    def get(entry) -> torch.Tensor:
+        dtype, shape, off, nbytes = entry
+        raw = payload[off : off + nbytes].clone()
+        return raw.view(getattr(torch, dtype)).reshape(shape).to(template.device)
+
+    m = clone_metric(template)
+    for name, (kind, v) in states.items():
+        if kind == "tensor":
+            setattr(m, name, get(v))
+        elif kind == "list":
+            setattr(m, name, [get(e) for e in v])
+        elif kind == "dict":
+            d = getattr(m, name)
+            d.clear()
+            for k, e in v:
+                d[k] = get(e)
+        else:
+            setattr(m, name, v)
+    return m
+
+
+def _gather_metrics(metrics: List[Metric], process_group) -> List[List[Metric]]:
+    """For every rank q, clones of `metrics` holding rank q's states — what the reference gets
+    from ``dist.all_gather_object`` of the pickled objects (toolkit.py:371-391), with the tensor
+    data moved by ONE padded all-gather of a flat byte buffer (NCCL on GPUs) and only the
+    shape/dtype table pickled.  Configuration attributes are taken from the local object: as in
+    the reference, the ranks are expected to hold identically configured metrics."""
+    world = dist.get_world_size(process_group)
+    dev = _comm_device(metrics[0].device, process_group)
+    meta, payload = _flatten_states(metrics, dev)
+    metas: List[Any] = [None] * world
+    dist.all_gather_object(metas, (meta, payload.numel()), group=process_group)
+    cap = max(n for _, n in metas)
+    buf = torch.zeros(max(cap, 1), dtype=torch.uint8, device=dev)
+    buf[: payload.numel()] = payload
+    out = [torch.empty_like(buf) for _ in range(world)]
+    dist.all_gather(out, buf, group=process_group)
+    return [[_unflatten_states(t, st, out[q]) for t, st in zip(metrics, metas[q][0])] for q in range(world)]
 
 
 # ------------------------------------------------------------------------------ public API
@@ -166,8 +233,9 @@ def get_synced_metric(metric: Metric, process_group: Optional[dist.ProcessGroup]
     merged = _gather_sample_store(metric, process_group)
     if merged is not None:
         return merged
-    gathered = _sync_metric_object(metric, process_group if process_group else dist.group.WORLD, world_size)
-    return clone_metric(gathered[0]).to(metric.device).merge_state(gathered[1:])
+    # any other Metric: its states travel as one flat byte buffer, no pickling of tensor data
+    gathered = [g[0] for g in _gather_metrics([metric], process_group)]
+    return gathered[0].to(metric.device).merge_state(gathered[1:])
 
 
 def sync_and_compute(metric: Metric, process_group: Optional[dist.ProcessGroup] = None) -> Any:
