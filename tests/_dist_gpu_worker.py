@@ -75,6 +75,15 @@ def main():
     res["ovr/mc_auprc"] = [toolkit.sync_and_compute(m2).tolist(), oracle.multiclass_auprc(xi, yi).tolist()]
     m3 = MultilabelAUPRC(num_labels=CC, average="macro", device=dev).update(xd, ld)
     res["ovr/ml_auprc_macro"] = [float(toolkit.sync_and_compute(m3)), float(oracle.multilabel_auprc(xi, li).mean())]
+    # generic state gather over NCCL (flat byte buffer): a metric without a dedicated sync path
+    from torcheval_b200.metrics import WindowedBinaryAUROC
+
+    wx, wy = rs.random((world, 300), dtype=np.float32) + 0.01, rs.integers(0, 2, (world, 300))
+    wm = WindowedBinaryAUROC(max_num_samples=200, device=dev).update(torch.from_numpy(wx[rank]).to(dev), torch.from_numpy(wy[rank]).to(dev))
+    res["generic/windowed"] = [
+        float(toolkit.sync_and_compute(wm)),
+        oracle.binary_auroc(np.concatenate([wx[r, 100:] for r in range(world)]), np.concatenate([wy[r, 100:] for r in range(world)]))[0],
+    ]
     Path(os.environ["TE_TEST_OUT"] + f".{rank}").write_text(json.dumps(res))
     dist.barrier()
     dist.destroy_process_group()
