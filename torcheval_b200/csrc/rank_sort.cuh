@@ -200,19 +200,9 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
   const uint32_t group = tid >> 4;
   const uint32_t gbase = group * kGroupKeys;  // tile-relative start of this half-warp's records
 
-  // ---- a digit that is the same for every key (digit_scan_kernel found one full bin: low bits of
-  //      bf16-valued scores, the exponent byte of one binade, constant scores) leaves the order
-  //      as it is: the tile is copied through, no ranking, no look-back ----
-  if (skip_flag && *skip_flag) {
-    if (zero_next && tid < kRadix) zero_next[(size_t)tile * kRadix + tid] = 0u;
-#pragma unroll 4
-    for (uint32_t r = tid; r < valid; r += kSortBlock) {
-      keys_out[base + r] = keys_in[base + r];
-      if (HAS_VAL) vals_out[base + r] = vals_in[base + r];
-    }
-    return;
-  }
-
+  // "this pass is a no-op" flag (see below): requested ahead of the key loads so that it is back
+  // before they are, and looked at only after the set-up work
+  const uint32_t skip_pass = skip_flag ? ld_relaxed_u32(skip_flag) : 0u;
   // ---- load: a warp instruction fetches two 64-byte runs, one per half-warp.  The loads are
   //      issued first; the ranking tables are cleared while they are in flight. ----
   KeyT key[kSortIpt];
@@ -228,6 +218,20 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
   dop.stage(s_sp, tid);
   if (kPeerScatter && tid <= (unsigned)kMaxSplitters) s_peer[tid] = peers.p[tid];
   __syncthreads();
+  // ---- a digit that is the same for every key (digit_scan_kernel found one full bin: low bits of
+  //      bf16-valued scores, the exponent byte of one binade, constant scores) leaves the order
+  //      as it is: the tile is copied through, no ranking, no look-back ----
+  if (skip_pass) {
+#pragma unroll
+    for (int i = 0; i < kSortIpt; ++i) {
+      const uint32_t r = gbase + i * 16 + sub;
+      if (r < valid) {
+        keys_out[base + r] = key[i];
+        if (HAS_VAL) vals_out[base + r] = vals_in[base + r];
+      }
+    }
+    return;
+  }
   TE_PHASE_MARK(0);  // setup
 #ifdef TE_PHASE_STATS
   {  // force the loads to complete here so that the load phase is visible on its own
