@@ -256,6 +256,42 @@ __device__ __forceinline__ FState f_shfl(const FState& v, int src) {
   return u;
 }
 
+// Exclusive warp scan of the lane states + the warp total, specialised for this monoid: S is a
+// plain prefix sum; "does a group start in the lanes before me" is one ballot; and the (M, Mp) of
+// the LAST such lane come from one indexed shuffle each — instead of five rounds of four shuffles
+// and a conditional combine.  Relative to the start of the step, like f_combine over the lanes.
+template <bool WITH_POS>
+__device__ __forceinline__ void f_warp_scan(const FState& mine, unsigned lane, FState& excl, FState& total) {
+  uint32_t s_incl = mine.S;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t u = __shfl_up_sync(kFull, s_incl, o);
+    if (lane >= (unsigned)o) s_incl += u;
+  }
+  const uint32_t s_excl = s_incl - mine.S;
+  const uint32_t fb = __ballot_sync(kFull, mine.F != 0);
+  const uint32_t m_abs = s_excl + mine.M;  // negatives before my last group start, from the step start
+  const uint32_t below = fb & ((1u << lane) - 1u);
+  const int src = below ? 31 - __clz(below) : 0;
+  const int last = fb ? 31 - __clz(fb) : 0;
+  const uint32_t m_src = __shfl_sync(kFull, m_abs, src);
+  const uint32_t m_last = __shfl_sync(kFull, m_abs, last);
+  excl.S = s_excl;
+  excl.F = below ? 1u : 0u;
+  excl.M = below ? m_src : 0u;
+  total.S = __shfl_sync(kFull, s_incl, 31);
+  total.F = fb ? 1u : 0u;
+  total.M = fb ? m_last : 0u;
+  if (WITH_POS) {
+    const uint32_t p_src = __shfl_sync(kFull, mine.Mp, src);
+    const uint32_t p_last = __shfl_sync(kFull, mine.Mp, last);
+    excl.Mp = below ? p_src : 0u;
+    total.Mp = fb ? p_last : 0u;
+  } else {
+    excl.Mp = total.Mp = 0u;
+  }
+}
+
 struct alignas(16) ChunkRec {
   FState st;                 // state of the whole chunk
   unsigned long long A;      // AUROC: local part of 2U
@@ -392,15 +428,8 @@ __global__ void __launch_bounds__(kFinBlock, kFinWarpsPerSm / (kFinBlock / kWarp
     }
 
     // warp scan of the lane aggregates
-    FState incl = mine;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const FState u = f_shfl_up<POS>(incl, o);
-      if (lane >= (unsigned)o) incl = f_combine(u, incl);
-    }
-    FState excl = f_shfl_up<POS>(incl, 1);
-    if (lane == 0) excl = f_identity();
-    const FState step_agg = f_shfl<POS>(incl, 31);
+    FState excl, step_agg;
+    f_warp_scan<POS>(mine, lane, excl, step_agg);
     const FState g = f_combine(carry, excl);
 
     if (MODE == 0) {
