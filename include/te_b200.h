@@ -235,7 +235,8 @@ TE_API int te_ovr_rank(const float* input, int64_t ld, const int64_t* target, in
  *    senders and hands the result to te_binary_auroc_from_keys / te_binary_auprc_from_keys_begin as
  *    digit_hist (uint32[4][256]; NULL there = histogram the keys first), which saves one read of
  *    the received keys.
- *  te_partition_u32: stable partition of keys by the same kind of splitters; counts_in (device,
+ *  te_partition_u32: partition of keys by the same kind of splitters (the order of the keys INSIDE
+ *    a bucket is unspecified: they are sorted next); counts_in (device,
  *    may be NULL) are bucket sizes already known from te_rank_pack, counts receives them again,
  *    keys_out the keys grouped by bucket.
  *  te_binary_auroc_from_keys: sort packed keys and integrate; out[] as te_binary_auroc plus

@@ -1842,10 +1842,12 @@ static int partition_impl(const uint32_t* keys_in, int64_t n, const uint32_t* sp
   uint32_t* lb = at<uint32_t>(scratch, p.off_lookback);
   uint32_t* gp = at<uint32_t>(scratch, p.off_gprefix);
   const bool peer = peer_ptrs_host != nullptr;
+  // kUnstable: the keys of a bucket are sorted afterwards, so their order inside it is free and
+  // ranks can be handed out in arrival order (one ATOMS.ADD instead of ATOMS.OR + LDS + STS)
   TE_PROF(peer ? "onesweep_partition_peer" : "onesweep_partition", st);
 #define TE_LAUNCH_PART(B, PEER)                                                                          \
   do {                                                                                                   \
-    auto fn = onesweep_pass_kernel<uint32_t, false, B, SplitterDigit, kSortIptDefault, PEER>;            \
+    auto fn = onesweep_pass_kernel<uint32_t, false, B, SplitterDigit, kSortIptDefault, PEER, true>;      \
     const size_t smem = onesweep_smem_bytes<uint32_t, B>();                                              \
     TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
     fn<<<p.sort_tiles, B, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist, lb, gp, pp, hot, \
