@@ -42,9 +42,10 @@ def main():
             dest.append(bufs[b].data_ptr() + 4 * ((b % 4) - excl))
             excl += c
         t_pack = timeit(lambda: ops.rank_pack(x, y, sp))
+        t_pack_h = timeit(lambda: ops.rank_pack(x, y, sp, want_hist=True))
         t_loc = timeit(lambda: ops.partition_u32(keys, sp, counts))
         t_sc = timeit(lambda: ops.partition_scatter_u32(keys, sp, counts, dest))
-        print(f"  world={world:2d}  pack {t_pack:.3f} ms   partition(local) {t_loc:.3f} ms   scatter(to local buffers) {t_sc:.3f} ms")
+        print(f"  world={world:2d}  pack {t_pack:.3f} ms (+digit hist {t_pack_h:.3f})   partition(local) {t_loc:.3f} ms   scatter(to local buffers) {t_sc:.3f} ms")
 
 
 if __name__ == "__main__":

@@ -1434,7 +1434,7 @@ __global__ void __launch_bounds__(1024)
       if (j < (int)cnt) {
         npos += lab[j];
         const uint32_t bkt = dop(k[j]);
-        atomicAdd(sh + bkt * kWarp + lane, 1u);
+        if (!HIST) atomicAdd(sh + bkt * kWarp + lane, 1u);  // HIST: the size is the sum of the digit-0 bins
         if (HIST) {
           uint32_t* bins = s_dh + bkt * kPackBinsPerBucket;
           atomicAdd(bins + (k[j] & 255u), 1u);
@@ -1451,10 +1451,19 @@ __global__ void __launch_bounds__(1024)
     }
   }
   __syncthreads();
-  if (tid < 16) {
+  if (!HIST && tid < 16) {
     uint32_t s = 0;
     for (int r = 0; r < kWarp; ++r) s += sh[tid * kWarp + r];
     if (s) atomicAdd(hist + tid, s);
+  }
+  if (HIST) {  // bucket sizes: warp w sums the 256 digit-0 bins of bucket w
+    const unsigned w = tid >> 5;
+    if (w <= (unsigned)dop_in.nsp) {
+      unsigned long long s = 0;
+      for (int d = lane; d < kRadix; d += kWarp) s += s_dh[w * kPackBinsPerBucket + d];
+      s = warp_sum(s);
+      if (lane == 0 && s) atomicAdd(hist + w, (uint32_t)s);
+    }
   }
   if (HIST) {  // digit_hist[bucket][pass][digit]
     const uint32_t total = (uint32_t)(dop_in.nsp + 1) * 4 * kRadix;
