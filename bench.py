@@ -258,6 +258,7 @@ def run_ours(args) -> dict:
     cpu = None
     secondary = None
     binned = None
+    ovr = None
     if world == 1:
         binned = binned_bench(args, x, y, peak_gbs, peak_src)
     else:
@@ -289,6 +290,7 @@ def run_ours(args) -> dict:
         cpu = cpu_baseline_auroc(xh, yh)
         del xh, yh
         secondary = confusion_matrix_bench(args, device, peak_gbs, peak_src)
+        ovr = one_vs_rest_bench(args, device)
 
     if world > 1:
         # end to end at N GPUs through the class API + toolkit: every rank feeds its pinned HOST
@@ -368,6 +370,8 @@ def run_ours(args) -> dict:
         line["secondary"] = secondary
     if binned:
         line["secondary_binned"] = binned
+    if ovr:
+        line["secondary_ovr"] = ovr
     if world > 1:
         import torch.distributed as dist
 
@@ -478,6 +482,36 @@ def binned_sync_bench(args, x, y, world, device) -> dict:
             "workload": f"BinaryBinnedAUPRC update + sync_and_compute, T={T} thresholds, N=2^{n_total.bit_length() - 1} scores over {world} GPUs, int64 counter all-reduce",
             "binned_auprc": float(out[0].item()),
         },
+    }
+
+
+def one_vs_rest_bench(args, device) -> dict:
+    """configs[4] shape at a size one step finishes in tens of milliseconds: MulticlassAUROC
+    one-vs-rest (segmented sort), C = 1000 classes, N = 2^20 samples = 1.05e9 scores on one GPU."""
+    from torcheval_b200 import ops
+
+    n, C = 1 << 20, 1000
+    g = torch.Generator(device=device).manual_seed(SEED + 5)
+    x = torch.rand((n, C), device=device, generator=g, dtype=torch.float32)
+    y = torch.randint(0, C, (n,), device=device, generator=g, dtype=torch.int64)
+    for _ in range(2):
+        out = ops.ovr_rank(x, y, False, 0)
+    torch.cuda.synchronize()
+    steps = 3
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(steps):
+        out = ops.ovr_rank(x, y, False, 0)
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1) / steps
+    return {
+        "metric": "multiclass_auroc_one_vs_rest_scores_per_sec",
+        "value": n * C / (ms * 1e-3),
+        "unit": "scores/s",
+        "ms_per_step": ms,
+        "config": {"workload": f"MulticlassAUROC one-vs-rest, C={C}, N=2^20 samples, float32 (N, C) scores, 1 GPU",
+                   "macro_auroc": float(out[:, 0].mean().item())},
     }
 
 
