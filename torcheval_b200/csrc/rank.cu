@@ -397,32 +397,58 @@ __global__ void __launch_bounds__(kFinBlock, kFinWarpsPerSm / (kFinBlock / kWarp
     uint32_t n_pre = 0, n_post = 0;  // positives before / after the first group start seen here
     uint32_t s_lc = 0;               // sum over positives of (#negatives before it, local)
     uint32_t s_lgs = 0;              // sum over "post" positives of (#negatives before its group, local)
-    uint32_t lgs = 0;
+    if (MODE == 0 && cnt == (uint32_t)kFinIpt) {
+      // full lane, counting sweep: straight-line integer arithmetic, no predicates per record
+      uint32_t S = 0, M = 0, F = 0, npos = 0, Mp = 0;
 #pragma unroll
-    for (int j = 0; j < kFinIpt; ++j) {
-      if (j < (int)cnt) {
-        const uint32_t sc = k[j] >> 1;
-        const bool st = (j == 0 && i0 == 0) || sc != prev;
+      for (int j = 0; j < kFinIpt; ++j) {
+        const uint32_t sc = k[j] >> 1, lab = k[j] & 1u;
+        uint32_t st = sc != prev ? 1u : 0u;
+        if (j == 0) st |= (i0 == 0) ? 1u : 0u;  // the first record of the array starts a group
         prev = sc;
-        if (st) {
-          starts |= 1u << j;
-          mine.F = 1;
-          mine.M = mine.S;
-          if (POS) mine.Mp = i0 + j;
-          lgs = mine.S;
+        M = st ? S : M;
+        F |= st;
+        if (POS) {
+          starts |= st << j;
+          Mp = st ? i0 + j : Mp;
         }
-        if (k[j] & 1u) {
-          if (MODE == 0) {
-            s_lc += mine.S;
-            if (mine.F) {
-              ++n_post;
-              s_lgs += lgs;
-            } else {
-              ++n_pre;
-            }
+        const uint32_t lf = lab & F;
+        s_lc += lab * S;
+        s_lgs += lf * M;
+        npos += lab;
+        n_post += lf;
+        S += 1u - lab;
+      }
+      n_pre = npos - n_post;
+      mine.S = S, mine.M = M, mine.F = F, mine.Mp = Mp;
+    } else {
+      uint32_t lgs = 0;
+#pragma unroll
+      for (int j = 0; j < kFinIpt; ++j) {
+        if (j < (int)cnt) {
+          const uint32_t sc = k[j] >> 1;
+          const bool st = (j == 0 && i0 == 0) || sc != prev;
+          prev = sc;
+          if (st) {
+            starts |= 1u << j;
+            mine.F = 1;
+            mine.M = mine.S;
+            if (POS) mine.Mp = i0 + j;
+            lgs = mine.S;
           }
-        } else {
-          ++mine.S;
+          if (k[j] & 1u) {
+            if (MODE == 0) {
+              s_lc += mine.S;
+              if (mine.F) {
+                ++n_post;
+                s_lgs += lgs;
+              } else {
+                ++n_pre;
+              }
+            }
+          } else {
+            ++mine.S;
+          }
         }
       }
     }
