@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(kBinBlock, 1)
   const int64_t nvec = n / VEC;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int64_t first = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  constexpr int UNROLL = 2;
+  constexpr int UNROLL = VEC == 4 ? 3 : 2;
   for (int64_t base = first; base < nvec; base += stride * UNROLL) {
     float xv[UNROLL][VEC];
     long long tv[UNROLL][VEC];
