@@ -415,7 +415,9 @@ def class_sharded_one_vs_rest(
 
     x_loc = transpose_sharding(input)
     if multilabel:
-        t_loc = transpose_sharding(target)
+        # labels cross the links as one byte each (only "== 1" matters: auprc.py:330-347 calls the
+        # per-label routine with pos_label 1), not as the int64 they are stored in
+        t_loc = transpose_sharding((target == 1).to(torch.uint8)).to(torch.int64)
     else:
         # every rank needs all N class labels; shifted so that local column j is class j
         pad = torch.zeros(max(ns), dtype=torch.int64, device=dev)
