@@ -123,7 +123,8 @@ class _PeerInbox:
 
 def choose_splitters(samples_sorted, world: int):
     """W-1 ascending splitters from the sorted pool of sampled keys; label bit cleared so that
-    both labels of one score compare alike."""
+    both labels of one score compare alike.  (Host restatement of what te_select_splitters does
+    on the device; the tests check the kernel against it.)"""
     m = len(samples_sorted)
     out = []
     for i in range(1, world):
@@ -134,7 +135,8 @@ def choose_splitters(samples_sorted, world: int):
 
 def combine_rank_stats(stats):
     """stats: list over ranks (ascending score ranges) of (P_r, N_r, 2U_r) Python ints.
-    Returns (auroc, P, N, 2U) with exact integer arithmetic."""
+    Returns (auroc, P, N, 2U) with exact integer arithmetic.  (Host restatement of
+    te_combine_auroc_stats / combine_rank_stats_tensor; the tests check both against it.)"""
     u2 = 0
     neg_below = 0
     P = N = 0
@@ -321,19 +323,6 @@ def sharded_binary_auroc(
     somewhere) means the packed representation does not apply and [0] is not valid.
     One host read in total (bucket sizes); everything else stays on the device."""
     return _sharded_binary_auroc(score, target, group)[0]
-
-
-def combine_rank_ap(sums, positives):
-    """sums[r] = sum over rank r's positives of the precision at their threshold (float),
-    positives[r] = P_r.  AP of the union; no positives anywhere -> -0.0 like the reference
-    (precision_recall_curve.py:227-229)."""
-    P = sum(int(p) for p in positives)
-    if P == 0:
-        return -0.0
-    total = 0.0
-    for v in sums:  # fixed rank order: the same bits on every rank and every run
-        total += float(v)
-    return total / P
 
 
 def _sharded_binary_auprc(score, target, group):
