@@ -81,8 +81,12 @@ __global__ void __launch_bounds__(kIngestBlock, 1)
     rank_ingest_kernel(const float* __restrict__ score, const TargetT* __restrict__ target,
                        const uint32_t* __restrict__ raw_keys, uint32_t n, bool vec_ok,
                        uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
-                       uint32_t* ghist, RankScalars* scal) {
+                       uint32_t* ghist, RankScalars* scal, const uint32_t* __restrict__ payload_bad) {
   extern __shared__ uint32_t sh[];  // [pass][digit][lane]
+  // kIndexed: the 32-bit payload that travels with a key is its index — or, when every target is
+  // exactly a float32 and there are no weights (payload_bad given and 0), the target value itself,
+  // which spares the final sweep a random gather by index
+  const bool as_payload = MODE == kIndexed && payload_bad && *payload_bad == 0u;
   const unsigned tid = threadIdx.x, lane = tid & 31;
   for (int i = tid; i < 4 * kRadix * kWarp; i += kIngestBlock) sh[i] = 0;
   __syncthreads();
@@ -153,12 +157,17 @@ __global__ void __launch_bounds__(kIngestBlock, 1)
       }
       if (cnt == 4) {
         st_stream_v4(keys_out + i0, make_int4((int)k[0], (int)k[1], (int)k[2], (int)k[3]));
-        if (MODE == kIndexed)
-          st_stream_v4(vals_out + i0, make_int4((int)i0, (int)i0 + 1, (int)i0 + 2, (int)i0 + 3));
+        if (MODE == kIndexed) {
+          if (as_payload)
+            st_stream_v4(vals_out + i0, make_int4(__float_as_int((float)target[i0]), __float_as_int((float)target[i0 + 1]),
+                                                  __float_as_int((float)target[i0 + 2]), __float_as_int((float)target[i0 + 3])));
+          else
+            st_stream_v4(vals_out + i0, make_int4((int)i0, (int)i0 + 1, (int)i0 + 2, (int)i0 + 3));
+        }
       } else {
         for (uint32_t j = 0; j < cnt; ++j) {
           keys_out[i0 + j] = k[j];
-          if (MODE == kIndexed) vals_out[i0 + j] = i0 + j;
+          if (MODE == kIndexed) vals_out[i0 + j] = as_payload ? __float_as_uint((float)target[i0 + j]) : i0 + j;
         }
       }
     }
@@ -913,7 +922,8 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
 
 template <int MODE, typename TargetT>
 int launch_ingest(const float* score, const void* target, const uint32_t* raw, const RankPlan& p,
-                  uint32_t* keys_out, uint32_t* vals_out, void* scratch, int sms, cudaStream_t st) {
+                  uint32_t* keys_out, uint32_t* vals_out, void* scratch, int sms, cudaStream_t st,
+                  const uint32_t* payload_bad = nullptr) {
   auto kern = rank_ingest_kernel<MODE, TargetT>;
   TE_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)kIngestSmem));
@@ -926,7 +936,7 @@ int launch_ingest(const float* score, const void* target, const uint32_t* raw, c
   TE_PROF(MODE == kPacked ? "rank_ingest_packed" : (MODE == kIndexed ? "rank_ingest_indexed" : "rank_hist_keys"), st);
   kern<<<grid, kIngestBlock, kIngestSmem, st>>>(score, (const TargetT*)target, raw, p.n, vec_ok,
                                                  keys_out, vals_out, at<uint32_t>(scratch, p.off_hist),
-                                                 at<RankScalars>(scratch, p.off_scal));
+                                                 at<RankScalars>(scratch, p.off_scal), payload_bad);
   TE_LAUNCH_CHECK();
   return TE_OK;
 }
@@ -1024,12 +1034,14 @@ int binary_rank_packed(const float* score, const void* target, int32_t dt, int64
 // path.  AUPRC (positives are target == 1, precision_recall_curve.py:216):
 //     AP = (1/P) * sum_{j positive} (P - TPb(j)) / (n - TPb(j) - FPb(j)).
 // ------------------------------------------------------------------------------------------
-constexpr int kGenBlock = 256;
+constexpr int kGenBlock = 512;
 constexpr int kGenIpt = 8;
 constexpr int kGenTile = kGenBlock * kGenIpt;
 
 struct GenScalars {
   double tp_total, fp_total;
+  uint32_t payload_bad;  // != 0: some target is not exactly a float32 (or there are weights): gather by index
+  uint32_t pad;
 };
 
 struct GState {
@@ -1094,6 +1106,18 @@ __device__ __forceinline__ void gen_terms(const TargetT* __restrict__ target,
   }
 }
 
+// the same from a payload that IS the target value (float32 bits), no weights
+__device__ __forceinline__ void gen_terms_payload(uint32_t val, int mode, double& tp, double& fp) {
+  const double t = (double)__uint_as_float(val);
+  if (mode == 0) {
+    tp = t;
+    fp = 1.0 - t;
+  } else {
+    tp = t == 1.0 ? 1.0 : 0.0;
+    fp = 1.0 - tp;
+  }
+}
+
 // totals needed up front by the AUPRC integrand (and reported for AUROC)
 template <typename TargetT>
 __global__ void __launch_bounds__(256)
@@ -1101,12 +1125,16 @@ __global__ void __launch_bounds__(256)
                        uint32_t n, int mode, GenScalars* gs) {
   __shared__ double ws[8];
   double a = 0.0, b = 0.0;
+  uint32_t inexact = weight ? 1u : 0u;
   for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
     double tp, fp;
     gen_terms(target, weight, i, mode, tp, fp);
     a += tp;
     b += fp;
+    const TargetT t = target[i];
+    inexact |= ((TargetT)(float)t != t) ? 1u : 0u;
   }
+  if (__any_sync(kFull, inexact != 0u) && (threadIdx.x & 31) == 0) atomicOr(&gs->payload_bad, 1u);
   double ta, tb;
   block_scan_incl<double, 256>(a, ws, ta);
   block_scan_incl<double, 256>(b, ws, tb);
@@ -1136,11 +1164,15 @@ __global__ void __launch_bounds__(kGenBlock)
 
   uint32_t k[kGenIpt];
   double tp[kGenIpt], fp[kGenIpt];
+  const bool as_payload = gs->payload_bad == 0u;  // uniform: what the ingest kernel stored in vals
 #pragma unroll
   for (int j = 0; j < kGenIpt; ++j) {
     if (j < (int)cnt) {
       k[j] = keys[i0 + j];
-      gen_terms(target, weight, vals[i0 + j], mode, tp[j], fp[j]);
+      if (as_payload)
+        gen_terms_payload(vals[i0 + j], mode, tp[j], fp[j]);
+      else
+        gen_terms(target, weight, vals[i0 + j], mode, tp[j], fp[j]);
     } else {
       k[j] = 0u;
       tp[j] = fp[j] = 0.0;
@@ -1329,16 +1361,16 @@ int binary_rank_general_t(const float* score, const TargetT* target, const doubl
   uint32_t tiles = 0;
   if (n > 0) {
     tiles = g.tiles;
-    int rc = launch_ingest<kIndexed, long long>(score, nullptr, nullptr, p, ka, va, scratch, sms, st);
-    if (rc) return rc;
-    rc = run_passes(p, scratch, ka, kb, ka, va, vb, va, st);  // sorted pairs end in (ka, va)
-    if (rc) return rc;
-    {
+    {  // totals first: it also decides whether the target values can ride along as the payload
       TE_PROF("rank_totals", st);
       const uint32_t grid = (uint32_t)min((int64_t)sms * 8, (n + 255) / 256);
       rank_totals_kernel<TargetT><<<grid, 256, 0, st>>>(target, weight, p.n, mode, gs);
     }
     TE_LAUNCH_CHECK();
+    int rc = launch_ingest<kIndexed, TargetT>(score, target, nullptr, p, ka, va, scratch, sms, st, &gs->payload_bad);
+    if (rc) return rc;
+    rc = run_passes(p, scratch, ka, kb, ka, va, vb, va, st);  // sorted pairs end in (ka, va)
+    if (rc) return rc;
     {
       TE_PROF("rank_final_general", st);
       rank_final_general_kernel<TargetT><<<tiles, kGenBlock, 0, st>>>(
