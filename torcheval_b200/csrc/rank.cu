@@ -1317,9 +1317,208 @@ __global__ void __launch_bounds__(1024)
   }
 }
 
+// ---- chunked form of the general AUROC sweep (mode 0) ----------------------------------------
+// Same idea as rank_chunk_kernel: the area term  sum_j tp_j * FPb(j) - fp_j * TPb(j)  is LINEAR in
+// the state E of everything before a chunk, so every warp sweeps one contiguous chunk with its
+// state in registers and reports
+//   A      the part that needs nothing from outside the chunk
+//   TP2/FP2      sum of tp / fp over records whose tie group starts inside the chunk (they see E.S)
+//   TPlead/FPlead  the same over the leading run whose group started before the chunk (they see E.M)
+// and one CTA finishes:  sum_c A_c + E_c.Sfp*TP2_c - E_c.Stp*FP2_c + E_c.Mfp*TPlead_c - E_c.Mtp*FPlead_c.
+constexpr int kGcIpt = 8;
+constexpr int kGcStep = kWarp * kGcIpt;  // 256 records per warp step
+constexpr int kGcBlock = 256;
+
+struct alignas(16) GenChunkRec {
+  double Stp, Sfp, Mtp, Mfp;
+  double A, TP2, FP2, TPlead, FPlead;
+  unsigned long long F;
+};
+
+inline ChunkGeom gen_chunk_geom(uint32_t n, int sms) {
+  ChunkGeom g;
+  uint32_t steps = (n + kGcStep - 1) / kGcStep;
+  if (steps < 1) steps = 1;
+  uint32_t want = (uint32_t)sms * 32u;
+  if (want > (uint32_t)kMaxChunks) want = kMaxChunks;
+  if (want > steps) want = steps;
+  g.steps_per_chunk = (steps + want - 1) / want;
+  g.nchunks = (steps + g.steps_per_chunk - 1) / g.steps_per_chunk;
+  return g;
+}
+
+// exclusive warp scan of GState + warp total (prefix sums, one ballot, indexed shuffles)
+__device__ __forceinline__ void g_warp_scan(const GState& mine, unsigned lane, GState& excl, GState& total) {
+  double st = mine.Stp, sf = mine.Sfp;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const double ut = __shfl_up_sync(kFull, st, o), uf = __shfl_up_sync(kFull, sf, o);
+    if (lane >= (unsigned)o) st += ut, sf += uf;
+  }
+  const double et = __shfl_up_sync(kFull, st, 1), ef = __shfl_up_sync(kFull, sf, 1);
+  excl.Stp = lane ? et : 0.0;
+  excl.Sfp = lane ? ef : 0.0;
+  const uint32_t fb = __ballot_sync(kFull, mine.F != 0);
+  const double mt_abs = excl.Stp + mine.Mtp, mf_abs = excl.Sfp + mine.Mfp;
+  const uint32_t below = fb & ((1u << lane) - 1u);
+  const int src = below ? 31 - __clz(below) : 0, last = fb ? 31 - __clz(fb) : 0;
+  const double mts = __shfl_sync(kFull, mt_abs, src), mfs = __shfl_sync(kFull, mf_abs, src);
+  const double mtl = __shfl_sync(kFull, mt_abs, last), mfl = __shfl_sync(kFull, mf_abs, last);
+  excl.F = below ? 1u : 0u;
+  excl.Mtp = below ? mts : 0.0;
+  excl.Mfp = below ? mfs : 0.0;
+  total.Stp = __shfl_sync(kFull, st, 31);
+  total.Sfp = __shfl_sync(kFull, sf, 31);
+  total.F = fb ? 1u : 0u;
+  total.Mtp = fb ? mtl : 0.0;
+  total.Mfp = fb ? mfl : 0.0;
+}
+
+template <typename TargetT>
+__global__ void __launch_bounds__(kGcBlock)
+    gen_chunk_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
+                     const TargetT* __restrict__ target, const double* __restrict__ weight, uint32_t n,
+                     uint32_t steps_per_chunk, uint32_t nchunks, const GenScalars* __restrict__ gs,
+                     GenChunkRec* rec) {
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t chunk = blockIdx.x * (kGcBlock / kWarp) + (threadIdx.x >> 5);
+  if (chunk >= nchunks) return;
+  const uint64_t begin64 = (uint64_t)chunk * steps_per_chunk * kGcStep;
+  if (begin64 >= n) return;
+  const uint32_t begin = (uint32_t)begin64;
+  const uint32_t end = (uint32_t)min((uint64_t)n, begin64 + (uint64_t)steps_per_chunk * kGcStep);
+  const bool as_payload = gs->payload_bad == 0u;  // what the ingest kernel stored in vals
+  GState carry = g_identity();
+  double A = 0.0, TP2 = 0.0, FP2 = 0.0, TPlead = 0.0, FPlead = 0.0;
+  uint32_t last = begin > 0 ? keys[begin - 1] : 0u;
+  for (uint32_t at = begin; at < end; at += kGcStep) {
+    const uint32_t i0 = at + lane * kGcIpt;
+    const uint32_t cnt = i0 < end ? min((uint32_t)kGcIpt, end - i0) : 0u;
+    uint32_t k[kGcIpt], v[kGcIpt];
+    if (cnt == (uint32_t)kGcIpt) {
+#pragma unroll
+      for (int q = 0; q < kGcIpt / 4; ++q) {
+        const int4 a = ld_stream_v4(keys + i0 + 4 * q), b = ld_stream_v4(vals + i0 + 4 * q);
+        k[4 * q] = a.x, k[4 * q + 1] = a.y, k[4 * q + 2] = a.z, k[4 * q + 3] = a.w;
+        v[4 * q] = b.x, v[4 * q + 1] = b.y, v[4 * q + 2] = b.z, v[4 * q + 3] = b.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < kGcIpt; ++j) {
+        k[j] = j < (int)cnt ? keys[i0 + j] : 0u;
+        v[j] = j < (int)cnt ? vals[i0 + j] : 0u;
+      }
+    }
+    // key before my first record: the previous lane's last one (only full lanes are followed by
+    // non-empty ones), lane 0: carried from the previous step
+    uint32_t prev = __shfl_up_sync(kFull, k[kGcIpt - 1], 1);
+    if (lane == 0) prev = last;
+    last = __shfl_sync(kFull, k[kGcIpt - 1], 31);
+
+    GState mine = g_identity();
+    double a_loc = 0.0, tp_post = 0.0, fp_post = 0.0, tp_pre = 0.0, fp_pre = 0.0;
+#pragma unroll
+    for (int j = 0; j < kGcIpt; ++j) {
+      if (j < (int)cnt) {
+        double tp, fp;
+        if (as_payload)
+          gen_terms_payload(v[j], 0, tp, fp);
+        else
+          gen_terms(target, weight, v[j], 0, tp, fp);
+        const bool st = (j == 0 && i0 == 0) || k[j] != prev;
+        prev = k[j];
+        if (st) {
+          mine.F = 1;
+          mine.Mtp = mine.Stp;
+          mine.Mfp = mine.Sfp;
+        }
+        if (mine.F) {
+          a_loc += tp * mine.Mfp - fp * mine.Mtp;
+          tp_post += tp;
+          fp_post += fp;
+        } else {
+          tp_pre += tp;
+          fp_pre += fp;
+        }
+        mine.Stp += tp;
+        mine.Sfp += fp;
+      }
+    }
+    GState excl, total;
+    g_warp_scan(mine, lane, excl, total);
+    const GState g = g_combine(carry, excl);  // everything before this lane, inside the chunk
+    A += a_loc + g.Sfp * tp_post - g.Stp * fp_post;
+    TP2 += tp_post;
+    FP2 += fp_post;
+    if (g.F) {
+      A += g.Mfp * tp_pre - g.Mtp * fp_pre;
+      TP2 += tp_pre;
+      FP2 += fp_pre;
+    } else {
+      TPlead += tp_pre;
+      FPlead += fp_pre;
+    }
+    carry = g_combine(carry, total);
+  }
+  A = warp_sum(A), TP2 = warp_sum(TP2), FP2 = warp_sum(FP2);  // butterflies: the same bits every run
+  TPlead = warp_sum(TPlead), FPlead = warp_sum(FPlead);
+  if (lane == 0) {
+    GenChunkRec r;
+    r.Stp = carry.Stp, r.Sfp = carry.Sfp, r.Mtp = carry.Mtp, r.Mfp = carry.Mfp, r.F = carry.F;
+    r.A = A, r.TP2 = TP2, r.FP2 = FP2, r.TPlead = TPlead, r.FPlead = FPlead;
+    rec[chunk] = r;
+  }
+}
+
+// One CTA: exclusive scan of the chunk states (strips of 1024) and the final sum.  Writes the
+// area term into partial[0] and the totals of the scan into inc[0] (where
+// rank_reduce_general_kernel looks for them).
+__global__ void __launch_bounds__(1024)
+    gen_chunk_scan_kernel(const GenChunkRec* __restrict__ rec, uint32_t nchunks, double* partial, GenRec* inc) {
+  __shared__ GState s_warp[32];
+  __shared__ double s_sum[32];
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  GState carry = g_identity();
+  double acc = 0.0;
+  for (uint32_t base = 0; base < nchunks; base += 1024) {
+    const uint32_t i = base + tid;
+    GenChunkRec r{};
+    if (i < nchunks) r = rec[i];
+    GState mine;
+    mine.Stp = r.Stp, mine.Sfp = r.Sfp, mine.Mtp = r.Mtp, mine.Mfp = r.Mfp, mine.F = (uint32_t)r.F;
+    GState excl, wtotal;
+    g_warp_scan(mine, lane, excl, wtotal);
+    if (lane == 31) s_warp[warp] = wtotal;
+    __syncthreads();
+    GState wprefix = g_identity(), strip = g_identity();
+    for (int w = 0; w < 32; ++w) {
+      const GState x = s_warp[w];
+      if (w < (int)warp) wprefix = g_combine(wprefix, x);
+      strip = g_combine(strip, x);
+    }
+    const GState E = g_combine(carry, g_combine(wprefix, excl));
+    if (i < nchunks) {
+      acc += r.A + E.Sfp * r.TP2 - E.Stp * r.FP2;
+      if (E.F) acc += E.Mfp * r.TPlead - E.Mtp * r.FPlead;
+    }
+    carry = g_combine(carry, strip);
+    __syncthreads();
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) s_sum[warp] = acc;
+  __syncthreads();
+  if (tid == 0) {
+    double t = 0.0;
+    for (int w = 0; w < 32; ++w) t += s_sum[w];
+    partial[0] = t;
+    inc[0].w[0] = (unsigned long long)__double_as_longlong(carry.Stp);
+    inc[0].w[1] = (unsigned long long)__double_as_longlong(carry.Sfp);
+  }
+}
+
 struct GenPlan {
   RankPlan base;
-  size_t off_gzero, gzero_bytes, off_gs, off_agg, off_inc, off_partial, total;
+  size_t off_gzero, gzero_bytes, off_gs, off_agg, off_inc, off_partial, off_chunks, total;
   uint32_t tiles;
 };
 GenPlan make_gen_plan(int64_t n) {
@@ -1339,6 +1538,7 @@ GenPlan make_gen_plan(int64_t n) {
   g.off_inc = take((size_t)g.tiles * sizeof(GenRec));
   g.gzero_bytes = o - g.off_gzero;
   g.off_partial = take((size_t)g.tiles * 8);
+  g.off_chunks = take((size_t)kMaxChunks * sizeof(GenChunkRec));
   g.total = o;
   return g;
 }
@@ -1371,7 +1571,19 @@ int binary_rank_general_t(const float* score, const TargetT* target, const doubl
     if (rc) return rc;
     rc = run_passes(p, scratch, ka, kb, ka, va, vb, va, st);  // sorted pairs end in (ka, va)
     if (rc) return rc;
-    {
+    if (mode == 0) {
+      // AUROC: linear in the carried prefix -> warp-private chunks + one scan, no look-back
+      const ChunkGeom cg = gen_chunk_geom(p.n, sms);
+      GenChunkRec* crec = at<GenChunkRec>(scratch, g.off_chunks);
+      {
+        TE_PROF("gen_chunk_sweep", st);
+        gen_chunk_kernel<TargetT><<<(cg.nchunks + kGcBlock / kWarp - 1) / (kGcBlock / kWarp), kGcBlock, 0, st>>>(
+            ka, va, target, weight, p.n, cg.steps_per_chunk, cg.nchunks, gs, crec);
+      }
+      TE_PROF("gen_chunk_scan", st);
+      gen_chunk_scan_kernel<<<1, 1024, 0, st>>>(crec, cg.nchunks, partial, inc);
+      tiles = 1;  // what the reduce below sums over
+    } else {
       TE_PROF("rank_final_general", st);
       rank_final_general_kernel<TargetT><<<tiles, kGenBlock, 0, st>>>(
           ka, va, target, weight, p.n, mode, agg, inc, at<uint32_t>(scratch, p.off_ticket) + 4, gs,
