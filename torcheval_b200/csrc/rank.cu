@@ -1059,38 +1059,11 @@ __device__ __forceinline__ GState g_combine(const GState& a, const GState& b) {
   r.Mfp = b.F ? a.Sfp + b.Mfp : a.Mfp;
   return r;
 }
-__device__ __forceinline__ GState g_shfl_up(const GState& v, int o) {
-  GState u;
-  u.Stp = __shfl_up_sync(kFull, v.Stp, o);
-  u.Sfp = __shfl_up_sync(kFull, v.Sfp, o);
-  u.Mtp = __shfl_up_sync(kFull, v.Mtp, o);
-  u.Mfp = __shfl_up_sync(kFull, v.Mfp, o);
-  u.F = __shfl_up_sync(kFull, v.F, o);
-  return u;
-}
 struct alignas(64) GenRec {
   unsigned long long flag;
   unsigned long long w[5];
   unsigned long long pad[2];
 };
-__device__ __forceinline__ void grec_publish(GenRec* r, const GState& s) {
-  st_relaxed_u64(&r->w[0], (unsigned long long)__double_as_longlong(s.Stp));
-  st_relaxed_u64(&r->w[1], (unsigned long long)__double_as_longlong(s.Sfp));
-  st_relaxed_u64(&r->w[2], (unsigned long long)__double_as_longlong(s.Mtp));
-  st_relaxed_u64(&r->w[3], (unsigned long long)__double_as_longlong(s.Mfp));
-  st_relaxed_u64(&r->w[4], (unsigned long long)s.F);
-  st_release_u64(&r->flag, 1ull);
-}
-__device__ __forceinline__ bool grec_try(const GenRec* r, GState& s) {
-  if (ld_acquire_u64(&r->flag) == 0ull) return false;
-  s.Stp = __longlong_as_double((long long)ld_relaxed_u64(&r->w[0]));
-  s.Sfp = __longlong_as_double((long long)ld_relaxed_u64(&r->w[1]));
-  s.Mtp = __longlong_as_double((long long)ld_relaxed_u64(&r->w[2]));
-  s.Mfp = __longlong_as_double((long long)ld_relaxed_u64(&r->w[3]));
-  s.F = (uint32_t)ld_relaxed_u64(&r->w[4]);
-  return true;
-}
-
 template <typename TargetT>
 __device__ __forceinline__ void gen_terms(const TargetT* __restrict__ target,
                                           const double* __restrict__ weight, uint32_t idx, int mode,
@@ -1141,144 +1114,6 @@ __global__ void __launch_bounds__(256)
   if (threadIdx.x == 0) {
     atomicAdd(&gs->tp_total, ta);
     atomicAdd(&gs->fp_total, tb);
-  }
-}
-
-template <typename TargetT>
-__global__ void __launch_bounds__(kGenBlock)
-    rank_final_general_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
-                              const TargetT* __restrict__ target,
-                              const double* __restrict__ weight, uint32_t n, int mode, GenRec* agg,
-                              GenRec* inc, uint32_t* ticket, const GenScalars* __restrict__ gs,
-                              double* partial) {
-  __shared__ GState s_warp[kGenBlock / kWarp];
-  __shared__ GState s_excl;
-  __shared__ uint32_t s_tile;
-  __shared__ double s_red[kGenBlock / kWarp];
-  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-  __syncthreads();
-  const uint32_t tile = s_tile;
-  const uint32_t i0 = tile * (uint32_t)kGenTile + tid * kGenIpt;
-  const uint32_t cnt = i0 < n ? min((uint32_t)kGenIpt, n - i0) : 0u;
-
-  uint32_t k[kGenIpt];
-  double tp[kGenIpt], fp[kGenIpt];
-  const bool as_payload = gs->payload_bad == 0u;  // uniform: what the ingest kernel stored in vals
-#pragma unroll
-  for (int j = 0; j < kGenIpt; ++j) {
-    if (j < (int)cnt) {
-      k[j] = keys[i0 + j];
-      if (as_payload)
-        gen_terms_payload(vals[i0 + j], mode, tp[j], fp[j]);
-      else
-        gen_terms(target, weight, vals[i0 + j], mode, tp[j], fp[j]);
-    } else {
-      k[j] = 0u;
-      tp[j] = fp[j] = 0.0;
-    }
-  }
-  uint32_t prev = (i0 > 0 && i0 < n) ? keys[i0 - 1] : 0u;
-
-  GState mine = g_identity();
-  uint32_t starts = 0;
-#pragma unroll
-  for (int j = 0; j < kGenIpt; ++j) {
-    if (j < (int)cnt) {
-      const bool st = (j == 0 && i0 == 0) || k[j] != prev;
-      prev = k[j];
-      if (st) {
-        starts |= 1u << j;
-        mine.F = 1;
-        mine.Mtp = mine.Stp;
-        mine.Mfp = mine.Sfp;
-      }
-      mine.Stp += tp[j];
-      mine.Sfp += fp[j];
-    }
-  }
-
-  GState incl = mine;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const GState u = g_shfl_up(incl, o);
-    if (lane >= (unsigned)o) incl = g_combine(u, incl);
-  }
-  if (lane == 31) s_warp[warp] = incl;
-  GState excl = g_shfl_up(incl, 1);
-  if (lane == 0) excl = g_identity();
-  __syncthreads();
-  GState wprefix = g_identity(), tile_agg = g_identity();
-#pragma unroll
-  for (int w = 0; w < kGenBlock / kWarp; ++w) {
-    const GState x = s_warp[w];
-    if (w < (int)warp) wprefix = g_combine(wprefix, x);
-    tile_agg = g_combine(tile_agg, x);
-  }
-  excl = g_combine(wprefix, excl);
-
-  if (warp == 0) {
-    if (lane == 0) grec_publish(agg + tile, tile_agg);
-    GState e = g_identity();
-    for (int64_t base = (int64_t)tile - 1; base >= 0; base -= 32) {
-      const int64_t idx = base - lane;
-      GState r = g_identity();
-      uint32_t incl, need;
-      do {
-        uint32_t st = 2;  // 0 nothing yet, 1 aggregate, 2 inclusive
-        if (idx >= 0) st = grec_try(inc + idx, r) ? 2u : (grec_try(agg + idx, r) ? 1u : 0u);
-        incl = __ballot_sync(kFull, st == 2u);
-        const uint32_t valid = __ballot_sync(kFull, st != 0u);
-        need = incl ? ((2u << (__ffs(incl) - 1)) - 1u) : kFull;
-        if ((valid & need) == need) break;
-      } while (true);
-      const unsigned first = incl ? (unsigned)(__ffs(incl) - 1) : 31u;
-      if (lane > first || idx < 0) r = g_identity();
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        GState u;
-        u.Stp = __shfl_down_sync(kFull, r.Stp, o);
-        u.Sfp = __shfl_down_sync(kFull, r.Sfp, o);
-        u.Mtp = __shfl_down_sync(kFull, r.Mtp, o);
-        u.Mfp = __shfl_down_sync(kFull, r.Mfp, o);
-        u.F = __shfl_down_sync(kFull, r.F, o);
-        if (lane + o < 32) r = g_combine(u, r);
-      }
-      e = g_combine(r, e);
-      if (incl) break;
-    }
-    if (lane == 0) {
-      grec_publish(inc + tile, g_combine(e, tile_agg));
-      s_excl = e;
-    }
-  }
-  __syncthreads();
-  const GState g = g_combine(s_excl, excl);
-
-  double ctp = g.Stp, cfp = g.Sfp, gtp = g.Mtp, gfp = g.Mfp, acc = 0.0;
-  const double ptot = gs->tp_total, ntot = gs->tp_total + gs->fp_total;
-#pragma unroll
-  for (int j = 0; j < kGenIpt; ++j) {
-    if (j < (int)cnt) {
-      if (starts & (1u << j)) {
-        gtp = ctp;
-        gfp = cfp;
-      }
-      if (mode == 0)
-        acc += tp[j] * gfp - fp[j] * gtp;
-      else if (tp[j] != 0.0)
-        acc += (ptot - gtp) / (ntot - gtp - gfp);
-      ctp += tp[j];
-      cfp += fp[j];
-    }
-  }
-  acc = warp_sum(acc);
-  if (lane == 0) s_red[warp] = acc;
-  __syncthreads();
-  if (tid == 0) {
-    double t = 0.0;
-    for (int w = 0; w < kGenBlock / kWarp; ++w) t += s_red[w];
-    partial[tile] = t;
   }
 }
 
@@ -1474,7 +1309,8 @@ __global__ void __launch_bounds__(kGcBlock)
 // area term into partial[0] and the totals of the scan into inc[0] (where
 // rank_reduce_general_kernel looks for them).
 __global__ void __launch_bounds__(1024)
-    gen_chunk_scan_kernel(const GenChunkRec* __restrict__ rec, uint32_t nchunks, double* partial, GenRec* inc) {
+    gen_chunk_scan_kernel(GenChunkRec* rec, uint32_t nchunks, double* partial, GenRec* inc,
+                          int write_excl) {
   __shared__ GState s_warp[32];
   __shared__ double s_sum[32];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -1500,6 +1336,10 @@ __global__ void __launch_bounds__(1024)
     if (i < nchunks) {
       acc += r.A + E.Sfp * r.TP2 - E.Stp * r.FP2;
       if (E.F) acc += E.Mfp * r.TPlead - E.Mtp * r.FPlead;
+      if (write_excl) {  // AUPRC: the integrate sweep starts every chunk from E
+        r.Stp = E.Stp, r.Sfp = E.Sfp, r.Mtp = E.Mtp, r.Mfp = E.Mfp, r.F = E.F;
+        rec[i] = r;
+      }
     }
     carry = g_combine(carry, strip);
     __syncthreads();
@@ -1510,10 +1350,90 @@ __global__ void __launch_bounds__(1024)
   if (tid == 0) {
     double t = 0.0;
     for (int w = 0; w < 32; ++w) t += s_sum[w];
-    partial[0] = t;
+    if (!write_excl) partial[0] = t;
     inc[0].w[0] = (unsigned long long)__double_as_longlong(carry.Stp);
     inc[0].w[1] = (unsigned long long)__double_as_longlong(carry.Sfp);
   }
+}
+
+// General AUPRC, second sweep: with E (the state of everything before the chunk, left in rec[] by
+// the scan) every positive's precision at its tie group's threshold is known exactly:
+//   (P - TPb) / (n - TPb - FPb),  TPb / FPb = sums over everything strictly below the group.
+template <typename TargetT>
+__global__ void __launch_bounds__(kGcBlock)
+    gen_chunk_integrate_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
+                               const TargetT* __restrict__ target, uint32_t n, uint32_t steps_per_chunk,
+                               uint32_t nchunks, const GenScalars* __restrict__ gs,
+                               const GenChunkRec* __restrict__ rec, double* partial) {
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t chunk = blockIdx.x * (kGcBlock / kWarp) + (threadIdx.x >> 5);
+  if (chunk >= nchunks) return;
+  const uint64_t begin64 = (uint64_t)chunk * steps_per_chunk * kGcStep;
+  if (begin64 >= n) return;
+  const uint32_t begin = (uint32_t)begin64;
+  const uint32_t end = (uint32_t)min((uint64_t)n, begin64 + (uint64_t)steps_per_chunk * kGcStep);
+  const bool as_payload = gs->payload_bad == 0u;
+  const double ptot = gs->tp_total, ntot = gs->tp_total + gs->fp_total;
+  GState carry;
+  {
+    const GenChunkRec e = rec[chunk];
+    carry.Stp = e.Stp, carry.Sfp = e.Sfp, carry.Mtp = e.Mtp, carry.Mfp = e.Mfp, carry.F = (uint32_t)e.F;
+  }
+  double acc = 0.0;
+  uint32_t last = begin > 0 ? keys[begin - 1] : 0u;
+  for (uint32_t at = begin; at < end; at += kGcStep) {
+    const uint32_t i0 = at + lane * kGcIpt;
+    const uint32_t cnt = i0 < end ? min((uint32_t)kGcIpt, end - i0) : 0u;
+    uint32_t k[kGcIpt];
+    double tp[kGcIpt], fp[kGcIpt];
+#pragma unroll
+    for (int j = 0; j < kGcIpt; ++j) {
+      k[j] = j < (int)cnt ? keys[i0 + j] : 0u;
+      tp[j] = fp[j] = 0.0;
+      if (j < (int)cnt) {
+        if (as_payload)
+          gen_terms_payload(vals[i0 + j], 1, tp[j], fp[j]);
+        else
+          gen_terms(target, (const double*)nullptr, vals[i0 + j], 1, tp[j], fp[j]);
+      }
+    }
+    uint32_t prev = __shfl_up_sync(kFull, k[kGcIpt - 1], 1);
+    if (lane == 0) prev = last;
+    last = __shfl_sync(kFull, k[kGcIpt - 1], 31);
+    GState mine = g_identity();
+    uint32_t starts = 0;
+#pragma unroll
+    for (int j = 0; j < kGcIpt; ++j) {
+      if (j < (int)cnt) {
+        const bool st = (j == 0 && i0 == 0) || k[j] != prev;
+        prev = k[j];
+        if (st) {
+          starts |= 1u << j;
+          mine.F = 1;
+          mine.Mtp = mine.Stp;
+          mine.Mfp = mine.Sfp;
+        }
+        mine.Stp += tp[j];
+        mine.Sfp += fp[j];
+      }
+    }
+    GState excl, total;
+    g_warp_scan(mine, lane, excl, total);
+    const GState g = g_combine(carry, excl);
+    double ctp = g.Stp, cfp = g.Sfp, gtp = g.Mtp, gfp = g.Mfp;
+#pragma unroll
+    for (int j = 0; j < kGcIpt; ++j) {
+      if (j < (int)cnt) {
+        if (starts & (1u << j)) gtp = ctp, gfp = cfp;
+        if (tp[j] != 0.0) acc += (ptot - gtp) / (ntot - gtp - gfp);
+        ctp += tp[j];
+        cfp += fp[j];
+      }
+    }
+    carry = g_combine(carry, total);
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) partial[chunk] = acc;
 }
 
 struct GenPlan {
@@ -1534,10 +1454,10 @@ GenPlan make_gen_plan(int64_t n) {
   };
   g.off_gzero = o;
   g.off_gs = take(sizeof(GenScalars));
-  g.off_agg = take((size_t)g.tiles * sizeof(GenRec));
-  g.off_inc = take((size_t)g.tiles * sizeof(GenRec));
+  g.off_agg = take(sizeof(GenRec));  // (unused since the sweeps became chunked; kept for layout)
+  g.off_inc = take(sizeof(GenRec));  // totals of the scan, read by the final reduce
   g.gzero_bytes = o - g.off_gzero;
-  g.off_partial = take((size_t)g.tiles * 8);
+  g.off_partial = take((size_t)(g.tiles > (uint32_t)kMaxChunks ? g.tiles : (uint32_t)kMaxChunks) * 8);
   g.off_chunks = take((size_t)kMaxChunks * sizeof(GenChunkRec));
   g.total = o;
   return g;
@@ -1555,7 +1475,6 @@ int binary_rank_general_t(const float* score, const TargetT* target, const doubl
   uint32_t* va = at<uint32_t>(scratch, p.off_vals_a);
   uint32_t* vb = at<uint32_t>(scratch, p.off_vals_b);
   GenScalars* gs = at<GenScalars>(scratch, g.off_gs);
-  GenRec* agg = at<GenRec>(scratch, g.off_agg);
   GenRec* inc = at<GenRec>(scratch, g.off_inc);
   double* partial = at<double>(scratch, g.off_partial);
   uint32_t tiles = 0;
@@ -1571,23 +1490,29 @@ int binary_rank_general_t(const float* score, const TargetT* target, const doubl
     if (rc) return rc;
     rc = run_passes(p, scratch, ka, kb, ka, va, vb, va, st);  // sorted pairs end in (ka, va)
     if (rc) return rc;
-    if (mode == 0) {
-      // AUROC: linear in the carried prefix -> warp-private chunks + one scan, no look-back
+    {
+      // AUROC is linear in the carried prefix: warp-private chunks + one scan CTA, no look-back.
+      // AUPRC is not (a ratio of prefix sums): the same count sweep, the scan leaves every chunk's
+      // starting state in place of its record, and a second sweep integrates.
       const ChunkGeom cg = gen_chunk_geom(p.n, sms);
+      const uint32_t grid = (cg.nchunks + kGcBlock / kWarp - 1) / (kGcBlock / kWarp);
       GenChunkRec* crec = at<GenChunkRec>(scratch, g.off_chunks);
       {
         TE_PROF("gen_chunk_sweep", st);
-        gen_chunk_kernel<TargetT><<<(cg.nchunks + kGcBlock / kWarp - 1) / (kGcBlock / kWarp), kGcBlock, 0, st>>>(
-            ka, va, target, weight, p.n, cg.steps_per_chunk, cg.nchunks, gs, crec);
+        gen_chunk_kernel<TargetT><<<grid, kGcBlock, 0, st>>>(ka, va, target, weight, p.n, cg.steps_per_chunk,
+                                                             cg.nchunks, gs, crec);
       }
-      TE_PROF("gen_chunk_scan", st);
-      gen_chunk_scan_kernel<<<1, 1024, 0, st>>>(crec, cg.nchunks, partial, inc);
+      {
+        TE_PROF("gen_chunk_scan", st);
+        gen_chunk_scan_kernel<<<1, 1024, 0, st>>>(crec, cg.nchunks, partial, inc, mode == 0 ? 0 : 1);
+      }
       tiles = 1;  // what the reduce below sums over
-    } else {
-      TE_PROF("rank_final_general", st);
-      rank_final_general_kernel<TargetT><<<tiles, kGenBlock, 0, st>>>(
-          ka, va, target, weight, p.n, mode, agg, inc, at<uint32_t>(scratch, p.off_ticket) + 4, gs,
-          partial);
+      if (mode != 0) {
+        TE_PROF("gen_chunk_integrate", st);
+        gen_chunk_integrate_kernel<TargetT><<<grid, kGcBlock, 0, st>>>(ka, va, target, p.n, cg.steps_per_chunk,
+                                                                       cg.nchunks, gs, crec, partial);
+        tiles = cg.nchunks;
+      }
     }
     TE_LAUNCH_CHECK();
   }
