@@ -798,7 +798,7 @@ struct RankPlan {
   size_t off_keys_a, off_keys_b, off_vals_a, off_vals_b;
   size_t off_zero;      // start of the region that must be zero before launch
   size_t off_hist;      // 4*256 u32
-  size_t off_ticket;    // 8 u32
+  size_t off_ticket;    // 8 u32: words 0..3 = "pass p is a no-op" flags (the name is historical)
   size_t off_hot;       // 8 u32
   size_t off_scal;      // RankScalars
   size_t off_lookback;  // look-back counts of the first pass: sort_tiles * 256 u32 (zeroed by memset)

@@ -1,10 +1,12 @@
 // Building blocks of the exact ranking path (K1/K2): single-sweep LSD radix sort.
 //
-// One pass = one kernel: every CTA takes a tile of keys (ticket order), ranks them by the
-// current 8-bit digit with warp-private shared-memory digit counters, learns where its digit
-// runs start in the output through a decoupled look-back chain over the preceding tiles
-// (one chain per digit), and writes the tile out through shared memory so that every digit run
-// leaves as a contiguous burst.  The four digit histograms are produced up front by the ingest
+// One pass = one kernel: every CTA takes a tile of keys (tile = block index), ranks them by the
+// current 8-bit digit with half-warp-private shared-memory tables (peer mask + running count in
+// one word), learns where its digit runs start in the output through a two-level decoupled
+// look-back over the preceding tiles, and writes the tile out through shared memory so that
+// every digit run leaves as a contiguous burst.  grid.y batches independent sorts of equal length
+// (one-vs-rest classes); the same kernel with "destination rank" as the digit is the partition
+// pass of the distributed sample sort (optionally storing straight into peer GPUs' memory).  The four digit histograms are produced up front by the ingest
 // kernel, so each pass reads and writes every record exactly once (2*r bytes per record, the
 // "bytes moved per sort pass" of BASELINE.json).
 #pragma once
