@@ -6,8 +6,11 @@
 Primary workload (BASELINE.json metric, configs[3]): exact BinaryAUROC over N = 2^30 synthetic
 float32 scores + int64 {0,1} labels, rank-sharded over the GPUs (strong scaling: the total is
 fixed, each of N ranks holds 2^30 / N).  One "step" = one full compute of the metric over the
-resident scores.  Secondary (configs[1], reported under "secondary"): MulticlassConfusionMatrix
-update, C = 1000, 2^28 label pairs on one GPU, as GB/s against the HBM roofline.
+resident scores.  Also in the line, at 1 GPU: "secondary" (configs[1]: MulticlassConfusionMatrix
+update, C = 1000, 2^28 label pairs, GB/s against the HBM roofline), "secondary_binned" (configs[2]:
+10k-threshold binned counting over the same 2^30 scores) and "secondary_ovr" (configs[4] shape:
+one-vs-rest MulticlassAUROC, C = 1000, N = 2^20); at N GPUs: "secondary_binned" = binned update +
+counter all-reduce through toolkit.sync_and_compute.
 
 Prints ONE JSON line on rank 0 (see the task contract): value = device-timed whole-job
 throughput with inputs resident in HBM; e2e = same metric through the public functional API
