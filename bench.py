@@ -250,7 +250,9 @@ def run_ours(args) -> dict:
             "algorithmic_bytes_per_launch": 8 * sorted_n,
             "step_share": round(k["total_ms"] / (ms_total), 4),
         }
-    step_bytes = 52.0 * n_local  # 16 ingest + 4 passes * 8 + 4 fused scan
+    # bytes the structure that ran actually moves per score: counting-stage path
+    # 16 ingest + 2 passes * 8 + 4 counting = 36; full sort 16 + 4 * 8 + 4 sweep = 52
+    step_bytes = (36.0 if "leaf_count" in kernels else 52.0) * n_local
     kernel_table = {
         name: {"avg_ms": round(v["total_ms"] / max(v["launches"], 1), 4), "launches_per_step": v["launches"] / args.steps}
         for name, v in kernels.items()

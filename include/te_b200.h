@@ -182,8 +182,19 @@ enum { TE_DTYPE_I64 = 0, TE_DTYPE_I32 = 1, TE_DTYPE_U8 = 2, TE_DTYPE_F32 = 3, TE
  * general entry point instead. */
 enum {
   TE_RANK_FLAG_BAD_LABEL = 1,      /* a target is not exactly 0 or 1 (soft labels)   */
-  TE_RANK_FLAG_NEGATIVE_SCORE = 2  /* a score has its sign bit set (other than -0.0) */
+  TE_RANK_FLAG_NEGATIVE_SCORE = 2, /* a score has its sign bit set (other than -0.0) */
+  TE_RANK_FLAG_WIDE_SCORE = 4      /* TE_RANK_COUNTING only: a score is >= 2.0 (its packed key
+                                      needs 32 bits); call again with TE_RANK_SORT              */
 };
+
+/* How te_binary_auroc orders the keys.
+ *  TE_RANK_SORT     : four 8-bit radix passes (a full sort) + one fused scan/integrate sweep;
+ *  TE_RANK_COUNTING : two 8-bit passes order the keys by their top 16 bits, then every segment of
+ *                     2^15 consecutive key values is counted into a shared-memory histogram and
+ *                     integrated from the counts (36 instead of 52 bytes per score).  Needs every
+ *                     score < 2.0, else out[4] carries TE_RANK_FLAG_WIDE_SCORE;
+ *  TE_RANK_AUTO     : TE_RANK_COUNTING from 2^24 scores on (env TE_B200_LEAF_MIN_N), else TE_RANK_SORT. */
+enum { TE_RANK_AUTO = 0, TE_RANK_SORT = 1, TE_RANK_COUNTING = 2 };
 
 TE_API size_t te_binary_rank_scratch_bytes(int64_t n);
 
@@ -193,6 +204,11 @@ TE_API size_t te_binary_rank_scratch_bytes(int64_t n);
  * [4] TE_RANK_FLAG_* (non-zero: [0..3] are not valid).  n <= 2^31 - 1. */
 TE_API int te_binary_auroc(const float* score, const void* target, int32_t target_dtype, int64_t n,
                            double* out, void* scratch, size_t scratch_bytes, void* stream);
+
+/* te_binary_auroc with the structure chosen by the caller (te_binary_auroc itself = TE_RANK_AUTO). */
+TE_API int te_binary_auroc_variant(const float* score, const void* target, int32_t target_dtype,
+                                   int64_t n, double* out, void* scratch, size_t scratch_bytes,
+                                   int32_t variant, void* stream);
 
 /* Same contract for AUPRC (average precision, step integration): out[0] = AP, -0.0 when there
  * are no positives (precision_recall_curve.py:227-229); out[3] = sum of per-positive precisions.

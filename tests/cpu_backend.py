@@ -113,7 +113,7 @@ def _exact_2u(x, y):
     return int(np.sum(pos.astype(object) * (2 * below.astype(object) + neg.astype(object))))
 
 
-def binary_auroc_packed(score, target):
+def binary_auroc_packed(score, target, variant=0):
     f = _flags(score, target)
     out = torch.zeros(8, dtype=torch.float64)
     out[4] = f

@@ -15,7 +15,8 @@ TE_OK = 0
 TE_CM_AUTO, TE_CM_GLOBAL64, TE_CM_GLOBAL32, TE_CM_SMEM_REPL, TE_CM_SMEM, TE_CM_CLUSTER, TE_CM_BUCKETED = range(7)
 TE_BINNED_AUROC, TE_BINNED_AUPRC = 0, 1
 TE_DTYPE_I64, TE_DTYPE_I32, TE_DTYPE_U8, TE_DTYPE_F32, TE_DTYPE_F64 = range(5)
-TE_RANK_FLAG_BAD_LABEL, TE_RANK_FLAG_NEGATIVE_SCORE = 1, 2
+TE_RANK_FLAG_BAD_LABEL, TE_RANK_FLAG_NEGATIVE_SCORE, TE_RANK_FLAG_WIDE_SCORE = 1, 2, 4
+TE_RANK_AUTO, TE_RANK_SORT, TE_RANK_COUNTING = 0, 1, 2
 
 _vp, _i32, _i64, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_size_t
 
@@ -40,6 +41,7 @@ SIGNATURES = {
     "te_binned_integrate": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),
     "te_binary_rank_scratch_bytes": (_sz, [_i64]),
     "te_binary_auroc": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp, _sz, _vp]),
+    "te_binary_auroc_variant": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp, _sz, _i32, _vp]),
     "te_binary_auprc": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp, _sz, _vp]),
     "te_binary_rank_general_scratch_bytes": (_sz, [_i64]),
     "te_binary_auroc_general": (C.c_int, [_vp, _vp, _i32, _vp, _i64, _vp, _vp, _sz, _vp]),

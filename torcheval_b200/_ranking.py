@@ -97,6 +97,9 @@ def _binary_auroc_row(x: torch.Tensor, t: torch.Tensor, w: Optional[torch.Tensor
     if w is None and t.dtype in ops._DTYPE_CODE:
         out = ops.binary_auroc_packed(x, t)
         flags = int(out[4].item())  # the one host read of this path
+        if flags == N.TE_RANK_FLAG_WIDE_SCORE:  # scores >= 2.0: the counting stage does not apply, the full sort does
+            out = ops.binary_auroc_packed(x, t, N.TE_RANK_SORT)
+            flags = int(out[4].item())
         if flags == 0:
             return out[0].clone()
     return ops.binary_auroc_general(x, t, w)[0].clone()

@@ -19,6 +19,7 @@
 #include <stdlib.h>
 
 #include "rank_sort.cuh"
+#include "rank_leaf.cuh"
 #include "prof.cuh"
 
 namespace te {
@@ -30,7 +31,7 @@ namespace {
 constexpr int kIngestBlock = 1024;
 constexpr size_t kIngestSmem = (size_t)4 * kRadix * kWarp * sizeof(uint32_t);  // 128 KB
 
-enum IngestMode { kPacked = 0, kIndexed = 1, kRawKeys = 2 };
+enum IngestMode { kPacked = 0, kIndexed = 1, kRawKeys = 2, kScoreHist = 3 };  // kScoreHist: histograms of the scores' keys only, nothing is written
 
 struct RankScalars {            // lives in the zeroed part of the scratch buffer
   unsigned long long positives; // #label==1 (packed mode)
@@ -38,45 +39,9 @@ struct RankScalars {            // lives in the zeroed part of the scratch buffe
   uint32_t pad;
 };
 
-template <typename T>
-struct LabelOf;
-template <>
-struct LabelOf<long long> {
-  static __device__ __forceinline__ uint32_t get(long long t, uint32_t& bad) {
-    bad |= ((unsigned long long)t > 1ull);
-    return (uint32_t)t & 1u;
-  }
-};
-template <>
-struct LabelOf<int> {
-  static __device__ __forceinline__ uint32_t get(int t, uint32_t& bad) {
-    bad |= ((unsigned)t > 1u);
-    return (uint32_t)t & 1u;
-  }
-};
-template <>
-struct LabelOf<unsigned char> {
-  static __device__ __forceinline__ uint32_t get(unsigned char t, uint32_t& bad) {
-    bad |= (t > 1);
-    return t & 1u;
-  }
-};
-template <>
-struct LabelOf<float> {
-  static __device__ __forceinline__ uint32_t get(float t, uint32_t& bad) {
-    bad |= !(t == 0.f || t == 1.f);
-    return t == 1.f ? 1u : 0u;
-  }
-};
-template <>
-struct LabelOf<double> {
-  static __device__ __forceinline__ uint32_t get(double t, uint32_t& bad) {
-    bad |= !(t == 0.0 || t == 1.0);
-    return t == 1.0 ? 1u : 0u;
-  }
-};
-
-template <int MODE, typename TargetT>
+// LEAF: the histograms the two-pass + counting-stage path needs (rank_leaf.cuh): digits at bits
+// 15..22 and 23..30 instead of the four bytes, and a flag if any key uses bit 31 (score >= 2.0).
+template <int MODE, typename TargetT, bool LEAF = false>
 __global__ void __launch_bounds__(kIngestBlock, 1)
     rank_ingest_kernel(const float* __restrict__ score, const TargetT* __restrict__ target,
                        const uint32_t* __restrict__ raw_keys, uint32_t n, bool vec_ok,
@@ -88,10 +53,11 @@ __global__ void __launch_bounds__(kIngestBlock, 1)
   // which spares the final sweep a random gather by index
   const bool as_payload = MODE == kIndexed && payload_bad && *payload_bad == 0u;
   const unsigned tid = threadIdx.x, lane = tid & 31;
-  for (int i = tid; i < 4 * kRadix * kWarp; i += kIngestBlock) sh[i] = 0;
+  constexpr int kHists = LEAF ? 2 : 4;
+  for (int i = tid; i < kHists * kRadix * kWarp; i += kIngestBlock) sh[i] = 0;
   __syncthreads();
 
-  uint32_t npos = 0, bad_label = 0, neg_score = 0;
+  uint32_t npos = 0, bad_label = 0, neg_score = 0, wide = 0;
   const uint32_t ngroups = (n + 3) / 4;
   const uint32_t stride = gridDim.x * kIngestBlock;
   for (uint32_t g = blockIdx.x * kIngestBlock + tid; g < ngroups; g += stride) {
@@ -151,11 +117,20 @@ __global__ void __launch_bounds__(kIngestBlock, 1)
           k[j] = (b << 1) | lab[j];
           if (j < (int)cnt) npos += lab[j];
         }
+      } else if (MODE == kScoreHist) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint32_t b = __float_as_uint(x[j]);
+          if (b == 0x80000000u) b = 0u;
+          neg_score |= b >> 31;
+          k[j] = b << 1;
+        }
       } else {
 #pragma unroll
         for (int j = 0; j < 4; ++j) k[j] = orderable_f32(x[j]);
       }
-      if (cnt == 4) {
+      if (MODE == kScoreHist) {
+      } else if (cnt == 4) {
         st_stream_v4(keys_out + i0, make_int4((int)k[0], (int)k[1], (int)k[2], (int)k[3]));
         if (MODE == kIndexed) {
           if (as_payload)
@@ -175,25 +150,27 @@ __global__ void __launch_bounds__(kIngestBlock, 1)
     for (int j = 0; j < 4; ++j) {
       if (j < (int)cnt) {
 #pragma unroll
-        for (int p = 0; p < 4; ++p) {
-          const uint32_t d = (k[j] >> (8 * p)) & 0xffu;
+        for (int p = 0; p < kHists; ++p) {
+          const uint32_t d = (k[j] >> (LEAF ? kLeafBits + 8 * p : 8 * p)) & 0xffu;
           atomicAdd(sh + ((p << 8) + d) * kWarp + lane, 1u);
         }
+        if (LEAF) wide |= k[j] >> 31;
       }
     }
   }
   __syncthreads();
-  {
+  if (tid < kHists * kRadix) {
     uint32_t s = 0;  // thread t owns (pass, digit) = t
 #pragma unroll
     for (int r = 0; r < kWarp; ++r) s += sh[tid * kWarp + ((r + tid) & 31)];
     if (s) atomicAdd(ghist + tid, s);
   }
+  if (LEAF && __any_sync(kFull, wide != 0) && lane == 0) atomicOr(&scal->flags, (uint32_t)TE_RANK_FLAG_WIDE_SCORE);
   if (MODE == kRawKeys) {
     npos = warp_sum(npos);
     if (lane == 0 && npos) atomicAdd(&scal->positives, (unsigned long long)npos);
   }
-  if (MODE == kPacked) {
+  if (MODE == kPacked || MODE == kScoreHist) {
     npos = warp_sum(npos);
     const uint32_t anybad = __any_sync(kFull, bad_label != 0);
     const uint32_t anyneg = __any_sync(kFull, neg_score != 0);
@@ -808,10 +785,21 @@ struct RankPlan {
   size_t off_starts;    // exclusive count of tie-group starts per chunk (+ total): PR curve
   size_t zero_bytes;
   size_t off_partial;
+  // counting-stage path (rank_leaf.cuh)
+  uint32_t leaf_piece, leaf_max_items, leaf_max_slabs;
+  size_t off_leaf_hdr, off_seg_stats;  // inside the zeroed region
+  size_t off_seg_start, off_leaf_items, off_leaf_multi, off_leaf_slabs;
   size_t total;
 };
 
-RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final) {
+inline uint32_t leaf_piece_of(int64_t n) {
+  uint64_t m = ((uint64_t)n / 1024 + 4095) / 4096 * 4096;
+  if (m < kLeafMinPiece) m = kLeafMinPiece;
+  if (m > kLeafMaxPiece) m = kLeafMaxPiece;
+  return (uint32_t)m;
+}
+
+RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final, bool with_leaf = false) {
   RankPlan p{};
   p.n = (uint32_t)n64;
   p.sort_block = sort_block_from_env();
@@ -841,9 +829,18 @@ RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final)
   p.off_agg = take(with_final ? (size_t)kMaxChunks * sizeof(ChunkRec) : 0);
   p.off_inc = take(with_final ? (size_t)kMaxChunks * sizeof(FState) : 0);
   p.off_starts = take(with_final ? (size_t)(kMaxChunks + 1) * 4 : 0);
+  p.leaf_piece = leaf_piece_of(n64);
+  p.leaf_max_items = with_leaf ? (uint32_t)(kLeafSegs + (uint64_t)n64 / p.leaf_piece + 1) : 0;
+  p.leaf_max_slabs = with_leaf ? (uint32_t)(2 * ((uint64_t)n64 / p.leaf_piece) + 2) : 0;
+  p.off_leaf_hdr = take(with_leaf ? sizeof(LeafHeader) : 0);
+  p.off_seg_stats = take(with_leaf ? (size_t)kLeafSegs * sizeof(SegStat) : 0);
   p.zero_bytes = o - p.off_zero;
   p.off_lookback_rest = take((size_t)3 * p.sort_tiles * kRadix * 4);
   p.off_partial = take(with_final ? (size_t)kMaxChunks * 8 : 0);
+  p.off_seg_start = take(with_leaf ? (size_t)(kLeafSegs + 1) * 4 : 0);
+  p.off_leaf_items = take((size_t)p.leaf_max_items * sizeof(LeafItem));
+  p.off_leaf_multi = take(with_leaf ? (size_t)kLeafSegs * sizeof(LeafMulti) : 0);
+  p.off_leaf_slabs = take((size_t)p.leaf_max_slabs * kLeafBins * 4);
   p.total = o;
   return p;
 }
@@ -853,12 +850,17 @@ T* at(void* base, size_t off) {
   return reinterpret_cast<T*>(static_cast<char*>(base) + off);
 }
 
+struct RankPlan;
+int launch_fused_first_pass_dtype(const RankPlan& p, void* scratch, const float* score, const void* target,
+                                  int32_t dt, uint32_t* keys_out, cudaStream_t st);
+
 // nb > 1: nb independent sorts of the same length whose scratch blocks (and key arrays) lie
 // bstride bytes apart, done by the same launches (grid.y = nb).
 int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t* k_x, uint32_t* k_y,
                const uint32_t* v_in0, uint32_t* v_x, uint32_t* v_y, cudaStream_t st, int nb = 1,
-               size_t bstride = 0) {
-  // 4 passes: in0 -> x -> y -> x -> y
+               size_t bstride = 0, int npasses = 4, int shift0 = 0, const float* fused_score = nullptr,
+               const void* fused_target = nullptr, int32_t fused_dt = 0) {
+  // npasses passes on the digits at bits shift0 + 8 * pass: in0 -> x -> y -> x -> y
   uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
   uint32_t* hot = hot_digits_from_env() ? at<uint32_t>(scratch, p.off_hot) : nullptr;
   // words 0..3 of the (zeroed) ticket block: "pass p is a no-op" flags, set by digit_scan_kernel
@@ -870,14 +872,14 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   };
   {
     TE_PROF("digit_scan", st);
-    digit_scan_kernel<<<dim3(1, nb), 1024, 0, st>>>(hist, 4, hot, bstride, skip);
+    digit_scan_kernel<<<dim3(1, nb), 1024, 0, st>>>(hist, npasses, hot, bstride, skip);
   }
   TE_LAUNCH_CHECK();
   const int block = p.sort_block;
   const size_t smem = block == 256 ? onesweep_smem_bytes<uint32_t, 256>() : onesweep_smem_bytes<uint32_t, 512>();
   using PassFn = void (*)(const uint32_t*, uint32_t*, const uint32_t*, uint32_t*, uint32_t,
                           const RadixDigit, const uint32_t*, uint32_t*, uint32_t*, const PeerPtrs,
-                          const uint32_t*, uint32_t*, size_t, const uint32_t*);
+                          const uint32_t*, uint32_t*, size_t, const uint32_t*, const ArraySrc<uint32_t>);
   PassFn fn = nullptr;
   if (v_in0)
     fn = block == 256 ? onesweep_pass_kernel<uint32_t, true, 256, RadixDigit>
@@ -902,17 +904,23 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
                             : onesweep_pass_kernel<uint32_t, false, 512, RadixDigit, kSortIptDefault, false, true>;
     TE_CUDA_TRY(cudaFuncSetAttribute(fn_first, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_used));
   }
-  for (int pass = 0; pass < 4; ++pass) {
+  for (int pass = 0; pass < npasses; ++pass) {
     uint32_t* kout = (pass & 1) ? k_y : k_x;
     uint32_t* vout = (pass & 1) ? v_y : v_x;
     uint32_t* lbp = lb_counts(pass);
     uint32_t* gpp = at<uint32_t>(scratch, p.off_gprefix) + (size_t)pass * lb_groups * kRadix;
+    if (pass == 0 && fused_score) {  // (score, target) -> first partition, no packed copy in between
+      const int rc = launch_fused_first_pass_dtype(p, scratch, fused_score, fused_target, fused_dt, kout, st);
+      if (rc) return rc;
+      kin = kout;
+      continue;
+    }
     TE_PROF(v_in0 ? "onesweep_pass_pairs" : (pass == 0 && fn_first != fn ? "onesweep_pass_keys_first" : "onesweep_pass_keys"), st);
-    (pass == 0 ? fn_first : fn)<<<dim3(p.sort_tiles, nb), block, smem_used, st>>>(kin, kout, vin, vout, p.n, RadixDigit{8 * pass},
+    (pass == 0 ? fn_first : fn)<<<dim3(p.sort_tiles, nb), block, smem_used, st>>>(kin, kout, vin, vout, p.n, RadixDigit{shift0 + 8 * pass},
                                                hist + pass * kRadix, lbp, gpp, PeerPtrs{},
                                                hot ? hot + 2 * pass : nullptr,
-                                               pass < 3 ? lb_counts(pass + 1) : nullptr, bstride,
-                                               skip ? skip + pass : nullptr);
+                                               pass + 1 < npasses ? lb_counts(pass + 1) : nullptr, bstride,
+                                               skip ? skip + pass : nullptr, ArraySrc<uint32_t>{});
     TE_LAUNCH_CHECK();
     kin = kout;
     vin = vout;
@@ -920,11 +928,11 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   return TE_OK;
 }
 
-template <int MODE, typename TargetT>
+template <int MODE, typename TargetT, bool LEAF = false>
 int launch_ingest(const float* score, const void* target, const uint32_t* raw, const RankPlan& p,
                   uint32_t* keys_out, uint32_t* vals_out, void* scratch, int sms, cudaStream_t st,
                   const uint32_t* payload_bad = nullptr) {
-  auto kern = rank_ingest_kernel<MODE, TargetT>;
+  auto kern = rank_ingest_kernel<MODE, TargetT, LEAF>;
   TE_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)kIngestSmem));
   const uint32_t ngroups = (p.n + 3) / 4;
@@ -933,7 +941,8 @@ int launch_ingest(const float* score, const void* target, const uint32_t* raw, c
   if (grid < 1) grid = 1;
   uintptr_t a = (uintptr_t)score | (uintptr_t)target | (uintptr_t)raw;
   const bool vec_ok = (a & 15) == 0;
-  TE_PROF(MODE == kPacked ? "rank_ingest_packed" : (MODE == kIndexed ? "rank_ingest_indexed" : "rank_hist_keys"), st);
+  TE_PROF(MODE == kPacked ? (LEAF ? "rank_ingest_packed2" : "rank_ingest_packed")
+                          : (MODE == kIndexed ? "rank_ingest_indexed" : (MODE == kScoreHist ? "rank_score_hist" : "rank_hist_keys")), st);
   kern<<<grid, kIngestBlock, kIngestSmem, st>>>(score, (const TargetT*)target, raw, p.n, vec_ok,
                                                  keys_out, vals_out, at<uint32_t>(scratch, p.off_hist),
                                                  at<RankScalars>(scratch, p.off_scal), payload_bad);
@@ -941,21 +950,21 @@ int launch_ingest(const float* score, const void* target, const uint32_t* raw, c
   return TE_OK;
 }
 
-template <int MODE>
+template <int MODE, bool LEAF = false>
 int launch_ingest_dtype(const float* score, const void* target, int32_t dt, const RankPlan& p,
                         uint32_t* keys_out, uint32_t* vals_out, void* scratch, int sms,
                         cudaStream_t st) {
   switch (dt) {
     case TE_DTYPE_I64:
-      return launch_ingest<MODE, long long>(score, target, nullptr, p, keys_out, vals_out, scratch, sms, st);
+      return launch_ingest<MODE, long long, LEAF>(score, target, nullptr, p, keys_out, vals_out, scratch, sms, st);
     case TE_DTYPE_I32:
-      return launch_ingest<MODE, int>(score, target, nullptr, p, keys_out, vals_out, scratch, sms, st);
+      return launch_ingest<MODE, int, LEAF>(score, target, nullptr, p, keys_out, vals_out, scratch, sms, st);
     case TE_DTYPE_U8:
-      return launch_ingest<MODE, unsigned char>(score, target, nullptr, p, keys_out, vals_out, scratch, sms, st);
+      return launch_ingest<MODE, unsigned char, LEAF>(score, target, nullptr, p, keys_out, vals_out, scratch, sms, st);
     case TE_DTYPE_F32:
-      return launch_ingest<MODE, float>(score, target, nullptr, p, keys_out, vals_out, scratch, sms, st);
+      return launch_ingest<MODE, float, LEAF>(score, target, nullptr, p, keys_out, vals_out, scratch, sms, st);
     case TE_DTYPE_F64:
-      return launch_ingest<MODE, double>(score, target, nullptr, p, keys_out, vals_out, scratch, sms, st);
+      return launch_ingest<MODE, double, LEAF>(score, target, nullptr, p, keys_out, vals_out, scratch, sms, st);
     default:
       return TE_ERR_INVALID_ARGUMENT;
   }
@@ -1002,9 +1011,132 @@ int finish_packed(const RankPlan& p, const uint32_t* ka, int mode, double* out, 
   return TE_OK;
 }
 
+// Counting stage over keys ordered by their top 16 bits (rank_leaf.cuh): segment bounds -> work
+// list -> histogram pieces -> merge of the segments counted in several pieces -> combine.
+int finish_leaf(const RankPlan& p, const uint32_t* keys, double* out, void* scratch, int sms, cudaStream_t st) {
+  uint32_t* seg_start = at<uint32_t>(scratch, p.off_seg_start);
+  LeafItem* items = at<LeafItem>(scratch, p.off_leaf_items);
+  LeafMulti* multi = at<LeafMulti>(scratch, p.off_leaf_multi);
+  LeafHeader* hdr = at<LeafHeader>(scratch, p.off_leaf_hdr);
+  SegStat* stats = at<SegStat>(scratch, p.off_seg_stats);
+  uint32_t* slabs = at<uint32_t>(scratch, p.off_leaf_slabs);
+  {
+    TE_PROF("leaf_seg_bounds", st);
+    leaf_seg_bounds_kernel<<<(kLeafSegs + 1 + 255) / 256, 256, 0, st>>>(keys, p.n, seg_start);
+  }
+  {
+    TE_PROF("leaf_plan", st);
+    leaf_plan_kernel<<<1, 1024, 0, st>>>(seg_start, p.leaf_piece, p.leaf_max_items, p.leaf_max_slabs, items, multi, hdr);
+  }
+  TE_LAUNCH_CHECK();
+  TE_CUDA_TRY(cudaFuncSetAttribute(leaf_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLeafSmem));
+  {
+    TE_PROF("leaf_count", st);
+    leaf_count_kernel<<<sms, kLeafBlock, kLeafSmem, st>>>(keys, items, hdr, stats, slabs);
+  }
+  {
+    TE_PROF("leaf_merge", st);
+    leaf_merge_kernel<<<sms, kLeafBlock, 0, st>>>(multi, hdr, slabs, stats);
+  }
+  {
+    TE_PROF("leaf_combine", st);
+    leaf_combine_kernel<<<1, 1024, 0, st>>>(stats, p.n, &at<RankScalars>(scratch, p.off_scal)->flags, out);
+  }
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+// Which structure te_binary_auroc uses: TE_RANK_AUTO picks the counting-stage path from
+// TE_B200_LEAF_MIN_N scores on (the fixed cost of walking up to 65 536 segment histograms only
+// pays off for large inputs).
+inline int64_t leaf_min_n_from_env() {
+  static const int64_t v = [] {
+    const char* e = getenv("TE_B200_LEAF_MIN_N");
+    return e ? atoll(e) : (int64_t)1 << 24;
+  }();
+  return v;
+}
+
+inline bool fused_ingest_from_env() {
+  static const bool b = [] {
+    const char* e = getenv("TE_B200_FUSED_INGEST");
+    return e ? atoi(e) != 0 : false;  // measured a wash (profiles/r02_leaf_bench_v2.txt): the pass is not
+                                      // HBM-bound, but tripling what its load phase reads costs what the
+                                      // separate pack kernel did
+  }();
+  return b;
+}
+
+// First pass of the counting-stage path with the ingest fused in: reads (score, target), packs,
+// partitions by key bits 15..22 in arrival order.  The digit histograms come from a scores-only
+// histogram kernel (4 bytes per score) instead of the pack kernel (16 bytes per score).
+template <typename TargetT>
+int launch_fused_first_pass(const RankPlan& p, void* scratch, const float* score, const TargetT* target,
+                            uint32_t* keys_out, cudaStream_t st) {
+  if (p.sort_block != 512 || p.sort_ipt != kSortIptDefault) return TE_ERR_UNSUPPORTED;
+  using Src = PackSrc<TargetT>;
+  auto fn = onesweep_pass_kernel<uint32_t, false, 512, RadixDigit, kSortIptDefault, false, true, Src>;
+  const size_t smem = onesweep_smem_bytes<uint32_t, 512>();
+  TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
+  const size_t lb_groups = (p.sort_tiles + kLbGroup - 1) / kLbGroup;
+  Src src;
+  src.score = score, src.target = target, src.flags = &at<RankScalars>(scratch, p.off_scal)->flags;
+  src.vec_ok = (((uintptr_t)score | (uintptr_t)target) & 15) == 0;
+  TE_PROF("onesweep_pass_fused_ingest", st);
+  fn<<<dim3(p.sort_tiles, 1), 512, smem, st>>>(nullptr, keys_out, nullptr, nullptr, p.n, RadixDigit{kLeafBits}, hist,
+                                              at<uint32_t>(scratch, p.off_lookback), at<uint32_t>(scratch, p.off_gprefix),
+                                              PeerPtrs{}, nullptr, at<uint32_t>(scratch, p.off_lookback_rest), 0,
+                                              skip_passes_from_env() ? at<uint32_t>(scratch, p.off_ticket) : nullptr, src);
+  TE_LAUNCH_CHECK();
+  (void)lb_groups;
+  return TE_OK;
+}
+
+int launch_fused_first_pass_dtype(const RankPlan& p, void* scratch, const float* score, const void* target,
+                                  int32_t dt, uint32_t* keys_out, cudaStream_t st) {
+  switch (dt) {
+    case TE_DTYPE_I64: return launch_fused_first_pass(p, scratch, score, (const long long*)target, keys_out, st);
+    case TE_DTYPE_I32: return launch_fused_first_pass(p, scratch, score, (const int*)target, keys_out, st);
+    case TE_DTYPE_U8: return launch_fused_first_pass(p, scratch, score, (const unsigned char*)target, keys_out, st);
+    case TE_DTYPE_F32: return launch_fused_first_pass(p, scratch, score, (const float*)target, keys_out, st);
+    case TE_DTYPE_F64: return launch_fused_first_pass(p, scratch, score, (const double*)target, keys_out, st);
+    default: return TE_ERR_INVALID_ARGUMENT;
+  }
+}
+
+int binary_auroc_leaf(const float* score, const void* target, int32_t dt, int64_t n, double* out, void* scratch,
+                      size_t scratch_bytes, cudaStream_t st) {
+  const RankPlan p = make_plan(n, false, true, true, true);
+  if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
+  uint32_t* ka = at<uint32_t>(scratch, p.off_keys_a);
+  uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
+  if (n > 0 && fused_ingest_from_env() && p.sort_block == 512 && p.sort_ipt == kSortIptDefault) {
+    if (dt < TE_DTYPE_I64 || dt > TE_DTYPE_F64) return TE_ERR_INVALID_ARGUMENT;
+    // scores -> histograms; (score, target) -> b (fused ingest + pass on bits 15..22); b -> a
+    int rc = launch_ingest<kScoreHist, long long, true>(score, nullptr, nullptr, p, nullptr, nullptr, scratch, sms, st);
+    if (rc) return rc;
+    rc = run_passes(p, scratch, nullptr, kb, ka, nullptr, nullptr, nullptr, st, 1, 0, 2, kLeafBits, score, target, dt);
+    if (rc) return rc;
+  } else if (n > 0) {
+    int rc = launch_ingest_dtype<kPacked, true>(score, target, dt, p, ka, nullptr, scratch, sms, st);
+    if (rc) return rc;
+    // a -> b -> a: keys ordered by bits 15..30 end in `ka`
+    rc = run_passes(p, scratch, ka, kb, ka, nullptr, nullptr, nullptr, st, 1, 0, 2, kLeafBits);
+    if (rc) return rc;
+  }
+  return finish_leaf(p, ka, out, scratch, sms, st);
+}
+
 int binary_rank_packed(const float* score, const void* target, int32_t dt, int64_t n, int mode,
-                       double* out, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+                       double* out, void* scratch, size_t scratch_bytes, cudaStream_t st,
+                       int variant = TE_RANK_AUTO) {
   if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  if (mode == 0 && (variant == TE_RANK_COUNTING || (variant == TE_RANK_AUTO && n >= leaf_min_n_from_env())))
+    return binary_auroc_leaf(score, target, dt, n, out, scratch, scratch_bytes, st);
   const RankPlan p = make_plan(n, false, true, true);
   if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
   int sms = 0;
@@ -1830,7 +1962,7 @@ using namespace te;
 
 extern "C" size_t te_binary_rank_scratch_bytes(int64_t n) {
   if (n < 0 || n > 0x7fffffffLL) return 0;
-  return make_plan(n, false, true, true).total;
+  return make_plan(n, false, true, true, true).total;  // (a superset of the plan without the counting stage)
 }
 
 extern "C" int te_binary_auroc(const float* score, const void* target, int32_t target_dtype,
@@ -1839,6 +1971,15 @@ extern "C" int te_binary_auroc(const float* score, const void* target, int32_t t
   if (!out || (n > 0 && (!score || !target))) return TE_ERR_INVALID_ARGUMENT;
   return binary_rank_packed(score, target, target_dtype, n, 0, out, scratch, scratch_bytes,
                             (cudaStream_t)stream);
+}
+
+extern "C" int te_binary_auroc_variant(const float* score, const void* target, int32_t target_dtype,
+                                       int64_t n, double* out, void* scratch, size_t scratch_bytes,
+                                       int32_t variant, void* stream) {
+  if (!out || (n > 0 && (!score || !target))) return TE_ERR_INVALID_ARGUMENT;
+  if (variant != TE_RANK_AUTO && variant != TE_RANK_SORT && variant != TE_RANK_COUNTING) return TE_ERR_INVALID_ARGUMENT;
+  return binary_rank_packed(score, target, target_dtype, n, 0, out, scratch, scratch_bytes,
+                            (cudaStream_t)stream, variant);
 }
 
 extern "C" int te_binary_auprc(const float* score, const void* target, int32_t target_dtype,
@@ -2055,7 +2196,7 @@ static int partition_impl(const uint32_t* keys_in, int64_t n, const uint32_t* sp
     const size_t smem = onesweep_smem_bytes<uint32_t, B>();                                              \
     TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
     fn<<<p.sort_tiles, B, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist, lb, gp, pp, hot, \
-                                      nullptr, 0, nullptr);                                              \
+                                      nullptr, 0, nullptr, ArraySrc<uint32_t>{});                        \
   } while (0)
   if (p.sort_ipt != kSortIptDefault) return TE_ERR_UNSUPPORTED;
   if (p.sort_block == 256) {

@@ -221,7 +221,7 @@ def binned_integrate(tp: torch.Tensor, fp: torch.Tensor, fn: Optional[torch.Tens
 
 
 # ----------------------------------------------------------------------------- K1
-def _binary_rank(fn_name: str, score: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+def _binary_rank(fn_name: str, score: torch.Tensor, target: torch.Tensor, variant: Optional[int] = None) -> torch.Tensor:
     lib = N.load()
     dev = _require_cuda(score, target)
     assert score.dim() == 1 and score.shape == target.shape and score.dtype == torch.float32
@@ -235,15 +235,16 @@ def _binary_rank(fn_name: str, score: torch.Tensor, target: torch.Tensor) -> tor
             fn_name,
             getattr(lib, fn_name)(
                 score.data_ptr(), target.data_ptr(), code, n, out.data_ptr(), scratch.data_ptr(),
-                scratch.numel(), _stream_ptr(dev),
+                scratch.numel(), *(() if variant is None else (variant,)), _stream_ptr(dev),
             ),
         )
     return out
 
 
-def binary_auroc_packed(score: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
-    """float64[8] device tensor: [auroc, #pos, #neg, 2U, flags, ...] (see te_binary_auroc)."""
-    return _binary_rank("te_binary_auroc", score, target)
+def binary_auroc_packed(score: torch.Tensor, target: torch.Tensor, variant: int = N.TE_RANK_AUTO) -> torch.Tensor:
+    """float64[8] device tensor: [auroc, #pos, #neg, 2U, flags, ...] (see te_binary_auroc).
+    `variant`: TE_RANK_AUTO / TE_RANK_SORT / TE_RANK_COUNTING (te_binary_auroc_variant)."""
+    return _binary_rank("te_binary_auroc_variant", score, target, variant)
 
 
 def binary_auprc_packed(score: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
