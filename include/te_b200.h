@@ -284,6 +284,12 @@ TE_API int te_partition_scatter_u32(const uint32_t* keys_in, int64_t n, const ui
                                     size_t scratch_bytes, void* stream);
 TE_API int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, const uint32_t* digit_hist,
                                      double* out, void* scratch, size_t scratch_bytes, void* stream);
+/* te_binary_auroc_from_keys with the structure chosen by the caller (TE_RANK_*; the plain entry
+ * point = TE_RANK_AUTO).  TE_RANK_COUNTING ignores digit_hist and reports keys >= 2^31 through
+ * TE_RANK_FLAG_WIDE_SCORE in out[4]. */
+TE_API int te_binary_auroc_from_keys_variant(const uint32_t* keys, int64_t n, const uint32_t* digit_hist,
+                                             double* out, void* scratch, size_t scratch_bytes,
+                                             int32_t variant, void* stream);
 /* Average precision of rank-sharded scores (precision is a ratio of prefix
  * counts, so the step integral of precision_recall_curve.py:208-231 + tensor_utils.py:12-16 takes
  * two phases around one exchange of (P_r, N_r)):

@@ -204,7 +204,7 @@ def partition_u32(keys, splitters, counts_in=None):
     return torch.from_numpy(k[order].view(np.int32).copy()), torch.from_numpy(counts)
 
 
-def binary_auroc_from_keys(keys, hist=None):
+def binary_auroc_from_keys(keys, hist=None, variant=0):
     k = _np(keys).view(np.uint32)
     if hist is not None:  # histograms that travelled with the keys must be THE histograms of the keys
         assert np.array_equal(_np(hist), _digit_hist(k)), "digit histograms do not match the received keys"

@@ -155,3 +155,24 @@ def test_functional_falls_back_for_wide_scores(ops, monkeypatch):
     got = R.binary_auroc(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda())
     assert calls == [0, SORT]
     np.testing.assert_allclose(got.item(), oracle.binary_auroc(x, y)[0], rtol=1e-12)
+
+
+def test_counting_from_keys(ops):
+    """te_binary_auroc_from_keys_variant (the receive side of the distributed sample sort): packed
+    keys in, both structures agree with each other and with the oracle; keys >= 2^31 are flagged."""
+    rs = np.random.default_rng(17)
+    for n in (0, 5, 8193, 300_001, (1 << 21) + 3):
+        x = rs.random(n, dtype=np.float32)
+        x[: n // 3] = np.round(x[: n // 3] * 512) / 512
+        y = rs.integers(0, 2, n)
+        keys = ((x.view(np.uint32) << np.uint32(1)) | y.astype(np.uint32)).view(np.int32)
+        a = ops.binary_auroc_from_keys(dev(keys), None, COUNTING).cpu().numpy()
+        b = ops.binary_auroc_from_keys(dev(keys), None, SORT).cpu().numpy()
+        np.testing.assert_array_equal(a, b)
+        if n:
+            want, tp, fp = oracle.binary_auroc(x, y)
+            assert (a[1], a[2]) == (tp, fp)
+            assert (int(a[5]) << 32) | int(a[6]) == _exact_2u(x, y)
+    keys = keys.copy()
+    keys[3] = np.int32(-5)  # bit 31 set
+    assert int(ops.binary_auroc_from_keys(dev(keys), None, COUNTING).cpu().numpy()[4]) == 4

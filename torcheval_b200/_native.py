@@ -55,6 +55,7 @@ SIGNATURES = {
     "te_partition_u32": (C.c_int, [_vp, _i64, _vp, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
     "te_partition_scatter_u32": (C.c_int, [_vp, _i64, _vp, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
     "te_binary_auroc_from_keys": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _sz, _vp]),
+    "te_binary_auroc_from_keys_variant": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _sz, _i32, _vp]),
     "te_binary_auprc_from_keys_begin": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _sz, _vp]),
     "te_binary_auprc_from_keys_finish": (C.c_int, [_i64, C.c_double, C.c_double, _vp, _vp, _vp, _sz, _vp]),
     "te_select_splitters": (C.c_int, [_vp, _i64, _i32, _vp, _vp, _vp]),

@@ -20,6 +20,7 @@
 
 #include "rank_sort.cuh"
 #include "rank_leaf.cuh"
+#include "rank_part.cuh"
 #include "prof.cuh"
 
 namespace te {
@@ -31,7 +32,7 @@ namespace {
 constexpr int kIngestBlock = 1024;
 constexpr size_t kIngestSmem = (size_t)4 * kRadix * kWarp * sizeof(uint32_t);  // 128 KB
 
-enum IngestMode { kPacked = 0, kIndexed = 1, kRawKeys = 2, kScoreHist = 3 };  // kScoreHist: histograms of the scores' keys only, nothing is written
+enum IngestMode { kPacked = 0, kIndexed = 1, kRawKeys = 2 };
 
 struct RankScalars {            // lives in the zeroed part of the scratch buffer
   unsigned long long positives; // #label==1 (packed mode)
@@ -117,20 +118,11 @@ __global__ void __launch_bounds__(kIngestBlock, 1)
           k[j] = (b << 1) | lab[j];
           if (j < (int)cnt) npos += lab[j];
         }
-      } else if (MODE == kScoreHist) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          uint32_t b = __float_as_uint(x[j]);
-          if (b == 0x80000000u) b = 0u;
-          neg_score |= b >> 31;
-          k[j] = b << 1;
-        }
       } else {
 #pragma unroll
         for (int j = 0; j < 4; ++j) k[j] = orderable_f32(x[j]);
       }
-      if (MODE == kScoreHist) {
-      } else if (cnt == 4) {
+      if (cnt == 4) {
         st_stream_v4(keys_out + i0, make_int4((int)k[0], (int)k[1], (int)k[2], (int)k[3]));
         if (MODE == kIndexed) {
           if (as_payload)
@@ -170,7 +162,7 @@ __global__ void __launch_bounds__(kIngestBlock, 1)
     npos = warp_sum(npos);
     if (lane == 0 && npos) atomicAdd(&scal->positives, (unsigned long long)npos);
   }
-  if (MODE == kPacked || MODE == kScoreHist) {
+  if (MODE == kPacked) {
     npos = warp_sum(npos);
     const uint32_t anybad = __any_sync(kFull, bad_label != 0);
     const uint32_t anyneg = __any_sync(kFull, neg_score != 0);
@@ -789,8 +781,10 @@ struct RankPlan {
   uint32_t leaf_piece, leaf_max_items, leaf_max_slabs;
   size_t off_leaf_hdr, off_seg_stats;  // inside the zeroed region
   size_t off_seg_start, off_leaf_items, off_leaf_multi, off_leaf_slabs;
+  size_t off_range_hist, off_range_base;  // uint32[kMaxRanges][256] each (rank_part.cuh)
   size_t total;
 };
+constexpr uint32_t kMaxRanges = 1024;
 
 inline uint32_t leaf_piece_of(int64_t n) {
   uint64_t m = ((uint64_t)n / 1024 + 4095) / 4096 * 4096;
@@ -841,6 +835,8 @@ RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final,
   p.off_leaf_items = take((size_t)p.leaf_max_items * sizeof(LeafItem));
   p.off_leaf_multi = take(with_leaf ? (size_t)kLeafSegs * sizeof(LeafMulti) : 0);
   p.off_leaf_slabs = take((size_t)p.leaf_max_slabs * kLeafBins * 4);
+  p.off_range_hist = take(with_leaf ? (size_t)kMaxRanges * kRadix * 4 : 0);
+  p.off_range_base = take(with_leaf ? (size_t)kMaxRanges * kRadix * 4 : 0);
   p.total = o;
   return p;
 }
@@ -850,16 +846,11 @@ T* at(void* base, size_t off) {
   return reinterpret_cast<T*>(static_cast<char*>(base) + off);
 }
 
-struct RankPlan;
-int launch_fused_first_pass_dtype(const RankPlan& p, void* scratch, const float* score, const void* target,
-                                  int32_t dt, uint32_t* keys_out, cudaStream_t st);
-
 // nb > 1: nb independent sorts of the same length whose scratch blocks (and key arrays) lie
 // bstride bytes apart, done by the same launches (grid.y = nb).
 int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t* k_x, uint32_t* k_y,
                const uint32_t* v_in0, uint32_t* v_x, uint32_t* v_y, cudaStream_t st, int nb = 1,
-               size_t bstride = 0, int npasses = 4, int shift0 = 0, const float* fused_score = nullptr,
-               const void* fused_target = nullptr, int32_t fused_dt = 0) {
+               size_t bstride = 0, int npasses = 4, int shift0 = 0) {
   // npasses passes on the digits at bits shift0 + 8 * pass: in0 -> x -> y -> x -> y
   uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
   uint32_t* hot = hot_digits_from_env() ? at<uint32_t>(scratch, p.off_hot) : nullptr;
@@ -879,7 +870,7 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   const size_t smem = block == 256 ? onesweep_smem_bytes<uint32_t, 256>() : onesweep_smem_bytes<uint32_t, 512>();
   using PassFn = void (*)(const uint32_t*, uint32_t*, const uint32_t*, uint32_t*, uint32_t,
                           const RadixDigit, const uint32_t*, uint32_t*, uint32_t*, const PeerPtrs,
-                          const uint32_t*, uint32_t*, size_t, const uint32_t*, const ArraySrc<uint32_t>);
+                          const uint32_t*, uint32_t*, size_t, const uint32_t*);
   PassFn fn = nullptr;
   if (v_in0)
     fn = block == 256 ? onesweep_pass_kernel<uint32_t, true, 256, RadixDigit>
@@ -909,18 +900,12 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
     uint32_t* vout = (pass & 1) ? v_y : v_x;
     uint32_t* lbp = lb_counts(pass);
     uint32_t* gpp = at<uint32_t>(scratch, p.off_gprefix) + (size_t)pass * lb_groups * kRadix;
-    if (pass == 0 && fused_score) {  // (score, target) -> first partition, no packed copy in between
-      const int rc = launch_fused_first_pass_dtype(p, scratch, fused_score, fused_target, fused_dt, kout, st);
-      if (rc) return rc;
-      kin = kout;
-      continue;
-    }
     TE_PROF(v_in0 ? "onesweep_pass_pairs" : (pass == 0 && fn_first != fn ? "onesweep_pass_keys_first" : "onesweep_pass_keys"), st);
     (pass == 0 ? fn_first : fn)<<<dim3(p.sort_tiles, nb), block, smem_used, st>>>(kin, kout, vin, vout, p.n, RadixDigit{shift0 + 8 * pass},
                                                hist + pass * kRadix, lbp, gpp, PeerPtrs{},
                                                hot ? hot + 2 * pass : nullptr,
                                                pass + 1 < npasses ? lb_counts(pass + 1) : nullptr, bstride,
-                                               skip ? skip + pass : nullptr, ArraySrc<uint32_t>{});
+                                               skip ? skip + pass : nullptr);
     TE_LAUNCH_CHECK();
     kin = kout;
     vin = vout;
@@ -942,7 +927,7 @@ int launch_ingest(const float* score, const void* target, const uint32_t* raw, c
   uintptr_t a = (uintptr_t)score | (uintptr_t)target | (uintptr_t)raw;
   const bool vec_ok = (a & 15) == 0;
   TE_PROF(MODE == kPacked ? (LEAF ? "rank_ingest_packed2" : "rank_ingest_packed")
-                          : (MODE == kIndexed ? "rank_ingest_indexed" : (MODE == kScoreHist ? "rank_score_hist" : "rank_hist_keys")), st);
+                          : (MODE == kIndexed ? "rank_ingest_indexed" : "rank_hist_keys"), st);
   kern<<<grid, kIngestBlock, kIngestSmem, st>>>(score, (const TargetT*)target, raw, p.n, vec_ok,
                                                  keys_out, vals_out, at<uint32_t>(scratch, p.off_hist),
                                                  at<RankScalars>(scratch, p.off_scal), payload_bad);
@@ -1057,50 +1042,85 @@ inline int64_t leaf_min_n_from_env() {
   return v;
 }
 
-inline bool fused_ingest_from_env() {
+inline bool range_pass_from_env() {
   static const bool b = [] {
-    const char* e = getenv("TE_B200_FUSED_INGEST");
-    return e ? atoi(e) != 0 : false;  // measured a wash (profiles/r02_leaf_bench_v2.txt): the pass is not
-                                      // HBM-bound, but tripling what its load phase reads costs what the
-                                      // separate pack kernel did
+    const char* e = getenv("TE_B200_RANGE_PASS");
+    return e ? atoi(e) != 0 : true;
   }();
   return b;
 }
 
-// First pass of the counting-stage path with the ingest fused in: reads (score, target), packs,
-// partitions by key bits 15..22 in arrival order.  The digit histograms come from a scores-only
-// histogram kernel (4 bytes per score) instead of the pack kernel (16 bytes per score).
+// ingest (per-range histograms) -> range bases -> first partition pass without look-back
+// (rank_part.cuh) -> one stable look-back pass on the top digit.
+//   raw_keys == nullptr: (score, target) are packed into `ka`;  ka -> kb -> ka, result in ka.
+//   raw_keys given (packed already, the receive side of the sample sort): raw -> ka -> kb, result in kb.
 template <typename TargetT>
-int launch_fused_first_pass(const RankPlan& p, void* scratch, const float* score, const TargetT* target,
-                            uint32_t* keys_out, cudaStream_t st) {
+int leaf_passes_ranges(const RankPlan& p, void* scratch, const float* score, const TargetT* target,
+                       const uint32_t* raw_keys, uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st) {
+  auto part = partition_ranges_kernel<RadixDigit>;
+  const size_t part_smem = (size_t)2 * kPrTile * sizeof(uint32_t);
+  TE_CUDA_TRY(cudaFuncSetAttribute(part, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)part_smem));
+  int per_sm = 0;
+  TE_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, part, kPrBlock, part_smem));
+  if (per_sm < 1) return TE_ERR_UNSUPPORTED;
+  int resident = per_sm * sms;
+  if (resident > (int)kMaxRanges) resident = kMaxRanges;
+  const RangeGeom rg = range_geom(p.n, resident);
+  uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
+  uint32_t* range_hist = at<uint32_t>(scratch, p.off_range_hist);
+  uint32_t* range_base = at<uint32_t>(scratch, p.off_range_base);
+  uint32_t* flags = &at<RankScalars>(scratch, p.off_scal)->flags;
+  uint32_t* skip = skip_passes_from_env() ? at<uint32_t>(scratch, p.off_ticket) : nullptr;
+  if (raw_keys) {
+    auto ing = rank_ingest_ranges_kernel<long long, true>;
+    TE_CUDA_TRY(cudaFuncSetAttribute(ing, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kIrSmem));
+    TE_PROF("rank_hist_ranges", st);
+    ing<<<rg.ranges, kIrBlock, kIrSmem, st>>>(reinterpret_cast<const float*>(raw_keys), nullptr, p.n,
+                                              ((uintptr_t)raw_keys & 15) == 0, rg.tiles_per_range, nullptr, hist,
+                                              range_hist, flags);
+  } else {
+    auto ing = rank_ingest_ranges_kernel<TargetT, false>;
+    TE_CUDA_TRY(cudaFuncSetAttribute(ing, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kIrSmem));
+    TE_PROF("rank_ingest_ranges", st);
+    ing<<<rg.ranges, kIrBlock, kIrSmem, st>>>(score, target, p.n, (((uintptr_t)score | (uintptr_t)target) & 15) == 0,
+                                              rg.tiles_per_range, ka, hist, range_hist, flags);
+  }
+  TE_LAUNCH_CHECK();
+  {
+    TE_PROF("digit_scan", st);
+    digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 2, nullptr, 0, skip);
+    range_base_kernel<<<1, kRadix, 0, st>>>(range_hist, rg.ranges, hist, range_base);
+  }
+  TE_LAUNCH_CHECK();
+  const uint32_t* in1 = raw_keys ? raw_keys : ka;
+  uint32_t* out1 = raw_keys ? ka : kb;
+  uint32_t* out2 = raw_keys ? kb : ka;
+  {
+    TE_PROF("partition_ranges", st);
+    part<<<rg.ranges, kPrBlock, part_smem, st>>>(in1, out1, p.n, RadixDigit{kLeafBits}, range_base, rg.tiles_per_range, skip);
+  }
+  TE_LAUNCH_CHECK();
+  // second pass: the look-back kernel, stable, on bits 23..30 (its look-back rows are the memset ones)
   if (p.sort_block != 512 || p.sort_ipt != kSortIptDefault) return TE_ERR_UNSUPPORTED;
-  using Src = PackSrc<TargetT>;
-  auto fn = onesweep_pass_kernel<uint32_t, false, 512, RadixDigit, kSortIptDefault, false, true, Src>;
+  auto fn = onesweep_pass_kernel<uint32_t, false, 512, RadixDigit>;
   const size_t smem = onesweep_smem_bytes<uint32_t, 512>();
   TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
-  const size_t lb_groups = (p.sort_tiles + kLbGroup - 1) / kLbGroup;
-  Src src;
-  src.score = score, src.target = target, src.flags = &at<RankScalars>(scratch, p.off_scal)->flags;
-  src.vec_ok = (((uintptr_t)score | (uintptr_t)target) & 15) == 0;
-  TE_PROF("onesweep_pass_fused_ingest", st);
-  fn<<<dim3(p.sort_tiles, 1), 512, smem, st>>>(nullptr, keys_out, nullptr, nullptr, p.n, RadixDigit{kLeafBits}, hist,
+  TE_PROF("onesweep_pass_keys", st);
+  fn<<<dim3(p.sort_tiles, 1), 512, smem, st>>>(out1, out2, nullptr, nullptr, p.n, RadixDigit{kLeafBits + 8}, hist + kRadix,
                                               at<uint32_t>(scratch, p.off_lookback), at<uint32_t>(scratch, p.off_gprefix),
-                                              PeerPtrs{}, nullptr, at<uint32_t>(scratch, p.off_lookback_rest), 0,
-                                              skip_passes_from_env() ? at<uint32_t>(scratch, p.off_ticket) : nullptr, src);
+                                              PeerPtrs{}, nullptr, nullptr, 0, skip ? skip + 1 : nullptr);
   TE_LAUNCH_CHECK();
-  (void)lb_groups;
   return TE_OK;
 }
 
-int launch_fused_first_pass_dtype(const RankPlan& p, void* scratch, const float* score, const void* target,
-                                  int32_t dt, uint32_t* keys_out, cudaStream_t st) {
+int leaf_passes_ranges_dtype(const RankPlan& p, void* scratch, const float* score, const void* target, int32_t dt,
+                             uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st) {
   switch (dt) {
-    case TE_DTYPE_I64: return launch_fused_first_pass(p, scratch, score, (const long long*)target, keys_out, st);
-    case TE_DTYPE_I32: return launch_fused_first_pass(p, scratch, score, (const int*)target, keys_out, st);
-    case TE_DTYPE_U8: return launch_fused_first_pass(p, scratch, score, (const unsigned char*)target, keys_out, st);
-    case TE_DTYPE_F32: return launch_fused_first_pass(p, scratch, score, (const float*)target, keys_out, st);
-    case TE_DTYPE_F64: return launch_fused_first_pass(p, scratch, score, (const double*)target, keys_out, st);
+    case TE_DTYPE_I64: return leaf_passes_ranges(p, scratch, score, (const long long*)target, nullptr, ka, kb, sms, st);
+    case TE_DTYPE_I32: return leaf_passes_ranges(p, scratch, score, (const int*)target, nullptr, ka, kb, sms, st);
+    case TE_DTYPE_U8: return leaf_passes_ranges(p, scratch, score, (const unsigned char*)target, nullptr, ka, kb, sms, st);
+    case TE_DTYPE_F32: return leaf_passes_ranges(p, scratch, score, (const float*)target, nullptr, ka, kb, sms, st);
+    case TE_DTYPE_F64: return leaf_passes_ranges(p, scratch, score, (const double*)target, nullptr, ka, kb, sms, st);
     default: return TE_ERR_INVALID_ARGUMENT;
   }
 }
@@ -1114,12 +1134,8 @@ int binary_auroc_leaf(const float* score, const void* target, int32_t dt, int64_
   TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
   uint32_t* ka = at<uint32_t>(scratch, p.off_keys_a);
   uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
-  if (n > 0 && fused_ingest_from_env() && p.sort_block == 512 && p.sort_ipt == kSortIptDefault) {
-    if (dt < TE_DTYPE_I64 || dt > TE_DTYPE_F64) return TE_ERR_INVALID_ARGUMENT;
-    // scores -> histograms; (score, target) -> b (fused ingest + pass on bits 15..22); b -> a
-    int rc = launch_ingest<kScoreHist, long long, true>(score, nullptr, nullptr, p, nullptr, nullptr, scratch, sms, st);
-    if (rc) return rc;
-    rc = run_passes(p, scratch, nullptr, kb, ka, nullptr, nullptr, nullptr, st, 1, 0, 2, kLeafBits, score, target, dt);
+  if (n > 0 && range_pass_from_env() && p.sort_block == 512 && p.sort_ipt == kSortIptDefault) {
+    const int rc = leaf_passes_ranges_dtype(p, scratch, score, target, dt, ka, kb, sms, st);
     if (rc) return rc;
   } else if (n > 0) {
     int rc = launch_ingest_dtype<kPacked, true>(score, target, dt, p, ka, nullptr, scratch, sms, st);
@@ -1719,7 +1735,7 @@ __global__ void __launch_bounds__(1024)
     s_sp[tid] = (int)tid < dop_in.nsp ? (splitters_dev ? splitters_dev[tid] : dop_in.sp[tid]) : 0xffffffffu;
   __syncthreads();
   auto dop = [&](uint32_t k) { return dop_in.eval(k, s_sp); };
-  uint32_t npos = 0, bad_label = 0, neg_score = 0;
+  uint32_t npos = 0, bad_label = 0, neg_score = 0, wide = 0;
   const uint32_t ngroups = (n + 3) / 4;
   for (uint32_t g = blockIdx.x * blockDim.x + tid; g < ngroups; g += gridDim.x * blockDim.x) {
     const uint32_t i0 = g * 4, cnt = min(4u, n - i0);
@@ -1757,6 +1773,7 @@ __global__ void __launch_bounds__(1024)
       uint32_t b = __float_as_uint(x[j]);
       if (b == 0x80000000u) b = 0u;
       neg_score |= b >> 31;
+      wide |= (b >> 30) & 1u;  // score >= 2.0: the key uses bit 31
       k[j] = (b << 1) | lab[j];
       if (j < (int)cnt) {
         npos += lab[j];
@@ -1811,9 +1828,11 @@ __global__ void __launch_bounds__(1024)
   npos = warp_sum(npos);
   const uint32_t anybad = __any_sync(kFull, bad_label != 0);
   const uint32_t anyneg = __any_sync(kFull, neg_score != 0);
+  const uint32_t anywide = __any_sync(kFull, wide != 0);
   if (lane == 0) {
     if (npos) atomicAdd(&scal->positives, (unsigned long long)npos);
-    const uint32_t f = (anybad ? TE_RANK_FLAG_BAD_LABEL : 0) | (anyneg ? TE_RANK_FLAG_NEGATIVE_SCORE : 0);
+    const uint32_t f = (anybad ? TE_RANK_FLAG_BAD_LABEL : 0) | (anyneg ? TE_RANK_FLAG_NEGATIVE_SCORE : 0) |
+                       (anywide ? TE_RANK_FLAG_WIDE_SCORE : 0);
     if (f) atomicOr(&scal->flags, f);
   }
 }
@@ -2196,7 +2215,7 @@ static int partition_impl(const uint32_t* keys_in, int64_t n, const uint32_t* sp
     const size_t smem = onesweep_smem_bytes<uint32_t, B>();                                              \
     TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
     fn<<<p.sort_tiles, B, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist, lb, gp, pp, hot, \
-                                      nullptr, 0, nullptr, ArraySrc<uint32_t>{});                        \
+                                      nullptr, 0, nullptr);                                              \
   } while (0)
   if (p.sort_ipt != kSortIptDefault) return TE_ERR_UNSUPPORTED;
   if (p.sort_block == 256) {
@@ -2229,15 +2248,29 @@ extern "C" int te_partition_scatter_u32(const uint32_t* keys_in, int64_t n, cons
 // mode 0: AUROC of the keys.  mode 1: the same, and the chunk states the AUPRC integrate sweep
 // starts from are left in `scratch` next to the sorted keys (te_binary_auprc_from_keys_finish).
 static int rank_from_keys(const uint32_t* keys, int64_t n, int mode, const uint32_t* digit_hist, double* out,
-                          void* scratch, size_t scratch_bytes, void* stream) {
+                          void* scratch, size_t scratch_bytes, void* stream, int variant = TE_RANK_SORT) {
   if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
   if (!out || (n > 0 && !keys)) return TE_ERR_INVALID_ARGUMENT;
   if (((uintptr_t)keys & 15) != 0) return TE_ERR_INVALID_ARGUMENT;
-  const RankPlan p = make_plan(n, false, true, true);
-  if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
   cudaStream_t st = (cudaStream_t)stream;
   int sms = 0;
   TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  if (mode == 0 && (variant == TE_RANK_COUNTING || (variant == TE_RANK_AUTO && n >= leaf_min_n_from_env()))) {
+    // counting-stage path (rank_leaf.cuh); the senders' byte histograms are not the ones it needs
+    const RankPlan p = make_plan(n, false, true, true, true);
+    if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
+    if (p.sort_block != 512 || p.sort_ipt != kSortIptDefault) return TE_ERR_UNSUPPORTED;
+    TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
+    uint32_t* ka = at<uint32_t>(scratch, p.off_keys_a);
+    uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
+    if (n > 0) {
+      const int rc = leaf_passes_ranges<long long>(p, scratch, nullptr, nullptr, keys, ka, kb, sms, st);
+      if (rc) return rc;
+    }
+    return finish_leaf(p, kb, out, scratch, sms, st);
+  }
+  const RankPlan p = make_plan(n, false, true, true);
+  if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
   TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
   uint32_t* ka = at<uint32_t>(scratch, p.off_keys_a);
   uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
@@ -2267,7 +2300,14 @@ static int rank_from_keys(const uint32_t* keys, int64_t n, int mode, const uint3
 
 extern "C" int te_binary_auroc_from_keys(const uint32_t* keys, int64_t n, const uint32_t* digit_hist,
                                          double* out, void* scratch, size_t scratch_bytes, void* stream) {
-  return rank_from_keys(keys, n, 0, digit_hist, out, scratch, scratch_bytes, stream);
+  return rank_from_keys(keys, n, 0, digit_hist, out, scratch, scratch_bytes, stream, TE_RANK_AUTO);
+}
+
+extern "C" int te_binary_auroc_from_keys_variant(const uint32_t* keys, int64_t n, const uint32_t* digit_hist,
+                                                 double* out, void* scratch, size_t scratch_bytes, int32_t variant,
+                                                 void* stream) {
+  if (variant != TE_RANK_AUTO && variant != TE_RANK_SORT && variant != TE_RANK_COUNTING) return TE_ERR_INVALID_ARGUMENT;
+  return rank_from_keys(keys, n, 0, digit_hist, out, scratch, scratch_bytes, stream, variant);
 }
 
 extern "C" int te_binary_auprc_from_keys_begin(const uint32_t* keys, int64_t n, const uint32_t* digit_hist,

@@ -1,0 +1,268 @@
+// First partition pass of the counting-stage AUROC path as an upsweep / downsweep pair without
+// any traffic between thread blocks.
+//
+// The array is cut into R contiguous RANGES of whole 8192-record tiles, one per resident CTA.
+//   upsweep   = the ingest kernel below: it reads (score, target), writes the packed keys, and
+//               leaves, per range, the histogram of the digit the first pass partitions by (plus
+//               the global histograms of both digits, as before);
+//   range_base_kernel turns those into the output offset of every (range, digit) pair;
+//   downsweep = partition_ranges_kernel: a persistent CTA walks the tiles of its range with the
+//               running output offset of each digit in a register.  No look-back, no flags, no
+//               spinning: nothing a CTA needs is produced while it runs.
+// A first pass of a keys-only sort has no order to preserve, so ranks inside a tile come from ONE
+// shared atomic per record on a CTA-wide table of 256 counters (arrival order): no per-warp
+// tables to clear, sum and scan (rank_sort.cuh pays ~4 shared wavefronts per 32 records for
+// those), no digit phase.
+#pragma once
+#include "rank_leaf.cuh"
+#include "rank_sort.cuh"
+
+namespace te {
+
+constexpr int kPrBlock = 512;
+constexpr int kPrIpt = 16;
+constexpr int kPrTile = kPrBlock * kPrIpt;  // 8192 records
+constexpr int kIrBlock = 512;
+constexpr size_t kIrSmem = (size_t)2 * kRadix * kWarp * sizeof(uint32_t);  // two lane-replicated histograms: 64 KB
+
+struct RangeGeom {
+  uint32_t ranges, tiles_per_range;
+};
+inline RangeGeom range_geom(uint32_t n, int resident_ctas) {
+  RangeGeom g;
+  uint32_t tiles = (n + kPrTile - 1) / kPrTile;
+  if (tiles < 1) tiles = 1;
+  uint32_t want = (uint32_t)resident_ctas < tiles ? (uint32_t)resident_ctas : tiles;
+  g.tiles_per_range = (tiles + want - 1) / want;
+  g.ranges = (tiles + g.tiles_per_range - 1) / g.tiles_per_range;
+  return g;
+}
+
+// (score, target) -> packed keys, range by range.  flags: TE_RANK_FLAG_* seen.  hist: uint32[2][256]
+// (+=), digits at key bits 15..22 and 23..30; range_hist: uint32[ranges][256] (=), the first digit
+// per range.  RAW_KEYS: `score` holds packed keys already (the receive side of the distributed
+// sample sort): histograms and the wide-key flag only, nothing is written.
+template <typename TargetT, bool RAW_KEYS>
+__global__ void __launch_bounds__(kIrBlock)
+    rank_ingest_ranges_kernel(const float* __restrict__ score, const TargetT* __restrict__ target, uint32_t n,
+                              bool vec_ok, uint32_t tiles_per_range, uint32_t* __restrict__ keys_out,
+                              uint32_t* ghist, uint32_t* __restrict__ range_hist, uint32_t* flags) {
+  extern __shared__ uint32_t sh[];  // [2][256][32 lanes]
+  const unsigned tid = threadIdx.x, lane = tid & 31;
+  for (int i = tid; i < 2 * kRadix * kWarp; i += kIrBlock) sh[i] = 0;
+  __syncthreads();
+  const uint64_t e0 = (uint64_t)blockIdx.x * tiles_per_range * kPrTile;
+  const uint32_t e1 = (uint32_t)min((uint64_t)n, e0 + (uint64_t)tiles_per_range * kPrTile);
+  uint32_t bad_label = 0, neg_score = 0, wide = 0;
+  for (uint64_t i64 = e0 + 4ull * tid; i64 < e1; i64 += 4ull * kIrBlock) {
+    const uint32_t i0 = (uint32_t)i64;
+    const uint32_t cnt = min(4u, e1 - i0);
+    uint32_t b[4], lab[4] = {0, 0, 0, 0};
+    if (cnt == 4 && vec_ok) {
+      const int4 a = ld_stream_v4(score + i0);
+      b[0] = (uint32_t)a.x, b[1] = (uint32_t)a.y, b[2] = (uint32_t)a.z, b[3] = (uint32_t)a.w;
+      if constexpr (!RAW_KEYS) {
+        if constexpr (sizeof(TargetT) == 8) {
+          const int4 t0 = ld_stream_v4(target + i0);
+          const int4 t1 = ld_stream_v4(target + i0 + 2);
+          TargetT tv[4];
+          const unsigned long long u0 = ((unsigned long long)(uint32_t)t0.y << 32) | (uint32_t)t0.x;
+          const unsigned long long u1 = ((unsigned long long)(uint32_t)t0.w << 32) | (uint32_t)t0.z;
+          const unsigned long long u2 = ((unsigned long long)(uint32_t)t1.y << 32) | (uint32_t)t1.x;
+          const unsigned long long u3 = ((unsigned long long)(uint32_t)t1.w << 32) | (uint32_t)t1.z;
+          memcpy(&tv[0], &u0, 8), memcpy(&tv[1], &u1, 8), memcpy(&tv[2], &u2, 8), memcpy(&tv[3], &u3, 8);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) lab[j] = LabelOf<TargetT>::get(tv[j], bad_label);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) lab[j] = LabelOf<TargetT>::get(target[i0 + j], bad_label);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        b[j] = j < (int)cnt ? __float_as_uint(score[i0 + j]) : 0u;
+        if (!RAW_KEYS && j < (int)cnt) lab[j] = LabelOf<TargetT>::get(target[i0 + j], bad_label);
+      }
+    }
+    uint32_t k[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (RAW_KEYS) {
+        k[j] = b[j];
+        wide |= b[j] >> 31;
+      } else {
+        const uint32_t bb = b[j] == 0x80000000u ? 0u : b[j];  // -0.0 ties with +0.0
+        neg_score |= bb >> 31;
+        k[j] = (bb << 1) | lab[j];
+        wide |= (bb >> 30) & 1u;  // key bit 31: score >= 2.0
+      }
+    }
+    if constexpr (!RAW_KEYS) {
+      if (cnt == 4) {
+        st_stream_v4(keys_out + i0, make_int4((int)k[0], (int)k[1], (int)k[2], (int)k[3]));
+      } else {
+        for (uint32_t j = 0; j < cnt; ++j) keys_out[i0 + j] = k[j];
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (j < (int)cnt) {
+        atomicAdd(sh + ((k[j] >> kLeafBits) & 0xffu) * kWarp + lane, 1u);
+        atomicAdd(sh + (kRadix + ((k[j] >> (kLeafBits + 8)) & 0xffu)) * kWarp + lane, 1u);
+      }
+    }
+  }
+  __syncthreads();
+  {
+    uint32_t s = 0;  // thread t owns (digit position, digit) = t
+#pragma unroll
+    for (int r = 0; r < kWarp; ++r) s += sh[tid * kWarp + ((r + tid) & 31)];
+    if (tid < kRadix) range_hist[(size_t)blockIdx.x * kRadix + tid] = s;
+    if (s) atomicAdd(ghist + tid, s);
+  }
+  const uint32_t f = (__any_sync(kFull, bad_label != 0) ? TE_RANK_FLAG_BAD_LABEL : 0) |
+                     (__any_sync(kFull, neg_score != 0) ? TE_RANK_FLAG_NEGATIVE_SCORE : 0) |
+                     (__any_sync(kFull, wide != 0) ? TE_RANK_FLAG_WIDE_SCORE : 0);
+  if (lane == 0 && f) atomicOr(flags, f);
+}
+
+// range_base[r][d] = digit_base[d] + sum over ranges r' < r of range_hist[r'][d]: where the records
+// of range r with digit d start in the output of the first pass.
+__global__ void __launch_bounds__(kRadix)
+    range_base_kernel(const uint32_t* __restrict__ range_hist, uint32_t ranges,
+                      const uint32_t* __restrict__ digit_base, uint32_t* __restrict__ range_base) {
+  const unsigned d = threadIdx.x;
+  uint32_t acc = digit_base[d];
+#pragma unroll 8
+  for (uint32_t r = 0; r < ranges; ++r) {
+    const uint32_t c = range_hist[(size_t)r * kRadix + d];
+    range_base[(size_t)r * kRadix + d] = acc;
+    acc += c;
+  }
+}
+
+// 16-byte asynchronous global -> shared copy (LDGSTS): no register, no scoreboard stall; completion
+// is observed per thread with wait_group and made CTA-visible by the barrier that follows.
+__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// Downsweep: one persistent CTA per range.  Slot i of thread t is record (i / 4 * 512 + t) * 4 + i % 4
+// of the tile (16-byte accesses); any assignment will do, ranks are handed out in arrival order.
+// The tiles of a range are known in advance, so tile k + 1 is copied into the other half of a
+// two-tile shared buffer (cp.async) while tile k is ranked, scattered INTO ITS OWN BUFFER (every
+// thread holds its records in registers by then) and written out: the kernel was bound by the
+// latency of the loads at the head of every tile (ncu: long_scoreboard the top stall, LSU data
+// pipe at 52 %: profiles/r02_ncu_summary_v1.txt), not by the pipe.
+template <typename DigitOp>
+__global__ void __launch_bounds__(kPrBlock, 3)
+    partition_ranges_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out, uint32_t n,
+                            const DigitOp dop, const uint32_t* __restrict__ range_base, uint32_t tiles_per_range,
+                            const uint32_t* __restrict__ skip_flag) {
+  extern __shared__ __align__(16) uint32_t s_buf[];  // [2][kPrTile]
+  __shared__ uint32_t s_cnt[kRadix], s_start[kRadix], s_goff[kRadix], s_wsum[kRadix / kWarp];
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t ntiles = (n + kPrTile - 1) / kPrTile;
+  const uint32_t t0 = blockIdx.x * tiles_per_range;
+  const uint32_t t1 = min(ntiles, t0 + tiles_per_range);
+  const bool skip_pass = skip_flag ? ld_relaxed_u32(skip_flag) != 0u : false;
+  uint32_t run = tid < kRadix ? range_base[(size_t)blockIdx.x * kRadix + tid] : 0u;  // output offset of digit tid
+  if (tid < kRadix) s_cnt[tid] = 0u;
+  auto rec = [&](int i) -> uint32_t { return (((uint32_t)i >> 2) * kPrBlock + tid) * 4u + ((uint32_t)i & 3u); };
+  // full tiles travel through cp.async; a partial one (the last of the array) is read directly
+  auto prefetch = [&](uint32_t tile) {
+    if (tile < t1 && (uint64_t)(tile + 1) * kPrTile <= n) {
+      uint32_t* dst = s_buf + (tile & 1u) * kPrTile;
+      const uint32_t* src = keys_in + (size_t)tile * kPrTile;
+#pragma unroll
+      for (int q = 0; q < kPrIpt / 4; ++q) cp_async_16(dst + rec(4 * q), src + rec(4 * q));
+    }
+    cp_async_commit();  // (an empty group keeps the wait_group arithmetic uniform)
+  };
+  prefetch(t0);
+  for (uint32_t tile = t0; tile < t1; ++tile) {
+    const uint32_t base = tile * (uint32_t)kPrTile;
+    const uint32_t valid = min((uint32_t)kPrTile, n - base);
+    uint32_t* s_keys = s_buf + (tile & 1u) * kPrTile;
+    prefetch(tile + 1);   // into the half whose tile left at the end of the previous round
+    cp_async_wait<1>();   // everything but the newest group: this tile has landed
+    __syncthreads();
+    uint32_t key[kPrIpt];
+    if (valid == (uint32_t)kPrTile) {
+#pragma unroll
+      for (int q = 0; q < kPrIpt / 4; ++q) {
+        const uint4 a = *reinterpret_cast<const uint4*>(s_keys + rec(4 * q));
+        key[4 * q] = a.x, key[4 * q + 1] = a.y, key[4 * q + 2] = a.z, key[4 * q + 3] = a.w;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < kPrIpt; ++i) key[i] = rec(i) < valid ? keys_in[base + rec(i)] : 0u;
+    }
+    if (skip_pass) {  // one digit value only: the order stays as it is
+#pragma unroll
+      for (int i = 0; i < kPrIpt; ++i)
+        if (rec(i) < valid) keys_out[base + rec(i)] = key[i];
+      continue;
+    }
+    // ---- rank: arrival order inside the digit, straight from the CTA-wide counters ----
+    uint32_t rk[kPrIpt / 2];
+#pragma unroll
+    for (int i = 0; i < kPrIpt; ++i) {
+      const uint32_t r = rec(i) < valid ? atomicAdd(&s_cnt[dop(key[i])], 1u) : 0u;
+      if (i & 1)
+        rk[i >> 1] |= r << 16;
+      else
+        rk[i >> 1] = r;
+    }
+    __syncthreads();  // all counts in; every thread holds its records, the buffer may be overwritten
+    // ---- 256 digit threads: where each digit's run starts in the tile and in the output ----
+    if (tid < kRadix) {
+      const uint32_t c = s_cnt[tid];
+      uint32_t incl = c;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t u = __shfl_up_sync(kFull, incl, o);
+        if (lane >= (unsigned)o) incl += u;
+      }
+      if (lane == 31) s_wsum[warp] = incl;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      uint32_t wb = 0;
+#pragma unroll
+      for (int w = 0; w < kRadix / kWarp; ++w)
+        if (w < (int)warp) wb += s_wsum[w];
+      const uint32_t excl = wb + incl - c;
+      s_start[tid] = excl;
+      s_goff[tid] = run - excl;  // output index = s_goff[d] + tile position
+      run += c;
+      s_cnt[tid] = 0u;           // for the next tile
+    }
+    __syncthreads();
+    // ---- scatter into tile order ----
+#pragma unroll
+    for (int i = 0; i < kPrIpt; ++i) {
+      const uint32_t r = (i & 1) ? rk[i >> 1] >> 16 : rk[i >> 1] & 0xffffu;
+      if (rec(i) < valid) s_keys[s_start[dop(key[i])] + r] = key[i];
+    }
+    __syncthreads();
+    // ---- output: every digit run leaves as one contiguous burst ----
+#pragma unroll
+    for (int k = 0; k < kPrIpt; ++k) {
+      const uint32_t p = tid + k * kPrBlock;
+      if (p < valid) {
+        const uint32_t kk = s_keys[p];
+        keys_out[s_goff[dop(kk)] + p] = kk;
+      }
+    }
+    __syncthreads();  // this half, s_start, s_goff are rewritten from the next round on
+  }
+  cp_async_wait<0>();
+}
+
+}  // namespace te

@@ -126,27 +126,6 @@ struct LabelOf<double> {
   }
 };
 
-// Where a pass takes its keys from: an array of keys (every pass but possibly the first), or the
-// raw (score, target) arrays, packed on the fly into (float bits << 1) | label — the ingest fused
-// into the first pass, which then reads 12 instead of 4 bytes per record but spares the
-// 16 bytes per score of a separate pack kernel.  The fused form loads 16 bytes per instruction
-// and hands thread slot i the record  tile + group * 256 + ((i / 4) * 16 + sub) * 4 + i % 4;
-// any fixed assignment will do, because it is only used with arrival-order (kUnstable) ranking.
-template <typename KeyT>
-struct ArraySrc {
-  static constexpr bool kFused = false;
-  using Target = int;
-};
-template <typename TargetT>
-struct PackSrc {
-  static constexpr bool kFused = true;
-  using Target = TargetT;
-  const float* __restrict__ score;
-  const TargetT* __restrict__ target;
-  uint32_t* flags;  // TE_RANK_FLAG_BAD_LABEL is OR-ed in (negative / wide scores were seen by the histogram kernel)
-  bool vec_ok;      // both arrays 16-byte aligned
-};
-
 // Optional per-phase cycle accounting of the pass kernel (compile with -DTE_PHASE_STATS; read with
 // te_debug_phase_stats).  Thread 0 of every CTA adds the clock64() deltas between phase boundaries.
 __device__ unsigned long long g_phase_cycles[8];
@@ -217,15 +196,14 @@ constexpr uint32_t kNoHotDigit = 0xffffffffu;
 // digits carries no information: the FIRST pass of a keys-only sort (records that agree in all
 // 32 bits are indistinguishable, and later passes are stable), never for (key, value) pairs.
 template <typename KeyT, bool HAS_VAL, int kSortBlock, typename DigitOp, int kSortIpt = kSortIptDefault,
-          bool kPeerScatter = false, bool kUnstable = false, typename Src = ArraySrc<KeyT>>
+          bool kPeerScatter = false, bool kUnstable = false>
 __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / kSortBlock)
     onesweep_pass_kernel(const KeyT* __restrict__ keys_in_, KeyT* __restrict__ keys_out_,
                          const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
                          uint32_t n, const DigitOp dop, const uint32_t* __restrict__ digit_base_,
                          uint32_t* lookback_, uint32_t* group_prefix_, const PeerPtrs peers,
                          const uint32_t* __restrict__ hot_info_, uint32_t* __restrict__ zero_next_,
-                         size_t bstride, const uint32_t* __restrict__ skip_flag_ = nullptr, const Src src = Src{}) {
-  static_assert(!Src::kFused || (kUnstable && !HAS_VAL && sizeof(KeyT) == 4), "the fused ingest feeds an arrival-order keys-only pass");
+                         size_t bstride, const uint32_t* __restrict__ skip_flag_ = nullptr) {
   const uint32_t* __restrict__ skip_flag = batch_ptr(skip_flag_, bstride);
   const KeyT* __restrict__ keys_in = batch_ptr(keys_in_, bstride);
   KeyT* __restrict__ keys_out = batch_ptr(keys_out_, bstride);
@@ -270,61 +248,11 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
   //      issued first; the ranking tables are cleared while they are in flight. ----
   KeyT key[kSortIpt];
   // tile-relative index of the record in slot i of this thread
-  auto rec = [&](int i) -> uint32_t {
-    return Src::kFused ? gbase + (((uint32_t)i >> 2) * 16u + sub) * 4u + ((uint32_t)i & 3u) : gbase + i * 16 + sub;
-  };
-  if constexpr (Src::kFused) {
-    using TargetT = typename Src::Target;
-    uint32_t bad = 0;
+  auto rec = [&](int i) -> uint32_t { return gbase + i * 16 + sub; };
 #pragma unroll
-    for (int q = 0; q < kSortIpt / 4; ++q) {
-      const uint32_t r0 = rec(4 * q);
-      uint32_t b[4], lab[4];
-      if (r0 + 4 <= valid && src.vec_ok) {
-        const int4 a = ld_stream_v4(src.score + base + r0);
-        b[0] = (uint32_t)a.x, b[1] = (uint32_t)a.y, b[2] = (uint32_t)a.z, b[3] = (uint32_t)a.w;
-        if constexpr (sizeof(TargetT) == 8) {
-          const int4 t0 = ld_stream_v4(src.target + base + r0);
-          const int4 t1 = ld_stream_v4(src.target + base + r0 + 2);
-          TargetT tv[4];
-          const unsigned long long u0 = ((unsigned long long)(uint32_t)t0.y << 32) | (uint32_t)t0.x;
-          const unsigned long long u1 = ((unsigned long long)(uint32_t)t0.w << 32) | (uint32_t)t0.z;
-          const unsigned long long u2 = ((unsigned long long)(uint32_t)t1.y << 32) | (uint32_t)t1.x;
-          const unsigned long long u3 = ((unsigned long long)(uint32_t)t1.w << 32) | (uint32_t)t1.z;
-          memcpy(&tv[0], &u0, 8), memcpy(&tv[1], &u1, 8), memcpy(&tv[2], &u2, 8), memcpy(&tv[3], &u3, 8);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) lab[j] = LabelOf<TargetT>::get(tv[j], bad);
-        } else if constexpr (sizeof(TargetT) == 4) {
-          const int4 t0 = ld_stream_v4(src.target + base + r0);
-          TargetT tv[4];
-          memcpy(&tv[0], &t0.x, 4), memcpy(&tv[1], &t0.y, 4), memcpy(&tv[2], &t0.z, 4), memcpy(&tv[3], &t0.w, 4);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) lab[j] = LabelOf<TargetT>::get(tv[j], bad);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) lab[j] = LabelOf<TargetT>::get(src.target[base + r0 + j], bad);
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const bool in = r0 + j < valid;
-          b[j] = in ? __float_as_uint(src.score[base + r0 + j]) : 0u;
-          lab[j] = in ? LabelOf<TargetT>::get(src.target[base + r0 + j], bad) : 0u;
-        }
-      }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const uint32_t bb = b[j] == 0x80000000u ? 0u : b[j];  // -0.0 ties with +0.0
-        key[4 * q + j] = r0 + j < valid ? (KeyT)((bb << 1) | lab[j]) : ~(KeyT)0;
-      }
-    }
-    if (__any_sync(kFull, bad != 0) && lane == 0) atomicOr(src.flags, (uint32_t)TE_RANK_FLAG_BAD_LABEL);
-  } else {
-#pragma unroll
-    for (int i = 0; i < kSortIpt; ++i) {
-      const uint32_t r = rec(i);
-      key[i] = r < valid ? keys_in[base + r] : ~(KeyT)0;  // padding sorts last, is never written
-    }
+  for (int i = 0; i < kSortIpt; ++i) {
+    const uint32_t r = rec(i);
+    key[i] = r < valid ? keys_in[base + r] : ~(KeyT)0;  // padding sorts last, is never written
   }
   for (int i = tid; i < GROUPS * kRadix; i += kSortBlock) s_rank[i] = 0u;
   // the next pass's look-back row of this tile must read as "not published": clearing it here

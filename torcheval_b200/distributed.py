@@ -25,8 +25,10 @@ from typing import Optional
 import torch
 import torch.distributed as dist
 
+from . import _native as N_
 from . import ops
 
+_WIDE = N_.TE_RANK_FLAG_WIDE_SCORE  # informational flag of the pack kernel: not a reason to leave the packed path
 SAMPLES_PER_RANK = 4096
 # All samples are sorted by ONE thread block (te_select_splitters, bitonic in shared memory:
 # 0.05 ms for 8192 keys, 0.3 ms for 32768), so the pool is capped; 8192 samples put the quantile
@@ -73,8 +75,8 @@ class _LocalKernels:
         return ops.partition_u32(keys, splitters, counts)
 
     @staticmethod
-    def auroc_from_keys(keys: torch.Tensor, hist=None) -> torch.Tensor:
-        return ops.binary_auroc_from_keys(keys, hist)
+    def auroc_from_keys(keys: torch.Tensor, hist=None, variant: int = 0) -> torch.Tensor:
+        return ops.binary_auroc_from_keys(keys, hist, variant)
 
     @staticmethod
     def auprc_begin(keys: torch.Tensor, hist=None):
@@ -220,8 +222,8 @@ def _exchange_keys(score: torch.Tensor, target: torch.Tensor, group, tm: _PhaseT
     flags = 0
     for r in rows:
         flags |= int(r[world])
-    if flags:
-        return None, flags, None
+    if flags & ~_WIDE:
+        return None, flags & ~_WIDE, None
     splitters = [int(v) for v in rows[rank][world + 1 :]]
     send = [int(c) for c in rows[rank][:world]]
     recv = [int(rows[q][rank]) for q in range(world)]
@@ -252,7 +254,7 @@ def _exchange_keys(score: torch.Tensor, target: torch.Tensor, group, tm: _PhaseT
         inbox = torch.empty(sum(recv), dtype=keys.dtype, device=dev)
         dist.all_to_all_single(inbox, part, recv, send, group=group)
         tm.mark("all_to_all")
-    return inbox, 0, my_hist
+    return inbox, flags & _WIDE, my_hist
 
 
 def _sum_rows_to_owner(rows: torch.Tensor, world: int, rank: int, group) -> torch.Tensor:
@@ -295,10 +297,12 @@ def _sharded_binary_auroc(score, target, group):
     dev = score.device
     tm = _PhaseTimer(dev)
     inbox, flags, hist = _exchange_keys(score, target, group, tm)
-    if flags:
+    if flags & ~_WIDE:
         return _flags_only(flags, dev), flags
-    # --- local sort + integrate, then the fix-up of three integers per rank, on the device -------
-    loc = _local.auroc_from_keys(inbox, hist)
+    # --- local ordering + integrate, then the fix-up of three integers per rank, on the device ---
+    # (scores >= 2.0 somewhere: their keys need all 32 bits, which only the full sort handles; every
+    # rank takes the same branch, the flag was part of the one host read)
+    loc = _local.auroc_from_keys(inbox, hist, N_.TE_RANK_SORT if flags & _WIDE else N_.TE_RANK_AUTO)
     tm.mark("local_sort_sweep")
     rows = _gather_rows(loc, world, group)  # (W, 8) float64
     tm.mark("fix:gather")
@@ -331,7 +335,7 @@ def _sharded_binary_auprc(score, target, group):
     dev = score.device
     tm = _PhaseTimer(dev)
     inbox, flags, hist = _exchange_keys(score, target, group, tm)
-    if flags:
+    if flags & ~_WIDE:  # (wide keys are fine here: this path sorts all 32 bits)
         return _flags_only(flags, dev), flags
     loc, state = _local.auprc_begin(inbox, hist)
     tm.mark("local_sort_count")

@@ -436,9 +436,10 @@ def _hist_ptr(hist: Optional[torch.Tensor], dev) -> Optional[int]:
     return hist.data_ptr()
 
 
-def binary_auroc_from_keys(keys: torch.Tensor, hist: Optional[torch.Tensor] = None) -> torch.Tensor:
+def binary_auroc_from_keys(keys: torch.Tensor, hist: Optional[torch.Tensor] = None, variant: int = N.TE_RANK_AUTO) -> torch.Tensor:
     """float64[8] as te_binary_auroc_from_keys: [auroc, P, N, 2U, flags, 2U_hi32, 2U_lo32, n].
-    hist: int32[4 * 256] radix-digit histograms of `keys` if they are already known."""
+    hist: int32[4 * 256] radix-digit histograms of `keys` if they are already known (used by
+    TE_RANK_SORT).  variant: TE_RANK_* (te_binary_auroc_from_keys_variant)."""
     lib = N.load()
     dev = _require_cuda(keys)
     keys = keys.contiguous()
@@ -447,9 +448,9 @@ def binary_auroc_from_keys(keys: torch.Tensor, hist: Optional[torch.Tensor] = No
     scratch = _scratch(lib.te_binary_rank_scratch_bytes(n), dev)
     with torch.cuda.device(dev):
         N.check(
-            "te_binary_auroc_from_keys",
-            lib.te_binary_auroc_from_keys(keys.data_ptr(), n, _hist_ptr(hist, dev), out.data_ptr(), scratch.data_ptr(),
-                                          scratch.numel(), _stream_ptr(dev)),
+            "te_binary_auroc_from_keys_variant",
+            lib.te_binary_auroc_from_keys_variant(keys.data_ptr(), n, _hist_ptr(hist, dev), out.data_ptr(), scratch.data_ptr(),
+                                                  scratch.numel(), variant, _stream_ptr(dev)),
         )
     return out
 
