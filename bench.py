@@ -8,9 +8,13 @@ float32 scores + int64 {0,1} labels, rank-sharded over the GPUs (strong scaling:
 fixed, each of N ranks holds 2^30 / N).  One "step" = one full compute of the metric over the
 resident scores.  Also in the line, at 1 GPU: "secondary" (configs[1]: MulticlassConfusionMatrix
 update, C = 1000, 2^28 label pairs, GB/s against the HBM roofline), "secondary_binned" (configs[2]:
-10k-threshold binned counting over the same 2^30 scores) and "secondary_ovr" (configs[4] shape:
-one-vs-rest MulticlassAUROC, C = 1000, N = 2^20); at N GPUs: "secondary_binned" = binned update +
-counter all-reduce through toolkit.sync_and_compute.
+10k-threshold binned counting over the same 2^30 scores) and "secondary_ovr" (configs[4] at its
+stated size: one-vs-rest MulticlassAUROC, C = 1000, N = 2^24 samples, 1.7e10 scores); at N GPUs:
+"secondary_binned" = binned update + counter all-reduce through toolkit.sync_and_compute,
+"secondary_ovr" = the same 2^24 x 1000 matrix sample-sharded, through MulticlassAUROC +
+sync_and_compute (class-sharded transpose), and "parity": the sharded results checked, outside
+the timed region, against an independent single-GPU computation on the gathered keys and
+against closed forms on grid-valued scores.
 
 Prints ONE JSON line on rank 0 (see the task contract): value = device-timed whole-job
 throughput with inputs resident in HBM; e2e = same metric through the public functional API
@@ -52,12 +56,13 @@ def measured_peaks() -> tuple[float, str]:
 
 
 def ncu_traffic(kernel: str, n_records: int):
-    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture, or None when
-    the capture was taken on a different record count than this run."""
-    p = ROOT / "profiles" / "r01_ncu_traffic.json"
+    """DRAM bytes per launch of `kernel` (dram__bytes_read + dram__bytes_write of one
+    `ncu --set full` capture of this round's kernels, profiles/r02_ncu_traffic.json), scaled from
+    the record count of the capture to this run's: the kernels stream, traffic is per record."""
+    p = ROOT / "profiles" / "r02_ncu_traffic.json"
     try:
         t = json.loads(p.read_text())
-        return int(t[kernel]) if int(t["n_records"]) == int(n_records) else None
+        return int(round(float(t["bytes_per_record"][kernel]) * n_records))
     except Exception:
         return None
 
@@ -264,10 +269,12 @@ def run_ours(args) -> dict:
     secondary = None
     binned = None
     ovr = None
+    parity = None
     if world == 1:
-        binned = binned_bench(args, x, y, peak_gbs, peak_src)
+        binned = guarded(binned_bench, args, x, y, peak_gbs, peak_src)
     else:
-        binned = binned_sync_bench(args, x, y, world, device)
+        binned = guarded(binned_sync_bench, args, x, y, world, device)
+        parity = parity_checks(x, y, out, world, rank, device)  # raises: a wrong sharded result fails the run
     if world == 1:
         xh = torch.empty(n_local, dtype=torch.float32, pin_memory=True)
         yh = torch.empty(n_local, dtype=torch.int64, pin_memory=True)
@@ -294,8 +301,8 @@ def run_ours(args) -> dict:
         }
         cpu = cpu_baseline_auroc(xh, yh)
         del xh, yh
-        secondary = confusion_matrix_bench(args, device, peak_gbs, peak_src)
-        ovr = one_vs_rest_bench(args, device)
+        secondary = guarded(confusion_matrix_bench, args, device, peak_gbs, peak_src)
+        ovr = guarded(one_vs_rest_bench, args, device, peak_gbs, peak_src)
 
     if world > 1:
         # end to end at N GPUs through the class API + toolkit: every rank feeds its pinned HOST
@@ -334,6 +341,11 @@ def run_ours(args) -> dict:
             "steps": e2e_steps,
             "note": "per-rank bytes; class API update() + toolkit.sync_and_compute()",
         }
+
+    if world > 1:
+        del xh, yh
+        torch.cuda.empty_cache()
+        ovr = guarded(one_vs_rest_sharded_bench, args, world, rank, device)
 
     line = {
         "metric": "exact_binary_auroc_scores_per_sec",
@@ -377,6 +389,8 @@ def run_ours(args) -> dict:
         line["secondary_binned"] = binned
     if ovr:
         line["secondary_ovr"] = ovr
+    if parity:
+        line["parity"] = parity
     if world > 1:
         import torch.distributed as dist
 
@@ -490,34 +504,227 @@ def binned_sync_bench(args, x, y, world, device) -> dict:
     }
 
 
-def one_vs_rest_bench(args, device) -> dict:
-    """configs[4] shape at a size one step finishes in tens of milliseconds: MulticlassAUROC
-    one-vs-rest (segmented sort), C = 1000 classes, N = 2^20 samples = 1.05e9 scores on one GPU."""
+def guarded(fn, *a):
+    """A secondary line must never cost the primary one: failures are reported in place."""
+    try:
+        return fn(*a)
+    except Exception as e:  # noqa: BLE001
+        torch.cuda.empty_cache()
+        return {"error": f"{type(e).__name__}: {e}"[:300]}
+
+
+OVR_LOG2_N = int(os.environ.get("TE_BENCH_OVR_LOG2_N", "24"))
+OVR_CLASSES = 1000
+
+
+def _ovr_matrix(rows: int, C: int, device, seed: int):
+    """(rows, C) uniform float32 scores generated in row chunks into one allocation (67 GB at
+    2^24 x 1000: the input of configs[4] itself; nothing else of that size is ever held)."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    x = torch.empty((rows, C), device=device, dtype=torch.float32)
+    step = 1 << 18
+    for r0 in range(0, rows, step):
+        torch.rand((min(step, rows - r0), C), device=device, generator=g, dtype=torch.float32, out=x[r0 : r0 + step])
+    y = torch.randint(0, C, (rows,), device=device, generator=g, dtype=torch.int64)
+    return x, y
+
+
+def one_vs_rest_bench(args, device, peak_gbs, peak_src) -> dict:
+    """configs[4] at its stated size on one GPU: MulticlassAUROC one-vs-rest, C = 1000 classes,
+    N = 2^24 samples = 1.68e10 scores (67 GB of float32, resident; the segmented sort works through
+    it eight classes at a time with ~1 GB of scratch)."""
     from torcheval_b200 import ops
 
-    n, C = 1 << 20, 1000
-    g = torch.Generator(device=device).manual_seed(SEED + 5)
-    x = torch.rand((n, C), device=device, generator=g, dtype=torch.float32)
-    y = torch.randint(0, C, (n,), device=device, generator=g, dtype=torch.int64)
-    for _ in range(2):
-        out = ops.ovr_rank(x, y, False, 0)
+    n, C = 1 << OVR_LOG2_N, OVR_CLASSES
+    x, y = _ovr_matrix(n, C, device, SEED + 5)
+    out = ops.ovr_rank(x, y, False, 0)
     torch.cuda.synchronize()
-    steps = 3
+    steps = 2
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    for _ in range(steps):
-        out = ops.ovr_rank(x, y, False, 0)
-    ev1.record()
-    torch.cuda.synchronize()
+    with KernelProfile() as prof:
+        ev0.record()
+        for _ in range(steps):
+            out = ops.ovr_rank(x, y, False, 0)
+        ev1.record()
+        torch.cuda.synchronize()
+        kernels = prof.read()
     ms = ev0.elapsed_time(ev1) / steps
+    # closed form per class is not available for uniform scores; the macro mean of 1000 independent
+    # AUROCs of random labels must sit at 0.5 +- a few 1e-5, and every class must have seen n samples
+    counts_ok = bool(((out[:, 1] + out[:, 2]) == n).all().item()) and bool((out[:, 4] == 0).all().item())
+    macro = float(out[:, 0].mean().item())
+    assert counts_ok and abs(macro - 0.5) < 1e-3, (counts_ok, macro)
+    # SURVEY section 8d (K2): ingest reads N*C*4 and writes N*C*4 packed keys, P = 4 passes of 8 B, 4 B sweep
+    bytes_step = float(n) * C * (8 + 4 * 8 + 4)
+    gbs = bytes_step / (ms * 1e-3) / 1e9
+    dom = max(kernels, key=lambda k: kernels[k]["total_ms"]) if kernels else None
     return {
         "metric": "multiclass_auroc_one_vs_rest_scores_per_sec",
         "value": n * C / (ms * 1e-3),
         "unit": "scores/s",
         "ms_per_step": ms,
-        "config": {"workload": f"MulticlassAUROC one-vs-rest, C={C}, N=2^20 samples, float32 (N, C) scores, 1 GPU",
-                   "macro_auroc": float(out[:, 0].mean().item())},
+        "config": {"workload": f"MulticlassAUROC one-vs-rest, C={C}, N=2^{OVR_LOG2_N} samples, float32 (N, C) scores resident, 1 GPU",
+                   "macro_auroc": macro},
+        "roofline": {
+            "kernel": "whole step (ovr_ingest + 4 radix passes + sweep, 8 classes per launch)",
+            "bound": "hbm",
+            "achieved": round(gbs, 1),
+            "peak": peak_gbs,
+            "peak_source": peak_src,
+            "unit": "GB/s",
+            "frac": round(gbs / peak_gbs, 4),
+            "traffic": None,
+            "algorithmic_bytes_per_step": bytes_step,
+            "dominant_kernel": dom,
+            "kernels_ms_per_step": {k: round(v["total_ms"] / steps, 3) for k, v in kernels.items()},
+        },
     }
+
+
+def one_vs_rest_sharded_bench(args, world, rank, device) -> dict:
+    """configs[4] at N GPUs: the 2^24 x 1000 matrix sample-sharded (2^24 / N rows per rank), through
+    the class API: MulticlassAUROC.update + toolkit.sync_and_compute = class-sharded transpose
+    (one all_to_all), local segmented sorts of C / N classes, all_gather of the C values."""
+    from torcheval_b200.metrics import MulticlassAUROC
+    from torcheval_b200.metrics.toolkit import sync_and_compute
+
+    n, C = 1 << OVR_LOG2_N, OVR_CLASSES
+    rows = n // world
+    x, y = _ovr_matrix(rows, C, device, SEED + 5 + 97 * rank)
+
+    def step():
+        m = MulticlassAUROC(num_classes=C, average=None, device=device)
+        m.update(x, y)
+        return sync_and_compute(m)
+
+    out = step()
+    barrier(world)
+    steps = 2
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(steps):
+        out = step()
+    ev1.record()
+    barrier(world)
+    ms = max_over_ranks(ev0.elapsed_time(ev1), world, device) / steps
+    macro = float(out.double().mean().item())
+    assert out.numel() == C and abs(macro - 0.5) < 1e-3, macro
+    return {
+        "metric": "multiclass_auroc_one_vs_rest_scores_per_sec",
+        "value": n * C / (ms * 1e-3),
+        "unit": "scores/s",
+        "ms_per_step": ms,
+        "scaling": "strong",
+        "config": {"workload": f"MulticlassAUROC one-vs-rest, C={C}, N=2^{OVR_LOG2_N} samples sample-sharded over {world} GPUs, "
+                               "update + sync_and_compute (class-sharded all_to_all transpose)",
+                   "macro_auroc": macro},
+    }
+
+
+def parity_checks(x, y, out, world, rank, device) -> dict:
+    """Outside the timed region, at N > 1: the sharded results against computations that share no
+    code with the sample sort / all-reduce paths.  Any mismatch raises (the run fails).
+      1. gathered keys: every rank's packed keys are all-gathered; rank 0 computes AUROC over all
+         of them with the single-GPU kernel path and requires the sharded 2U, P, N digit for digit;
+      2. closed forms: scores on a 2^12-level grid, sharded by rank; the (level, label) histogram
+         (torch.bincount + all_reduce) gives 2U, AUROC and AUPRC in closed form, ties included;
+      3. binned counters: BinaryBinnedAUPRC.update + sync_and_compute against the 10k-threshold
+         histogram of the gathered scores computed on one GPU;
+      4. class-sharded one-vs-rest (MulticlassAUROC, 2^16 x 64) against the single-GPU kernel on
+         the gathered matrix."""
+    import numpy as np
+    import torch.distributed as dist
+
+    from torcheval_b200 import distributed as tdist
+    from torcheval_b200 import ops
+    from torcheval_b200.metrics import BinaryBinnedAUPRC, MulticlassAUROC
+    from torcheval_b200.metrics.toolkit import sync_and_compute
+
+    checked = []
+    n_local = x.numel()
+    sh = out.cpu().numpy()  # [auroc, P, N, 2U, flags, ...] of the timed sharded run
+
+    # 1 -----------------------------------------------------------------------------------------
+    keys = ops.rank_pack(x, y, ())[0]
+    allk = torch.empty(n_local * world, dtype=keys.dtype, device=device)
+    dist.all_gather_into_tensor(allk, keys)
+    del keys
+    ok = torch.ones(1, dtype=torch.int32, device=device)
+    if rank == 0:
+        one = ops.binary_auroc_from_keys(allk).cpu().numpy()
+        same = one[1] == sh[1] and one[2] == sh[2] and one[3] == sh[3] and one[4] == 0
+        ok[0] = 1 if same else 0
+        detail = {"single_gpu": [one[1], one[2], one[3]], "sharded": [sh[1], sh[2], sh[3]]}
+    dist.broadcast(ok, 0)
+    assert int(ok.item()) == 1, f"sharded AUROC differs from the single-GPU result on the gathered keys: {detail if rank == 0 else ''}"
+    checked.append(f"auroc_2U_P_N_vs_single_gpu_on_gathered_keys(n=2^{(n_local * world).bit_length() - 1})")
+
+    # 3 (uses the gathered keys) ----------------------------------------------------------------
+    T = 10_000
+    m = BinaryBinnedAUPRC(threshold=T, device=device)
+    m.update(x, y)
+    sync_and_compute(m)
+    from torcheval_b200.metrics.toolkit import get_synced_metric
+
+    synced = get_synced_metric(m)
+    if rank == 0:
+        xs = (allk >> 1).view(torch.float32)  # key = (float bits << 1) | label, bits < 2^31 here
+        ys = (allk & 1).to(torch.int64)
+        thr = torch.linspace(0, 1, T, device=device)
+        hist = torch.zeros((1, T + 1, 2), dtype=torch.int64, device=device)
+        ops.binned_hist_update_(hist, xs, ys, thr)
+        tp, fp, fn = ops.binned_counts(hist, T)
+        same = bool((synced.num_tp.to(torch.int64) == tp).all()) and bool((synced.num_fp.to(torch.int64) == fp).all())
+        ok[0] = 1 if same else 0
+        del xs, ys
+    dist.broadcast(ok, 0)
+    assert int(ok.item()) == 1, "synced binned counters differ from the single-GPU histogram of the gathered scores"
+    checked.append(f"binned_counts_T{T}_vs_single_gpu")
+    del allk
+    torch.cuda.empty_cache()
+
+    # 2 -----------------------------------------------------------------------------------------
+    G = 1 << 12
+    g = torch.Generator(device=device).manual_seed(SEED + 1000 + rank)
+    lev = torch.randint(0, G, (n_local,), device=device, generator=g)
+    yy = (torch.rand(n_local, device=device, generator=g) < 0.25).long()
+    xx = lev.float() / G
+    neg = torch.bincount(lev[yy == 0], minlength=G)
+    pos = torch.bincount(lev[yy == 1], minlength=G)
+    del lev
+    dist.all_reduce(neg)
+    dist.all_reduce(pos)
+    neg, pos = neg.cpu().numpy().astype(np.int64), pos.cpu().numpy().astype(np.int64)
+    below = np.concatenate([[0], np.cumsum(neg)[:-1]])
+    u2 = int(np.sum(pos.astype(object) * (2 * below.astype(object) + neg.astype(object))))
+    a = tdist.sharded_binary_auroc(xx, yy).cpu().numpy()
+    assert a[4] == 0 and a[1] == pos.sum() and a[2] == neg.sum() and int(a[3]) == u2 and float(u2) == a[3], (a, u2)
+    want = u2 / (2.0 * float(pos.sum()) * float(neg.sum()))
+    assert abs(a[0] - want) <= 1e-12 * want
+    ap = tdist.sharded_binary_auprc(xx, yy).cpu().numpy()
+    tp_ge = np.cumsum(pos[::-1])[::-1].astype(np.float64)
+    all_ge = np.cumsum((pos + neg)[::-1])[::-1].astype(np.float64)
+    want_ap = float(np.sum(pos * (tp_ge / np.maximum(all_ge, 1))) / pos.sum())
+    assert abs(ap[0] - want_ap) <= 1e-9 * want_ap, (ap[0], want_ap)
+    checked.append("auroc_exact_2U_and_auprc_vs_closed_form_on_grid_scores")
+    del xx, yy
+
+    # 4 -----------------------------------------------------------------------------------------
+    rows, C = (1 << 16) // world, 64
+    g = torch.Generator(device=device).manual_seed(SEED + 2000 + rank)
+    xm = torch.rand((rows, C), device=device, generator=g)
+    ym = torch.randint(0, C, (rows,), device=device, generator=g)
+    mm = MulticlassAUROC(num_classes=C, average=None, device=device)
+    mm.update(xm, ym)
+    got = sync_and_compute(mm).double()
+    allx = torch.empty((rows * world, C), device=device)
+    ally = torch.empty(rows * world, dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(allx, xm)
+    dist.all_gather_into_tensor(ally, ym)
+    ref = ops.ovr_rank(allx, ally, False, 0)[:, 0]
+    assert bool((torch.abs(got - ref) <= 1e-6 * ref).all()), "class-sharded one-vs-rest differs from the single-GPU result"
+    checked.append("multiclass_auroc_class_sharded_vs_single_gpu")
+    return {"checked": checked, "ok": True}
 
 
 def confusion_matrix_bench(args, device, peak_gbs, peak_src) -> dict:
@@ -605,33 +812,54 @@ def confusion_matrix_bench(args, device, peak_gbs, peak_src) -> dict:
 
 # ----------------------------------------------------------------------------------- reference arm
 def run_reference(args) -> dict:
-    """The reference's CPU path (port in oracle/oracle_torch.py: the same ATen op sequence) on the
-    host cores; each step is a bounded sample (2^24 scores) of the same synthetic workload."""
+    """The reference's CPU path — its own ATen op sequence, restated op for op in
+    oracle/oracle_torch.py because /root/reference does not exist on the GPU box — on all host
+    cores; each step is a bounded sample (2^25 scores, the same sample as the in-line cpu_baseline
+    of the GPU arm) of the same synthetic workload.  Also timed, once each, for BASELINE.md: the
+    confusion-matrix and binned-AUPRC reference paths at 2^24."""
     rank, world, _ = dist_env()
     if rank != 0:
         return {}
+    # torchrun exports OMP_NUM_THREADS=1; the reference arm is the CPU path at full strength
+    ncpu = os.cpu_count() or 1
+    torch.set_num_threads(ncpu)
     from oracle import oracle_torch
 
-    m = 1 << int(os.environ.get("TE_BENCH_REF_LOG2_N", "24"))
+    m = 1 << int(os.environ.get("TE_BENCH_REF_LOG2_N", "25"))
     g = torch.Generator().manual_seed(SEED)
     x = torch.rand(m, generator=g, dtype=torch.float32)
     y = torch.randint(0, 2, (m,), generator=g, dtype=torch.int64)
-    for _ in range(args.warmup):
+    for _ in range(min(args.warmup, 1)):
         oracle_torch.binary_auroc(x, y)
+    steps = max(1, min(args.steps, 3))  # ~4 s per step: keeps the run within a few minutes
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(steps):
         v = oracle_torch.binary_auroc(x, y)
-    dt = (time.perf_counter() - t0) / args.steps
+    dt = (time.perf_counter() - t0) / steps
     value = m / dt
-    sample = f"2^{m.bit_length() - 1} scores per step (bounded sample of the 2^{LOG2_N_TOTAL} workload)"
+    sample = f"2^{m.bit_length() - 1} scores per step (bounded sample of the 2^{LOG2_N_TOTAL} workload), {steps} timed steps"
+    extra = {}
+    try:
+        k = 1 << 24
+        for C in (10, 1000):
+            p_, t_ = torch.randint(0, C, (k,), generator=g), torch.randint(0, C, (k,), generator=g)
+            t0 = time.perf_counter()
+            oracle_torch.confusion_matrix(p_, t_, C)
+            extra[f"confusion_matrix_C{C}_2p24_samples_per_s"] = k / (time.perf_counter() - t0)
+        thr = torch.linspace(0, 1, 10_000)
+        t0 = time.perf_counter()
+        oracle_torch.binned_counts(x[:k], y[:k], thr)
+        extra["binned_counts_T10000_2p24_scores_per_s"] = k / (time.perf_counter() - t0)
+    except Exception as e:  # noqa: BLE001
+        extra["error"] = str(e)[:200]
     return {
         "impl": "reference",
         "metric": "exact_binary_auroc_scores_per_sec",
         "value": value,
         "unit": "scores/s",
         "n_gpus": args.gpus,
-        "steps": args.steps,
-        "warmup": args.warmup,
+        "steps": steps,
+        "warmup": min(args.warmup, 1),
         "ms_per_step": dt * 1e3,
         "higher_is_better": True,
         "scaling": "strong",
@@ -643,8 +871,10 @@ def run_reference(args) -> dict:
             "sample": sample,
             "auroc": float(v),
         },
-        "cpu_baseline": {"value": value, "unit": "scores/s", "cores": torch.get_num_threads(), "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "scores/s", "cores": torch.get_num_threads(), "host_cpus": ncpu,
+                         "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "scores/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "other_reference_paths": extra,
     }
 
 

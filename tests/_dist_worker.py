@@ -29,14 +29,25 @@ def main():
     cpu_backend.install()
     from torcheval_b200 import distributed as tdist
     from torcheval_b200.metrics import (
-        BinaryAUPRC, BinaryAUROC, BinaryBinnedAUPRC, MulticlassAccuracy, MulticlassAUPRC, MulticlassAUROC,
-        MulticlassConfusionMatrix, MultilabelAUPRC,
+        BinaryAUPRC, BinaryAUROC, BinaryBinnedAUPRC, Metric, MulticlassAccuracy, MulticlassAUPRC, MulticlassAUROC,
+        MulticlassConfusionMatrix, MultilabelAUPRC, WindowedBinaryAUROC,
     )
     from torcheval_b200.metrics import toolkit
 
     res = {}
-    calls = {"auprc": 0, "ovr": 0}
+    calls = {"auprc": 0, "ovr": 0, "auroc": 0, "gather": 0}
     real_auprc, real_ovr = tdist._sharded_binary_auprc, tdist.class_sharded_one_vs_rest
+    real_auroc, real_gather = tdist._sharded_binary_auroc, toolkit._gather_metrics
+
+    def counting_auroc(*a, **k):
+        calls["auroc"] += 1
+        return real_auroc(*a, **k)
+
+    def counting_gather(*a, **k):
+        calls["gather"] += 1
+        return real_gather(*a, **k)
+
+    tdist._sharded_binary_auroc, toolkit._gather_metrics = counting_auroc, counting_gather
 
     def counting_auprc(*a, **k):
         calls["auprc"] += 1
@@ -139,6 +150,37 @@ def main():
     )
     res["ovr/two_classes"] = [toolkit.sync_and_compute(m4).tolist(), oracle.multiclass_auroc(x2, y2).tolist()]
     res["calls"] = [calls["auprc"], calls["ovr"]]
+    # a collection mixing every kind of member: the exact metrics take their sharded paths (nobody
+    # gathers their samples), the counters share one all-reduce, the weighted AUROC and the windowed
+    # metric — no sharded path — share ONE flat all-gather
+    x, y = cases["ties"]
+    xs_, ys_ = torch.from_numpy(shard(x, rank, world)), torch.from_numpy(shard(y, rank, world))
+    ws_ = torch.from_numpy(shard(w, rank, world))
+    before = dict(calls)
+    coll = toolkit.sync_and_compute_collection({
+        "auroc": BinaryAUROC().update(xs_, ys_),
+        "cm": cm,
+        "auprc": BinaryAUPRC().update(xs_, ys_),
+        "mc": MulticlassAUROC(num_classes=CC, average=None).update(torch.from_numpy(xi[sl]), torch.from_numpy(yi[sl])),
+        "bb": bb,
+        "weighted": BinaryAUROC().update(xs_, ys_, ws_),
+        "windowed": WindowedBinaryAUROC(max_num_samples=50).update(xs_[:50], ys_[:50]),
+    })
+    res["coll2/auroc"] = [float(coll["auroc"]), oracle.binary_auroc(x, y)[0]]
+    res["coll2/auprc"] = [float(coll["auprc"]), oracle.binary_auprc(x, y)]
+    res["coll2/weighted"] = [float(coll["weighted"]), oracle.binary_auroc(x, y, w)[0]]
+    res["coll2/mc"] = [coll["mc"].tolist(), oracle.multiclass_auroc(xi, yi).tolist()]
+    res["coll2/cm_equal"] = bool(np.array_equal(coll["cm"].numpy(), oracle.confusion_matrix(p, t, C)[0].astype(np.float32)))
+    res["coll2/paths"] = [
+        [calls["auroc"] - before["auroc"], calls["auprc"] - before["auprc"], calls["ovr"] - before["ovr"], calls["gather"] - before["gather"]],
+        [1, 1, 1, 1],
+    ]
+    # more ranks than the sample sort has splitters for: everybody takes the generic path together
+    tdist.MAX_SAMPLE_SORT_RANKS = world - 1
+    before = dict(calls)
+    res["sync/over_cap"] = [float(toolkit.sync_and_compute(BinaryAUROC().update(xs_, ys_))), oracle.binary_auroc(x, y)[0]]
+    res["sync/over_cap_paths"] = [[calls["auroc"] - before["auroc"]], [0]]
+    tdist.MAX_SAMPLE_SORT_RANKS = 16
     # a rank with no data: generic object path still works
     me = BinaryAUROC()
     if rank != 0:
@@ -149,8 +191,6 @@ def main():
     except Exception as e:  # noqa: BLE001
         res["sync/empty_rank_ok"] = f"raised {type(e).__name__}: {e}"
     # a user-defined metric with every kind of state (tensor, list, dict, int): the generic path
-    from torcheval_b200.metrics import Metric, WindowedBinaryAUROC
-
     class Toy(Metric):
         def __init__(self):
             super().__init__()

@@ -40,7 +40,9 @@ def test_sample_sort_and_toolkit_sync(world, port, tmp_path):
             got, want, P, tp, N, fp = val
             np.testing.assert_allclose(got, want, rtol=1e-12, err_msg=key)
             assert (P, N) == (tp, fp), key
-        elif key in ("sync/cm_equal", "sync/cm_input_unchanged", "sync/empty_rank_ok"):
+        elif key in ("coll2/paths", "sync/over_cap_paths"):
+            assert val[0] == val[1], (key, val)
+        elif key in ("sync/cm_equal", "sync/cm_input_unchanged", "sync/empty_rank_ok", "coll2/cm_equal"):
             assert val is True, (key, val)
         elif key == "generic/toy_meta":
             assert val[0] == val[1], val

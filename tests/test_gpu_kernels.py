@@ -745,6 +745,65 @@ def test_ovr_rank_vs_oracle(ops, n, C):
     np.testing.assert_array_equal(a3[1:, 0], a[1:, 0])
 
 
+def test_ovr_config5_classes_closed_form(ops):
+    """BASELINE configs[4] shape at C = 1000 with N = 2^20 rows (1.05e9 scores): scores on a
+    256-level grid, so per class the exact integer 2U, AUROC and the average precision follow in
+    closed form from that class's (level, label) histogram — ties on every level."""
+    n, C, G = 1 << 20, 1000, 256
+    g = torch.Generator(device="cuda").manual_seed(55)
+    lev = torch.randint(0, G, (n, C), device="cuda", generator=g, dtype=torch.int16)
+    y = torch.randint(0, C, (n,), device="cuda", generator=g)
+    y[y == 7] = 8  # class 7 never occurs: AUROC 0.5, AUPRC -0.0
+    x = lev.float() / G
+    # (class, level) histograms of all rows and of the positive rows
+    all_h = torch.zeros(C * G, dtype=torch.int64, device="cuda")
+    cls = torch.arange(C, device="cuda", dtype=torch.int64) * G
+    for r0 in range(0, n, 1 << 16):
+        idx = (lev[r0 : r0 + (1 << 16)].long() + cls).reshape(-1)
+        all_h += torch.bincount(idx, minlength=C * G)
+    pos_h = torch.bincount(y * G + lev[torch.arange(n, device="cuda"), y].long(), minlength=C * G)
+    allh = all_h.reshape(C, G).cpu().numpy()
+    pos = pos_h.reshape(C, G).cpu().numpy()
+    neg = allh - pos
+    del lev, all_h, pos_h
+    below = np.cumsum(neg, axis=1) - neg
+    u2 = (pos * (2 * below + neg)).sum(axis=1)  # < 2^53: exact in the float64 the kernel reports
+    P, N = pos.sum(axis=1), neg.sum(axis=1)
+    a = ops.ovr_rank(x, y, False, 0).cpu().numpy()
+    assert (a[:, 4] == 0).all()
+    np.testing.assert_array_equal(a[:, 1], P)
+    np.testing.assert_array_equal(a[:, 2], N)
+    np.testing.assert_array_equal(a[:, 3], u2.astype(np.float64))
+    want = np.where(P * N == 0, 0.5, u2 / np.maximum(2.0 * P * N, 1))
+    np.testing.assert_allclose(a[:, 0], want, rtol=1e-12)
+    assert a[7, 0] == 0.5
+    p = ops.ovr_rank(x, y, False, 1).cpu().numpy()
+    tp_ge = np.cumsum(pos[:, ::-1], axis=1)[:, ::-1].astype(np.float64)
+    all_ge = np.cumsum(allh[:, ::-1], axis=1)[:, ::-1].astype(np.float64)
+    ap = (pos * (tp_ge / np.maximum(all_ge, 1))).sum(axis=1) / np.maximum(P, 1)
+    keep = P > 0
+    np.testing.assert_allclose(p[keep, 0], ap[keep], rtol=1e-9)
+    assert p[7, 0] == 0 and np.signbit(p[7, 0])
+    # multilabel targets (n, C) int64 at C = 1000 (2^17 rows: 1 GB of targets)
+    m = 1 << 17
+    ml = (torch.rand((m, C), device="cuda", generator=g) < 0.1).long()
+    xm = x[:m]
+    q = ops.ovr_rank(xm, ml, True, 1).cpu().numpy()
+    levm = (xm * G).long()
+    pos_m = torch.zeros(C * G, dtype=torch.int64, device="cuda")
+    all_m = torch.zeros(C * G, dtype=torch.int64, device="cuda")
+    for r0 in range(0, m, 1 << 15):
+        idx = (levm[r0 : r0 + (1 << 15)] + cls).reshape(-1)
+        all_m += torch.bincount(idx, minlength=C * G)
+        pos_m += torch.bincount(idx, weights=ml[r0 : r0 + (1 << 15)].reshape(-1).double(), minlength=C * G).long()
+    posm, allm = pos_m.reshape(C, G).cpu().numpy(), all_m.reshape(C, G).cpu().numpy()
+    tp_ge = np.cumsum(posm[:, ::-1], axis=1)[:, ::-1].astype(np.float64)
+    all_ge = np.cumsum(allm[:, ::-1], axis=1)[:, ::-1].astype(np.float64)
+    apm = (posm * (tp_ge / np.maximum(all_ge, 1))).sum(axis=1) / posm.sum(axis=1)
+    np.testing.assert_allclose(q[:, 0], apm, rtol=1e-9)
+    np.testing.assert_array_equal(q[:, 1], posm.sum(axis=1))
+
+
 def test_functional_multiclass_with_negative_columns(ops):
     from torcheval_b200.metrics import functional as F
 

@@ -60,6 +60,12 @@ def test_noalloc_matches_te_cm_update_on_two_calls_in_a_row():
         np.testing.assert_array_equal(got1, want1)  # integer counts: no tolerance
         np.testing.assert_array_equal(rng1, wrng1)
     assert got1.sum() == n1
+    # ... and against the CPU oracle itself, not only against the entry point it mirrors
+    import oracle
+
+    want_cpu, bad, _ = oracle.confusion_matrix(p1.cpu().numpy(), t1.cpu().numpy(), C1)
+    assert not bad
+    np.testing.assert_array_equal(got1, want_cpu)
 
     # call 2, right after: fewer classes, out-of-range labels, an unaligned view, accumulation
     # into a matrix that already holds counts
@@ -71,6 +77,9 @@ def test_noalloc_matches_te_cm_update_on_two_calls_in_a_row():
     got2, rng2 = _noalloc_counts(lib, p2, t2, C2, cm2)
     want2, wrng2 = _reference_counts(lib, p2.clone(), t2.clone(), C2, _native.TE_CM_GLOBAL32)
     np.testing.assert_array_equal(got2, want2 + 7)
+    keep = ((p2 >= 0) & (p2 < C2) & (t2 >= 0) & (t2 < C2)).cpu().numpy()  # out-of-range samples are not counted
+    want2_cpu, _, _ = oracle.confusion_matrix(p2.cpu().numpy()[keep], t2.cpu().numpy()[keep], C2)
+    np.testing.assert_array_equal(got2, want2_cpu + 7)
     np.testing.assert_array_equal(rng2, wrng2)
     assert list(rng2) == [99, 99, -4, -4] and got2.sum() == 7 * C2 * C2 + n2 - 2
 

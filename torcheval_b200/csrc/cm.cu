@@ -971,6 +971,9 @@ static __device__ __align__(256) uint32_t g_cm_static_bins[TE_CM_NOALLOC_MAX_CLA
 
 namespace {
 constexpr int kMaxDevices = 64;
+// Device address of g_cm_static_bins per device, filled on first use.  Written without a lock:
+// two host threads making the first call on one device at the same time both look the symbol up
+// and store the SAME address, so the race is benign (an aligned pointer store is not torn).
 uint32_t* g_static_bins_ptr[kMaxDevices] = {};
 }  // namespace
 

@@ -1057,15 +1057,25 @@ inline bool range_pass_from_env() {
 template <typename TargetT>
 int leaf_passes_ranges(const RankPlan& p, void* scratch, const float* score, const TargetT* target,
                        const uint32_t* raw_keys, uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st) {
-  auto part = partition_ranges_kernel<RadixDigit>;
-  const size_t part_smem = (size_t)2 * kPrTile * sizeof(uint32_t);
+  static const bool small_tiles = [] {
+    const char* e = getenv("TE_B200_PART_BLOCK");
+    return e && atoi(e) == kPrBlockSmall;
+  }();
+  const int pblock = small_tiles ? kPrBlockSmall : kPrBlock;
+  auto part = small_tiles ? partition_ranges_kernel<RadixDigit, kPrBlockSmall, kPrIptSmall>
+                          : partition_ranges_kernel<RadixDigit, kPrBlock, kPrIpt>;
+  const size_t part_smem = (size_t)2 * pblock * (small_tiles ? kPrIptSmall : kPrIpt) * sizeof(uint32_t);
   TE_CUDA_TRY(cudaFuncSetAttribute(part, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)part_smem));
   int per_sm = 0;
-  TE_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, part, kPrBlock, part_smem));
+  TE_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, part, pblock, part_smem));
   if (per_sm < 1) return TE_ERR_UNSUPPORTED;
-  int resident = per_sm * sms;
-  if (resident > (int)kMaxRanges) resident = kMaxRanges;
-  const RangeGeom rg = range_geom(p.n, resident);
+  // the ingest wants ~3 CTAs of 512 threads per SM to saturate HBM, the downsweep runs per_sm
+  // (1 for the 1024-thread geometry): a downsweep CTA takes `rpc` consecutive ingest ranges
+  const int rpc = per_sm >= 3 ? 1 : (per_sm == 2 ? 2 : 3);
+  int resident = per_sm * sms * rpc;
+  if (resident > (int)kMaxRanges) resident = kMaxRanges / rpc * rpc;
+  RangeGeom rg = range_geom(p.n, resident);
+  const uint32_t part_grid = (rg.ranges + rpc - 1) / rpc;
   uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
   uint32_t* range_hist = at<uint32_t>(scratch, p.off_range_hist);
   uint32_t* range_base = at<uint32_t>(scratch, p.off_range_base);
@@ -1076,14 +1086,14 @@ int leaf_passes_ranges(const RankPlan& p, void* scratch, const float* score, con
     TE_CUDA_TRY(cudaFuncSetAttribute(ing, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kIrSmem));
     TE_PROF("rank_hist_ranges", st);
     ing<<<rg.ranges, kIrBlock, kIrSmem, st>>>(reinterpret_cast<const float*>(raw_keys), nullptr, p.n,
-                                              ((uintptr_t)raw_keys & 15) == 0, rg.tiles_per_range, nullptr, hist,
+                                              ((uintptr_t)raw_keys & 15) == 0, rg.range_records, nullptr, hist,
                                               range_hist, flags);
   } else {
     auto ing = rank_ingest_ranges_kernel<TargetT, false>;
     TE_CUDA_TRY(cudaFuncSetAttribute(ing, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kIrSmem));
     TE_PROF("rank_ingest_ranges", st);
     ing<<<rg.ranges, kIrBlock, kIrSmem, st>>>(score, target, p.n, (((uintptr_t)score | (uintptr_t)target) & 15) == 0,
-                                              rg.tiles_per_range, ka, hist, range_hist, flags);
+                                              rg.range_records, ka, hist, range_hist, flags);
   }
   TE_LAUNCH_CHECK();
   {
@@ -1097,7 +1107,8 @@ int leaf_passes_ranges(const RankPlan& p, void* scratch, const float* score, con
   uint32_t* out2 = raw_keys ? kb : ka;
   {
     TE_PROF("partition_ranges", st);
-    part<<<rg.ranges, kPrBlock, part_smem, st>>>(in1, out1, p.n, RadixDigit{kLeafBits}, range_base, rg.tiles_per_range, skip);
+    part<<<part_grid, pblock, part_smem, st>>>(in1, out1, p.n, RadixDigit{kLeafBits}, range_base, rg.range_records,
+                                               (uint32_t)rpc, skip);
   }
   TE_LAUNCH_CHECK();
   // second pass: the look-back kernel, stable, on bits 23..30 (its look-back rows are the memset ones)

@@ -19,22 +19,28 @@
 
 namespace te {
 
-constexpr int kPrBlock = 512;
-constexpr int kPrIpt = 16;
-constexpr int kPrTile = kPrBlock * kPrIpt;  // 8192 records
+// Downsweep geometry: 1024 threads x 24 records = 24 576-record tiles, one CTA per SM.  The runs a
+// tile writes per digit are 96 records long on average; with 8192-record tiles (32-record runs, three
+// CTAs per SM) the same kernel took 3.38 ms instead of 2.50 ms at 2^30 keys, with 4096-record tiles
+// 4.33 ms (profiles/r02_part_block.txt): the length of the output bursts decides.
+constexpr int kPrBlock = 1024;
+constexpr int kPrIpt = 24;
+constexpr int kPrBlockSmall = 512, kPrIptSmall = 16;  // the 8192-record geometry (TE_B200_PART_BLOCK=512)
 constexpr int kIrBlock = 512;
 constexpr size_t kIrSmem = (size_t)2 * kRadix * kWarp * sizeof(uint32_t);  // two lane-replicated histograms: 64 KB
 
 struct RangeGeom {
-  uint32_t ranges, tiles_per_range;
+  uint32_t ranges, range_records;  // records per range: a multiple of kRangeUnit
 };
+constexpr uint32_t kRangeUnit = 24576;  // a multiple of the tile sizes of both downsweep geometries (1024 x 24 and 512 x 16)
 inline RangeGeom range_geom(uint32_t n, int resident_ctas) {
   RangeGeom g;
-  uint32_t tiles = (n + kPrTile - 1) / kPrTile;
-  if (tiles < 1) tiles = 1;
-  uint32_t want = (uint32_t)resident_ctas < tiles ? (uint32_t)resident_ctas : tiles;
-  g.tiles_per_range = (tiles + want - 1) / want;
-  g.ranges = (tiles + g.tiles_per_range - 1) / g.tiles_per_range;
+  uint32_t units = (n + kRangeUnit - 1) / kRangeUnit;
+  if (units < 1) units = 1;
+  const uint32_t want = (uint32_t)resident_ctas < units ? (uint32_t)resident_ctas : units;
+  const uint32_t per = (units + want - 1) / want;
+  g.range_records = per * kRangeUnit;
+  g.ranges = (units + per - 1) / per;
   return g;
 }
 
@@ -45,14 +51,14 @@ inline RangeGeom range_geom(uint32_t n, int resident_ctas) {
 template <typename TargetT, bool RAW_KEYS>
 __global__ void __launch_bounds__(kIrBlock)
     rank_ingest_ranges_kernel(const float* __restrict__ score, const TargetT* __restrict__ target, uint32_t n,
-                              bool vec_ok, uint32_t tiles_per_range, uint32_t* __restrict__ keys_out,
+                              bool vec_ok, uint32_t range_records, uint32_t* __restrict__ keys_out,
                               uint32_t* ghist, uint32_t* __restrict__ range_hist, uint32_t* flags) {
   extern __shared__ uint32_t sh[];  // [2][256][32 lanes]
   const unsigned tid = threadIdx.x, lane = tid & 31;
   for (int i = tid; i < 2 * kRadix * kWarp; i += kIrBlock) sh[i] = 0;
   __syncthreads();
-  const uint64_t e0 = (uint64_t)blockIdx.x * tiles_per_range * kPrTile;
-  const uint32_t e1 = (uint32_t)min((uint64_t)n, e0 + (uint64_t)tiles_per_range * kPrTile);
+  const uint64_t e0 = (uint64_t)blockIdx.x * range_records;
+  const uint32_t e1 = (uint32_t)min((uint64_t)n, e0 + (uint64_t)range_records);
   uint32_t bad_label = 0, neg_score = 0, wide = 0;
   for (uint64_t i64 = e0 + 4ull * tid; i64 < e1; i64 += 4ull * kIrBlock) {
     const uint32_t i0 = (uint32_t)i64;
@@ -161,60 +167,66 @@ __device__ __forceinline__ void cp_async_wait() {
 // thread holds its records in registers by then) and written out: the kernel was bound by the
 // latency of the loads at the head of every tile (ncu: long_scoreboard the top stall, LSU data
 // pipe at 52 %: profiles/r02_ncu_summary_v1.txt), not by the pipe.
-template <typename DigitOp>
-__global__ void __launch_bounds__(kPrBlock, 3)
+template <typename DigitOp, int BLOCK = kPrBlock, int IPT = kPrIpt>
+__global__ void __launch_bounds__(BLOCK, BLOCK >= 1024 ? 1 : 3)
     partition_ranges_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out, uint32_t n,
-                            const DigitOp dop, const uint32_t* __restrict__ range_base, uint32_t tiles_per_range,
-                            const uint32_t* __restrict__ skip_flag) {
-  extern __shared__ __align__(16) uint32_t s_buf[];  // [2][kPrTile]
+                            const DigitOp dop, const uint32_t* __restrict__ range_base, uint32_t range_records,
+                            uint32_t ranges_per_cta, const uint32_t* __restrict__ skip_flag) {
+  extern __shared__ __align__(16) uint32_t s_buf[];  // [2][TILE]
+  constexpr int TILE = BLOCK * IPT;
+  static_assert(IPT % 4 == 0 && TILE <= 65536, "16-byte slots; ranks are packed as 16-bit halves");
+  static_assert(kRangeUnit % TILE == 0 && BLOCK >= kRadix, "ranges are made of whole tiles");
   __shared__ uint32_t s_cnt[kRadix], s_start[kRadix], s_goff[kRadix], s_wsum[kRadix / kWarp];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const uint32_t ntiles = (n + kPrTile - 1) / kPrTile;
-  const uint32_t t0 = blockIdx.x * tiles_per_range;
-  const uint32_t t1 = min(ntiles, t0 + tiles_per_range);
+  const uint32_t ntiles = (n + TILE - 1) / TILE;
+  // a CTA takes ranges_per_cta consecutive ranges: where one range ends in the output of a digit
+  // is where the next one starts, so only the first range's bases are needed
+  const uint32_t tiles_per_cta = range_records / TILE * ranges_per_cta;
+  const uint32_t t0 = blockIdx.x * tiles_per_cta;
+  const uint32_t t1 = min(ntiles, t0 + tiles_per_cta);
   const bool skip_pass = skip_flag ? ld_relaxed_u32(skip_flag) != 0u : false;
-  uint32_t run = tid < kRadix ? range_base[(size_t)blockIdx.x * kRadix + tid] : 0u;  // output offset of digit tid
+  uint32_t run = tid < kRadix ? range_base[(size_t)blockIdx.x * ranges_per_cta * kRadix + tid] : 0u;  // output offset of digit tid
   if (tid < kRadix) s_cnt[tid] = 0u;
-  auto rec = [&](int i) -> uint32_t { return (((uint32_t)i >> 2) * kPrBlock + tid) * 4u + ((uint32_t)i & 3u); };
+  auto rec = [&](int i) -> uint32_t { return (((uint32_t)i >> 2) * BLOCK + tid) * 4u + ((uint32_t)i & 3u); };
   // full tiles travel through cp.async; a partial one (the last of the array) is read directly
   auto prefetch = [&](uint32_t tile) {
-    if (tile < t1 && (uint64_t)(tile + 1) * kPrTile <= n) {
-      uint32_t* dst = s_buf + (tile & 1u) * kPrTile;
-      const uint32_t* src = keys_in + (size_t)tile * kPrTile;
+    if (tile < t1 && (uint64_t)(tile + 1) * TILE <= n) {
+      uint32_t* dst = s_buf + (tile & 1u) * TILE;
+      const uint32_t* src = keys_in + (size_t)tile * TILE;
 #pragma unroll
-      for (int q = 0; q < kPrIpt / 4; ++q) cp_async_16(dst + rec(4 * q), src + rec(4 * q));
+      for (int q = 0; q < IPT / 4; ++q) cp_async_16(dst + rec(4 * q), src + rec(4 * q));
     }
     cp_async_commit();  // (an empty group keeps the wait_group arithmetic uniform)
   };
   prefetch(t0);
   for (uint32_t tile = t0; tile < t1; ++tile) {
-    const uint32_t base = tile * (uint32_t)kPrTile;
-    const uint32_t valid = min((uint32_t)kPrTile, n - base);
-    uint32_t* s_keys = s_buf + (tile & 1u) * kPrTile;
+    const uint32_t base = tile * (uint32_t)TILE;
+    const uint32_t valid = min((uint32_t)TILE, n - base);
+    uint32_t* s_keys = s_buf + (tile & 1u) * TILE;
     prefetch(tile + 1);   // into the half whose tile left at the end of the previous round
     cp_async_wait<1>();   // everything but the newest group: this tile has landed
     __syncthreads();
-    uint32_t key[kPrIpt];
-    if (valid == (uint32_t)kPrTile) {
+    uint32_t key[IPT];
+    if (valid == (uint32_t)TILE) {
 #pragma unroll
-      for (int q = 0; q < kPrIpt / 4; ++q) {
+      for (int q = 0; q < IPT / 4; ++q) {
         const uint4 a = *reinterpret_cast<const uint4*>(s_keys + rec(4 * q));
         key[4 * q] = a.x, key[4 * q + 1] = a.y, key[4 * q + 2] = a.z, key[4 * q + 3] = a.w;
       }
     } else {
 #pragma unroll
-      for (int i = 0; i < kPrIpt; ++i) key[i] = rec(i) < valid ? keys_in[base + rec(i)] : 0u;
+      for (int i = 0; i < IPT; ++i) key[i] = rec(i) < valid ? keys_in[base + rec(i)] : 0u;
     }
     if (skip_pass) {  // one digit value only: the order stays as it is
 #pragma unroll
-      for (int i = 0; i < kPrIpt; ++i)
+      for (int i = 0; i < IPT; ++i)
         if (rec(i) < valid) keys_out[base + rec(i)] = key[i];
       continue;
     }
     // ---- rank: arrival order inside the digit, straight from the CTA-wide counters ----
-    uint32_t rk[kPrIpt / 2];
+    uint32_t rk[IPT / 2];
 #pragma unroll
-    for (int i = 0; i < kPrIpt; ++i) {
+    for (int i = 0; i < IPT; ++i) {
       const uint32_t r = rec(i) < valid ? atomicAdd(&s_cnt[dop(key[i])], 1u) : 0u;
       if (i & 1)
         rk[i >> 1] |= r << 16;
@@ -246,15 +258,15 @@ __global__ void __launch_bounds__(kPrBlock, 3)
     __syncthreads();
     // ---- scatter into tile order ----
 #pragma unroll
-    for (int i = 0; i < kPrIpt; ++i) {
+    for (int i = 0; i < IPT; ++i) {
       const uint32_t r = (i & 1) ? rk[i >> 1] >> 16 : rk[i >> 1] & 0xffffu;
       if (rec(i) < valid) s_keys[s_start[dop(key[i])] + r] = key[i];
     }
     __syncthreads();
     // ---- output: every digit run leaves as one contiguous burst ----
 #pragma unroll
-    for (int k = 0; k < kPrIpt; ++k) {
-      const uint32_t p = tid + k * kPrBlock;
+    for (int k = 0; k < IPT; ++k) {
+      const uint32_t p = tid + k * BLOCK;
       if (p < valid) {
         const uint32_t kk = s_keys[p];
         keys_out[s_goff[dop(kk)] + p] = kk;

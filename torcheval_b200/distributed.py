@@ -29,6 +29,7 @@ from . import _native as N_
 from . import ops
 
 _WIDE = N_.TE_RANK_FLAG_WIDE_SCORE  # informational flag of the pack kernel: not a reason to leave the packed path
+MAX_SAMPLE_SORT_RANKS = 16  # kMaxSplitters + 1 of csrc/rank_sort.cuh
 SAMPLES_PER_RANK = 4096
 # All samples are sorted by ONE thread block (te_select_splitters, bitonic in shared memory:
 # 0.05 ms for 8192 keys, 0.3 ms for 32768), so the pool is capped; 8192 samples put the quantile
@@ -454,6 +455,9 @@ def try_sharded_compute(metric, group: Optional[dist.ProcessGroup] = None):
     ok = len(metric.inputs) > 0
     if is_auroc or is_auprc:
         ok = ok and metric.num_tasks == 1 and metric.inputs[0].dim() == 1
+        # the sample sort picks at most MAX_SAMPLE_SORT_RANKS - 1 splitters (te_select_splitters,
+        # the partition kernels): larger groups take the generic gather path, like any other metric
+        ok = ok and dist.get_world_size(group) <= MAX_SAMPLE_SORT_RANKS
         if is_auroc:
             ok = ok and _resolve_weights(metric.inputs, metric.weights) is None
     xs = None
