@@ -1010,6 +1010,10 @@ int finish_leaf(const RankPlan& p, const uint32_t* keys, double* out, void* scra
     leaf_seg_bounds_kernel<<<(kLeafSegs + 1 + 255) / 256, 256, 0, st>>>(keys, p.n, seg_start);
   }
   {
+    TE_PROF("leaf_tiny", st);
+    leaf_tiny_kernel<<<kLeafSegs / 8, 256, 0, st>>>(keys, seg_start, stats);
+  }
+  {
     TE_PROF("leaf_plan", st);
     leaf_plan_kernel<<<1, 1024, 0, st>>>(seg_start, p.leaf_piece, p.leaf_max_items, p.leaf_max_slabs, items, multi, hdr);
   }

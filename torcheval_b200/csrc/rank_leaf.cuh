@@ -36,6 +36,7 @@ constexpr size_t kLeafSmem = (size_t)kLeafBins * sizeof(uint32_t);  // 128 KB
 constexpr int kLeafWarps = kLeafBlock / kWarp;
 constexpr int kLeafVecPerThread = (int)(kLeafBins / 4 / kLeafBlock);  // uint4 per thread: 8
 constexpr uint32_t kLeafMinPiece = 1u << 17, kLeafMaxPiece = 1u << 20;
+constexpr uint32_t kLeafTiny = 128;  // segments of at most this many keys never see a histogram (leaf_tiny_kernel)
 
 struct LeafItem {   // one piece of one segment
   uint32_t seg, begin, end;
@@ -81,7 +82,7 @@ __global__ void __launch_bounds__(1024)
   auto pieces_of = [&](uint32_t s, uint32_t& b, uint32_t& e) -> uint32_t {
     b = seg_start[s], e = seg_start[s + 1];
     const uint32_t cnt = e > b ? e - b : 0u;
-    return (cnt + piece - 1) / piece;
+    return cnt <= kLeafTiny ? 0u : (cnt + piece - 1) / piece;  // (tiny segments: leaf_tiny_kernel)
   };
   uint32_t n_it = 0, n_sl = 0, n_mu = 0;
 #pragma unroll 4
@@ -137,6 +138,54 @@ __global__ void __launch_bounds__(1024)
     at_it += __shfl_sync(kFull, i_it, 31);
     at_sl += __shfl_sync(kFull, i_sl, 31);
     at_mu += __shfl_sync(kFull, i_mu, 31);
+  }
+}
+
+// Segments of at most kLeafTiny keys — for [0, 1) scores the thousands of segments of the low
+// binades — are not worth clearing and walking 32 768 counters (~2 us of a whole CTA each): one
+// WARP takes such a segment, four keys per lane, and counts pairs directly.  With packed keys
+// (value << 1 | label) a positive ki and a negative kj contribute
+//     2 [v_j < v_i] + [v_j == v_i]  =  [kj < ki] + [kj + 1 < ki],
+// so sources that are not negatives are replaced by 0xfffffffe (no key of this path reaches 2^31)
+// and own keys that are not positives by 0, and the inner loop is two compares per pair.
+__global__ void __launch_bounds__(256)
+    leaf_tiny_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ seg_start,
+                     SegStat* __restrict__ seg_stats) {
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (s >= kLeafSegs) return;
+  const uint32_t b = seg_start[s], e = seg_start[s + 1];
+  if (e <= b || e - b > kLeafTiny) return;
+  const uint32_t cnt = e - b;
+  constexpr int SLOTS = kLeafTiny / 32;
+  uint32_t mine[SLOTS], src[SLOTS];
+  uint32_t npos = 0;
+#pragma unroll
+  for (int m = 0; m < SLOTS; ++m) {
+    const uint32_t i = m * 32 + lane;
+    const uint32_t k = i < cnt ? keys[b + i] : 0u;
+    const bool pos = i < cnt && (k & 1u);
+    npos += pos ? 1u : 0u;
+    mine[m] = pos ? k : 0u;
+    src[m] = (i < cnt && !(k & 1u)) ? k : 0xfffffffeu;
+  }
+  uint32_t acc = 0;  // <= 2 * 128 * 128
+#pragma unroll
+  for (int m = 0; m < SLOTS; ++m) {
+    if ((uint32_t)m * 32 < cnt) {  // uniform across the warp
+      for (int j = 0; j < 32; ++j) {
+        const uint32_t kj = __shfl_sync(kFull, src[m], j);
+#pragma unroll
+        for (int q = 0; q < SLOTS; ++q) acc += (kj < mine[q] ? 1u : 0u) + (kj + 1u < mine[q] ? 1u : 0u);
+      }
+    }
+  }
+  acc = warp_sum(acc);
+  npos = warp_sum(npos);
+  if (lane == 0) {
+    SegStat r;
+    r.A = acc, r.P = npos, r.N = cnt - npos, r.pad = 0;
+    seg_stats[s] = r;
   }
 }
 
@@ -198,16 +247,25 @@ __global__ void __launch_bounds__(kLeafBlock, 1)
   __shared__ uint32_t s_ticket;
   __shared__ LeafWarpTot s_tot[kLeafWarps];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ LeafItem s_item;
   const uint32_t n_items = hdr->n_items;
   uint4* s_hist4 = reinterpret_cast<uint4*>(s_hist);
+  // the ticket (a global atomic) and the item it names (a dependent load) for round r + 1 are
+  // fetched by thread 0 while round r is counted: ~2 us that thousands of light pieces would
+  // otherwise each pay on their own
+  if (tid == 0) {
+    s_ticket = atomicAdd(&hdr->ticket, 1u);
+    if (s_ticket < n_items) s_item = items[n_items - 1u - s_ticket];  // highest keys first: the heavy segments
+  }
   for (;;) {
-    if (tid == 0) s_ticket = atomicAdd(&hdr->ticket, 1u);
 #pragma unroll
     for (int j = 0; j < kLeafVecPerThread; ++j) s_hist4[j * kLeafBlock + tid] = make_uint4(0, 0, 0, 0);
     __syncthreads();
     const uint32_t t = s_ticket;
     if (t >= n_items) break;
-    const LeafItem it = items[n_items - 1u - t];  // highest keys first: the heavy segments
+    const LeafItem it = s_item;
+    uint32_t next_ticket = 0;
+    if (tid == 0) next_ticket = atomicAdd(&hdr->ticket, 1u);
     const uint32_t cnt = it.end - it.begin;
     const uint32_t* __restrict__ k = keys + it.begin;
     // scalar head up to the first 16-byte boundary, vector body, scalar tail
@@ -233,7 +291,10 @@ __global__ void __launch_bounds__(kLeafBlock, 1)
     }
     const uint32_t done = head + 4u * nvec;
     if (tid < cnt - done) atomicAdd(&s_hist[k[done + tid] & kLeafMask], 1u);
-    __syncthreads();
+    LeafItem next_item = it;
+    if (tid == 0 && next_ticket < n_items) next_item = items[n_items - 1u - next_ticket];
+    __syncthreads();  // counts complete; everybody has read s_ticket / s_item of this round
+    if (tid == 0) s_ticket = next_ticket, s_item = next_item;
     if (it.slab >= 0) {
       uint4* dst = reinterpret_cast<uint4*>(slabs + (size_t)it.slab * kLeafBins);
 #pragma unroll
@@ -244,7 +305,7 @@ __global__ void __launch_bounds__(kLeafBlock, 1)
       for (int j = 0; j < kLeafVecPerThread; ++j) v[j] = s_hist4[(warp * kLeafVecPerThread + j) * 32 + lane];
       leaf_walk(v, s_tot, seg_stats + it.seg);
     }
-    __syncthreads();  // the histogram and s_ticket are rewritten by the next round
+    __syncthreads();  // the histogram is cleared by the next round, which reads the new s_ticket / s_item
   }
 }
 
