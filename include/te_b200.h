@@ -193,7 +193,7 @@ enum {
  *                     2^15 consecutive key values is counted into a shared-memory histogram and
  *                     integrated from the counts (36 instead of 52 bytes per score).  Needs every
  *                     score < 2.0, else out[4] carries TE_RANK_FLAG_WIDE_SCORE;
- *  TE_RANK_AUTO     : TE_RANK_COUNTING from 2^24 scores on (env TE_B200_LEAF_MIN_N), else TE_RANK_SORT. */
+ *  TE_RANK_AUTO     : TE_RANK_COUNTING from 2^25 scores on (env TE_B200_LEAF_MIN_N), else TE_RANK_SORT. */
 enum { TE_RANK_AUTO = 0, TE_RANK_SORT = 1, TE_RANK_COUNTING = 2 };
 
 TE_API size_t te_binary_rank_scratch_bytes(int64_t n);

@@ -1041,7 +1041,7 @@ int finish_leaf(const RankPlan& p, const uint32_t* keys, double* out, void* scra
 inline int64_t leaf_min_n_from_env() {
   static const int64_t v = [] {
     const char* e = getenv("TE_B200_LEAF_MIN_N");
-    return e ? atoll(e) : (int64_t)1 << 24;
+    return e ? atoll(e) : (int64_t)1 << 25;  // crossover measured at ~2^24.7 (profiles/r02_leaf_bench_v5.txt)
   }();
   return v;
 }
