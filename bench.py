@@ -209,7 +209,9 @@ def run_ours(args) -> dict:
         from torcheval_b200 import distributed as tdist
 
         def step():
-            return tdist.sharded_binary_auroc(x, y)
+            # no host read inside: splitters, slab exchange, counting stage and fix-up queue up on
+            # the stream; out[4] (flags, 0 = valid) is checked after the timed region
+            return tdist.sharded_binary_auroc_async(x, y)
     else:
         def step():
             return ops.binary_auroc_packed(x, y)
@@ -229,6 +231,7 @@ def run_ours(args) -> dict:
     ms_total = max_over_ranks(ev0.elapsed_time(ev1), world, device)
     ms_step = ms_total / args.steps
     value = n_total / (ms_step * 1e-3)
+    assert int(out[4].item()) == 0, f"flags {out[4].item()}: the timed path did not produce a valid result"
     auroc = float(out[0].item())
     launches = sum(k["launches"] for k in kernels.values())
 
@@ -698,7 +701,7 @@ def parity_checks(x, y, out, world, rank, device) -> dict:
     below = np.concatenate([[0], np.cumsum(neg)[:-1]])
     u2 = int(np.sum(pos.astype(object) * (2 * below.astype(object) + neg.astype(object))))
     a = tdist.sharded_binary_auroc(xx, yy).cpu().numpy()
-    assert a[4] == 0 and a[1] == pos.sum() and a[2] == neg.sum() and int(a[3]) == u2 and float(u2) == a[3], (a, u2)
+    assert a[4] == 0 and a[1] == pos.sum() and a[2] == neg.sum() and (int(a[6]) << 32) | int(a[7]) == u2, (a, u2)
     want = u2 / (2.0 * float(pos.sum()) * float(neg.sum()))
     assert abs(a[0] - want) <= 1e-12 * want
     ap = tdist.sharded_binary_auprc(xx, yy).cpu().numpy()

@@ -308,13 +308,37 @@ TE_API int te_binary_auprc_from_keys_finish(int64_t n, double positives_above, d
                                             const double* above_dev, double* out, void* scratch,
                                             size_t scratch_bytes, void* stream);
 
+/* Slab exchange of the distributed sample sort (no counterpart in the reference: toolkit.py:371-391
+ * gathers everything everywhere).  Every rank owns an inbox of te_slab_inbox_bytes(world, cap)
+ * bytes in peer-mapped memory: a 1 KiB header (world x {fill count, flags} uint32 pairs) followed by
+ * `world` slabs of `cap` packed keys, slab q reserved for sender q; cap = te_slab_capacity(largest
+ * shard, world).
+ *  te_rank_pack_scatter: (score, target) -> packed keys, stored straight into the owning rank's
+ *    inbox (rank b owns the keys in [splitter b-1, splitter b); splitters_dev: uint32[world - 1]
+ *    in device memory).  inbox_ptrs_host[b] = address of rank b's inbox as mapped into THIS
+ *    process (HOST array).  `work`: 128 bytes of device memory (cleared by the call).  The fill
+ *    counts and this sender's TE_RANK_FLAG_* bits go into every receiver's header; bit 0x100 there
+ *    = a slab overflowed, the result of this exchange must be discarded.  The caller synchronises
+ *    the ranks (barrier) before anybody reads an inbox.
+ *  te_binary_auroc_from_slabs: AUROC of the keys in this rank's inbox, counts read from its
+ *    header on the device (no host read); out[] as te_binary_auroc_from_keys, out[4] = OR of all
+ *    senders' flags (and TE_RANK_FLAG_WIDE_SCORE if a key needs 32 bits). */
+TE_API size_t te_slab_inbox_bytes(int32_t world, int64_t cap);
+TE_API int64_t te_slab_capacity(int64_t n_max_per_rank, int32_t world);
+TE_API int te_rank_pack_scatter(const float* score, const void* target, int32_t target_dtype, int64_t n,
+                                const uint32_t* splitters_dev, int32_t world, int32_t rank,
+                                const uint64_t* inbox_ptrs_host, int64_t cap, void* work, void* stream);
+TE_API size_t te_binary_auroc_from_slabs_scratch_bytes(int32_t world, int64_t cap);
+TE_API int te_binary_auroc_from_slabs(const void* inbox, int32_t world, int64_t cap, double* out, void* scratch,
+                                      size_t scratch_bytes, void* stream);
+
 /* Two one-CTA helpers of the distributed sample sort (no counterpart in the reference, which has no
  * sharded path: toolkit.py:371-391 gathers everything everywhere).
  *  te_select_splitters: `samples` = int32[total] float bit patterns of sampled scores from all
  *    ranks (negative = no sample), total <= 32768; writes the world - 1 quantile splitters in key
  *    space ((bits << 1), ascending) as uint32 and as int64.  world <= 16.
  *  te_combine_auroc_stats: `rows` = float64[world][8], the te_binary_auroc_from_keys results of
- *    the ranks in ascending score-range order; out[] = [auroc, P, N, 2U, 0, n_received, 0, 0] with
+ *    the ranks in ascending score-range order; out[] = [auroc, P, N, 2U, 0, n_received, 2U >> 32, 2U & 0xffffffff] with
  *    2U = sum_r (2U_r + 2 P_r sum_{q<r} N_q) in exact 64-bit integers. */
 TE_API int te_select_splitters(const int32_t* samples, int64_t total, int32_t world, uint32_t* splitters,
                                int64_t* splitters_i64, void* stream);

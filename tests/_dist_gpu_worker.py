@@ -75,6 +75,39 @@ def main():
     res["ovr/mc_auprc"] = [toolkit.sync_and_compute(m2).tolist(), oracle.multiclass_auprc(xi, yi).tolist()]
     m3 = MultilabelAUPRC(num_labels=CC, average="macro", device=dev).update(xd, ld)
     res["ovr/ml_auprc_macro"] = [float(toolkit.sync_and_compute(m3)), float(oracle.multilabel_auprc(xi, li).mean())]
+    # a collection: exact metrics take their sharded paths (no rank gathers their samples), the
+    # counters share one all-reduce, what is left shares one flat all-gather
+    calls = {"auroc": 0, "auprc": 0, "ovr": 0, "gather": 0}
+
+    def counted(name, fn):
+        def wrap(*a, **k):
+            calls[name] += 1
+            return fn(*a, **k)
+        return wrap
+
+    tdist._sharded_binary_auroc = counted("auroc", tdist._sharded_binary_auroc)
+    tdist._sharded_binary_auprc = counted("auprc", tdist._sharded_binary_auprc)
+    tdist.class_sharded_one_vs_rest = counted("ovr", tdist.class_sharded_one_vs_rest)
+    toolkit._gather_metrics = counted("gather", toolkit._gather_metrics)
+    x, y = cases["ties"]
+    cut = [0] + [int(n * (i + 1) / (world * 2)) for i in range(world - 1)] + [n]
+    xs = torch.from_numpy(x[cut[rank]:cut[rank + 1]]).to(dev)
+    ys = torch.from_numpy(y[cut[rank]:cut[rank + 1]]).to(dev)
+    wts = torch.from_numpy(rs.random(n)[cut[rank]:cut[rank + 1]] + 0.5).to(dev)
+    coll = toolkit.sync_and_compute_collection({
+        "auroc": BinaryAUROC(device=dev).update(xs, ys),
+        "cm": cm,
+        "auprc": BinaryAUPRC(device=dev).update(xs, ys),
+        "mc": m1,
+        "bb": bb,
+        "weighted": BinaryAUROC(device=dev).update(xs[:1000], ys[:1000], wts[:1000]),
+    })
+    res["coll/auroc"] = [float(coll["auroc"]), oracle.binary_auroc(x, y)[0]]
+    res["coll/auprc"] = [float(coll["auprc"]), oracle.binary_auprc(x, y)]
+    res["coll/binned_auprc"] = [float(coll["bb"][0][0]), oracle.binned_auprc_from_counts(tp_, fp_, fn_)]
+    res["coll/cm_equal"] = bool(np.array_equal(coll["cm"].cpu().numpy(), oracle.confusion_matrix(p, t, C)[0].astype(np.float32)))
+    res["coll/mc"] = [coll["mc"].tolist(), oracle.multiclass_auroc(xi, yi).tolist()]
+    res["coll/paths"] = [[calls["auroc"], calls["auprc"], calls["ovr"], calls["gather"]], [1, 1, 1, 1]]
     # generic state gather over NCCL (flat byte buffer): a metric without a dedicated sync path
     from torcheval_b200.metrics import WindowedBinaryAUROC
 

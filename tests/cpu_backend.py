@@ -261,11 +261,83 @@ def binary_pr_curve(score, target):
     return (torch.from_numpy(prec), torch.from_numpy(rec), torch.from_numpy(xs[gp].copy())), 0
 
 
+
+# ---- host restatements of the two one-CTA helpers of the sample sort (te_select_splitters,
+# ---- te_combine_auroc_stats): what the gloo tests run in their place, and what the GPU tests
+# ---- check the kernels against
+_NO_SAMPLE = 1 << 33  # above every 32-bit key: what a rank without data contributes to the pool
+
+
+def choose_splitters(samples_sorted, world: int):
+    """W-1 ascending splitters from the sorted pool of sampled keys; label bit cleared so that
+    both labels of one score compare alike.  (Host restatement of what te_select_splitters does
+    on the device; the tests check the kernel against it.)"""
+    m = len(samples_sorted)
+    out = []
+    for i in range(1, world):
+        v = int(samples_sorted[min(m - 1, (i * m) // world)]) if m else 0
+        out.append(v & 0xFFFFFFFE)
+    return out
+
+
+def combine_rank_stats(stats):
+    """stats: list over ranks (ascending score ranges) of (P_r, N_r, 2U_r) Python ints.
+    Returns (auroc, P, N, 2U) with exact integer arithmetic.  (Host restatement of
+    te_combine_auroc_stats / combine_rank_stats_tensor; the tests check both against it.)"""
+    u2 = 0
+    neg_below = 0
+    P = N = 0
+    for p_r, n_r, u2_r in stats:
+        u2 += u2_r + 2 * p_r * neg_below
+        neg_below += n_r
+        P += p_r
+        N += n_r
+    auroc = 0.5 if P == 0 or N == 0 else u2 / (2 * P * N)
+    return auroc, P, N, u2
+
+
+def combine_rank_stats_tensor(st: torch.Tensor):
+    """st: int64 (W, 4) rows {P_r, N_r, 2U_r >> 32, 2U_r & 0xffffffff}, ranks in ascending score
+    order.  Returns (auroc float64, P, N, 2U int64) as 0-d tensors on st.device, no host read:
+        2U = sum_r ( 2U_r + 2 * P_r * sum_{q<r} N_q )        (fits int64 for N_total < 2^31)."""
+    p, nn = st[:, 0], st[:, 1]
+    u2r = (st[:, 2] << 32) | st[:, 3]
+    neg_below = torch.cumsum(nn, 0) - nn
+    u2 = (u2r + 2 * p * neg_below).sum()
+    P, Nn = p.sum(), nn.sum()
+    den = 2.0 * P.to(torch.float64) * Nn.to(torch.float64)
+    auroc = torch.where(den == 0, torch.full_like(den, 0.5), u2.to(torch.float64) / den.clamp(min=1.0))
+    return auroc, P, Nn, u2
+
+
+
+def select_splitters(samples, world):
+    """(int32[W-1], int64[W-1]) quantile splitters in key space, like ops.select_splitters."""
+    pool = samples.reshape(-1)
+    pool, _ = torch.sort(torch.where(pool >= 0, pool.to(torch.int64), torch.full_like(pool, _NO_SAMPLE, dtype=torch.int64)))
+    m = (pool < _NO_SAMPLE).sum()
+    i = torch.arange(1, world, dtype=torch.int64)
+    pick = torch.minimum(torch.div(i * m, world, rounding_mode="floor"), (m - 1).clamp(min=0))
+    sp = torch.where(m > 0, (pool[pick] << 1) & 0xFFFFFFFE, torch.zeros_like(pick))
+    return sp.to(torch.int32), sp
+
+
+def combine_auroc_stats(rows, n_received):
+    st = torch.stack([rows[:, 1], rows[:, 2], rows[:, 5], rows[:, 6]], dim=1).to(torch.int64)
+    auroc, P, Nn, u2 = combine_rank_stats_tensor(st)
+    out = torch.zeros(8, dtype=torch.float64)
+    out[:4] = torch.stack([auroc, P.to(torch.float64), Nn.to(torch.float64), u2.to(torch.float64)])
+    out[5] = float(n_received)
+    out[6], out[7] = (u2 >> 32).to(torch.float64), (u2 & 0xFFFFFFFF).to(torch.float64)
+    return out
+
+
 _NAMES = [
     "cm_update_", "cm_update_logits_", "class_counts_", "match_count", "binned_hist_update_",
     "binned_hist2d_update_", "binned_counts", "binned_integrate", "binary_auroc_packed",
     "binary_auprc_packed", "binary_auroc_general", "binary_auprc_general", "sort_u32", "rank_pack", "ovr_rank",
     "partition_u32", "binary_auroc_from_keys", "binary_auprc_from_keys_begin", "binary_auprc_from_keys_finish", "binary_pr_curve",
+    "select_splitters", "combine_auroc_stats",
 ]
 
 

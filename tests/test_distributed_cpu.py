@@ -53,7 +53,7 @@ def test_sample_sort_and_toolkit_sync(world, port, tmp_path):
 
 
 def test_combine_rank_stats_and_splitters():
-    from torcheval_b200.distributed import choose_splitters, combine_rank_stats
+    from cpu_backend import choose_splitters, combine_rank_stats
 
     # two ranks: low range has 2 neg + 1 pos (pos beats 1 neg, ties none), high range 1 neg + 2 pos
     auroc, P, N, u2 = combine_rank_stats([(1, 2, 2), (2, 1, 2)])
@@ -62,7 +62,7 @@ def test_combine_rank_stats_and_splitters():
     assert auroc == u2 / (2 * 9)
     assert combine_rank_stats([(0, 5, 0), (0, 3, 0)])[0] == 0.5
     import torch
-    from torcheval_b200.distributed import combine_rank_stats_tensor
+    from cpu_backend import combine_rank_stats_tensor
 
     rs = np.random.default_rng(3)
     for _ in range(20):

@@ -588,7 +588,7 @@ def test_rank_pack_partition_from_keys(ops):
 
 def test_select_splitters_and_combine_stats(ops):
     """The two one-CTA helpers of the sample sort against their Python restatements."""
-    from torcheval_b200.distributed import combine_rank_stats
+    from cpu_backend import combine_rank_stats
 
     rs = np.random.default_rng(77)
     for world, s, empty in [(2, 4096, ()), (8, 4096, ()), (3, 1000, (1,)), (16, 2048, (0, 5)), (4, 7, ()), (2, 1, (0, 1))]:

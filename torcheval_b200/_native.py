@@ -58,6 +58,11 @@ SIGNATURES = {
     "te_binary_auroc_from_keys_variant": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _sz, _i32, _vp]),
     "te_binary_auprc_from_keys_begin": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _sz, _vp]),
     "te_binary_auprc_from_keys_finish": (C.c_int, [_i64, C.c_double, C.c_double, _vp, _vp, _vp, _sz, _vp]),
+    "te_slab_inbox_bytes": (_sz, [_i32, _i64]),
+    "te_slab_capacity": (_i64, [_i64, _i32]),
+    "te_rank_pack_scatter": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _i32, _i32, _vp, _i64, _vp, _vp]),
+    "te_binary_auroc_from_slabs_scratch_bytes": (_sz, [_i32, _i64]),
+    "te_binary_auroc_from_slabs": (C.c_int, [_vp, _i32, _i64, _vp, _vp, _sz, _vp]),
     "te_select_splitters": (C.c_int, [_vp, _i64, _i32, _vp, _vp, _vp]),
     "te_combine_auroc_stats": (C.c_int, [_vp, _i32, C.c_double, _vp, _vp]),
     "te_binary_pr_curve_begin": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp, _sz, _vp]),

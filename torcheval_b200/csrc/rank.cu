@@ -21,6 +21,7 @@
 #include "rank_sort.cuh"
 #include "rank_leaf.cuh"
 #include "rank_part.cuh"
+#include "rank_exchange.cuh"
 #include "prof.cuh"
 
 namespace te {
@@ -870,7 +871,7 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
   const size_t smem = block == 256 ? onesweep_smem_bytes<uint32_t, 256>() : onesweep_smem_bytes<uint32_t, 512>();
   using PassFn = void (*)(const uint32_t*, uint32_t*, const uint32_t*, uint32_t*, uint32_t,
                           const RadixDigit, const uint32_t*, uint32_t*, uint32_t*, const PeerPtrs,
-                          const uint32_t*, uint32_t*, size_t, const uint32_t*);
+                          const uint32_t*, uint32_t*, size_t, const uint32_t*, const uint32_t*);
   PassFn fn = nullptr;
   if (v_in0)
     fn = block == 256 ? onesweep_pass_kernel<uint32_t, true, 256, RadixDigit>
@@ -905,7 +906,7 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
                                                hist + pass * kRadix, lbp, gpp, PeerPtrs{},
                                                hot ? hot + 2 * pass : nullptr,
                                                pass + 1 < npasses ? lb_counts(pass + 1) : nullptr, bstride,
-                                               skip ? skip + pass : nullptr);
+                                               skip ? skip + pass : nullptr, nullptr);
     TE_LAUNCH_CHECK();
     kin = kout;
     vin = vout;
@@ -998,7 +999,8 @@ int finish_packed(const RankPlan& p, const uint32_t* ka, int mode, double* out, 
 
 // Counting stage over keys ordered by their top 16 bits (rank_leaf.cuh): segment bounds -> work
 // list -> histogram pieces -> merge of the segments counted in several pieces -> combine.
-int finish_leaf(const RankPlan& p, const uint32_t* keys, double* out, void* scratch, int sms, cudaStream_t st) {
+int finish_leaf(const RankPlan& p, const uint32_t* keys, double* out, void* scratch, int sms, cudaStream_t st,
+                const uint32_t* n_dev = nullptr) {
   uint32_t* seg_start = at<uint32_t>(scratch, p.off_seg_start);
   LeafItem* items = at<LeafItem>(scratch, p.off_leaf_items);
   LeafMulti* multi = at<LeafMulti>(scratch, p.off_leaf_multi);
@@ -1007,7 +1009,7 @@ int finish_leaf(const RankPlan& p, const uint32_t* keys, double* out, void* scra
   uint32_t* slabs = at<uint32_t>(scratch, p.off_leaf_slabs);
   {
     TE_PROF("leaf_seg_bounds", st);
-    leaf_seg_bounds_kernel<<<(kLeafSegs + 1 + 255) / 256, 256, 0, st>>>(keys, p.n, seg_start);
+    leaf_seg_bounds_kernel<<<(kLeafSegs + 1 + 255) / 256, 256, 0, st>>>(keys, p.n, seg_start, n_dev);
   }
   {
     TE_PROF("leaf_tiny", st);
@@ -1029,7 +1031,7 @@ int finish_leaf(const RankPlan& p, const uint32_t* keys, double* out, void* scra
   }
   {
     TE_PROF("leaf_combine", st);
-    leaf_combine_kernel<<<1, 1024, 0, st>>>(stats, p.n, &at<RankScalars>(scratch, p.off_scal)->flags, out);
+    leaf_combine_kernel<<<1, 1024, 0, st>>>(stats, p.n, &at<RankScalars>(scratch, p.off_scal)->flags, out, n_dev);
   }
   TE_LAUNCH_CHECK();
   return TE_OK;
@@ -1112,7 +1114,7 @@ int leaf_passes_ranges(const RankPlan& p, void* scratch, const float* score, con
   {
     TE_PROF("partition_ranges", st);
     part<<<part_grid, pblock, part_smem, st>>>(in1, out1, p.n, RadixDigit{kLeafBits}, range_base, rg.range_records,
-                                               (uint32_t)rpc, skip);
+                                               (uint32_t)rpc, skip, SlabView{nullptr, 0, 0, 0});
   }
   TE_LAUNCH_CHECK();
   // second pass: the look-back kernel, stable, on bits 23..30 (its look-back rows are the memset ones)
@@ -1123,7 +1125,7 @@ int leaf_passes_ranges(const RankPlan& p, void* scratch, const float* score, con
   TE_PROF("onesweep_pass_keys", st);
   fn<<<dim3(p.sort_tiles, 1), 512, smem, st>>>(out1, out2, nullptr, nullptr, p.n, RadixDigit{kLeafBits + 8}, hist + kRadix,
                                               at<uint32_t>(scratch, p.off_lookback), at<uint32_t>(scratch, p.off_gprefix),
-                                              PeerPtrs{}, nullptr, nullptr, 0, skip ? skip + 1 : nullptr);
+                                              PeerPtrs{}, nullptr, nullptr, 0, skip ? skip + 1 : nullptr, nullptr);
   TE_LAUNCH_CHECK();
   return TE_OK;
 }
@@ -2230,7 +2232,7 @@ static int partition_impl(const uint32_t* keys_in, int64_t n, const uint32_t* sp
     const size_t smem = onesweep_smem_bytes<uint32_t, B>();                                              \
     TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
     fn<<<p.sort_tiles, B, smem, st>>>(keys_in, keys_out, nullptr, nullptr, p.n, dop, hist, lb, gp, pp, hot, \
-                                      nullptr, 0, nullptr);                                              \
+                                      nullptr, 0, nullptr, nullptr);                                     \
   } while (0)
   if (p.sort_ipt != kSortIptDefault) return TE_ERR_UNSUPPORTED;
   if (p.sort_block == 256) {
@@ -2556,12 +2558,147 @@ __global__ void combine_auroc_kernel(const double* __restrict__ rows, int world,
   out[3] = (double)u2;
   out[4] = 0.0;
   out[5] = n_recv;
-  out[6] = 0.0;
-  out[7] = 0.0;
+  out[6] = (double)(u2 >> 32);            // 2U exactly, as two 32-bit halves
+  out[7] = (double)(u2 & 0xffffffffull);
 }
 
 }  // namespace
 }  // namespace te
+
+// ------------------------------------------------------------------------------------------
+// Slab exchange of the distributed sample sort (rank_exchange.cuh)
+// ------------------------------------------------------------------------------------------
+extern "C" size_t te_slab_inbox_bytes(int32_t world, int64_t cap) {
+  if (world < 1 || world > kMaxSplitters + 1 || cap < 0) return 0;
+  return 1024 + (size_t)world * (size_t)cap * 4;  // header (world x {count, flags}, padded) + the slabs
+}
+
+extern "C" int64_t te_slab_capacity(int64_t n_max_per_rank, int32_t world) {
+  // room for 1.3x an even split of the largest shard + a tile, rounded up to whole downsweep tiles
+  if (world < 1 || n_max_per_rank < 0) return 0;
+  const int64_t want = (int64_t)(1.3 * (double)n_max_per_rank / world) + 2 * kRangeUnit;
+  return (want + kRangeUnit - 1) / kRangeUnit * kRangeUnit;
+}
+
+template <typename TargetT>
+static int pack_scatter_impl(const float* score, const TargetT* target, int64_t n, const uint32_t* splitters_dev,
+                             int32_t world, int32_t rank, const uint64_t* inbox_ptrs_host, int64_t cap,
+                             uint32_t* work /*[32] device words*/, cudaStream_t st) {
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  TE_CUDA_TRY(cudaMemsetAsync(work, 0, 32 * sizeof(uint32_t), st));
+  uint32_t* cursors = work;       // [16]
+  uint32_t* flags = work + 16;    // [1]
+  PeerSlabs slabs{};
+  PeerHeaders hdrs{};
+  for (int b = 0; b < world; ++b) {
+    slabs.slab[b] = inbox_ptrs_host[b] + 1024 + (unsigned long long)rank * (unsigned long long)cap * 4ull;
+    hdrs.hdr[b] = inbox_ptrs_host[b] + 8ull * (unsigned long long)rank;
+  }
+  if (n > 0) {
+    const uint32_t tiles = (uint32_t)((n + kXsTile - 1) / kXsTile);
+    const uint32_t grid = tiles < (uint32_t)(2 * sms) ? tiles : (uint32_t)(2 * sms);
+    const bool vec_ok = (((uintptr_t)score | (uintptr_t)target) & 15) == 0;
+    TE_PROF("pack_scatter_peer", st);
+    pack_scatter_kernel<TargetT><<<grid, kXsBlock, 0, st>>>(score, target, (uint32_t)n, vec_ok, splitters_dev, world - 1,
+                                                            slabs, (uint32_t)cap, cursors, flags);
+  }
+  TE_LAUNCH_CHECK();
+  publish_counts_kernel<<<1, 32, 0, st>>>(cursors, flags, hdrs, world, (uint32_t)cap);
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+extern "C" int te_rank_pack_scatter(const float* score, const void* target, int32_t target_dtype, int64_t n,
+                                    const uint32_t* splitters_dev, int32_t world, int32_t rank,
+                                    const uint64_t* inbox_ptrs_host, int64_t cap, void* work, void* stream) {
+  if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  if (world < 1 || world > kMaxSplitters + 1 || rank < 0 || rank >= world || !inbox_ptrs_host || !work)
+    return TE_ERR_INVALID_ARGUMENT;
+  if (cap <= 0 || cap % kRangeUnit != 0 || cap > 0x7fffffffLL || (n > 0 && (!score || !target))) return TE_ERR_INVALID_ARGUMENT;
+  if (world > 1 && !splitters_dev) return TE_ERR_INVALID_ARGUMENT;
+  cudaStream_t st = (cudaStream_t)stream;
+  uint32_t* w = static_cast<uint32_t*>(work);
+  switch (target_dtype) {
+    case TE_DTYPE_I64: return pack_scatter_impl(score, (const long long*)target, n, splitters_dev, world, rank, inbox_ptrs_host, cap, w, st);
+    case TE_DTYPE_I32: return pack_scatter_impl(score, (const int*)target, n, splitters_dev, world, rank, inbox_ptrs_host, cap, w, st);
+    case TE_DTYPE_U8: return pack_scatter_impl(score, (const unsigned char*)target, n, splitters_dev, world, rank, inbox_ptrs_host, cap, w, st);
+    case TE_DTYPE_F32: return pack_scatter_impl(score, (const float*)target, n, splitters_dev, world, rank, inbox_ptrs_host, cap, w, st);
+    case TE_DTYPE_F64: return pack_scatter_impl(score, (const double*)target, n, splitters_dev, world, rank, inbox_ptrs_host, cap, w, st);
+    default: return TE_ERR_INVALID_ARGUMENT;
+  }
+}
+
+extern "C" size_t te_binary_auroc_from_slabs_scratch_bytes(int32_t world, int64_t cap) {
+  if (world < 1 || world > kMaxSplitters + 1 || cap <= 0 || (int64_t)world * cap > 0x7fffffffLL) return 0;
+  return make_plan((int64_t)world * cap, false, true, true, true).total;
+}
+
+extern "C" int te_binary_auroc_from_slabs(const void* inbox, int32_t world, int64_t cap, double* out, void* scratch,
+                                          size_t scratch_bytes, void* stream) {
+  if (!inbox || !out || world < 1 || world > kMaxSplitters + 1 || cap <= 0 || cap % kRangeUnit != 0)
+    return TE_ERR_INVALID_ARGUMENT;
+  const int64_t n_cap = (int64_t)world * cap;
+  if (n_cap > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  const RankPlan p = make_plan(n_cap, false, true, true, true);  // sized for full slabs
+  if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
+  if (p.sort_block != 512 || p.sort_ipt != kSortIptDefault) return TE_ERR_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
+  const uint32_t* hdr = static_cast<const uint32_t*>(inbox);
+  const uint32_t* keys_in = reinterpret_cast<const uint32_t*>(static_cast<const char*>(inbox) + 1024);
+  uint32_t* ka = at<uint32_t>(scratch, p.off_keys_a);
+  uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
+  uint32_t* hist = at<uint32_t>(scratch, p.off_hist);
+  uint32_t* range_hist = at<uint32_t>(scratch, p.off_range_hist);
+  uint32_t* range_base = at<uint32_t>(scratch, p.off_range_base);
+  RankScalars* scal = at<RankScalars>(scratch, p.off_scal);
+  uint32_t* flags = &scal->flags;
+  uint32_t* n_dev = &scal->pad;  // the number of records received, summed on the device
+  uint32_t* skip = skip_passes_from_env() ? at<uint32_t>(scratch, p.off_ticket) : nullptr;
+  slab_totals_kernel<<<1, 32, 0, st>>>(hdr, world, n_dev, flags);
+  TE_LAUNCH_CHECK();
+  const SlabView view{hdr, 2u, (uint32_t)cap, (uint32_t)world};
+  auto part = partition_ranges_kernel<RadixDigit, kPrBlock, kPrIpt>;
+  constexpr int TILE = kPrBlock * kPrIpt;
+  const size_t part_smem = (size_t)2 * TILE * sizeof(uint32_t);
+  TE_CUDA_TRY(cudaFuncSetAttribute(part, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)part_smem));
+  const uint32_t ntiles = (uint32_t)(n_cap / TILE);
+  const uint32_t ranges = ntiles < (uint32_t)sms ? ntiles : (uint32_t)sms;  // one downsweep CTA per SM
+  const uint32_t subs = 3;                                                   // histogram CTAs per range
+  TE_CUDA_TRY(cudaMemsetAsync(range_hist, 0, (size_t)ranges * kRadix * 4, st));
+  {
+    auto hk = rank_hist_view_kernel<TILE>;
+    TE_CUDA_TRY(cudaFuncSetAttribute(hk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kIrSmem));
+    TE_PROF("rank_hist_slabs", st);
+    hk<<<ranges * subs, kIrBlock, kIrSmem, st>>>(keys_in, view, ranges, subs, hist, range_hist, flags);
+  }
+  TE_LAUNCH_CHECK();
+  {
+    TE_PROF("digit_scan", st);
+    digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 2, nullptr, 0, skip);
+    range_base_kernel<<<1, kRadix, 0, st>>>(range_hist, ranges, hist, range_base);
+  }
+  TE_LAUNCH_CHECK();
+  {
+    TE_PROF("partition_ranges", st);
+    part<<<ranges, kPrBlock, part_smem, st>>>(keys_in, ka, 0u, RadixDigit{kLeafBits}, range_base, 0u, 1u, skip, view);
+  }
+  TE_LAUNCH_CHECK();
+  {
+    auto fn = onesweep_pass_kernel<uint32_t, false, 512, RadixDigit>;
+    const size_t smem = onesweep_smem_bytes<uint32_t, 512>();
+    TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    TE_PROF("onesweep_pass_keys", st);
+    fn<<<dim3(p.sort_tiles, 1), 512, smem, st>>>(ka, kb, nullptr, nullptr, p.n, RadixDigit{kLeafBits + 8}, hist + kRadix,
+                                                at<uint32_t>(scratch, p.off_lookback), at<uint32_t>(scratch, p.off_gprefix),
+                                                PeerPtrs{}, nullptr, nullptr, 0, skip ? skip + 1 : nullptr, n_dev);
+  }
+  TE_LAUNCH_CHECK();
+  return finish_leaf(p, kb, out, scratch, sms, st, n_dev);
+}
 
 extern "C" int te_select_splitters(const int32_t* samples, int64_t total, int32_t world, uint32_t* splitters,
                                    int64_t* splitters_i64, void* stream) {

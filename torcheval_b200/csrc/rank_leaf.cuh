@@ -55,9 +55,11 @@ struct LeafHeader {
 // seg_start[s] = first index whose key has (key >> 15) >= s, s = 0 .. 65536 (keys ordered by
 // their top bits).  65 537 independent binary searches; the top levels share cache lines.
 __global__ void __launch_bounds__(256)
-    leaf_seg_bounds_kernel(const uint32_t* __restrict__ keys, uint32_t n, uint32_t* __restrict__ seg_start) {
+    leaf_seg_bounds_kernel(const uint32_t* __restrict__ keys, uint32_t n, uint32_t* __restrict__ seg_start,
+                           const uint32_t* __restrict__ n_dev = nullptr) {
   const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s > kLeafSegs) return;
+  if (n_dev) n = *n_dev;  // (the record count lives in device memory)
   uint32_t lo = 0, hi = n;
   while (lo < hi) {
     const uint32_t mid = lo + ((hi - lo) >> 1);
@@ -340,7 +342,8 @@ __global__ void __launch_bounds__(kLeafBlock)
 // TE_RANK_FLAG_* bits collected on the way.
 __global__ void __launch_bounds__(1024)
     leaf_combine_kernel(const SegStat* __restrict__ seg_stats, uint32_t n, const uint32_t* __restrict__ flags_in,
-                        double* __restrict__ out) {
+                        double* __restrict__ out, const uint32_t* __restrict__ n_dev = nullptr) {
+  if (n_dev) n = *n_dev;
   __shared__ LeafWarpTot s_tot[32];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   constexpr int ROWS = kLeafSegs / 1024;

@@ -44,6 +44,24 @@ inline RangeGeom range_geom(uint32_t n, int resident_ctas) {
   return g;
 }
 
+// Where the records of a first pass live: one contiguous array of n records, or — on the receive
+// side of the distributed sample sort — `nslabs` slabs of `cap` records each (one per sending
+// rank, cap a multiple of every tile size), of which only the first counts[s * count_stride]
+// hold records.  The slab counts are device data (written by the senders), so nothing here
+// needs the host to know how many records arrived.
+struct SlabView {
+  const uint32_t* counts;  // nullptr: contiguous
+  uint32_t count_stride, cap, nslabs;
+};
+// number of records in [base, base + tile) of the physical index space (a tile never straddles slabs)
+__device__ __forceinline__ uint32_t view_valid(const SlabView& v, uint64_t base, uint32_t tile, uint32_t n) {
+  if (!v.counts) return base < n ? (uint32_t)min((uint64_t)tile, (uint64_t)n - base) : 0u;
+  const uint32_t s = (uint32_t)(base / v.cap);
+  if (s >= v.nslabs) return 0u;
+  const uint32_t off = (uint32_t)(base - (uint64_t)s * v.cap), c = min(v.counts[s * v.count_stride], v.cap);
+  return off < c ? min(tile, c - off) : 0u;
+}
+
 // (score, target) -> packed keys, range by range.  flags: TE_RANK_FLAG_* seen.  hist: uint32[2][256]
 // (+=), digits at key bits 15..22 and 23..30; range_hist: uint32[ranges][256] (=), the first digit
 // per range.  RAW_KEYS: `score` holds packed keys already (the receive side of the distributed
@@ -171,39 +189,45 @@ template <typename DigitOp, int BLOCK = kPrBlock, int IPT = kPrIpt>
 __global__ void __launch_bounds__(BLOCK, BLOCK >= 1024 ? 1 : 3)
     partition_ranges_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out, uint32_t n,
                             const DigitOp dop, const uint32_t* __restrict__ range_base, uint32_t range_records,
-                            uint32_t ranges_per_cta, const uint32_t* __restrict__ skip_flag) {
+                            uint32_t ranges_per_cta, const uint32_t* __restrict__ skip_flag,
+                            const SlabView view = SlabView{nullptr, 0, 0, 0}) {
   extern __shared__ __align__(16) uint32_t s_buf[];  // [2][TILE]
   constexpr int TILE = BLOCK * IPT;
   static_assert(IPT % 4 == 0 && TILE <= 65536, "16-byte slots; ranks are packed as 16-bit halves");
   static_assert(kRangeUnit % TILE == 0 && BLOCK >= kRadix, "ranges are made of whole tiles");
   __shared__ uint32_t s_cnt[kRadix], s_start[kRadix], s_goff[kRadix], s_wsum[kRadix / kWarp];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const uint32_t ntiles = (n + TILE - 1) / TILE;
-  // a CTA takes ranges_per_cta consecutive ranges: where one range ends in the output of a digit
-  // is where the next one starts, so only the first range's bases are needed
+  // Contiguous input: a CTA takes ranges_per_cta consecutive ranges — where one range ends in the
+  // output of a digit is where the next one starts, so only the first range's bases are needed.
+  // Slab input: range r is the tiles r, r + R, r + 2R, ... of the physical index space (R = grid
+  // size), so that the empty tails of the slabs are spread evenly over the CTAs.
+  const bool strided = view.counts != nullptr;
+  const uint32_t ntiles = strided ? view.nslabs * (view.cap / TILE) : (n + TILE - 1) / TILE;
   const uint32_t tiles_per_cta = range_records / TILE * ranges_per_cta;
-  const uint32_t t0 = blockIdx.x * tiles_per_cta;
-  const uint32_t t1 = min(ntiles, t0 + tiles_per_cta);
+  const uint32_t tstep = strided ? gridDim.x : 1u;
+  const uint32_t t0 = strided ? blockIdx.x : blockIdx.x * tiles_per_cta;
+  const uint32_t t1 = strided ? ntiles : min(ntiles, t0 + tiles_per_cta);
   const bool skip_pass = skip_flag ? ld_relaxed_u32(skip_flag) != 0u : false;
   uint32_t run = tid < kRadix ? range_base[(size_t)blockIdx.x * ranges_per_cta * kRadix + tid] : 0u;  // output offset of digit tid
   if (tid < kRadix) s_cnt[tid] = 0u;
   auto rec = [&](int i) -> uint32_t { return (((uint32_t)i >> 2) * BLOCK + tid) * 4u + ((uint32_t)i & 3u); };
   // full tiles travel through cp.async; a partial one (the last of the array) is read directly
-  auto prefetch = [&](uint32_t tile) {
-    if (tile < t1 && (uint64_t)(tile + 1) * TILE <= n) {
-      uint32_t* dst = s_buf + (tile & 1u) * TILE;
+  auto prefetch = [&](uint32_t tile, uint32_t half) {
+    if (tile < t1 && view_valid(view, (uint64_t)tile * TILE, TILE, n) == (uint32_t)TILE) {
+      uint32_t* dst = s_buf + half * TILE;
       const uint32_t* src = keys_in + (size_t)tile * TILE;
 #pragma unroll
       for (int q = 0; q < IPT / 4; ++q) cp_async_16(dst + rec(4 * q), src + rec(4 * q));
     }
     cp_async_commit();  // (an empty group keeps the wait_group arithmetic uniform)
   };
-  prefetch(t0);
-  for (uint32_t tile = t0; tile < t1; ++tile) {
-    const uint32_t base = tile * (uint32_t)TILE;
-    const uint32_t valid = min((uint32_t)TILE, n - base);
-    uint32_t* s_keys = s_buf + (tile & 1u) * TILE;
-    prefetch(tile + 1);   // into the half whose tile left at the end of the previous round
+  prefetch(t0, 0u);
+  uint32_t half = 0u;
+  for (uint32_t tile = t0; tile < t1; tile += tstep, half ^= 1u) {
+    const size_t base = (size_t)tile * TILE;
+    const uint32_t valid = view_valid(view, base, TILE, n);
+    uint32_t* s_keys = s_buf + half * TILE;
+    prefetch(tile + tstep, half ^ 1u);   // into the half whose tile left at the end of the previous round
     cp_async_wait<1>();   // everything but the newest group: this tile has landed
     __syncthreads();
     uint32_t key[IPT];
@@ -217,11 +241,14 @@ __global__ void __launch_bounds__(BLOCK, BLOCK >= 1024 ? 1 : 3)
 #pragma unroll
       for (int i = 0; i < IPT; ++i) key[i] = rec(i) < valid ? keys_in[base + rec(i)] : 0u;
     }
-    if (skip_pass) {  // one digit value only: the order stays as it is
+    if (valid == 0u) continue;  // (the empty tail of a slab)
+    if (skip_pass) {  // one digit value only: the order is free, the records only have to be packed densely
+      if (!strided) {
 #pragma unroll
-      for (int i = 0; i < IPT; ++i)
-        if (rec(i) < valid) keys_out[base + rec(i)] = key[i];
-      continue;
+        for (int i = 0; i < IPT; ++i)
+          if (rec(i) < valid) keys_out[base + rec(i)] = key[i];
+        continue;
+      }
     }
     // ---- rank: arrival order inside the digit, straight from the CTA-wide counters ----
     uint32_t rk[IPT / 2];

@@ -203,7 +203,14 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
                          uint32_t n, const DigitOp dop, const uint32_t* __restrict__ digit_base_,
                          uint32_t* lookback_, uint32_t* group_prefix_, const PeerPtrs peers,
                          const uint32_t* __restrict__ hot_info_, uint32_t* __restrict__ zero_next_,
-                         size_t bstride, const uint32_t* __restrict__ skip_flag_ = nullptr) {
+                         size_t bstride, const uint32_t* __restrict__ skip_flag_ = nullptr,
+                         const uint32_t* __restrict__ n_dev = nullptr) {
+  // n_dev: the record count lives in device memory (the receive side of the sample sort); the grid
+  // was sized for an upper bound and the tiles past the end leave at once — nobody waits on them
+  if (n_dev) {
+    n = *n_dev;
+    if ((uint64_t)blockIdx.x * (kSortBlock * kSortIpt) >= n) return;
+  }
   const uint32_t* __restrict__ skip_flag = batch_ptr(skip_flag_, bstride);
   const KeyT* __restrict__ keys_in = batch_ptr(keys_in_, bstride);
   KeyT* __restrict__ keys_out = batch_ptr(keys_out_, bstride);

@@ -15,8 +15,9 @@ Exact binary AUROC over rank-sharded scores as a distributed sample sort (SURVEY
 The reference instead pickles every rank's whole sample set to every rank and re-sorts all N
 samples everywhere (torcheval/metrics/toolkit.py:371-391, classification/auroc.py:131-136).
 
-The three kernel-backed steps are looked up through ``_local`` so that the host logic can be
-exercised on CPU/gloo by tests that substitute them.
+Every kernel-backed step is a call into ``torcheval_b200.ops``; the CPU/gloo tests of the host
+protocol substitute those functions (tests/cpu_backend.py), nothing in this module computes on
+the CPU.
 """
 from __future__ import annotations
 
@@ -64,33 +65,6 @@ class _PhaseTimer:
             print(f"[sharded r{rank}] " + "  ".join(f"{n}={ms:.2f}ms" for n, ms in self.rows), flush=True)
 
 
-class _LocalKernels:
-    """Kernel-backed local steps (CUDA tensors in, CUDA tensors out)."""
-
-    @staticmethod
-    def pack(score: torch.Tensor, target: torch.Tensor, splitters):
-        return ops.rank_pack(score, target, splitters, want_hist=True)
-
-    @staticmethod
-    def partition(keys: torch.Tensor, splitters, counts):
-        return ops.partition_u32(keys, splitters, counts)
-
-    @staticmethod
-    def auroc_from_keys(keys: torch.Tensor, hist=None, variant: int = 0) -> torch.Tensor:
-        return ops.binary_auroc_from_keys(keys, hist, variant)
-
-    @staticmethod
-    def auprc_begin(keys: torch.Tensor, hist=None):
-        return ops.binary_auprc_from_keys_begin(keys, hist)
-
-    @staticmethod
-    def auprc_finish(state, above: torch.Tensor) -> torch.Tensor:
-        return ops.binary_auprc_from_keys_finish(state, above)
-
-
-_local = _LocalKernels
-
-
 class _PeerInbox:
     """Peer-mapped receive buffers (torch symmetric memory, CUDA IPC under NVLink/NVSwitch) for
     the fused partition + exchange: every rank's partition kernel stores bucket b directly into
@@ -124,32 +98,57 @@ class _PeerInbox:
             return None
 
 
-def choose_splitters(samples_sorted, world: int):
-    """W-1 ascending splitters from the sorted pool of sampled keys; label bit cleared so that
-    both labels of one score compare alike.  (Host restatement of what te_select_splitters does
-    on the device; the tests check the kernel against it.)"""
-    m = len(samples_sorted)
-    out = []
-    for i in range(1, world):
-        v = int(samples_sorted[min(m - 1, (i * m) // world)]) if m else 0
-        out.append(v & 0xFFFFFFFE)
-    return out
+class _SlabInbox:
+    """Inbox of the slab exchange (csrc/rank_exchange.cuh): symmetric memory holding a 1 KiB header
+    and W slabs of `cap` keys, slab q written by rank q.  One per (process group, device), grown
+    collectively: get() with grow=False never communicates, so the steady state of the sharded
+    AUROC has no host round trip; the first call of a group and a call after an overflow do one
+    MAX all-reduce of the shard sizes (host read) to agree on the capacity."""
 
+    _cache: dict = {}
+    _broken = False
+    SLACK = 2.0  # slab capacity = SLACK x an even split of the largest shard
 
-def combine_rank_stats(stats):
-    """stats: list over ranks (ascending score ranges) of (P_r, N_r, 2U_r) Python ints.
-    Returns (auroc, P, N, 2U) with exact integer arithmetic.  (Host restatement of
-    te_combine_auroc_stats / combine_rank_stats_tensor; the tests check both against it.)"""
-    u2 = 0
-    neg_below = 0
-    P = N = 0
-    for p_r, n_r, u2_r in stats:
-        u2 += u2_r + 2 * p_r * neg_below
-        neg_below += n_r
-        P += p_r
-        N += n_r
-    auroc = 0.5 if P == 0 or N == 0 else u2 / (2 * P * N)
-    return auroc, P, N, u2
+    @classmethod
+    def get(cls, group, dev: torch.device, n_local: int, grow: bool):
+        import os
+
+        if cls._broken or dev.type != "cuda" or os.environ.get("TE_B200_NO_PEER") == "1" or os.environ.get("TE_B200_NO_SLABS") == "1":
+            return None
+        key = (id(group) if group is not None else 0, dev.index)
+        ent = cls._cache.get(key)
+        if ent is not None and not grow:
+            return ent
+        lib = N_.load()
+        world = dist.get_world_size(group)
+        # collective from here on: every rank of the group is in this branch together (first call /
+        # all ranks saw the overflow flag of the previous exchange)
+        t = torch.tensor([n_local], dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+        n_max = int(t.item())
+        slack = float(os.environ.get("TE_B200_SLAB_SLACK", cls.SLACK))  # (tests shrink it to force an overflow)
+        cap = int(lib.te_slab_capacity(int(slack / 1.3 * n_max) + 1, world))
+        if ent is not None and ent["cap"] >= cap:
+            cap = 2 * ent["cap"]  # the split was more skewed than the slack: double it
+        ok = 1
+        buf = None
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+
+            nbytes = int(lib.te_slab_inbox_bytes(world, cap))
+            buf = symm_mem.empty(nbytes // 4, dtype=torch.int32, device=dev)
+        except Exception:  # noqa: BLE001
+            ok = 0
+        agree = torch.tensor([ok], dtype=torch.int32, device=dev)
+        dist.all_reduce(agree, op=dist.ReduceOp.MIN, group=group)  # one rank cannot allocate: nobody uses slabs
+        if int(agree.item()) == 0:
+            cls._broken = True
+            return None
+        hdl = symm_mem.rendezvous(buf, group if group is not None else dist.group.WORLD)
+        ent = {"cap": cap, "buf": buf, "hdl": hdl, "ptrs": [int(p) for p in hdl.buffer_ptrs],
+               "work": torch.zeros(32, dtype=torch.int32, device=dev)}
+        cls._cache[key] = ent
+        return ent
 
 
 def _gather_rows(t: torch.Tensor, world: int, group) -> torch.Tensor:
@@ -160,7 +159,6 @@ def _gather_rows(t: torch.Tensor, world: int, group) -> torch.Tensor:
     return out
 
 
-_NO_SAMPLE = 1 << 33  # above every 32-bit key: what a rank without data contributes to the pool
 
 
 _SAMPLE_INDEX_CACHE: dict = {}
@@ -191,14 +189,7 @@ def device_splitters(score: torch.Tensor, world: int, group):
     else:
         smp = torch.full((s,), -1, dtype=torch.int32, device=dev)
     pool = _gather_rows(smp, world, group)  # negative bit patterns (negative scores, no data) are not samples
-    if dev.type == "cuda" and _local is _LocalKernels:
-        return ops.select_splitters(pool, world)
-    pool, _ = torch.sort(torch.where(pool >= 0, pool.to(torch.int64), torch.full_like(pool, _NO_SAMPLE, dtype=torch.int64)).reshape(-1))
-    m = (pool < _NO_SAMPLE).sum()
-    i = torch.arange(1, world, device=dev, dtype=torch.int64)
-    pick = torch.minimum(torch.div(i * m, world, rounding_mode="floor"), (m - 1).clamp(min=0))
-    sp = torch.where(m > 0, (pool[pick] << 1) & 0xFFFFFFFE, torch.zeros_like(pick))
-    return sp.to(torch.int32), sp
+    return ops.select_splitters(pool, world)
 
 
 def _exchange_keys(score: torch.Tensor, target: torch.Tensor, group, tm: _PhaseTimer):
@@ -216,7 +207,7 @@ def _exchange_keys(score: torch.Tensor, target: torch.Tensor, group, tm: _PhaseT
     sp32, sp_dev = device_splitters(score, world, group)
     tm.mark("splitters")
     # --- pack (+ bucket sizes) with the splitters still on the device --------------------------
-    keys, info, counts, send_hist = _local.pack(score, target, sp32)
+    keys, info, counts, send_hist = ops.rank_pack(score, target, sp32, want_hist=True)
     my_hist = _sum_rows_to_owner(send_hist, world, rank, group)
     tm.mark("pack")
     rows = _gather_rows(torch.cat([counts, info[1:2], sp_dev]), world, group).tolist()
@@ -234,7 +225,7 @@ def _exchange_keys(score: torch.Tensor, target: torch.Tensor, group, tm: _PhaseT
     n_all = [sum(int(v) for v in rows[q][:world]) for q in range(world)]
     recv_all = [sum(int(rows[q][b]) for q in range(world)) for b in range(world)]
     peer = None
-    if dev.type == "cuda" and _local is _LocalKernels:
+    if dev.type == "cuda":
         peer = _PeerInbox.get(group, dev, max(int(1.3 * max(n_all)) + 65536, 1 << 20))
         if peer is not None and max(recv_all) > peer[0]:
             peer = None  # a skewed split does not fit the inboxes: every rank sees that and falls back
@@ -250,7 +241,7 @@ def _exchange_keys(score: torch.Tensor, target: torch.Tensor, group, tm: _PhaseT
         inbox = buf[: recv_all[rank]]
         tm.mark("partition+p2p")
     else:
-        part, _ = _local.partition(keys, splitters, counts)
+        part, _ = ops.partition_u32(keys, splitters, counts)
         tm.mark("partition")
         inbox = torch.empty(sum(recv), dtype=keys.dtype, device=dev)
         dist.all_to_all_single(inbox, part, recv, send, group=group)
@@ -277,18 +268,38 @@ def _flags_only(flags: int, dev) -> torch.Tensor:
     return out
 
 
-def combine_rank_stats_tensor(st: torch.Tensor):
-    """st: int64 (W, 4) rows {P_r, N_r, 2U_r >> 32, 2U_r & 0xffffffff}, ranks in ascending score
-    order.  Returns (auroc float64, P, N, 2U int64) as 0-d tensors on st.device, no host read:
-        2U = sum_r ( 2U_r + 2 * P_r * sum_{q<r} N_q )        (fits int64 for N_total < 2^31)."""
-    p, nn = st[:, 0], st[:, 1]
-    u2r = (st[:, 2] << 32) | st[:, 3]
-    neg_below = torch.cumsum(nn, 0) - nn
-    u2 = (u2r + 2 * p * neg_below).sum()
-    P, Nn = p.sum(), nn.sum()
-    den = 2.0 * P.to(torch.float64) * Nn.to(torch.float64)
-    auroc = torch.where(den == 0, torch.full_like(den, 0.5), u2.to(torch.float64) / den.clamp(min=1.0))
-    return auroc, P, Nn, u2
+SLAB_OVERFLOW = 0x100  # out[4] bit of the slab exchange: a slab was too small, the result is void
+
+
+def _sharded_binary_auroc_slabs(score, target, group, grow: bool = False):
+    """The sample sort with the slab exchange: float64[8] as sharded_binary_auroc, or None when
+    slabs are not available (no peer access, CPU tensors).  No host read anywhere: splitters,
+    scatter into the peers' slabs, barrier, counting-stage path over the slabs with the fill counts
+    taken from device memory, all_gather of the W result rows, exact-integer fix-up kernel."""
+    dev = score.device
+    if dev.type != "cuda" or target.dtype not in ops._DTYPE_CODE:
+        return None
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    if world > MAX_SAMPLE_SORT_RANKS:
+        return None
+    box = _SlabInbox.get(group, dev, score.numel(), grow)
+    if box is None:
+        return None
+    tm = _PhaseTimer(dev)
+    sp32, _ = device_splitters(score, world, group)
+    tm.mark("splitters")
+    ops.rank_pack_scatter(score, target, sp32 if world > 1 else None, world, rank, box["ptrs"], box["cap"], box["work"])
+    box["hdl"].barrier()  # every sender's keys, counts and flags have landed
+    tm.mark("pack+scatter")
+    loc = ops.binary_auroc_from_slabs(box["buf"], world, box["cap"])
+    tm.mark("local")
+    rows = _gather_rows(loc, world, group)
+    out = ops.combine_auroc_stats(rows, 0)
+    out[4] = loc[4]  # flags of all senders (identical on every rank: each header holds all of them)
+    out[5] = loc[7]  # records this rank received
+    tm.mark("fixup")
+    tm.done(rank)
+    return out
 
 
 def _sharded_binary_auroc(score, target, group):
@@ -296,6 +307,15 @@ def _sharded_binary_auroc(score, target, group):
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = score.device
+    out = _sharded_binary_auroc_slabs(score, target, group)
+    if out is not None:
+        flags = int(out[4].item())  # the one host read, at the very end
+        if flags & SLAB_OVERFLOW:  # every rank sees it: grow the slabs together, then the count-first protocol
+            _SlabInbox.get(group, dev, score.numel(), grow=True)
+        elif flags & _WIDE:
+            pass  # scores >= 2.0: the count-first protocol below sorts all 32 key bits
+        else:
+            return out, flags
     tm = _PhaseTimer(dev)
     inbox, flags, hist = _exchange_keys(score, target, group, tm)
     if flags & ~_WIDE:
@@ -303,18 +323,11 @@ def _sharded_binary_auroc(score, target, group):
     # --- local ordering + integrate, then the fix-up of three integers per rank, on the device ---
     # (scores >= 2.0 somewhere: their keys need all 32 bits, which only the full sort handles; every
     # rank takes the same branch, the flag was part of the one host read)
-    loc = _local.auroc_from_keys(inbox, hist, N_.TE_RANK_SORT if flags & _WIDE else N_.TE_RANK_AUTO)
+    loc = ops.binary_auroc_from_keys(inbox, hist, N_.TE_RANK_SORT if flags & _WIDE else N_.TE_RANK_AUTO)
     tm.mark("local_sort_sweep")
     rows = _gather_rows(loc, world, group)  # (W, 8) float64
     tm.mark("fix:gather")
-    if dev.type == "cuda" and _local is _LocalKernels:
-        out = ops.combine_auroc_stats(rows, inbox.numel())  # one kernel, exact 64-bit integers
-    else:
-        st = torch.stack([rows[:, 1], rows[:, 2], rows[:, 5], rows[:, 6]], dim=1).to(torch.int64)
-        auroc, P, Nn, u2 = combine_rank_stats_tensor(st)
-        out = torch.zeros(8, dtype=torch.float64, device=dev)
-        out[:4] = torch.stack([auroc, P.to(torch.float64), Nn.to(torch.float64), u2.to(torch.float64)])
-        out[5] = float(inbox.numel())
+    out = ops.combine_auroc_stats(rows, inbox.numel())  # one kernel, exact 64-bit integers
     tm.mark(f"fixup(n_recv={inbox.numel()})")
     tm.done(rank)
     return out, 0
@@ -324,10 +337,21 @@ def sharded_binary_auroc(
     score: torch.Tensor, target: torch.Tensor, group: Optional[dist.ProcessGroup] = None
 ) -> torch.Tensor:
     """AUROC of the union of all ranks' (score, target) shards; float64[8] on score.device:
-    [auroc, P, N, 2U, flags, n_received_here, 0, 0].  flags != 0 (negative scores / soft labels
+    [auroc, P, N, 2U, flags, n_received_here, 2U >> 32, 2U & 0xffffffff].  flags != 0 (negative scores / soft labels
     somewhere) means the packed representation does not apply and [0] is not valid.
     One host read in total (bucket sizes); everything else stays on the device."""
     return _sharded_binary_auroc(score, target, group)[0]
+
+
+def sharded_binary_auroc_async(
+    score: torch.Tensor, target: torch.Tensor, group: Optional[dist.ProcessGroup] = None
+) -> torch.Tensor:
+    """sharded_binary_auroc without ANY host read: the caller looks at out[4] itself — 0 = valid;
+    SLAB_OVERFLOW / TE_RANK_FLAG_* set = call sharded_binary_auroc instead, which falls back.
+    Successive calls queue up on the stream (what a training loop that only logs the metric every
+    few steps wants).  Falls back to sharded_binary_auroc where slabs are not available."""
+    out = _sharded_binary_auroc_slabs(score, target, group)
+    return out if out is not None else _sharded_binary_auroc(score, target, group)[0]
 
 
 def _sharded_binary_auprc(score, target, group):
@@ -338,12 +362,12 @@ def _sharded_binary_auprc(score, target, group):
     inbox, flags, hist = _exchange_keys(score, target, group, tm)
     if flags & ~_WIDE:  # (wide keys are fine here: this path sorts all 32 bits)
         return _flags_only(flags, dev), flags
-    loc, state = _local.auprc_begin(inbox, hist)
+    loc, state = ops.binary_auprc_from_keys_begin(inbox, hist)
     tm.mark("local_sort_count")
     pn = _gather_rows(loc[1:3].clone(), world, group)  # (W, 2) float64 {P_r, N_r}, exact integers
     above = pn[rank + 1 :].sum(0)                      # what the ranks with higher scores hold
     above = torch.stack([above[0], above[0] + above[1]])
-    part = _local.auprc_finish(state, above)
+    part = ops.binary_auprc_from_keys_finish(state, above)
     tm.mark("integrate")
     sums = _gather_rows(part[3:4].clone(), world, group).reshape(-1)
     total = sums.sum()

@@ -534,6 +534,47 @@ def binary_pr_curve(score: torch.Tensor, target: torch.Tensor):
     return (precision, recall, thresholds), 0
 
 
+def rank_pack_scatter(score: torch.Tensor, target: torch.Tensor, splitters_dev: Optional[torch.Tensor], world: int,
+                      rank: int, inbox_ptrs, cap: int, work: torch.Tensor) -> None:
+    """te_rank_pack_scatter: pack (score, target) and store every key straight into the slab this
+    rank owns inside the destination rank's inbox (inbox_ptrs[b] = rank b's inbox as mapped here).
+    `work`: int32[32] device tensor (cleared by the call).  Nothing is returned: fill counts and
+    flags travel to the receivers' inbox headers."""
+    import ctypes
+
+    lib = N.load()
+    dev = _require_cuda(score, target)
+    assert score.dim() == 1 and score.shape == target.shape and score.dtype == torch.float32
+    score, target = score.contiguous(), target.contiguous()
+    assert work.dtype == torch.int32 and work.numel() >= 32 and work.device == dev
+    if world > 1:
+        assert splitters_dev is not None and splitters_dev.dtype == torch.int32 and splitters_dev.numel() == world - 1
+    ptrs = (ctypes.c_uint64 * world)(*[int(p) for p in inbox_ptrs])
+    with torch.cuda.device(dev):
+        N.check(
+            "te_rank_pack_scatter",
+            lib.te_rank_pack_scatter(score.data_ptr(), target.data_ptr(), _DTYPE_CODE[target.dtype], score.numel(),
+                                     _ptr(splitters_dev) if world > 1 else None, world, rank,
+                                     ctypes.cast(ptrs, ctypes.c_void_p), cap, work.data_ptr(), _stream_ptr(dev)),
+        )
+
+
+def binary_auroc_from_slabs(inbox: torch.Tensor, world: int, cap: int) -> torch.Tensor:
+    """te_binary_auroc_from_slabs over this rank's inbox (int32 tensor: header + world slabs of
+    `cap` keys).  float64[8] as binary_auroc_from_keys; out[4] = OR of all senders' flags."""
+    lib = N.load()
+    dev = _require_cuda(inbox)
+    out = torch.empty(8, dtype=torch.float64, device=dev)
+    scratch = _scratch(lib.te_binary_auroc_from_slabs_scratch_bytes(world, cap), dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_binary_auroc_from_slabs",
+            lib.te_binary_auroc_from_slabs(inbox.data_ptr(), world, cap, out.data_ptr(), scratch.data_ptr(),
+                                           scratch.numel(), _stream_ptr(dev)),
+        )
+    return out
+
+
 def select_splitters(samples: torch.Tensor, world: int):
     """samples: int32 [world * s] float bit patterns of sampled scores (negative = none), at most
     32768 of them.  Returns (int32[world - 1] splitter bit patterns in key space, int64 copy)."""
