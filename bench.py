@@ -260,7 +260,9 @@ def run_ours(args) -> dict:
         }
     # bytes the structure that ran actually moves per score: counting-stage path
     # 16 ingest + 2 passes * 8 + 4 counting = 36; full sort 16 + 4 * 8 + 4 sweep = 52
-    step_bytes = (36.0 if "leaf_count" in kernels else 52.0) * n_local
+    # (32.25 when the upsweep leaves label bits instead of packed keys: 12.125 upsweep + 8.125
+    # first pass + 8 second pass + 4 counting)
+    step_bytes = (32.25 if "rank_upsweep_bits" in kernels else 36.0 if "leaf_count" in kernels else 52.0) * n_local
     kernel_table = {
         name: {"avg_ms": round(v["total_ms"] / max(v["launches"], 1), 4), "launches_per_step": v["launches"] / args.steps}
         for name, v in kernels.items()

@@ -783,6 +783,7 @@ struct RankPlan {
   size_t off_leaf_hdr, off_seg_stats;  // inside the zeroed region
   size_t off_seg_start, off_leaf_items, off_leaf_multi, off_leaf_slabs;
   size_t off_range_hist, off_range_base;  // uint32[kMaxRanges][256] each (rank_part.cuh)
+  size_t off_label_bits;                  // one bit per record, in 128-record groups of 16 bytes
   size_t total;
 };
 constexpr uint32_t kMaxRanges = 1024;
@@ -838,6 +839,7 @@ RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final,
   p.off_leaf_slabs = take((size_t)p.leaf_max_slabs * kLeafBins * 4);
   p.off_range_hist = take(with_leaf ? (size_t)kMaxRanges * kRadix * 4 : 0);
   p.off_range_base = take(with_leaf ? (size_t)kMaxRanges * kRadix * 4 : 0);
+  p.off_label_bits = take(with_leaf ? ((size_t)n64 + 127) / 128 * 16 : 0);
   p.total = o;
   return p;
 }
@@ -1087,19 +1089,31 @@ int leaf_passes_ranges(const RankPlan& p, void* scratch, const float* score, con
   uint32_t* range_base = at<uint32_t>(scratch, p.off_range_base);
   uint32_t* flags = &at<RankScalars>(scratch, p.off_scal)->flags;
   uint32_t* skip = skip_passes_from_env() ? at<uint32_t>(scratch, p.off_ticket) : nullptr;
+  static const bool bits_ok = [] {
+    const char* e = getenv("TE_B200_LABEL_BITS");
+    return e ? atoi(e) != 0 : true;
+  }();
+  uint32_t* label_bits = (!raw_keys && bits_ok && ((uintptr_t)score & 15) == 0) ? at<uint32_t>(scratch, p.off_label_bits) : nullptr;
   if (raw_keys) {
-    auto ing = rank_ingest_ranges_kernel<long long, true>;
+    auto ing = rank_ingest_ranges_kernel<long long, kIrRaw>;
     TE_CUDA_TRY(cudaFuncSetAttribute(ing, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kIrSmem));
     TE_PROF("rank_hist_ranges", st);
     ing<<<rg.ranges, kIrBlock, kIrSmem, st>>>(reinterpret_cast<const float*>(raw_keys), nullptr, p.n,
                                               ((uintptr_t)raw_keys & 15) == 0, rg.range_records, nullptr, hist,
                                               range_hist, flags);
   } else {
-    auto ing = rank_ingest_ranges_kernel<TargetT, false>;
-    TE_CUDA_TRY(cudaFuncSetAttribute(ing, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kIrSmem));
-    TE_PROF("rank_ingest_ranges", st);
-    ing<<<rg.ranges, kIrBlock, kIrSmem, st>>>(score, target, p.n, (((uintptr_t)score | (uintptr_t)target) & 15) == 0,
-                                              rg.range_records, ka, hist, range_hist, flags);
+    // label_bits: the upsweep leaves one bit per label instead of the packed keys, the first pass
+    // packs from the scores and the bits (needs 16-byte aligned scores for its cp.async copies)
+    auto ing_keys = rank_ingest_ranges_kernel<TargetT, kIrKeys>;
+    auto ing_bits = rank_ingest_ranges_kernel<TargetT, kIrBits>;
+    TE_CUDA_TRY(cudaFuncSetAttribute(ing_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kIrSmem));
+    TE_CUDA_TRY(cudaFuncSetAttribute(ing_bits, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kIrSmem));
+    const bool vec_ok = (((uintptr_t)score | (uintptr_t)target) & 15) == 0;
+    TE_PROF(label_bits ? "rank_upsweep_bits" : "rank_ingest_ranges", st);
+    if (label_bits)
+      ing_bits<<<rg.ranges, kIrBlock, kIrSmem, st>>>(score, target, p.n, vec_ok, rg.range_records, label_bits, hist, range_hist, flags);
+    else
+      ing_keys<<<rg.ranges, kIrBlock, kIrSmem, st>>>(score, target, p.n, vec_ok, rg.range_records, ka, hist, range_hist, flags);
   }
   TE_LAUNCH_CHECK();
   {
@@ -1108,13 +1122,13 @@ int leaf_passes_ranges(const RankPlan& p, void* scratch, const float* score, con
     range_base_kernel<<<1, kRadix, 0, st>>>(range_hist, rg.ranges, hist, range_base);
   }
   TE_LAUNCH_CHECK();
-  const uint32_t* in1 = raw_keys ? raw_keys : ka;
+  const uint32_t* in1 = raw_keys ? raw_keys : (label_bits ? reinterpret_cast<const uint32_t*>(score) : ka);
   uint32_t* out1 = raw_keys ? ka : kb;
   uint32_t* out2 = raw_keys ? kb : ka;
   {
-    TE_PROF("partition_ranges", st);
+    TE_PROF(label_bits ? "partition_ranges_pack" : "partition_ranges", st);
     part<<<part_grid, pblock, part_smem, st>>>(in1, out1, p.n, RadixDigit{kLeafBits}, range_base, rg.range_records,
-                                               (uint32_t)rpc, skip, SlabView{nullptr, 0, 0, 0});
+                                               (uint32_t)rpc, skip, SlabView{nullptr, 0, 0, 0}, label_bits);
   }
   TE_LAUNCH_CHECK();
   // second pass: the look-back kernel, stable, on bits 23..30 (its look-back rows are the memset ones)
@@ -2684,7 +2698,7 @@ extern "C" int te_binary_auroc_from_slabs(const void* inbox, int32_t world, int6
   TE_LAUNCH_CHECK();
   {
     TE_PROF("partition_ranges", st);
-    part<<<ranges, kPrBlock, part_smem, st>>>(keys_in, ka, 0u, RadixDigit{kLeafBits}, range_base, 0u, 1u, skip, view);
+    part<<<ranges, kPrBlock, part_smem, st>>>(keys_in, ka, 0u, RadixDigit{kLeafBits}, range_base, 0u, 1u, skip, view, nullptr);
   }
   TE_LAUNCH_CHECK();
   {

@@ -62,15 +62,24 @@ __device__ __forceinline__ uint32_t view_valid(const SlabView& v, uint64_t base,
   return off < c ? min(tile, c - off) : 0u;
 }
 
-// (score, target) -> packed keys, range by range.  flags: TE_RANK_FLAG_* seen.  hist: uint32[2][256]
+// Upsweep of the first pass, range by range.  flags: TE_RANK_FLAG_* seen.  hist: uint32[2][256]
 // (+=), digits at key bits 15..22 and 23..30; range_hist: uint32[ranges][256] (=), the first digit
-// per range.  RAW_KEYS: `score` holds packed keys already (the receive side of the distributed
-// sample sort): histograms and the wide-key flag only, nothing is written.
-template <typename TargetT, bool RAW_KEYS>
+// per range.  What else it does depends on MODE:
+//   kIrKeys : (score, target) -> packed keys written to keys_out (12 B read + 4 B written per record);
+//   kIrBits : (score, target) -> the 0/1 labels only, ONE BIT per record, written to keys_out: the
+//             first pass then packs keys itself from the scores and these bits, and the packed keys
+//             never make a round trip through HBM (12 + 1/8 B per record here).  Layout: records
+//             come in groups of 128; word j (0..3) of a group holds, in bit L, the label of record
+//             4 L + j of the group — what a warp of the first pass reads with one 16-byte load;
+//   kIrRaw  : `score` holds packed keys already (the receive side of the distributed sample sort):
+//             histograms and the wide-key flag only, nothing is written.
+enum IngestRangesMode { kIrKeys = 0, kIrRaw = 1, kIrBits = 2 };
+template <typename TargetT, int MODE>
 __global__ void __launch_bounds__(kIrBlock)
     rank_ingest_ranges_kernel(const float* __restrict__ score, const TargetT* __restrict__ target, uint32_t n,
                               bool vec_ok, uint32_t range_records, uint32_t* __restrict__ keys_out,
                               uint32_t* ghist, uint32_t* __restrict__ range_hist, uint32_t* flags) {
+  constexpr bool RAW_KEYS = MODE == kIrRaw;
   extern __shared__ uint32_t sh[];  // [2][256][32 lanes]
   const unsigned tid = threadIdx.x, lane = tid & 31;
   for (int i = tid; i < 2 * kRadix * kWarp; i += kIrBlock) sh[i] = 0;
@@ -78,10 +87,13 @@ __global__ void __launch_bounds__(kIrBlock)
   const uint64_t e0 = (uint64_t)blockIdx.x * range_records;
   const uint32_t e1 = (uint32_t)min((uint64_t)n, e0 + (uint64_t)range_records);
   uint32_t bad_label = 0, neg_score = 0, wide = 0;
-  for (uint64_t i64 = e0 + 4ull * tid; i64 < e1; i64 += 4ull * kIrBlock) {
+  // a warp takes 128 consecutive records per step; the loop bound is the warp's, so that every lane
+  // is there for the ballots of kIrBits
+  for (uint64_t w64 = e0 + 4ull * (tid - lane); w64 < e1; w64 += 4ull * kIrBlock) {
+    const uint64_t i64 = w64 + 4ull * lane;
     const uint32_t i0 = (uint32_t)i64;
-    const uint32_t cnt = min(4u, e1 - i0);
-    uint32_t b[4], lab[4] = {0, 0, 0, 0};
+    const uint32_t cnt = i64 < e1 ? min(4u, e1 - i0) : 0u;
+    uint32_t b[4] = {0, 0, 0, 0}, lab[4] = {0, 0, 0, 0};
     if (cnt == 4 && vec_ok) {
       const int4 a = ld_stream_v4(score + i0);
       b[0] = (uint32_t)a.x, b[1] = (uint32_t)a.y, b[2] = (uint32_t)a.z, b[3] = (uint32_t)a.w;
@@ -122,12 +134,19 @@ __global__ void __launch_bounds__(kIrBlock)
         wide |= (bb >> 30) & 1u;  // key bit 31: score >= 2.0
       }
     }
-    if constexpr (!RAW_KEYS) {
+    if constexpr (MODE == kIrKeys) {
       if (cnt == 4) {
         st_stream_v4(keys_out + i0, make_int4((int)k[0], (int)k[1], (int)k[2], (int)k[3]));
       } else {
         for (uint32_t j = 0; j < cnt; ++j) keys_out[i0 + j] = k[j];
       }
+    }
+    if constexpr (MODE == kIrBits) {
+      uint32_t wj[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) wj[j] = __ballot_sync(kFull, lab[j] != 0u);  // (records past the end: 0)
+      if (lane == 0)
+        *reinterpret_cast<uint4*>(keys_out + (w64 >> 7) * 4) = make_uint4(wj[0], wj[1], wj[2], wj[3]);
     }
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -190,12 +209,16 @@ __global__ void __launch_bounds__(BLOCK, BLOCK >= 1024 ? 1 : 3)
     partition_ranges_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out, uint32_t n,
                             const DigitOp dop, const uint32_t* __restrict__ range_base, uint32_t range_records,
                             uint32_t ranges_per_cta, const uint32_t* __restrict__ skip_flag,
-                            const SlabView view = SlabView{nullptr, 0, 0, 0}) {
+                            const SlabView view = SlabView{nullptr, 0, 0, 0},
+                            const uint32_t* __restrict__ label_bits = nullptr) {
+  // label_bits given: keys_in holds the raw float32 SCORES and the labels come as one bit per
+  // record (rank_ingest_ranges_kernel<kIrBits>); the key is packed here, on the way into registers
   extern __shared__ __align__(16) uint32_t s_buf[];  // [2][TILE]
   constexpr int TILE = BLOCK * IPT;
   static_assert(IPT % 4 == 0 && TILE <= 65536, "16-byte slots; ranks are packed as 16-bit halves");
   static_assert(kRangeUnit % TILE == 0 && BLOCK >= kRadix, "ranges are made of whole tiles");
   __shared__ uint32_t s_cnt[kRadix], s_start[kRadix], s_goff[kRadix], s_wsum[kRadix / kWarp];
+  __shared__ __align__(16) uint32_t s_bits[2][TILE / 32];  // label bits of the two tiles in flight
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   // Contiguous input: a CTA takes ranges_per_cta consecutive ranges — where one range ends in the
   // output of a digit is where the next one starts, so only the first range's bases are needed.
@@ -218,6 +241,7 @@ __global__ void __launch_bounds__(BLOCK, BLOCK >= 1024 ? 1 : 3)
       const uint32_t* src = keys_in + (size_t)tile * TILE;
 #pragma unroll
       for (int q = 0; q < IPT / 4; ++q) cp_async_16(dst + rec(4 * q), src + rec(4 * q));
+      if (label_bits && tid < TILE / 128) cp_async_16(&s_bits[half][tid * 4], label_bits + (size_t)tile * (TILE / 32) + tid * 4);
     }
     cp_async_commit();  // (an empty group keeps the wait_group arithmetic uniform)
   };
@@ -236,10 +260,26 @@ __global__ void __launch_bounds__(BLOCK, BLOCK >= 1024 ? 1 : 3)
       for (int q = 0; q < IPT / 4; ++q) {
         const uint4 a = *reinterpret_cast<const uint4*>(s_keys + rec(4 * q));
         key[4 * q] = a.x, key[4 * q + 1] = a.y, key[4 * q + 2] = a.z, key[4 * q + 3] = a.w;
+        if (label_bits) {  // the four label words of my warp's 128-record group (one broadcast load)
+          const uint4 w = *reinterpret_cast<const uint4*>(&s_bits[half][(q * (BLOCK / 32) + warp) * 4]);
+          const uint32_t wj[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t bb = key[4 * q + j] == 0x80000000u ? 0u : key[4 * q + j];  // -0.0 ties with +0.0
+            key[4 * q + j] = (bb << 1) | ((wj[j] >> lane) & 1u);
+          }
+        }
       }
     } else {
 #pragma unroll
-      for (int i = 0; i < IPT; ++i) key[i] = rec(i) < valid ? keys_in[base + rec(i)] : 0u;
+      for (int i = 0; i < IPT; ++i) {
+        key[i] = rec(i) < valid ? keys_in[base + rec(i)] : 0u;
+        if (label_bits && rec(i) < valid) {
+          const size_t idx = base + rec(i);
+          const uint32_t bb = key[i] == 0x80000000u ? 0u : key[i];
+          key[i] = (bb << 1) | ((label_bits[(idx >> 7) * 4 + (idx & 3)] >> ((idx >> 2) & 31)) & 1u);
+        }
+      }
     }
     if (valid == 0u) continue;  // (the empty tail of a slab)
     if (skip_pass) {  // one digit value only: the order is free, the records only have to be packed densely
