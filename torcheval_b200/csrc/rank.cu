@@ -2611,7 +2611,10 @@ static int pack_scatter_impl(const float* score, const TargetT* target, int64_t 
   }
   if (n > 0) {
     const uint32_t tiles = (uint32_t)((n + kXsTile - 1) / kXsTile);
-    const uint32_t grid = tiles < (uint32_t)(2 * sms) ? tiles : (uint32_t)(2 * sms);
+    int per_sm = 0;
+    TE_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pack_scatter_kernel<TargetT>, kXsBlock, 0));
+    if (per_sm < 1) per_sm = 1;
+    const uint32_t grid = tiles < (uint32_t)(per_sm * sms) ? tiles : (uint32_t)(per_sm * sms);
     const bool vec_ok = (((uintptr_t)score | (uintptr_t)target) & 15) == 0;
     TE_PROF("pack_scatter_peer", st);
     pack_scatter_kernel<TargetT><<<grid, kXsBlock, 0, st>>>(score, target, (uint32_t)n, vec_ok, splitters_dev, world - 1,

@@ -130,6 +130,17 @@ class _SlabInbox:
         cap = int(lib.te_slab_capacity(int(slack / 1.3 * n_max) + 1, world))
         if ent is not None and ent["cap"] >= cap:
             cap = 2 * ent["cap"]  # the split was more skewed than the slack: double it
+        if world == 1 and os.environ.get("TE_B200_SLAB_PLAIN") == "1":  # (measurement aid: ordinary device memory)
+            buf = torch.empty(int(lib.te_slab_inbox_bytes(world, cap)) // 4, dtype=torch.int32, device=dev)
+
+            class _NoBarrier:
+                def barrier(self):
+                    pass
+
+            ent = {"cap": cap, "buf": buf, "hdl": _NoBarrier(), "ptrs": [buf.data_ptr()],
+                   "work": torch.zeros(32, dtype=torch.int32, device=dev)}
+            cls._cache[key] = ent
+            return ent
         ok = 1
         buf = None
         try:
