@@ -1,5 +1,6 @@
 """Times te_binary_auroc_variant (TE_RANK_SORT vs TE_RANK_COUNTING) and prints the per-kernel
 breakdown from the library's own CUDA-event profile.  Usage: python tools/leaf_bench.py [log2n ...]"""
+import os
 import sys
 from pathlib import Path
 
@@ -18,6 +19,10 @@ def run(log2n, kind="uniform", reps=5):
         x = 0.875 + x / 8
     elif kind == "grid":
         x = torch.floor(x * 4096) / 4096
+    elif kind == "const":
+        x = torch.full_like(x, 0.375)
+    elif kind == "two":
+        x = torch.where(x < 0.3, torch.full_like(x, 0.25), torch.full_like(x, 0.75))
     y = torch.randint(0, 2, (n,), device="cuda", generator=g)
     res = {}
     for variant, name in ((1, "sort"), (2, "counting")):
@@ -43,5 +48,5 @@ def run(log2n, kind="uniform", reps=5):
 if __name__ == "__main__":
     sizes = [int(a) for a in sys.argv[1:] if a.isdigit()] or [24, 27, 30]
     for s in sizes:
-        for kind in ("uniform", "band", "grid"):
+        for kind in os.environ.get("KINDS", "uniform,band,grid").split(","):
             run(s, kind)

@@ -22,6 +22,7 @@
 #include "rank_leaf.cuh"
 #include "rank_part.cuh"
 #include "rank_exchange.cuh"
+#include "rank_msd.cuh"
 #include "prof.cuh"
 
 namespace te {
@@ -784,6 +785,8 @@ struct RankPlan {
   size_t off_seg_start, off_leaf_items, off_leaf_multi, off_leaf_slabs;
   size_t off_range_hist, off_range_base;  // uint32[kMaxRanges][256] each (rank_part.cuh)
   size_t off_label_bits;                  // one bit per record, in 128-record groups of 16 bytes
+  size_t off_joint;                       // uint32[65536] joint digit histogram (zeroed region), rank_msd.cuh
+  size_t off_cursor1, off_cursor2, off_msd_tables;
   size_t total;
 };
 constexpr uint32_t kMaxRanges = 1024;
@@ -830,6 +833,7 @@ RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final,
   p.leaf_max_slabs = with_leaf ? (uint32_t)(2 * ((uint64_t)n64 / p.leaf_piece) + 2) : 0;
   p.off_leaf_hdr = take(with_leaf ? sizeof(LeafHeader) : 0);
   p.off_seg_stats = take(with_leaf ? (size_t)kLeafSegs * sizeof(SegStat) : 0);
+  p.off_joint = take(with_leaf ? (size_t)kLeafSegs * 4 : 0);
   p.zero_bytes = o - p.off_zero;
   p.off_lookback_rest = take((size_t)3 * p.sort_tiles * kRadix * 4);
   p.off_partial = take(with_final ? (size_t)kMaxChunks * 8 : 0);
@@ -840,6 +844,9 @@ RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final,
   p.off_range_hist = take(with_leaf ? (size_t)kMaxRanges * kRadix * 4 : 0);
   p.off_range_base = take(with_leaf ? (size_t)kMaxRanges * kRadix * 4 : 0);
   p.off_label_bits = take(with_leaf ? ((size_t)n64 + 127) / 128 * 16 : 0);
+  p.off_cursor1 = take(with_leaf ? kRadix * 4 : 0);
+  p.off_cursor2 = take(with_leaf ? (size_t)kLeafSegs * 4 : 0);
+  p.off_msd_tables = take(with_leaf ? sizeof(MsdTables) : 0);
   p.total = o;
   return p;
 }
@@ -1002,14 +1009,14 @@ int finish_packed(const RankPlan& p, const uint32_t* ka, int mode, double* out, 
 // Counting stage over keys ordered by their top 16 bits (rank_leaf.cuh): segment bounds -> work
 // list -> histogram pieces -> merge of the segments counted in several pieces -> combine.
 int finish_leaf(const RankPlan& p, const uint32_t* keys, double* out, void* scratch, int sms, cudaStream_t st,
-                const uint32_t* n_dev = nullptr) {
+                const uint32_t* n_dev = nullptr, bool have_seg_start = false) {
   uint32_t* seg_start = at<uint32_t>(scratch, p.off_seg_start);
   LeafItem* items = at<LeafItem>(scratch, p.off_leaf_items);
   LeafMulti* multi = at<LeafMulti>(scratch, p.off_leaf_multi);
   LeafHeader* hdr = at<LeafHeader>(scratch, p.off_leaf_hdr);
   SegStat* stats = at<SegStat>(scratch, p.off_seg_stats);
   uint32_t* slabs = at<uint32_t>(scratch, p.off_leaf_slabs);
-  {
+  if (!have_seg_start) {  // (the MSD passes leave the segment bounds: the prefix of their joint histogram)
     TE_PROF("leaf_seg_bounds", st);
     leaf_seg_bounds_kernel<<<(kLeafSegs + 1 + 255) / 256, 256, 0, st>>>(keys, p.n, seg_start, n_dev);
   }
@@ -1144,6 +1151,84 @@ int leaf_passes_ranges(const RankPlan& p, void* scratch, const float* score, con
   return TE_OK;
 }
 
+// Upsweep (joint histogram of both digits + label bits) -> prefix -> two cursor-placed partition
+// passes, most significant digit first (rank_msd.cuh).  seg_start is left for the counting stage.
+//   raw_keys == nullptr: (score, target) in; pass 1 packs into kb, pass 2 -> ka; result in ka.
+//   raw_keys given: raw -> ka -> kb; result in kb.
+template <typename TargetT>
+int leaf_passes_msd(const RankPlan& p, void* scratch, const float* score, const TargetT* target,
+                    const uint32_t* raw_keys, uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st) {
+  constexpr int TILE = kPrBlock * kPrIpt;
+  const size_t part_smem = (size_t)2 * TILE * sizeof(uint32_t);
+  uint32_t* joint = at<uint32_t>(scratch, p.off_joint);
+  uint32_t* seg_start = at<uint32_t>(scratch, p.off_seg_start);
+  uint32_t* cursor1 = at<uint32_t>(scratch, p.off_cursor1);
+  uint32_t* cursor2 = at<uint32_t>(scratch, p.off_cursor2);
+  MsdTables* tables = at<MsdTables>(scratch, p.off_msd_tables);
+  uint32_t* label_bits = at<uint32_t>(scratch, p.off_label_bits);
+  uint32_t* flags = &at<RankScalars>(scratch, p.off_scal)->flags;
+  const uint32_t nchunks = (p.n + kUjChunk - 1) / kUjChunk;
+  const uint32_t ugrid = nchunks < (uint32_t)sms ? nchunks : (uint32_t)sms;
+  if (raw_keys) {
+    auto up = rank_upsweep_joint_kernel<long long, true>;
+    TE_CUDA_TRY(cudaFuncSetAttribute(up, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUjSmem));
+    TE_PROF("rank_upsweep_joint_keys", st);
+    up<<<ugrid, kUjBlock, kUjSmem, st>>>(reinterpret_cast<const float*>(raw_keys), nullptr, p.n,
+                                         ((uintptr_t)raw_keys & 15) == 0, nullptr, joint, flags);
+  } else {
+    auto up = rank_upsweep_joint_kernel<TargetT, false>;
+    TE_CUDA_TRY(cudaFuncSetAttribute(up, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUjSmem));
+    TE_PROF("rank_upsweep_joint", st);
+    up<<<ugrid, kUjBlock, kUjSmem, st>>>(score, target, p.n, (((uintptr_t)score | (uintptr_t)target) & 15) == 0,
+                                         label_bits, joint, flags);
+  }
+  TE_LAUNCH_CHECK();
+  {
+    TE_PROF("joint_scan", st);
+    joint_scan_kernel<TILE><<<1, 1024, 0, st>>>(joint, seg_start, cursor1, cursor2, tables);
+  }
+  TE_LAUNCH_CHECK();
+  // both instantiations of a pass are launched; the device-side tables decide which one works
+  // (the host never sees the histogram)
+  const uint32_t tiles1 = (p.n + TILE - 1) / TILE;
+  const uint32_t grid1 = tiles1 < (uint32_t)sms ? tiles1 : (uint32_t)sms;
+  uint32_t* out1 = raw_keys ? ka : kb;
+  uint32_t* out2 = raw_keys ? kb : ka;
+  const uint32_t* in1 = raw_keys ? raw_keys : reinterpret_cast<const uint32_t*>(score);
+  const uint32_t* bits1 = raw_keys ? nullptr : label_bits;
+  auto launch = [&](auto kern, const char* name, uint32_t grid, const uint32_t* in, const uint32_t* bits, uint32_t* outp,
+                    const uint32_t* segs, uint32_t* cursors) -> int {
+    TE_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)part_smem));
+    TE_PROF(name, st);
+    kern<<<grid, kPrBlock, part_smem, st>>>(in, bits, outp, p.n, nullptr, segs, tables, cursors);
+    TE_LAUNCH_CHECK();
+    return TE_OK;
+  };
+  int rc;
+  if (raw_keys) {
+    if ((rc = launch(cursor_partition_kernel<false, false, false>, "cursor_pass_top", grid1, in1, bits1, out1, nullptr, cursor1))) return rc;
+    if ((rc = launch(cursor_partition_kernel<false, false, true>, "cursor_pass_top_hot", grid1, in1, bits1, out1, nullptr, cursor1))) return rc;
+  } else {
+    if ((rc = launch(cursor_partition_kernel<false, true, false>, "cursor_pass_top_pack", grid1, in1, bits1, out1, nullptr, cursor1))) return rc;
+    if ((rc = launch(cursor_partition_kernel<false, true, true>, "cursor_pass_top_pack_hot", grid1, in1, bits1, out1, nullptr, cursor1))) return rc;
+  }
+  if ((rc = launch(cursor_partition_kernel<true, false, false>, "cursor_pass_low", (uint32_t)sms, out1, nullptr, out2, seg_start, cursor2))) return rc;
+  if ((rc = launch(cursor_partition_kernel<true, false, true>, "cursor_pass_low_hot", (uint32_t)sms, out1, nullptr, out2, seg_start, cursor2))) return rc;
+  return TE_OK;
+}
+
+int leaf_passes_msd_dtype(const RankPlan& p, void* scratch, const float* score, const void* target, int32_t dt,
+                          uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st) {
+  switch (dt) {
+    case TE_DTYPE_I64: return leaf_passes_msd(p, scratch, score, (const long long*)target, nullptr, ka, kb, sms, st);
+    case TE_DTYPE_I32: return leaf_passes_msd(p, scratch, score, (const int*)target, nullptr, ka, kb, sms, st);
+    case TE_DTYPE_U8: return leaf_passes_msd(p, scratch, score, (const unsigned char*)target, nullptr, ka, kb, sms, st);
+    case TE_DTYPE_F32: return leaf_passes_msd(p, scratch, score, (const float*)target, nullptr, ka, kb, sms, st);
+    case TE_DTYPE_F64: return leaf_passes_msd(p, scratch, score, (const double*)target, nullptr, ka, kb, sms, st);
+    default: return TE_ERR_INVALID_ARGUMENT;
+  }
+}
+
 int leaf_passes_ranges_dtype(const RankPlan& p, void* scratch, const float* score, const void* target, int32_t dt,
                              uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st) {
   switch (dt) {
@@ -1165,6 +1250,15 @@ int binary_auroc_leaf(const float* score, const void* target, int32_t dt, int64_
   TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
   uint32_t* ka = at<uint32_t>(scratch, p.off_keys_a);
   uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
+  static const bool msd = [] {
+    const char* e = getenv("TE_B200_MSD_PASSES");
+    return e ? atoi(e) != 0 : true;
+  }();
+  if (n > 0 && msd && ((uintptr_t)score & 15) == 0) {
+    const int rc = leaf_passes_msd_dtype(p, scratch, score, target, dt, ka, kb, sms, st);
+    if (rc) return rc;
+    return finish_leaf(p, ka, out, scratch, sms, st, nullptr, true);
+  }
   if (n > 0 && range_pass_from_env() && p.sort_block == 512 && p.sort_ipt == kSortIptDefault) {
     const int rc = leaf_passes_ranges_dtype(p, scratch, score, target, dt, ka, kb, sms, st);
     if (rc) return rc;
