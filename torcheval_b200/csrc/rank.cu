@@ -1157,7 +1157,8 @@ int leaf_passes_ranges(const RankPlan& p, void* scratch, const float* score, con
 //   raw_keys given: raw -> ka -> kb; result in kb.
 template <typename TargetT>
 int leaf_passes_msd(const RankPlan& p, void* scratch, const float* score, const TargetT* target,
-                    const uint32_t* raw_keys, uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st) {
+                    const uint32_t* raw_keys, uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st,
+                    const SlabView view = SlabView{nullptr, 0, 0, 0}, const uint32_t* n_dev = nullptr) {
   constexpr int TILE = kPrBlock * kPrIpt;
   const size_t part_smem = (size_t)2 * TILE * sizeof(uint32_t);
   uint32_t* joint = at<uint32_t>(scratch, p.off_joint);
@@ -1167,20 +1168,20 @@ int leaf_passes_msd(const RankPlan& p, void* scratch, const float* score, const 
   MsdTables* tables = at<MsdTables>(scratch, p.off_msd_tables);
   uint32_t* label_bits = at<uint32_t>(scratch, p.off_label_bits);
   uint32_t* flags = &at<RankScalars>(scratch, p.off_scal)->flags;
-  const uint32_t nchunks = (p.n + kUjChunk - 1) / kUjChunk;
+  const uint32_t nchunks = (p.n + kUjChunk - 1) / kUjChunk;  // (slab view: p.n is the capacity of the inbox)
   const uint32_t ugrid = nchunks < (uint32_t)sms ? nchunks : (uint32_t)sms;
   if (raw_keys) {
     auto up = rank_upsweep_joint_kernel<long long, true>;
     TE_CUDA_TRY(cudaFuncSetAttribute(up, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUjSmem));
     TE_PROF("rank_upsweep_joint_keys", st);
     up<<<ugrid, kUjBlock, kUjSmem, st>>>(reinterpret_cast<const float*>(raw_keys), nullptr, p.n,
-                                         ((uintptr_t)raw_keys & 15) == 0, nullptr, joint, flags);
+                                         ((uintptr_t)raw_keys & 15) == 0, nullptr, joint, flags, view);
   } else {
     auto up = rank_upsweep_joint_kernel<TargetT, false>;
     TE_CUDA_TRY(cudaFuncSetAttribute(up, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUjSmem));
     TE_PROF("rank_upsweep_joint", st);
     up<<<ugrid, kUjBlock, kUjSmem, st>>>(score, target, p.n, (((uintptr_t)score | (uintptr_t)target) & 15) == 0,
-                                         label_bits, joint, flags);
+                                         label_bits, joint, flags, SlabView{nullptr, 0, 0, 0});
   }
   TE_LAUNCH_CHECK();
   {
@@ -1200,7 +1201,9 @@ int leaf_passes_msd(const RankPlan& p, void* scratch, const float* score, const 
                     const uint32_t* segs, uint32_t* cursors) -> int {
     TE_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)part_smem));
     TE_PROF(name, st);
-    kern<<<grid, kPrBlock, part_smem, st>>>(in, bits, outp, p.n, nullptr, segs, tables, cursors);
+    // (pass 1 reads through the view and needs no count; pass 2 and later take it from n_dev)
+    kern<<<grid, kPrBlock, part_smem, st>>>(in, bits, outp, p.n, segs ? n_dev : nullptr, segs, tables, cursors,
+                                            segs ? SlabView{nullptr, 0, 0, 0} : view);
     TE_LAUNCH_CHECK();
     return TE_OK;
   };
@@ -2772,43 +2775,10 @@ extern "C" int te_binary_auroc_from_slabs(const void* inbox, int32_t world, int6
   slab_totals_kernel<<<1, 32, 0, st>>>(hdr, world, n_dev, flags);
   TE_LAUNCH_CHECK();
   const SlabView view{hdr, 2u, (uint32_t)cap, (uint32_t)world};
-  auto part = partition_ranges_kernel<RadixDigit, kPrBlock, kPrIpt>;
-  constexpr int TILE = kPrBlock * kPrIpt;
-  const size_t part_smem = (size_t)2 * TILE * sizeof(uint32_t);
-  TE_CUDA_TRY(cudaFuncSetAttribute(part, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)part_smem));
-  const uint32_t ntiles = (uint32_t)(n_cap / TILE);
-  const uint32_t ranges = ntiles < (uint32_t)sms ? ntiles : (uint32_t)sms;  // one downsweep CTA per SM
-  const uint32_t subs = 3;                                                   // histogram CTAs per range
-  TE_CUDA_TRY(cudaMemsetAsync(range_hist, 0, (size_t)ranges * kRadix * 4, st));
-  {
-    auto hk = rank_hist_view_kernel<TILE>;
-    TE_CUDA_TRY(cudaFuncSetAttribute(hk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kIrSmem));
-    TE_PROF("rank_hist_slabs", st);
-    hk<<<ranges * subs, kIrBlock, kIrSmem, st>>>(keys_in, view, ranges, subs, hist, range_hist, flags);
-  }
-  TE_LAUNCH_CHECK();
-  {
-    TE_PROF("digit_scan", st);
-    digit_scan_kernel<<<1, 1024, 0, st>>>(hist, 2, nullptr, 0, skip);
-    range_base_kernel<<<1, kRadix, 0, st>>>(range_hist, ranges, hist, range_base);
-  }
-  TE_LAUNCH_CHECK();
-  {
-    TE_PROF("partition_ranges", st);
-    part<<<ranges, kPrBlock, part_smem, st>>>(keys_in, ka, 0u, RadixDigit{kLeafBits}, range_base, 0u, 1u, skip, view, nullptr);
-  }
-  TE_LAUNCH_CHECK();
-  {
-    auto fn = onesweep_pass_kernel<uint32_t, false, 512, RadixDigit>;
-    const size_t smem = onesweep_smem_bytes<uint32_t, 512>();
-    TE_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    TE_PROF("onesweep_pass_keys", st);
-    fn<<<dim3(p.sort_tiles, 1), 512, smem, st>>>(ka, kb, nullptr, nullptr, p.n, RadixDigit{kLeafBits + 8}, hist + kRadix,
-                                                at<uint32_t>(scratch, p.off_lookback), at<uint32_t>(scratch, p.off_gprefix),
-                                                PeerPtrs{}, nullptr, nullptr, 0, skip ? skip + 1 : nullptr, n_dev);
-  }
-  TE_LAUNCH_CHECK();
-  return finish_leaf(p, kb, out, scratch, sms, st, n_dev);
+  // upsweep over the slabs (joint histogram) -> cursors -> two cursor-placed passes -> counting stage
+  const int rc = leaf_passes_msd<long long>(p, scratch, nullptr, nullptr, keys_in, ka, kb, sms, st, view, n_dev);
+  if (rc) return rc;
+  return finish_leaf(p, kb, out, scratch, sms, st, n_dev, true);
 }
 
 extern "C" int te_select_splitters(const int32_t* samples, int64_t total, int32_t world, uint32_t* splitters,

@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(kIrBlock)
   uint32_t wide = 0;
   for (uint64_t tile = r + (uint64_t)k * ranges; tile < ntiles; tile += (uint64_t)subs * ranges) {
     const size_t base = (size_t)tile * TILE;
-    const uint32_t valid = view_valid(view, base, TILE, 0);
+    const uint32_t valid = view_valid_tile(view, (uint32_t)tile, TILE, 0);
     for (uint32_t i0 = 4 * tid; i0 < valid; i0 += 4 * kIrBlock) {
       uint32_t kk[4];
       const uint32_t cnt = min(4u, valid - i0);
