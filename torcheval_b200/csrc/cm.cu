@@ -506,7 +506,8 @@ inline BucketPlan bucket_plan(int64_t n) {
 
 constexpr int kRtParts = 4;  // slice counters are split over 4 interleaved thread classes
 
-__global__ void __launch_bounds__(kRtBlock)
+__global__ void __launch_bounds__(kRtBlock, 2)  // pins 64 registers = two CTAs per SM (one more kernel argument took
+                                                // ptxas to 69 registers and one CTA: 0.81 -> 1.30 ms, profiles/r02_cm_batches_overlap.txt)
     cm_route_kernel(const long long* __restrict__ pred, const long long* __restrict__ target, int64_t n,
                     uint32_t C, uint32_t rows, uint32_t inv_rows, bool vec_ok,
                     uint16_t* __restrict__ keys, uint16_t* __restrict__ table,
