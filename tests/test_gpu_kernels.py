@@ -518,6 +518,35 @@ def test_general_random_vs_oracle(ops, n, kind):
         close(a1[0], a2[0], 1e-12)
 
 
+def test_general_weights_as_payload(ops):
+    """Weights that are non-negative float32 values (the usual case: ones, class weights, float32
+    tensors cast up) on 0/1 targets travel through the sort as the payload, label in the sign bit;
+    anything else is gathered by index.  Both against the oracle, and against each other."""
+    rs = np.random.default_rng(21)
+    for n in (1, 5, 4097, 300_001):
+        x = (rs.standard_normal(n) * 3).astype(np.float32)
+        x[: n // 4] = np.round(x[: n // 4])  # ties, and -0.0 / +0.0
+        y = rs.integers(0, 2, n)
+        w32 = rs.random(n).astype(np.float32).astype(np.float64)
+        w32[: n // 10] = 0.0
+        a = run_general(ops, x, y, w32, torch.int64)
+        v, tp, fp = oracle.binary_auroc(x, y, w32)
+        close(a[0], v, RTOL64)
+        close(a[1], tp, 1e-12)
+        close(a[2], fp, 1e-12)
+        # a weight float32 cannot hold, a negative weight, a soft label: each falls back to the gather
+        for kind in ("inexact", "negative", "soft"):
+            w2, y2 = w32.copy(), y.astype(np.float64)
+            if kind == "inexact":
+                w2[n // 2] = 1.0 + 2.0 ** -40
+            elif kind == "negative":
+                w2[n // 2] = -0.5
+            else:
+                y2[n // 2] = 0.25
+            b = run_general(ops, x, y2, w2, torch.float64)
+            close(b[0], oracle.binary_auroc(x, y2, w2)[0], RTOL64)
+
+
 def test_functional_binary_auroc_dispatch(ops, golden):
     from torcheval_b200.metrics.functional.classification.auroc import binary_auroc
 

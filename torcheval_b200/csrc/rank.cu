@@ -49,12 +49,19 @@ __global__ void __launch_bounds__(kIngestBlock, 1)
     rank_ingest_kernel(const float* __restrict__ score, const TargetT* __restrict__ target,
                        const uint32_t* __restrict__ raw_keys, uint32_t n, bool vec_ok,
                        uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
-                       uint32_t* ghist, RankScalars* scal, const uint32_t* __restrict__ payload_bad) {
+                       uint32_t* ghist, RankScalars* scal, const uint32_t* __restrict__ payload_bad,
+                       const double* __restrict__ weight = nullptr) {
   extern __shared__ uint32_t sh[];  // [pass][digit][lane]
   // kIndexed: the 32-bit payload that travels with a key is its index — or, when every target is
   // exactly a float32 and there are no weights (payload_bad given and 0), the target value itself,
   // which spares the final sweep a random gather by index
   const bool as_payload = MODE == kIndexed && payload_bad && *payload_bad == 0u;
+  // ... or, with weights that are all non-negative float32 values on 0/1 targets (rank_totals_kernel
+  // checked), the weight's float32 bits with the label in the sign bit: no gather in the sweep either
+  auto payload_of = [&](uint32_t i) -> uint32_t {
+    if (weight) return __float_as_uint((float)weight[i]) | (target[i] == (TargetT)1 ? 0x80000000u : 0u);
+    return __float_as_uint((float)target[i]);
+  };
   const unsigned tid = threadIdx.x, lane = tid & 31;
   constexpr int kHists = LEAF ? 2 : 4;
   for (int i = tid; i < kHists * kRadix * kWarp; i += kIngestBlock) sh[i] = 0;
@@ -128,15 +135,15 @@ __global__ void __launch_bounds__(kIngestBlock, 1)
         st_stream_v4(keys_out + i0, make_int4((int)k[0], (int)k[1], (int)k[2], (int)k[3]));
         if (MODE == kIndexed) {
           if (as_payload)
-            st_stream_v4(vals_out + i0, make_int4(__float_as_int((float)target[i0]), __float_as_int((float)target[i0 + 1]),
-                                                  __float_as_int((float)target[i0 + 2]), __float_as_int((float)target[i0 + 3])));
+            st_stream_v4(vals_out + i0, make_int4((int)payload_of(i0), (int)payload_of(i0 + 1), (int)payload_of(i0 + 2),
+                                                  (int)payload_of(i0 + 3)));
           else
             st_stream_v4(vals_out + i0, make_int4((int)i0, (int)i0 + 1, (int)i0 + 2, (int)i0 + 3));
         }
       } else {
         for (uint32_t j = 0; j < cnt; ++j) {
           keys_out[i0 + j] = k[j];
-          if (MODE == kIndexed) vals_out[i0 + j] = as_payload ? __float_as_uint((float)target[i0 + j]) : i0 + j;
+          if (MODE == kIndexed) vals_out[i0 + j] = as_payload ? payload_of(i0 + j) : i0 + j;
         }
       }
     }
@@ -926,7 +933,7 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
 template <int MODE, typename TargetT, bool LEAF = false>
 int launch_ingest(const float* score, const void* target, const uint32_t* raw, const RankPlan& p,
                   uint32_t* keys_out, uint32_t* vals_out, void* scratch, int sms, cudaStream_t st,
-                  const uint32_t* payload_bad = nullptr) {
+                  const uint32_t* payload_bad = nullptr, const double* weight = nullptr) {
   auto kern = rank_ingest_kernel<MODE, TargetT, LEAF>;
   TE_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)kIngestSmem));
@@ -940,7 +947,7 @@ int launch_ingest(const float* score, const void* target, const uint32_t* raw, c
                           : (MODE == kIndexed ? "rank_ingest_indexed" : "rank_hist_keys"), st);
   kern<<<grid, kIngestBlock, kIngestSmem, st>>>(score, (const TargetT*)target, raw, p.n, vec_ok,
                                                  keys_out, vals_out, at<uint32_t>(scratch, p.off_hist),
-                                                 at<RankScalars>(scratch, p.off_scal), payload_bad);
+                                                 at<RankScalars>(scratch, p.off_scal), payload_bad, weight);
   TE_LAUNCH_CHECK();
   return TE_OK;
 }
@@ -1316,7 +1323,8 @@ constexpr int kGenTile = kGenBlock * kGenIpt;
 
 struct GenScalars {
   double tp_total, fp_total;
-  uint32_t payload_bad;  // != 0: some target is not exactly a float32 (or there are weights): gather by index
+  uint32_t payload_bad;  // != 0: gather target / weight by index; 0: the payload carries them (target value as
+                         // float32, or — with weights — float32 weight bits + the 0/1 label in the sign bit)
   uint32_t pad;
 };
 
@@ -1356,7 +1364,13 @@ __device__ __forceinline__ void gen_terms(const TargetT* __restrict__ target,
 }
 
 // the same from a payload that IS the target value (float32 bits), no weights
-__device__ __forceinline__ void gen_terms_payload(uint32_t val, int mode, double& tp, double& fp) {
+__device__ __forceinline__ void gen_terms_payload(uint32_t val, int mode, double& tp, double& fp, bool weighted = false) {
+  if (weighted) {  // float32 weight bits, 0/1 label in the sign bit (mode 0 only: AUPRC takes no weights)
+    const double w = (double)__uint_as_float(val & 0x7fffffffu);
+    tp = (val >> 31) ? w : 0.0;
+    fp = (val >> 31) ? 0.0 : w;
+    return;
+  }
   const double t = (double)__uint_as_float(val);
   if (mode == 0) {
     tp = t;
@@ -1374,14 +1388,22 @@ __global__ void __launch_bounds__(256)
                        uint32_t n, int mode, GenScalars* gs) {
   __shared__ double ws[8];
   double a = 0.0, b = 0.0;
-  uint32_t inexact = weight ? 1u : 0u;
+  uint32_t inexact = 0u;
   for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
     double tp, fp;
     gen_terms(target, weight, i, mode, tp, fp);
     a += tp;
     b += fp;
     const TargetT t = target[i];
-    inexact |= ((TargetT)(float)t != t) ? 1u : 0u;
+    if (weight) {
+      // weights ride along as float32 bits with the label in the sign bit: needs 0/1 targets and
+      // weights that are non-negative (sign bit clear) float32 values
+      const double w = weight[i];
+      const float wf = (float)w;
+      inexact |= ((double)wf != w || (__float_as_uint(wf) >> 31) || !(t == (TargetT)0 || t == (TargetT)1)) ? 1u : 0u;
+    } else {
+      inexact |= ((TargetT)(float)t != t) ? 1u : 0u;
+    }
   }
   if (__any_sync(kFull, inexact != 0u) && (threadIdx.x & 31) == 0) atomicOr(&gs->payload_bad, 1u);
   double ta, tb;
@@ -1533,7 +1555,7 @@ __global__ void __launch_bounds__(kGcBlock)
       if (j < (int)cnt) {
         double tp, fp;
         if (as_payload)
-          gen_terms_payload(v[j], 0, tp, fp);
+          gen_terms_payload(v[j], 0, tp, fp, weight != nullptr);
         else
           gen_terms(target, weight, v[j], 0, tp, fp);
         const bool st = (j == 0 && i0 == 0) || k[j] != prev;
@@ -1762,7 +1784,7 @@ int binary_rank_general_t(const float* score, const TargetT* target, const doubl
       rank_totals_kernel<TargetT><<<grid, 256, 0, st>>>(target, weight, p.n, mode, gs);
     }
     TE_LAUNCH_CHECK();
-    int rc = launch_ingest<kIndexed, TargetT>(score, target, nullptr, p, ka, va, scratch, sms, st, &gs->payload_bad);
+    int rc = launch_ingest<kIndexed, TargetT>(score, target, nullptr, p, ka, va, scratch, sms, st, &gs->payload_bad, weight);
     if (rc) return rc;
     rc = run_passes(p, scratch, ka, kb, ka, va, vb, va, st);  // sorted pairs end in (ka, va)
     if (rc) return rc;
