@@ -348,6 +348,23 @@ def run_ours(args) -> dict:
         torch.cuda.synchronize()
         dt = max_over_ranks((time.perf_counter() - t0) * 1e3, world, device) / 1e3 / e2e_steps
         assert abs(e2e_val - auroc) <= 1e-9 * max(1.0, abs(auroc)), (e2e_val, auroc)
+        # where the step goes (one extra, untimed step with a device sync after each phase)
+        barrier(world)
+        t0 = time.perf_counter()
+        m = BinaryAUROC(device=device)
+        m.update(xh, yh)
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        v = sync_and_compute(m)
+        torch.cuda.synchronize()
+        t2 = time.perf_counter()
+        float(v.item())
+        t3 = time.perf_counter()
+        phases = {
+            "update_h2d_ms": max_over_ranks((t1 - t0) * 1e3, world, device),
+            "sync_and_compute_ms": max_over_ranks((t2 - t1) * 1e3, world, device),
+            "result_d2h_ms": max_over_ranks((t3 - t2) * 1e3, world, device),
+        }
         e2e = {
             "value": n_total / dt,
             "unit": "scores/s",
@@ -355,7 +372,9 @@ def run_ours(args) -> dict:
             "d2h_bytes_per_step": 8,
             "ms_per_step": dt * 1e3,
             "steps": e2e_steps,
-            "note": "per-rank bytes; class API update() + toolkit.sync_and_compute()",
+            "phases_ms": {k: round(v_, 3) for k, v_ in phases.items()},
+            "note": "per-rank bytes; class API update() + toolkit.sync_and_compute(); phases_ms: max over ranks, "
+                    "one untimed step with a device sync after each phase",
         }
 
     if world > 1:
