@@ -216,6 +216,14 @@ TE_API int te_binary_auroc_variant(const float* score, const void* target, int32
 TE_API int te_binary_auprc(const float* score, const void* target, int32_t target_dtype, int64_t n,
                            double* out, void* scratch, size_t scratch_bytes, void* stream);
 
+/* te_binary_auprc with the structure chosen by the caller (te_binary_auprc itself = TE_RANK_AUTO).
+ * TE_RANK_COUNTING runs the counting stage twice over the grouped keys (counts, then the integral
+ * with exact prefix counts); it needs scores < 2.0 (else TE_RANK_FLAG_WIDE_SCORE in out[4]) and a
+ * 16-byte aligned score array (else it falls back to TE_RANK_SORT by itself). */
+TE_API int te_binary_auprc_variant(const float* score, const void* target, int32_t target_dtype,
+                                   int64_t n, double* out, void* scratch, size_t scratch_bytes,
+                                   int32_t variant, void* stream);
+
 /* General variants: any float32 score (negative values, mixed signs), soft labels (AUROC uses
  * w*t and w*(1-t) as auroc.py:129-130), optional float64 per-sample weights (NULL = 1).  Same
  * out[] layout with [1] = sum w*t, [2] = sum w*(1-t), [3] = the signed cross term; [4] = 0.

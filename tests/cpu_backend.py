@@ -127,7 +127,7 @@ def binary_auroc_packed(score, target, variant=0):
     return out
 
 
-def binary_auprc_packed(score, target):
+def binary_auprc_packed(score, target, variant=0):
     f = _flags(score, target)
     out = torch.zeros(8, dtype=torch.float64)
     out[4] = f

@@ -176,3 +176,45 @@ def test_counting_from_keys(ops):
     keys = keys.copy()
     keys[3] = np.int32(-5)  # bit 31 set
     assert int(ops.binary_auroc_from_keys(dev(keys), None, COUNTING).cpu().numpy()[4]) == 4
+
+
+def check_ap(ops, x, y, what=""):
+    p = ops.binary_auprc_packed(dev(x), dev(y), COUNTING).cpu().numpy()
+    q = ops.binary_auprc_packed(dev(x), dev(y), SORT).cpu().numpy()
+    assert p[4] == 0, what
+    assert (p[1], p[2]) == (q[1], q[2]) == (float(y.sum()), float(x.size - y.sum())), what
+    want = oracle.binary_auprc(x, y) if x.size else -0.0
+    np.testing.assert_allclose(p[0], want, rtol=1e-9, atol=1e-15, err_msg=what)
+    np.testing.assert_allclose(p[0], q[0], rtol=1e-12, atol=1e-15, err_msg=what)
+    if y.sum() == 0:
+        assert p[0] == 0 and np.signbit(p[0]), what  # the reference's -0.0 (precision_recall_curve.py:227-229)
+
+
+def test_counting_auprc(ops):
+    """Average precision on the counting stage (two passes over the grouped keys) against the oracle
+    and the sort-based kernel: edge sizes, ties, segments of every kind (tiny, single-piece,
+    multi-piece), degenerate label sets."""
+    rs = np.random.default_rng(9)
+    for n in [1, 2, 5, 33, 129, 4097, 24577, 131073]:
+        y = rs.integers(0, 2, n)
+        check_ap(ops, (rs.integers(0, 64, n) / 64).astype(np.float32), y, f"ties n={n}")
+        check_ap(ops, rs.random(n, dtype=np.float32), y, f"uniform n={n}")
+    n = (1 << 21) + 7
+    u = rs.random(n, dtype=np.float32)
+    y = rs.integers(0, 2, n)
+    cases = {
+        "uniform": u,
+        "narrow": (0.7 + 1e-4 * u).astype(np.float32),
+        "one_segment": (np.float32(0.75) + (rs.integers(0, 1 << 14, n).astype(np.float32) * np.float32(2.0 ** -24))).astype(np.float32),
+        "two_values": np.where(u < 0.3, np.float32(0.25), np.float32(0.75)),
+        "constant": np.full(n, 0.375, dtype=np.float32),
+        "tiny": (u * np.float32(1e-38)).astype(np.float32),
+    }
+    for name, x in cases.items():
+        check_ap(ops, x, y, name)
+    check_ap(ops, u, np.ones(n, dtype=np.int64), "all_pos")
+    check_ap(ops, u, np.zeros(n, dtype=np.int64), "all_neg")
+    check_ap(ops, u, (rs.random(n) < 0.01).astype(np.int64), "skewed_labels")
+    xw = u.copy()
+    xw[5] = 2.5
+    assert int(ops.binary_auprc_packed(dev(xw), dev(y), COUNTING).cpu().numpy()[4]) == 4

@@ -43,6 +43,18 @@ def run(log2n, kind="uniform", reps=5):
         for kn, v in sorted(k.items(), key=lambda kv: -kv[1]["total_ms"]):
             print(f"      {kn:28s} {v['total_ms'] / reps:8.3f} ms/step  ({v['launches'] // reps} launches)")
     assert (res["sort"] == res["counting"]).all(), (res["sort"], res["counting"])
+    if os.environ.get("AUPRC") == "1":
+        for variant, name in ((1, "sort"), (2, "counting")):
+            for _ in range(2):
+                out = ops.binary_auprc_packed(x, y, variant)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                out = ops.binary_auprc_packed(x, y, variant)
+            e1.record()
+            torch.cuda.synchronize()
+            print(f"n=2^{log2n} {kind:8s} AUPRC {name:9s} {e0.elapsed_time(e1) / reps:8.3f} ms/step  ap={out[0].item():.12f}")
 
 
 if __name__ == "__main__":

@@ -43,6 +43,7 @@ SIGNATURES = {
     "te_binary_auroc": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp, _sz, _vp]),
     "te_binary_auroc_variant": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp, _sz, _i32, _vp]),
     "te_binary_auprc": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp, _sz, _vp]),
+    "te_binary_auprc_variant": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp, _sz, _i32, _vp]),
     "te_binary_rank_general_scratch_bytes": (_sz, [_i64]),
     "te_binary_auroc_general": (C.c_int, [_vp, _vp, _i32, _vp, _i64, _vp, _vp, _sz, _vp]),
     "te_binary_auprc_general": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp, _sz, _vp]),

@@ -108,7 +108,11 @@ def _binary_auroc_row(x: torch.Tensor, t: torch.Tensor, w: Optional[torch.Tensor
 def _binary_auprc_row(x: torch.Tensor, t: torch.Tensor) -> torch.Tensor:
     if t.dtype in ops._DTYPE_CODE:
         out = ops.binary_auprc_packed(x, t)
-        if int(out[4].item()) == 0:
+        flags = int(out[4].item())
+        if flags == N.TE_RANK_FLAG_WIDE_SCORE:  # scores >= 2.0: the full sort handles all 32 key bits
+            out = ops.binary_auprc_packed(x, t, N.TE_RANK_SORT)
+            flags = int(out[4].item())
+        if flags == 0:
             return out[0].clone()
     return ops.binary_auprc_general(x, t)[0].clone()
 

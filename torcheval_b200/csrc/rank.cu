@@ -23,6 +23,7 @@
 #include "rank_part.cuh"
 #include "rank_exchange.cuh"
 #include "rank_msd.cuh"
+#include "rank_leaf_ap.cuh"
 #include "prof.cuh"
 
 namespace te {
@@ -794,6 +795,7 @@ struct RankPlan {
   size_t off_label_bits;                  // one bit per record, in 128-record groups of 16 bytes
   size_t off_joint;                       // uint32[65536] joint digit histogram (zeroed region), rank_msd.cuh
   size_t off_cursor1, off_cursor2, off_msd_tables;
+  size_t off_pos_below, off_ap_part, off_ap_totals;  // average precision on the counting stage (rank_leaf_ap.cuh)
   size_t total;
 };
 constexpr uint32_t kMaxRanges = 1024;
@@ -854,6 +856,9 @@ RankPlan make_plan(int64_t n64, bool with_vals, bool with_keys, bool with_final,
   p.off_cursor1 = take(with_leaf ? kRadix * 4 : 0);
   p.off_cursor2 = take(with_leaf ? (size_t)kLeafSegs * 4 : 0);
   p.off_msd_tables = take(with_leaf ? sizeof(MsdTables) : 0);
+  p.off_pos_below = take(with_leaf ? (size_t)kLeafSegs * 4 : 0);
+  p.off_ap_part = take(with_leaf ? (size_t)kLeafSegs * 8 : 0);
+  p.off_ap_totals = take(with_leaf ? sizeof(ApTotals) : 0);
   p.total = o;
   return p;
 }
@@ -1048,6 +1053,64 @@ int finish_leaf(const RankPlan& p, const uint32_t* keys, double* out, void* scra
   {
     TE_PROF("leaf_combine", st);
     leaf_combine_kernel<<<1, 1024, 0, st>>>(stats, p.n, &at<RankScalars>(scratch, p.off_scal)->flags, out, n_dev);
+  }
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
+// Average precision on the counting stage: phase A = the AUROC stage without its combine ({P, N} per
+// segment), prefix, phase B over the same work list (rank_leaf_ap.cuh).  seg_start must be there
+// already (the MSD passes leave it).
+int finish_leaf_ap(const RankPlan& p, const uint32_t* keys, double* out, void* scratch, int sms, cudaStream_t st) {
+  uint32_t* seg_start = at<uint32_t>(scratch, p.off_seg_start);
+  LeafItem* items = at<LeafItem>(scratch, p.off_leaf_items);
+  LeafMulti* multi = at<LeafMulti>(scratch, p.off_leaf_multi);
+  LeafHeader* hdr = at<LeafHeader>(scratch, p.off_leaf_hdr);
+  SegStat* stats = at<SegStat>(scratch, p.off_seg_stats);
+  uint32_t* slabs = at<uint32_t>(scratch, p.off_leaf_slabs);
+  uint32_t* pos_below = at<uint32_t>(scratch, p.off_pos_below);
+  double* ap_part = at<double>(scratch, p.off_ap_part);
+  ApTotals* totals = at<ApTotals>(scratch, p.off_ap_totals);
+  TE_CUDA_TRY(cudaFuncSetAttribute(leaf_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLeafSmem));
+  TE_CUDA_TRY(cudaFuncSetAttribute(leaf_count_ap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLeafSmem));
+  TE_CUDA_TRY(cudaMemsetAsync(ap_part, 0, (size_t)kLeafSegs * 8, st));
+  {
+    TE_PROF("leaf_tiny", st);
+    leaf_tiny_kernel<<<kLeafSegs / 8, 256, 0, st>>>(keys, seg_start, stats);
+  }
+  {
+    TE_PROF("leaf_plan", st);
+    leaf_plan_kernel<<<1, 1024, 0, st>>>(seg_start, p.leaf_piece, p.leaf_max_items, p.leaf_max_slabs, items, multi, hdr);
+  }
+  {
+    TE_PROF("leaf_count", st);
+    leaf_count_kernel<<<sms, kLeafBlock, kLeafSmem, st>>>(keys, items, hdr, stats, slabs);
+  }
+  {
+    TE_PROF("leaf_merge", st);
+    leaf_merge_kernel<<<sms, kLeafBlock, 0, st>>>(multi, hdr, slabs, stats);
+  }
+  {
+    TE_PROF("leaf_ap_prefix", st);
+    leaf_ap_prefix_kernel<<<1, 1024, 0, st>>>(stats, pos_below, totals);
+  }
+  TE_LAUNCH_CHECK();
+  TE_CUDA_TRY(cudaMemsetAsync(&hdr->ticket, 0, sizeof(uint32_t), st));  // the same work list, from the top
+  {
+    TE_PROF("leaf_tiny_ap", st);
+    leaf_tiny_ap_kernel<<<kLeafSegs / 8, 256, 0, st>>>(keys, seg_start, pos_below, totals, ap_part);
+  }
+  {
+    TE_PROF("leaf_count_ap", st);
+    leaf_count_ap_kernel<<<sms, kLeafBlock, kLeafSmem, st>>>(keys, items, hdr, seg_start, pos_below, totals, ap_part, slabs);
+  }
+  {
+    TE_PROF("leaf_merge_ap", st);
+    leaf_merge_ap_kernel<<<sms, kLeafBlock, 0, st>>>(multi, hdr, slabs, seg_start, pos_below, totals, ap_part);
+  }
+  {
+    TE_PROF("leaf_ap_reduce", st);
+    leaf_ap_reduce_kernel<<<1, 1024, 0, st>>>(ap_part, totals, &at<RankScalars>(scratch, p.off_scal)->flags, out);
   }
   TE_LAUNCH_CHECK();
   return TE_OK;
@@ -1252,7 +1315,7 @@ int leaf_passes_ranges_dtype(const RankPlan& p, void* scratch, const float* scor
 }
 
 int binary_auroc_leaf(const float* score, const void* target, int32_t dt, int64_t n, double* out, void* scratch,
-                      size_t scratch_bytes, cudaStream_t st) {
+                      size_t scratch_bytes, cudaStream_t st, int mode = 0) {
   const RankPlan p = make_plan(n, false, true, true, true);
   if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
   int sms = 0;
@@ -1267,8 +1330,9 @@ int binary_auroc_leaf(const float* score, const void* target, int32_t dt, int64_
   if (n > 0 && msd && ((uintptr_t)score & 15) == 0) {
     const int rc = leaf_passes_msd_dtype(p, scratch, score, target, dt, ka, kb, sms, st);
     if (rc) return rc;
-    return finish_leaf(p, ka, out, scratch, sms, st, nullptr, true);
+    return mode == 1 ? finish_leaf_ap(p, ka, out, scratch, sms, st) : finish_leaf(p, ka, out, scratch, sms, st, nullptr, true);
   }
+  if (mode == 1) return TE_ERR_UNSUPPORTED;  // (average precision rides on the MSD passes only)
   if (n > 0 && range_pass_from_env() && p.sort_block == 512 && p.sort_ipt == kSortIptDefault) {
     const int rc = leaf_passes_ranges_dtype(p, scratch, score, target, dt, ka, kb, sms, st);
     if (rc) return rc;
@@ -1286,8 +1350,13 @@ int binary_rank_packed(const float* score, const void* target, int32_t dt, int64
                        double* out, void* scratch, size_t scratch_bytes, cudaStream_t st,
                        int variant = TE_RANK_AUTO) {
   if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
-  if (mode == 0 && (variant == TE_RANK_COUNTING || (variant == TE_RANK_AUTO && n >= leaf_min_n_from_env())))
-    return binary_auroc_leaf(score, target, dt, n, out, scratch, scratch_bytes, st);
+  static const bool msd_on = [] {
+    const char* e = getenv("TE_B200_MSD_PASSES");
+    return e ? atoi(e) != 0 : true;
+  }();
+  const bool counting_ok = mode == 0 || (msd_on && n > 0 && ((uintptr_t)score & 15) == 0);
+  if (counting_ok && (variant == TE_RANK_COUNTING || (variant == TE_RANK_AUTO && n >= leaf_min_n_from_env())))
+    return binary_auroc_leaf(score, target, dt, n, out, scratch, scratch_bytes, st, mode);
   const RankPlan p = make_plan(n, false, true, true);
   if (!scratch || scratch_bytes < p.total) return TE_ERR_SCRATCH_TOO_SMALL;
   int sms = 0;
@@ -2157,6 +2226,15 @@ extern "C" int te_binary_auprc(const float* score, const void* target, int32_t t
   if (!out || (n > 0 && (!score || !target))) return TE_ERR_INVALID_ARGUMENT;
   return binary_rank_packed(score, target, target_dtype, n, 1, out, scratch, scratch_bytes,
                             (cudaStream_t)stream);
+}
+
+extern "C" int te_binary_auprc_variant(const float* score, const void* target, int32_t target_dtype,
+                                       int64_t n, double* out, void* scratch, size_t scratch_bytes,
+                                       int32_t variant, void* stream) {
+  if (!out || (n > 0 && (!score || !target))) return TE_ERR_INVALID_ARGUMENT;
+  if (variant != TE_RANK_AUTO && variant != TE_RANK_SORT && variant != TE_RANK_COUNTING) return TE_ERR_INVALID_ARGUMENT;
+  return binary_rank_packed(score, target, target_dtype, n, 1, out, scratch, scratch_bytes,
+                            (cudaStream_t)stream, variant);
 }
 
 extern "C" size_t te_sort_u32_scratch_bytes(int64_t n, int32_t with_values) {

@@ -247,8 +247,8 @@ def binary_auroc_packed(score: torch.Tensor, target: torch.Tensor, variant: int 
     return _binary_rank("te_binary_auroc_variant", score, target, variant)
 
 
-def binary_auprc_packed(score: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
-    return _binary_rank("te_binary_auprc", score, target)
+def binary_auprc_packed(score: torch.Tensor, target: torch.Tensor, variant: int = N.TE_RANK_AUTO) -> torch.Tensor:
+    return _binary_rank("te_binary_auprc_variant", score, target, variant)
 
 
 def _binary_rank_general(mode: int, score: torch.Tensor, target: torch.Tensor, weight: Optional[torch.Tensor]) -> torch.Tensor:
