@@ -1226,10 +1226,23 @@ int leaf_passes_ranges(const RankPlan& p, void* scratch, const float* score, con
 //   raw_keys == nullptr: (score, target) in; pass 1 packs into kb, pass 2 -> ka; result in ka.
 //   raw_keys given: raw -> ka -> kb; result in kb.
 template <typename TargetT>
+int leaf_passes_msd_geom(const RankPlan& p, void* scratch, const float* score, const TargetT* target,
+                         const uint32_t* raw_keys, uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st,
+                         const SlabView view, const uint32_t* n_dev);
+
+template <typename TargetT>
 int leaf_passes_msd(const RankPlan& p, void* scratch, const float* score, const TargetT* target,
                     const uint32_t* raw_keys, uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st,
                     const SlabView view = SlabView{nullptr, 0, 0, 0}, const uint32_t* n_dev = nullptr) {
-  constexpr int TILE = kPrBlock * kPrIpt;
+  return leaf_passes_msd_geom<TargetT>(p, scratch, score, target, raw_keys, ka, kb, sms, st, view, n_dev);
+}
+
+template <typename TargetT, int PBLOCK, int PIPT>
+int leaf_passes_msd_impl(const RankPlan& p, void* scratch, const float* score, const TargetT* target,
+                    const uint32_t* raw_keys, uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st,
+                    const SlabView view, const uint32_t* n_dev) {
+  constexpr int TILE = PBLOCK * PIPT;
+  constexpr int kCtasPerSm = 1024 / PBLOCK;
   const size_t part_smem = (size_t)2 * TILE * sizeof(uint32_t);
   uint32_t* joint = at<uint32_t>(scratch, p.off_joint);
   uint32_t* seg_start = at<uint32_t>(scratch, p.off_seg_start);
@@ -1262,7 +1275,7 @@ int leaf_passes_msd(const RankPlan& p, void* scratch, const float* score, const 
   // both instantiations of a pass are launched; the device-side tables decide which one works
   // (the host never sees the histogram)
   const uint32_t tiles1 = (p.n + TILE - 1) / TILE;
-  const uint32_t grid1 = tiles1 < (uint32_t)sms ? tiles1 : (uint32_t)sms;
+  const uint32_t grid1 = tiles1 < (uint32_t)(sms * kCtasPerSm) ? tiles1 : (uint32_t)(sms * kCtasPerSm);
   uint32_t* out1 = raw_keys ? ka : kb;
   uint32_t* out2 = raw_keys ? kb : ka;
   const uint32_t* in1 = raw_keys ? raw_keys : reinterpret_cast<const uint32_t*>(score);
@@ -1272,22 +1285,34 @@ int leaf_passes_msd(const RankPlan& p, void* scratch, const float* score, const 
     TE_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)part_smem));
     TE_PROF(name, st);
     // (pass 1 reads through the view and needs no count; pass 2 and later take it from n_dev)
-    kern<<<grid, kPrBlock, part_smem, st>>>(in, bits, outp, p.n, segs ? n_dev : nullptr, segs, tables, cursors,
+    kern<<<grid, PBLOCK, part_smem, st>>>(in, bits, outp, p.n, segs ? n_dev : nullptr, segs, tables, cursors,
                                             segs ? SlabView{nullptr, 0, 0, 0} : view);
     TE_LAUNCH_CHECK();
     return TE_OK;
   };
   int rc;
   if (raw_keys) {
-    if ((rc = launch(cursor_partition_kernel<false, false, false>, "cursor_pass_top", grid1, in1, bits1, out1, nullptr, cursor1))) return rc;
-    if ((rc = launch(cursor_partition_kernel<false, false, true>, "cursor_pass_top_hot", grid1, in1, bits1, out1, nullptr, cursor1))) return rc;
+    if ((rc = launch(cursor_partition_kernel<false, false, false, PBLOCK, PIPT>, "cursor_pass_top", grid1, in1, bits1, out1, nullptr, cursor1))) return rc;
+    if ((rc = launch(cursor_partition_kernel<false, false, true, PBLOCK, PIPT>, "cursor_pass_top_hot", grid1, in1, bits1, out1, nullptr, cursor1))) return rc;
   } else {
-    if ((rc = launch(cursor_partition_kernel<false, true, false>, "cursor_pass_top_pack", grid1, in1, bits1, out1, nullptr, cursor1))) return rc;
-    if ((rc = launch(cursor_partition_kernel<false, true, true>, "cursor_pass_top_pack_hot", grid1, in1, bits1, out1, nullptr, cursor1))) return rc;
+    if ((rc = launch(cursor_partition_kernel<false, true, false, PBLOCK, PIPT>, "cursor_pass_top_pack", grid1, in1, bits1, out1, nullptr, cursor1))) return rc;
+    if ((rc = launch(cursor_partition_kernel<false, true, true, PBLOCK, PIPT>, "cursor_pass_top_pack_hot", grid1, in1, bits1, out1, nullptr, cursor1))) return rc;
   }
-  if ((rc = launch(cursor_partition_kernel<true, false, false>, "cursor_pass_low", (uint32_t)sms, out1, nullptr, out2, seg_start, cursor2))) return rc;
-  if ((rc = launch(cursor_partition_kernel<true, false, true>, "cursor_pass_low_hot", (uint32_t)sms, out1, nullptr, out2, seg_start, cursor2))) return rc;
+  if ((rc = launch(cursor_partition_kernel<true, false, false, PBLOCK, PIPT>, "cursor_pass_low", (uint32_t)(sms * kCtasPerSm), out1, nullptr, out2, seg_start, cursor2))) return rc;
+  if ((rc = launch(cursor_partition_kernel<true, false, true, PBLOCK, PIPT>, "cursor_pass_low_hot", (uint32_t)(sms * kCtasPerSm), out1, nullptr, out2, seg_start, cursor2))) return rc;
   return TE_OK;
+}
+
+template <typename TargetT>
+int leaf_passes_msd_geom(const RankPlan& p, void* scratch, const float* score, const TargetT* target,
+                         const uint32_t* raw_keys, uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st,
+                         const SlabView view, const uint32_t* n_dev) {
+  static const int geom = [] {
+    const char* e = getenv("TE_B200_PART_GEOM");
+    return e ? atoi(e) : 0;
+  }();
+  if (geom == 1) return leaf_passes_msd_impl<TargetT, 512, 24>(p, scratch, score, target, raw_keys, ka, kb, sms, st, view, n_dev);
+  return leaf_passes_msd_impl<TargetT, kPrBlock, kPrIpt>(p, scratch, score, target, raw_keys, ka, kb, sms, st, view, n_dev);
 }
 
 int leaf_passes_msd_dtype(const RankPlan& p, void* scratch, const float* score, const void* target, int32_t dt,

@@ -45,8 +45,9 @@ struct LeafItem {   // one piece of one segment
 struct LeafMulti {  // a segment with several pieces
   uint32_t seg, first_slab, npieces, pad;
 };
-struct alignas(32) SegStat {
-  unsigned long long A, P, N, pad;  // 2U inside the segment, positives, negatives
+struct alignas(16) SegStat {  // 16 bytes: the 65 536 of them are read by ONE CTA at the end, through one SM's L2 port
+  unsigned long long A;        // 2U inside the segment
+  uint32_t P, N;               // positives, negatives (a segment holds fewer than 2^31 keys)
 };
 struct LeafHeader {
   uint32_t ticket, n_items, n_multi, pad;
@@ -87,7 +88,7 @@ __global__ void __launch_bounds__(1024)
     return cnt <= kLeafTiny ? 0u : (cnt + piece - 1) / piece;  // (tiny segments: leaf_tiny_kernel)
   };
   uint32_t n_it = 0, n_sl = 0, n_mu = 0;
-#pragma unroll 4
+#pragma unroll 16
   for (int j = 0; j < ROWS; ++j) {
     uint32_t b, e;
     const uint32_t np = pieces_of((warp * ROWS + j) * 32 + lane, b, e);
@@ -110,10 +111,14 @@ __global__ void __launch_bounds__(1024)
     hdr->n_multi = fits ? tot_mu : 0u;
   }
   if (!fits) return;
-  for (int j = 0; j < ROWS; ++j) {
-    const uint32_t s = (warp * ROWS + j) * 32 + lane;
-    uint32_t b, e;
-    const uint32_t np = pieces_of(s, b, e);
+  for (int j0 = 0; j0 < ROWS; j0 += 8) {
+   uint32_t b8[8], e8[8], np8[8];  // eight rows' loads in flight at once (one CTA: latency is all there is)
+#pragma unroll
+   for (int q = 0; q < 8; ++q) np8[q] = pieces_of((warp * ROWS + j0 + q) * 32 + lane, b8[q], e8[q]);
+#pragma unroll
+   for (int q = 0; q < 8; ++q) {
+    const uint32_t s = (warp * ROWS + j0 + q) * 32 + lane;
+    const uint32_t b = b8[q], e = e8[q], np = np8[q];
     const uint32_t sl = np > 1 ? np : 0u, mu = np > 1 ? 1u : 0u;
     uint32_t i_it = np, i_sl = sl, i_mu = mu;
 #pragma unroll
@@ -140,6 +145,7 @@ __global__ void __launch_bounds__(1024)
     at_it += __shfl_sync(kFull, i_it, 31);
     at_sl += __shfl_sync(kFull, i_sl, 31);
     at_mu += __shfl_sync(kFull, i_mu, 31);
+   }
   }
 }
 
@@ -186,7 +192,7 @@ __global__ void __launch_bounds__(256)
   npos = warp_sum(npos);
   if (lane == 0) {
     SegStat r;
-    r.A = acc, r.P = npos, r.N = cnt - npos, r.pad = 0;
+    r.A = acc, r.P = npos, r.N = cnt - npos;
     seg_stats[s] = r;
   }
 }
@@ -235,7 +241,7 @@ __device__ __forceinline__ void leaf_walk(const uint4 (&v)[kLeafVecPerThread], L
       nn += t.N;
     }
     SegStat r;
-    r.A = a, r.P = p, r.N = nn, r.pad = 0;
+    r.A = a, r.P = (uint32_t)p, r.N = (uint32_t)nn;
     *out = r;
   }
 }
@@ -349,9 +355,13 @@ __global__ void __launch_bounds__(1024)
   constexpr int ROWS = kLeafSegs / 1024;
   unsigned long long a = 0;
   uint32_t p = 0, carry = 0;
-#pragma unroll 4
-  for (int j = 0; j < ROWS; ++j) {
-    const SegStat s = seg_stats[(warp * ROWS + j) * 32 + lane];
+  for (int j0 = 0; j0 < ROWS; j0 += 8) {
+   SegStat s8[8];
+#pragma unroll
+   for (int q = 0; q < 8; ++q) s8[q] = seg_stats[(warp * ROWS + j0 + q) * 32 + lane];
+#pragma unroll
+   for (int q = 0; q < 8; ++q) {
+    const SegStat s = s8[q];
     const uint32_t nn = (uint32_t)s.N;
     uint32_t incl = nn;
 #pragma unroll
@@ -362,6 +372,7 @@ __global__ void __launch_bounds__(1024)
     a += s.A + 2ull * s.P * (unsigned long long)(carry + incl - nn);
     p += (uint32_t)s.P;
     carry += __shfl_sync(kFull, incl, 31);
+   }
   }
   a = warp_sum(a);
   const unsigned long long pw = warp_sum((unsigned long long)p);

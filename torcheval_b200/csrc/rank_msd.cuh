@@ -258,16 +258,21 @@ __global__ void __launch_bounds__(1024)
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   constexpr int ROWS = kLeafSegs / 1024;
   uint32_t tot = 0;
-#pragma unroll 8
+#pragma unroll 16
   for (int j = 0; j < ROWS; ++j) tot += joint[(warp * ROWS + j) * 32 + lane];
   tot = warp_sum(tot);
   if (lane == 0) ws[warp] = tot;
   __syncthreads();
   uint32_t at = 0;
   for (int w = 0; w < (int)warp; ++w) at += ws[w];
-  for (int j = 0; j < ROWS; ++j) {
-    const uint32_t s = (warp * ROWS + j) * 32 + lane;
-    const uint32_t c = joint[s];
+  for (int j0 = 0; j0 < ROWS; j0 += 8) {
+   uint32_t c8[8];  // eight independent loads in flight, then eight warp scans (one CTA: latency is all there is)
+#pragma unroll
+   for (int q = 0; q < 8; ++q) c8[q] = joint[(warp * ROWS + j0 + q) * 32 + lane];
+#pragma unroll
+   for (int q = 0; q < 8; ++q) {
+    const uint32_t s = (warp * ROWS + j0 + q) * 32 + lane;
+    const uint32_t c = c8[q];
     uint32_t incl = c;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -280,6 +285,7 @@ __global__ void __launch_bounds__(1024)
     if ((s & (kRadix - 1)) == 0) cursor1[s >> kRadixBits] = excl;
     at += __shfl_sync(kFull, incl, 31);
     if (s == kLeafSegs - 1) seg_start[kLeafSegs] = excl + c;
+   }
   }
   __syncthreads();  // seg_start of every bucket boundary is in global memory, visible to this CTA
   if (tid < kRadix) {
@@ -335,7 +341,7 @@ __global__ void __launch_bounds__(1024)
 // Slot i of thread t is record (i / 4 * BLOCK + t) * 4 + i % 4 of the tile (16-byte accesses); ranks
 // inside a digit are handed out in arrival order (one shared atomic per record on a CTA-wide table).
 template <bool BUCKETED, bool PACK, bool HOT, int BLOCK = kPrBlock, int IPT = kPrIpt>
-__global__ void __launch_bounds__(BLOCK, 1)
+__global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
     cursor_partition_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ label_bits,
                             uint32_t* __restrict__ keys_out, uint32_t n, const uint32_t* __restrict__ n_dev,
                             const uint32_t* __restrict__ seg_start, const MsdTables* __restrict__ tables,
