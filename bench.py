@@ -158,6 +158,44 @@ def dist_env():
     return rank, world, local
 
 
+# ----------------------------------------------------------------------------------- host side
+def gpu_numa_cpus(local: int):
+    """(numa node, cpus of that node) of CUDA device `local`, from sysfs; (None, None) when the host
+    does not say (single node, a VM without topology, no sysfs)."""
+    try:
+        pr = torch.cuda.get_device_properties(local)
+        addr = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        node = int(Path(f"/sys/bus/pci/devices/{addr}/numa_node").read_text())
+        if node < 0:
+            return None, None
+        cpus = set()
+        for part in Path(f"/sys/devices/system/node/node{node}/cpulist").read_text().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        return (node, cpus) if cpus else (None, None)
+    except Exception:
+        return None, None
+
+
+def pinned_like(x: torch.Tensor, local: int) -> torch.Tensor:
+    """A pinned host copy of x whose pages sit on the NUMA node of GPU `local` (the process is
+    bound to that node only while the pages are allocated: first touch places them).  What a
+    NUMA-aware data loader does; TE_BENCH_NUMA=0 leaves the pages where the launcher put the
+    process."""
+    node, cpus = gpu_numa_cpus(local) if os.environ.get("TE_BENCH_NUMA", "1") != "0" else (None, None)
+    before = os.sched_getaffinity(0)
+    if cpus:
+        os.sched_setaffinity(0, cpus)
+    try:
+        h = torch.empty(x.shape, dtype=x.dtype, pin_memory=True)
+    finally:
+        if cpus:
+            os.sched_setaffinity(0, before)
+    h.copy_(x)
+    return h
+
+
 # ----------------------------------------------------------------------------------- data
 def make_scores(n: int, device, rank: int):
     g = torch.Generator(device=device).manual_seed(SEED + rank)
@@ -292,10 +330,8 @@ def run_ours(args) -> dict:
         binned = guarded(binned_sync_bench, args, x, y, world, device)
         parity = parity_checks(x, y, out, world, rank, device)  # raises: a wrong sharded result fails the run
     if world == 1:
-        xh = torch.empty(n_local, dtype=torch.float32, pin_memory=True)
-        yh = torch.empty(n_local, dtype=torch.int64, pin_memory=True)
-        xh.copy_(x)
-        yh.copy_(y)
+        xh = pinned_like(x, local)
+        yh = pinned_like(y, local)
         torch.cuda.synchronize()
         del x, y
         torch.cuda.empty_cache()
@@ -328,8 +364,8 @@ def run_ours(args) -> dict:
         from torcheval_b200.metrics import BinaryAUROC
         from torcheval_b200.metrics.toolkit import sync_and_compute
 
-        xh = torch.empty(n_local, dtype=torch.float32, pin_memory=True).copy_(x)
-        yh = torch.empty(n_local, dtype=torch.int64, pin_memory=True).copy_(y)
+        xh = pinned_like(x, local)
+        yh = pinned_like(y, local)
         torch.cuda.synchronize()
         del x, y
         torch.cuda.empty_cache()

@@ -8,7 +8,7 @@ from typing import List, Optional, Tuple, Union
 import torch
 
 from .... import _binned
-from ..tensor_utils import _create_threshold_tensor
+from ..tensor_utils import THR_FIRST, THR_LAST, THR_RANGE, THR_UNSORTED, _create_threshold_tensor, _threshold_faults
 from .binned_precision_recall_curve import _optimization_param_check
 
 DEFAULT_NUM_THRESHOLD = 100
@@ -122,13 +122,21 @@ def _compute_riemann_integrals_from_counts(
 def _auprc_threshold_check(threshold: torch.Tensor) -> None:
     if threshold.ndim != 1:
         raise ValueError(f"`threshold` should be 1-dimensional, but got {threshold.ndim}D tensor.")
-    if (torch.diff(threshold) < 0.0).any():
+    faults = _threshold_faults(threshold)
+    if faults is None:  # empty: the reference's statements and their errors, one by one
+        faults = (
+            (THR_UNSORTED if (torch.diff(threshold) < 0.0).any() else 0)
+            | (THR_RANGE if (threshold < 0.0).any() or (threshold > 1.0).any() else 0)
+            | (THR_FIRST if threshold[0] != 0 else 0)
+            | (THR_LAST if threshold[-1] != 1 else 0)
+        )
+    if faults & THR_UNSORTED:
         raise ValueError("The `threshold` should be a sorted tensor.")
-    if (threshold < 0.0).any() or (threshold > 1.0).any():
+    if faults & THR_RANGE:
         raise ValueError("The values in `threshold` should be in the range of [0, 1].")
-    if threshold[0] != 0:
+    if faults & THR_FIRST:
         raise ValueError("First value in `threshold` should be 0.")
-    if threshold[-1] != 1:
+    if faults & THR_LAST:
         raise ValueError("Last value in `threshold` should be 1.")
 
 

@@ -8,7 +8,7 @@ import torch
 
 from .... import _binned
 from ...._ranking import compute_device, stage
-from ..tensor_utils import _create_threshold_tensor
+from ..tensor_utils import THR_RANGE, THR_UNSORTED, _create_threshold_tensor, _threshold_faults
 
 DEFAULT_NUM_THRESHOLD = 200
 
@@ -80,9 +80,14 @@ def _multiclass_binned_auroc_compute(
 
 
 def _threshold_range_check(threshold: torch.Tensor) -> None:
-    if (torch.diff(threshold) < 0.0).any():
+    faults = _threshold_faults(threshold)
+    if faults is None:
+        faults = (THR_UNSORTED if (torch.diff(threshold) < 0.0).any() else 0) | (
+            THR_RANGE if (threshold < 0.0).any() or (threshold > 1.0).any() else 0
+        )
+    if faults & THR_UNSORTED:
         raise ValueError("The `threshold` should be a sorted tensor.")
-    if (threshold < 0.0).any() or (threshold > 1.0).any():
+    if faults & THR_RANGE:
         raise ValueError("The values in `threshold` should be in the range of [0, 1].")
 
 
