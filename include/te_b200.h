@@ -375,6 +375,19 @@ TE_API int te_sort_u32(const uint32_t* keys_in, uint32_t* keys_out, const uint32
                        uint32_t* vals_out, int64_t n, void* scratch, size_t scratch_bytes,
                        void* stream);
 
+/* Dense ranks of 64-bit scores: rank_out[i] = #{distinct values < x[i]} (uint32, device), the road
+ * for scores the packed 32-bit key cannot hold (float64 probabilities, int64 beyond 2^24).  The
+ * reference sorts any dtype in place (functional/classification/auroc.py:121); the ranking kernels
+ * here only look at order and ties, which the dense rank carries (as the bit pattern of a
+ * non-negative float it goes through te_binary_auroc and friends unchanged).  dtype: TE_DTYPE_F64
+ * (-0.0 ties with +0.0; NaNs order above +inf by bit pattern) or TE_DTYPE_I64.  values_out (NULL or
+ * n elements of the input's type): values_out[r] = the score of rank r — the thresholds of
+ * precision_recall_curve.py:89-98; n_distinct (NULL or one uint32, device) = number of ranks.
+ * Two stable pair sorts (low word, high word) with te_sort_u32's passes + a chunked scan. */
+TE_API size_t te_dense_rank_scratch_bytes(int64_t n);
+TE_API int te_dense_rank(const void* x, int32_t dtype, int64_t n, uint32_t* rank_out, void* values_out,
+                         uint32_t* n_distinct, void* scratch, size_t scratch_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -169,6 +169,12 @@ def sort_u32(keys, vals=None):
     return ok, (None if vals is None else vals[torch.from_numpy(order)])
 
 
+def dense_rank(x, with_values=False):
+    vals, inv = np.unique(_np(x), return_inverse=True)
+    rank = torch.from_numpy(inv.reshape(tuple(x.shape)).astype(np.int32))
+    return rank, (torch.from_numpy(vals) if with_values else None)
+
+
 def _digit_hist(k):
     """int32[1024]: the four 8-bit digit histograms of uint32 keys (pass-major)."""
     return np.concatenate([np.bincount((k >> np.uint32(8 * p)) & np.uint32(255), minlength=256) for p in range(4)]).astype(np.int32)
@@ -337,7 +343,7 @@ _NAMES = [
     "binned_hist2d_update_", "binned_counts", "binned_integrate", "binary_auroc_packed",
     "binary_auprc_packed", "binary_auroc_general", "binary_auprc_general", "sort_u32", "rank_pack", "ovr_rank",
     "partition_u32", "binary_auroc_from_keys", "binary_auprc_from_keys_begin", "binary_auprc_from_keys_finish", "binary_pr_curve",
-    "select_splitters", "combine_auroc_stats",
+    "select_splitters", "combine_auroc_stats", "dense_rank",
 ]
 
 

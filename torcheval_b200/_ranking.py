@@ -57,20 +57,33 @@ def _floor_f32_scores(x: torch.Tensor) -> torch.Tensor:
         return torch.where(above, torch.nextafter(y, torch.full_like(y, float("-inf"))), y)
 
 
+def _dense_rank_scores(x: torch.Tensor, with_values: bool = False):
+    """(dense ranks of `x` as float32 BIT PATTERNS, distinct values ascending or None): the native
+    rank transform (te_dense_rank: two pair sorts on the 64-bit image of the scores + a scan).
+    Ranks order and tie exactly like the scores, non-negative floats order like their bit patterns,
+    and the kernels only ever compare and sort the bits."""
+    if x.numel() > 0x7F800000:  # a rank would read as inf / NaN
+        raise NotImplementedError(f"{x.numel()} scores of dtype {x.dtype}")
+    if x.is_floating_point():
+        wide = x if x.dtype == torch.float64 else x.double()  # exact
+    else:
+        wide = x if x.dtype == torch.int64 else x.to(torch.int64)
+    rank, values = ops.dense_rank(wide, with_values)
+    if values is not None and values.dtype != x.dtype:
+        values = values.to(x.dtype)
+    return rank.view(torch.float32), values
+
+
 def _rank_scores(x: torch.Tensor) -> torch.Tensor:
     """A float32 tensor with the same order and the same ties as `x` — all the ranking kernels
     look at.  Scores that float32 holds exactly are passed through; anything else (float64
-    probabilities, large integers) is replaced by its dense rank, stored as the float whose BIT
-    PATTERN is the rank: non-negative floats order like their bit patterns, and the kernels only
-    ever compare and sort the bits.  (The rank transform is a library sort, torch.unique; it is
-    the slow road for inputs the packed 32-bit key cannot hold.)"""
+    probabilities, large integers) is replaced by its dense rank (the reference sorts any dtype in
+    place, auroc.py:121; here the 64-bit sort is its own kernel train and the 32-bit kernels stay
+    as they are)."""
     try:
         return _as_f32_scores(x)
     except NotImplementedError:
-        _, inv = torch.unique(x, sorted=True, return_inverse=True)
-        if inv.numel() and int(inv.max()) >= 0x7F800000:
-            raise
-        return inv.to(torch.int32).view(torch.float32)
+        return _dense_rank_scores(x)[0]
 
 
 def binary_auroc(input: torch.Tensor, target: torch.Tensor, weight: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -181,10 +194,10 @@ def binary_precision_recall_curve(input: torch.Tensor, target: torch.Tensor, pos
     if flags:
         # negative scores, or a dtype float32 cannot hold: dense ranks go through the kernel (they
         # order and tie like the scores), the thresholds are the distinct score values themselves
-        values, inv = torch.unique(x, sorted=True, return_inverse=True)
+        ranks, values = _dense_rank_scores(x, with_values=True)
         if lab.dtype != torch.uint8:
             lab = (t == pos_label).to(torch.uint8)
-        curve, flags = ops.binary_pr_curve(inv.to(torch.int32).view(torch.float32), lab)
+        curve, flags = ops.binary_pr_curve(ranks, lab)
         assert flags == 0
     precision, recall, thresholds = curve
     thresholds = values if values is not None else thresholds.to(input.dtype)

@@ -19,6 +19,7 @@
 #include <stdlib.h>
 
 #include "rank_sort.cuh"
+#include "rank_dense.cuh"
 #include "rank_leaf.cuh"
 #include "rank_part.cuh"
 #include "rank_exchange.cuh"
@@ -2286,6 +2287,113 @@ extern "C" int te_sort_u32(const uint32_t* keys_in, uint32_t* keys_out, const ui
   // in -> tmp -> out -> tmp -> out
   return run_passes(p, scratch, keys_in, at<uint32_t>(scratch, p.off_keys_a), keys_out, vals_in,
                     wv ? at<uint32_t>(scratch, p.off_vals_a) : nullptr, vals_out, st);
+}
+
+// ---- dense ranks of 64-bit scores (rank_dense.cuh) ------------------------------------------------
+namespace {
+struct DensePlan {
+  RankPlan sort;
+  size_t off_buf[6], off_chunks, off_sort, total;
+  uint32_t n, nchunks;
+};
+DensePlan make_dense_plan(int64_t n64) {
+  DensePlan d;
+  d.n = (uint32_t)n64;
+  d.nchunks = (uint32_t)((n64 + kDrChunk - 1) / kDrChunk);
+  d.sort = make_plan(n64, true, true, false);
+  size_t off = 0;
+  for (int b = 0; b < 6; ++b) {
+    d.off_buf[b] = off;
+    off += align_up((size_t)n64 * sizeof(uint32_t), 256);
+  }
+  d.off_chunks = off;
+  off += align_up(((size_t)d.nchunks + 1) * sizeof(uint32_t), 256);
+  d.off_sort = off;
+  off += d.sort.total;
+  d.total = off;
+  return d;
+}
+// stable pair sort through the scratch of one RankPlan: (k_in, v_in) -> (k_out, v_out)
+int sort_pairs_u32(const RankPlan& p, void* scratch, const uint32_t* k_in, uint32_t* k_out, const uint32_t* v_in,
+                   uint32_t* v_out, int sms, cudaStream_t st) {
+  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
+  const int rc = launch_ingest<kRawKeys, long long>(nullptr, nullptr, k_in, p, nullptr, nullptr, scratch, sms, st);
+  if (rc) return rc;
+  return run_passes(p, scratch, k_in, at<uint32_t>(scratch, p.off_keys_a), k_out, v_in,
+                    at<uint32_t>(scratch, p.off_vals_a), v_out, st);
+}
+}  // namespace
+
+extern "C" size_t te_dense_rank_scratch_bytes(int64_t n) {
+  if (n < 0 || n > 0x7fffffffLL) return 0;
+  return make_dense_plan(n).total;
+}
+
+extern "C" int te_dense_rank(const void* x, int32_t dtype, int64_t n, uint32_t* rank_out, void* values_out,
+                             uint32_t* n_distinct, void* scratch, size_t scratch_bytes, void* stream) {
+  if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  if (dtype != TE_DTYPE_F64 && dtype != TE_DTYPE_I64) return TE_ERR_UNSUPPORTED;
+  if (n > 0 && (!x || !rank_out)) return TE_ERR_INVALID_ARGUMENT;
+  const DensePlan d = make_dense_plan(n);
+  if (!scratch || scratch_bytes < d.total) return TE_ERR_SCRATCH_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n == 0) {
+    if (n_distinct) TE_CUDA_TRY(cudaMemsetAsync(n_distinct, 0, sizeof(uint32_t), st));
+    return TE_OK;
+  }
+  int sms = 0;
+  TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  uint32_t* lo = at<uint32_t>(scratch, d.off_buf[0]);
+  uint32_t* hi = at<uint32_t>(scratch, d.off_buf[1]);
+  uint32_t* idx = at<uint32_t>(scratch, d.off_buf[2]);   // iota, later the final permutation
+  uint32_t* tmp = at<uint32_t>(scratch, d.off_buf[3]);   // sorted low words / gathered words
+  uint32_t* perm1 = at<uint32_t>(scratch, d.off_buf[4]);
+  uint32_t* hi_s = at<uint32_t>(scratch, d.off_buf[5]);
+  uint32_t* chunks = at<uint32_t>(scratch, d.off_chunks);
+  void* sort_scratch = at<char>(scratch, d.off_sort);
+  const uint32_t un = (uint32_t)n;
+  const int64_t want_blocks = (n + kDrBlock - 1) / kDrBlock;
+  const int grid = (int)(want_blocks < (int64_t)sms * 16 ? want_blocks : (int64_t)sms * 16);
+  const unsigned long long* xx = (const unsigned long long*)x;
+  {
+    TE_PROF("dense_split", st);
+    if (dtype == TE_DTYPE_F64)
+      dense_split_kernel<true><<<grid, kDrBlock, 0, st>>>(xx, un, lo, hi, idx);
+    else
+      dense_split_kernel<false><<<grid, kDrBlock, 0, st>>>(xx, un, lo, hi, idx);
+  }
+  TE_LAUNCH_CHECK();
+  int rc = sort_pairs_u32(d.sort, sort_scratch, lo, tmp, idx, perm1, sms, st);  // by the low word
+  if (rc) return rc;
+  {
+    TE_PROF("dense_gather", st);
+    dense_gather_kernel<<<grid, kDrBlock, 0, st>>>(hi, perm1, un, tmp);
+  }
+  TE_LAUNCH_CHECK();
+  rc = sort_pairs_u32(d.sort, sort_scratch, tmp, hi_s, perm1, idx, sms, st);  // stable, by the high word
+  if (rc) return rc;
+  {
+    TE_PROF("dense_gather", st);
+    dense_gather_kernel<<<grid, kDrBlock, 0, st>>>(lo, idx, un, tmp);  // low words in sorted order
+  }
+  TE_LAUNCH_CHECK();
+  {
+    TE_PROF("dense_count", st);
+    dense_count_kernel<<<d.nchunks, kDrBlock, 0, st>>>(hi_s, tmp, un, chunks);
+  }
+  TE_LAUNCH_CHECK();
+  {
+    TE_PROF("dense_scan", st);
+    dense_scan_kernel<<<1, 1024, 0, st>>>(chunks, d.nchunks, n_distinct);
+  }
+  TE_LAUNCH_CHECK();
+  {
+    TE_PROF("dense_write", st);
+    dense_write_kernel<<<d.nchunks, kDrBlock, 0, st>>>(hi_s, tmp, idx, un, chunks, rank_out, xx,
+                                                       (unsigned long long*)values_out);
+  }
+  TE_LAUNCH_CHECK();
+  return TE_OK;
 }
 
 extern "C" size_t te_binary_rank_general_scratch_bytes(int64_t n) {

@@ -310,6 +310,33 @@ def sort_u32(keys: torch.Tensor, vals: Optional[torch.Tensor] = None) -> Tuple[t
     return out_k, out_v
 
 
+def dense_rank(x: torch.Tensor, with_values: bool = False):
+    """Dense ranks of float64 / int64 scores (any shape, ranked as one pool): (int32 tensor of x's
+    shape, distinct values ascending or None).  One host read (the number of distinct values) only
+    when the values are asked for."""
+    lib = N.load()
+    dev = _require_cuda(x)
+    assert x.dtype in (torch.float64, torch.int64)
+    flat = x.contiguous().reshape(-1)
+    n = flat.numel()
+    rank = torch.empty(n, dtype=torch.int32, device=dev)
+    values = torch.empty(n, dtype=x.dtype, device=dev) if with_values else None
+    count = torch.zeros(1, dtype=torch.int32, device=dev)
+    scratch = _scratch(lib.te_dense_rank_scratch_bytes(n), dev)
+    with torch.cuda.device(dev):
+        N.check(
+            "te_dense_rank",
+            lib.te_dense_rank(
+                flat.data_ptr(), N.TE_DTYPE_F64 if x.dtype == torch.float64 else N.TE_DTYPE_I64, n,
+                rank.data_ptr(), _ptr(values), count.data_ptr(), scratch.data_ptr(), scratch.numel(),
+                _stream_ptr(dev),
+            ),
+        )
+    if with_values:
+        values = values[: int(count.item())]
+    return rank.reshape(x.shape), values
+
+
 def ovr_rank(input: torch.Tensor, target: torch.Tensor, multilabel: bool, mode: int) -> torch.Tensor:
     """One-vs-rest AUROC (mode 0) / AUPRC (mode 1) of an (n, C) float32 matrix; float64 [C, 8],
     row c = [value, #pos, #neg, raw, flags, ...] as te_binary_auroc."""
