@@ -232,6 +232,16 @@ TE_API size_t te_binary_rank_general_scratch_bytes(int64_t n);
 TE_API int te_binary_auroc_general(const float* score, const void* target, int32_t target_dtype,
                                    const double* weight, int64_t n, double* out, void* scratch,
                                    size_t scratch_bytes, void* stream);
+
+/* `tasks` independent rankings of equal length in ONE launch train (grid.y = task): row y of
+ * score / target / weight starts y * ld elements after row 0 (ld >= n), out is [tasks][8] with row y
+ * as te_binary_auroc_general writes it.  What WindowedBinaryAUROC.compute and (tasks, n) inputs with
+ * weights need (torcheval/metrics/window/auroc.py:176-185 -> _binary_auroc_compute on 2-D tensors);
+ * tasks <= 65535. */
+TE_API size_t te_binary_auroc_general_batched_scratch_bytes(int64_t tasks, int64_t n);
+TE_API int te_binary_auroc_general_batched(const float* score, const void* target, int32_t target_dtype,
+                                           const double* weight, int64_t tasks, int64_t n, int64_t ld,
+                                           double* out, void* scratch, size_t scratch_bytes, void* stream);
 TE_API int te_binary_auprc_general(const float* score, const void* target, int32_t target_dtype,
                                    int64_t n, double* out, void* scratch, size_t scratch_bytes,
                                    void* stream);

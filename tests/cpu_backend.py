@@ -145,6 +145,11 @@ def binary_auroc_general(score, target, weight=None):
     return out
 
 
+def binary_auroc_general_batched(score, target, weight=None):
+    rows = [binary_auroc_general(score[k], target[k], None if weight is None else weight[k]) for k in range(score.shape[0])]
+    return torch.stack(rows) if rows else torch.zeros((0, 8), dtype=torch.float64)
+
+
 def binary_auprc_general(score, target):
     t = _np(target)
     out = torch.zeros(8, dtype=torch.float64)
@@ -343,7 +348,7 @@ _NAMES = [
     "binned_hist2d_update_", "binned_counts", "binned_integrate", "binary_auroc_packed",
     "binary_auprc_packed", "binary_auroc_general", "binary_auprc_general", "sort_u32", "rank_pack", "ovr_rank",
     "partition_u32", "binary_auroc_from_keys", "binary_auprc_from_keys_begin", "binary_auprc_from_keys_finish", "binary_pr_curve",
-    "select_splitters", "combine_auroc_stats", "dense_rank",
+    "select_splitters", "combine_auroc_stats", "dense_rank", "binary_auroc_general_batched",
 ]
 
 

@@ -547,6 +547,49 @@ def test_general_weights_as_payload(ops):
             close(b[0], oracle.binary_auroc(x, y2, w2)[0], RTOL64)
 
 
+def test_general_batched_tasks_vs_oracle(ops):
+    """(tasks, n) rankings in one launch train (grid.y = task): every row against the oracle and
+    against the single-task entry point; rows differ in what their payload can carry (float32
+    weights ride along, an inexact weight or a soft label makes that ROW gather by index)."""
+    rs = np.random.default_rng(77)
+    for tasks, n in ((3, 1), (5, 1000), (64, 1 << 14), (2, 300_001), (7, 8192 * 3 + 5)):
+        x = (rs.standard_normal((tasks, n)) * 3).astype(np.float32)
+        x[:, : n // 3] = np.round(x[:, : n // 3])
+        y = rs.integers(0, 2, (tasks, n)).astype(np.float64)
+        w = rs.random((tasks, n)).astype(np.float32).astype(np.float64)
+        if n > 10:
+            w[1, n // 2] = 1.0 + 2.0**-40  # row 1: weights float32 cannot hold
+            y[0, n // 3] = 0.25  # row 0: a soft label
+            y[tasks - 1] = 1.0  # last row: no negatives -> 0.5
+        for weight in (w, None):
+            W = None if weight is None else dev(weight, torch.float64)
+            got = ops.binary_auroc_general_batched(dev(x), dev(y, torch.float64), W).cpu().numpy()
+            assert got.shape == (tasks, 8)
+            for k in range(tasks):
+                v, tp, fp = oracle.binary_auroc(x[k], y[k], None if weight is None else weight[k])
+                close(got[k, 0], v, RTOL64)
+                close(got[k, 1], tp, 1e-9)
+                close(got[k, 2], fp, 1e-9)
+                one = ops.binary_auroc_general(dev(x[k]), dev(y[k], torch.float64), None if weight is None else dev(weight[k], torch.float64)).cpu().numpy()
+                close(got[k, 0], one[0], 1e-13)
+    # the functional entry point on 2-D input with weights, and the windowed metric on top of it
+    from torcheval_b200.metrics import WindowedBinaryAUROC
+    from torcheval_b200.metrics.functional.classification.auroc import binary_auroc
+
+    tasks, n = 6, 5000
+    x = rs.standard_normal((tasks, n)).astype(np.float32)
+    y = rs.integers(0, 2, (tasks, n))
+    w = rs.random((tasks, n)).astype(np.float32)
+    got = binary_auroc(dev(x), dev(y), num_tasks=tasks, weight=dev(w)).cpu().numpy()
+    want = [oracle.binary_auroc(x[k], y[k], w[k].astype(np.float64))[0] for k in range(tasks)]
+    np.testing.assert_allclose(got, want, rtol=RTOL64)
+    m = WindowedBinaryAUROC(num_tasks=tasks, max_num_samples=3000, device="cuda")
+    m.update(dev(x), dev(y), dev(w))
+    got = m.compute().cpu().numpy()
+    want = [oracle.binary_auroc(x[k, -3000:], y[k, -3000:], w[k, -3000:].astype(np.float64))[0] for k in range(tasks)]
+    np.testing.assert_allclose(got, want, rtol=RTOL64)
+
+
 def test_functional_binary_auroc_dispatch(ops, golden):
     from torcheval_b200.metrics.functional.classification.auroc import binary_auroc
 

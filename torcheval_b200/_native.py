@@ -46,6 +46,8 @@ SIGNATURES = {
     "te_binary_auprc_variant": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp, _sz, _i32, _vp]),
     "te_binary_rank_general_scratch_bytes": (_sz, [_i64]),
     "te_binary_auroc_general": (C.c_int, [_vp, _vp, _i32, _vp, _i64, _vp, _vp, _sz, _vp]),
+    "te_binary_auroc_general_batched_scratch_bytes": (_sz, [_i64, _i64]),
+    "te_binary_auroc_general_batched": (C.c_int, [_vp, _vp, _i32, _vp, _i64, _i64, _i64, _vp, _vp, _sz, _vp]),
     "te_binary_auprc_general": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp, _sz, _vp]),
     "te_ovr_rank_scratch_bytes": (_sz, [_i64]),
     "te_ovr_rank": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i32, _i32, _i32, _vp, _vp, _sz, _vp]),

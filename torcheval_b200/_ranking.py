@@ -94,16 +94,19 @@ def binary_auroc(input: torch.Tensor, target: torch.Tensor, weight: Optional[tor
     w = None if weight is None else stage(weight, dev, torch.float64)
     if x.dim() == 1:
         return _binary_auroc_row(x, t, w).to(out_dev)
-    if w is None and x.shape[0] > 1 and not t.is_floating_point() and bool(((t == 0) | (t == 1)).all()):
+    if x.shape[0] == 1:
+        return _binary_auroc_row(x[0], t[0], None if w is None else w[0]).reshape(1).to(out_dev)
+    if w is None and not t.is_floating_point() and bool(((t == 0) | (t == 1)).all()):
         # (tasks, n) without weights: the tasks are independent rankings of equal length, i.e. the
         # multilabel one-vs-rest problem on the transposed arrays — eight tasks per launch
         out = ops.ovr_rank(x.t().contiguous(), t.t().contiguous().to(torch.int64), True, 0)
         vals = out[:, 0].clone()
-        for k in torch.nonzero(out[:, 4] != 0).flatten().tolist():  # negative scores / soft labels
-            vals[k] = ops.binary_auroc_general(x[k], t[k], None)[0]
+        bad = torch.nonzero(out[:, 4] != 0).flatten()  # rows with negative scores
+        if bad.numel():
+            vals[bad] = ops.binary_auroc_general_batched(x[bad], t[bad], None)[:, 0]
         return vals.to(out_dev)
-    vals = [_binary_auroc_row(x[k], t[k], None if w is None else w[k]) for k in range(x.shape[0])]
-    return torch.stack(vals).to(out_dev)
+    # weights, soft labels: the general path, all tasks in one launch train (grid.y = task)
+    return ops.binary_auroc_general_batched(x, t, w)[:, 0].clone().to(out_dev)
 
 
 def _binary_auroc_row(x: torch.Tensor, t: torch.Tensor, w: Optional[torch.Tensor]) -> torch.Tensor:

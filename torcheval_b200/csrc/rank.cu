@@ -52,8 +52,17 @@ __global__ void __launch_bounds__(kIngestBlock, 1)
                        const uint32_t* __restrict__ raw_keys, uint32_t n, bool vec_ok,
                        uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                        uint32_t* ghist, RankScalars* scal, const uint32_t* __restrict__ payload_bad,
-                       const double* __restrict__ weight = nullptr) {
+                       const double* __restrict__ weight = nullptr, size_t bstride = 0, size_t in_stride = 0) {
   extern __shared__ uint32_t sh[];  // [pass][digit][lane]
+  // batched launches (grid.y = task): the inputs of task y start in_stride ELEMENTS further on,
+  // everything that lives in the scratch buffer bstride BYTES further on
+  if (in_stride) {
+    if (score) score += (size_t)blockIdx.y * in_stride;
+    if (target) target += (size_t)blockIdx.y * in_stride;
+    if (weight) weight += (size_t)blockIdx.y * in_stride;
+  }
+  keys_out = batch_ptr(keys_out, bstride), vals_out = batch_ptr(vals_out, bstride);
+  ghist = batch_ptr(ghist, bstride), scal = batch_ptr(scal, bstride), payload_bad = batch_ptr(payload_bad, bstride);
   // kIndexed: the 32-bit payload that travels with a key is its index — or, when every target is
   // exactly a float32 and there are no weights (payload_bad given and 0), the target value itself,
   // which spares the final sweep a random gather by index
@@ -939,7 +948,8 @@ int run_passes(const RankPlan& p, void* scratch, const uint32_t* k_in0, uint32_t
 template <int MODE, typename TargetT, bool LEAF = false>
 int launch_ingest(const float* score, const void* target, const uint32_t* raw, const RankPlan& p,
                   uint32_t* keys_out, uint32_t* vals_out, void* scratch, int sms, cudaStream_t st,
-                  const uint32_t* payload_bad = nullptr, const double* weight = nullptr) {
+                  const uint32_t* payload_bad = nullptr, const double* weight = nullptr, int nb = 1,
+                  size_t bstride = 0, size_t in_stride = 0) {
   auto kern = rank_ingest_kernel<MODE, TargetT, LEAF>;
   TE_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)kIngestSmem));
@@ -948,12 +958,13 @@ int launch_ingest(const float* score, const void* target, const uint32_t* raw, c
   if (grid > (uint32_t)sms) grid = sms;
   if (grid < 1) grid = 1;
   uintptr_t a = (uintptr_t)score | (uintptr_t)target | (uintptr_t)raw;
-  const bool vec_ok = (a & 15) == 0;
+  const bool vec_ok = (a & 15) == 0 && in_stride % 16 == 0;  // (every task's rows stay 16-byte aligned)
   TE_PROF(MODE == kPacked ? (LEAF ? "rank_ingest_packed2" : "rank_ingest_packed")
                           : (MODE == kIndexed ? "rank_ingest_indexed" : "rank_hist_keys"), st);
-  kern<<<grid, kIngestBlock, kIngestSmem, st>>>(score, (const TargetT*)target, raw, p.n, vec_ok,
-                                                 keys_out, vals_out, at<uint32_t>(scratch, p.off_hist),
-                                                 at<RankScalars>(scratch, p.off_scal), payload_bad, weight);
+  kern<<<dim3(grid, nb), kIngestBlock, kIngestSmem, st>>>(score, (const TargetT*)target, raw, p.n, vec_ok,
+                                                           keys_out, vals_out, at<uint32_t>(scratch, p.off_hist),
+                                                           at<RankScalars>(scratch, p.off_scal), payload_bad, weight,
+                                                           bstride, in_stride);
   TE_LAUNCH_CHECK();
   return TE_OK;
 }
@@ -1480,8 +1491,11 @@ __device__ __forceinline__ void gen_terms_payload(uint32_t val, int mode, double
 template <typename TargetT>
 __global__ void __launch_bounds__(256)
     rank_totals_kernel(const TargetT* __restrict__ target, const double* __restrict__ weight,
-                       uint32_t n, int mode, GenScalars* gs) {
+                       uint32_t n, int mode, GenScalars* gs, size_t bstride = 0, size_t in_stride = 0) {
   __shared__ double ws[8];
+  target += (size_t)blockIdx.y * in_stride;
+  if (weight) weight += (size_t)blockIdx.y * in_stride;
+  gs = batch_ptr(gs, bstride);
   double a = 0.0, b = 0.0;
   uint32_t inexact = 0u;
   for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
@@ -1513,8 +1527,10 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(1024)
     rank_reduce_general_kernel(const double* __restrict__ partial, uint32_t ntiles, int mode,
                                const GenRec* __restrict__ inc, const GenScalars* __restrict__ gs,
-                               double* out) {
+                               double* out, size_t bstride = 0) {
   __shared__ double s_d[32];
+  partial = batch_ptr(partial, bstride), inc = batch_ptr(inc, bstride), gs = batch_ptr(gs, bstride);
+  out += (size_t)blockIdx.y * 8;
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   double ad = 0.0;
   const uint32_t per = (ntiles + 1023) / 1024;
@@ -1607,7 +1623,11 @@ __global__ void __launch_bounds__(kGcBlock)
     gen_chunk_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
                      const TargetT* __restrict__ target, const double* __restrict__ weight, uint32_t n,
                      uint32_t steps_per_chunk, uint32_t nchunks, const GenScalars* __restrict__ gs,
-                     GenChunkRec* rec) {
+                     GenChunkRec* rec, size_t bstride = 0, size_t in_stride = 0) {
+  keys = batch_ptr(keys, bstride), vals = batch_ptr(vals, bstride);
+  gs = batch_ptr(gs, bstride), rec = batch_ptr(rec, bstride);
+  target += (size_t)blockIdx.y * in_stride;
+  if (weight) weight += (size_t)blockIdx.y * in_stride;
   const unsigned lane = threadIdx.x & 31;
   const uint32_t chunk = blockIdx.x * (kGcBlock / kWarp) + (threadIdx.x >> 5);
   if (chunk >= nchunks) return;
@@ -1703,7 +1723,8 @@ __global__ void __launch_bounds__(kGcBlock)
 // rank_reduce_general_kernel looks for them).
 __global__ void __launch_bounds__(1024)
     gen_chunk_scan_kernel(GenChunkRec* rec, uint32_t nchunks, double* partial, GenRec* inc,
-                          int write_excl) {
+                          int write_excl, size_t bstride = 0) {
+  rec = batch_ptr(rec, bstride), partial = batch_ptr(partial, bstride), inc = batch_ptr(inc, bstride);
   __shared__ GState s_warp[32];
   __shared__ double s_sum[32];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -1856,13 +1877,22 @@ GenPlan make_gen_plan(int64_t n) {
   return g;
 }
 
+// nb > 1: nb independent tasks in the same launches (grid.y = task): task y reads its inputs
+// y * in_stride elements further on, works in the scratch slice y * bstride bytes further on and
+// writes out[8 y ..] — WindowedBinaryAUROC.compute and (tasks, n) inputs with weights
+// (window/auroc.py:176-185) are one launch train instead of a Python loop over tasks.
 template <typename TargetT>
 int binary_rank_general_t(const float* score, const TargetT* target, const double* weight, int64_t n,
                           int mode, double* out, void* scratch, const GenPlan& g, int sms,
-                          cudaStream_t st) {
+                          cudaStream_t st, int nb = 1, size_t bstride = 0, size_t in_stride = 0) {
   const RankPlan& p = g.base;
-  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
-  TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, g.off_gzero), 0, g.gzero_bytes, st));
+  if (nb == 1) {
+    TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, p.off_zero), 0, p.zero_bytes, st));
+    TE_CUDA_TRY(cudaMemsetAsync(at<char>(scratch, g.off_gzero), 0, g.gzero_bytes, st));
+  } else {  // the same two regions of every task's slice
+    TE_CUDA_TRY(cudaMemset2DAsync(at<char>(scratch, p.off_zero), bstride, 0, p.zero_bytes, nb, st));
+    TE_CUDA_TRY(cudaMemset2DAsync(at<char>(scratch, g.off_gzero), bstride, 0, g.gzero_bytes, nb, st));
+  }
   uint32_t* ka = at<uint32_t>(scratch, p.off_keys_a);
   uint32_t* kb = at<uint32_t>(scratch, p.off_keys_b);
   uint32_t* va = at<uint32_t>(scratch, p.off_vals_a);
@@ -1876,12 +1906,13 @@ int binary_rank_general_t(const float* score, const TargetT* target, const doubl
     {  // totals first: it also decides whether the target values can ride along as the payload
       TE_PROF("rank_totals", st);
       const uint32_t grid = (uint32_t)min((int64_t)sms * 8, (n + 255) / 256);
-      rank_totals_kernel<TargetT><<<grid, 256, 0, st>>>(target, weight, p.n, mode, gs);
+      rank_totals_kernel<TargetT><<<dim3(grid, nb), 256, 0, st>>>(target, weight, p.n, mode, gs, bstride, in_stride);
     }
     TE_LAUNCH_CHECK();
-    int rc = launch_ingest<kIndexed, TargetT>(score, target, nullptr, p, ka, va, scratch, sms, st, &gs->payload_bad, weight);
+    int rc = launch_ingest<kIndexed, TargetT>(score, target, nullptr, p, ka, va, scratch, sms, st, &gs->payload_bad,
+                                              weight, nb, bstride, in_stride);
     if (rc) return rc;
-    rc = run_passes(p, scratch, ka, kb, ka, va, vb, va, st);  // sorted pairs end in (ka, va)
+    rc = run_passes(p, scratch, ka, kb, ka, va, vb, va, st, nb, bstride);  // sorted pairs end in (ka, va)
     if (rc) return rc;
     {
       // AUROC is linear in the carried prefix: warp-private chunks + one scan CTA, no look-back.
@@ -1892,15 +1923,16 @@ int binary_rank_general_t(const float* score, const TargetT* target, const doubl
       GenChunkRec* crec = at<GenChunkRec>(scratch, g.off_chunks);
       {
         TE_PROF("gen_chunk_sweep", st);
-        gen_chunk_kernel<TargetT><<<grid, kGcBlock, 0, st>>>(ka, va, target, weight, p.n, cg.steps_per_chunk,
-                                                             cg.nchunks, gs, crec);
+        gen_chunk_kernel<TargetT><<<dim3(grid, nb), kGcBlock, 0, st>>>(ka, va, target, weight, p.n, cg.steps_per_chunk,
+                                                                       cg.nchunks, gs, crec, bstride, in_stride);
       }
       {
         TE_PROF("gen_chunk_scan", st);
-        gen_chunk_scan_kernel<<<1, 1024, 0, st>>>(crec, cg.nchunks, partial, inc, mode == 0 ? 0 : 1);
+        gen_chunk_scan_kernel<<<dim3(1, nb), 1024, 0, st>>>(crec, cg.nchunks, partial, inc, mode == 0 ? 0 : 1, bstride);
       }
       tiles = 1;  // what the reduce below sums over
       if (mode != 0) {
+        if (nb != 1) return TE_ERR_UNSUPPORTED;  // (only the AUROC sweep is batched)
         TE_PROF("gen_chunk_integrate", st);
         gen_chunk_integrate_kernel<TargetT><<<grid, kGcBlock, 0, st>>>(ka, va, target, p.n, cg.steps_per_chunk,
                                                                        cg.nchunks, gs, crec, partial);
@@ -1910,30 +1942,34 @@ int binary_rank_general_t(const float* score, const TargetT* target, const doubl
     TE_LAUNCH_CHECK();
   }
   TE_PROF("rank_reduce_general", st);
-  rank_reduce_general_kernel<<<1, 1024, 0, st>>>(partial, tiles, mode, inc, gs, out);
+  rank_reduce_general_kernel<<<dim3(1, nb), 1024, 0, st>>>(partial, tiles, mode, inc, gs, out, bstride);
   TE_LAUNCH_CHECK();
   return TE_OK;
 }
 
 int binary_rank_general(const float* score, const void* target, int32_t dt, const double* weight,
                         int64_t n, int mode, double* out, void* scratch, size_t scratch_bytes,
-                        cudaStream_t st) {
+                        cudaStream_t st, int64_t tasks = 1, int64_t ld = 0) {
   if (n < 0 || n > 0x7fffffffLL) return TE_ERR_UNSUPPORTED;
+  if (tasks < 1 || tasks > 65535 || (tasks > 1 && (mode != 0 || ld < n))) return TE_ERR_UNSUPPORTED;
   const GenPlan g = make_gen_plan(n);
-  if (!scratch || scratch_bytes < g.total) return TE_ERR_SCRATCH_TOO_SMALL;
+  const size_t bstride = tasks > 1 ? align_up(g.total, 256) : 0;
+  if (!scratch || scratch_bytes < (tasks > 1 ? bstride * (size_t)tasks : g.total)) return TE_ERR_SCRATCH_TOO_SMALL;
   int sms = 0;
   TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  const int nb = (int)tasks;
+  const size_t is = tasks > 1 ? (size_t)ld : 0;
   switch (dt) {
     case TE_DTYPE_I64:
-      return binary_rank_general_t(score, (const long long*)target, weight, n, mode, out, scratch, g, sms, st);
+      return binary_rank_general_t(score, (const long long*)target, weight, n, mode, out, scratch, g, sms, st, nb, bstride, is);
     case TE_DTYPE_I32:
-      return binary_rank_general_t(score, (const int*)target, weight, n, mode, out, scratch, g, sms, st);
+      return binary_rank_general_t(score, (const int*)target, weight, n, mode, out, scratch, g, sms, st, nb, bstride, is);
     case TE_DTYPE_U8:
-      return binary_rank_general_t(score, (const unsigned char*)target, weight, n, mode, out, scratch, g, sms, st);
+      return binary_rank_general_t(score, (const unsigned char*)target, weight, n, mode, out, scratch, g, sms, st, nb, bstride, is);
     case TE_DTYPE_F32:
-      return binary_rank_general_t(score, (const float*)target, weight, n, mode, out, scratch, g, sms, st);
+      return binary_rank_general_t(score, (const float*)target, weight, n, mode, out, scratch, g, sms, st, nb, bstride, is);
     case TE_DTYPE_F64:
-      return binary_rank_general_t(score, (const double*)target, weight, n, mode, out, scratch, g, sms, st);
+      return binary_rank_general_t(score, (const double*)target, weight, n, mode, out, scratch, g, sms, st, nb, bstride, is);
     default:
       return TE_ERR_INVALID_ARGUMENT;
   }
@@ -2399,6 +2435,21 @@ extern "C" int te_dense_rank(const void* x, int32_t dtype, int64_t n, uint32_t* 
 extern "C" size_t te_binary_rank_general_scratch_bytes(int64_t n) {
   if (n < 0 || n > 0x7fffffffLL) return 0;
   return make_gen_plan(n).total;
+}
+
+extern "C" size_t te_binary_auroc_general_batched_scratch_bytes(int64_t tasks, int64_t n) {
+  if (n < 0 || n > 0x7fffffffLL || tasks < 1 || tasks > 65535) return 0;
+  return align_up(make_gen_plan(n).total, 256) * (size_t)tasks;
+}
+
+extern "C" int te_binary_auroc_general_batched(const float* score, const void* target, int32_t target_dtype,
+                                               const double* weight, int64_t tasks, int64_t n, int64_t ld,
+                                               double* out, void* scratch, size_t scratch_bytes, void* stream) {
+  if (!out || (n > 0 && (!score || !target))) return TE_ERR_INVALID_ARGUMENT;
+  if (tasks == 1)
+    return binary_rank_general(score, target, target_dtype, weight, n, 0, out, scratch, scratch_bytes, (cudaStream_t)stream);
+  return binary_rank_general(score, target, target_dtype, weight, n, 0, out, scratch, scratch_bytes,
+                             (cudaStream_t)stream, tasks, ld);
 }
 
 extern "C" int te_binary_auroc_general(const float* score, const void* target, int32_t target_dtype,

@@ -212,6 +212,7 @@ __global__ void __launch_bounds__(kSortBlock, (kSortIpt <= 12 ? 1536 : 1024) / k
     if ((uint64_t)blockIdx.x * (kSortBlock * kSortIpt) >= n) return;
   }
   const uint32_t* __restrict__ skip_flag = batch_ptr(skip_flag_, bstride);
+  if (HAS_VAL) vals_in = batch_ptr(vals_in, bstride), vals_out = batch_ptr(vals_out, bstride);
   const KeyT* __restrict__ keys_in = batch_ptr(keys_in_, bstride);
   KeyT* __restrict__ keys_out = batch_ptr(keys_out_, bstride);
   const uint32_t* __restrict__ digit_base = batch_ptr(digit_base_, bstride);

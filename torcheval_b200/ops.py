@@ -286,6 +286,36 @@ def binary_auroc_general(score: torch.Tensor, target: torch.Tensor, weight: Opti
     return _binary_rank_general(0, score, target, weight)
 
 
+def binary_auroc_general_batched(score: torch.Tensor, target: torch.Tensor, weight: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """(tasks, n) scores / targets / weights -> float64 [tasks, 8], row y as binary_auroc_general of
+    row y; all tasks share every launch."""
+    lib = N.load()
+    dev = _require_cuda(score, target, weight)
+    assert score.dim() == 2 and score.shape == target.shape and score.dtype == torch.float32
+    score, target = score.contiguous(), target.contiguous()
+    if target.dtype not in _DTYPE_CODE:
+        target = target.to(torch.float64)
+    if weight is not None:
+        assert weight.shape == score.shape
+        weight = weight.to(torch.float64).contiguous()
+    tasks, n = score.shape
+    out = torch.empty((tasks, 8), dtype=torch.float64, device=dev)
+    step = 65535
+    with torch.cuda.device(dev):
+        for t0 in range(0, tasks, step):
+            k = min(step, tasks - t0)
+            scratch = _scratch(lib.te_binary_auroc_general_batched_scratch_bytes(k, n), dev)
+            N.check(
+                "te_binary_auroc_general_batched",
+                lib.te_binary_auroc_general_batched(
+                    score[t0:].data_ptr(), target[t0:].data_ptr(), _DTYPE_CODE[target.dtype],
+                    None if weight is None else weight[t0:].data_ptr(), k, n, n, out[t0:].data_ptr(),
+                    scratch.data_ptr(), scratch.numel(), _stream_ptr(dev),
+                ),
+            )
+    return out
+
+
 def binary_auprc_general(score: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
     return _binary_rank_general(1, score, target, None)
 
