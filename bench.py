@@ -625,8 +625,10 @@ def one_vs_rest_bench(args, device, peak_gbs, peak_src) -> dict:
     counts_ok = bool(((out[:, 1] + out[:, 2]) == n).all().item()) and bool((out[:, 4] == 0).all().item())
     macro = float(out[:, 0].mean().item())
     assert counts_ok and abs(macro - 0.5) < 1e-3, (counts_ok, macro)
-    # ingest reads N*C*4 and writes N*C*4 packed keys, P = 4 passes of 8 B, 4 B sweep
-    bytes_step = float(n) * C * (8 + 4 * 8 + 4)
+    # ingest reads N*C*4 and writes N*C*4 packed keys; then either P = 4 passes
+    # of 8 B + 4 B sweep, or (counting-stage path, long columns) 4 B upsweep + 2 passes of 8 B + 4 B counting
+    counting = "leaf_count" in kernels
+    bytes_step = float(n) * C * ((8 + 4 + 2 * 8 + 4) if counting else (8 + 4 * 8 + 4))
     gbs = bytes_step / (ms * 1e-3) / 1e9
     dom = max(kernels, key=lambda k: kernels[k]["total_ms"]) if kernels else None
     return {
@@ -637,7 +639,8 @@ def one_vs_rest_bench(args, device, peak_gbs, peak_src) -> dict:
         "config": {"workload": f"MulticlassAUROC one-vs-rest, C={C}, N=2^{OVR_LOG2_N} samples, float32 (N, C) scores resident, 1 GPU",
                    "macro_auroc": macro},
         "roofline": {
-            "kernel": "whole step (ovr_ingest + 4 radix passes + sweep, 8 classes per launch)",
+            "kernel": ("whole step (ovr_ingest + upsweep + 2 cursor passes + counting stage, 8 classes per launch)" if counting
+                       else "whole step (ovr_ingest + 4 radix passes + sweep, 8 classes per launch)"),
             "bound": "hbm",
             "achieved": round(gbs, 1),
             "peak": peak_gbs,

@@ -813,8 +813,35 @@ def test_ovr_rank_vs_oracle(ops, n, C):
     x2 = x.copy()
     x2[:, 0] -= 2.0
     a3 = ops.ovr_rank(dev(x2), dev(y), False, 0).cpu().numpy()
-    assert a3[0, 4] == 2 and (a3[1:, 4] == 0).all()
+    assert (int(a3[0, 4]) & 2) and (a3[1:, 4] == 0).all()  # (the counting-stage path also reports |score| >= 2)
     np.testing.assert_array_equal(a3[1:, 0], a[1:, 0])
+
+
+def test_ovr_counting_path_equals_sort_path(ops):
+    """te_ovr_rank has two structures for AUROC (four-pass sort; counting-stage path with the classes
+    of a batch in grid.y, taken from TE_B200_OVR_LEAF_MIN_N samples on): same integers from both.
+    The switch is read once per process, so the comparison runs in a child process."""
+    import os
+    import subprocess
+    import sys
+
+    code = (
+        "import numpy as np, torch, sys; sys.path.insert(0, %r)\n"
+        "from torcheval_b200 import ops\n"
+        "g = torch.Generator(device='cuda').manual_seed(3)\n"
+        "for n, C in ((70001, 19), (1 << 19, 9)):\n"
+        "    x = torch.rand((n, C), device='cuda', generator=g); x[:, 1] = torch.round(x[:, 1] * 50) / 50\n"
+        "    y = torch.randint(0, C, (n,), device='cuda', generator=g)\n"
+        "    o = ops.ovr_rank(x, y, False, 0).cpu().numpy()\n"
+        "    print(n, C, ' '.join(f'{int(v)}' for v in np.concatenate([o[:, 1], o[:, 2], o[:, 3], o[:, 4]])))\n"
+    ) % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for min_n in ("1", "99999999999"):
+        env = dict(os.environ, TE_B200_OVR_LEAF_MIN_N=min_n)
+        r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(r.stdout)
+    assert outs[0] == outs[1] and len(outs[0].splitlines()) == 2
 
 
 def test_ovr_config5_classes_closed_form(ops):

@@ -1,33 +1,35 @@
-"""One-vs-rest multiclass AUROC / multilabel AUPRC throughput (K2) on one GPU."""
+"""One-vs-rest AUROC (te_ovr_rank) at C classes x 2^k samples, counting-stage path against the
+four-pass sort (TE_B200_OVR_LEAF_MIN_N decides), per-kernel times, and equality of the two."""
+import os
 import sys
-import time
 from pathlib import Path
 
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import torch
 
-sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+sys.path.insert(0, str(Path(__file__).resolve().parent))
+from bench import KernelProfile  # noqa: E402
 from torcheval_b200 import ops  # noqa: E402
 
-
-def main():
-    dev = torch.device("cuda", 0)
-    g = torch.Generator(device=dev).manual_seed(5)
-    for log2n, C in [(20, 1000), (22, 1000), (24, 64), (18, 1000)]:
-        n = 1 << log2n
-        x = torch.rand((n, C), device=dev, generator=g)
-        y = torch.randint(0, C, (n,), device=dev, generator=g)
-        for mode, name in [(0, "multiclass_auroc"), (1, "multiclass_auprc")]:
-            ops.ovr_rank(x, y, False, mode)
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            reps = 2
-            for _ in range(reps):
-                out = ops.ovr_rank(x, y, False, mode)
-            torch.cuda.synchronize()
-            dt = (time.perf_counter() - t0) / reps
-            print(f"N=2^{log2n} C={C:5d} {name:18s} {dt * 1e3:9.2f} ms  {n * C / dt / 1e9:7.2f} G scores/s  mean={float(out[:, 0].mean()):.5f}", flush=True)
-        del x, y
-
-
-if __name__ == "__main__":
-    main()
+C = int(sys.argv[1]) if len(sys.argv) > 1 else 64
+ks = [int(a) for a in sys.argv[2:]] or [20, 22, 24]
+for k in ks:
+    n = 1 << k
+    g = torch.Generator(device="cuda").manual_seed(k)
+    x = torch.rand((n, C), device="cuda", generator=g)
+    y = torch.randint(0, C, (n,), device="cuda", generator=g)
+    out = ops.ovr_rank(x, y, False, 0)
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with KernelProfile() as prof:
+        ev0.record()
+        for _ in range(3):
+            out = ops.ovr_rank(x, y, False, 0)
+        ev1.record()
+        torch.cuda.synchronize()
+        kern = prof.read()
+    ms = ev0.elapsed_time(ev1) / 3
+    o = out.cpu().numpy()
+    print(f"C={C} n=2^{k} LEAF_MIN_N={os.environ.get('TE_B200_OVR_LEAF_MIN_N', 'default')}: {ms:.3f} ms  {n * C / ms / 1e6:.1f} G scores/s  "
+          f"mean={o[:, 0].mean():.9f} sum2U={o[:, 3].sum():.0f} flags={o[:, 4].max()}")
+    print("   ", {kk: round(v["total_ms"] / 3, 3) for kk, v in kern.items()})

@@ -1033,7 +1033,9 @@ int finish_packed(const RankPlan& p, const uint32_t* ka, int mode, double* out, 
 // Counting stage over keys ordered by their top 16 bits (rank_leaf.cuh): segment bounds -> work
 // list -> histogram pieces -> merge of the segments counted in several pieces -> combine.
 int finish_leaf(const RankPlan& p, const uint32_t* keys, double* out, void* scratch, int sms, cudaStream_t st,
-                const uint32_t* n_dev = nullptr, bool have_seg_start = false) {
+                const uint32_t* n_dev = nullptr, bool have_seg_start = false, int nb = 1, size_t bstride = 0) {
+  // nb > 1: nb independent problems in the same launches (grid.y), scratch slices bstride bytes apart,
+  // out rows 8 doubles apart (needs have_seg_start: the batched callers come from the MSD passes)
   uint32_t* seg_start = at<uint32_t>(scratch, p.off_seg_start);
   LeafItem* items = at<LeafItem>(scratch, p.off_leaf_items);
   LeafMulti* multi = at<LeafMulti>(scratch, p.off_leaf_multi);
@@ -1046,25 +1048,27 @@ int finish_leaf(const RankPlan& p, const uint32_t* keys, double* out, void* scra
   }
   {
     TE_PROF("leaf_tiny", st);
-    leaf_tiny_kernel<<<kLeafSegs / 8, 256, 0, st>>>(keys, seg_start, stats);
+    leaf_tiny_kernel<<<dim3(kLeafSegs / 8, nb), 256, 0, st>>>(keys, seg_start, stats, bstride);
   }
   {
     TE_PROF("leaf_plan", st);
-    leaf_plan_kernel<<<1, 1024, 0, st>>>(seg_start, p.leaf_piece, p.leaf_max_items, p.leaf_max_slabs, items, multi, hdr);
+    leaf_plan_kernel<<<dim3(1, nb), 1024, 0, st>>>(seg_start, p.leaf_piece, p.leaf_max_items, p.leaf_max_slabs, items, multi,
+                                                   hdr, bstride);
   }
   TE_LAUNCH_CHECK();
   TE_CUDA_TRY(cudaFuncSetAttribute(leaf_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLeafSmem));
   {
     TE_PROF("leaf_count", st);
-    leaf_count_kernel<<<sms, kLeafBlock, kLeafSmem, st>>>(keys, items, hdr, stats, slabs);
+    leaf_count_kernel<<<dim3(sms, nb), kLeafBlock, kLeafSmem, st>>>(keys, items, hdr, stats, slabs, bstride);
   }
   {
     TE_PROF("leaf_merge", st);
-    leaf_merge_kernel<<<sms, kLeafBlock, 0, st>>>(multi, hdr, slabs, stats);
+    leaf_merge_kernel<<<dim3(sms, nb), kLeafBlock, 0, st>>>(multi, hdr, slabs, stats, bstride);
   }
   {
     TE_PROF("leaf_combine", st);
-    leaf_combine_kernel<<<1, 1024, 0, st>>>(stats, p.n, &at<RankScalars>(scratch, p.off_scal)->flags, out, n_dev);
+    leaf_combine_kernel<<<dim3(1, nb), 1024, 0, st>>>(stats, p.n, &at<RankScalars>(scratch, p.off_scal)->flags, out, n_dev,
+                                                      bstride);
   }
   TE_LAUNCH_CHECK();
   return TE_OK;
@@ -1240,19 +1244,22 @@ int leaf_passes_ranges(const RankPlan& p, void* scratch, const float* score, con
 template <typename TargetT>
 int leaf_passes_msd_geom(const RankPlan& p, void* scratch, const float* score, const TargetT* target,
                          const uint32_t* raw_keys, uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st,
-                         const SlabView view, const uint32_t* n_dev);
+                         const SlabView view, const uint32_t* n_dev, int nb, size_t bstride);
 
+// nb > 1 (raw_keys only): nb key arrays of p.n records each in the same launches (grid.y), every
+// scratch-resident pointer bstride bytes apart — the classes of a one-vs-rest batch.
 template <typename TargetT>
 int leaf_passes_msd(const RankPlan& p, void* scratch, const float* score, const TargetT* target,
                     const uint32_t* raw_keys, uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st,
-                    const SlabView view = SlabView{nullptr, 0, 0, 0}, const uint32_t* n_dev = nullptr) {
-  return leaf_passes_msd_geom<TargetT>(p, scratch, score, target, raw_keys, ka, kb, sms, st, view, n_dev);
+                    const SlabView view = SlabView{nullptr, 0, 0, 0}, const uint32_t* n_dev = nullptr, int nb = 1,
+                    size_t bstride = 0) {
+  return leaf_passes_msd_geom<TargetT>(p, scratch, score, target, raw_keys, ka, kb, sms, st, view, n_dev, nb, bstride);
 }
 
 template <typename TargetT, int PBLOCK, int PIPT>
 int leaf_passes_msd_impl(const RankPlan& p, void* scratch, const float* score, const TargetT* target,
                     const uint32_t* raw_keys, uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st,
-                    const SlabView view, const uint32_t* n_dev) {
+                    const SlabView view, const uint32_t* n_dev, int nb = 1, size_t bstride = 0) {
   constexpr int TILE = PBLOCK * PIPT;
   constexpr int kCtasPerSm = 1024 / PBLOCK;
   const size_t part_smem = (size_t)2 * TILE * sizeof(uint32_t);
@@ -1269,19 +1276,19 @@ int leaf_passes_msd_impl(const RankPlan& p, void* scratch, const float* score, c
     auto up = rank_upsweep_joint_kernel<long long, true>;
     TE_CUDA_TRY(cudaFuncSetAttribute(up, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUjSmem));
     TE_PROF("rank_upsweep_joint_keys", st);
-    up<<<ugrid, kUjBlock, kUjSmem, st>>>(reinterpret_cast<const float*>(raw_keys), nullptr, p.n,
-                                         ((uintptr_t)raw_keys & 15) == 0, nullptr, joint, flags, view);
+    up<<<dim3(ugrid, nb), kUjBlock, kUjSmem, st>>>(reinterpret_cast<const float*>(raw_keys), nullptr, p.n,
+                                                   ((uintptr_t)raw_keys & 15) == 0, nullptr, joint, flags, view, bstride);
   } else {
     auto up = rank_upsweep_joint_kernel<TargetT, false>;
     TE_CUDA_TRY(cudaFuncSetAttribute(up, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUjSmem));
     TE_PROF("rank_upsweep_joint", st);
     up<<<ugrid, kUjBlock, kUjSmem, st>>>(score, target, p.n, (((uintptr_t)score | (uintptr_t)target) & 15) == 0,
-                                         label_bits, joint, flags, SlabView{nullptr, 0, 0, 0});
+                                         label_bits, joint, flags, SlabView{nullptr, 0, 0, 0}, (size_t)0);
   }
   TE_LAUNCH_CHECK();
   {
     TE_PROF("joint_scan", st);
-    joint_scan_kernel<TILE><<<1, 1024, 0, st>>>(joint, seg_start, cursor1, cursor2, tables);
+    joint_scan_kernel<TILE><<<dim3(1, nb), 1024, 0, st>>>(joint, seg_start, cursor1, cursor2, tables, bstride);
   }
   TE_LAUNCH_CHECK();
   // both instantiations of a pass are launched; the device-side tables decide which one works
@@ -1297,8 +1304,8 @@ int leaf_passes_msd_impl(const RankPlan& p, void* scratch, const float* score, c
     TE_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)part_smem));
     TE_PROF(name, st);
     // (pass 1 reads through the view and needs no count; pass 2 and later take it from n_dev)
-    kern<<<grid, PBLOCK, part_smem, st>>>(in, bits, outp, p.n, segs ? n_dev : nullptr, segs, tables, cursors,
-                                            segs ? SlabView{nullptr, 0, 0, 0} : view);
+    kern<<<dim3(grid, nb), PBLOCK, part_smem, st>>>(in, bits, outp, p.n, segs ? n_dev : nullptr, segs, tables, cursors,
+                                                      segs ? SlabView{nullptr, 0, 0, 0} : view, bstride);
     TE_LAUNCH_CHECK();
     return TE_OK;
   };
@@ -1318,13 +1325,13 @@ int leaf_passes_msd_impl(const RankPlan& p, void* scratch, const float* score, c
 template <typename TargetT>
 int leaf_passes_msd_geom(const RankPlan& p, void* scratch, const float* score, const TargetT* target,
                          const uint32_t* raw_keys, uint32_t* ka, uint32_t* kb, int sms, cudaStream_t st,
-                         const SlabView view, const uint32_t* n_dev) {
+                         const SlabView view, const uint32_t* n_dev, int nb, size_t bstride) {
   static const int geom = [] {
     const char* e = getenv("TE_B200_PART_GEOM");
     return e ? atoi(e) : 0;
   }();
-  if (geom == 1) return leaf_passes_msd_impl<TargetT, 512, 24>(p, scratch, score, target, raw_keys, ka, kb, sms, st, view, n_dev);
-  return leaf_passes_msd_impl<TargetT, kPrBlock, kPrIpt>(p, scratch, score, target, raw_keys, ka, kb, sms, st, view, n_dev);
+  if (geom == 1) return leaf_passes_msd_impl<TargetT, 512, 24>(p, scratch, score, target, raw_keys, ka, kb, sms, st, view, n_dev, nb, bstride);
+  return leaf_passes_msd_impl<TargetT, kPrBlock, kPrIpt>(p, scratch, score, target, raw_keys, ka, kb, sms, st, view, n_dev, nb, bstride);
 }
 
 int leaf_passes_msd_dtype(const RankPlan& p, void* scratch, const float* score, const void* target, int32_t dt,
@@ -2184,14 +2191,18 @@ __global__ void copy_counts_kernel(const uint32_t* __restrict__ hist, long long*
 constexpr int kOvrBatch = 8;
 constexpr int kOvrBlock = 512;
 
-template <bool MULTILABEL>
+// HIST: the four digit histograms of the LSD passes; the counting-stage path builds its own joint
+// histogram from the keys (rank_upsweep_joint_kernel) and skips them — four shared atomics per key
+// are what bounds this kernel otherwise.
+template <bool MULTILABEL, bool HIST = true>
 __global__ void __launch_bounds__(kOvrBlock)
     ovr_ingest_kernel(const float* __restrict__ input, int64_t ld, const long long* __restrict__ target,
                       int64_t ld_t, uint32_t n, int c0, int nb, bool vec_ok, char* scratch0,
                       size_t plan_stride, size_t off_keys, size_t off_hist, size_t off_scal) {
   extern __shared__ uint32_t sh[];  // [nb][4][256]
   const unsigned tid = threadIdx.x, lane = tid & 31;
-  for (int i = tid; i < kOvrBatch * 4 * kRadix; i += kOvrBlock) sh[i] = 0;
+  if (HIST)
+    for (int i = tid; i < kOvrBatch * 4 * kRadix; i += kOvrBlock) sh[i] = 0;
   __syncthreads();
   uint32_t npos[kOvrBatch];
   uint32_t negmask = 0, badmask = 0;
@@ -2226,14 +2237,16 @@ __global__ void __launch_bounds__(kOvrBlock)
         const uint32_t k = (bits << 1) | lab;
         npos[j] += lab;
         reinterpret_cast<uint32_t*>(scratch0 + (size_t)j * plan_stride + off_keys)[i] = k;
-        uint32_t* h = sh + j * 4 * kRadix;
+        if (HIST) {
+          uint32_t* h = sh + j * 4 * kRadix;
 #pragma unroll
-        for (int p = 0; p < 4; ++p) atomicAdd(h + p * kRadix + ((k >> (8 * p)) & 0xffu), 1u);
+          for (int p = 0; p < 4; ++p) atomicAdd(h + p * kRadix + ((k >> (8 * p)) & 0xffu), 1u);
+        }
       }
     }
   }
   __syncthreads();
-  for (int i = tid; i < nb * 4 * kRadix; i += kOvrBlock) {
+  for (int i = tid; HIST && i < nb * 4 * kRadix; i += kOvrBlock) {
     const uint32_t v = sh[i];
     if (v) {
       const int j = i / (4 * kRadix);
@@ -2831,7 +2844,9 @@ extern "C" int te_debug_phase_stats(uint64_t* out8, int reset) {
 
 extern "C" size_t te_ovr_rank_scratch_bytes(int64_t n) {
   if (n < 0 || n > 0x7fffffffLL) return 0;
-  return align_up(make_plan(n, false, true, true).total, 256) * kOvrBatch;
+  const size_t a = align_up(make_plan(n, false, true, true).total, 256);
+  const size_t b = align_up(make_plan(n, false, true, true, true).total, 256);  // counting-stage path
+  return (a > b ? a : b) * kOvrBatch;
 }
 
 extern "C" int te_ovr_rank(const float* input, int64_t ld, const int64_t* target, int64_t target_ld,
@@ -2841,12 +2856,51 @@ extern "C" int te_ovr_rank(const float* input, int64_t ld, const int64_t* target
   if (num_classes < 1 || !out || (mode != 0 && mode != 1) || ld < num_classes) return TE_ERR_INVALID_ARGUMENT;
   if (n > 0 && (!input || !target)) return TE_ERR_INVALID_ARGUMENT;
   if (multilabel && target_ld < num_classes) return TE_ERR_INVALID_ARGUMENT;
-  const RankPlan p = make_plan(n, false, true, true);
-  const size_t stride = align_up(p.total, 256);
-  if (!scratch || scratch_bytes < stride * kOvrBatch) return TE_ERR_SCRATCH_TOO_SMALL;
   cudaStream_t st = (cudaStream_t)stream;
   int sms = 0;
   TE_CUDA_TRY((cudaError_t)sm_count_of_current_device(&sms));
+  // AUROC of long columns: the counting-stage path of the binary metric, the classes of a batch in
+  // the same launches (grid.y).  Its fixed work per class (65 536 segments to plan and walk) pays
+  // off from TE_B200_OVR_LEAF_MIN_N samples on.
+  static const int64_t ovr_leaf_min_n = [] {
+    const char* e = getenv("TE_B200_OVR_LEAF_MIN_N");
+    return e ? atoll(e) : (int64_t)1 << 25;  // 2^24: 22.6 vs 21.5 ms, 2^25: 8.1 vs 9.8, 2^26: 13.5 vs 19.4 (profiles/r02_ovr_bench.txt)
+  }();
+  if (mode == 0 && n >= ovr_leaf_min_n && (((uintptr_t)scratch) & 255) == 0) {
+    const RankPlan p = make_plan(n, false, true, true, true);
+    const size_t stride = align_up(p.total, 256);
+    if (!scratch || scratch_bytes < stride * kOvrBatch) return TE_ERR_SCRATCH_TOO_SMALL;
+    char* base = static_cast<char*>(scratch);
+    for (int c0 = 0; c0 < num_classes; c0 += kOvrBatch) {
+      const int nb = num_classes - c0 < kOvrBatch ? num_classes - c0 : kOvrBatch;
+      TE_CUDA_TRY(cudaMemset2DAsync(base + p.off_zero, stride, 0, p.zero_bytes, nb, st));
+      const bool vec_ok = (((uintptr_t)input) & 15) == 0 && (ld % 4) == 0 && (c0 % 4) == 0;
+      int64_t want = (n + kOvrBlock - 1) / kOvrBlock;
+      const int grid = (int)(want < (int64_t)sms * 4 ? want : (int64_t)sms * 4);
+      {
+        TE_PROF("ovr_ingest_keys", st);  // packed keys of class c0 + j -> keys_b of slice j
+        if (multilabel)
+          ovr_ingest_kernel<true, false><<<grid, kOvrBlock, 0, st>>>(input, ld, (const long long*)target, target_ld, p.n, c0, nb,
+                                                                     vec_ok, base, stride, p.off_keys_b, p.off_hist, p.off_scal);
+        else
+          ovr_ingest_kernel<false, false><<<grid, kOvrBlock, 0, st>>>(input, ld, (const long long*)target, target_ld, p.n, c0, nb,
+                                                                      vec_ok, base, stride, p.off_keys_b, p.off_hist, p.off_scal);
+      }
+      TE_LAUNCH_CHECK();
+      uint32_t* ka = at<uint32_t>(base, p.off_keys_a);
+      uint32_t* kb = at<uint32_t>(base, p.off_keys_b);
+      // raw keys in kb -> ka -> kb (grouped by their top 16 bits), then the counting stage
+      int rc = leaf_passes_msd<long long>(p, base, nullptr, nullptr, kb, ka, kb, sms, st, SlabView{nullptr, 0, 0, 0}, nullptr,
+                                          nb, stride);
+      if (rc) return rc;
+      rc = finish_leaf(p, kb, out + (size_t)c0 * 8, base, sms, st, nullptr, true, nb, stride);
+      if (rc) return rc;
+    }
+    return TE_OK;
+  }
+  const RankPlan p = make_plan(n, false, true, true);
+  const size_t stride = align_up(p.total, 256);
+  if (!scratch || scratch_bytes < stride * kOvrBatch) return TE_ERR_SCRATCH_TOO_SMALL;
   const size_t smem = (size_t)kOvrBatch * 4 * kRadix * sizeof(uint32_t);
   char* base = static_cast<char*>(scratch);
   for (int c0 = 0; c0 < num_classes; c0 += kOvrBatch) {

@@ -24,6 +24,7 @@
 // the top binades).
 #pragma once
 #include "common.cuh"
+#include "rank_sort.cuh"  // batch_ptr
 
 namespace te {
 
@@ -78,7 +79,9 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(1024)
     leaf_plan_kernel(const uint32_t* __restrict__ seg_start, uint32_t piece, uint32_t max_items,
                      uint32_t max_slabs, LeafItem* __restrict__ items, LeafMulti* __restrict__ multi,
-                     LeafHeader* hdr) {
+                     LeafHeader* hdr, size_t bstride = 0) {
+  seg_start = batch_ptr(seg_start, bstride), items = batch_ptr(items, bstride);
+  multi = batch_ptr(multi, bstride), hdr = batch_ptr(hdr, bstride);
   __shared__ uint32_t ws[3][32];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   constexpr int ROWS = kLeafSegs / 1024;
@@ -158,7 +161,8 @@ __global__ void __launch_bounds__(1024)
 // and own keys that are not positives by 0, and the inner loop is two compares per pair.
 __global__ void __launch_bounds__(256)
     leaf_tiny_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ seg_start,
-                     SegStat* __restrict__ seg_stats) {
+                     SegStat* __restrict__ seg_stats, size_t bstride = 0) {
+  keys = batch_ptr(keys, bstride), seg_start = batch_ptr(seg_start, bstride), seg_stats = batch_ptr(seg_stats, bstride);
   const unsigned lane = threadIdx.x & 31;
   const uint32_t s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (s >= kLeafSegs) return;
@@ -204,6 +208,7 @@ __global__ void __launch_bounds__(256)
 struct LeafWarpTot {
   unsigned long long A, P, N;
 };
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void leaf_walk(const uint4 (&v)[kLeafVecPerThread], LeafWarpTot* s_tot,
                                           SegStat* __restrict__ out) {
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -232,17 +237,24 @@ __device__ __forceinline__ void leaf_walk(const uint4 (&v)[kLeafVecPerThread], L
     s_tot[warp] = t;
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    unsigned long long a = 0, p = 0, nn = 0;
-    for (int w = 0; w < kLeafWarps; ++w) {
-      const LeafWarpTot t = s_tot[w];
-      a += t.A + 2ull * t.P * nn;
-      p += t.P;
-      nn += t.N;
+  if (warp == 0) {  // lane w holds warp w's totals: negatives below it by a warp scan, the rest by warp sums
+    static_assert(kLeafWarps == 32, "one lane per warp");
+    const LeafWarpTot t = s_tot[lane];
+    const uint32_t nw = (uint32_t)t.N;
+    uint32_t incl = nw;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t u = __shfl_up_sync(kFull, incl, o);
+      if (lane >= (unsigned)o) incl += u;
     }
-    SegStat r;
-    r.A = a, r.P = (uint32_t)p, r.N = (uint32_t)nn;
-    *out = r;
+    const unsigned long long a = warp_sum(t.A + 2ull * t.P * (unsigned long long)(incl - nw));
+    const unsigned long long p = warp_sum(t.P);
+    const uint32_t nn = __shfl_sync(kFull, incl, 31);
+    if (lane == 0) {
+      SegStat r;
+      r.A = a, r.P = (uint32_t)p, r.N = nn;
+      *out = r;
+    }
   }
 }
 
@@ -250,30 +262,45 @@ __device__ __forceinline__ void leaf_walk(const uint4 (&v)[kLeafVecPerThread], L
 // pieces from the work list.
 __global__ void __launch_bounds__(kLeafBlock, 1)
     leaf_count_kernel(const uint32_t* __restrict__ keys, const LeafItem* __restrict__ items, LeafHeader* hdr,
-                      SegStat* __restrict__ seg_stats, uint32_t* __restrict__ slabs) {
+                      SegStat* __restrict__ seg_stats, uint32_t* __restrict__ slabs, size_t bstride = 0) {
+  keys = batch_ptr(keys, bstride), items = batch_ptr(items, bstride), hdr = batch_ptr(hdr, bstride);
+  seg_stats = batch_ptr(seg_stats, bstride), slabs = batch_ptr(slabs, bstride);
   extern __shared__ __align__(16) uint32_t s_hist[];
   __shared__ uint32_t s_ticket;
   __shared__ LeafWarpTot s_tot[kLeafWarps];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  __shared__ LeafItem s_item;
+  __shared__ LeafItem s_item, s_next;
+  __shared__ uint32_t s_next_ok;
   const uint32_t n_items = hdr->n_items;
   uint4* s_hist4 = reinterpret_cast<uint4*>(s_hist);
-  // the ticket (a global atomic) and the item it names (a dependent load) for round r + 1 are
-  // fetched by thread 0 while round r is counted: ~2 us that thousands of light pieces would
-  // otherwise each pay on their own
+  // The ticket (a global atomic) and the item it names (a dependent load) are two round trips of
+  // ~0.4 us each, and a light piece is counted in less than that.  Thread 0 therefore runs two rounds
+  // ahead: in round r it draws the ticket of round r + 2 and loads the item of round r + 1, whose
+  // ticket it drew in round r - 1 — neither wait ends up on the path of a round.
+  uint32_t pend = 0;  // (thread 0) the ticket of the round after this one
   if (tid == 0) {
     s_ticket = atomicAdd(&hdr->ticket, 1u);
+    pend = atomicAdd(&hdr->ticket, 1u);
     if (s_ticket < n_items) s_item = items[n_items - 1u - s_ticket];  // highest keys first: the heavy segments
   }
-  for (;;) {
+  // the histogram is cleared once here; every round leaves it cleared behind itself (the walk and the
+  // slab copy write zeros where they have just read: one pass over the 128 KB per piece instead of two)
 #pragma unroll
-    for (int j = 0; j < kLeafVecPerThread; ++j) s_hist4[j * kLeafBlock + tid] = make_uint4(0, 0, 0, 0);
+  for (int j = 0; j < kLeafVecPerThread; ++j) s_hist4[j * kLeafBlock + tid] = make_uint4(0, 0, 0, 0);
+  for (;;) {
     __syncthreads();
     const uint32_t t = s_ticket;
     if (t >= n_items) break;
     const LeafItem it = s_item;
     uint32_t next_ticket = 0;
-    if (tid == 0) next_ticket = atomicAdd(&hdr->ticket, 1u);
+    LeafItem next_item = it;
+    if (tid == 0) {
+      next_ticket = pend;
+      if (next_ticket < n_items) {
+        pend = atomicAdd(&hdr->ticket, 1u);
+        next_item = items[n_items - 1u - next_ticket];
+      }
+    }
     const uint32_t cnt = it.end - it.begin;
     const uint32_t* __restrict__ k = keys + it.begin;
     // scalar head up to the first 16-byte boundary, vector body, scalar tail
@@ -299,28 +326,44 @@ __global__ void __launch_bounds__(kLeafBlock, 1)
     }
     const uint32_t done = head + 4u * nvec;
     if (tid < cnt - done) atomicAdd(&s_hist[k[done + tid] & kLeafMask], 1u);
-    LeafItem next_item = it;
-    if (tid == 0 && next_ticket < n_items) next_item = items[n_items - 1u - next_ticket];
+    if (tid == 0) {
+      s_next = next_item;
+      s_next_ok = next_ticket < n_items ? 1u : 0u;
+    }
     __syncthreads();  // counts complete; everybody has read s_ticket / s_item of this round
     if (tid == 0) s_ticket = next_ticket, s_item = next_item;
+    // the next piece's first lines on their way from DRAM to L2 while this one is walked (a light
+    // piece is all latency: ~1 us of its ~4 is the first load)
+    if (s_next_ok) {
+      const uint32_t nb0 = s_next.begin, ne0 = s_next.end;
+      if (tid < min((ne0 - nb0 + 31u) >> 5, (uint32_t)kLeafBlock)) prefetch_l2(keys + nb0 + 32u * tid);
+    }
     if (it.slab >= 0) {
       uint4* dst = reinterpret_cast<uint4*>(slabs + (size_t)it.slab * kLeafBins);
 #pragma unroll
-      for (int j = 0; j < kLeafVecPerThread; ++j) dst[j * kLeafBlock + tid] = s_hist4[j * kLeafBlock + tid];
+      for (int j = 0; j < kLeafVecPerThread; ++j) {
+        dst[j * kLeafBlock + tid] = s_hist4[j * kLeafBlock + tid];
+        s_hist4[j * kLeafBlock + tid] = make_uint4(0, 0, 0, 0);
+      }
     } else {
       uint4 v[kLeafVecPerThread];
 #pragma unroll
-      for (int j = 0; j < kLeafVecPerThread; ++j) v[j] = s_hist4[(warp * kLeafVecPerThread + j) * 32 + lane];
+      for (int j = 0; j < kLeafVecPerThread; ++j) {
+        v[j] = s_hist4[(warp * kLeafVecPerThread + j) * 32 + lane];
+        s_hist4[(warp * kLeafVecPerThread + j) * 32 + lane] = make_uint4(0, 0, 0, 0);
+      }
       leaf_walk(v, s_tot, seg_stats + it.seg);
     }
-    __syncthreads();  // the histogram is cleared by the next round, which reads the new s_ticket / s_item
+    // (the sync at the top of the loop: the cleared histogram and the new s_ticket / s_item are visible)
   }
 }
 
 // Segments counted in several pieces: one CTA adds up the slabs of one segment and walks the sum.
 __global__ void __launch_bounds__(kLeafBlock)
     leaf_merge_kernel(const LeafMulti* __restrict__ multi, const LeafHeader* __restrict__ hdr,
-                      const uint32_t* __restrict__ slabs, SegStat* __restrict__ seg_stats) {
+                      const uint32_t* __restrict__ slabs, SegStat* __restrict__ seg_stats, size_t bstride = 0) {
+  multi = batch_ptr(multi, bstride), hdr = batch_ptr(hdr, bstride);
+  slabs = batch_ptr(slabs, bstride), seg_stats = batch_ptr(seg_stats, bstride);
   __shared__ LeafWarpTot s_tot[kLeafWarps];
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t n_multi = hdr->n_multi;
@@ -348,7 +391,9 @@ __global__ void __launch_bounds__(kLeafBlock)
 // TE_RANK_FLAG_* bits collected on the way.
 __global__ void __launch_bounds__(1024)
     leaf_combine_kernel(const SegStat* __restrict__ seg_stats, uint32_t n, const uint32_t* __restrict__ flags_in,
-                        double* __restrict__ out, const uint32_t* __restrict__ n_dev = nullptr) {
+                        double* __restrict__ out, const uint32_t* __restrict__ n_dev = nullptr, size_t bstride = 0) {
+  seg_stats = batch_ptr(seg_stats, bstride), flags_in = batch_ptr(flags_in, bstride);
+  out += (size_t)blockIdx.y * 8;  // (batched: one 8-double row per problem)
   if (n_dev) n = *n_dev;
   __shared__ LeafWarpTot s_tot[32];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;

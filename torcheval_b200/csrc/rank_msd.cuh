@@ -35,7 +35,10 @@ template <typename TargetT, bool RAW>
 __global__ void __launch_bounds__(kUjBlock, 1)
     rank_upsweep_joint_kernel(const float* __restrict__ score, const TargetT* __restrict__ target, uint32_t n,
                               bool vec_ok, uint32_t* __restrict__ label_bits, uint32_t* joint, uint32_t* flags,
-                              const SlabView view = SlabView{nullptr, 0, 0, 0}) {
+                              const SlabView view = SlabView{nullptr, 0, 0, 0}, size_t bstride = 0) {
+  // bstride (RAW only): grid.y independent key arrays of n records each, one scratch slice apart
+  if (RAW) score = batch_ptr(score, bstride);
+  joint = batch_ptr(joint, bstride), flags = batch_ptr(flags, bstride);
   extern __shared__ __align__(16) uint32_t s_j[];  // [32768] words = 65536 16-bit counters
   __shared__ uint32_t s_best[2][kUjBlock / kWarp];
   __shared__ uint32_t s_hotseg[2], s_hotsum[2];
@@ -252,7 +255,9 @@ struct MsdTables {
 template <int TILE>
 __global__ void __launch_bounds__(1024)
     joint_scan_kernel(const uint32_t* __restrict__ joint, uint32_t* __restrict__ seg_start, uint32_t* __restrict__ cursor1,
-                      uint32_t* __restrict__ cursor2, MsdTables* __restrict__ tables) {
+                      uint32_t* __restrict__ cursor2, MsdTables* __restrict__ tables, size_t bstride = 0) {
+  joint = batch_ptr(joint, bstride), seg_start = batch_ptr(seg_start, bstride), cursor1 = batch_ptr(cursor1, bstride);
+  cursor2 = batch_ptr(cursor2, bstride), tables = batch_ptr(tables, bstride);
   __shared__ uint32_t ws[32];
   __shared__ uint32_t s_tiles[kRadix], s_size[kRadix], s_hotsum[kRadix];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -345,7 +350,10 @@ __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
     cursor_partition_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ label_bits,
                             uint32_t* __restrict__ keys_out, uint32_t n, const uint32_t* __restrict__ n_dev,
                             const uint32_t* __restrict__ seg_start, const MsdTables* __restrict__ tables,
-                            uint32_t* cursors, const SlabView view = SlabView{nullptr, 0, 0, 0}) {
+                            uint32_t* cursors, const SlabView view = SlabView{nullptr, 0, 0, 0}, size_t bstride = 0) {
+  // bstride: grid.y independent problems of n records each (one-vs-rest classes), one scratch slice apart
+  keys_in = batch_ptr(keys_in, bstride), keys_out = batch_ptr(keys_out, bstride), label_bits = batch_ptr(label_bits, bstride);
+  seg_start = batch_ptr(seg_start, bstride), tables = batch_ptr(tables, bstride), cursors = batch_ptr(cursors, bstride);
   // view (pass 1 only): the input is an inbox of slabs; tiles are tiles of the physical index space
   static_assert(!(BUCKETED && PACK), "only the first pass packs");
   extern __shared__ __align__(16) uint32_t s_buf[];  // [2][TILE]
