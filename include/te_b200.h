@@ -346,6 +346,11 @@ TE_API int64_t te_slab_capacity(int64_t n_max_per_rank, int32_t world);
 TE_API int te_rank_pack_scatter(const float* score, const void* target, int32_t target_dtype, int64_t n,
                                 const uint32_t* splitters_dev, int32_t world, int32_t rank,
                                 const uint64_t* inbox_ptrs_host, int64_t cap, void* work, void* stream);
+/* Measurement only (tools/p2p_store_bench.py): every CTA of `grid` stores 8 KB chunks into the ndst
+ * (<= 16) buffers of words_per_dst uint32 each; mode 0 = 16-byte st.global per lane, mode 1 = one bulk
+ * async copy (shared -> global, no multicast) per chunk.  Nothing is read back. */
+TE_API int te_debug_p2p_store_bench(const uint64_t* dst_ptrs_host, int32_t ndst, int64_t words_per_dst, int32_t mode,
+                                    int32_t grid, void* stream);
 TE_API size_t te_binary_auroc_from_slabs_scratch_bytes(int32_t world, int64_t cap);
 TE_API int te_binary_auroc_from_slabs(const void* inbox, int32_t world, int64_t cap, double* out, void* scratch,
                                       size_t scratch_bytes, void* stream);

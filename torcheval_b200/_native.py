@@ -72,6 +72,7 @@ SIGNATURES = {
     "te_binary_pr_curve_finish": (C.c_int, [_i64, _vp, _vp, _vp, _vp, _sz, _vp]),
     "te_sort_u32_scratch_bytes": (_sz, [_i64, _i32]),
     "te_sort_u32": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _sz, _vp]),
+    "te_debug_p2p_store_bench": (C.c_int, [_vp, _i32, _i64, _i32, _i32, _vp]),
     "te_dense_rank_scratch_bytes": (_sz, [_i64]),
     "te_dense_rank": (C.c_int, [_vp, _i32, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
 }

@@ -3081,6 +3081,17 @@ extern "C" int te_rank_pack_scatter(const float* score, const void* target, int3
   }
 }
 
+// measurement only (tools/p2p_store_bench.py): raw store bandwidth into up to 16 destinations
+extern "C" int te_debug_p2p_store_bench(const uint64_t* dst_ptrs_host, int32_t ndst, int64_t words_per_dst, int32_t mode,
+                                        int32_t grid, void* stream) {
+  if (!dst_ptrs_host || ndst < 1 || ndst > kMaxSplitters + 1 || words_per_dst < 2048 || grid < 1) return TE_ERR_INVALID_ARGUMENT;
+  PeerSlabs ps{};
+  for (int b = 0; b < ndst; ++b) ps.slab[b] = dst_ptrs_host[b];
+  p2p_store_bench_kernel<<<grid, 512, 0, (cudaStream_t)stream>>>(ps, ndst, (uint32_t)words_per_dst, mode);
+  TE_LAUNCH_CHECK();
+  return TE_OK;
+}
+
 extern "C" size_t te_binary_auroc_from_slabs_scratch_bytes(int32_t world, int64_t cap) {
   if (world < 1 || world > kMaxSplitters + 1 || cap <= 0 || (int64_t)world * cap > 0x7fffffffLL) return 0;
   return make_plan((int64_t)world * cap, false, true, true, true).total;

@@ -252,4 +252,35 @@ __global__ void __launch_bounds__(kIrBlock)
   if (__any_sync(kFull, wide != 0) && lane == 0) atomicOr(flags, (uint32_t)TE_RANK_FLAG_WIDE_SCORE);
 }
 
+
+// ---- measurement only: what one GPU can push into its peers' memory -------------------------------
+// Every CTA stores 8 KB chunks of a constant shared-memory buffer, chunk c to destination c % ndst.
+// mode 0: one 16-byte st.global per lane (what pack_scatter_kernel does); mode 1: one bulk async
+// copy shared -> global per chunk, issued by one thread (plain cp.async.bulk store, no multicast).
+__global__ void __launch_bounds__(512, 2)
+    p2p_store_bench_kernel(const PeerSlabs dst, int ndst, uint32_t words_per_dst, int mode) {
+  constexpr uint32_t kChunk = 2048;  // words
+  __shared__ __align__(128) uint32_t s_buf[kChunk];
+  const unsigned tid = threadIdx.x;
+  for (uint32_t i = tid; i < kChunk; i += blockDim.x) s_buf[i] = i;
+  __syncthreads();
+  if (mode == 1 && tid == 0) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  const uint64_t total = (uint64_t)(words_per_dst / kChunk) * (uint64_t)ndst;
+  const uint32_t s_addr = (uint32_t)__cvta_generic_to_shared(s_buf);
+  for (uint64_t c = blockIdx.x; c < total; c += gridDim.x) {
+    const int d = (int)(c % (uint64_t)ndst);
+    uint32_t* p = reinterpret_cast<uint32_t*>(dst.slab[d]) + (size_t)(c / (uint64_t)ndst) * kChunk;
+    if (mode == 0) {
+      const uint4 v = *reinterpret_cast<const uint4*>(&s_buf[tid * 4]);
+      *reinterpret_cast<uint4*>(p + tid * 4) = v;
+    } else if (tid == 0) {
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(p), "r"(s_addr), "r"(kChunk * 4u)
+                   : "memory");
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      asm volatile("cp.async.bulk.wait_group.read 8;" ::: "memory");  // (the source never changes: a bound on what is in flight)
+    }
+  }
+  if (mode == 1 && tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
 }  // namespace te
