@@ -25,7 +25,7 @@ NVCC_FLAGS = [
     "--expt-relaxed-constexpr",
     "-Xptxas", "-v",
     "-cudart", "static",
-]
+] + os.environ.get("TE_EXTRA_NVCC", "").split()
 
 
 def _nvcc() -> str:

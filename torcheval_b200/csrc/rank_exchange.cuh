@@ -37,12 +37,19 @@ __global__ void __launch_bounds__(kXsBlock, 2)
                         const uint32_t* __restrict__ splitters_dev, int nsp, const PeerSlabs peers, uint32_t cap,
                         uint32_t* cursors /*[W], zeroed*/, uint32_t* flags) {
   __shared__ __align__(16) uint32_t s_keys[kXsTile];
-  __shared__ uint32_t s_sp[16], s_cnt[kMaxSplitters + 1], s_start[kMaxSplitters + 2], s_dst[kMaxSplitters + 1];
+  // the per-destination counters in kXsRepl copies (lane l counts in copy l % kXsRepl, the copies in
+  // different banks): with W destinations 32 / W lanes of every instruction hit one counter, and a
+  // shared atomic on one address serialises them (2 ranks: 16 deep)
+  constexpr int kXsRepl = 8, kXsCopy = 20;
+  __shared__ uint32_t s_sp[16], s_cnt[kXsRepl * kXsCopy], s_startc[kXsRepl * kXsCopy], s_start[kMaxSplitters + 2],
+      s_dst[kMaxSplitters + 1];
   __shared__ unsigned long long s_peer[kMaxSplitters + 1];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t nb = (uint32_t)nsp + 1u;
   if (tid < 16) s_sp[tid] = (int)tid < nsp ? splitters_dev[tid] : 0xffffffffu;
-  if (tid <= (unsigned)kMaxSplitters) s_cnt[tid] = 0u, s_peer[tid] = peers.slab[tid];
+  if (tid <= (unsigned)kMaxSplitters) s_peer[tid] = peers.slab[tid];
+  if (tid < kXsRepl * kXsCopy) s_cnt[tid] = 0u;
+  const uint32_t my_copy = (lane & (uint32_t)(kXsRepl - 1)) * (uint32_t)kXsCopy;
   __syncthreads();
   auto bucket_of = [&](uint32_t k) -> uint32_t {  // #{splitters <= k}: branch-free binary search
     if (nsp == 1) return s_sp[0] <= k ? 1u : 0u;
@@ -102,7 +109,7 @@ __global__ void __launch_bounds__(kXsBlock, 2)
 #pragma unroll
     for (int i = 0; i < kXsIpt; ++i) {
       const uint32_t d = bucket_of(key[i]);
-      const uint32_t r = rec(i) < valid ? atomicAdd(&s_cnt[d], 1u) : 0u;
+      const uint32_t r = rec(i) < valid ? atomicAdd(&s_cnt[my_copy + d], 1u) : 0u;
       if (i & 1)
         rk[i >> 1] |= r << 16;
       else
@@ -117,7 +124,9 @@ __global__ void __launch_bounds__(kXsBlock, 2)
     // per destination with records; the atomics' round trip overlaps with the scatter below
     uint32_t my_off = 0u, my_cnt = 0u;
     if (warp == 0) {
-      const uint32_t c = lane < nb ? s_cnt[lane] : 0u;
+      uint32_t cc[kXsRepl], c = 0u;
+#pragma unroll
+      for (int q = 0; q < kXsRepl; ++q) cc[q] = lane < nb ? s_cnt[q * kXsCopy + lane] : 0u, c += cc[q];
       uint32_t incl = c;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
@@ -126,7 +135,13 @@ __global__ void __launch_bounds__(kXsBlock, 2)
       }
       if (lane <= nb) s_start[lane] = incl - c;  // (lane == nb: the tile total)
       if (lane < nb) {
-        s_cnt[lane] = 0u;
+        uint32_t at = incl - c;  // the copies of a destination follow one another inside its group
+#pragma unroll
+        for (int q = 0; q < kXsRepl; ++q) {
+          s_startc[q * kXsCopy + lane] = at;
+          at += cc[q];
+          s_cnt[q * kXsCopy + lane] = 0u;
+        }
         my_cnt = c;
         my_off = c ? atomicAdd(&cursors[lane], c) : 0u;  // (first looked at after the scatter)
       }
@@ -136,7 +151,7 @@ __global__ void __launch_bounds__(kXsBlock, 2)
     for (int i = 0; i < kXsIpt; ++i) {
       const uint32_t d = (bk[i >> 3] >> (4 * (i & 7))) & 15u;
       const uint32_t r = (i & 1) ? rk[i >> 1] >> 16 : rk[i >> 1] & 0xffffu;
-      if (rec(i) < valid) s_keys[s_start[d] + r] = key[i];
+      if (rec(i) < valid) s_keys[s_startc[my_copy + d] + r] = key[i];
     }
     if (warp == 0 && lane < nb) {
       if (my_off + my_cnt > cap) {  // the slab is full: nothing of this group is written, the call is redone

@@ -76,12 +76,9 @@ __global__ void __launch_bounds__(256)
 // One CTA: the work list.  Warp w owns segments [2048 w, 2048 w + 2048) and reads them 32 at a
 // time (coalesced); a first sweep gives every warp its totals, a second one hands every segment
 // its first item, its first slab and its slot in the multi-piece list (warp scans + a carry).
-__global__ void __launch_bounds__(1024)
-    leaf_plan_kernel(const uint32_t* __restrict__ seg_start, uint32_t piece, uint32_t max_items,
-                     uint32_t max_slabs, LeafItem* __restrict__ items, LeafMulti* __restrict__ multi,
-                     LeafHeader* hdr, size_t bstride = 0) {
-  seg_start = batch_ptr(seg_start, bstride), items = batch_ptr(items, bstride);
-  multi = batch_ptr(multi, bstride), hdr = batch_ptr(hdr, bstride);
+__device__ __forceinline__ void leaf_plan_body(const uint32_t* __restrict__ seg_start, uint32_t piece, uint32_t max_items,
+                                               uint32_t max_slabs, LeafItem* __restrict__ items,
+                                               LeafMulti* __restrict__ multi, LeafHeader* hdr) {
   __shared__ uint32_t ws[3][32];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   constexpr int ROWS = kLeafSegs / 1024;
@@ -152,6 +149,14 @@ __global__ void __launch_bounds__(1024)
   }
 }
 
+__global__ void __launch_bounds__(1024)
+    leaf_plan_kernel(const uint32_t* __restrict__ seg_start, uint32_t piece, uint32_t max_items,
+                     uint32_t max_slabs, LeafItem* __restrict__ items, LeafMulti* __restrict__ multi,
+                     LeafHeader* hdr, size_t bstride = 0) {
+  leaf_plan_body(batch_ptr(seg_start, bstride), piece, max_items, max_slabs, batch_ptr(items, bstride),
+                 batch_ptr(multi, bstride), batch_ptr(hdr, bstride));
+}
+
 // Segments of at most kLeafTiny keys — for [0, 1) scores the thousands of segments of the low
 // binades — are not worth clearing and walking 32 768 counters (~2 us of a whole CTA each): one
 // WARP takes such a segment, four keys per lane, and counts pairs directly.  With packed keys
@@ -159,12 +164,9 @@ __global__ void __launch_bounds__(1024)
 //     2 [v_j < v_i] + [v_j == v_i]  =  [kj < ki] + [kj + 1 < ki],
 // so sources that are not negatives are replaced by 0xfffffffe (no key of this path reaches 2^31)
 // and own keys that are not positives by 0, and the inner loop is two compares per pair.
-__global__ void __launch_bounds__(256)
-    leaf_tiny_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ seg_start,
-                     SegStat* __restrict__ seg_stats, size_t bstride = 0) {
-  keys = batch_ptr(keys, bstride), seg_start = batch_ptr(seg_start, bstride), seg_stats = batch_ptr(seg_stats, bstride);
+__device__ __forceinline__ void leaf_tiny_body(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ seg_start,
+                                               SegStat* __restrict__ seg_stats, uint32_t s) {
   const unsigned lane = threadIdx.x & 31;
-  const uint32_t s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (s >= kLeafSegs) return;
   const uint32_t b = seg_start[s], e = seg_start[s + 1];
   if (e <= b || e - b > kLeafTiny) return;
@@ -199,6 +201,30 @@ __global__ void __launch_bounds__(256)
     r.A = acc, r.P = npos, r.N = cnt - npos;
     seg_stats[s] = r;
   }
+}
+
+__global__ void __launch_bounds__(256)
+    leaf_tiny_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ seg_start,
+                     SegStat* __restrict__ seg_stats, size_t bstride = 0) {
+  leaf_tiny_body(batch_ptr(keys, bstride), batch_ptr(seg_start, bstride), batch_ptr(seg_stats, bstride),
+                 blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5));
+}
+
+// Both of the above in one launch: CTA 0 writes the work list (one CTA, ~50 us of latency) while the
+// other CTAs take the tiny segments, a warp each — the two are independent, and on their own they
+// were two launches in a row on the critical path.
+__global__ void __launch_bounds__(1024)
+    leaf_tiny_plan_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ seg_start,
+                          SegStat* __restrict__ seg_stats, uint32_t piece, uint32_t max_items, uint32_t max_slabs,
+                          LeafItem* __restrict__ items, LeafMulti* __restrict__ multi, LeafHeader* hdr, size_t bstride = 0) {
+  seg_start = batch_ptr(seg_start, bstride);
+  if (blockIdx.x == 0) {
+    leaf_plan_body(seg_start, piece, max_items, max_slabs, batch_ptr(items, bstride), batch_ptr(multi, bstride),
+                   batch_ptr(hdr, bstride));
+    return;
+  }
+  leaf_tiny_body(batch_ptr(keys, bstride), seg_start, batch_ptr(seg_stats, bstride),
+                 (blockIdx.x - 1u) * 32u + (threadIdx.x >> 5));
 }
 
 // Walk of one segment's histogram, held as kLeafVecPerThread uint4 per thread in the layout

@@ -255,7 +255,8 @@ struct MsdTables {
 template <int TILE>
 __global__ void __launch_bounds__(1024)
     joint_scan_kernel(const uint32_t* __restrict__ joint, uint32_t* __restrict__ seg_start, uint32_t* __restrict__ cursor1,
-                      uint32_t* __restrict__ cursor2, MsdTables* __restrict__ tables, size_t bstride = 0) {
+                      uint32_t* __restrict__ cursor2, MsdTables* __restrict__ tables, size_t bstride = 0,
+                      uint32_t hot8_top = 3, uint32_t hot8_low = 3) {
   joint = batch_ptr(joint, bstride), seg_start = batch_ptr(seg_start, bstride), cursor1 = batch_ptr(cursor1, bstride);
   cursor2 = batch_ptr(cursor2, bstride), tables = batch_ptr(tables, bstride);
   __shared__ uint32_t ws[32];
@@ -310,7 +311,7 @@ __global__ void __launch_bounds__(1024)
     }
     const uint32_t need = max((E - B + 7) / 8, 1u);
     tables->hot_low[tid] = (c0 >= need ? d0 : kNoHot) | ((c1 >= need ? d1 : kNoHot) << 16);
-    s_hotsum[tid] = (unsigned long long)c0 * 8 >= 3ull * (E - B) ? E - B : 0u;  // buckets dominated by one run
+    s_hotsum[tid] = (unsigned long long)c0 * 8 >= (unsigned long long)hot8_low * (E - B) ? E - B : 0u;  // buckets dominated by one run
   }
   __syncthreads();
   if (tid == 0) {
@@ -331,7 +332,7 @@ __global__ void __launch_bounds__(1024)
     for (int b = 0; b < kRadix; ++b) hot_low += s_hotsum[b];
     // (what hurts is the multiplicity on ONE counter: two digits of 25 % each — uniform [0, 1)
     // scores — are served faster by plain atomics, 3.0 against 3.8 ms at 2^30)
-    tables->use_hot[0] = (unsigned long long)c0 * 8 >= 3ull * n && n ? 1u : 0u;
+    tables->use_hot[0] = (unsigned long long)c0 * 8 >= (unsigned long long)hot8_top * n && n ? 1u : 0u;
     tables->use_hot[1] = hot_low * 2 >= n && n ? 1u : 0u;
     tables->tile_prefix[kRadix] = acc;
   }
@@ -345,7 +346,13 @@ __global__ void __launch_bounds__(1024)
 //     (tables->tile_prefix), digit = key bits 15..22, cursors = cursor2 + 256 b.
 // Slot i of thread t is record (i / 4 * BLOCK + t) * 4 + i % 4 of the tile (16-byte accesses); ranks
 // inside a digit are handed out in arrival order (one shared atomic per record on a CTA-wide table).
-template <bool BUCKETED, bool PACK, bool HOT, int BLOCK = kPrBlock, int IPT = kPrIpt>
+// REPL: the CTA-wide counter table is kept in REPL copies, lane l counting in copy l % REPL, the
+// copies 8 banks apart.  The digit of pass 1 is the float exponent: uniform [0, 1) scores put 25 % of
+// the records on each of two counters, 8 lanes of every instruction on one address, and a shared
+// atomic serialises them; with 4 copies it is 2 lanes per address.
+// HOT: which of the two instantiations launched for a pass this is (tables->use_hot picks one);
+// BALLOT: records carrying one of the two named hot digit values are ranked inside the warp.
+template <bool BUCKETED, bool PACK, bool HOT, int BLOCK = kPrBlock, int IPT = kPrIpt, int REPL = 1, bool BALLOT = HOT>
 __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
     cursor_partition_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ label_bits,
                             uint32_t* __restrict__ keys_out, uint32_t n, const uint32_t* __restrict__ n_dev,
@@ -360,7 +367,9 @@ __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
   constexpr int TILE = BLOCK * IPT;
   static_assert(IPT % 4 == 0 && TILE <= 65536 && BLOCK >= kRadix, "16-byte slots; 16-bit ranks");
   constexpr int SHIFT = BUCKETED ? kLeafBits : kLeafBits + kRadixBits;
-  __shared__ uint32_t s_cnt[kRadix], s_start[kRadix], s_goff[kRadix], s_wsum[kRadix / kWarp];
+  constexpr int kCopy = kRadix + 32 / REPL;  // words per copy: copy c starts c * 32 / REPL banks further on
+  static_assert(REPL == 1 || REPL == 2 || REPL == 4 || REPL == 8, "copies are picked by the low lane bits");
+  __shared__ uint32_t s_cnt[REPL * kCopy], s_start[REPL * kCopy], s_goff[kRadix], s_wsum[kRadix / kWarp];
   __shared__ uint32_t s_tp[kRadix + 1];
   __shared__ __align__(16) uint32_t s_bits[2][PACK ? TILE / 32 : 4];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -368,8 +377,9 @@ __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
   if (n_dev) n = *n_dev;  // (the record count lives in device memory: receive side of the sample sort)
   if (BUCKETED)
     for (int i = tid; i <= kRadix; i += BLOCK) s_tp[i] = tables->tile_prefix[i];
-  if (tid < kRadix) s_cnt[tid] = 0u;
+  for (int i = tid; i < REPL * kCopy; i += BLOCK) s_cnt[i] = 0u;
   __syncthreads();
+  const uint32_t my_copy = (lane & (uint32_t)(REPL - 1)) * (uint32_t)kCopy;
   const bool slabs = !BUCKETED && view.counts != nullptr;
   const uint32_t ntiles = BUCKETED ? s_tp[kRadix] : (slabs ? view.nslabs * (view.cap / TILE) : (n + TILE - 1) / TILE);
   auto digit = [&](uint32_t k) -> uint32_t { return (k >> SHIFT) & (kRadix - 1); };
@@ -453,7 +463,7 @@ __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
     // 5.6 instead of 3.0 ms per pass).  The histogram names up to two hot digit values; records that
     // carry one are ranked inside the warp — a ballot, and a running count in a register — and the
     // warp adds its total to the counter ONCE per tile; that base is added to the ranks at scatter time.
-    const uint32_t hot = !HOT ? (kNoHot | (kNoHot << 16)) : (BUCKETED ? tables->hot_low[w.bucket] : tables->hot_top);
+    const uint32_t hot = !BALLOT ? (kNoHot | (kNoHot << 16)) : (BUCKETED ? tables->hot_low[w.bucket] : tables->hot_top);
     const uint32_t h0 = hot & 0xffffu, h1 = hot >> 16;
     uint32_t hc0 = 0u, hc1 = 0u;  // hot records of this warp so far (uniform over the lanes)
     uint32_t rk[IPT / 2];
@@ -464,7 +474,7 @@ __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
       const bool in = r0 >= w.lo && r0 < w.hi;
       uint32_t r = 0u;
       bool cold = in;
-      if (HOT && h0 != kNoHot) {  // uniform
+      if (BALLOT && h0 != kNoHot) {  // uniform
         const bool is0 = in && d == h0, is1 = in && d == h1;
         const uint32_t m0 = __ballot_sync(kFull, is0), m1 = __ballot_sync(kFull, is1);
         const uint32_t lt = (1u << lane) - 1u;
@@ -474,14 +484,14 @@ __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
         hc1 += __popc(m1);
         cold = in && !is0 && !is1;
       }
-      if (cold) r = atomicAdd(&s_cnt[d], 1u);
+      if (cold) r = atomicAdd(&s_cnt[my_copy + d], 1u);
       if (i & 1)
         rk[i >> 1] |= r << 16;
       else
         rk[i >> 1] = r;
     }
     uint32_t wb0 = 0u, wb1 = 0u;  // where this warp's hot records start inside their digit's run
-    if (HOT && h0 != kNoHot) {
+    if (BALLOT && h0 != kNoHot) {
       if (lane == 0 && hc0) wb0 = atomicAdd(&s_cnt[h0], hc0);
       if (lane == 0 && hc1) wb1 = atomicAdd(&s_cnt[h1], hc1);  // (h1 == kNoHot: hc1 stays 0)
       wb0 = __shfl_sync(kFull, wb0, 0);
@@ -492,7 +502,9 @@ __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
     //      (its round trip overlaps with the scatter) ----
     uint32_t g = 0u, excl = 0u;
     if (tid < kRadix) {
-      const uint32_t c = s_cnt[tid];
+      uint32_t cc[REPL], c = 0u;
+#pragma unroll
+      for (int q = 0; q < REPL; ++q) cc[q] = s_cnt[q * kCopy + tid], c += cc[q];
       uint32_t incl = c;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
@@ -506,8 +518,13 @@ __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
       for (int ww = 0; ww < kRadix / kWarp; ++ww)
         if (ww < (int)warp) wb += s_wsum[ww];
       excl = wb + incl - c;
-      s_start[tid] = excl;
-      s_cnt[tid] = 0u;  // for the next tile
+      uint32_t at = excl;  // the copies of a digit follow one another inside its run
+#pragma unroll
+      for (int q = 0; q < REPL; ++q) {
+        s_start[q * kCopy + tid] = at;
+        at += cc[q];
+        s_cnt[q * kCopy + tid] = 0u;  // for the next tile
+      }
       if (c) g = atomicAdd(cursors + (BUCKETED ? w.bucket * kRadix : 0u) + tid, c);
     }
     __syncthreads();
@@ -517,9 +534,11 @@ __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
       const uint32_t r0 = rec(i);
       uint32_t r = (i & 1) ? rk[i >> 1] >> 16 : rk[i >> 1] & 0xffffu;
       const uint32_t d = digit(key[i]);
-      if (HOT && d == h0) r += wb0;
-      if (HOT && d == h1) r += wb1;
-      if (r0 >= w.lo && r0 < w.hi) s_keys[s_start[d] + r] = key[i];
+      if (BALLOT && d == h0) r += wb0;
+      if (BALLOT && d == h1) r += wb1;
+      // (hot records were ranked in copy 0's space by their warp: wb0 / wb1 came from copy 0)
+      const uint32_t cp = (BALLOT && (d == h0 || d == h1)) ? 0u : my_copy;
+      if (r0 >= w.lo && r0 < w.hi) s_keys[s_start[cp + d] + r] = key[i];
     }
     if (tid < kRadix) s_goff[tid] = g - excl;  // output index = s_goff[d] + tile position
     __syncthreads();
