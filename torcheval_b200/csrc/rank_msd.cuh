@@ -371,12 +371,13 @@ __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
   static_assert(REPL == 1 || REPL == 2 || REPL == 4 || REPL == 8, "copies are picked by the low lane bits");
   __shared__ uint32_t s_cnt[REPL * kCopy], s_start[REPL * kCopy], s_goff[kRadix], s_wsum[kRadix / kWarp];
   __shared__ uint32_t s_tp[kRadix + 1];
+  __shared__ uint32_t s_bs[BUCKETED ? kRadix + 1 : 1];  // where the buckets of pass 1 start (pass 2 looks them up per tile)
   __shared__ __align__(16) uint32_t s_bits[2][PACK ? TILE / 32 : 4];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if ((tables->use_hot[BUCKETED ? 1 : 0] != 0u) != HOT) return;  // the other instantiation's turn
   if (n_dev) n = *n_dev;  // (the record count lives in device memory: receive side of the sample sort)
   if (BUCKETED)
-    for (int i = tid; i <= kRadix; i += BLOCK) s_tp[i] = tables->tile_prefix[i];
+    for (int i = tid; i <= kRadix; i += BLOCK) s_tp[i] = tables->tile_prefix[i], s_bs[i] = seg_start[i * kRadix];
   for (int i = tid; i < REPL * kCopy; i += BLOCK) s_cnt[i] = 0u;
   __syncthreads();
   const uint32_t my_copy = (lane & (uint32_t)(REPL - 1)) * (uint32_t)kCopy;
@@ -400,7 +401,7 @@ __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
 #pragma unroll
     for (int step = kRadix / 2; step >= 1; step >>= 1)
       if (s_tp[b + step] <= t) b += step;
-    const uint32_t B = seg_start[b * kRadix], E = seg_start[(b + 1) * kRadix];
+    const uint32_t B = s_bs[BUCKETED ? b : 0], E = s_bs[BUCKETED ? b + 1 : 0];
     w.bucket = b;
     w.base = (B & ~3u) + (t - s_tp[b]) * (uint32_t)TILE;
     w.lo = B > w.base ? B - w.base : 0u;
