@@ -260,9 +260,9 @@ __global__ void __launch_bounds__(1024)
   joint = batch_ptr(joint, bstride), seg_start = batch_ptr(seg_start, bstride), cursor1 = batch_ptr(cursor1, bstride);
   cursor2 = batch_ptr(cursor2, bstride), tables = batch_ptr(tables, bstride);
   __shared__ uint32_t ws[32];
-  __shared__ uint32_t s_tiles[kRadix], s_size[kRadix], s_hotsum[kRadix];
+  __shared__ uint32_t s_tiles[kRadix], s_size[kRadix], s_hotsum[kRadix], s_bmax[kRadix], s_w8[3][8];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  constexpr int ROWS = kLeafSegs / 1024;
+  constexpr int ROWS = kLeafSegs / 1024;  // 64 rows of 32 segments per warp = 8 buckets of pass 1
   uint32_t tot = 0;
 #pragma unroll 16
   for (int j = 0; j < ROWS; ++j) tot += joint[(warp * ROWS + j) * 32 + lane];
@@ -271,7 +271,8 @@ __global__ void __launch_bounds__(1024)
   __syncthreads();
   uint32_t at = 0;
   for (int w = 0; w < (int)warp; ++w) at += ws[w];
-  for (int j0 = 0; j0 < ROWS; j0 += 8) {
+  uint32_t bmax = 0;  // fullest run of the bucket being scanned (lanes hold partial maxima)
+  for (int j0 = 0; j0 < ROWS; j0 += 8) {  // one bucket of pass 1 per round
    uint32_t c8[8];  // eight independent loads in flight, then eight warp scans (one CTA: latency is all there is)
 #pragma unroll
    for (int q = 0; q < 8; ++q) c8[q] = joint[(warp * ROWS + j0 + q) * 32 + lane];
@@ -279,6 +280,7 @@ __global__ void __launch_bounds__(1024)
    for (int q = 0; q < 8; ++q) {
     const uint32_t s = (warp * ROWS + j0 + q) * 32 + lane;
     const uint32_t c = c8[q];
+    bmax = max(bmax, c);
     uint32_t incl = c;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -292,50 +294,51 @@ __global__ void __launch_bounds__(1024)
     at += __shfl_sync(kFull, incl, 31);
     if (s == kLeafSegs - 1) seg_start[kLeafSegs] = excl + c;
    }
+#pragma unroll
+   for (int o = 16; o > 0; o >>= 1) bmax = max(bmax, __shfl_xor_sync(kFull, bmax, o));
+   if (lane == 0) s_bmax[(warp * ROWS + j0) >> 3] = bmax;  // bucket = segment >> 8 = row >> 3
+   bmax = 0;
   }
   __syncthreads();  // seg_start of every bucket boundary is in global memory, visible to this CTA
+  // 256 threads, one per bucket: its tiles, its size, whether one run dominates it; then the
+  // exclusive prefix of the tiles and the three totals by warp scans (8 warps)
+  uint32_t my_tiles = 0, my_size = 0, my_hot = 0;
   if (tid < kRadix) {
     const uint32_t B = seg_start[tid * kRadix], E = seg_start[(tid + 1) * kRadix];
     const uint32_t A = B & ~3u;
-    s_tiles[tid] = E > B ? (E - A + TILE - 1) / TILE : 0u;
-    s_size[tid] = E - B;
-    // the two largest runs of this bucket, if they hold >= 1/8 of it
-    uint32_t c0 = 0, c1 = 0, d0 = kNoHot, d1 = kNoHot;
-    for (int q = 0; q < kRadix; ++q) {
-      const uint32_t d = (q + tid) & (kRadix - 1);
-      const uint32_t c = joint[tid * kRadix + d];
-      if (c > c0)
-        c1 = c0, d1 = d0, c0 = c, d0 = d;
-      else if (c > c1)
-        c1 = c, d1 = d;
+    my_tiles = E > B ? (E - A + TILE - 1) / TILE : 0u;
+    my_size = E - B;
+    my_hot = (unsigned long long)s_bmax[tid] * 8 >= (unsigned long long)hot8_low * (E - B) ? E - B : 0u;  // dominated by one run
+    tables->hot_low[tid] = kNoHot | (kNoHot << 16);  // (no instantiation ranks hot digits by ballot any more)
+    uint32_t i_t = my_tiles, i_s = my_size, i_h = my_hot, mx = my_size;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t u0 = __shfl_up_sync(kFull, i_t, o), u1 = __shfl_up_sync(kFull, i_s, o), u2 = __shfl_up_sync(kFull, i_h, o);
+      if (lane >= (unsigned)o) i_t += u0, i_s += u1, i_h += u2;
+      mx = max(mx, __shfl_xor_sync(kFull, mx, o));
     }
-    const uint32_t need = max((E - B + 7) / 8, 1u);
-    tables->hot_low[tid] = (c0 >= need ? d0 : kNoHot) | ((c1 >= need ? d1 : kNoHot) << 16);
-    s_hotsum[tid] = (unsigned long long)c0 * 8 >= (unsigned long long)hot8_low * (E - B) ? E - B : 0u;  // buckets dominated by one run
-  }
-  __syncthreads();
-  if (tid == 0) {
-    uint32_t acc = 0, n = 0, c0 = 0, c1 = 0, d0 = kNoHot, d1 = kNoHot;
-    for (int b = 0; b < kRadix; ++b) {
-      tables->tile_prefix[b] = acc;
-      acc += s_tiles[b];
-      n += s_size[b];
-      const uint32_t c = s_size[b];
-      if (c > c0)
-        c1 = c0, d1 = d0, c0 = c, d0 = (uint32_t)b;
-      else if (c > c1)
-        c1 = c, d1 = (uint32_t)b;
+    if (lane == 31) s_w8[0][warp] = i_t, s_w8[1][warp] = i_s, s_w8[2][warp] = i_h;
+    if (lane == 0) s_size[warp] = mx;  // (the largest bucket of this warp's 32)
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    uint32_t base_t = 0, n = 0, hot = 0, c0 = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      if (w < (int)warp) base_t += s_w8[0][w];
+      n += s_w8[1][w];
+      hot += s_w8[2][w];
+      c0 = max(c0, s_size[w]);
     }
-    const uint32_t need = max((n + 7) / 8, 1u);
-    tables->hot_top = (c0 >= need ? d0 : kNoHot) | ((c1 >= need ? d1 : kNoHot) << 16);
-    unsigned long long hot_low = 0;
-    for (int b = 0; b < kRadix; ++b) hot_low += s_hotsum[b];
-    // (what hurts is the multiplicity on ONE counter: two digits of 25 % each — uniform [0, 1)
-    // scores — are served faster by plain atomics, 3.0 against 3.8 ms at 2^30)
-    tables->use_hot[0] = (unsigned long long)c0 * 8 >= (unsigned long long)hot8_top * n && n ? 1u : 0u;
-    tables->use_hot[1] = hot_low * 2 >= n && n ? 1u : 0u;
-    tables->tile_prefix[kRadix] = acc;
+    tables->tile_prefix[tid] = base_t + i_t - my_tiles;
+    if (tid == kRadix - 1) {
+      tables->tile_prefix[kRadix] = base_t + i_t;
+      tables->hot_top = kNoHot | (kNoHot << 16);
+      // (what hurts is the multiplicity on ONE counter: two digits of 25 % each — uniform [0, 1)
+      // scores — are served by plain atomics)
+      tables->use_hot[0] = (unsigned long long)c0 * 8 >= (unsigned long long)hot8_top * n && n ? 1u : 0u;
+      tables->use_hot[1] = (unsigned long long)hot * 2 >= n && n ? 1u : 0u;
+    }
   }
+  (void)s_tiles, (void)s_hotsum;
 }
 
 // One partition pass with cursor placement.  Persistent CTAs, tile t = blockIdx.x + k * gridDim.x.
