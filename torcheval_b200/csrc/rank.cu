@@ -1325,7 +1325,7 @@ int leaf_passes_msd_impl(const RankPlan& p, void* scratch, const float* score, c
     if ((rc = launch(cursor_partition_kernel<false, true, false, PBLOCK, PIPT, kTopRepl>, "cursor_pass_top_pack", grid1, in1, bits1, out1, nullptr, cursor1))) return rc;
   }
   if ((rc = launch(cursor_partition_kernel<true, false, false, PBLOCK, PIPT, kLowRepl>, "cursor_pass_low", (uint32_t)(sms * kCtasPerSm), out1, nullptr, out2, seg_start, cursor2))) return rc;
-  if ((rc = launch(cursor_partition_kernel<true, false, true, PBLOCK, PIPT, 8, false>, "cursor_pass_low_hot", (uint32_t)(sms * kCtasPerSm), out1, nullptr, out2, seg_start, cursor2))) return rc;
+  if ((rc = launch(cursor_partition_kernel<true, false, true, PBLOCK, PIPT, 8>, "cursor_pass_low_hot", (uint32_t)(sms * kCtasPerSm), out1, nullptr, out2, seg_start, cursor2))) return rc;
   return TE_OK;
 }
 

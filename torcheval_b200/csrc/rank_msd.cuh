@@ -235,18 +235,11 @@ __global__ void __launch_bounds__(kUjBlock, 1)
 // [seg_start[256 b], seg_start[256 (b + 1)]) of the first pass's output; its tiles start at that
 // start rounded down to a multiple of 4 records (16-byte copies), so the first tile of a bucket may
 // begin with up to 3 records of the previous bucket, which are masked out.
-constexpr uint32_t kNoHot = 0xffffu;
 struct MsdTables {
   uint32_t tile_prefix[kRadix + 1];  // tiles of the buckets before b; [256] = total
-  // Skew: up to two "hot" digit values per pass-1 input / per pass-2 bucket — values that hold at
-  // least 1/8 of the records there — packed as hot0 | hot1 << 16 (kNoHot = none).  Records with a
-  // hot digit are ranked with a ballot and a per-warp register counter instead of a shared atomic
-  // (see cursor_partition_kernel).
-  uint32_t hot_top;
-  uint32_t hot_low[kRadix];
-  // Which instantiation of each pass does the work (both are launched, the other one returns at
-  // once): the hot-digit one costs registers and ~0.6 ms at 2^30 records, so it only runs when one
-  // digit value holds >= 3/8 of the records (top pass) / of most buckets (low pass).
+  // Which instantiation of a pass does the work (both are launched, the other one returns at once).
+  // [1], pass 2: the one with eight counter copies when most records sit in buckets where one run
+  // holds >= 3/8 (tied or quantised scores); [0], pass 1: always 0, it has a single instantiation.
   uint32_t use_hot[2];
 };
 
@@ -309,7 +302,6 @@ __global__ void __launch_bounds__(1024)
     my_tiles = E > B ? (E - A + TILE - 1) / TILE : 0u;
     my_size = E - B;
     my_hot = (unsigned long long)s_bmax[tid] * 8 >= (unsigned long long)hot8_low * (E - B) ? E - B : 0u;  // dominated by one run
-    tables->hot_low[tid] = kNoHot | (kNoHot << 16);  // (no instantiation ranks hot digits by ballot any more)
     uint32_t i_t = my_tiles, i_s = my_size, i_h = my_hot, mx = my_size;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -331,7 +323,6 @@ __global__ void __launch_bounds__(1024)
     tables->tile_prefix[tid] = base_t + i_t - my_tiles;
     if (tid == kRadix - 1) {
       tables->tile_prefix[kRadix] = base_t + i_t;
-      tables->hot_top = kNoHot | (kNoHot << 16);
       // (what hurts is the multiplicity on ONE counter: two digits of 25 % each — uniform [0, 1)
       // scores — are served by plain atomics)
       tables->use_hot[0] = (unsigned long long)c0 * 8 >= (unsigned long long)hot8_top * n && n ? 1u : 0u;
@@ -353,9 +344,9 @@ __global__ void __launch_bounds__(1024)
 // copies 8 banks apart.  The digit of pass 1 is the float exponent: uniform [0, 1) scores put 25 % of
 // the records on each of two counters, 8 lanes of every instruction on one address, and a shared
 // atomic serialises them; with 4 copies it is 2 lanes per address.
-// HOT: which of the two instantiations launched for a pass this is (tables->use_hot picks one);
-// BALLOT: records carrying one of the two named hot digit values are ranked inside the warp.
-template <bool BUCKETED, bool PACK, bool HOT, int BLOCK = kPrBlock, int IPT = kPrIpt, int REPL = 1, bool BALLOT = HOT>
+// HOT: which of the two instantiations launched for pass 2 this is (tables->use_hot picks one: the
+// plain one, or the one with more copies for buckets dominated by a single run; pass 1 has one).
+template <bool BUCKETED, bool PACK, bool HOT, int BLOCK = kPrBlock, int IPT = kPrIpt, int REPL = 1>
 __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
     cursor_partition_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ label_bits,
                             uint32_t* __restrict__ keys_out, uint32_t n, const uint32_t* __restrict__ n_dev,
@@ -461,45 +452,21 @@ __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
         }
       }
     }
-    // ---- rank: arrival order inside the digit, straight from the CTA-wide counters ----
+    // ---- rank: arrival order inside (digit, copy), straight from the CTA-wide counters ----
     // Skewed digits (one binade = one top digit; tied or quantised scores = few low digits): up to 32
     // lanes of an instruction hit ONE counter and the atomic serialises them (two values 50 / 50:
-    // 5.6 instead of 3.0 ms per pass).  The histogram names up to two hot digit values; records that
-    // carry one are ranked inside the warp — a ballot, and a running count in a register — and the
-    // warp adds its total to the counter ONCE per tile; that base is added to the ranks at scatter time.
-    const uint32_t hot = !BALLOT ? (kNoHot | (kNoHot << 16)) : (BUCKETED ? tables->hot_low[w.bucket] : tables->hot_top);
-    const uint32_t h0 = hot & 0xffffu, h1 = hot >> 16;
-    uint32_t hc0 = 0u, hc1 = 0u;  // hot records of this warp so far (uniform over the lanes)
+    // 5.6 instead of 3.0 ms per pass with one table).  The copies spread them over REPL addresses.
     uint32_t rk[IPT / 2];
 #pragma unroll
     for (int i = 0; i < IPT; ++i) {
       const uint32_t r0 = rec(i);
       const uint32_t d = digit(key[i]);
       const bool in = r0 >= w.lo && r0 < w.hi;
-      uint32_t r = 0u;
-      bool cold = in;
-      if (BALLOT && h0 != kNoHot) {  // uniform
-        const bool is0 = in && d == h0, is1 = in && d == h1;
-        const uint32_t m0 = __ballot_sync(kFull, is0), m1 = __ballot_sync(kFull, is1);
-        const uint32_t lt = (1u << lane) - 1u;
-        if (is0) r = hc0 + __popc(m0 & lt);
-        if (is1) r = hc1 + __popc(m1 & lt);
-        hc0 += __popc(m0);
-        hc1 += __popc(m1);
-        cold = in && !is0 && !is1;
-      }
-      if (cold) r = atomicAdd(&s_cnt[my_copy + d], 1u);
+      const uint32_t r = in ? atomicAdd(&s_cnt[my_copy + d], 1u) : 0u;
       if (i & 1)
         rk[i >> 1] |= r << 16;
       else
         rk[i >> 1] = r;
-    }
-    uint32_t wb0 = 0u, wb1 = 0u;  // where this warp's hot records start inside their digit's run
-    if (BALLOT && h0 != kNoHot) {
-      if (lane == 0 && hc0) wb0 = atomicAdd(&s_cnt[h0], hc0);
-      if (lane == 0 && hc1) wb1 = atomicAdd(&s_cnt[h1], hc1);  // (h1 == kNoHot: hc1 stays 0)
-      wb0 = __shfl_sync(kFull, wb0, 0);
-      wb1 = __shfl_sync(kFull, wb1, 0);
     }
     __syncthreads();  // all counts in; every thread holds its records, the buffer may be overwritten
     // ---- 256 digit threads: tile-local run starts, and room in the output from the global cursor
@@ -536,13 +503,9 @@ __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
 #pragma unroll
     for (int i = 0; i < IPT; ++i) {
       const uint32_t r0 = rec(i);
-      uint32_t r = (i & 1) ? rk[i >> 1] >> 16 : rk[i >> 1] & 0xffffu;
+      const uint32_t r = (i & 1) ? rk[i >> 1] >> 16 : rk[i >> 1] & 0xffffu;
       const uint32_t d = digit(key[i]);
-      if (BALLOT && d == h0) r += wb0;
-      if (BALLOT && d == h1) r += wb1;
-      // (hot records were ranked in copy 0's space by their warp: wb0 / wb1 came from copy 0)
-      const uint32_t cp = (BALLOT && (d == h0 || d == h1)) ? 0u : my_copy;
-      if (r0 >= w.lo && r0 < w.hi) s_keys[s_start[cp + d] + r] = key[i];
+      if (r0 >= w.lo && r0 < w.hi) s_keys[s_start[my_copy + d] + r] = key[i];
     }
     if (tid < kRadix) s_goff[tid] = g - excl;  // output index = s_goff[d] + tile position
     __syncthreads();
