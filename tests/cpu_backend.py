@@ -375,7 +375,10 @@ def install(monkeypatch=None):
     import torcheval_b200.metrics.functional.classification.binned_auroc as bauroc
     import torcheval_b200.metrics.functional.classification.f1_score as f1
 
-    for mod in (acc, bauroc, f1):
+    import torcheval_b200.metrics.functional.classification.precision as prec
+    import torcheval_b200.metrics.functional.classification.recall as rec
+
+    for mod in (acc, bauroc, f1, prec, rec):  # (modules that bound the name at import time)
         setter(mod, "compute_device", cpu)
     import torcheval_b200.distributed as tdist
 
