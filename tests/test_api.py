@@ -183,8 +183,12 @@ def test_functional_counting(backend, golden):
     for avg, key in (("micro", "f1_micro"), ("macro", "f1_macro"), ("weighted", "f1_weighted"), (None, "f1_none")):
         close(F.multiclass_f1_score(p, t, num_classes=5, average=avg), c[key])
     close(F.binary_accuracy(T([0.1, 0.9, 0.6, 0.2]), T([0, 1, 0, 0])), 0.75)
+    # float targets are compared as they are (reference accuracy.py:78): 0.5 matches no prediction
+    close(F.binary_accuracy(T([0.1, 0.9, 0.2, 0.3]), T([0.5, 1.0, 0.0, float("nan")])), 0.5)
     close(F.binary_f1_score(T([0.1, 0.9, 0.6, 0.2]), T([0, 1, 0, 0])), 2 / 3)
     close(F.multiclass_accuracy(T([[0.9, 0.1, 0], [0.1, 0.2, 0.7], [0.3, 0.4, 0.3]]), T([0, 1, 1]), k=2), 1.0)
+    # micro accuracy on scores: a target outside [0, C) is a miss, not an error (reference accuracy.py:269-272)
+    close(F.multiclass_accuracy(T([[0.9, 0.1, 0], [0.1, 0.2, 0.7], [0.3, 0.4, 0.3]]), T([0, 7, 1])), 2 / 3)
 
 
 def test_functional_precision_recall(backend, golden):

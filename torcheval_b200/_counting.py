@@ -86,7 +86,8 @@ def match_count(input: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
         C = x.shape[1]
         x = x.float() if x.dtype != torch.float32 else x
         c3 = torch.zeros((3, C), dtype=torch.int64, device=dev)
-        rng = ops.class_counts_(c3, x, t, C)
-        _raise_for_range(rng, C)
+        ops.class_counts_(c3, x, t, C)
+        # (a target outside [0, C) is skipped by the kernel = counted as a miss, which is what the
+        # reference's `(argmax == target).sum()` does with it, accuracy.py:269-272: no error here)
         return c3[0].sum()
     return ops.match_count(x.to(torch.int64), t)

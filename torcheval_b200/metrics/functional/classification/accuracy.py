@@ -75,7 +75,13 @@ def _binary_accuracy_update(
     out_dev = input.device
     dev = compute_device(input)
     pred = torch.where(stage(input, dev) < threshold, 0, 1)
-    num_correct = _counting.match_count(pred, stage(target, dev).to(torch.int64)).to(out_dev)
+    t = stage(target, dev)
+    if t.is_floating_point():
+        # the reference compares in the target's own dtype (accuracy.py:78: `input == target`): a
+        # target that is not an integer value never equals a prediction
+        ti = t.to(torch.int64)
+        t = torch.where(ti.to(t.dtype) == t, ti, torch.full_like(ti, -1))
+    num_correct = _counting.match_count(pred, t.to(torch.int64)).to(out_dev)
     return num_correct, torch.tensor(target.shape[0], dtype=torch.int64, device=out_dev)
 
 
