@@ -232,6 +232,23 @@ def main():
     wv = float(toolkit.sync_and_compute(wm))
     # merged window = the last 20 samples of every rank, concatenated
     res["generic/windowed"] = [wv, oracle.binary_auroc(np.concatenate([wx[r, 10:] for r in range(world)]), np.concatenate([wy[r, 10:] for r in range(world)]))[0]]
+    # multi-task BinaryAUROC with weights (2-D states: the gather path; compute = the batched general path)
+    K, nt = 3, 4001
+    mx, my, mw = rs.standard_normal((K, nt)).astype(np.float32), rs.integers(0, 2, (K, nt)), rs.random((K, nt)).astype(np.float32)
+    cut2 = [0] + [int(nt * (i + 1) / (world * 2)) for i in range(world - 1)] + [nt]
+    sl2 = slice(cut2[rank], cut2[rank + 1])
+    mt = BinaryAUROC(num_tasks=K).update(torch.from_numpy(mx[:, sl2]), torch.from_numpy(my[:, sl2]), torch.from_numpy(mw[:, sl2]))
+    res["sync/multitask_weighted"] = [
+        toolkit.sync_and_compute(mt).tolist(),
+        [oracle.binary_auroc(mx[k], my[k], mw[k].astype(np.float64))[0] for k in range(K)],
+    ]
+    # float64 scores that float32 cannot tell apart: the sync must rank them as float64 (gather path)
+    base = rs.integers(0, 300, nt) / 300.0
+    x64 = base + rs.integers(0, 4, nt) * 2.0**-40
+    y64 = (rs.random(nt) < 0.3 + 0.4 * base).astype(np.int64)
+    m64 = BinaryAUROC().update(torch.from_numpy(x64[sl2]), torch.from_numpy(y64[sl2]))
+    _, inv = np.unique(x64, return_inverse=True)
+    res["sync/float64_scores"] = [float(toolkit.sync_and_compute(m64)), oracle.binary_auroc(inv.astype(np.float32), y64)[0]]
     Path(os.environ["TE_TEST_OUT"] + f".{rank}").write_text(json.dumps(res))
     dist.barrier()
     dist.destroy_process_group()
