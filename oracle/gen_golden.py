@@ -266,6 +266,24 @@ def main() -> None:
         x1=x1, y1=y1, single=m1.compute(),
     )
 
+    # ---------------- appended in round 2 (after everything else: the generator sequence above is unchanged)
+    # multi-task AUROC with per-sample weights on logits (the batched general path); row 1 carries a
+    # weight float32 cannot hold, row 2 soft labels
+    K, nt = 4, 2000
+    xk = torch.randn(K, nt, generator=g)
+    xk[:, : nt // 3] = torch.round(xk[:, : nt // 3])
+    yk = randint(0, 2, (K, nt)).double()
+    wk = rand(K, nt).double()
+    wk[1, 7] = 1.0 + 2.0**-40
+    yk[2] = rand(nt).double()
+    put("binary_multitask_weighted/t4", x=xk, y=yk, w=wk, auroc=F.binary_auroc(xk, yk, num_tasks=K, weight=wk))
+    # float64 scores that float32 cannot tell apart (the dense-rank road), and int64 beyond 2^24
+    x64 = (randint(0, 50, (n,)).double() / 50) + randint(0, 5, (n,)).double() * 1e-9
+    y64 = randint(0, 2, (n,))
+    put("binary_f64/close", x=x64, y=y64, auroc=F.binary_auroc(x64, y64), auprc=F.binary_auprc(x64, y64))
+    xi64 = (1 << 40) + randint(0, 40, (n,))
+    put("binary_f64/int64", x=xi64, y=y64, auroc=F.binary_auroc(xi64, y64), auprc=F.binary_auprc(xi64, y64))
+
     OUT.parent.mkdir(parents=True, exist_ok=True)
     np.savez_compressed(OUT, **store)
     print(f"wrote {OUT} ({OUT.stat().st_size / 1024:.0f} KiB, {len(store)} arrays)")

@@ -51,6 +51,16 @@ def test_functional_exact(backend, golden):
     assert p.shape == (3,) and p.dtype == torch.float32
     close(p, c["auprc"], 1e-4)
     assert F.binary_auprc(T(c["x"][:1]), T(c["y"][:1])).shape == (1,)  # 1 x N keeps its leading dim
+    # reference outputs for the paths added in round 2: (tasks, n) with weights (one launch train for
+    # all tasks; row 1 carries a weight float32 cannot hold, row 2 soft labels) and 64-bit scores
+    c = golden.case("binary_multitask_weighted/t4")
+    a = F.binary_auroc(T(c["x"]), T(c["y"]), num_tasks=4, weight=T(c["w"]))
+    assert a.shape == (4,) and a.dtype == torch.float64
+    close(a, c["auroc"])
+    for name in ("close", "int64"):
+        c = golden.case(f"binary_f64/{name}")
+        close(F.binary_auroc(T(c["x"]), T(c["y"])), c["auroc"])
+        close(F.binary_auprc(T(c["x"]), T(c["y"])), c["auprc"], 1e-4)
     for name in golden.cases("multiclass"):
         c = golden.case(f"multiclass/{name}")
         C = c["x"].shape[1]

@@ -40,6 +40,19 @@ def test_binary_multitask(golden):
         close(oracle.binary_auprc(c["x"][k], c["y"][k]), c["auprc"][k], RTOL32)
 
 
+def test_round2_fixtures(golden):
+    """Fixtures appended in round 2: multi-task weighted AUROC; 64-bit scores (the C oracle takes
+    float32 scores, so it is handed their dense ranks: same order, same ties)."""
+    c = golden.case("binary_multitask_weighted/t4")
+    for k in range(4):
+        close(oracle.binary_auroc(c["x"][k], c["y"][k], c["w"][k])[0], c["auroc"][k], RTOL64)
+    for name in ("close", "int64"):
+        c = golden.case(f"binary_f64/{name}")
+        ranks = np.unique(c["x"], return_inverse=True)[1].astype(np.float32)
+        close(oracle.binary_auroc(ranks, c["y"])[0], c["auroc"], RTOL64)
+        close(oracle.binary_auprc(ranks, c["y"]), c["auprc"], RTOL32)
+
+
 def test_multiclass_multilabel(golden):
     for name in golden.cases("multiclass"):
         c = golden.case(f"multiclass/{name}")
