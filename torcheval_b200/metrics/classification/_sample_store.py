@@ -8,7 +8,7 @@ from typing import Iterable, TypeVar
 
 import torch
 
-from ..metric import Metric
+from ..metric import Metric, cat_all
 
 TSelf = TypeVar("TSelf")
 
@@ -25,17 +25,17 @@ class SampleStoreMetric(Metric[torch.Tensor]):
         self.targets.append(target)
 
     def _all_inputs(self) -> torch.Tensor:
-        return torch.cat(self.inputs, self._cat_dim)
+        return cat_all(self.inputs, self._cat_dim)
 
     def _all_targets(self) -> torch.Tensor:
-        return torch.cat(self.targets, self._cat_dim)
+        return cat_all(self.targets, self._cat_dim)
 
     @torch.inference_mode()
     def merge_state(self: TSelf, metrics: Iterable[TSelf]) -> TSelf:
         for metric in metrics:
             if metric.inputs:
-                self.inputs.append(torch.cat(metric.inputs, self._cat_dim).to(self.device))
-                self.targets.append(torch.cat(metric.targets, self._cat_dim).to(self.device))
+                self.inputs.append(cat_all(metric.inputs, self._cat_dim).to(self.device))
+                self.targets.append(cat_all(metric.targets, self._cat_dim).to(self.device))
         return self
 
     @torch.inference_mode()

@@ -19,7 +19,7 @@ from ..functional.classification.auroc import (
     _multiclass_auroc_param_check,
     _multiclass_auroc_update_input_check,
 )
-from ..metric import Metric
+from ..metric import Metric, cat_all
 
 TAUROC = TypeVar("TAUROC")
 TMulticlassAUROC = TypeVar("TMulticlassAUROC")
@@ -41,8 +41,8 @@ def _resolve_weights(inputs: List[torch.Tensor], weights: List[torch.Tensor]) ->
             w if w.shape[-1] == i.shape[-1] else torch.ones_like(i, dtype=torch.double)
             for i, w in zip(inputs, weights)
         ]
-        return torch.cat(full, -1)
-    return torch.cat(weights, -1)
+        return cat_all(full, -1)
+    return cat_all(weights, -1)
 
 
 class BinaryAUROC(Metric[torch.Tensor]):
@@ -94,8 +94,8 @@ class BinaryAUROC(Metric[torch.Tensor]):
     def compute(self: TAUROC) -> torch.Tensor:
         # like the reference, compute() before any update() raises (torch.cat of an empty list)
         return _binary_auroc_compute(
-            torch.cat(self.inputs, -1),
-            torch.cat(self.targets, -1),
+            cat_all(self.inputs, -1),
+            cat_all(self.targets, -1),
             _resolve_weights(self.inputs, self.weights),
             self.use_fbgemm,
         )
@@ -105,9 +105,9 @@ class BinaryAUROC(Metric[torch.Tensor]):
         for metric in metrics:
             if metric.inputs:
                 w = _resolve_weights(metric.inputs, metric.weights)
-                metric_inputs = torch.cat(metric.inputs, -1).to(self.device)
+                metric_inputs = cat_all(metric.inputs, -1).to(self.device)
                 self.inputs.append(metric_inputs)
-                self.targets.append(torch.cat(metric.targets, -1).to(self.device))
+                self.targets.append(cat_all(metric.targets, -1).to(self.device))
                 self.weights.append(_empty_weight_like(metric_inputs) if w is None else w.to(self.device))
         return self
 
@@ -115,8 +115,8 @@ class BinaryAUROC(Metric[torch.Tensor]):
     def _prepare_for_merge_state(self: TAUROC) -> None:
         if self.inputs and self.targets:
             w = _resolve_weights(self.inputs, self.weights)
-            self.inputs = [torch.cat(self.inputs, -1)]
-            self.targets = [torch.cat(self.targets, -1)]
+            self.inputs = [cat_all(self.inputs, -1)]
+            self.targets = [cat_all(self.targets, -1)]
             self.weights = [_empty_weight_like(self.inputs[0]) if w is None else w]
 
 
@@ -149,19 +149,19 @@ class MulticlassAUROC(Metric[torch.Tensor]):
     @torch.inference_mode()
     def compute(self: TMulticlassAUROC) -> torch.Tensor:
         return _multiclass_auroc_compute(
-            torch.cat(self.inputs), torch.cat(self.targets), self.num_classes, self.average
+            cat_all(self.inputs), cat_all(self.targets), self.num_classes, self.average
         )
 
     @torch.inference_mode()
     def merge_state(self: TMulticlassAUROC, metrics: Iterable[TMulticlassAUROC]) -> TMulticlassAUROC:
         for metric in metrics:
             if metric.inputs:
-                self.inputs.append(torch.cat(metric.inputs).to(self.device))
-                self.targets.append(torch.cat(metric.targets).to(self.device))
+                self.inputs.append(cat_all(metric.inputs).to(self.device))
+                self.targets.append(cat_all(metric.targets).to(self.device))
         return self
 
     @torch.inference_mode()
     def _prepare_for_merge_state(self: TMulticlassAUROC) -> None:
         if self.inputs and self.targets:
-            self.inputs = [torch.cat(self.inputs)]
-            self.targets = [torch.cat(self.targets)]
+            self.inputs = [cat_all(self.inputs)]
+            self.targets = [cat_all(self.targets)]
