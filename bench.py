@@ -18,8 +18,9 @@ against closed forms on grid-valued scores.
 
 Prints ONE JSON line on rank 0 (see the task contract): value = device-timed whole-job
 throughput with inputs resident in HBM; e2e = same metric through the public functional API
-with pinned HOST tensors (H2D + D2H inside the timed region); roofline = dominant kernel
-(one radix pass), timed with CUDA events on the launching stream during the timed steps;
+with pinned HOST tensors (H2D + D2H inside the timed region); roofline = the dominant kernel of
+the step (a cursor partition pass at 1 GPU, the exchange's sender at 8), timed with CUDA events on
+the launching stream during the timed steps;
 cpu_baseline = the CPU port of the reference path (oracle/oracle_torch.py) on the host cores.
 """
 from __future__ import annotations
